@@ -1,0 +1,267 @@
+"""Host-side mirror of the reference's interface for the hot path, on top of the C-ABI (include/b3d.h).
+
+Names, argument meaning and error behaviour follow the reference (jonH34400/3DBodyAnimation):
+  AvatarModel / Avatar / Avatar.update        external/avatar/include/Avatar.h:64-220, Avatar.cpp:22-75
+  GaussianMixture                             external/avatar/include/GaussianMixture.h:9-49
+  PixelKP, Sim3Params, FramePoseParams        include/Sim3BA.h:9-19, include/MultiFrameBA.h:9-14
+  OptimizePoseReprojection                    include/Sim3BA.h:515-683
+  OptimizePoseShapeReprojection               include/Sim3BA.h:348-511
+  mean_pixel_error                            include/Utils.h:102-115
+plus the batched calls the GPU wants (smpl_forward, fit_single_batch).  Every computation goes through
+lib3dba_b200.so; there is no numpy/CPU fallback.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import numpy as np
+
+from . import _capi as capi
+from ._capi import F32, F64, FIT_POSE, FIT_POSE_SHAPE, ITER_DTYPE, KP_DTYPE, MAXKP, NJ, NPF, NS, check, lib, ptr
+
+# MediaPipe-33 -> SMPL-24 tables (include/Utils.h:18-23): bit-exact indexing outputs
+MP_MAP = np.array([-1, 23, 24, -1, 25, 26, -1, 27, 28, -1, 31, 32, -1, -1, -1, 0, 11, 12, 13, 14, 15, 16, -1, -1], dtype=np.int32)
+USE_SMPL = np.array([1, 2, 4, 5, 7, 8, 10, 11, 15, 16, 17, 18, 19, 20, 21, 0, 0], dtype=np.int32)
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def fit_opts(mode=FIT_POSE, max_iters=100, beta_pose=0.0, beta_shape=0.0, lambda_temp=0.0, cam=(432.0, 432.0, 240.0, 135.0),
+             huber=3.0, scale_bounds=(0.3, 3.0)) -> capi.FitOpts:
+    return capi.FitOpts(mode, max_iters, beta_pose, beta_shape, lambda_temp, cam[0], cam[1], cam[2], cam[3], huber,
+                        scale_bounds[0], scale_bounds[1])
+
+
+class AvatarModel:
+    """ark::AvatarModel: built from the arrays of SMPL's model.npz (a dict or an .npz path)."""
+
+    def __init__(self, model):
+        if isinstance(model, str):
+            with np.load(model) as z:
+                model = {k: z[k] for k in z.files}
+        self._keep = {}
+        dt = np.float64 if model["v_template"].dtype == np.float64 else np.float32
+        for k in ("v_template", "shapedirs", "J_regressor", "weights"):
+            self._keep[k] = np.ascontiguousarray(model[k], dtype=dt)
+        kt = np.ascontiguousarray(np.asarray(model["kintree_table"])[0].astype(np.uint32))
+        faces = np.ascontiguousarray(model["f"], dtype=np.uint32) if "f" in model else None
+        pd = np.ascontiguousarray(model["posedirs"], dtype=dt) if "posedirs" in model else None
+        self._keep.update(kt=kt, faces=faces, pd=pd)
+        v, j, s = self._keep["v_template"].shape[0], kt.shape[0], self._keep["shapedirs"].shape[2]
+        desc = capi.ModelDesc(v, j, s, 0 if faces is None else faces.shape[0], F64 if dt == np.float64 else F32, 0,
+                              ptr(self._keep["v_template"]), ptr(self._keep["shapedirs"]), ptr(self._keep["J_regressor"]),
+                              ptr(self._keep["weights"]), ptr(kt), ptr(faces), ptr(pd))
+        h = C.c_void_p()
+        check(lib().b3d_model_create(C.byref(desc), C.byref(h)), "b3d_model_create")
+        self.h = h
+        self.numPoints, self.numJoints, self.numShapeKeys = v, j, s
+        self.parent = np.zeros(NJ, dtype=np.int32)
+        check(lib().b3d_model_get_parents(self.h, ptr(self.parent)), "b3d_model_get_parents")
+        self.initialJointPos, self.jointShapeReg, self.offset = np.zeros((NJ, 3)), np.zeros((NJ, 3, NS)), np.zeros((NJ, 3))
+        check(lib().b3d_model_get_constants(self.h, ptr(self.initialJointPos), ptr(self.jointShapeReg), ptr(self.offset)),
+              "b3d_model_get_constants")
+        self.useJointShapeRegressor = True
+        self.posePrior = None      # GaussianMixture or None (AvatarModel.cpp:296 loads pose_prior.txt when present)
+
+    def __del__(self):
+        h = getattr(self, "h", None)
+        if h is not None and h.value:
+            lib().b3d_model_destroy(h)
+            self.h = None
+
+
+class GaussianMixture:
+    """ark::GaussianMixture.  nComps == -1 when the prior file is missing (GaussianMixture.cpp:15-19)."""
+
+    def __init__(self, path: str | None = None, prior: dict | None = None):
+        self.h = None
+        self.nComps = -1
+        self.nDims = 0
+        h = C.c_void_p()
+        if path is not None:
+            rc = lib().b3d_gmm_load(path.encode(), C.byref(h))
+            if rc == 4:      # B3D_ENOFILE: warn-and-continue, like the reference
+                return
+            check(rc, "b3d_gmm_load")
+        elif prior is not None:
+            check(lib().b3d_gmm_create(int(prior["nComps"]), int(prior["nDims"]), ptr(_f64(prior["weights"])),
+                                       ptr(_f64(prior["means"])), ptr(_f64(prior["covs"])), C.byref(h)), "b3d_gmm_create")
+        else:
+            return
+        self.h = h
+        nc, nd = C.c_int32(0), C.c_int32(0)
+        check(lib().b3d_gmm_dims(self.h, C.byref(nc), C.byref(nd)), "b3d_gmm_dims")
+        self.nComps, self.nDims = nc.value, nd.value
+
+    def arrays(self):
+        out = dict(prec_cho=np.zeros((self.nComps, self.nDims, self.nDims)), consts_log=np.zeros(self.nComps))
+        check(lib().b3d_gmm_get(self.h, ptr(out["prec_cho"]), ptr(out["consts_log"])), "b3d_gmm_get")
+        return out
+
+    def residual(self, x):
+        """GaussianMixture::residual for one (69,) or a batch (B, 69) of poses; returns (out (B,70), comp (B,))."""
+        x = np.atleast_2d(_f64(x))
+        out, comp = np.zeros((x.shape[0], self.nDims + 1)), np.zeros(x.shape[0], dtype=np.int32)
+        check(lib().b3d_gmm_residual(self.h, x.shape[0], ptr(x), ptr(out), ptr(comp)), "b3d_gmm_residual")
+        return out, comp
+
+    def __del__(self):
+        h = getattr(self, "h", None)
+        if h is not None and h.value:
+            lib().b3d_gmm_destroy(h)
+            self.h = None
+
+
+def _gmm_handle(gmm):
+    return gmm.h if (gmm is not None and gmm.h is not None and gmm.nComps > 0) else None
+
+
+# ---------------------------------------------------------------------------------------------------------
+# batched calls
+# ---------------------------------------------------------------------------------------------------------
+def smpl_forward(model: AvatarModel, w, p, r, dtype=np.float64, posedirs=False, want_cloud=True):
+    """Batched Avatar::update.  w (B,10), p (B,3), r (B,24,9 col-major).  Returns cloud (B,V,3), jointPos (B,24,3),
+    jointTrans (B,24,12) in ``dtype`` (float32 or float64)."""
+    dt = np.dtype(dtype)
+    code = F64 if dt == np.float64 else F32
+    w = np.ascontiguousarray(w, dtype=dt).reshape(-1, NS)
+    b = w.shape[0]
+    p = np.ascontiguousarray(p, dtype=dt).reshape(b, 3)
+    r = np.ascontiguousarray(r, dtype=dt).reshape(b, NJ, 9)
+    cloud = np.empty((b, model.numPoints, 3), dtype=dt) if want_cloud else None
+    jp, jt = np.empty((b, NJ, 3), dtype=dt), np.empty((b, NJ, 12), dtype=dt)
+    check(lib().b3d_smpl_forward(model.h, b, code, ptr(w), ptr(p), ptr(r), ptr(cloud), ptr(jp), ptr(jt), 1 if posedirs else 0),
+          "b3d_smpl_forward")
+    return cloud, jp, jt
+
+
+def fit_single_batch(model: AvatarModel, gmm, opts: capi.FitOpts, kps, nkp, R0, sim3, w, want_trace=True):
+    """B independent single-frame fits (frame loop of src/main_single_frame.cpp:192-249)."""
+    kps = np.ascontiguousarray(kps, dtype=KP_DTYPE).reshape(-1, MAXKP)
+    b = kps.shape[0]
+    nkp = np.ascontiguousarray(nkp, dtype=np.int32).reshape(b)
+    R0, sim3, w = _f64(R0).reshape(b, 9), _f64(sim3).reshape(b, 7).copy(), _f64(w).reshape(b, NS).copy()
+    jaa = np.zeros((b, NJ, 3))
+    usable = np.zeros(b, dtype=np.uint8)
+    stride = opts.max_iters + 2
+    trace = np.zeros((b, stride), dtype=ITER_DTYPE) if want_trace else None
+    niters, term = np.zeros(b, dtype=np.int32), np.zeros(b, dtype=np.int32)
+    check(lib().b3d_fit_single(model.h, _gmm_handle(gmm), C.byref(opts), b, ptr(kps), ptr(nkp), ptr(R0), ptr(sim3), ptr(w),
+                               ptr(jaa), ptr(usable), ptr(trace), stride, ptr(niters), ptr(term)), "b3d_fit_single")
+    return dict(sim3=sim3, w=w, jointAA=jaa, usable=usable, trace=trace, niters=niters, term=term)
+
+
+def writeback(poses, R0):
+    """a15: R0 <- R(rootAA) R0; r[0] = R0, r[j] = R(jointAA_j); p = rootT.  poses (F,76), R0 (F,9)."""
+    poses = _f64(poses).reshape(-1, NPF)
+    f = poses.shape[0]
+    R0 = _f64(R0).reshape(f, 9).copy()
+    r, p = np.zeros((f, NJ, 9)), np.zeros((f, 3))
+    check(lib().b3d_writeback(f, ptr(poses), ptr(R0), ptr(r), ptr(p)), "b3d_writeback")
+    return R0, r, p
+
+
+def mean_pixel_error_batch(kps, nkp, jointPos, cam):
+    kps = np.ascontiguousarray(kps, dtype=KP_DTYPE).reshape(-1, MAXKP)
+    f = kps.shape[0]
+    nkp = np.ascontiguousarray(nkp, dtype=np.int32).reshape(f)
+    jp = _f64(jointPos).reshape(f, NJ, 3)
+    err = np.zeros(f)
+    check(lib().b3d_mean_pixel_error(f, ptr(kps), ptr(nkp), ptr(jp), C.c_double(cam[0]), C.c_double(cam[1]), C.c_double(cam[2]),
+                                     C.c_double(cam[3]), ptr(err)), "b3d_mean_pixel_error")
+    return err
+
+
+# ---------------------------------------------------------------------------------------------------------
+# the reference's per-object interface
+# ---------------------------------------------------------------------------------------------------------
+@dataclass
+class PixelKP:           # include/Sim3BA.h:9
+    jid: int
+    u: float
+    v: float
+
+
+@dataclass
+class Sim3Params:        # include/Sim3BA.h:11-19: data = [s, aa(3), t(3)]
+    data: np.ndarray = field(default_factory=lambda: np.array([1.0, 0, 0, 0, 0, 0, 0], dtype=np.float64))
+
+
+@dataclass
+class FramePoseParams:   # include/MultiFrameBA.h:9-14
+    scale: float = 1.0
+    rootAA: np.ndarray = field(default_factory=lambda: np.zeros(3))
+    rootT: np.ndarray = field(default_factory=lambda: np.zeros(3))
+    jointAA: np.ndarray = field(default_factory=lambda: np.zeros((NJ, 3)))
+
+    def pack(self) -> np.ndarray:
+        return np.concatenate([[self.scale], self.rootAA, self.rootT, np.asarray(self.jointAA)[1:].ravel()])
+
+    def unpack(self, v):
+        self.scale, self.rootAA, self.rootT = float(v[0]), np.array(v[1:4]), np.array(v[4:7])
+        self.jointAA = np.vstack([np.zeros((1, 3)), np.asarray(v[7:76]).reshape(NJ - 1, 3)])
+
+
+class Avatar:
+    """ark::Avatar: public w, p, r in; cloud, jointPos, jointTrans out of update() (Avatar.h:191-219)."""
+
+    def __init__(self, model: AvatarModel):
+        self.model = model
+        self.w = np.zeros(NS)
+        self.p = np.zeros(3)
+        self.r = np.tile(np.eye(3).reshape(9), (NJ, 1))     # col-major 3x3 per joint (identity either way)
+        self.cloud = np.zeros((model.numPoints, 3))
+        self.jointPos = np.zeros((NJ, 3))
+        self.jointTrans = np.zeros((NJ, 12))
+
+    def update(self):
+        c, jp, jt = smpl_forward(self.model, self.w[None], self.p[None], self.r[None], dtype=np.float64)
+        self.cloud, self.jointPos, self.jointTrans = c[0], jp[0], jt[0]
+
+
+def _kp_array(kps):
+    arr = np.zeros((1, MAXKP), dtype=KP_DTYPE)
+    if len(kps) > MAXKP:
+        raise ValueError(f"at most {MAXKP} keypoints per frame")
+    for i, k in enumerate(kps):
+        arr[0, i] = (k.jid, 0, k.u, k.v)
+    return arr, np.array([len(kps)], dtype=np.int32)
+
+
+def _optimize_single(mode, model, avatar, kps, fx, fy, cx, cy, valid_joint_ids, initSim3, max_iters, betaPose, betaShape, gmm):
+    valid = set(int(j) for j in valid_joint_ids)
+    if valid:                                            # Sim3BA.h:410-413: a non-empty list filters, an empty one does not
+        kps = [k for k in kps if k.jid in valid]
+    arr, nkp = _kp_array(kps)
+    o = fit_opts(mode, max_iters, betaPose, betaShape, 0.0, (fx, fy, cx, cy))
+    res = fit_single_batch(model, gmm, o, arr, nkp, avatar.r[0][None], initSim3.data[None], avatar.w[None])
+    # write-back (Sim3BA.h:481-507 / 649-679)
+    pose = np.concatenate([res["sim3"][0], res["jointAA"][0, 1:].ravel()])
+    R0, r, p = writeback(pose[None], avatar.r[0][None])
+    avatar.r = r[0].copy()
+    avatar.p = p[0].copy()
+    avatar.w = res["w"][0].copy()
+    initSim3.data = res["sim3"][0].copy()
+    report = f"iterations {int(res['niters'][0])}, termination {int(res['term'][0])}, final cost {res['trace'][0]['cost'][max(int(res['niters'][0]) - 1, 0)]:.6e}"
+    return bool(res["usable"][0]), report
+
+
+def OptimizePoseReprojection(model, avatar, kps, fx, fy, cx, cy, valid_joint_ids, initSim3, max_iters=100, betaPose=0.0,
+                             betaShape=0.0, gmm=None):
+    """include/Sim3BA.h:515-525.  Returns (IsSolutionUsable, report)."""
+    return _optimize_single(FIT_POSE, model, avatar, kps, fx, fy, cx, cy, valid_joint_ids, initSim3, max_iters, betaPose, betaShape, gmm)
+
+
+def OptimizePoseShapeReprojection(model, avatar, kps, fx, fy, cx, cy, valid_joint_ids, initSim3, max_iters=100, betaPose=0.0,
+                                  betaShape=0.0, gmm=None):
+    """include/Sim3BA.h:348-358.  Returns (IsSolutionUsable, report)."""
+    return _optimize_single(FIT_POSE_SHAPE, model, avatar, kps, fx, fy, cx, cy, valid_joint_ids, initSim3, max_iters, betaPose, betaShape, gmm)
+
+
+def mean_pixel_error(kps, avatar: Avatar, fx, fy, cx, cy) -> float:
+    """include/Utils.h:102-115 (uses the avatar's posed joints: scale is not applied)."""
+    arr, nkp = _kp_array(kps)
+    return float(mean_pixel_error_batch(arr, nkp, avatar.jointPos[None], (fx, fy, cx, cy))[0])

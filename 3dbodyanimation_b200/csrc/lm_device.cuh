@@ -1,0 +1,286 @@
+// Device-side building blocks shared by the single-frame and window LM kernels.
+//
+// Residual model (reference: include/Sim3BA.h:34-88 ReprojCost, :126-227 ReprojCostShape; analytic Jacobians replace
+// ceres::DynamicAutoDiffCostFunction, whose Jets give the exact derivative of the same expressions):
+//   chain of keypoint joint jid:  a_0 = jid, a_i = parent(a_{i-1}) while that parent is neither -1 nor 0
+//   q_0 = bone(a_0);  q_i = Rot(aa_{a_i}) q_{i-1} + bone(a_i);  pc = R0 q_d;  X' = Rot(rootAA) pc;  X = s X' + t
+//   bone(j) = offset_j + (JSR_j - JSR_parent(j)) w          (shape term only when the functor was given jointShapeReg)
+//   r = (fx X0/X2 + cx - u, fy X1/X2 + cy - v),  robustified by Huber(a) via the Corrector's sqrt(rho') scaling.
+// Rot follows ceres::AngleAxisRotatePoint: Rodrigues for theta^2 > DBL_EPSILON, first-order p + aa x p otherwise.
+#pragma once
+#include <cfloat>
+
+#include "internal.hpp"
+
+namespace b3d {
+
+constexpr int MAXCHAIN = 8;                    // a_0 .. a_7 (hands have 7 strict non-root ancestors)
+constexpr int MAXNNZ = 7 + 3 * (MAXCHAIN - 1) + NS;   // 38 non-zero Jacobian columns per keypoint row pair
+constexpr int NNZPAD = 40;
+
+// Launch-constant data of a fit, built on the host, read-only on the device.
+struct FitConst {
+    int32_t parent[NJ];
+    int32_t chain_len[NJ];                 // d + 1
+    int32_t chain[NJ][MAXCHAIN];           // a_0 .. a_d
+    double offset[NJ][3];
+    double DB[NJ][3][NS];                  // d bone / d w; all zero when the shape term is off
+    double cam[4];                         // fx fy cx cy
+    double huber, beta_pose, beta_shape, lambda_temp, scale_lo, scale_hi;
+    int32_t mode, max_iters, with_shape, has_w, use_gmm, n;   // n = number of free parameters
+    int32_t free_idx[NFULL];               // free -> full (86-layout)
+    int32_t col_of[NFULL];                 // full -> free, -1 = held constant
+    int32_t gmm_ncomp, pad;
+    const double* gmm_mean;                // ncomp x 69
+    const double* gmm_L;                   // ncomp x 69 x 69, lower, row-major  (prec_cho)
+    const double* gmm_LT;                  // ncomp x 69 x 69, = L^T row-major
+    const double* gmm_P;                   // ncomp x 69 x 69, = L L^T
+    const double* gmm_consts;              // ncomp
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// rotations
+// ---------------------------------------------------------------------------------------------------------------
+// R (row-major 3x3) of ceres::AngleAxisRotatePoint(aa, .), and optionally dR[k] = dR/daa_k (3 row-major 3x3).
+template <bool JAC>
+__device__ __forceinline__ void aa_rotation(const double* aa, double* R, double* dR) {
+    const double a0 = aa[0], a1 = aa[1], a2 = aa[2];
+    const double th2 = a0 * a0 + a1 * a1 + a2 * a2;
+    if (th2 > DBL_EPSILON) {
+        const double th = sqrt(th2), ti = 1.0 / th;
+        double s, c;
+        sincos(th, &s, &c);
+        const double w[3] = {a0 * ti, a1 * ti, a2 * ti};
+        const double oc = 1.0 - c;
+        R[0] = c + oc * w[0] * w[0];         R[1] = -s * w[2] + oc * w[0] * w[1];  R[2] = s * w[1] + oc * w[0] * w[2];
+        R[3] = s * w[2] + oc * w[1] * w[0];  R[4] = c + oc * w[1] * w[1];          R[5] = -s * w[0] + oc * w[1] * w[2];
+        R[6] = -s * w[1] + oc * w[2] * w[0]; R[7] = s * w[0] + oc * w[2] * w[1];   R[8] = c + oc * w[2] * w[2];
+        if (JAC) {
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const double wk = w[k];
+                // dw = (e_k - w w_k) / theta
+                double dw[3];
+#pragma unroll
+                for (int i = 0; i < 3; ++i) dw[i] = ((i == k ? 1.0 : 0.0) - w[i] * wk) * ti;
+                double* D = dR + 9 * k;
+                const double cs = c * wk, sw = s * wk;
+                // d/daa_k [ c I + s [w]x + (1-c) w w^T ]
+#pragma unroll
+                for (int i = 0; i < 3; ++i)
+#pragma unroll
+                    for (int j = 0; j < 3; ++j)
+                        D[3 * i + j] = (i == j ? -sw : 0.0) + sw * w[i] * w[j] + oc * (dw[i] * w[j] + w[i] * dw[j]);
+                // + c w_k [w]x + s [dw]x
+                const double x0 = cs * w[0] + s * dw[0], x1 = cs * w[1] + s * dw[1], x2 = cs * w[2] + s * dw[2];
+                D[1] -= x2; D[2] += x1; D[3] += x2; D[5] -= x0; D[6] -= x1; D[7] += x0;
+            }
+        }
+    } else {
+        R[0] = 1.0; R[1] = -a2; R[2] = a1;
+        R[3] = a2;  R[4] = 1.0; R[5] = -a0;
+        R[6] = -a1; R[7] = a0;  R[8] = 1.0;
+        if (JAC) {
+#pragma unroll
+            for (int i = 0; i < 27; ++i) dR[i] = 0.0;
+            // d(p + aa x p)/daa_k = e_k x p  =>  dR_k = [e_k]x
+            dR[5] = -1.0; dR[7] = 1.0;            // k = 0
+            dR[9 + 2] = 1.0; dR[9 + 6] = -1.0;    // k = 1
+            dR[18 + 1] = -1.0; dR[18 + 3] = 1.0;  // k = 2
+        }
+    }
+}
+
+__device__ __forceinline__ void mat3_vec(const double* M, const double* v, double* o) {
+    const double x = v[0], y = v[1], z = v[2];
+    o[0] = M[0] * x + M[1] * y + M[2] * z;
+    o[1] = M[3] * x + M[4] * y + M[5] * z;
+    o[2] = M[6] * x + M[7] * y + M[8] * z;
+}
+
+// N (2x3 row-major) <- N * M (3x3 row-major)
+__device__ __forceinline__ void n23_mul(const double* N, const double* M, double* o) {
+#pragma unroll
+    for (int r = 0; r < 2; ++r)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) o[3 * r + c] = N[3 * r] * M[c] + N[3 * r + 1] * M[3 + c] + N[3 * r + 2] * M[6 + c];
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// block-wide sum in a fixed order (deterministic): every thread gets the result.  red: >= 33 doubles of shared memory.
+// ---------------------------------------------------------------------------------------------------------------
+template <int T>
+__device__ __forceinline__ double block_sum(double v, double* red) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    __syncthreads();   // red may still be read from a previous call
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    double s = 0.0;
+#pragma unroll
+    for (int i = 0; i < T / 32; ++i) s += red[i];
+    return s;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// per-frame evaluation scratch (shared memory)
+// ---------------------------------------------------------------------------------------------------------------
+// temporaries of one evaluation: dead once eval_reproj returns, so callers may alias them with other storage
+struct EvalTmp {
+    double R[NJ][9];              // R[0] = Rot(rootAA), R[j] = Rot(jointAA_j)
+    double dR[NJ][27];            // derivative matrices (JAC only)
+    double bone[NJ][3];
+    double q[MAXKP][MAXCHAIN][3]; // chain positions q_0 .. q_d
+    double pc[MAXKP][3];          // R0 q_d
+    double Xp[MAXKP][3];          // Rot(rootAA) pc
+    double N[MAXKP][MAXCHAIN + 1][6];   // N[.][0] = d r / d X (2x3); N[.][1 + i] = d r / d q_i
+};
+// results of one evaluation
+struct EvalOut {
+    double res[MAXKP][2];         // robustified residuals
+    double kcost[MAXKP];          // rho/2 per keypoint
+    double J[MAXKP][2][NNZPAD];   // robustified Jacobian entries, local column slots (JAC only)
+    int32_t jcol[MAXKP][NNZPAD];  // full-layout column of each slot
+    int32_t jnnz[MAXKP];
+};
+
+// Evaluate all reprojection blocks of one frame.  x: 86-layout parameters in shared memory.  All T threads call this.
+// After return (and a __syncthreads inside), O.res / O.kcost are valid; with JAC also O.J / O.jcol / O.jnnz.
+template <int T, bool JAC>
+__device__ void eval_reproj(const FitConst* __restrict__ C, const double* x, const b3d_kp* __restrict__ kps, int nkp,
+                            const double* R0 /*col-major 3x3, shared or global*/, EvalTmp& S, EvalOut& O) {
+    const int tid = threadIdx.x;
+    // phase A: joint rotations (24 tasks) and bone vectors (72 tasks)
+    for (int t = tid; t < NJ + 3 * NJ; t += T) {
+        if (t < NJ) {
+            const double* aa = t == 0 ? x + IDX_RAA : x + IDX_JAA + 3 * (t - 1);
+            aa_rotation<JAC>(aa, S.R[t], S.dR[t]);
+        } else {
+            const int j = (t - NJ) / 3, c = (t - NJ) % 3;
+            double b = C->offset[j][c];
+            if (C->with_shape) {
+#pragma unroll
+                for (int s = 0; s < NS; ++s) b += C->DB[j][c][s] * x[IDX_W + s];
+            }
+            S.bone[j][c] = b;
+        }
+    }
+    __syncthreads();
+    // phase B1: one thread per keypoint — forward chain, residual, Huber, row-vector back-propagation
+    if (tid < nkp) {
+        const int k = tid;
+        const int jid = kps[k].jid;
+        const int len = C->chain_len[jid];
+        double q[3] = {S.bone[jid][0], S.bone[jid][1], S.bone[jid][2]};
+        S.q[k][0][0] = q[0]; S.q[k][0][1] = q[1]; S.q[k][0][2] = q[2];
+        for (int i = 1; i < len; ++i) {
+            const int a = C->chain[jid][i];
+            double o[3];
+            mat3_vec(S.R[a], q, o);
+            q[0] = o[0] + S.bone[a][0]; q[1] = o[1] + S.bone[a][1]; q[2] = o[2] + S.bone[a][2];
+            S.q[k][i][0] = q[0]; S.q[k][i][1] = q[1]; S.q[k][i][2] = q[2];
+        }
+        double pc[3], Xp[3];
+#pragma unroll
+        for (int r = 0; r < 3; ++r) pc[r] = R0[r] * q[0] + R0[3 + r] * q[1] + R0[6 + r] * q[2];
+        mat3_vec(S.R[0], pc, Xp);
+        const double s = x[IDX_S];
+        const double X0 = s * Xp[0] + x[IDX_T], X1 = s * Xp[1] + x[IDX_T + 1], X2 = s * Xp[2] + x[IDX_T + 2];
+        const double iz = 1.0 / X2;
+        double r0 = C->cam[0] * X0 * iz + C->cam[2] - kps[k].u;
+        double r1 = C->cam[1] * X1 * iz + C->cam[3] - kps[k].v;
+        // HuberLoss(a) + Corrector (rho'' <= 0 branch)
+        const double sq = r0 * r0 + r1 * r1, b = C->huber * C->huber;
+        double rho0, rho1;
+        if (sq > b) { const double rr = sqrt(sq); rho0 = 2.0 * C->huber * rr - b; rho1 = fmax(DBL_MIN, C->huber / rr); }
+        else { rho0 = sq; rho1 = 1.0; }
+        const double sc = sqrt(rho1);
+        O.res[k][0] = r0 * sc; O.res[k][1] = r1 * sc;
+        O.kcost[k] = 0.5 * rho0;
+        if (JAC) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) { S.pc[k][c] = pc[c]; S.Xp[k][c] = Xp[c]; }
+            double N[6];
+            N[0] = sc * C->cam[0] * iz; N[1] = 0.0;                  N[2] = -sc * C->cam[0] * X0 * iz * iz;
+            N[3] = 0.0;                 N[4] = sc * C->cam[1] * iz;  N[5] = -sc * C->cam[1] * X1 * iz * iz;
+#pragma unroll
+            for (int e = 0; e < 6; ++e) S.N[k][0][e] = N[e];
+            // d r / d q_d = s N Rot(rootAA) R0
+            double A[6], Bm[6];
+            n23_mul(N, S.R[0], A);
+            const double R0rm[9] = {R0[0], R0[3], R0[6], R0[1], R0[4], R0[7], R0[2], R0[5], R0[8]};
+            n23_mul(A, R0rm, Bm);
+#pragma unroll
+            for (int e = 0; e < 6; ++e) Bm[e] *= s;
+            // S.N[k][1 + i] = d r / d q_i
+            for (int i = len - 1; i >= 0; --i) {
+#pragma unroll
+                for (int e = 0; e < 6; ++e) S.N[k][1 + i][e] = Bm[e];
+                if (i > 0) {
+                    n23_mul(Bm, S.R[C->chain[jid][i]], A);
+#pragma unroll
+                    for (int e = 0; e < 6; ++e) Bm[e] = A[e];
+                }
+            }
+            O.jnnz[k] = 7 + 3 * (len - 1) + (C->with_shape ? NS : 0);
+        }
+    }
+    __syncthreads();
+    if (!JAC) return;
+    // phase B2: one task per (keypoint, non-zero column)
+    for (int t = tid; t < nkp * NNZPAD; t += T) {
+        const int k = t / NNZPAD, slot = t % NNZPAD;
+        const int jid = kps[k].jid;
+        const int len = C->chain_len[jid];
+        const int naa = 3 * (len - 1);
+        if (slot >= 7 + naa + (C->with_shape ? NS : 0)) continue;
+        const double* N0 = S.N[k][0];
+        double j0, j1;
+        int col;
+        if (slot == 0) {                     // scale
+            j0 = N0[0] * S.Xp[k][0] + N0[1] * S.Xp[k][1] + N0[2] * S.Xp[k][2];
+            j1 = N0[3] * S.Xp[k][0] + N0[4] * S.Xp[k][1] + N0[5] * S.Xp[k][2];
+            col = IDX_S;
+        } else if (slot < 4) {               // root axis-angle
+            double dv[3];
+            mat3_vec(S.dR[0] + 9 * (slot - 1), S.pc[k], dv);
+            const double s = x[IDX_S];
+            j0 = s * (N0[0] * dv[0] + N0[1] * dv[1] + N0[2] * dv[2]);
+            j1 = s * (N0[3] * dv[0] + N0[4] * dv[1] + N0[5] * dv[2]);
+            col = IDX_RAA + slot - 1;
+        } else if (slot < 7) {               // translation
+            j0 = N0[slot - 4]; j1 = N0[3 + slot - 4];
+            col = IDX_T + slot - 4;
+        } else if (slot < 7 + naa) {         // axis-angle of chain ancestor a_i, i = 1..d
+            const int i = (slot - 7) / 3 + 1, kk = (slot - 7) % 3;
+            const int a = C->chain[jid][i];
+            double dv[3];
+            mat3_vec(S.dR[a] + 9 * kk, S.q[k][i - 1], dv);
+            const double* Ni = S.N[k][1 + i];
+            j0 = Ni[0] * dv[0] + Ni[1] * dv[1] + Ni[2] * dv[2];
+            j1 = Ni[3] * dv[0] + Ni[4] * dv[1] + Ni[5] * dv[2];
+            col = IDX_JAA + 3 * (a - 1) + kk;
+        } else {                             // shape key
+            const int s = slot - 7 - naa;
+            j0 = 0.0; j1 = 0.0;
+            for (int i = 0; i < len; ++i) {
+                const int a = C->chain[jid][i];
+                const double* Ni = S.N[k][1 + i];
+                const double d0 = C->DB[a][0][s], d1 = C->DB[a][1][s], d2 = C->DB[a][2][s];
+                j0 += Ni[0] * d0 + Ni[1] * d1 + Ni[2] * d2;
+                j1 += Ni[3] * d0 + Ni[4] * d1 + Ni[5] * d2;
+            }
+            col = IDX_W + s;
+        }
+        O.J[k][0][slot] = j0;
+        O.J[k][1][slot] = j1;
+        O.jcol[k][slot] = col;
+    }
+    __syncthreads();
+}
+
+// packed lower-triangular index, i >= j
+__device__ __forceinline__ int tri(int i, int j) { return i * (i + 1) / 2 + j; }
+
+}  // namespace b3d

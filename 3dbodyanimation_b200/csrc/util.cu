@@ -1,0 +1,130 @@
+// Small per-frame kernels around the solves: the AA -> rotation write-back (include/Sim3BA.h:481-507, 649-679;
+// include/MultiFrameBA.h:154-172) and mean_pixel_error (include/Utils.h:102-115).
+#include "internal.hpp"
+
+namespace b3d {
+
+// Eigen::AngleAxisd(theta, aa/theta).toRotationMatrix() for theta > 1e-12, identity otherwise (Sim3BA.h:483-489). Col-major out.
+__device__ __forceinline__ void aa_to_matrix_cm(const double* aa, double* R) {
+    const double th = sqrt(aa[0] * aa[0] + aa[1] * aa[1] + aa[2] * aa[2]);
+    if (th > 1e-12) {
+        const double x = aa[0] / th, y = aa[1] / th, z = aa[2] / th;
+        double s, c;
+        sincos(th, &s, &c);
+        const double t = 1.0 - c;
+        R[0] = t * x * x + c;     R[3] = t * x * y - s * z; R[6] = t * x * z + s * y;
+        R[1] = t * x * y + s * z; R[4] = t * y * y + c;     R[7] = t * y * z - s * x;
+        R[2] = t * x * z - s * y; R[5] = t * y * z + s * x; R[8] = t * z * z + c;
+    } else {
+        R[0] = 1; R[1] = 0; R[2] = 0; R[3] = 0; R[4] = 1; R[5] = 0; R[6] = 0; R[7] = 0; R[8] = 1;
+    }
+}
+
+// one thread per (frame, joint)
+__global__ void writeback_kernel(int F, const double* __restrict__ poses, double* __restrict__ R0, double* __restrict__ r,
+                                 double* __restrict__ p) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= F * NJ) return;
+    const int f = t / NJ, j = t % NJ;
+    const double* pose = poses + (size_t)f * NPF;
+    double R[9];
+    if (j == 0) {
+        double Rr[9], A[9];
+        aa_to_matrix_cm(pose + IDX_RAA, Rr);
+#pragma unroll
+        for (int k = 0; k < 9; ++k) A[k] = R0[(size_t)f * 9 + k];
+        // r[0] <- R(rootAA) * r[0]  (col-major product)
+#pragma unroll
+        for (int col = 0; col < 3; ++col)
+#pragma unroll
+            for (int row = 0; row < 3; ++row)
+                R[3 * col + row] = Rr[row] * A[3 * col] + Rr[3 + row] * A[3 * col + 1] + Rr[6 + row] * A[3 * col + 2];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) R0[(size_t)f * 9 + k] = R[k];
+        if (p) { p[(size_t)f * 3] = pose[IDX_T]; p[(size_t)f * 3 + 1] = pose[IDX_T + 1]; p[(size_t)f * 3 + 2] = pose[IDX_T + 2]; }
+    } else {
+        aa_to_matrix_cm(pose + IDX_JAA + 3 * (j - 1), R);
+    }
+    if (r) {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) r[((size_t)f * NJ + j) * 9 + k] = R[k];
+    }
+}
+
+__global__ void pixel_error_kernel(int F, const b3d_kp* __restrict__ kps, const int32_t* __restrict__ nkp,
+                                   const double* __restrict__ jointPos, double fx, double fy, double cx, double cy,
+                                   double* __restrict__ err) {
+    const int f = blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= F) return;
+    const int n = min(max(nkp[f], 0), MAXKP);
+    double sum = 0.0;
+    for (int k = 0; k < n; ++k) {
+        const b3d_kp kp = kps[(size_t)f * MAXKP + k];
+        const double* J = jointPos + ((size_t)f * NJ + kp.jid) * 3;
+        const double u = fx * J[0] / J[2] + cx, v = fy * J[1] / J[2] + cy;
+        sum += hypot(u - kp.u, v - kp.v);
+    }
+    err[f] = n > 0 ? sum / n : 0.0;
+}
+
+}  // namespace b3d
+
+using namespace b3d;
+
+extern "C" {
+
+int b3d_writeback_dev(int32_t F, const double* poses, double* R0, double* r, double* p, void* stream) {
+    if (!poses || !R0) return set_error(B3D_EINVAL, "b3d_writeback: null argument");
+    if (F <= 0) return F < 0 ? set_error(B3D_EINVAL, "b3d_writeback: F < 0") : B3D_OK;
+    const int n = F * NJ;
+    writeback_kernel<<<(n + 127) / 128, 128, 0, (cudaStream_t)stream>>>(F, poses, R0, r, p);
+    B3D_LAUNCH_CHECK();
+    return B3D_OK;
+}
+
+int b3d_writeback(int32_t F, const double* poses, double* R0, double* r, double* p) {
+    if (!poses || !R0) return set_error(B3D_EINVAL, "b3d_writeback: null argument");
+    if (F <= 0) return F < 0 ? set_error(B3D_EINVAL, "b3d_writeback: F < 0") : B3D_OK;
+    const size_t nf = (size_t)F;
+    double *dp = nullptr;
+    B3D_CUDA(cudaMalloc(&dp, 8 * nf * (NPF + 9 + NJ * 9 + 3)));
+    double *dR0 = dp + nf * NPF, *dr = dR0 + nf * 9, *dpp = dr + nf * NJ * 9;
+    cudaError_t e = cudaMemcpy(dp, poses, 8 * nf * NPF, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(dR0, R0, 8 * nf * 9, cudaMemcpyHostToDevice);
+    int rc = B3D_OK;
+    if (e == cudaSuccess) rc = b3d_writeback_dev(F, dp, dR0, dr, dpp, nullptr);
+    if (e == cudaSuccess && !rc) {
+        e = cudaStreamSynchronize(nullptr);
+        if (e == cudaSuccess) e = cudaMemcpy(R0, dR0, 8 * nf * 9, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess && r) e = cudaMemcpy(r, dr, 8 * nf * NJ * 9, cudaMemcpyDeviceToHost);
+        if (e == cudaSuccess && p) e = cudaMemcpy(p, dpp, 8 * nf * 3, cudaMemcpyDeviceToHost);
+    }
+    cudaFree(dp);
+    if (e != cudaSuccess) return set_error(B3D_ECUDA, "b3d_writeback: %s", cudaGetErrorString(e));
+    return rc;
+}
+
+int b3d_mean_pixel_error(int32_t F, const b3d_kp* kps, const int32_t* nkp, const double* jointPos, double fx, double fy, double cx,
+                         double cy, double* err) {
+    if (!kps || !nkp || !jointPos || !err) return set_error(B3D_EINVAL, "b3d_mean_pixel_error: null argument");
+    if (F <= 0) return F < 0 ? set_error(B3D_EINVAL, "b3d_mean_pixel_error: F < 0") : B3D_OK;
+    const size_t nf = (size_t)F;
+    char* base = nullptr;
+    const size_t s_kp = sizeof(b3d_kp) * nf * MAXKP, s_jp = 8 * nf * NJ * 3, s_nk = (4 * nf + 7) / 8 * 8;
+    B3D_CUDA(cudaMalloc(&base, s_kp + s_jp + 8 * nf + s_nk));
+    b3d_kp* dk = (b3d_kp*)base; double* dj = (double*)(base + s_kp); double* de = dj + nf * NJ * 3; int32_t* dn = (int32_t*)(de + nf);
+    cudaError_t e = cudaMemcpy(dk, kps, s_kp, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(dj, jointPos, s_jp, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(dn, nkp, 4 * nf, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        pixel_error_kernel<<<(F + 127) / 128, 128>>>(F, dk, dn, dj, fx, fy, cx, cy, de);
+        count_launch();
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(err, de, 8 * nf, cudaMemcpyDeviceToHost);
+    cudaFree(base);
+    if (e != cudaSuccess) return set_error(B3D_ECUDA, "b3d_mean_pixel_error: %s", cudaGetErrorString(e));
+    return B3D_OK;
+}
+
+}  // extern "C"

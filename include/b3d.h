@@ -1,0 +1,192 @@
+/* b3d.h — C-ABI of lib3dba_b200.so: the B200-native replacement for the per-frame SMPL fitting hot path of
+ * jonH34400/3DBodyAnimation (reference @ eb48afe).  Plain pointers and sizes only; no C++/torch types.
+ *
+ * The reference has no FFI layer of its own: its boundary is three inline C++ functions plus the public fields of
+ * ark::Avatar / ark::AvatarModel.  Every entry point below names the reference interface it
+ * replaces (paths relative to the reference root).  include/b3d_shim.hpp offers the reference's own C++ signatures
+ * on top of this header; INTEGRATION.md shows the binding a maintainer would add.
+ *
+ * Conventions
+ *   - All fitting arithmetic is float64, as in the reference (Eigen double / ceres::Jet<double,4>).
+ *   - 3x3 rotations are column-major (Eigen default): R[3*col + row].  jointTrans columns are col-major 3x4 [R|t].
+ *   - Per-frame parameter vector ("pose", 76 doubles): [scale, rootAA(3), rootT(3), jointAA[1..23](69)]
+ *     (FramePoseParams, include/MultiFrameBA.h:9-14; Sim3Params = first 7, include/Sim3BA.h:11-19).
+ *   - Functions without a suffix take HOST pointers, copy in/out, and return when the result is in host memory.
+ *     Functions ending in _dev take DEVICE pointers, enqueue on `stream` (a cudaStream_t passed as void*) and
+ *     return without synchronising.
+ *   - The library uses the calling thread's current CUDA device.  Handles belong to the device they were created on.
+ *   - There is no CPU fallback: every entry point fails with B3D_ECUDA when no sm_100 device is usable.
+ */
+#ifndef B3D_H_
+#define B3D_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B3D_NUM_JOINTS 24      /* SMPL joints (external/avatar/include/Avatar.h:27-59) */
+#define B3D_NUM_SHAPE 10       /* shape keys */
+#define B3D_POSE_DIM 76        /* per-frame parameters */
+#define B3D_MAX_KP 17          /* USE_SMPL has 17 slots (include/Utils.h:22-23) */
+#define B3D_POSEDIRS_DIM 207   /* optional pose blendshapes, 23*9 (NOT in the reference, AvatarModel.cpp:104-109) */
+
+/* ---- status codes (reference: bool + std::exit / throw; SURVEY §8(b) "Errors") ---- */
+enum {
+    B3D_OK = 0,
+    B3D_EINVAL = 1,    /* bad argument (null pointer, wrong size, kintree root parent != -1 — _ARK_ASSERT_EQ AvatarModel.cpp:41) */
+    B3D_ECUDA = 2,     /* CUDA runtime error or no usable sm_100 device */
+    B3D_ENOTPD = 3,    /* GMM covariance not positive definite (GaussianMixture.cpp:55 throws "Decomposition failed!") */
+    B3D_ENOFILE = 4,   /* file missing / unreadable */
+    B3D_ENOMEM = 5,
+    B3D_EFORMAT = 6    /* malformed model / prior file */
+};
+
+/* Text of the last error raised on the calling thread ("" if none). */
+const char* b3d_last_error(void);
+/* Library version string and the SM architecture the kernels were compiled for ("sm_100a"). */
+const char* b3d_version(void);
+/* Number of kernel launches this library has issued in this process (all threads); for bench accounting. */
+uint64_t b3d_launch_count(void);
+
+/* ===================================================================================================== */
+/* Model: replaces ark::AvatarModel (external/avatar/include/Avatar.h:64-147; AvatarModel.cpp:23-127)      */
+/* ===================================================================================================== */
+typedef struct b3d_model b3d_model;
+
+enum { B3D_F32 = 0, B3D_F64 = 1 };
+
+/* Raw arrays in the layout of SMPL's model.npz as the reference reads it (C order):
+ *   v_template  V x 3           (AvatarModel.cpp:44-48)     shapedirs  V x 3 x S   (:93-102)
+ *   J_regressor J x V  dense    (:60-64)                     weights    V x J dense (:66-71)
+ *   kintree_row0 J  uint32, root = 0xFFFFFFFF -> parent -1  (:35-41)
+ *   faces       F x 3  uint32 (optional; rendering only, :50-58)
+ *   posedirs    V x 3 x 207 (optional; standard SMPL pose blendshapes — an extension, see b3d_smpl_forward flags) */
+typedef struct b3d_model_desc {
+    int32_t num_verts;       /* V (6890 for SMPL) */
+    int32_t num_joints;      /* must be 24 */
+    int32_t num_shape;       /* must be 10 */
+    int32_t num_faces;       /* F or 0 */
+    int32_t dtype;           /* B3D_F32 or B3D_F64: element type of the five float arrays below */
+    int32_t reserved;
+    const void* v_template;
+    const void* shapedirs;
+    const void* J_regressor;
+    const void* weights;
+    const uint32_t* kintree_row0;
+    const uint32_t* faces;   /* may be NULL */
+    const void* posedirs;    /* may be NULL */
+} b3d_model_desc;
+
+int b3d_model_create(const b3d_model_desc* desc, b3d_model** out);
+void b3d_model_destroy(b3d_model* m);
+int b3d_model_num_verts(const b3d_model* m);
+/* parent[24], bit-exact indexing output (AvatarModel.cpp:35-41). */
+int b3d_model_get_parents(const b3d_model* m, int32_t* parent);
+/* Derived constants in float64 (any pointer may be NULL):
+ *   J0 24x3 = initialJointPos (AvatarModel.cpp:113-117), JSR 24x3x10 = jointShapeReg (:121-127),
+ *   offset 24x3 = rest bone vectors used by the fitting functors (include/Sim3BA.h:533-555). */
+int b3d_model_get_constants(const b3d_model* m, double* J0, double* JSR, double* offset);
+
+/* ===================================================================================================== */
+/* GMM pose prior: replaces ark::GaussianMixture::load (external/avatar/GaussianMixture.cpp:12-75)         */
+/* ===================================================================================================== */
+typedef struct b3d_gmm b3d_gmm;
+
+/* weights nComps; means nComps x nDims; covs nComps x nDims x nDims (row-major).  nDims must be 69. */
+int b3d_gmm_create(int32_t nComps, int32_t nDims, const double* weights, const double* means, const double* covs,
+                   b3d_gmm** out);
+/* pose_prior.txt parser (format: scripts/convert_gmm_to_avatar.py:17-29).  A missing file returns B3D_ENOFILE and
+ * *out = NULL; passing NULL as the gmm of a fit degrades to the L2 prior exactly like the reference's nComps = -1
+ * (GaussianMixture.cpp:15-19, include/Sim3BA.h:266). */
+int b3d_gmm_load(const char* path, b3d_gmm** out);
+void b3d_gmm_destroy(b3d_gmm* g);
+int b3d_gmm_dims(const b3d_gmm* g, int32_t* nComps, int32_t* nDims);
+/* Derived arrays in float64 (any may be NULL): prec_cho nComps x nDims x nDims lower (chol of cov^-1), consts_log nComps. */
+int b3d_gmm_get(const b3d_gmm* g, double* prec_cho, double* consts_log);
+/* GaussianMixture::residual (GaussianMixture.cpp:94-113) for B pose vectors x (B x 69) evaluated on the GPU:
+ * out B x 70, comp B (argmin component, strict '<', first wins). */
+int b3d_gmm_residual(const b3d_gmm* g, int32_t B, const double* x, double* out, int32_t* comp);
+
+/* ===================================================================================================== */
+/* Entry (1) batched SMPL evaluator: replaces ark::Avatar::update (external/avatar/Avatar.cpp:22-75)       */
+/* ===================================================================================================== */
+enum {
+    B3D_FWD_DEFAULT = 0,
+    B3D_FWD_POSEDIRS = 1   /* add posedirs . vec(R_j - I) (standard SMPL; the reference has this commented out) */
+};
+
+/* Inputs per body: w (10) = Avatar::w, p (3) = Avatar::p, r (24 x 9, col-major) = Avatar::r.
+ * Outputs per body (any may be NULL): cloud V x 3 (= Avatar::cloud, 3 x V col-major), jointPos 24 x 3 (posed joints),
+ * jointTrans 24 x 12 (col-major 3x4 rest->posed affine per joint).  dtype selects float or double for ALL six arrays. */
+int b3d_smpl_forward(const b3d_model* m, int32_t B, int32_t dtype, const void* w, const void* p, const void* r,
+                     void* cloud, void* jointPos, void* jointTrans, int32_t flags);
+int b3d_smpl_forward_dev(const b3d_model* m, int32_t B, int32_t dtype, const void* w, const void* p, const void* r,
+                         void* cloud, void* jointPos, void* jointTrans, int32_t flags, void* stream);
+
+/* ===================================================================================================== */
+/* Entry (2) batched Levenberg-Marquardt driver: replaces the ceres::Problem + ceres::Solve inside          */
+/*   OptimizePoseReprojection (include/Sim3BA.h:515-683), OptimizePoseShapeReprojection (:348-511)          */
+/* ===================================================================================================== */
+typedef struct b3d_kp {        /* PixelKP (include/Sim3BA.h:9) */
+    int32_t jid;
+    int32_t pad;
+    double u, v;
+} b3d_kp;
+
+enum { B3D_FIT_POSE = 0, B3D_FIT_POSE_SHAPE = 1 };
+
+typedef struct b3d_fit_opts {
+    int32_t mode;              /* B3D_FIT_POSE (Sim3BA.h:515) or B3D_FIT_POSE_SHAPE (Sim3BA.h:348) */
+    int32_t max_iters;         /* ceres max_num_iterations (default 100) */
+    double beta_pose;          /* betaPose  */
+    double beta_shape;         /* betaShape */
+    double lambda_temp;        /* lambdaTemp (multi-frame only) */
+    double fx, fy, cx, cy;     /* pinhole intrinsics */
+    double huber;              /* ceres::HuberLoss(3.0) */
+    double scale_lo, scale_hi; /* SetParameterLowerBound/UpperBound on scale: 0.3, 3.0 (Sim3BA.h:450-451) */
+} b3d_fit_opts;
+
+/* One ceres::IterationSummary as printed by minimizer_progress_to_stdout (Sim3BA.h:477). */
+typedef struct b3d_iter_record {
+    double cost, cost_change, gradient_max_norm, step_norm, relative_decrease, radius;
+    int32_t flags;             /* bit0 step_is_valid, bit1 step_is_successful, bit2 line search contracted the step */
+    int32_t aux;               /* GMM component active at x after this iteration, or -1 */
+} b3d_iter_record;
+
+/* ceres::TerminationType / message class of the solve */
+enum {
+    B3D_TERM_PARAM_TOL = 1, B3D_TERM_FUNC_TOL = 2, B3D_TERM_GRAD_TOL = 3, B3D_TERM_MAX_ITERS = 4,
+    B3D_TERM_MIN_RADIUS = 5, B3D_TERM_INVALID_STEPS = 6, B3D_TERM_EVAL_FAILURE = 7
+};
+
+/* B independent single-frame fits (the frame loop of src/main_single_frame.cpp:192-249).
+ *   kps   B x 17 (first nkp[b] valid)     nkp B            R0  B x 9 = avatar.r[0] on entry (Sim3BA.h:395/558)
+ *   sim3  B x 7 in/out (initSim3)         w   B x 10 in/out (avatar.w)
+ *   jointAA B x 24 x 3 out (row 0 zero)   usable B out = summary.IsSolutionUsable()
+ *   trace  B x trace_stride records or NULL; niters / term B or NULL.
+ * The caller applies the write-back (b3d_writeback) and the final update (b3d_smpl_forward), as the reference does. */
+int b3d_fit_single(const b3d_model* m, const b3d_gmm* gmm, const b3d_fit_opts* opts, int32_t B, const b3d_kp* kps,
+                   const int32_t* nkp, const double* R0, double* sim3, double* w, double* jointAA, uint8_t* usable,
+                   b3d_iter_record* trace, int32_t trace_stride, int32_t* niters, int32_t* term);
+int b3d_fit_single_dev(const b3d_model* m, const b3d_gmm* gmm, const b3d_fit_opts* opts, int32_t B, const b3d_kp* kps,
+                       const int32_t* nkp, const double* R0, double* sim3, double* w, double* jointAA, uint8_t* usable,
+                       b3d_iter_record* trace, int32_t trace_stride, int32_t* niters, int32_t* term, void* stream);
+
+/* AA -> rotation write-back (include/Sim3BA.h:481-507, 649-679; include/MultiFrameBA.h:154-172) for F frames:
+ *   R0 F x 9 in/out: R0 <- R(rootAA) * R0 (cumulative, in place);  r F x 24 x 9 out: r[0] = R0, r[j] = R(jointAA_j);
+ *   p F x 3 out = rootT.  poses F x 76.  Scale is NOT applied (reference behaviour). */
+int b3d_writeback(int32_t F, const double* poses, double* R0, double* r, double* p);
+int b3d_writeback_dev(int32_t F, const double* poses, double* R0, double* r, double* p, void* stream);
+
+/* mean_pixel_error (include/Utils.h:102-115): per frame mean over keypoints of hypot(fx*Jx/Jz+cx-u, fy*Jy/Jz+cy-v)
+ * with jointPos (F x 24 x 3, float64) from the final update; frames with nkp = 0 give 0. */
+int b3d_mean_pixel_error(int32_t F, const b3d_kp* kps, const int32_t* nkp, const double* jointPos, double fx, double fy,
+                         double cx, double cy, double* err);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B3D_H_ */
