@@ -154,6 +154,53 @@ def fit_single_batch(model: AvatarModel, gmm, opts: capi.FitOpts, kps, nkp, R0, 
     return dict(sim3=sim3, w=w, jointAA=jaa, usable=usable, trace=trace, niters=niters, term=term)
 
 
+class Workspace:
+    """Reusable device buffers + one CUDA stream for fit_frames (b3d_workspace)."""
+
+    def __init__(self):
+        h = C.c_void_p()
+        check(lib().b3d_workspace_create(C.byref(h)), "b3d_workspace_create")
+        self.h = h
+
+    def __del__(self):
+        h = getattr(self, "h", None)
+        if h is not None and h.value:
+            lib().b3d_workspace_destroy(h)
+            self.h = None
+
+
+def fit_frames(ws: Workspace, model: AvatarModel, gmm, opts: capi.FitOpts, kps, nkp, R0, sim3, w, out=None, cloud_dtype=np.float32,
+               want_cloud=False):
+    """The per-frame body of src/main_single_frame.cpp:205-255 for B frames in one call: fit -> write-back -> update ->
+    mean pixel error.  Host arrays in, host arrays out; sim3 and w are updated in place when they are float64 C arrays.
+    ``out`` may carry preallocated (e.g. pinned) output arrays keyed jointAA/usable/niters/term/r/p/jointPos/px_err/cloud."""
+    kps = np.ascontiguousarray(kps, dtype=KP_DTYPE).reshape(-1, MAXKP)
+    b = kps.shape[0]
+    nkp = np.ascontiguousarray(nkp, dtype=np.int32).reshape(b)
+    R0 = _f64(R0).reshape(b, 9)
+    sim3 = sim3 if (isinstance(sim3, np.ndarray) and sim3.dtype == np.float64 and sim3.flags.c_contiguous) else _f64(sim3).copy()
+    w = w if (isinstance(w, np.ndarray) and w.dtype == np.float64 and w.flags.c_contiguous) else _f64(w).copy()
+    out = {} if out is None else out
+    cdt = np.dtype(cloud_dtype)
+
+    def buf(name, shape, dt):
+        a = out.get(name)
+        if a is None:
+            a = out[name] = np.zeros(shape, dtype=dt)
+        return a
+
+    jaa, us = buf("jointAA", (b, NJ, 3), np.float64), buf("usable", (b,), np.uint8)
+    ni, te = buf("niters", (b,), np.int32), buf("term", (b,), np.int32)
+    r, p, jp = buf("r", (b, NJ, 9), np.float64), buf("p", (b, 3), np.float64), buf("jointPos", (b, NJ, 3), np.float64)
+    pe = buf("px_err", (b,), np.float64)
+    cloud = buf("cloud", (b, model.numPoints, 3), cdt) if want_cloud else None
+    check(lib().b3d_fit_frames(ws.h, model.h, _gmm_handle(gmm), C.byref(opts), b, ptr(kps), ptr(nkp), ptr(R0), ptr(sim3), ptr(w),
+                               ptr(jaa), ptr(us), ptr(ni), ptr(te), ptr(r), ptr(p), ptr(jp), ptr(pe), ptr(cloud),
+                               F64 if cdt == np.float64 else F32), "b3d_fit_frames")
+    out.update(sim3=sim3, w=w)
+    return out
+
+
 def writeback(poses, R0):
     """a15: R0 <- R(rootAA) R0; r[0] = R0, r[j] = R(jointAA_j); p = rootT.  poses (F,76), R0 (F,9)."""
     poses = _f64(poses).reshape(-1, NPF)

@@ -40,6 +40,9 @@ void count_launch(int n = 1);
             return b3d::set_error(B3D_ECUDA, "kernel launch failed: %s (%s:%d)", cudaGetErrorString(e_), __FILE__, __LINE__); \
     } while (0)
 
+// element-wise double -> float conversion on the device (util.cu)
+int b3d_convert_f64_f32_dev(const double* src, float* dst, size_t n, cudaStream_t st);
+
 // Verifies that the current device can run sm_100a code.  No CPU fallback: callers propagate the error.
 int require_device();
 

@@ -67,6 +67,18 @@ __global__ void pixel_error_kernel(int F, const b3d_kp* __restrict__ kps, const 
     err[f] = n > 0 ? sum / n : 0.0;
 }
 
+__global__ void convert_kernel(const double* __restrict__ src, float* __restrict__ dst, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = (float)src[i];
+}
+
+int b3d_convert_f64_f32_dev(const double* src, float* dst, size_t n, cudaStream_t st) {
+    if (n == 0) return B3D_OK;
+    convert_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(src, dst, n);
+    B3D_LAUNCH_CHECK();
+    return B3D_OK;
+}
+
 }  // namespace b3d
 
 using namespace b3d;
@@ -102,6 +114,15 @@ int b3d_writeback(int32_t F, const double* poses, double* R0, double* r, double*
     cudaFree(dp);
     if (e != cudaSuccess) return set_error(B3D_ECUDA, "b3d_writeback: %s", cudaGetErrorString(e));
     return rc;
+}
+
+int b3d_mean_pixel_error_dev(int32_t F, const b3d_kp* kps, const int32_t* nkp, const double* jointPos, double fx, double fy, double cx,
+                             double cy, double* err, void* stream) {
+    if (!kps || !nkp || !jointPos || !err) return set_error(B3D_EINVAL, "b3d_mean_pixel_error: null argument");
+    if (F <= 0) return F < 0 ? set_error(B3D_EINVAL, "b3d_mean_pixel_error: F < 0") : B3D_OK;
+    pixel_error_kernel<<<(F + 127) / 128, 128, 0, (cudaStream_t)stream>>>(F, kps, nkp, jointPos, fx, fy, cx, cy, err);
+    B3D_LAUNCH_CHECK();
+    return B3D_OK;
 }
 
 int b3d_mean_pixel_error(int32_t F, const b3d_kp* kps, const int32_t* nkp, const double* jointPos, double fx, double fy, double cx,

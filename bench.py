@@ -1,0 +1,379 @@
+#!/usr/bin/env python
+"""bench.py — frames fitted/s of the `3dba_single --opt-shape --use-gmm` hot path (BASELINE.json configs[1]) on N B200s.
+
+A step = one pass of the hot path over one batch of synthetic frames per GPU (default 1,000 frames, the configuration the
+metric is quoted on): LM fit (OptimizePoseShapeReprojection) -> AA write-back -> Avatar::update (6890-vertex cloud) ->
+mean pixel error — the per-frame body of src/main_single_frame.cpp:205-255.
+
+  value     : whole-job frames/s with inputs resident in HBM, device-timed (CUDA events, max over ranks)
+  e2e       : the same through the host-pointer C-ABI call b3d_fit_frames with pinned HOST buffers (H2D + D2H inside)
+  roofline  : the HBM-bound kernel of the path (smpl_lbs_kernel, float32 cloud) timed live at a batch larger than L2
+  roofline_lm : the dominant kernel of the step (fit_single_kernel): fp64-ALU/latency bound, reported as achieved GFLOP/s
+  cpu_baseline : the CPU oracle (Ceres-1.14-faithful: dense QR + Jet autodiff) on the box's host cores, bounded sample
+
+`--impl reference` times the reference's CPU algorithm (the oracle port: the reference needs Eigen + Ceres 1.14 and cannot be
+built offline) on all host threads for the same metric/config.
+"""
+import argparse
+import ctypes as C
+import importlib
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FRAMES_PER_GPU = 1000
+FLOP_PER_FRAME_ITER_C2 = 0.37e6      # residual+Jacobian, J^T J, GMM, Cholesky n=86, candidate evaluation
+FWD_BYTES_PER_BODY_F32 = 85036       # 916 B in + 82,680 B cloud + 288 B jointPos + 1,152 B jointTrans
+CAM = None
+
+
+def pkg(name=""):
+    return importlib.import_module("3dbodyanimation_b200" + ("." + name if name else ""))
+
+
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def make_workload(n, seed):
+    synth = pkg("synth")
+    model_np = synth.make_model()
+    prior = synth.load_pose_prior(os.path.join(ROOT, "tests", "golden", "pose_prior.txt"))
+    fr = synth.make_frames(model_np, n, seed, shape=True, prior=prior)
+    cam = (synth.FX, synth.FY, synth.CX, synth.CY)
+    return model_np, prior, fr, cam
+
+
+FIT_KW = dict(mode=1, max_iters=100, beta_pose=20.0, beta_shape=30.0)   # `3dba_single --opt-shape --use-gmm` defaults
+
+
+# -------------------------------------------------------------------------------------------------------------
+# CPU arm: the oracle (reference port).  Only this function and tests/ / smoke() touch oracle/.
+# -------------------------------------------------------------------------------------------------------------
+def cpu_fit_frames(om, og, orc, fr, cam, idx, threads):
+    """fit -> write-back -> update -> pixel error for frames idx on `threads` host threads; returns seconds."""
+    o = orc.fit_options(cam=cam, linear_solver=orc.LS_DENSE_QR, use_jets=1, **FIT_KW)
+    t0 = time.perf_counter()
+    res = om.fit_single(og, o, fr["kps"][idx], fr["nkp"][idx], fr["R0"][idx], fr["sim3"][idx], fr["w"][idx], nthreads=threads,
+                        want_trace=False)
+    poses = np.concatenate([res["sim3"], res["jointAA"][:, 1:].reshape(len(idx), 69)], axis=1)
+    _, r, p = orc.writeback(poses, fr["R0"][idx])
+    _, jp, _ = om.forward(res["w"], p, r, nthreads=threads)
+    k = fr["kps"][idx]
+    j = np.take_along_axis(jp, k["jid"][:, :, None].astype(np.int64), axis=1)
+    err = np.hypot(cam[0] * j[..., 0] / j[..., 2] + cam[2] - k["u"], cam[1] * j[..., 1] / j[..., 2] + cam[3] - k["v"])
+    _ = err.mean()
+    return time.perf_counter() - t0
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import oracle_api as orc
+    threads = host_threads()
+    sample = max(8, min(FRAMES_PER_GPU, 4 * threads))
+    model_np, prior, fr, cam = make_workload(sample, 1000)
+    om, og = orc.Model(model_np), orc.GMM(prior=prior)
+    idx = np.arange(sample)
+    for _ in range(args.warmup):
+        cpu_fit_frames(om, og, orc, fr, cam, idx, threads)
+    times = [cpu_fit_frames(om, og, orc, fr, cam, idx, threads) for _ in range(args.steps)]
+    dt = float(np.mean(times))
+    val = sample / dt
+    desc = f"{sample} of the 1000 frames per step, all {threads} host threads (OpenMP over frames), dense QR + Jet autodiff"
+    print(json.dumps({
+        "impl": "reference", "metric": "frames_fitted_per_sec", "value": val, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": {"workload": "3dba_single --opt-shape --use-gmm, 1000 synthetic frames (BASELINE configs[1]); bounded sample per step",
+                                        "frames_per_step": sample},
+        "cpu_baseline": {"value": val, "unit": "frames/s", "cores": threads, "kind": "port", "sample": desc},
+        "e2e": {"value": val, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "reference = CPU oracle port of the reference algorithm (Ceres 1.14 LM restated); the reference itself needs Eigen+Ceres 1.14, absent offline",
+    }))
+
+
+# -------------------------------------------------------------------------------------------------------------
+# clocks sampler
+# -------------------------------------------------------------------------------------------------------------
+class Clocks:
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.index)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2]))
+            except Exception:
+                continue
+            for name, col in (("hw_slowdown", 5), ("hw_thermal_slowdown", 6), ("sw_thermal_slowdown", 7), ("sw_power_cap", 8)):
+                if len(r) > col and r[col].lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# -------------------------------------------------------------------------------------------------------------
+# GPU arm
+# -------------------------------------------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+    capi, api = pkg("_capi"), pkg("api")
+    lib = capi.lib()
+    nf = args.frames
+    # frames are sharded across ranks with no data-path collective: rank r owns frames [r * nf, (r + 1) * nf) of the job
+    model_np, prior, fr, cam = make_workload(nf, 1000 + rank)
+    gm, gg = api.AvatarModel(model_np), api.GaussianMixture(prior=prior)
+    opts = api.fit_opts(cam=cam, **FIT_KW)
+    V = gm.numPoints
+    st = torch.cuda.current_stream().cuda_stream
+    P = lambda t: C.c_void_p(t.data_ptr())
+
+    def to_dev(a, dt=None):
+        t = torch.from_numpy(np.ascontiguousarray(a))
+        return (t.to(dt) if dt else t).to(dev)
+
+    kps_d = torch.from_numpy(np.ascontiguousarray(fr["kps"]).view(np.uint8).reshape(nf, -1)).to(dev)
+    nkp_d, R0_init, sim3_init, w_init = to_dev(fr["nkp"]), to_dev(fr["R0"]), to_dev(fr["sim3"]), to_dev(fr["w"])
+    R0_d, sim3_d, w_d = R0_init.clone(), sim3_init.clone(), w_init.clone()
+    jaa_d = torch.zeros(nf, 24, 3, dtype=torch.float64, device=dev)
+    us_d = torch.zeros(nf, dtype=torch.uint8, device=dev)
+    ni_d, te_d = torch.zeros(nf, dtype=torch.int32, device=dev), torch.zeros(nf, dtype=torch.int32, device=dev)
+    poses_d = torch.zeros(nf, 76, dtype=torch.float64, device=dev)
+    r_d, p_d = torch.zeros(nf, 24, 9, dtype=torch.float64, device=dev), torch.zeros(nf, 3, dtype=torch.float64, device=dev)
+    jp_d, jt_d = torch.zeros(nf, 24, 3, dtype=torch.float64, device=dev), torch.zeros(nf, 24, 12, dtype=torch.float64, device=dev)
+    pe_d = torch.zeros(nf, dtype=torch.float64, device=dev)
+    cloud_d = torch.zeros(nf, V, 3, dtype=torch.float32, device=dev)
+    jp32, jt32 = torch.zeros(nf, 24, 3, dtype=torch.float32, device=dev), torch.zeros(nf, 24, 12, dtype=torch.float32, device=dev)
+    gh = gg.h
+
+    def step_resident():
+        # inputs already in HBM; the in/out blocks are re-initialised from the resident initial values (device copies)
+        sim3_d.copy_(sim3_init); w_d.copy_(w_init); R0_d.copy_(R0_init)
+        capi.check(lib.b3d_fit_single_dev(gm.h, gh, C.byref(opts), nf, P(kps_d), P(nkp_d), P(R0_d), P(sim3_d), P(w_d), P(jaa_d), P(us_d),
+                                          None, 0, P(ni_d), P(te_d), C.c_void_p(st)), "fit_single_dev")
+        poses_d[:, :7] = sim3_d
+        poses_d[:, 7:] = jaa_d[:, 1:].reshape(nf, 69)
+        capi.check(lib.b3d_writeback_dev(nf, P(poses_d), P(R0_d), P(r_d), P(p_d), C.c_void_p(st)), "writeback_dev")
+        capi.check(lib.b3d_smpl_forward_dev(gm.h, nf, capi.F64, P(w_d), P(p_d), P(r_d), None, P(jp_d), P(jt_d), 0, C.c_void_p(st)), "forward_dev f64 joints")
+        w32, p32, r32 = w_d.float(), p_d.float(), r_d.float()
+        capi.check(lib.b3d_smpl_forward_dev(gm.h, nf, capi.F32, P(w32), P(p32), P(r32), P(cloud_d), P(jp32), P(jt32), 0, C.c_void_p(st)), "forward_dev f32 cloud")
+        capi.check(lib.b3d_mean_pixel_error_dev(nf, P(kps_d), P(nkp_d), P(jp_d), C.c_double(cam[0]), C.c_double(cam[1]), C.c_double(cam[2]),
+                                                C.c_double(cam[3]), P(pe_d), C.c_void_p(st)), "pixel_error_dev")
+
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    barrier()
+    clocks = Clocks(local)
+    if rank == 0:
+        clocks.start()
+    l0 = lib.b3d_launch_count()
+    evs = []
+    barrier()
+    for _ in range(args.steps):
+        flush.fill_(1)                       # L2 flush between timed iterations (inputs are smaller than L2)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); step_resident(); e1.record()
+        evs.append((e0, e1))
+    barrier()
+    launches = int(lib.b3d_launch_count() - l0)
+    step_ms = float(np.mean([a.elapsed_time(b) for a, b in evs]))
+    iters_total = int(ni_d.sum().item())
+    usable = int(us_d.sum().item())
+
+    # fit kernel alone (for roofline_lm)
+    fit_ms = []
+    for _ in range(max(3, min(args.steps, 10))):
+        sim3_d.copy_(sim3_init); w_d.copy_(w_init); R0_d.copy_(R0_init)
+        flush.fill_(1)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        capi.check(lib.b3d_fit_single_dev(gm.h, gh, C.byref(opts), nf, P(kps_d), P(nkp_d), P(R0_d), P(sim3_d), P(w_d), P(jaa_d), P(us_d),
+                                          None, 0, P(ni_d), P(te_d), C.c_void_p(st)), "fit_single_dev")
+        e1.record(); torch.cuda.synchronize()
+        fit_ms.append(e0.elapsed_time(e1))
+    fit_ms = float(np.mean(fit_ms))
+
+    # e2e: host-pointer call with pinned host buffers, H2D + D2H inside the timed region
+    ws = api.Workspace()
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+    h_kps = torch.from_numpy(np.ascontiguousarray(fr["kps"]).view(np.uint8).reshape(nf, -1)).pin_memory().numpy().view(capi.KP_DTYPE).reshape(nf, 17)
+    h_nkp, h_R0 = pin(fr["nkp"]), pin(fr["R0"])
+    h_s3_init, h_w_init = fr["sim3"].copy(), fr["w"].copy()
+    h_s3, h_w = pin(fr["sim3"]), pin(fr["w"])
+    out = dict(jointAA=pin(np.zeros((nf, 24, 3))), usable=pin(np.zeros(nf, dtype=np.uint8)), niters=pin(np.zeros(nf, dtype=np.int32)),
+               term=pin(np.zeros(nf, dtype=np.int32)), r=pin(np.zeros((nf, 24, 9))), p=pin(np.zeros((nf, 3))),
+               jointPos=pin(np.zeros((nf, 24, 3))), px_err=pin(np.zeros(nf)))
+    h2d = h_kps.nbytes + h_nkp.nbytes + h_R0.nbytes + h_s3.nbytes + h_w.nbytes
+    d2h = h_s3.nbytes + h_w.nbytes + sum(v.nbytes for v in out.values())
+
+    def step_e2e():
+        h_s3[...] = h_s3_init; h_w[...] = h_w_init
+        api.fit_frames(ws, gm, gg, opts, h_kps, h_nkp, h_R0, h_s3, h_w, out=out, cloud_dtype=np.float32, want_cloud=False)
+
+    for _ in range(3):
+        step_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step_e2e()
+    torch.cuda.synchronize()
+    e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
+    px_err_mean = float(out["px_err"].mean())
+
+    # roofline of the HBM-bound kernel: float32 forward at a batch whose cloud (1.36 GB) is far larger than L2
+    FB = args.forward_batch
+    synth = pkg("synth")
+    fin = synth.make_forward_inputs(FB, 5)
+    fw, fp_, fr_ = to_dev(fin["w"], torch.float32), to_dev(fin["p"], torch.float32), to_dev(fin["r"], torch.float32)
+    fcloud = torch.empty(FB, V, 3, dtype=torch.float32, device=dev)
+    fjp, fjt = torch.empty(FB, 24, 3, dtype=torch.float32, device=dev), torch.empty(FB, 24, 12, dtype=torch.float32, device=dev)
+    fwd = lambda: capi.check(lib.b3d_smpl_forward_dev(gm.h, FB, capi.F32, P(fw), P(fp_), P(fr_), P(fcloud), P(fjp), P(fjt), 0, C.c_void_p(st)), "forward sweep")
+    for _ in range(3):
+        fwd()
+    torch.cuda.synchronize()
+    fevs = []
+    for _ in range(10):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fwd(); e1.record()
+        fevs.append((e0, e1))
+    torch.cuda.synchronize()
+    fwd_ms = float(np.mean([a.elapsed_time(b) for a, b in fevs]))
+    clk = clocks.stop() if rank == 0 else None
+
+    # max over ranks of the device-timed step, the e2e step and the forward
+    tt = torch.tensor([step_ms, e2e_ms, fwd_ms, fit_ms], dtype=torch.float64, device=dev)
+    cnt = torch.tensor([float(iters_total), float(usable)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    step_ms, e2e_ms, fwd_ms, fit_ms = [float(x) for x in tt.tolist()]
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peaks = {}
+    pk = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(pk):
+        peaks = json.load(open(pk))
+    hbm_peak, peak_src = (float(peaks["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)") if "hbm_gbs" in peaks else (6650.0, "fallback (B200_PROFILING.md)")
+    achieved = FB * FWD_BYTES_PER_BODY_F32 / (fwd_ms * 1e-3) / 1e9
+    traffic = None
+    tfile = os.path.join(ROOT, "profiles", "lbs_traffic.json")
+    if os.path.exists(tfile):
+        try:
+            traffic = json.load(open(tfile)).get("dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+
+    # CPU baseline on rank 0, N = 1 only: bounded sample of the same workload
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        from oracle import oracle_api as orc
+        threads = host_threads()
+        om, og = orc.Model(model_np), orc.GMM(prior=prior)
+        cal = np.arange(min(nf, 2 * threads))
+        tc = cpu_fit_frames(om, og, orc, fr, cam, cal, threads)
+        sample = int(max(len(cal), min(nf, len(cal) * 12.0 / max(tc, 1e-3))))
+        ts = cpu_fit_frames(om, og, orc, fr, cam, np.arange(sample), threads)
+        cpu = {"value": sample / ts, "unit": "frames/s", "cores": threads, "kind": "port",
+               "sample": f"first {sample} of the {nf} frames, oracle (dense QR + Jet autodiff, Ceres-1.14 LM restated), OpenMP over frames on {threads} threads, {ts:.1f} s"}
+
+    total_frames = nf * world
+    line = {
+        "metric": "frames_fitted_per_sec", "value": total_frames / (step_ms * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": "3dba_single --opt-shape --use-gmm (BASELINE configs[1]): fit + write-back + Avatar::update + pixel error",
+                   "frames_per_gpu": nf, "model": "random-init SMPL-shaped (6890 v, 24 j, 10 betas), real pose_prior.txt GMM", "beta_pose": 20.0,
+                   "beta_shape": 30.0, "max_iters": 100, "parallelism": f"frames sharded over {world} rank(s), no data-path collective",
+                   "l2": "256 MB flush write between timed steps", "cloud_dtype": "f32 (joints/pixel error f64)"},
+        "e2e": {"value": total_frames / (e2e_ms * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": e2e_ms, "call": "b3d_fit_frames (host pointers, pinned); cloud computed and left on the device"},
+        "gpu_launches": launches,
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
+                     "kernel": "smpl_joints_kernel<float> + smpl_lbs_kernel<float,4> (one b3d_smpl_forward_dev call)",
+                     "workload": f"forward sweep point B={FB} (BASELINE configs[3]), {FWD_BYTES_PER_BODY_F32} algorithmic B/body", "ms_per_launch": fwd_ms,
+                     "verts_per_sec": world * FB * V / (fwd_ms * 1e-3), "peak_source": peak_src},
+        "roofline_lm": {"kernel": "fit_single_kernel<128>", "bound": "fp64 ALU / latency (not HBM: ~1.2 KB algorithmic I/O per frame)",
+                        "ms_per_launch": fit_ms, "share_of_step": fit_ms / step_ms, "lm_iterations_per_step": cnt[0].item() / world,
+                        "achieved_gflops": cnt[0].item() / world * FLOP_PER_FRAME_ITER_C2 / (fit_ms * 1e-3) / 1e9,
+                        "flop_model": "0.37 Mflop per frame-iteration (SURVEY 8d)"},
+        "cpu_baseline": cpu,
+        "clocks": clk,
+        "quality": {"usable_frames": int(cnt[1].item()), "mean_lm_iterations": cnt[0].item() / total_frames, "mean_pixel_error_px": px_err_mean},
+    }
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--frames", type=int, default=FRAMES_PER_GPU, help="frames per GPU per step")
+    ap.add_argument("--forward-batch", type=int, default=16384)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -186,6 +186,31 @@ int b3d_writeback_dev(int32_t F, const double* poses, double* R0, double* r, dou
 int b3d_mean_pixel_error(int32_t F, const b3d_kp* kps, const int32_t* nkp, const double* jointPos, double fx, double fy,
                          double cx, double cy, double* err);
 
+int b3d_mean_pixel_error_dev(int32_t F, const b3d_kp* kps, const int32_t* nkp, const double* jointPos, double fx, double fy,
+                             double cx, double cy, double* err, void* stream);
+
+/* ===================================================================================================== */
+/* The per-frame body of src/main_single_frame.cpp:205-255, batched: fit -> write-back -> update -> pixel error */
+/* ===================================================================================================== */
+/* Reusable device buffers + one CUDA stream, so that repeated calls do not allocate.  Not thread-safe per handle. */
+typedef struct b3d_workspace b3d_workspace;
+int b3d_workspace_create(b3d_workspace** out);
+void b3d_workspace_destroy(b3d_workspace* ws);
+
+/* Host pointers in, host pointers out (pinned host memory makes the copies asynchronous).  For each of B frames:
+ *   OptimizePose[Shape]Reprojection (Sim3BA.h:348/515) from sim3 / w / R0, then the caller-side steps of the reference
+ *   main: write-back of r, p (Sim3BA.h:481-507), Avatar::update (main_single_frame.cpp:254), mean_pixel_error (:255).
+ * in : kps B x 17, nkp B, R0 B x 9 (avatar.r[0] before the solve), sim3 B x 7 and w B x 10 (both in/out)
+ * out: jointAA B x 24 x 3; usable B; niters, term B (may be NULL); r B x 24 x 9, p B x 3, jointPos B x 24 x 3 (float64,
+ *      may be NULL); px_err B (may be NULL); cloud B x V x 3 of cloud_dtype (may be NULL: the cloud is then computed and
+ *      left in the workspace on the device — b3d_workspace_cloud returns its device address). */
+int b3d_fit_frames(b3d_workspace* ws, const b3d_model* m, const b3d_gmm* gmm, const b3d_fit_opts* opts, int32_t B,
+                   const b3d_kp* kps, const int32_t* nkp, const double* R0, double* sim3, double* w, double* jointAA,
+                   uint8_t* usable, int32_t* niters, int32_t* term, double* r, double* p, double* jointPos, double* px_err,
+                   void* cloud, int32_t cloud_dtype);
+/* Device address and element type of the cloud left by the last b3d_fit_frames on this workspace (NULL before). */
+const void* b3d_workspace_cloud(const b3d_workspace* ws, int32_t* dtype);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,156 @@
+"""Parity of the batched single-frame LM driver (b3d_fit_single through the C-ABI) with the oracle.
+
+Tolerances (BASELINE.json north_star): per-iteration residual norms (cost) 1e-4 relative, fitted parameters 1e-3.
+Two oracle variants are checked:
+  * Cholesky + analytic Jacobians  — the same algebra as the GPU kernel: trajectories must agree tightly;
+  * dense Householder QR + Jet autodiff — what the reference's ceres::Solve does (DENSE_QR, DynamicAutoDiffCostFunction).
+The reprojection cost is exactly invariant under (s, t) -> a (s, t) (X = s q + t, pixels depend on X/X_z), so J^T J is
+singular along that gauge direction and only the LM damping D^2 / radius regularises it.  Once the radius has grown past
+~1e12 the step along the gauge is rounding noise in ANY implementation (QR-vs-Cholesky in the oracle itself differ there,
+see DESIGN.md "gauge freedom"), so per-iteration checks are made on the prefix with radius <= 1e12, and scale/translation are
+compared through the gauge-invariant t / s unless the whole solve stayed in the stable regime."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+COST_TOL = 1e-4     # north_star: per-iteration residual norms to 1e-4
+PARAM_TOL = 1e-3    # north_star: fitted pose/shape/Sim3 parameters to 1e-3
+STABLE_RADIUS = 1e12
+
+
+def _cfg(name, synth, model_np, prior_np, n, seed, drop=0.0):
+    if name == "C1":
+        fr = synth.make_frames(model_np, n, seed, shape=False, drop_prob=drop)
+        return fr, dict(mode=0, max_iters=100, beta_pose=20.0, beta_shape=30.0), False
+    fr = synth.make_frames(model_np, n, seed, shape=True, prior=prior_np, drop_prob=drop)
+    return fr, dict(mode=1, max_iters=100, beta_pose=20.0, beta_shape=30.0), True
+
+
+def _compare(g, o, tight):
+    B = g["niters"].shape[0]
+    assert g["usable"].all() and o["usable"].all()
+    n_full = 0
+    for f in range(B):
+        ng, no = int(g["niters"][f]), int(o["niters"][f])
+        n = min(ng, no)
+        rad = o["trace"][f]["radius"][:n]
+        stable = np.cumprod(rad <= STABLE_RADIUS).astype(bool)
+        k = int(stable.sum())
+        assert k >= 3
+        cg, co = g["trace"][f]["cost"][:k], o["trace"][f]["cost"][:k]
+        assert np.max(np.abs(cg - co) / np.abs(co)) < COST_TOL, f"frame {f}"
+        if tight:
+            assert np.array_equal(g["trace"][f]["flags"][:k], o["trace"][f]["flags"][:k])
+            assert np.allclose(g["trace"][f]["radius"][:k], o["trace"][f]["radius"][:k], rtol=1e-6)
+            assert np.array_equal(g["trace"][f]["aux"][:k], o["trace"][f]["aux"][:k])
+        # final cost
+        fg, fo = g["trace"][f]["cost"][:ng], o["trace"][f]["cost"][:no]
+        assert abs(fg.min() - fo.min()) / fo.min() < COST_TOL
+        # gauge-invariant parameters
+        assert np.max(np.abs(g["jointAA"][f] - o["jointAA"][f])) < PARAM_TOL
+        assert np.max(np.abs(g["sim3"][f, 1:4] - o["sim3"][f, 1:4])) < PARAM_TOL
+        assert np.max(np.abs(g["w"][f] - o["w"][f])) < PARAM_TOL
+        assert np.max(np.abs(g["sim3"][f, 4:7] / g["sim3"][f, 0] - o["sim3"][f, 4:7] / o["sim3"][f, 0])) < PARAM_TOL * 3.5
+        if k == n and ng == no:     # the whole solve stayed in the stable regime: scale and translation themselves
+            n_full += 1
+            assert np.max(np.abs(g["sim3"][f] - o["sim3"][f])) < PARAM_TOL
+            assert g["term"][f] == o["term"][f]
+    return n_full
+
+
+@pytest.mark.parametrize("name", ["C1", "C2"])
+def test_fit_single_vs_oracle(api, orc, gmodel, ggmm, omodel, ogmm, synth, model_np, prior_np, name):
+    fr, kw, use_gmm = _cfg(name, synth, model_np, prior_np, 48, 21)
+    cam = (synth.FX, synth.FY, synth.CX, synth.CY)
+    g = api.fit_single_batch(gmodel, ggmm if use_gmm else None, api.fit_opts(cam=cam, **kw), fr["kps"], fr["nkp"], fr["R0"], fr["sim3"], fr["w"])
+    o_ch = omodel.fit_single(ogmm if use_gmm else None, orc.fit_options(cam=cam, linear_solver=orc.LS_DENSE_CHOLESKY, use_jets=0, **kw),
+                             fr["kps"], fr["nkp"], fr["R0"], fr["sim3"], fr["w"], nthreads=8)
+    o_qr = omodel.fit_single(ogmm if use_gmm else None, orc.fit_options(cam=cam, linear_solver=orc.LS_DENSE_QR, use_jets=1, **kw),
+                             fr["kps"], fr["nkp"], fr["R0"], fr["sim3"], fr["w"], nthreads=8)
+    n1 = _compare(g, o_ch, tight=True)
+    n2 = _compare(g, o_qr, tight=False)
+    assert n1 >= 24 and n2 >= 24      # most frames converge before the gauge noise regime
+    # recovered pose is close to the ground truth pose that generated the keypoints (sanity of the whole pipeline)
+    gt = fr["gt"]
+    if name == "C2":
+        assert np.median(np.abs(g["sim3"][:, 1:4] - gt[:, 1:4])) < 0.2
+
+
+def test_fit_single_ragged_and_degenerate(api, orc, gmodel, ggmm, omodel, ogmm, synth, model_np, prior_np):
+    """Dropped keypoints (ragged nkp), a frame with a single keypoint, scale starting outside its bounds."""
+    fr, kw, _ = _cfg("C2", synth, model_np, prior_np, 12, 5, drop=0.3)
+    fr["nkp"][3] = 1
+    fr["sim3"][4, 0] = 5.0     # projected onto [0.3, 3] at iteration 0
+    cam = (synth.FX, synth.FY, synth.CX, synth.CY)
+    g = api.fit_single_batch(gmodel, ggmm, api.fit_opts(cam=cam, **kw), fr["kps"], fr["nkp"], fr["R0"], fr["sim3"], fr["w"])
+    o = omodel.fit_single(ogmm, orc.fit_options(cam=cam, linear_solver=orc.LS_DENSE_CHOLESKY, use_jets=0, **kw),
+                          fr["kps"], fr["nkp"], fr["R0"], fr["sim3"], fr["w"], nthreads=8)
+    _compare(g, o, tight=True)
+    assert np.all(g["sim3"][:, 0] >= 0.3) and np.all(g["sim3"][:, 0] <= 3.0)
+
+
+def test_fit_single_l2_prior_and_no_gmm_degrade(api, orc, gmodel, omodel, synth, model_np, prior_np):
+    """gmm == NULL with --use-gmm semantics degrades silently to the L2 prior (Sim3BA.h:266); max_iters cap is honoured."""
+    fr, kw, _ = _cfg("C2", synth, model_np, prior_np, 8, 9)
+    kw["max_iters"] = 7
+    cam = (synth.FX, synth.FY, synth.CX, synth.CY)
+    g = api.fit_single_batch(gmodel, None, api.fit_opts(cam=cam, **kw), fr["kps"], fr["nkp"], fr["R0"], fr["sim3"], fr["w"])
+    o = omodel.fit_single(None, orc.fit_options(cam=cam, linear_solver=orc.LS_DENSE_CHOLESKY, use_jets=0, **kw),
+                          fr["kps"], fr["nkp"], fr["R0"], fr["sim3"], fr["w"], nthreads=8)
+    assert np.array_equal(g["niters"], o["niters"]) and np.array_equal(g["term"], o["term"])
+    assert (g["term"] == 4).any()
+    for f in range(8):
+        n = g["niters"][f]
+        assert np.max(np.abs(g["trace"][f]["cost"][:n] - o["trace"][f]["cost"][:n]) / o["trace"][f]["cost"][:n]) < 1e-8
+        assert np.all(g["trace"][f]["aux"][:n] == -1)
+
+
+def test_reference_style_call(api, orc, gmodel, ggmm, omodel, ogmm, synth, model_np, prior_np):
+    """The per-frame call of src/main_single_frame.cpp:205-255 through the mirrored interface."""
+    fr, kw, _ = _cfg("C2", synth, model_np, prior_np, 1, 33)
+    av = api.Avatar(gmodel)
+    av.p = np.array([0.0, 0.0, 3.0])
+    av.r[0] = synth.initial_root_rotation().T.reshape(9)
+    av.update()
+    kps = [api.PixelKP(int(k["jid"]), float(k["u"]), float(k["v"])) for k in fr["kps"][0][:fr["nkp"][0]]]
+    sim3 = api.Sim3Params(np.array([1.0, 0, 0, 0, 0, 0, 3.0]))
+    ok, report = api.OptimizePoseShapeReprojection(gmodel, av, kps, synth.FX, synth.FY, synth.CX, synth.CY, [k.jid for k in kps], sim3,
+                                                   100, 20.0, 30.0, ggmm)
+    assert ok and "termination" in report
+    av.update()
+    err = api.mean_pixel_error(kps, av, synth.FX, synth.FY, synth.CX, synth.CY)
+    # oracle: same solve, write-back, update, pixel error in numpy
+    o = omodel.fit_single(ogmm, orc.fit_options(cam=(synth.FX, synth.FY, synth.CX, synth.CY), linear_solver=orc.LS_DENSE_CHOLESKY, use_jets=0, **kw),
+                          fr["kps"], fr["nkp"], fr["R0"], fr["sim3"], fr["w"])
+    pose = np.concatenate([o["sim3"][0], o["jointAA"][0, 1:].ravel()])
+    R0, r, p = orc.writeback(pose[None], fr["R0"][:1])
+    _, jp, _ = omodel.forward(o["w"], p, r)
+    e0 = np.mean([np.hypot(synth.FX * jp[0, k.jid, 0] / jp[0, k.jid, 2] + synth.CX - k.u, synth.FY * jp[0, k.jid, 1] / jp[0, k.jid, 2] + synth.CY - k.v) for k in kps])
+    assert abs(err - e0) < 1e-3 * max(1.0, e0)
+    assert np.max(np.abs(av.r - r[0])) < 1e-3 and np.max(np.abs(sim3.data[1:4] - o["sim3"][0, 1:4])) < 1e-3
+
+
+def test_fit_frames_pipeline(api, orc, gmodel, ggmm, omodel, ogmm, synth, model_np, prior_np):
+    """b3d_fit_frames = fit -> write-back -> update -> pixel error in one call equals the staged calls."""
+    fr, kw, _ = _cfg("C2", synth, model_np, prior_np, 20, 17)
+    cam = (synth.FX, synth.FY, synth.CX, synth.CY)
+    o = api.fit_opts(cam=cam, **kw)
+    ws = api.Workspace()
+    res = api.fit_frames(ws, gmodel, ggmm, o, fr["kps"], fr["nkp"], fr["R0"], fr["sim3"].copy(), fr["w"].copy(), want_cloud=True,
+                         cloud_dtype=np.float64)
+    g = api.fit_single_batch(gmodel, ggmm, o, fr["kps"], fr["nkp"], fr["R0"], fr["sim3"], fr["w"])
+    assert np.array_equal(res["sim3"], g["sim3"]) and np.array_equal(res["jointAA"], g["jointAA"]) and np.array_equal(res["w"], g["w"])
+    assert np.array_equal(res["niters"], g["niters"]) and res["usable"].all()
+    poses = np.concatenate([g["sim3"], g["jointAA"][:, 1:].reshape(20, 69)], axis=1)
+    R0, r, p = orc.writeback(poses, fr["R0"])
+    c0, jp0, _ = omodel.forward(g["w"], p, r)
+    assert np.max(np.abs(res["r"] - r)) < 1e-13 and np.max(np.abs(res["p"] - p)) == 0.0
+    assert np.max(np.abs(res["cloud"] - c0)) / np.max(np.abs(c0)) < 1e-12
+    e0 = np.array([np.mean([np.hypot(synth.FX * jp0[f, k["jid"], 0] / jp0[f, k["jid"], 2] + synth.CX - k["u"],
+                                     synth.FY * jp0[f, k["jid"], 1] / jp0[f, k["jid"], 2] + synth.CY - k["v"]) for k in fr["kps"][f][:fr["nkp"][f]]])
+                   for f in range(20)])
+    assert np.max(np.abs(res["px_err"] - e0)) < 1e-9
+    # float32 cloud variant and a second call on the same workspace (buffers reused)
+    res32 = api.fit_frames(ws, gmodel, ggmm, o, fr["kps"], fr["nkp"], fr["R0"], fr["sim3"].copy(), fr["w"].copy(), want_cloud=True)
+    assert res32["cloud"].dtype == np.float32 and np.max(np.abs(res32["cloud"] - c0)) / np.max(np.abs(c0)) < 1e-5

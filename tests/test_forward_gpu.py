@@ -1,0 +1,86 @@
+"""Parity of the batched SMPL evaluator (b3d_smpl_forward, through the C-ABI) with the oracle's Avatar::update restatement.
+Tolerance (BASELINE.json north_star): vertices 1e-5 relative; indexing outputs bit-exact."""
+import numpy as np
+import pytest
+
+from conftest import rel_err
+
+pytestmark = pytest.mark.gpu
+
+TOL_F32 = 1e-5     # north_star: "SMPL vertices must match the reference's avatar/Eigen path to 1e-5 relative"
+TOL_F64 = 1e-12
+
+
+def test_parents_bit_exact(gmodel, omodel, synth):
+    assert gmodel.parent.dtype == np.int32
+    assert np.array_equal(gmodel.parent, omodel.constants()["parent"])
+    assert np.array_equal(gmodel.parent, synth.PARENT)
+    k = omodel.constants()
+    assert rel_err(gmodel.initialJointPos, k["J0"]) < 1e-14
+    assert rel_err(gmodel.jointShapeReg, k["JSR"]) < 1e-13
+    assert np.max(np.abs(gmodel.offset - k["offset"])) < 1e-15
+
+
+@pytest.mark.parametrize("B", [1, 7, 100, 1000])
+@pytest.mark.parametrize("dtype,tol", [(np.float32, TOL_F32), (np.float64, TOL_F64)])
+def test_forward_parity(api, gmodel, omodel, synth, B, dtype, tol):
+    inp = synth.make_forward_inputs(B, 100 + B)
+    c, jp, jt = api.smpl_forward(gmodel, inp["w"], inp["p"], inp["r"], dtype=dtype)
+    # the oracle sees the same (possibly float32-rounded) inputs
+    w, p, r = (np.asarray(inp[k], dtype=dtype).astype(np.float64) for k in ("w", "p", "r"))
+    c0, jp0, jt0 = omodel.forward(w, p, r, nthreads=8)
+    assert c.dtype == dtype and c.shape == (B, 6890, 3)
+    for b in range(B):   # per-body relative error, as a per-frame user would measure it
+        assert rel_err(c[b], c0[b]) < tol
+    assert rel_err(jp, jp0) < tol and rel_err(jt, jt0) < tol
+
+
+def test_forward_posedirs_extension(api, gmodel, omodel_pd, synth):
+    inp = synth.make_forward_inputs(9, 5)
+    c, _, _ = api.smpl_forward(gmodel, inp["w"], inp["p"], inp["r"], dtype=np.float64, posedirs=True)
+    c0, _, _ = omodel_pd.forward(inp["w"], inp["p"], inp["r"])
+    assert rel_err(c, c0) < 1e-12
+    c32, _, _ = api.smpl_forward(gmodel, inp["w"], inp["p"], inp["r"], dtype=np.float32, posedirs=True)
+    assert rel_err(c32, c0) < 2e-5
+
+
+def test_forward_edge_cases(api, gmodel, omodel, synth):
+    # rest pose: w = 0, r = I, p = 0 -> cloud equals the template exactly in float64 up to the weight sum rounding
+    w, p = np.zeros((1, 10)), np.zeros((1, 3))
+    r = np.tile(np.eye(3).reshape(9), (1, 24, 1))
+    c, jp, _ = api.smpl_forward(gmodel, w, p, r, dtype=np.float64)
+    c0, jp0, _ = omodel.forward(w, p, r)
+    assert rel_err(c, c0) < 1e-13 and np.max(np.abs(jp[0, 0])) == 0.0
+    # B = 0 is a no-op; joints-only call (no cloud) works
+    c, jp, jt = api.smpl_forward(gmodel, np.zeros((0, 10)), np.zeros((0, 3)), np.zeros((0, 24, 9)))
+    assert c.shape[0] == 0
+    inp = synth.make_forward_inputs(5, 1)
+    c, jp, jt = api.smpl_forward(gmodel, inp["w"], inp["p"], inp["r"], want_cloud=False)
+    assert c is None and rel_err(jp, omodel.forward(inp["w"], inp["p"], inp["r"], want_cloud=False)[1]) < 1e-12
+
+
+def test_forward_linearity_large_batch(api, gmodel, synth):
+    """Size-independent property at a BASELINE-scale batch: for fixed pose, the cloud is affine in the shape vector w, so
+    f(w1) + f(w2) - f(0) == f(w1 + w2) — holds only if every (body, vertex) was written by the right thread."""
+    B = 4096
+    inp = synth.make_forward_inputs(B, 77)
+    r, p = inp["r"], inp["p"]
+    r[B // 2:] = r[:B // 2]; p[B // 2:] = p[:B // 2]
+    w = inp["w"]
+    w[B // 2:] = 0.0
+    c, _, _ = api.smpl_forward(gmodel, w, p, r, dtype=np.float64)
+    w2 = w.copy(); w2[:B // 2] *= 2.0
+    c2, _, _ = api.smpl_forward(gmodel, w2, p, r, dtype=np.float64)
+    # f(2w) - f(0) == 2 (f(w) - f(0))
+    lhs = c2[:B // 2] - c[B // 2:]
+    rhs = 2.0 * (c[:B // 2] - c[B // 2:])
+    assert np.max(np.abs(lhs - rhs)) < 1e-12
+
+
+def test_avatar_object_interface(api, gmodel, omodel, synth):
+    av = api.Avatar(gmodel)
+    av.p = np.array([0.0, 0.0, 3.0])
+    av.r[0] = synth.initial_root_rotation().T.reshape(9)
+    av.update()
+    c0, jp0, jt0 = omodel.forward(av.w[None], av.p[None], av.r[None])
+    assert rel_err(av.cloud, c0[0]) < 1e-13 and rel_err(av.jointPos, jp0[0]) < 1e-13 and rel_err(av.jointTrans, jt0[0]) < 1e-13
