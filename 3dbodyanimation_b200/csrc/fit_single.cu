@@ -33,6 +33,7 @@ constexpr double kLsContractLo = 1e-3, kLsContractHi = 0.6;   // max_/min_line_s
 
 struct GmmTmp {
     double h[GMM_MAXC][NPRI];     // L_i^T (x - mu_i)
+    double d[GMM_MAXC][NPRI];     // x - mu_i
     double p[GMM_MAXC];           // |h_i|^2 / 2 - consts_log_i
     double sq[GMM_MAXC];          // |sqrt(1/2) h_i|^2
 };
@@ -54,6 +55,7 @@ struct SingleSmem {
     double red[40];
     double ls_step;
     int32_t comp, flag;
+    int16_t fcol[MAXKP][NNZPAD];          // free-layout column of each Jacobian slot (-1 = held constant)
 };
 
 // ---- polynomial helpers for the (rare) Armijo interpolation: thread 0 only --------------------------------------
@@ -168,13 +170,20 @@ template <int T, bool JAC>
 __device__ double gmm_eval(const FitConst* __restrict__ C, const double* xj /*69*/, SingleSmem& S) {
     const int tid = threadIdx.x, nc = C->gmm_ncomp;
     GmmTmp& G = S.u.gm;
+    for (int t = tid; t < nc * NPRI; t += T) G.d[t / NPRI][t % NPRI] = xj[t % NPRI] - C->gmm_mean[t];
+    __syncthreads();
     for (int t = tid; t < nc * NPRI; t += T) {
         const int i = t / NPRI, k = t % NPRI;
-        const double* L = C->gmm_L + (size_t)i * NPRI * NPRI;
-        const double* mu = C->gmm_mean + i * NPRI;
-        double acc = 0.0;
-        for (int m = k; m < NPRI; ++m) acc += L[m * NPRI + k] * (xj[m] - mu[m]);
-        G.h[i][k] = acc;
+        const double* __restrict__ L = C->gmm_L + (size_t)i * NPRI * NPRI + k;    // column k: consecutive threads, consecutive addresses
+        const double* dd = G.d[i];
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+        int m = k;
+        for (; m + 4 <= NPRI; m += 4) {
+            a0 += __ldg(L + m * NPRI) * dd[m];           a1 += __ldg(L + (m + 1) * NPRI) * dd[m + 1];
+            a2 += __ldg(L + (m + 2) * NPRI) * dd[m + 2]; a3 += __ldg(L + (m + 3) * NPRI) * dd[m + 3];
+        }
+        for (; m < NPRI; ++m) a0 += __ldg(L + m * NPRI) * dd[m];
+        G.h[i][k] = (a0 + a1) + (a2 + a3);
     }
     __syncthreads();
     if (tid < nc) {
@@ -195,9 +204,14 @@ __device__ double gmm_eval(const FitConst* __restrict__ C, const double* xj /*69
         const double f = C->beta_pose * C->beta_pose * sqrt(0.5);
         const double* LT = C->gmm_LT + (size_t)c * NPRI * NPRI;
         for (int m = tid; m < NPRI; m += T) {
-            double acc = 0.0;
-            for (int k = 0; k <= m; ++k) acc += LT[k * NPRI + m] * G.h[c][k];
-            S.gpri[m] = f * acc;
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+            int k = 0;
+            for (; k + 4 <= m + 1; k += 4) {
+                a0 += __ldg(LT + k * NPRI + m) * G.h[c][k];           a1 += __ldg(LT + (k + 1) * NPRI + m) * G.h[c][k + 1];
+                a2 += __ldg(LT + (k + 2) * NPRI + m) * G.h[c][k + 2]; a3 += __ldg(LT + (k + 3) * NPRI + m) * G.h[c][k + 3];
+            }
+            for (; k <= m; ++k) a0 += __ldg(LT + k * NPRI + m) * G.h[c][k];
+            S.gpri[m] = f * ((a0 + a1) + (a2 + a3));
         }
     }
     __syncthreads();
@@ -229,23 +243,26 @@ __device__ double evaluate(const FitConst* __restrict__ C, const double* xf, con
     double* H = S.u.L;
     for (int e = tid; e < n * (n + 1) / 2; e += T) H[e] = 0.0;
     for (int k = tid; k < n; k += T) S.g[k] = 0.0;
+    for (int t = tid; t < nkp * NNZPAD; t += T) {
+        const int k = t / NNZPAD, sl = t % NNZPAD;
+        S.fcol[k][sl] = sl < S.out.jnnz[k] ? (int16_t)C->col_of[S.out.jcol[k][sl]] : (int16_t)-1;
+    }
     __syncthreads();
     for (int k = 0; k < nkp; ++k) {
         const int nnz = S.out.jnnz[k];
         const double r0 = S.out.res[k][0], r1 = S.out.res[k][1];
         const double* J0 = S.out.J[k][0];
         const double* J1 = S.out.J[k][1];
-        const int* jc = S.out.jcol[k];
-        for (int e = tid; e < nnz * (nnz + 1) / 2; e += T) {
-            int i = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
-            while (i * (i + 1) / 2 > e) --i;
-            while ((i + 1) * (i + 2) / 2 <= e) ++i;
-            const int j = e - i * (i + 1) / 2;
-            const int ci = C->col_of[jc[i]], cj = C->col_of[jc[j]];
-            if (ci < 0 || cj < 0) continue;
-            const double hv = J0[i] * J0[j] + J1[i] * J1[j];
-            H[ci >= cj ? tri(ci, cj) : tri(cj, ci)] += hv;
-            if (i == j) S.g[ci] += J0[i] * r0 + J1[i] * r1;
+        for (int i = tid >> 5; i < nnz; i += T / 32) {          // row of the outer product: one warp; columns: lanes
+            const int ci = S.fcol[k][i];
+            if (ci < 0) continue;
+            const double a0 = J0[i], a1 = J1[i];
+            for (int j = tid & 31; j <= i; j += 32) {
+                const int cj = S.fcol[k][j];
+                if (cj < 0) continue;
+                H[ci >= cj ? tri(ci, cj) : tri(cj, ci)] += a0 * J0[j] + a1 * J1[j];
+                if (i == j) S.g[ci] += a0 * r0 + a1 * r1;
+            }
         }
         __syncthreads();
     }
@@ -254,14 +271,13 @@ __device__ double evaluate(const FitConst* __restrict__ C, const double* xf, con
         const double b2 = C->beta_pose * C->beta_pose;
         if (C->use_gmm) {
             const double* P = C->gmm_P + (size_t)S.comp * NPRI * NPRI;
-            for (int e = tid; e < NPRI * (NPRI + 1) / 2; e += T) {
-                int i = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
-                while (i * (i + 1) / 2 > e) --i;
-                while ((i + 1) * (i + 2) / 2 <= e) ++i;
-                const int j = e - i * (i + 1) / 2;
-                const int ci = C->col_of[IDX_JAA + i], cj = C->col_of[IDX_JAA + j];
-                if (ci < 0 || cj < 0) continue;
-                H[tri(ci, cj)] += b2 * P[i * NPRI + j];     // free order preserves pose-dim order, so ci >= cj
+            for (int i = tid >> 5; i < NPRI; i += T / 32) {
+                const int ci = C->col_of[IDX_JAA + i];
+                if (ci < 0) continue;
+                for (int j = tid & 31; j <= i; j += 32) {
+                    const int cj = C->col_of[IDX_JAA + j];
+                    if (cj >= 0) H[tri(ci, cj)] += b2 * P[i * NPRI + j];     // free order preserves pose-dim order, so ci >= cj
+                }
             }
             for (int k = tid; k < NPRI; k += T) { const int ck = C->col_of[IDX_JAA + k]; if (ck >= 0) S.g[ck] += S.gpri[k]; }
         } else {
@@ -279,35 +295,36 @@ __device__ double evaluate(const FitConst* __restrict__ C, const double* xf, con
     return cost;
 }
 
-// Cholesky of the packed lower matrix A (np x np; the last row is the right-hand side): on return rows 0..np-2 hold L and
-// row np-1 holds z = L^-1 rhs.  Returns false when a pivot is not positive (Eigen LLT / oracle criterion).
+// Cholesky (Crout / left-looking) of the packed lower matrix A (np x np; the last row is the right-hand side): on return rows
+// 0..np-2 hold L and row np-1 holds z = L^-1 rhs.  Every thread recomputes the pivot of column j (a length-j dot product over
+// row j, broadcast reads), so one barrier per column suffices; thread i owns row i.  Returns false when a pivot is not
+// positive (Eigen LLT / oracle criterion).
 template <int T>
-__device__ bool chol_factor_aug(double* A, int np, int* flag) {
+__device__ bool chol_factor_aug(double* A, int np) {
     const int tid = threadIdx.x, n = np - 1;
-    if (tid == 0) *flag = 1;
-    __syncthreads();
+    bool ok = true;
     for (int j = 0; j < n; ++j) {
-        const double d = A[tri(j, j)];
-        if (!(d > 0.0)) { if (tid == 0) *flag = 0; break; }     // uniform: every thread reads the same value
-        const double rinv = 1.0 / sqrt(d);
-        __syncthreads();                                        // everyone has read the pivot
-        for (int i = j + tid; i < np; i += T) A[tri(i, j)] = (i == j) ? sqrt(d) : A[tri(i, j)] * rinv;
-        __syncthreads();
-        // trailing update: rows i = j+1 .. np-1, columns k = j+1 .. min(i, n-1)
-        const int rem = np - 1 - j;                              // rows below j
-        for (int e = tid; e < rem * (rem + 1) / 2; e += T) {
-            int a = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
-            while (a * (a + 1) / 2 > e) --a;
-            while ((a + 1) * (a + 2) / 2 <= e) ++a;
-            const int b = e - a * (a + 1) / 2;
-            const int i = j + 1 + a, k = j + 1 + b;
-            if (k >= n && i >= n) continue;                     // (rhs, rhs) corner is unused
-            A[tri(i, k)] -= A[tri(i, j)] * A[tri(k, j)];
+        const double* rj = A + tri(j, 0);
+        double d0 = rj[j], d1 = 0.0, d2 = 0.0, d3 = 0.0;
+        int k = 0;
+        for (; k + 4 <= j; k += 4) { d0 -= rj[k] * rj[k]; d1 -= rj[k + 1] * rj[k + 1]; d2 -= rj[k + 2] * rj[k + 2]; d3 -= rj[k + 3] * rj[k + 3]; }
+        for (; k < j; ++k) d0 -= rj[k] * rj[k];
+        const double d = (d0 + d1) + (d2 + d3);
+        if (!(d > 0.0)) { ok = false; break; }              // uniform: every thread computed the same d from the same data
+        const double ljj = sqrt(d), inv = 1.0 / ljj;
+        for (int i = j + 1 + tid; i < np; i += T) {
+            double* ri = A + tri(i, 0);
+            double s0 = ri[j], s1 = 0.0, s2 = 0.0, s3 = 0.0;
+            int q = 0;
+            for (; q + 4 <= j; q += 4) { s0 -= ri[q] * rj[q]; s1 -= ri[q + 1] * rj[q + 1]; s2 -= ri[q + 2] * rj[q + 2]; s3 -= ri[q + 3] * rj[q + 3]; }
+            for (; q < j; ++q) s0 -= ri[q] * rj[q];
+            ri[j] = ((s0 + s1) + (s2 + s3)) * inv;
         }
         __syncthreads();
+        if (tid == 0) A[tri(j, j)] = ljj;                   // nobody reads the raw diagonal of column j any more
     }
     __syncthreads();
-    return *flag != 0;
+    return ok;
 }
 
 // back substitution L^T y = z with one warp (z = row n of the augmented factor)
@@ -372,14 +389,13 @@ __global__ void __launch_bounds__(T, 4) fit_single_kernel(const FitConst* __rest
         if (first)
             for (int k = tid; k < n; k += T) S.scale[k] = 1.0 / (1.0 + sqrt(H[tri(k, k)]));
         __syncthreads();
-        for (int e = tid; e < ntri; e += T) {
-            int i = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
-            while (i * (i + 1) / 2 > e) --i;
-            while ((i + 1) * (i + 2) / 2 <= e) ++i;
-            const int j = e - i * (i + 1) / 2;
-            const double hv = H[e] * S.scale[i] * S.scale[j];
-            Hs[e] = hv;
-            if (i == j) S.hdiag[i] = hv;
+        for (int i = tid >> 5; i < n; i += T / 32) {
+            const double si = S.scale[i];
+            for (int j = tid & 31; j <= i; j += 32) {
+                const double hv = H[tri(i, j)] * si * S.scale[j];
+                Hs[tri(i, j)] = hv;
+                if (i == j) S.hdiag[i] = hv;
+            }
         }
         double gm = 0.0;
         for (int k = tid; k < n; k += T) {
@@ -455,17 +471,14 @@ __global__ void __launch_bounds__(T, 4) fit_single_kernel(const FitConst* __rest
             __syncthreads();
             reuse_diagonal = true;
             bool step_valid = false;
-            if (chol_factor_aug<T>(A, n + 1, &S.flag)) {
+            if (chol_factor_aug<T>(A, n + 1)) {
                 if (tid < 32) chol_backsolve_warp(A, n, S.y);
                 __syncthreads();
                 // model_cost_change = -(J step)^T (r + J step / 2), step = -y:  y^T gs - y^T H_s y / 2
                 double v = 0.0, fin = 0.0;
-                for (int e = tid; e < ntri; e += T) {
-                    int i = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
-                    while (i * (i + 1) / 2 > e) --i;
-                    while ((i + 1) * (i + 2) / 2 <= e) ++i;
-                    const int j = e - i * (i + 1) / 2;
-                    v -= (i == j ? 0.5 : 1.0) * Hs[e] * S.y[i] * S.y[j];
+                for (int i = tid >> 5; i < n; i += T / 32) {
+                    const double yi = S.y[i];
+                    for (int j = tid & 31; j <= i; j += 32) v -= (i == j ? 0.5 : 1.0) * Hs[tri(i, j)] * yi * S.y[j];
                 }
                 for (int k = tid; k < n; k += T) { v += S.y[k] * S.gs[k]; fin += isfinite(S.y[k]) ? 0.0 : 1.0; }
                 mcc = block_sum<T>(v, S.red);

@@ -1,0 +1,89 @@
+"""Small drivers for ncu captures and quick timings: `python tools/prof.py forward [B]`, `python tools/prof.py fit [frames]`."""
+import ctypes as C
+import importlib
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+pkg = lambda n="": importlib.import_module("3dbodyanimation_b200" + ("." + n if n else ""))
+synth, api, capi = pkg("synth"), pkg("api"), pkg("_capi")
+lib = capi.lib()
+dev = torch.device("cuda", 0)
+P = lambda t: C.c_void_p(t.data_ptr())
+
+
+def timed(fn, reps):
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(reps):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    return float(np.mean(ts)), float(np.min(ts))
+
+
+def forward(B, dtype="f32", reps=5):
+    gm = api.AvatarModel(synth.make_model())
+    fin = synth.make_forward_inputs(B, 5)
+    td = torch.float32 if dtype == "f32" else torch.float64
+    code = capi.F32 if dtype == "f32" else capi.F64
+    w, p, r = (torch.from_numpy(fin[k]).to(td).to(dev) for k in ("w", "p", "r"))
+    cloud = torch.empty(B, gm.numPoints, 3, dtype=td, device=dev)
+    jp, jt = torch.empty(B, 24, 3, dtype=td, device=dev), torch.empty(B, 24, 12, dtype=td, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    fn = lambda: capi.check(lib.b3d_smpl_forward_dev(gm.h, B, code, P(w), P(p), P(r), P(cloud), P(jp), P(jt), 0, C.c_void_p(st)), "fwd")
+    mean, best = timed(fn, reps)
+    es = 4 if dtype == "f32" else 8
+    gb = B * (85036 * es / 4) / 1e9
+    print(f"forward {dtype} B={B}: {mean:.3f} ms (best {best:.3f}) -> {gb / mean * 1e3:.0f} GB/s algorithmic, {B * gm.numPoints / mean * 1e3:.3e} verts/s")
+
+
+def fit(n, mode="C2", reps=3):
+    model_np = synth.make_model()
+    prior = synth.load_pose_prior(os.path.join(ROOT, "tests", "golden", "pose_prior.txt"))
+    gm, gg = api.AvatarModel(model_np), api.GaussianMixture(prior=prior)
+    if mode == "C2":
+        fr = synth.make_frames(model_np, n, 1000, shape=True, prior=prior)
+        opts, g = api.fit_opts(cam=(synth.FX, synth.FY, synth.CX, synth.CY), mode=1, max_iters=100, beta_pose=20.0, beta_shape=30.0), gg.h
+    else:
+        fr = synth.make_frames(model_np, n, 1000, shape=False)
+        opts, g = api.fit_opts(cam=(synth.FX, synth.FY, synth.CX, synth.CY), mode=0, max_iters=100, beta_pose=20.0, beta_shape=30.0), None
+    kps = torch.from_numpy(np.ascontiguousarray(fr["kps"]).view(np.uint8).reshape(n, -1)).to(dev)
+    nkp, R0, s0, w0 = (torch.from_numpy(np.ascontiguousarray(fr[k])).to(dev) for k in ("nkp", "R0", "sim3", "w"))
+    s3, w = s0.clone(), w0.clone()
+    jaa = torch.zeros(n, 24, 3, dtype=torch.float64, device=dev)
+    us = torch.zeros(n, dtype=torch.uint8, device=dev)
+    ni, te = torch.zeros(n, dtype=torch.int32, device=dev), torch.zeros(n, dtype=torch.int32, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+
+    def fn():
+        s3.copy_(s0); w.copy_(w0)
+        capi.check(lib.b3d_fit_single_dev(gm.h, g, C.byref(opts), n, P(kps), P(nkp), P(R0), P(s3), P(w), P(jaa), P(us), None, 0, P(ni), P(te),
+                                          C.c_void_p(st)), "fit")
+    mean, best = timed(fn, reps)
+    it = ni.cpu().numpy()
+    print(f"fit {mode} frames={n}: {mean:.3f} ms (best {best:.3f}) -> {n / mean * 1e3:.0f} frames/s; LM iterations mean {it.mean():.1f} max {it.max()} "
+          f"sum {it.sum()}; {mean * 1e3 / max(it.max(), 1):.1f} us per iteration of the slowest frame; usable {int(us.sum())}")
+
+
+if __name__ == "__main__":
+    what = sys.argv[1]
+    if what == "forward":
+        forward(int(sys.argv[2]) if len(sys.argv) > 2 else 16384, sys.argv[3] if len(sys.argv) > 3 else "f32")
+    elif what == "fit":
+        fit(int(sys.argv[2]) if len(sys.argv) > 2 else 1000, sys.argv[3] if len(sys.argv) > 3 else "C2")
+    elif what == "sweep":
+        for b in (1, 16, 256, 1024, 4096, 16384, 65536):
+            forward(b, "f32")
+        for b in (1024, 16384):
+            forward(b, "f64")
+        for n in (100, 1000, 8000):
+            fit(n, "C2")
+        fit(100, "C1"); fit(1000, "C1")
