@@ -12,11 +12,17 @@
 // Residual blocks: <= 17 reprojection blocks + Huber (lm_device.cuh), pose prior PosePriorAAAnalytic
 // (Sim3BA.h:245-320: GMM min-component with the reference's Jacobian that omits sqrt(1/2), or L2), shape prior
 // ShapePriorL2Analytic (Sim3BA.h:323-346).
+//
+// The kernel is latency-bound (one frame's iterations are a serial chain), so the layout aims at few barriers and short
+// dependent chains: J^T J is assembled by element owners walking a per-column keypoint bitmask (no per-keypoint phases),
+// the Cholesky keeps running diagonals in registers and splits each row's dot product over a thread pair (one barrier per
+// column), and the scaled normal equations stay in shared memory across rejected steps.
 #include "lm_device.cuh"
+#include "ls_poly.cuh"
 
 namespace b3d {
 
-constexpr int FS_THREADS = 128;
+constexpr int FS_THREADS = 256;
 constexpr int NAUG = NFULL + 1;                       // augmented with the right-hand side row
 constexpr int LTRI = NAUG * (NAUG + 1) / 2;           // 3828 packed doubles
 constexpr int HTRI = NFULL * (NFULL + 1) / 2;         // 3741
@@ -27,141 +33,50 @@ constexpr double kMinDiagonal = 1e-6, kMaxDiagonal = 1e32;
 constexpr double kMinRelativeDecrease = 1e-3;
 constexpr double kFunctionTolerance = 1e-6, kGradientTolerance = 1e-10, kParameterTolerance = 1e-8;
 constexpr int kMaxConsecutiveInvalidSteps = 5;
-constexpr double kSufficientDecrease = 1e-4, kMinLineSearchStepSize = 1e-9;
-constexpr int kMaxLineSearchIters = 20;
-constexpr double kLsContractLo = 1e-3, kLsContractHi = 0.6;   // max_/min_line_search_step_contraction
+
+// Optional phase timing (debug hook, off unless b3d_debug_phase_timing(1) was called): cycles of block 0 per phase.
+__device__ long long g_phase_cycles[16];
+__device__ long long g_block_cycles[1024];   // total cycles and line-search evaluations per block (debug)
+__device__ int g_block_ls[1024];
+__device__ int g_phase_on;
+struct PhaseTimer {
+    long long t;
+    bool on;
+    __device__ void start() { on = g_phase_on != 0 && blockIdx.x == 0 && threadIdx.x == 0; if (on) t = clock64(); }
+    __device__ void mark(int i) { if (on) { const long long u = clock64(); g_phase_cycles[i] += u - t; t = u; } }
+};
 
 struct GmmTmp {
     double h[GMM_MAXC][NPRI];     // L_i^T (x - mu_i)
     double d[GMM_MAXC][NPRI];     // x - mu_i
     double p[GMM_MAXC];           // |h_i|^2 / 2 - consts_log_i
     double sq[GMM_MAXC];          // |sqrt(1/2) h_i|^2
+    double part[3][NPRI];         // partial sums of L_c h
 };
 
 union SingleUnion {
     EvalTmp ev;
     GmmTmp gm;
-    double L[LTRI];
+    double L[LTRI];               // damped system being factored, last row = right-hand side
 };
 
 struct SingleSmem {
     EvalOut out;
     SingleUnion u;
+    double Hs[HTRI];                       // Jacobi-scaled J^T J (free layout, packed lower), kept across rejected steps
     double xfull[NFULL], cfull[NFULL];     // current / candidate parameters, 86-layout
-    double g[NFULL], gs[NFULL], gc[NFULL]; // gradient (free layout): unscaled, Jacobi-scaled, at a line-search point
-    double scale[NFULL], diag[NFULL], hdiag[NFULL], y[NFULL], delta[NFULL];
+    double g[NFULL], gs[NFULL], gc[NFULL]; // gradient (free layout): unscaled, Jacobi-scaled, saved copy during a line search
+    double scale[NFULL], diag[NFULL], y[NFULL], delta[NFULL], invd[NFULL];
     double gpri[NPRI];                     // pose-prior gradient, pose-dim layout
     double R0[9];
     double red[40];
+    double piv[2];                         // pivot of the next Cholesky column: value, 1/sqrt
     double ls_step;
-    int32_t comp, flag;
-    int16_t fcol[MAXKP][NNZPAD];          // free-layout column of each Jacobian slot (-1 = held constant)
+    int32_t comp;
+    uint32_t kmask[NFULL];                 // per full-layout column: keypoints whose Jacobian touches it
+    uint8_t slot[MAXKP][NFULL + 2];        // per keypoint: local slot of each full-layout column
+    int8_t fcol[MAXKP][NNZPAD];            // per keypoint slot: free-layout column, -1 = held constant
 };
-
-// ---- polynomial helpers for the (rare) Armijo interpolation: thread 0 only --------------------------------------
-struct LsSample { double x, value, gradient; bool valid; };
-
-__device__ double poly_eval(const double* p, int nc, double x) { double v = 0; for (int i = 0; i < nc; ++i) v = v * x + p[i]; return v; }
-
-// Gaussian elimination with full pivoting (Eigen FullPivLU as used by ceres polynomial.cc); n <= 6
-__device__ bool lu_solve(double* A, int n, double* b, double* x) {
-    int perm[6];
-    for (int i = 0; i < n; ++i) perm[i] = i;
-    for (int k = 0; k < n; ++k) {
-        int pr = k, pc = k; double best = 0.0;
-        for (int i = k; i < n; ++i) for (int j = k; j < n; ++j) if (fabs(A[i * n + j]) > best) { best = fabs(A[i * n + j]); pr = i; pc = j; }
-        if (best == 0.0) return false;
-        if (pr != k) { for (int j = 0; j < n; ++j) { double t = A[k * n + j]; A[k * n + j] = A[pr * n + j]; A[pr * n + j] = t; } double t = b[k]; b[k] = b[pr]; b[pr] = t; }
-        if (pc != k) { for (int i = 0; i < n; ++i) { double t = A[i * n + k]; A[i * n + k] = A[i * n + pc]; A[i * n + pc] = t; } int t = perm[k]; perm[k] = perm[pc]; perm[pc] = t; }
-        for (int i = k + 1; i < n; ++i) {
-            const double f = A[i * n + k] / A[k * n + k];
-            for (int j = k; j < n; ++j) A[i * n + j] -= f * A[k * n + j];
-            b[i] -= f * b[k];
-        }
-    }
-    double z[6];
-    for (int i = n - 1; i >= 0; --i) { double s = b[i]; for (int j = i + 1; j < n; ++j) s -= A[i * n + j] * z[j]; z[i] = s / A[i * n + i]; }
-    for (int i = 0; i < n; ++i) x[perm[i]] = z[i];
-    return true;
-}
-
-// real parts of the roots of a polynomial of degree <= 4 (coefficients highest first): Aberth-Ehrlich iteration
-__device__ int poly_root_real_parts(const double* pin, int nc, double* out) {
-    int lead = 0;
-    while (lead + 1 < nc && pin[lead] == 0.0) ++lead;
-    const double* p = pin + lead;
-    const int deg = nc - lead - 1;
-    if (deg <= 0) return 0;
-    if (deg == 1) { out[0] = -p[1] / p[0]; return 1; }
-    if (deg == 2) {
-        const double a = p[0], b = p[1], c = p[2];
-        const double D = b * b - 4 * a * c, sD = sqrt(fabs(D));
-        if (D >= 0) {
-            if (b >= 0) { out[0] = (-b - sD) / (2.0 * a); out[1] = (2.0 * c) / (-b - sD); }
-            else { out[0] = (2.0 * c) / (-b + sD); out[1] = (-b + sD) / (2.0 * a); }
-        } else { out[0] = out[1] = -b / (2.0 * a); }
-        return 2;
-    }
-    double ar[6], zr[5], zi[5];
-    for (int i = 0; i <= deg; ++i) ar[i] = p[i] / p[0];
-    double rad = 0;
-    for (int i = 1; i <= deg; ++i) rad = fmax(rad, fabs(ar[i]));
-    rad = 1.0 + rad;
-    for (int i = 0; i < deg; ++i) { double s, c; sincos(2 * 3.14159265358979323846 * i / deg + 0.4, &s, &c); zr[i] = rad * 0.5 * c; zi[i] = rad * 0.5 * s; }
-    for (int it = 0; it < 500; ++it) {
-        double change = 0;
-        for (int i = 0; i < deg; ++i) {
-            double fr = ar[0], fi = 0, dr = 0, di = 0;
-            for (int k = 1; k <= deg; ++k) {
-                double t = dr * zr[i] - di * zi[i] + fr; di = dr * zi[i] + di * zr[i] + fi; dr = t;
-                t = fr * zr[i] - fi * zi[i] + ar[k]; fi = fr * zi[i] + fi * zr[i]; fr = t;
-            }
-            if (fr == 0.0 && fi == 0.0) continue;
-            const double dd = dr * dr + di * di;
-            const double rr = (fr * dr + fi * di) / dd, ri = (fi * dr - fr * di) / dd;   // ratio = f / df
-            double sr = 0, si = 0;
-            for (int j = 0; j < deg; ++j) if (j != i) { const double ur = zr[i] - zr[j], ui = zi[i] - zi[j], uu = ur * ur + ui * ui; sr += ur / uu; si -= ui / uu; }
-            const double er = 1.0 - (rr * sr - ri * si), ei = -(rr * si + ri * sr);
-            const double ee = er * er + ei * ei;
-            const double zr_d = (rr * er + ri * ei) / ee, zi_d = (ri * er - rr * ei) / ee;
-            zr[i] -= zr_d; zi[i] -= zi_d;
-            change = fmax(change, sqrt(zr_d * zr_d + zi_d * zi_d));
-        }
-        if (change < 1e-15 * rad) break;
-    }
-    for (int i = 0; i < deg; ++i) out[i] = zr[i];
-    return deg;
-}
-
-// ceres MinimizeInterpolatingPolynomial: every sample carries value and gradient
-__device__ double minimize_interpolating_polynomial(const LsSample* s, int ns, double x_min, double x_max) {
-    const int nc = 2 * ns, degree = nc - 1;
-    double lhs[36], rhs[6], coef[6];
-    for (int i = 0; i < nc * nc; ++i) lhs[i] = 0.0;
-    int row = 0;
-    for (int q = 0; q < ns; ++q) {
-        for (int j = 0; j <= degree; ++j) lhs[row * nc + j] = pow(s[q].x, (double)(degree - j));
-        rhs[row++] = s[q].value;
-        for (int j = 0; j < degree; ++j) lhs[row * nc + j] = (degree - j) * pow(s[q].x, (double)(degree - j - 1));
-        rhs[row++] = s[q].gradient;
-    }
-    double best_x = (x_min + x_max) / 2.0;
-    if (!lu_solve(lhs, nc, rhs, coef)) return best_x;
-    double best_v = poly_eval(coef, nc, best_x);
-    const double vmin = poly_eval(coef, nc, x_min);
-    if (vmin < best_v) { best_v = vmin; best_x = x_min; }
-    const double vmax = poly_eval(coef, nc, x_max);
-    if (vmax < best_v) { best_v = vmax; best_x = x_max; }
-    double dcoef[5], roots[5];
-    for (int i = 0; i < degree; ++i) dcoef[i] = (degree - i) * coef[i];
-    const int nr = poly_root_real_parts(dcoef, degree, roots);
-    for (int i = 0; i < nr; ++i) {
-        if (roots[i] < x_min || roots[i] > x_max) continue;
-        const double v = poly_eval(coef, nc, roots[i]);
-        if (v < best_v) { best_v = v; best_x = roots[i]; }
-    }
-    return best_x;
-}
 
 // ---- GMM pose prior (GaussianMixture::residual, external/avatar/GaussianMixture.cpp:94-113) --------------------
 // Returns 0.5 |beta r|^2 of the prior block and sets S.comp; with JAC also S.gpri = J^T r (pose-dim layout), where
@@ -172,18 +87,34 @@ __device__ double gmm_eval(const FitConst* __restrict__ C, const double* xj /*69
     GmmTmp& G = S.u.gm;
     for (int t = tid; t < nc * NPRI; t += T) G.d[t / NPRI][t % NPRI] = xj[t % NPRI] - C->gmm_mean[t];
     __syncthreads();
-    for (int t = tid; t < nc * NPRI; t += T) {
-        const int i = t / NPRI, k = t % NPRI;
-        const double* __restrict__ L = C->gmm_L + (size_t)i * NPRI * NPRI + k;    // column k: consecutive threads, consecutive addresses
+    // h_i[k] = sum_{m >= k} L_i[m][k] d_i[m].  A task takes columns k and 68 - k of one component, so every task has the same
+    // length (70 terms) and consecutive threads read consecutive addresses of L.
+    constexpr int HALF = (NPRI + 1) / 2;   // 35
+    for (int t = tid; t < nc * HALF; t += T) {
+        const int i = t / HALF, k0 = t % HALF, k1 = NPRI - 1 - k0;
+        const double* __restrict__ L = C->gmm_L + (size_t)i * NPRI * NPRI;
         const double* dd = G.d[i];
-        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-        int m = k;
-        for (; m + 4 <= NPRI; m += 4) {
-            a0 += __ldg(L + m * NPRI) * dd[m];           a1 += __ldg(L + (m + 1) * NPRI) * dd[m + 1];
-            a2 += __ldg(L + (m + 2) * NPRI) * dd[m + 2]; a3 += __ldg(L + (m + 3) * NPRI) * dd[m + 3];
+        // the two columns are walked together, eight independent loads in flight per pass
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0, b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;
+        const double* __restrict__ La = L + k0;
+        const double* __restrict__ Lb = L + k1;
+        int m = k0;
+        for (; m + 8 <= k1; m += 8) {     // rows k0 .. k1-1 touch column k0 only
+            const double v0 = __ldg(La + m * NPRI), v1 = __ldg(La + (m + 1) * NPRI), v2 = __ldg(La + (m + 2) * NPRI), v3 = __ldg(La + (m + 3) * NPRI);
+            const double v4 = __ldg(La + (m + 4) * NPRI), v5 = __ldg(La + (m + 5) * NPRI), v6 = __ldg(La + (m + 6) * NPRI), v7 = __ldg(La + (m + 7) * NPRI);
+            a0 += v0 * dd[m]; a1 += v1 * dd[m + 1]; a2 += v2 * dd[m + 2]; a3 += v3 * dd[m + 3];
+            a0 += v4 * dd[m + 4]; a1 += v5 * dd[m + 5]; a2 += v6 * dd[m + 6]; a3 += v7 * dd[m + 7];
         }
-        for (; m < NPRI; ++m) a0 += __ldg(L + m * NPRI) * dd[m];
-        G.h[i][k] = (a0 + a1) + (a2 + a3);
+        for (; m < k1; ++m) a0 += __ldg(La + m * NPRI) * dd[m];
+        for (m = k1; m + 4 <= NPRI; m += 4) {   // rows k1 .. 68 touch both columns
+            const double v0 = __ldg(La + m * NPRI), v1 = __ldg(La + (m + 1) * NPRI), v2 = __ldg(La + (m + 2) * NPRI), v3 = __ldg(La + (m + 3) * NPRI);
+            const double u0 = __ldg(Lb + m * NPRI), u1 = __ldg(Lb + (m + 1) * NPRI), u2 = __ldg(Lb + (m + 2) * NPRI), u3 = __ldg(Lb + (m + 3) * NPRI);
+            a0 += v0 * dd[m]; a1 += v1 * dd[m + 1]; a2 += v2 * dd[m + 2]; a3 += v3 * dd[m + 3];
+            b0 += u0 * dd[m]; b1 += u1 * dd[m + 1]; b2 += u2 * dd[m + 2]; b3 += u3 * dd[m + 3];
+        }
+        for (; m < NPRI; ++m) { a0 += __ldg(La + m * NPRI) * dd[m]; b0 += __ldg(Lb + m * NPRI) * dd[m]; }
+        G.h[i][k0] = (a0 + a1) + (a2 + a3);
+        if (k1 != k0) G.h[i][k1] = (b0 + b1) + (b2 + b3);
     }
     __syncthreads();
     if (tid < nc) {
@@ -196,168 +127,205 @@ __device__ double gmm_eval(const FitConst* __restrict__ C, const double* xj /*69
     __syncthreads();
     int c = 0;
     double best = DBL_MAX;
-    for (int i = 0; i < nc; ++i) { const double p = G.p[i]; if (p < best) { best = p; c = i; } }
+    for (int i = 0; i < nc; ++i) { const double p = G.p[i]; if (p < best) { best = p; c = i; } }   // strict '<': first wins ties
     if (tid == 0) S.comp = c;
     // residual = beta [h_c ; sqrt(-consts_log_c)]  =>  cost = 0.5 beta^2 (|h_c|^2 - consts_log_c)
     const double cost = 0.5 * C->beta_pose * C->beta_pose * (G.sq[c] + (-C->gmm_consts[c]));
     if (JAC) {
-        const double f = C->beta_pose * C->beta_pose * sqrt(0.5);
-        const double* LT = C->gmm_LT + (size_t)c * NPRI * NPRI;
-        for (int m = tid; m < NPRI; m += T) {
-            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-            int k = 0;
-            for (; k + 4 <= m + 1; k += 4) {
-                a0 += __ldg(LT + k * NPRI + m) * G.h[c][k];           a1 += __ldg(LT + (k + 1) * NPRI + m) * G.h[c][k + 1];
-                a2 += __ldg(LT + (k + 2) * NPRI + m) * G.h[c][k + 2]; a3 += __ldg(LT + (k + 3) * NPRI + m) * G.h[c][k + 3];
-            }
-            for (; k <= m; ++k) a0 += __ldg(LT + k * NPRI + m) * G.h[c][k];
-            S.gpri[m] = f * ((a0 + a1) + (a2 + a3));
+        // J^T r = beta^2 sqrt(1/2) L_c h: row m split over three threads
+        const double* __restrict__ LT = C->gmm_LT + (size_t)c * NPRI * NPRI;
+        if (tid < 3 * NPRI) {
+            const int part = tid / NPRI, m = tid % NPRI;
+            double a0 = 0.0, a1 = 0.0;
+            int k = part;
+            for (; k + 3 <= m; k += 6) { a0 += __ldg(LT + k * NPRI + m) * G.h[c][k]; a1 += __ldg(LT + (k + 3) * NPRI + m) * G.h[c][k + 3]; }
+            for (; k <= m; k += 3) a0 += __ldg(LT + k * NPRI + m) * G.h[c][k];
+            G.part[part][m] = a0 + a1;
         }
+        __syncthreads();
+        const double f = C->beta_pose * C->beta_pose * sqrt(0.5);
+        for (int m = tid; m < NPRI; m += T) S.gpri[m] = f * ((G.part[0][m] + G.part[1][m]) + G.part[2][m]);
     }
     __syncthreads();
     return cost;
 }
 
 // ---- cost (and with JAC the normal equations) at parameters xf --------------------------------------------------
-// JAC: S.u.L holds the packed UNSCALED J^T J (free layout) on return and S.g the unscaled gradient.
+// JAC: on return S.Hs holds the packed J^T J in the free layout — scaled by S.scale unless `first`, in which case it is
+// unscaled and the caller derives the Jacobi scaling from its diagonal — and S.g the unscaled gradient J^T r.
 template <int T, bool JAC>
-__device__ double evaluate(const FitConst* __restrict__ C, const double* xf, const b3d_kp* __restrict__ kps, int nkp, SingleSmem& S) {
+__device__ __noinline__ double evaluate(const FitConst* __restrict__ C, const double* xf, const b3d_kp* __restrict__ kps, int nkp, SingleSmem& S,
+                           bool first) {
     const int tid = threadIdx.x, n = C->n;
+    PhaseTimer pe;
+    pe.start();
     eval_reproj<T, JAC>(C, xf, kps, nkp, S.R0, S.u.ev, S.out);
+    pe.mark(JAC ? 9 : 12);
     double cost = 0.0;
     for (int k = 0; k < nkp; ++k) cost += S.out.kcost[k];
     double pcost = 0.0;
     const bool pose_prior = C->beta_pose > 0.0;
-    if (pose_prior && C->use_gmm) pcost = gmm_eval<T, JAC>(C, xf + IDX_JAA, S);   // aliases S.u.ev: eval temporaries are dead
+    const bool gmm = pose_prior && C->use_gmm;
+    if (gmm) pcost = gmm_eval<T, JAC>(C, xf + IDX_JAA, S);   // aliases S.u.ev: the evaluation temporaries are dead
     // the remaining prior costs are sums of squares over <= 79 terms: fixed-order block sum
     double v = 0.0;
-    if (pose_prior && !C->use_gmm)
+    if (pose_prior && !gmm)
         for (int k = tid; k < NPRI; k += T) { const double r = xf[IDX_JAA + k] * C->beta_pose; v += 0.5 * r * r; }
     if (C->has_w)
         for (int k = tid; k < NS; k += T) { const double r = xf[IDX_W + k] * C->beta_shape; v += 0.5 * r * r; }
+    if (JAC) {   // column -> keypoint tables for the assembly below (published by the barriers inside block_sum)
+        for (int k = tid; k < NFULL; k += T) S.kmask[k] = 0u;
+    }
     cost += pcost + block_sum<T>(v, S.red);
+    pe.mark(JAC ? 10 : 13);
     if (!JAC) return cost;
 
-    // ---- J^T J and J^T r ----
-    __syncthreads();
-    double* H = S.u.L;
-    for (int e = tid; e < n * (n + 1) / 2; e += T) H[e] = 0.0;
-    for (int k = tid; k < n; k += T) S.g[k] = 0.0;
     for (int t = tid; t < nkp * NNZPAD; t += T) {
         const int k = t / NNZPAD, sl = t % NNZPAD;
-        S.fcol[k][sl] = sl < S.out.jnnz[k] ? (int16_t)C->col_of[S.out.jcol[k][sl]] : (int16_t)-1;
-    }
-    __syncthreads();
-    for (int k = 0; k < nkp; ++k) {
-        const int nnz = S.out.jnnz[k];
-        const double r0 = S.out.res[k][0], r1 = S.out.res[k][1];
-        const double* J0 = S.out.J[k][0];
-        const double* J1 = S.out.J[k][1];
-        for (int i = tid >> 5; i < nnz; i += T / 32) {          // row of the outer product: one warp; columns: lanes
-            const int ci = S.fcol[k][i];
-            if (ci < 0) continue;
-            const double a0 = J0[i], a1 = J1[i];
-            for (int j = tid & 31; j <= i; j += 32) {
-                const int cj = S.fcol[k][j];
-                if (cj < 0) continue;
-                H[ci >= cj ? tri(ci, cj) : tri(cj, ci)] += a0 * J0[j] + a1 * J1[j];
-                if (i == j) S.g[ci] += a0 * r0 + a1 * r1;
-            }
-        }
-        __syncthreads();
-    }
-    // priors
-    if (pose_prior) {
-        const double b2 = C->beta_pose * C->beta_pose;
-        if (C->use_gmm) {
-            const double* P = C->gmm_P + (size_t)S.comp * NPRI * NPRI;
-            for (int i = tid >> 5; i < NPRI; i += T / 32) {
-                const int ci = C->col_of[IDX_JAA + i];
-                if (ci < 0) continue;
-                for (int j = tid & 31; j <= i; j += 32) {
-                    const int cj = C->col_of[IDX_JAA + j];
-                    if (cj >= 0) H[tri(ci, cj)] += b2 * P[i * NPRI + j];     // free order preserves pose-dim order, so ci >= cj
-                }
-            }
-            for (int k = tid; k < NPRI; k += T) { const int ck = C->col_of[IDX_JAA + k]; if (ck >= 0) S.g[ck] += S.gpri[k]; }
-        } else {
-            for (int k = tid; k < NPRI; k += T) {
-                const int ck = C->col_of[IDX_JAA + k];
-                if (ck >= 0) { H[tri(ck, ck)] += b2; S.g[ck] += b2 * xf[IDX_JAA + k]; }
-            }
+        if (sl < S.out.jnnz[k]) {
+            const int col = S.out.jcol[k][sl];
+            S.slot[k][col] = (uint8_t)sl;
+            S.fcol[k][sl] = (int8_t)C->col_of[col];
+            atomicOr(&S.kmask[col], 1u << k);
         }
     }
-    if (C->has_w) {
-        const double b2 = C->beta_shape * C->beta_shape;
-        for (int k = tid; k < NS; k += T) { const int ck = C->col_of[IDX_W + k]; H[tri(ck, ck)] += b2; S.g[ck] += b2 * xf[IDX_W + k]; }
+    for (int e = tid; e < n * (n + 1) / 2; e += T) S.Hs[e] = 0.0;
+    __syncthreads();
+    // ---- J^T J and J^T r of the reprojection blocks: a warp owns row i of H and walks the keypoints that touch column i in
+    // keypoint order; its lanes cover that keypoint's non-zero slots.  No two warps write the same element: no barriers. ----
+    const int lane = tid & 31;
+    for (int i = tid >> 5; i < n; i += T / 32) {
+        const int a = C->free_idx[i];
+        uint32_t m = S.kmask[a];
+        double gacc = 0.0;
+        while (m) {
+            const int k = __ffs(m) - 1;
+            m &= m - 1;
+            const int sa = S.slot[k][a], nnz = S.out.jnnz[k];
+            const double a0 = S.out.J[k][0][sa], a1 = S.out.J[k][1][sa];
+            for (int sb = lane; sb < nnz; sb += 32) {
+                const int j = S.fcol[k][sb];
+                if (j >= 0 && j <= i) S.Hs[tri(i, j)] += a0 * S.out.J[k][0][sb] + a1 * S.out.J[k][1][sb];
+            }
+            gacc += a0 * S.out.res[k][0] + a1 * S.out.res[k][1];
+        }
+        if (lane == 0) S.g[i] = gacc;
     }
     __syncthreads();
+    // ---- priors and Jacobi scaling ----
+    const double bp2 = C->beta_pose * C->beta_pose, bs2 = C->beta_shape * C->beta_shape;
+    const double* __restrict__ P = gmm ? C->gmm_P + (size_t)S.comp * NPRI * NPRI : nullptr;
+    for (int i = tid >> 5; i < n; i += T / 32) {
+        const int a = C->free_idx[i];
+        const double si = first ? 1.0 : S.scale[i];
+        for (int j = lane; j <= i; j += 32) {
+            const int b = C->free_idx[j];
+            double acc = S.Hs[tri(i, j)];
+            if (pose_prior && a >= IDX_JAA && a < IDX_W && b >= IDX_JAA) {
+                if (gmm) acc += bp2 * __ldg(P + (a - IDX_JAA) * NPRI + (b - IDX_JAA));
+                else if (a == b) acc += bp2;
+            }
+            if (C->has_w && a >= IDX_W && a == b) acc += bs2;
+            S.Hs[tri(i, j)] = first ? acc : acc * si * S.scale[j];
+        }
+    }
+    for (int i = tid; i < n; i += T) {
+        const int a = C->free_idx[i];
+        double acc = S.g[i];
+        if (pose_prior && a >= IDX_JAA && a < IDX_W) acc += gmm ? S.gpri[a - IDX_JAA] : bp2 * xf[a];
+        if (C->has_w && a >= IDX_W) acc += bs2 * xf[a];
+        S.g[i] = acc;
+    }
+    __syncthreads();
+    pe.mark(11);
     return cost;
 }
 
-// Cholesky (Crout / left-looking) of the packed lower matrix A (np x np; the last row is the right-hand side): on return rows
-// 0..np-2 hold L and row np-1 holds z = L^-1 rhs.  Every thread recomputes the pivot of column j (a length-j dot product over
-// row j, broadcast reads), so one barrier per column suffices; thread i owns row i.  Returns false when a pivot is not
-// positive (Eigen LLT / oracle criterion).
+// Cholesky (Crout) of the damped system in S.u.L, packed lower, (n + 1) rows: the last row is the right-hand side, so on
+// return it holds z = L^-1 rhs.  The thread pair p owns row p: the two halves split the length-j dot product of column j and
+// combine with one shuffle; the running diagonal A[p][p] - sum_k L[p][k]^2 lives in a register, and the owner of row j + 1
+// publishes the next pivot before the (single) barrier of column j.  Returns false when a pivot is not positive
+// (Eigen LLT / oracle criterion).
 template <int T>
-__device__ bool chol_factor_aug(double* A, int np) {
-    const int tid = threadIdx.x, n = np - 1;
+__device__ bool chol_factor_aug(SingleSmem& S, int n) {
+    static_assert(T >= 2 * NAUG, "one thread pair per row");
+    double* A = S.u.L;
+    const int tid = threadIdx.x, p = tid >> 1, half = tid & 1, np = n + 1;
+    double dg = p < n ? A[tri(p, p)] : 0.0;
+    if (tid == 0) {
+        const double il = rsqrt(dg);
+        S.piv[0] = dg; S.piv[1] = il; S.invd[0] = il;
+    }
     bool ok = true;
     for (int j = 0; j < n; ++j) {
-        const double* rj = A + tri(j, 0);
-        double d0 = rj[j], d1 = 0.0, d2 = 0.0, d3 = 0.0;
-        int k = 0;
-        for (; k + 4 <= j; k += 4) { d0 -= rj[k] * rj[k]; d1 -= rj[k + 1] * rj[k + 1]; d2 -= rj[k + 2] * rj[k + 2]; d3 -= rj[k + 3] * rj[k + 3]; }
-        for (; k < j; ++k) d0 -= rj[k] * rj[k];
-        const double d = (d0 + d1) + (d2 + d3);
-        if (!(d > 0.0)) { ok = false; break; }              // uniform: every thread computed the same d from the same data
-        const double ljj = sqrt(d), inv = 1.0 / ljj;
-        for (int i = j + 1 + tid; i < np; i += T) {
-            double* ri = A + tri(i, 0);
-            double s0 = ri[j], s1 = 0.0, s2 = 0.0, s3 = 0.0;
-            int q = 0;
-            for (; q + 4 <= j; q += 4) { s0 -= ri[q] * rj[q]; s1 -= ri[q + 1] * rj[q + 1]; s2 -= ri[q + 2] * rj[q + 2]; s3 -= ri[q + 3] * rj[q + 3]; }
-            for (; q < j; ++q) s0 -= ri[q] * rj[q];
-            ri[j] = ((s0 + s1) + (s2 + s3)) * inv;
-        }
         __syncthreads();
-        if (tid == 0) A[tri(j, j)] = ljj;                   // nobody reads the raw diagonal of column j any more
+        const double d = S.piv[0];
+        if (!(d > 0.0)) { ok = false; break; }                  // uniform
+        const double inv = S.piv[1];
+        const bool active = p > j && p < np;
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0, rij = 0.0;
+        double* ri = A + tri(active ? p : 0, 0);
+        if (active) {
+            const double* rj = A + tri(j, 0);
+            rij = ri[j];
+            int q = half;
+            for (; q + 6 < j; q += 8) {
+                const double a0 = ri[q], a1 = ri[q + 2], a2 = ri[q + 4], a3 = ri[q + 6];
+                const double b0 = rj[q], b1 = rj[q + 2], b2 = rj[q + 4], b3 = rj[q + 6];
+                s0 -= a0 * b0; s1 -= a1 * b1; s2 -= a2 * b2; s3 -= a3 * b3;
+            }
+            for (; q < j; q += 2) s0 -= ri[q] * rj[q];
+        }
+        double s = (s0 + s1) + (s2 + s3);
+        s += __shfl_xor_sync(0xffffffffu, s, 1);
+        if (active) {
+            const double val = (rij + s) * inv;
+            dg -= val * val;
+            if (half == 0) {
+                ri[j] = val;
+                if (p == j + 1 && p < n) {
+                    const double il = rsqrt(dg);
+                    S.piv[0] = dg; S.piv[1] = il; S.invd[p] = il;
+                }
+            }
+        }
     }
     __syncthreads();
     return ok;
 }
 
-// back substitution L^T y = z with one warp (z = row n of the augmented factor)
-__device__ void chol_backsolve_warp(const double* A, int n, double* y) {
+// back substitution L^T y = z with one warp (z = row n of the augmented factor; 1 / L_jj in S.invd)
+__device__ void chol_backsolve_warp(const SingleSmem& S, int n, double* y) {
+    const double* A = S.u.L;
     const int lane = threadIdx.x & 31;
     double z[3];
 #pragma unroll
     for (int q = 0; q < 3; ++q) { const int i = lane + 32 * q; z[q] = i < n ? A[tri(n, i)] : 0.0; }
     for (int j = n - 1; j >= 0; --j) {
-        const int owner = j & 31, slot = j >> 5;
-        double zj = slot == 0 ? z[0] : (slot == 1 ? z[1] : z[2]);
+        const int owner = j & 31, sl = j >> 5;
+        double zj = sl == 0 ? z[0] : (sl == 1 ? z[1] : z[2]);
         zj = __shfl_sync(0xffffffffu, zj, owner);
-        const double yj = zj / A[tri(j, j)];
+        const double yj = zj * S.invd[j];
         if (lane == owner) y[j] = yj;
+        const double* rj = A + tri(j, 0);
 #pragma unroll
-        for (int q = 0; q < 3; ++q) { const int i = lane + 32 * q; if (i < j) z[q] -= A[tri(j, i)] * yj; }
+        for (int q = 0; q < 3; ++q) { const int i = lane + 32 * q; if (i < j) z[q] -= rj[i] * yj; }
     }
 }
 
 template <int T>
-__global__ void __launch_bounds__(T, 4) fit_single_kernel(const FitConst* __restrict__ C, int B, const b3d_kp* __restrict__ kps_all,
-                                                       const int32_t* __restrict__ nkp_all, const double* __restrict__ R0_all,
-                                                       double* __restrict__ sim3, double* __restrict__ w, double* __restrict__ jointAA,
-                                                       uint8_t* __restrict__ usable, b3d_iter_record* __restrict__ trace, int trace_stride,
-                                                       int32_t* __restrict__ niters, int32_t* __restrict__ term, double* __restrict__ Hs_all) {
+__global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __restrict__ C, int B, const b3d_kp* __restrict__ kps_all,
+                                                          const int32_t* __restrict__ nkp_all, const double* __restrict__ R0_all,
+                                                          double* __restrict__ sim3, double* __restrict__ w, double* __restrict__ jointAA,
+                                                          uint8_t* __restrict__ usable, b3d_iter_record* __restrict__ trace, int trace_stride,
+                                                          int32_t* __restrict__ niters, int32_t* __restrict__ term) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SingleSmem& S = *reinterpret_cast<SingleSmem*>(smem_raw);
     const int tid = threadIdx.x, b = blockIdx.x;
     if (b >= B) return;
-    const int n = C->n, ntri = n * (n + 1) / 2;
+    const int n = C->n;
     const b3d_kp* kps = kps_all + (size_t)b * MAXKP;
     const int nkp = min(max(nkp_all[b], 0), MAXKP);
-    double* Hs = Hs_all + (size_t)b * HTRI;
     b3d_iter_record* tr = trace ? trace + (size_t)b * trace_stride : nullptr;
 
     // ---- problem set-up (Sim3BA.h:395-404 / 558-569): sim3 from the caller, jointAA = 0, w from the caller ----
@@ -380,21 +348,17 @@ __global__ void __launch_bounds__(T, 4) fit_single_kernel(const FitConst* __rest
     it.cost = it.cost_change = it.gradient_max_norm = it.step_norm = it.relative_decrease = it.radius = 0.0;
     it.flags = 0; it.aux = -1;
 
-    // evaluate at x with Jacobian, apply Jacobi scaling, publish H_s to global memory.  Returns false on non-finite cost.
+    // evaluate at x with Jacobian and apply the Jacobi scaling.  Returns false on non-finite cost.
     auto eval_grad_jac = [&](bool first) -> bool {
-        x_cost = evaluate<T, true>(C, S.xfull, kps, nkp, S);
+        x_cost = evaluate<T, true>(C, S.xfull, kps, nkp, S, first);
         if (!isfinite(x_cost)) return false;
         it.cost = x_cost;
-        double* H = S.u.L;
-        if (first)
-            for (int k = tid; k < n; k += T) S.scale[k] = 1.0 / (1.0 + sqrt(H[tri(k, k)]));
-        __syncthreads();
-        for (int i = tid >> 5; i < n; i += T / 32) {
-            const double si = S.scale[i];
-            for (int j = tid & 31; j <= i; j += 32) {
-                const double hv = H[tri(i, j)] * si * S.scale[j];
-                Hs[tri(i, j)] = hv;
-                if (i == j) S.hdiag[i] = hv;
+        if (first) {
+            for (int k = tid; k < n; k += T) S.scale[k] = 1.0 / (1.0 + sqrt(S.Hs[tri(k, k)]));
+            __syncthreads();
+            for (int i = tid >> 5; i < n; i += T / 32) {
+                const double si = S.scale[i];
+                for (int j = tid & 31; j <= i; j += 32) S.Hs[tri(i, j)] *= si * S.scale[j];
             }
         }
         double gm = 0.0;
@@ -406,7 +370,6 @@ __global__ void __launch_bounds__(T, 4) fit_single_kernel(const FitConst* __rest
             if (fk == IDX_S) xn = fmin(fmax(xn, C->scale_lo), C->scale_hi);
             gm = fmax(gm, fabs(S.xfull[fk] - xn));
         }
-        // max-reduce through the sum helper's scratch (order independent)
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) gm = fmax(gm, __shfl_down_sync(0xffffffffu, gm, o));
         __syncthreads();
@@ -442,6 +405,10 @@ __global__ void __launch_bounds__(T, 4) fit_single_kernel(const FitConst* __rest
         __syncthreads();
     };
 
+    PhaseTimer pt;
+    pt.start();
+    const long long t_begin = clock64();
+    int n_ls_evals = 0;
     double x_norm = x_norm_of(S.xfull);
     if (!eval_grad_jac(true)) {
         termination = B3D_TERM_EVAL_FAILURE;
@@ -460,30 +427,39 @@ __global__ void __launch_bounds__(T, 4) fit_single_kernel(const FitConst* __rest
             step_successful = false;
 
             // ---- LevenbergMarquardtStrategy::ComputeStep ----
+            pt.mark(0);
             if (!reuse_diagonal)
-                for (int k = tid; k < n; k += T) S.diag[k] = fmin(fmax(S.hdiag[k], kMinDiagonal), kMaxDiagonal);
+                for (int k = tid; k < n; k += T) S.diag[k] = fmin(fmax(S.Hs[tri(k, k)], kMinDiagonal), kMaxDiagonal);
             __syncthreads();
             double* A = S.u.L;
-            for (int e = tid; e < ntri; e += T) A[e] = Hs[e];
+            for (int i = tid >> 5; i < n; i += T / 32)
+                for (int j = tid & 31; j <= i; j += 32) {
+                    double v = S.Hs[tri(i, j)];
+                    if (i == j) { const double l = sqrt(S.diag[i] / radius); v += l * l; }
+                    A[tri(i, j)] = v;
+                }
             for (int k = tid; k < n; k += T) A[tri(n, k)] = S.gs[k];
-            __syncthreads();
-            for (int k = tid; k < n; k += T) { const double l = sqrt(S.diag[k] / radius); A[tri(k, k)] += l * l; }
             __syncthreads();
             reuse_diagonal = true;
             bool step_valid = false;
-            if (chol_factor_aug<T>(A, n + 1)) {
-                if (tid < 32) chol_backsolve_warp(A, n, S.y);
+            pt.mark(1);
+            const bool chol_ok = chol_factor_aug<T>(S, n);
+            pt.mark(2);
+            if (chol_ok) {
+                if (tid < 32) chol_backsolve_warp(S, n, S.y);
                 __syncthreads();
+                pt.mark(3);
                 // model_cost_change = -(J step)^T (r + J step / 2), step = -y:  y^T gs - y^T H_s y / 2
                 double v = 0.0, fin = 0.0;
                 for (int i = tid >> 5; i < n; i += T / 32) {
                     const double yi = S.y[i];
-                    for (int j = tid & 31; j <= i; j += 32) v -= (i == j ? 0.5 : 1.0) * Hs[tri(i, j)] * yi * S.y[j];
+                    for (int j = tid & 31; j <= i; j += 32) v -= (i == j ? 0.5 : 1.0) * S.Hs[tri(i, j)] * yi * S.y[j];
                 }
                 for (int k = tid; k < n; k += T) { v += S.y[k] * S.gs[k]; fin += isfinite(S.y[k]) ? 0.0 : 1.0; }
                 mcc = block_sum<T>(v, S.red);
                 const double bad = block_sum<T>(fin, S.red);
                 step_valid = (bad == 0.0) && (mcc > 0.0);
+                pt.mark(4);
             }
             if (!step_valid) {
                 // ---- HandleInvalidStep ----
@@ -499,26 +475,31 @@ __global__ void __launch_bounds__(T, 4) fit_single_kernel(const FitConst* __rest
 
             // ---- DoLineSearch (the problem is bounded: projected Armijo along delta) ----
             make_candidate(1.0);
-            cand_cost = evaluate<T, false>(C, S.cfull, kps, nkp, S);
+            pt.mark(5);
+            cand_cost = evaluate<T, false>(C, S.cfull, kps, nkp, S, false);
+            pt.mark(6);
+            bool hs_dirty = false;
             {
                 double v = 0.0;
                 for (int k = tid; k < n; k += T) v += S.g[k] * S.delta[k];
                 const double gd = block_sum<T>(v, S.red);
                 const bool valid1 = isfinite(cand_cost);
                 if (!valid1 || cand_cost > x_cost + kSufficientDecrease * gd * 1.0) {
-                    // rare path: interpolate.  Needs the directional derivative at every trial point.
+                    // rare path: interpolate.  Needs the directional derivative at every trial point; the trial evaluations
+                    // overwrite S.Hs / S.g, which are restored below if the step ends up rejected.
+                    hs_dirty = true;
+                    ++n_ls_evals;
                     double dmax = 0.0;
                     for (int k = 0; k < n; ++k) dmax = fmax(dmax, fabs(S.delta[k]));
+                    for (int k = tid; k < n; k += T) S.gc[k] = S.g[k];
+                    __syncthreads();
                     LsSample init{0.0, x_cost, gd, true}, prev{0, 0, 0, false}, cur{1.0, 0, 0, false};
-                    // S.g must survive: gradient at trial points goes to S.gc
                     auto ls_eval = [&](double a, LsSample& s) {
                         s.x = a; s.valid = false;
                         make_candidate(a);
-                        for (int k = tid; k < n; k += T) S.gc[k] = S.g[k];
-                        __syncthreads();
-                        const double c = evaluate<T, true>(C, S.cfull, kps, nkp, S);   // overwrites S.g
+                        const double c = evaluate<T, true>(C, S.cfull, kps, nkp, S, false);
                         double vv = 0.0;
-                        for (int k = tid; k < n; k += T) { const double t = S.g[k]; S.g[k] = S.gc[k]; vv += S.delta[k] * t; }
+                        for (int k = tid; k < n; k += T) vv += S.delta[k] * S.g[k];
                         const double gg = block_sum<T>(vv, S.red);
                         if (!isfinite(c) || !isfinite(gg)) return;
                         s.value = c; s.gradient = gg; s.valid = true;
@@ -552,7 +533,7 @@ __global__ void __launch_bounds__(T, 4) fit_single_kernel(const FitConst* __rest
                     __syncthreads();
                     // ---- ComputeCandidatePointAndEvaluateCost ----
                     make_candidate(1.0);
-                    cand_cost = evaluate<T, false>(C, S.cfull, kps, nkp, S);
+                    cand_cost = evaluate<T, false>(C, S.cfull, kps, nkp, S, false);
                 }
             }
             if (!isfinite(cand_cost)) cand_cost = DBL_MAX;
@@ -574,7 +555,9 @@ __global__ void __launch_bounds__(T, 4) fit_single_kernel(const FitConst* __rest
                 for (int k = tid; k < NFULL; k += T) S.xfull[k] = S.cfull[k];
                 __syncthreads();
                 x_norm = x_norm_of(S.xfull);
+                pt.mark(7);
                 if (!eval_grad_jac(false)) { termination = B3D_TERM_EVAL_FAILURE; break; }
+                pt.mark(8);
                 step_successful = true;
                 it.flags |= 2;
                 const double q = 2.0 * it.relative_decrease - 1.0;
@@ -585,6 +568,15 @@ __global__ void __launch_bounds__(T, 4) fit_single_kernel(const FitConst* __rest
             } else {
                 radius = radius / decrease_factor; decrease_factor *= 2.0;
                 it.cost = cand_cost;
+                if (hs_dirty) {   // restore the normal equations of x that the line-search evaluations overwrote
+                    __syncthreads();
+                    const int comp_keep = S.comp;
+                    (void)evaluate<T, true>(C, S.xfull, kps, nkp, S, false);
+                    for (int k = tid; k < n; k += T) S.gs[k] = S.g[k] * S.scale[k];
+                    __syncthreads();
+                    if (tid == 0) S.comp = comp_keep;
+                    __syncthreads();
+                }
             }
         }
     }
@@ -593,6 +585,7 @@ __global__ void __launch_bounds__(T, 4) fit_single_kernel(const FitConst* __rest
     if (tid < 7) sim3[(size_t)b * 7 + tid] = S.xfull[tid];
     for (int k = tid; k < NJ * 3; k += T) jointAA[(size_t)b * NJ * 3 + k] = k < 3 ? 0.0 : S.xfull[IDX_JAA + k - 3];
     if (C->has_w && tid < NS) w[(size_t)b * NS + tid] = S.xfull[IDX_W + tid];
+    if (tid == 0 && g_phase_on && b < 1024) { g_block_cycles[b] = clock64() - t_begin; g_block_ls[b] = n_ls_evals; }
     if (tid == 0) {
         if (usable) usable[b] = (termination >= B3D_TERM_PARAM_TOL && termination <= B3D_TERM_MIN_RADIUS) ? 1 : 0;
         if (niters) niters[b] = nrec;
@@ -656,6 +649,18 @@ using namespace b3d;
 
 extern "C" {
 
+// debug hooks (not part of include/b3d.h): per-phase cycle counters of block 0
+int b3d_debug_phase_timing(int on) {
+    long long z[16] = {0};
+    cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z));
+    return cudaMemcpyToSymbol(g_phase_on, &on, sizeof(int)) == cudaSuccess ? 0 : 2;
+}
+int b3d_debug_block_read(long long* cyc1024, int* ls1024) {
+    cudaMemcpyFromSymbol(ls1024, g_block_ls, 1024 * sizeof(int));
+    return cudaMemcpyFromSymbol(cyc1024, g_block_cycles, 1024 * sizeof(long long)) == cudaSuccess ? 0 : 2;
+}
+int b3d_debug_phase_read(long long* out16) { return cudaMemcpyFromSymbol(out16, g_phase_cycles, 16 * sizeof(long long)) == cudaSuccess ? 0 : 2; }
+
 int b3d_fit_single_dev(const b3d_model* m, const b3d_gmm* gmm, const b3d_fit_opts* opts, int32_t B, const b3d_kp* kps,
                        const int32_t* nkp, const double* R0, double* sim3, double* w, double* jointAA, uint8_t* usable,
                        b3d_iter_record* trace, int32_t trace_stride, int32_t* niters, int32_t* term, void* stream) {
@@ -668,9 +673,7 @@ int b3d_fit_single_dev(const b3d_model* m, const b3d_gmm* gmm, const b3d_fit_opt
     FitConst fc;
     if (int rc = build_fit_const(m, gmm, opts, false, &fc)) return rc;
     FitConst* dfc = nullptr;
-    double* Hs = nullptr;
     B3D_CUDA(cudaMallocAsync(&dfc, sizeof(FitConst), st));
-    B3D_CUDA(cudaMallocAsync(&Hs, sizeof(double) * (size_t)B * HTRI, st));
     // pageable source: the copy is staged before the call returns, so the stack object may go out of scope
     B3D_CUDA(cudaMemcpyAsync(dfc, &fc, sizeof(FitConst), cudaMemcpyHostToDevice, st));
     static bool attr_set = false;
@@ -679,9 +682,8 @@ int b3d_fit_single_dev(const b3d_model* m, const b3d_gmm* gmm, const b3d_fit_opt
         attr_set = true;
     }
     fit_single_kernel<FS_THREADS><<<B, FS_THREADS, sizeof(SingleSmem), st>>>(dfc, B, kps, nkp, R0, sim3, w, jointAA, usable, trace, trace_stride,
-                                                                            niters, term, Hs);
+                                                                            niters, term);
     B3D_LAUNCH_CHECK();
-    B3D_CUDA(cudaFreeAsync(Hs, st));
     B3D_CUDA(cudaFreeAsync(dfc, st));
     return B3D_OK;
 }

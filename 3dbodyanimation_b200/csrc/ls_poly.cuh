@@ -1,0 +1,119 @@
+// Armijo line-search helpers of Ceres 1.14 (ArmijoLineSearch + polynomial.cc MinimizeInterpolatingPolynomial), restated
+// for the device.  Only the rare path of the bounded single-frame problems uses them (the step size 1 normally already
+// satisfies the sufficient-decrease test), and then a single thread runs them.
+#pragma once
+#include <cfloat>
+
+namespace b3d {
+
+constexpr double kSufficientDecrease = 1e-4, kMinLineSearchStepSize = 1e-9;
+constexpr int kMaxLineSearchIters = 20;
+constexpr double kLsContractLo = 1e-3, kLsContractHi = 0.6;   // max_/min_line_search_step_contraction (Solver::Options defaults)
+
+// ---- polynomial helpers for the (rare) Armijo interpolation: thread 0 only --------------------------------------
+struct LsSample { double x, value, gradient; bool valid; };
+
+__device__ double poly_eval(const double* p, int nc, double x) { double v = 0; for (int i = 0; i < nc; ++i) v = v * x + p[i]; return v; }
+
+// Gaussian elimination with full pivoting (Eigen FullPivLU as used by ceres polynomial.cc); n <= 6
+__device__ bool lu_solve(double* A, int n, double* b, double* x) {
+    int perm[6];
+    for (int i = 0; i < n; ++i) perm[i] = i;
+    for (int k = 0; k < n; ++k) {
+        int pr = k, pc = k; double best = 0.0;
+        for (int i = k; i < n; ++i) for (int j = k; j < n; ++j) if (fabs(A[i * n + j]) > best) { best = fabs(A[i * n + j]); pr = i; pc = j; }
+        if (best == 0.0) return false;
+        if (pr != k) { for (int j = 0; j < n; ++j) { double t = A[k * n + j]; A[k * n + j] = A[pr * n + j]; A[pr * n + j] = t; } double t = b[k]; b[k] = b[pr]; b[pr] = t; }
+        if (pc != k) { for (int i = 0; i < n; ++i) { double t = A[i * n + k]; A[i * n + k] = A[i * n + pc]; A[i * n + pc] = t; } int t = perm[k]; perm[k] = perm[pc]; perm[pc] = t; }
+        for (int i = k + 1; i < n; ++i) {
+            const double f = A[i * n + k] / A[k * n + k];
+            for (int j = k; j < n; ++j) A[i * n + j] -= f * A[k * n + j];
+            b[i] -= f * b[k];
+        }
+    }
+    double z[6];
+    for (int i = n - 1; i >= 0; --i) { double s = b[i]; for (int j = i + 1; j < n; ++j) s -= A[i * n + j] * z[j]; z[i] = s / A[i * n + i]; }
+    for (int i = 0; i < n; ++i) x[perm[i]] = z[i];
+    return true;
+}
+
+// real parts of the roots of a polynomial of degree <= 4 (coefficients highest first): Aberth-Ehrlich iteration
+__device__ int poly_root_real_parts(const double* pin, int nc, double* out) {
+    int lead = 0;
+    while (lead + 1 < nc && pin[lead] == 0.0) ++lead;
+    const double* p = pin + lead;
+    const int deg = nc - lead - 1;
+    if (deg <= 0) return 0;
+    if (deg == 1) { out[0] = -p[1] / p[0]; return 1; }
+    if (deg == 2) {
+        const double a = p[0], b = p[1], c = p[2];
+        const double D = b * b - 4 * a * c, sD = sqrt(fabs(D));
+        if (D >= 0) {
+            if (b >= 0) { out[0] = (-b - sD) / (2.0 * a); out[1] = (2.0 * c) / (-b - sD); }
+            else { out[0] = (2.0 * c) / (-b + sD); out[1] = (-b + sD) / (2.0 * a); }
+        } else { out[0] = out[1] = -b / (2.0 * a); }
+        return 2;
+    }
+    double ar[6], zr[5], zi[5];
+    for (int i = 0; i <= deg; ++i) ar[i] = p[i] / p[0];
+    double rad = 0;
+    for (int i = 1; i <= deg; ++i) rad = fmax(rad, fabs(ar[i]));
+    rad = 1.0 + rad;
+    for (int i = 0; i < deg; ++i) { double s, c; sincos(2 * 3.14159265358979323846 * i / deg + 0.4, &s, &c); zr[i] = rad * 0.5 * c; zi[i] = rad * 0.5 * s; }
+    for (int it = 0; it < 64; ++it) {
+        double change = 0;
+        for (int i = 0; i < deg; ++i) {
+            double fr = ar[0], fi = 0, dr = 0, di = 0;
+            for (int k = 1; k <= deg; ++k) {
+                double t = dr * zr[i] - di * zi[i] + fr; di = dr * zi[i] + di * zr[i] + fi; dr = t;
+                t = fr * zr[i] - fi * zi[i] + ar[k]; fi = fr * zi[i] + fi * zr[i]; fr = t;
+            }
+            if (fr == 0.0 && fi == 0.0) continue;
+            const double dd = dr * dr + di * di;
+            const double rr = (fr * dr + fi * di) / dd, ri = (fi * dr - fr * di) / dd;   // ratio = f / df
+            double sr = 0, si = 0;
+            for (int j = 0; j < deg; ++j) if (j != i) { const double ur = zr[i] - zr[j], ui = zi[i] - zi[j], uu = ur * ur + ui * ui; sr += ur / uu; si -= ui / uu; }
+            const double er = 1.0 - (rr * sr - ri * si), ei = -(rr * si + ri * sr);
+            const double ee = er * er + ei * ei;
+            const double zr_d = (rr * er + ri * ei) / ee, zi_d = (ri * er - rr * ei) / ee;
+            zr[i] -= zr_d; zi[i] -= zi_d;
+            change = fmax(change, sqrt(zr_d * zr_d + zi_d * zi_d));
+        }
+        if (change < 1e-14 * rad) break;
+    }
+    for (int i = 0; i < deg; ++i) out[i] = zr[i];
+    return deg;
+}
+
+// ceres MinimizeInterpolatingPolynomial: every sample carries value and gradient
+__device__ double minimize_interpolating_polynomial(const LsSample* s, int ns, double x_min, double x_max) {
+    const int nc = 2 * ns, degree = nc - 1;
+    double lhs[36], rhs[6], coef[6];
+    for (int i = 0; i < nc * nc; ++i) lhs[i] = 0.0;
+    int row = 0;
+    for (int q = 0; q < ns; ++q) {
+        for (int j = 0; j <= degree; ++j) lhs[row * nc + j] = pow(s[q].x, (double)(degree - j));
+        rhs[row++] = s[q].value;
+        for (int j = 0; j < degree; ++j) lhs[row * nc + j] = (degree - j) * pow(s[q].x, (double)(degree - j - 1));
+        rhs[row++] = s[q].gradient;
+    }
+    double best_x = (x_min + x_max) / 2.0;
+    if (!lu_solve(lhs, nc, rhs, coef)) return best_x;
+    double best_v = poly_eval(coef, nc, best_x);
+    const double vmin = poly_eval(coef, nc, x_min);
+    if (vmin < best_v) { best_v = vmin; best_x = x_min; }
+    const double vmax = poly_eval(coef, nc, x_max);
+    if (vmax < best_v) { best_v = vmax; best_x = x_max; }
+    double dcoef[5], roots[5];
+    for (int i = 0; i < degree; ++i) dcoef[i] = (degree - i) * coef[i];
+    const int nr = poly_root_real_parts(dcoef, degree, roots);
+    for (int i = 0; i < nr; ++i) {
+        if (roots[i] < x_min || roots[i] > x_max) continue;
+        const double v = poly_eval(coef, nc, roots[i]);
+        if (v < best_v) { best_v = v; best_x = roots[i]; }
+    }
+    return best_x;
+}
+
+
+}  // namespace b3d

@@ -69,6 +69,8 @@ def fit(n, mode="C2", reps=3):
                                           C.c_void_p(st)), "fit")
     mean, best = timed(fn, reps)
     it = ni.cpu().numpy()
+    global LAST_NI
+    LAST_NI = it
     print(f"fit {mode} frames={n}: {mean:.3f} ms (best {best:.3f}) -> {n / mean * 1e3:.0f} frames/s; LM iterations mean {it.mean():.1f} max {it.max()} "
           f"sum {it.sum()}; {mean * 1e3 / max(it.max(), 1):.1f} us per iteration of the slowest frame; usable {int(us.sum())}")
 
@@ -87,3 +89,33 @@ if __name__ == "__main__":
         for n in (100, 1000, 8000):
             fit(n, "C2")
         fit(100, "C1"); fit(1000, "C1")
+
+
+def phases(n=148, mode="C2"):
+    """Per-phase cycle counts of block 0 (debug hook b3d_debug_phase_timing)."""
+    names = ["loop head", "build A", "cholesky", "backsolve", "mcc", "delta+candidate", "cand evaluate", "accept copy", "eval_grad_jac total",
+             "  JAC reproj", "  JAC gmm+cost", "  JAC assemble", "  cand reproj", "  cand gmm+cost", "", ""]
+    lib.b3d_debug_phase_timing(1)
+    import io, contextlib
+    fit(n, mode, reps=1)
+    out = (C.c_longlong * 16)()
+    lib.b3d_debug_phase_read(out)
+    tot = sum(out[i] for i in range(9))
+    for i in range(14):
+        print(f"{names[i]:22s} {out[i]:12d} cycles {out[i] / max(tot, 1) * 100:6.1f}%")
+    cyc, ls = (C.c_longlong * 1024)(), (C.c_int * 1024)()
+    lib.b3d_debug_block_read(cyc, ls)
+    m = min(n, 1024)
+    cy, lsv, ni = np.array(cyc[:m], dtype=np.float64), np.array(ls[:m]), LAST_NI[:m].astype(np.float64)
+    per = cy / ni
+    print("frame0 iters", int(ni[0]), "cycles", int(cy[0]))
+    print("cycles per iteration: min %.0f median %.0f max %.0f" % (per.min(), np.median(per), per.max()))
+    order = np.argsort(-cy)[:8]
+    for b in order:
+        print(f"  block {b}: {cy[b] / 1e6:.2f} Mcycles, iters {int(ni[b])}, per-iter {per[b]:.0f}, line-search fallbacks {lsv[b]}")
+    print("frames with line-search fallbacks:", int((lsv > 0).sum()), "total fallbacks", int(lsv.sum()))
+    lib.b3d_debug_phase_timing(0)
+
+
+if __name__ == "__main__" and sys.argv[1] == "phases":
+    phases(int(sys.argv[2]) if len(sys.argv) > 2 else 148, sys.argv[3] if len(sys.argv) > 3 else "C2")
