@@ -201,6 +201,21 @@ def fit_frames(ws: Workspace, model: AvatarModel, gmm, opts: capi.FitOpts, kps, 
     return out
 
 
+def fit_window(model: AvatarModel, opts: capi.FitOpts, kps, nkp, R0, poses, w, want_trace=True):
+    """One OptimizeMultiFrame solve (include/MultiFrameBA.h:33-177) over F frames; w is the shared shape block."""
+    kps = np.ascontiguousarray(kps, dtype=KP_DTYPE).reshape(-1, MAXKP)
+    f = kps.shape[0]
+    nkp = np.ascontiguousarray(nkp, dtype=np.int32).reshape(f)
+    R0, poses, w = _f64(R0).reshape(f, 9), _f64(poses).reshape(f, NPF).copy(), _f64(w).reshape(NS).copy()
+    cap = opts.max_iters + 2
+    trace = np.zeros(cap, dtype=ITER_DTYPE) if want_trace else None
+    usable, niters, term = np.zeros(1, dtype=np.uint8), np.zeros(1, dtype=np.int32), np.zeros(1, dtype=np.int32)
+    check(lib().b3d_fit_window(model.h, C.byref(opts), f, ptr(kps), ptr(nkp), ptr(R0), ptr(poses), ptr(w), ptr(usable), ptr(trace), cap,
+                               ptr(niters), ptr(term)), "b3d_fit_window")
+    n = int(niters[0])
+    return dict(poses=poses, w=w, usable=bool(usable[0]), trace=None if trace is None else trace[:n], niters=n, term=int(term[0]))
+
+
 def writeback(poses, R0):
     """a15: R0 <- R(rootAA) R0; r[0] = R0, r[j] = R(jointAA_j); p = rootT.  poses (F,76), R0 (F,9)."""
     poses = _f64(poses).reshape(-1, NPF)

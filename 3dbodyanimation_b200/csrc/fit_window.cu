@@ -1,0 +1,666 @@
+// Entry (2), multi-frame: one CTA runs the whole Levenberg-Marquardt solve of one window / anchor chain of F frames.
+//
+// Replaces the ceres::Problem built and solved by OptimizeMultiFrame (include/MultiFrameBA.h:33-177): per frame a 76-vector
+// [scale, rootAA, rootT, jointAA[1..23]], one shared shape block w (10), per keypoint a ReprojCostShape block + Huber(3)
+// (:71-103), per frame the L2 pose prior (:106-111; the GMM is never used here), the shape prior (:115-118) and, between
+// consecutive frames, 25 Vec3DiffCost blocks lambda (a - b) on rootT, rootAA and every jointAA (:121-142; the scale is not
+// smoothed).  No bounds, hence no line search.  The LM loop is the same Ceres 1.14 restatement as fit_single.cu.
+//
+// Where the reference hands the dense (m x n) Jacobian to DENSE_QR (m = 3,495, n = 1,530 for a 20-frame window: 1.6e10 flop
+// per iteration, all but 0.2 % of it on structural zeros), the normal equations here keep their structure: block tridiagonal
+// (76 x 76 blocks, off-diagonal blocks are the diagonal matrices -lambda^2 S_f E S_{f+1}) plus a 10-wide arrowhead for w.
+// They are factored frame by frame by one augmented Crout elimination per frame: the rows of the next off-diagonal block, the
+// 10 arrow rows and the right-hand side ride along below the 76 x 76 diagonal block, so that L_{f+1,f}, W_f and the forward
+// substitution come out of the same column sweep; the 10 x 10 Schur complement of w closes the system.
+#include "lm_device.cuh"
+
+namespace b3d {
+
+constexpr int FW_THREADS = 256;
+constexpr int NB = NPF;                 // 76: diagonal block size
+constexpr int LDM = NB + 1;             // padded leading dimension of the shared-memory blocks (bank-conflict free columns)
+constexpr int ROW_LO = NB;              // rows 76..151 of M: next off-diagonal block L_{f+1,f}
+constexpr int ROW_W = 2 * NB;           // rows 152..161: arrow rows W_f
+constexpr int ROW_Z = 2 * NB + NS;      // row 162: right-hand side
+constexpr int MROWS = ROW_Z + 1;        // 163
+constexpr int PROWS = NB + NS + 1;      // 87: previous [L_{f,f-1} ; W_{f-1} ; z_{f-1}]
+constexpr int HFTRI = NFULL * (NFULL + 1) / 2;
+
+constexpr double wInitialRadius = 1e4, wMaxRadius = 1e16, wMinRadius = 1e-32;
+constexpr double wMinDiagonal = 1e-6, wMaxDiagonal = 1e32;
+constexpr double wMinRelativeDecrease = 1e-3;
+constexpr double wFunctionTolerance = 1e-6, wGradientTolerance = 1e-10, wParameterTolerance = 1e-8;
+constexpr int wMaxConsecutiveInvalidSteps = 5;
+
+// per-problem global workspace, in doubles
+__host__ __device__ inline size_t win_ws_doubles(int F) {
+    const size_t n = (size_t)F * NB + NS;
+    return 10 * n + (size_t)F * (3 * NB * NB + 2 * NS * NB) + 2 * NS * NS + (size_t)F * NB;
+}
+
+struct WinWs {
+    double *x, *cand, *g, *gs, *scale, *diag, *y, *delta, *z, *tmp;   // n each
+    double *Hd, *Ld, *Lo;     // F x 76 x 76: scaled J^T J diagonal blocks; factor diagonal blocks; factor sub-diagonal blocks
+    double *Ha, *Wf;          // F x 10 x 76: scaled arrow rows; their factor
+    double *Hw, *Lw;          // 10 x 10
+    double* invd;             // F x 76: 1 / L_jj
+    __device__ void carve(double* base, int F) {
+        const size_t n = (size_t)F * NB + NS;
+        double* p = base;
+        x = p; p += n; cand = p; p += n; g = p; p += n; gs = p; p += n; scale = p; p += n;
+        diag = p; p += n; y = p; p += n; delta = p; p += n; z = p; p += n; tmp = p; p += n;
+        Hd = p; p += (size_t)F * NB * NB; Ld = p; p += (size_t)F * NB * NB; Lo = p; p += (size_t)F * NB * NB;
+        Ha = p; p += (size_t)F * NS * NB; Wf = p; p += (size_t)F * NS * NB;
+        Hw = p; p += NS * NS; Lw = p; p += NS * NS;
+        invd = p;
+    }
+};
+
+struct WinEval {
+    EvalOut out;
+    EvalTmp ev;
+    double Hf[HFTRI];                     // one frame's 86 x 86 J^T J, packed lower
+    double gf[NFULL];
+    uint32_t kmask[NFULL];
+    uint8_t slot[MAXKP][NFULL + 2];
+    uint8_t fcol[MAXKP][NNZPAD];
+};
+
+struct WinChain {
+    double M[MROWS][LDM];
+    double P[PROWS][LDM];
+    double yn[NB];                        // y of frame f + 1 during the backward sweep
+    double rhs[NB];
+};
+
+union WinUnion {
+    WinEval e;
+    WinChain c;
+};
+
+struct WinSmem {
+    WinUnion u;
+    double xfull[NFULL];
+    double R0[9];
+    double red[40];
+    double Hw[NS * NS], gw[NS], yw[NS], Sw[NS * NS], zw[NS];
+    double piv[2];
+    int32_t flag;
+};
+
+struct WinProblem {
+    int32_t first, count;     // frames [first, first + count) of the frame arrays; the shared w block is row `first` of W
+    int64_t ws_offset;        // doubles into the workspace
+};
+
+// ---- evaluate every frame of the problem at parameters xp (n = 76 F + 10) -----------------------------------------------
+// Returns the cost.  JAC: fills Hd / Ha / Hw (UNSCALED) and g in the workspace.
+template <int T, bool JAC>
+__device__ double win_evaluate(const FitConst* __restrict__ C, int F, const double* __restrict__ xp, const b3d_kp* __restrict__ kps,
+                               const int32_t* __restrict__ nkp_all, const double* __restrict__ R0_all, WinWs& W, WinSmem& S) {
+    const int tid = threadIdx.x, lane = tid & 31;
+    WinEval& E = S.u.e;
+    const double bp2 = C->beta_pose * C->beta_pose, bs2 = C->beta_shape * C->beta_shape, lam = C->lambda_temp, lam2 = lam * lam;
+    const bool pose_prior = C->beta_pose > 0.0, shape_prior = C->beta_shape > 0.0, temporal = lam > 0.0 && F > 1;
+    double part = 0.0;                      // this thread's share of the cost
+    if (JAC) {
+        for (int k = tid; k < NS * NS; k += T) S.Hw[k] = 0.0;
+        if (tid < NS) S.gw[tid] = 0.0;
+    }
+    if (tid < NS) S.xfull[IDX_W + tid] = xp[(size_t)F * NB + tid];
+    for (int f = 0; f < F; ++f) {
+        const int nkp = min(max(nkp_all[f], 0), MAXKP);
+        const double* xf = xp + (size_t)f * NB;
+        __syncthreads();                    // previous frame's consumers are done with xfull / R0 / E
+        for (int k = tid; k < NB; k += T) S.xfull[k] = xf[k];
+        if (tid < 9) S.R0[tid] = R0_all[(size_t)f * 9 + tid];
+        __syncthreads();
+        eval_reproj<T, JAC>(C, S.xfull, kps + (size_t)f * MAXKP, nkp, S.R0, E.ev, E.out);
+        if (tid < nkp) part += E.out.kcost[tid];
+        if (pose_prior)
+            for (int k = tid; k < NPRI; k += T) { const double r = S.xfull[IDX_JAA + k] * C->beta_pose; part += 0.5 * r * r; }
+        if (!JAC) continue;
+        // ---- this frame's 86 x 86 normal equations in shared memory (all 86 columns are free in the multi-frame problem) ----
+        for (int k = tid; k < NFULL; k += T) E.kmask[k] = 0u;
+        for (int e = tid; e < HFTRI; e += T) E.Hf[e] = 0.0;
+        __syncthreads();
+        for (int t = tid; t < nkp * NNZPAD; t += T) {
+            const int k = t / NNZPAD, sl = t % NNZPAD;
+            if (sl < E.out.jnnz[k]) {
+                const int col = E.out.jcol[k][sl];
+                E.slot[k][col] = (uint8_t)sl;
+                E.fcol[k][sl] = (uint8_t)col;
+                atomicOr(&E.kmask[col], 1u << k);
+            }
+        }
+        __syncthreads();
+        for (int i = tid >> 5; i < NFULL; i += T / 32) {      // a warp owns row i; lanes cover the slots of each keypoint touching i
+            uint32_t m = E.kmask[i];
+            double gacc = 0.0;
+            while (m) {
+                const int k = __ffs(m) - 1;
+                m &= m - 1;
+                const int sa = E.slot[k][i], nnz = E.out.jnnz[k];
+                const double a0 = E.out.J[k][0][sa], a1 = E.out.J[k][1][sa];
+                for (int sb = lane; sb < nnz; sb += 32) {
+                    const int j = E.fcol[k][sb];
+                    if (j <= i) E.Hf[tri(i, j)] += a0 * E.out.J[k][0][sb] + a1 * E.out.J[k][1][sb];
+                }
+                gacc += a0 * E.out.res[k][0] + a1 * E.out.res[k][1];
+            }
+            if (lane == 0) E.gf[i] = gacc;
+        }
+        __syncthreads();
+        // ---- scatter into the block structure, adding the L2 pose prior and the temporal terms ----
+        double* Hd = W.Hd + (size_t)f * NB * NB;
+        const int nadj = temporal ? (f > 0) + (f < F - 1) : 0;
+        for (int idx = tid; idx < NB * NB; idx += T) {
+            const int r = idx / NB, c = idx % NB;
+            double v = r >= c ? E.Hf[tri(r, c)] : E.Hf[tri(c, r)];
+            if (r == c) {
+                if (pose_prior && r >= IDX_JAA) v += bp2;
+                if (r >= 1) v += nadj * lam2;                     // Vec3DiffCost on every parameter but the scale
+            }
+            Hd[idx] = v;
+        }
+        double* Ha = W.Ha + (size_t)f * NS * NB;
+        for (int idx = tid; idx < NS * NB; idx += T) Ha[idx] = E.Hf[tri(IDX_W + idx / NB, idx % NB)];
+        for (int idx = tid; idx < NS * NS; idx += T) {
+            const int s = idx / NS, t2 = idx % NS;
+            S.Hw[idx] += s >= t2 ? E.Hf[tri(IDX_W + s, IDX_W + t2)] : E.Hf[tri(IDX_W + t2, IDX_W + s)];
+        }
+        if (tid < NS) S.gw[tid] += E.gf[IDX_W + tid];
+        for (int k = tid; k < NB; k += T) {
+            double v = E.gf[k];
+            if (pose_prior && k >= IDX_JAA) v += bp2 * S.xfull[k];
+            if (temporal && k >= 1) {
+                if (f < F - 1) v += lam2 * (xf[k] - xf[NB + k]);
+                if (f > 0) v -= lam2 * (xf[k - NB] - xf[k]);
+            }
+            W.g[(size_t)f * NB + k] = v;
+        }
+    }
+    // temporal residuals lambda (x_f - x_{f+1}) and the shape prior
+    if (temporal)
+        for (int idx = tid; idx < (F - 1) * (NB - 1); idx += T) {
+            const int f = idx / (NB - 1), k = 1 + idx % (NB - 1);
+            const double d = lam * (xp[(size_t)f * NB + k] - xp[(size_t)(f + 1) * NB + k]);
+            part += 0.5 * d * d;
+        }
+    if (shape_prior && tid < NS) { const double r = C->beta_shape * S.xfull[IDX_W + tid]; part += 0.5 * r * r; }
+    __syncthreads();
+    if (JAC) {
+        for (int idx = tid; idx < NS * NS; idx += T) W.Hw[idx] = S.Hw[idx] + ((shape_prior && idx / NS == idx % NS) ? bs2 : 0.0);
+        if (tid < NS) W.g[(size_t)F * NB + tid] = S.gw[tid] + (shape_prior ? bs2 * S.xfull[IDX_W + tid] : 0.0);
+    }
+    return block_sum<T>(part, S.red);
+}
+
+// ---- block-tridiagonal + arrowhead solve of (H_s + D^2 / radius) y = gs ---------------------------------------------------
+// H_s: scaled J^T J held as Hd (diagonal blocks), Ha (arrow rows), Hw, and the implicit off-diagonal blocks
+// -lambda^2 diag(scale_f,i scale_{f+1},i), i >= 1.  Returns false when a pivot is not positive.
+template <int T>
+__device__ bool win_solve(const FitConst* __restrict__ C, int F, double radius, WinWs& W, WinSmem& S) {
+    const int tid = threadIdx.x;
+    WinChain& K = S.u.c;
+    const double lam2 = C->lambda_temp * C->lambda_temp;
+    const bool temporal = C->lambda_temp > 0.0 && F > 1;
+    // running Schur complement of the arrow block: thread (s, t), t <= s, owns Sw[s][t]; threads 64..73 own zw[s]
+    int ss = -1, st = -1;
+    if (tid < NS * (NS + 1) / 2) { int s = 0; while ((s + 1) * (s + 2) / 2 <= tid) ++s; ss = s; st = tid - s * (s + 1) / 2; }
+    double sw_acc = 0.0, zw_acc = 0.0;
+    bool ok = true;
+    for (int f = 0; f < F && ok; ++f) {
+        const bool has_next = temporal && f < F - 1;
+        const bool has_prev = temporal && f > 0;
+        const int nrows = MROWS;
+        // (1) load this frame's rows: [Hd_f + damping ; next off-diagonal block ; Ha_f ; gs_f]
+        const double* Hd = W.Hd + (size_t)f * NB * NB;
+        for (int idx = tid; idx < NB * NB; idx += T) {
+            const int r = idx / NB, c = idx % NB;
+            double v = Hd[idx];
+            if (r == c) { const double l = sqrt(W.diag[(size_t)f * NB + r] / radius); v += l * l; }
+            K.M[r][c] = v;
+        }
+        for (int idx = tid; idx < NB * NB; idx += T) {
+            const int r = idx / NB, c = idx % NB;
+            double v = 0.0;
+            if (has_next && r == c && r >= 1) v = -lam2 * W.scale[(size_t)f * NB + r] * W.scale[(size_t)(f + 1) * NB + r];
+            K.M[ROW_LO + r][c] = v;
+        }
+        const double* Ha = W.Ha + (size_t)f * NS * NB;
+        for (int idx = tid; idx < NS * NB; idx += T) K.M[ROW_W + idx / NB][idx % NB] = Ha[idx];
+        for (int c = tid; c < NB; c += T) K.M[ROW_Z][c] = W.gs[(size_t)f * NB + c];
+        __syncthreads();
+        // (2) subtract the products with the previous block row P = [L_{f,f-1} ; W_{f-1} ; z_{f-1}].  L_{f,f-1} is upper
+        //     triangular (it is a diagonal matrix times L^-T), so row r of it starts at column r.
+        if (has_prev) {
+            for (int idx = tid; idx < NB * NB; idx += T) {
+                const int r = idx / NB, c = idx % NB;
+                if (c > r) continue;
+                double a0 = 0.0, a1 = 0.0;
+                int k = r;
+                for (; k + 1 < NB; k += 2) { a0 += K.P[r][k] * K.P[c][k]; a1 += K.P[r][k + 1] * K.P[c][k + 1]; }
+                if (k < NB) a0 += K.P[r][k] * K.P[c][k];
+                K.M[r][c] -= a0 + a1;
+            }
+            for (int idx = tid; idx < (NS + 1) * NB; idx += T) {
+                const int q = idx / NB, c = idx % NB;            // q: arrow row s (0..9) or the right-hand side (10)
+                double a0 = 0.0, a1 = 0.0;
+                int k = c;
+                for (; k + 1 < NB; k += 2) { a0 += K.P[NB + q][k] * K.P[c][k]; a1 += K.P[NB + q][k + 1] * K.P[c][k + 1]; }
+                if (k < NB) a0 += K.P[NB + q][k] * K.P[c][k];
+                K.M[ROW_W + q][c] -= a0 + a1;
+            }
+            __syncthreads();
+        }
+        // (3) augmented Crout: thread r owns row r; rows of the next off-diagonal block start at their diagonal column
+        {
+            const int r = tid;
+            const bool is_row = r < nrows && (has_next || r < ROW_LO || r >= ROW_W);
+            const int c0 = (r >= ROW_LO && r < ROW_W) ? r - ROW_LO : 0;
+            double dg = r < NB ? K.M[r][r] : 0.0;
+            if (tid == 0) { const double il = rsqrt(dg); S.piv[0] = dg; S.piv[1] = il; W.invd[(size_t)f * NB] = il; }
+            for (int j = 0; j < NB; ++j) {
+                __syncthreads();
+                const double d = S.piv[0];
+                if (!(d > 0.0)) { ok = false; break; }
+                const double inv = S.piv[1];
+                if (is_row && r > j && c0 <= j) {
+                    const double* rj = K.M[j];
+                    double* rr = K.M[r];
+                    double s0 = rr[j], s1 = 0.0, s2 = 0.0, s3 = 0.0;
+                    int k = c0;
+                    for (; k + 4 <= j; k += 4) {
+                        s0 -= rr[k] * rj[k]; s1 -= rr[k + 1] * rj[k + 1]; s2 -= rr[k + 2] * rj[k + 2]; s3 -= rr[k + 3] * rj[k + 3];
+                    }
+                    for (; k < j; ++k) s0 -= rr[k] * rj[k];
+                    const double val = ((s0 + s1) + (s2 + s3)) * inv;
+                    rr[j] = val;
+                    if (r < NB) {
+                        dg -= val * val;
+                        if (r == j + 1) { const double il = rsqrt(dg); S.piv[0] = dg; S.piv[1] = il; W.invd[(size_t)f * NB + r] = il; }
+                    }
+                }
+            }
+            __syncthreads();
+            if (!ok) break;
+        }
+        // (4) results of this frame: L_ff, L_{f+1,f}, W_f, z_f; running Schur complement; next P
+        double* Ld = W.Ld + (size_t)f * NB * NB;
+        for (int idx = tid; idx < NB * NB; idx += T) { const int r = idx / NB, c = idx % NB; if (c < r) Ld[idx] = K.M[r][c]; }
+        if (has_next) {
+            double* Lo = W.Lo + (size_t)f * NB * NB;
+            for (int idx = tid; idx < NB * NB; idx += T) {
+                const int r = idx / NB, c = idx % NB;
+                const double v = K.M[ROW_LO + r][c];
+                Lo[idx] = v;
+                K.P[r][c] = v;
+            }
+        }
+        double* Wf = W.Wf + (size_t)f * NS * NB;
+        for (int idx = tid; idx < NS * NB; idx += T) { const double v = K.M[ROW_W + idx / NB][idx % NB]; Wf[idx] = v; K.P[NB + idx / NB][idx % NB] = v; }
+        for (int c = tid; c < NB; c += T) { const double v = K.M[ROW_Z][c]; W.z[(size_t)f * NB + c] = v; K.P[NB + NS][c] = v; }
+        if (ss >= 0) {
+            double a = 0.0;
+            for (int k = 0; k < NB; ++k) a += K.M[ROW_W + ss][k] * K.M[ROW_W + st][k];
+            sw_acc += a;
+        } else if (tid >= 64 && tid < 64 + NS) {
+            double a = 0.0;
+            for (int k = 0; k < NB; ++k) a += K.M[ROW_W + tid - 64][k] * K.M[ROW_Z][k];
+            zw_acc += a;
+        }
+        __syncthreads();
+    }
+    if (!ok) return false;
+    // ---- arrow block: Sw = Hw + damping - sum_f W_f W_f^T ; zw = gs_w - sum_f W_f z_f ; 10 x 10 Cholesky by one thread ----
+    const size_t nw0 = (size_t)F * NB;
+    if (ss >= 0) {
+        double v = W.Hw[ss * NS + st] - sw_acc;
+        if (ss == st) { const double l = sqrt(W.diag[nw0 + ss] / radius); v += l * l; }
+        S.Sw[ss * NS + st] = v;
+    } else if (tid >= 64 && tid < 64 + NS) {
+        S.zw[tid - 64] = W.gs[nw0 + tid - 64] - zw_acc;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int good = 1;
+        for (int j = 0; j < NS && good; ++j) {
+            double d = S.Sw[j * NS + j];
+            for (int k = 0; k < j; ++k) d -= S.Sw[j * NS + k] * S.Sw[j * NS + k];
+            if (!(d > 0.0)) { good = 0; break; }
+            d = sqrt(d);
+            S.Sw[j * NS + j] = d;
+            for (int i = j + 1; i < NS; ++i) {
+                double s = S.Sw[i * NS + j];
+                for (int k = 0; k < j; ++k) s -= S.Sw[i * NS + k] * S.Sw[j * NS + k];
+                S.Sw[i * NS + j] = s / d;
+            }
+        }
+        if (good) {
+            for (int i = 0; i < NS; ++i) { double s = S.zw[i]; for (int k = 0; k < i; ++k) s -= S.Sw[i * NS + k] * S.zw[k]; S.zw[i] = s / S.Sw[i * NS + i]; }
+            for (int i = NS - 1; i >= 0; --i) { double s = S.zw[i]; for (int k = i + 1; k < NS; ++k) s -= S.Sw[k * NS + i] * S.yw[k]; S.yw[i] = s / S.Sw[i * NS + i]; }
+        }
+        S.flag = good;
+    }
+    __syncthreads();
+    if (!S.flag) return false;
+    if (tid < NS) W.y[nw0 + tid] = S.yw[tid];
+    // ---- backward sweep: L_ff^T y_f = z_f - W_f^T y_w - L_{f+1,f}^T y_{f+1} ----
+    for (int f = F - 1; f >= 0; --f) {
+        const bool has_next = temporal && f < F - 1;
+        const double* Ld = W.Ld + (size_t)f * NB * NB;
+        for (int idx = tid; idx < NB * NB; idx += T) { const int r = idx / NB, c = idx % NB; if (c < r) K.M[r][c] = Ld[idx]; }
+        if (has_next) {
+            const double* Lo = W.Lo + (size_t)f * NB * NB;
+            for (int idx = tid; idx < NB * NB; idx += T) K.M[ROW_LO + idx / NB][idx % NB] = Lo[idx];
+        }
+        const double* Wf = W.Wf + (size_t)f * NS * NB;
+        for (int idx = tid; idx < NS * NB; idx += T) K.M[ROW_W + idx / NB][idx % NB] = Wf[idx];
+        __syncthreads();
+        for (int i = tid; i < NB; i += T) {
+            double v = W.z[(size_t)f * NB + i];
+#pragma unroll
+            for (int s = 0; s < NS; ++s) v -= K.M[ROW_W + s][i] * S.yw[s];
+            if (has_next)
+                for (int k = 0; k <= i; ++k) v -= K.M[ROW_LO + k][i] * K.yn[k];      // L_{f+1,f} is upper triangular
+            K.rhs[i] = v;
+        }
+        __syncthreads();
+        if (tid < 32) {      // back substitution with one warp
+            const int lane = tid;
+            double zz[3];
+#pragma unroll
+            for (int q = 0; q < 3; ++q) { const int i = lane + 32 * q; zz[q] = i < NB ? K.rhs[i] : 0.0; }
+            for (int j = NB - 1; j >= 0; --j) {
+                const int owner = j & 31, sl = j >> 5;
+                double zj = sl == 0 ? zz[0] : (sl == 1 ? zz[1] : zz[2]);
+                zj = __shfl_sync(0xffffffffu, zj, owner);
+                const double yj = zj * W.invd[(size_t)f * NB + j];
+                if (lane == owner) { K.yn[j] = yj; W.y[(size_t)f * NB + j] = yj; }
+#pragma unroll
+                for (int q = 0; q < 3; ++q) { const int i = lane + 32 * q; if (i < j) zz[q] -= K.M[j][i] * yj; }
+            }
+        }
+        __syncthreads();
+    }
+    return true;
+}
+
+template <int T>
+__global__ void __launch_bounds__(T, 1) fit_window_kernel(const FitConst* __restrict__ C, int nprob, const WinProblem* __restrict__ probs,
+                                                          const b3d_kp* __restrict__ kps_all, const int32_t* __restrict__ nkp_all,
+                                                          const double* __restrict__ R0_all, double* __restrict__ poses,
+                                                          double* __restrict__ Wshape, uint8_t* __restrict__ usable,
+                                                          b3d_iter_record* __restrict__ trace, int trace_stride, int32_t* __restrict__ niters,
+                                                          int32_t* __restrict__ term, double* __restrict__ workspace) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    WinSmem& S = *reinterpret_cast<WinSmem*>(smem_raw);
+    const int tid = threadIdx.x, pb = blockIdx.x;
+    if (pb >= nprob) return;
+    const WinProblem pr = probs[pb];
+    const int F = pr.count, n = F * NB + NS;
+    const b3d_kp* kps = kps_all + (size_t)pr.first * MAXKP;
+    const int32_t* nkp = nkp_all + pr.first;
+    const double* R0 = R0_all + (size_t)pr.first * 9;
+    double* xin = poses + (size_t)pr.first * NB;
+    double* win = Wshape + (size_t)pr.first * NS;
+    b3d_iter_record* tr = trace ? trace + (size_t)pb * trace_stride : nullptr;
+    WinWs W;
+    W.carve(workspace + pr.ws_offset, F);
+    const double lam2 = C->lambda_temp * C->lambda_temp;
+    const bool temporal = C->lambda_temp > 0.0 && F > 1;
+
+    for (int k = tid; k < F * NB; k += T) W.x[k] = xin[k];
+    if (tid < NS) W.x[(size_t)F * NB + tid] = win[tid];
+    __syncthreads();
+
+    double radius = wInitialRadius, decrease_factor = 2.0, x_cost = 0.0, cand_cost = 0.0, mcc = 0.0;
+    bool reuse_diagonal = false, step_successful = true;
+    int num_invalid = 0, iteration = 0, nrec = 0, termination = 0;
+    b3d_iter_record it;
+    it.cost = it.cost_change = it.gradient_max_norm = it.step_norm = it.relative_decrease = it.radius = 0.0;
+    it.flags = 0; it.aux = -1;
+
+    auto block_max = [&](double v) -> double {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_down_sync(0xffffffffu, v, o));
+        __syncthreads();
+        if ((tid & 31) == 0) S.red[tid >> 5] = v;
+        __syncthreads();
+        double m = 0.0;
+        for (int i = 0; i < T / 32; ++i) m = fmax(m, S.red[i]);
+        __syncthreads();
+        return m;
+    };
+    auto eval_grad_jac = [&](bool first) -> bool {
+        x_cost = win_evaluate<T, true>(C, F, W.x, kps, nkp, R0, W, S);
+        if (!isfinite(x_cost)) return false;
+        it.cost = x_cost;
+        __syncthreads();
+        if (first) {
+            for (int k = tid; k < n; k += T) {
+                const double d = k < F * NB ? W.Hd[(size_t)(k / NB) * NB * NB + (k % NB) * (NB + 1)] : W.Hw[(k - F * NB) * (NS + 1)];
+                W.scale[k] = 1.0 / (1.0 + sqrt(d));
+            }
+            __syncthreads();
+        }
+        // Jacobi scaling of the blocks (column scaling of J on both sides of J^T J)
+        for (size_t idx = tid; idx < (size_t)F * NB * NB; idx += T) {
+            const int f = (int)(idx / (NB * NB)), r = (int)(idx % (NB * NB)) / NB, c = (int)(idx % NB);
+            W.Hd[idx] *= W.scale[(size_t)f * NB + r] * W.scale[(size_t)f * NB + c];
+        }
+        for (size_t idx = tid; idx < (size_t)F * NS * NB; idx += T) {
+            const int f = (int)(idx / (NS * NB)), s = (int)(idx % (NS * NB)) / NB, c = (int)(idx % NB);
+            W.Ha[idx] *= W.scale[(size_t)F * NB + s] * W.scale[(size_t)f * NB + c];
+        }
+        if (tid < NS * NS) W.Hw[tid] *= W.scale[(size_t)F * NB + tid / NS] * W.scale[(size_t)F * NB + tid % NS];
+        double gm = 0.0;
+        for (int k = tid; k < n; k += T) { const double gk = W.g[k]; W.gs[k] = gk * W.scale[k]; gm = fmax(gm, fabs(gk)); }
+        it.gradient_max_norm = block_max(gm);     // unconstrained: |x - (x - g)| = |g|
+        return true;
+    };
+    auto push = [&]() {
+        it.radius = radius;
+        it.aux = -1;
+        if (tr && nrec < trace_stride && tid == 0) tr[nrec] = it;
+        ++nrec;
+    };
+    auto norm_of = [&](const double* v) -> double {
+        double a = 0.0;
+        for (int k = tid; k < n; k += T) a += v[k] * v[k];
+        return sqrt(block_sum<T>(a, S.red));
+    };
+
+    double x_norm = norm_of(W.x);
+    if (!eval_grad_jac(true)) {
+        termination = B3D_TERM_EVAL_FAILURE;
+    } else {
+        it.flags = 3;
+        for (;;) {
+            push();
+            if (iteration >= C->max_iters) { termination = B3D_TERM_MAX_ITERS; break; }
+            if (step_successful && it.gradient_max_norm <= wGradientTolerance) { termination = B3D_TERM_GRAD_TOL; break; }
+            if (!(radius > wMinRadius)) { termination = B3D_TERM_MIN_RADIUS; break; }
+            const double prev_gmax = it.gradient_max_norm;
+            it.cost = it.cost_change = it.gradient_max_norm = it.step_norm = it.relative_decrease = 0.0;
+            it.flags = 0;
+            ++iteration;
+            step_successful = false;
+            if (!reuse_diagonal) {
+                for (int k = tid; k < n; k += T) {
+                    const double d = k < F * NB ? W.Hd[(size_t)(k / NB) * NB * NB + (k % NB) * (NB + 1)] : W.Hw[(k - F * NB) * (NS + 1)];
+                    W.diag[k] = fmin(fmax(d, wMinDiagonal), wMaxDiagonal);
+                }
+            }
+            __syncthreads();
+            reuse_diagonal = true;
+            bool step_valid = false;
+            if (win_solve<T>(C, F, radius, W, S)) {
+                __syncthreads();
+                // model_cost_change = y^T gs - y^T H_s y / 2 (step = -y)
+                double v = 0.0, fin = 0.0;
+                for (size_t idx = tid; idx < (size_t)F * NB * NB; idx += T) {
+                    const int f = (int)(idx / (NB * NB)), r = (int)(idx % (NB * NB)) / NB, c = (int)(idx % NB);
+                    v -= 0.5 * W.Hd[idx] * W.y[(size_t)f * NB + r] * W.y[(size_t)f * NB + c];
+                }
+                for (size_t idx = tid; idx < (size_t)F * NS * NB; idx += T) {
+                    const int f = (int)(idx / (NS * NB)), s = (int)(idx % (NS * NB)) / NB, c = (int)(idx % NB);
+                    v -= W.Ha[idx] * W.y[(size_t)F * NB + s] * W.y[(size_t)f * NB + c];
+                }
+                if (tid < NS * NS) v -= 0.5 * W.Hw[tid] * W.y[(size_t)F * NB + tid / NS] * W.y[(size_t)F * NB + tid % NS];
+                if (temporal)
+                    for (int idx = tid; idx < (F - 1) * (NB - 1); idx += T) {
+                        const int f = idx / (NB - 1), k = 1 + idx % (NB - 1);
+                        const size_t a = (size_t)f * NB + k, b = a + NB;
+                        v += lam2 * W.scale[a] * W.scale[b] * W.y[a] * W.y[b];     // off-diagonal entry is -lambda^2 s_a s_b, counted twice, halved
+                    }
+                for (int k = tid; k < n; k += T) { v += W.y[k] * W.gs[k]; fin += isfinite(W.y[k]) ? 0.0 : 1.0; }
+                mcc = block_sum<T>(v, S.red);
+                const double bad = block_sum<T>(fin, S.red);
+                step_valid = (bad == 0.0) && (mcc > 0.0);
+            }
+            if (!step_valid) {
+                if (++num_invalid >= wMaxConsecutiveInvalidSteps) { termination = B3D_TERM_INVALID_STEPS; break; }
+                radius = radius / decrease_factor; decrease_factor *= 2.0;
+                it.cost = x_cost; it.gradient_max_norm = prev_gmax;
+                continue;
+            }
+            num_invalid = 0;
+            double sn = 0.0;
+            for (int k = tid; k < n; k += T) {
+                const double d = -W.y[k] * W.scale[k];
+                const double c = W.x[k] + d;
+                W.cand[k] = c;
+                const double e = W.x[k] - c;
+                sn += e * e;
+            }
+            it.flags = 1;
+            __syncthreads();
+            cand_cost = win_evaluate<T, false>(C, F, W.cand, kps, nkp, R0, W, S);
+            if (!isfinite(cand_cost)) cand_cost = DBL_MAX;
+            it.step_norm = sqrt(block_sum<T>(sn, S.red));
+            if (it.step_norm <= wParameterTolerance * (x_norm + wParameterTolerance)) { termination = B3D_TERM_PARAM_TOL; break; }
+            it.cost_change = x_cost - cand_cost;
+            if (fabs(it.cost_change) <= wFunctionTolerance * x_cost) { termination = B3D_TERM_FUNC_TOL; break; }
+            it.relative_decrease = it.cost_change / mcc;
+            if (it.relative_decrease > wMinRelativeDecrease) {
+                __syncthreads();
+                for (int k = tid; k < n; k += T) W.x[k] = W.cand[k];
+                __syncthreads();
+                x_norm = norm_of(W.x);
+                if (!eval_grad_jac(false)) { termination = B3D_TERM_EVAL_FAILURE; break; }
+                step_successful = true;
+                it.flags |= 2;
+                const double q = 2.0 * it.relative_decrease - 1.0;
+                radius = radius / fmax(1.0 / 3.0, 1.0 - q * q * q);
+                radius = fmin(wMaxRadius, radius);
+                decrease_factor = 2.0;
+                reuse_diagonal = false;
+            } else {
+                radius = radius / decrease_factor; decrease_factor *= 2.0;
+                it.cost = cand_cost;
+            }
+        }
+    }
+    __syncthreads();
+    for (int k = tid; k < F * NB; k += T) xin[k] = W.x[k];
+    if (tid < NS) win[tid] = W.x[(size_t)F * NB + tid];
+    if (tid == 0) {
+        if (usable) usable[pb] = (termination >= B3D_TERM_PARAM_TOL && termination <= B3D_TERM_MIN_RADIUS) ? 1 : 0;
+        if (niters) niters[pb] = nrec;
+        if (term) term[pb] = termination;
+    }
+}
+
+int build_fit_const(const b3d_model* m, const b3d_gmm* gmm, const b3d_fit_opts* o, bool multi, FitConst* fc);   // fit_single.cu
+
+}  // namespace b3d
+
+using namespace b3d;
+
+extern "C" {
+
+int b3d_fit_windows_dev(const b3d_model* m, const b3d_fit_opts* opts, int32_t nprob, const int32_t* first, const int32_t* count,
+                        const b3d_kp* kps, const int32_t* nkp, const double* R0, double* poses, double* W, uint8_t* usable,
+                        b3d_iter_record* trace, int32_t trace_stride, int32_t* niters, int32_t* term, void* stream) {
+    if (!m || !opts || !first || !count || !kps || !nkp || !R0 || !poses || !W) return set_error(B3D_EINVAL, "b3d_fit_windows: null argument");
+    if (nprob < 0 || opts->max_iters < 0) return set_error(B3D_EINVAL, "b3d_fit_windows: negative size");
+    if (trace && trace_stride <= 0) return set_error(B3D_EINVAL, "b3d_fit_windows: trace without trace_stride");
+    if (nprob == 0) return B3D_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    std::vector<WinProblem> probs(nprob);
+    size_t total = 0;
+    for (int p = 0; p < nprob; ++p) {
+        if (count[p] <= 0 || first[p] < 0) return set_error(B3D_EINVAL, "b3d_fit_windows: problem %d has first=%d count=%d", p, first[p], count[p]);
+        probs[p].first = first[p]; probs[p].count = count[p]; probs[p].ws_offset = (int64_t)total;
+        total += win_ws_doubles(count[p]);
+    }
+    FitConst fc;
+    if (int rc = build_fit_const(m, nullptr, opts, true, &fc)) return rc;
+    FitConst* dfc = nullptr;
+    WinProblem* dpr = nullptr;
+    double* ws = nullptr;
+    B3D_CUDA(cudaMallocAsync(&dfc, sizeof(FitConst), st));
+    B3D_CUDA(cudaMallocAsync(&dpr, sizeof(WinProblem) * nprob, st));
+    B3D_CUDA(cudaMallocAsync(&ws, sizeof(double) * total, st));
+    B3D_CUDA(cudaMemcpyAsync(dfc, &fc, sizeof(FitConst), cudaMemcpyHostToDevice, st));
+    B3D_CUDA(cudaMemcpyAsync(dpr, probs.data(), sizeof(WinProblem) * nprob, cudaMemcpyHostToDevice, st));
+    B3D_CUDA(cudaStreamSynchronize(st));      // probs / fc are stack objects: the staged copies must have left them
+    static bool attr_set = false;
+    if (!attr_set) {
+        B3D_CUDA(cudaFuncSetAttribute(fit_window_kernel<FW_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(WinSmem)));
+        attr_set = true;
+    }
+    fit_window_kernel<FW_THREADS><<<nprob, FW_THREADS, sizeof(WinSmem), st>>>(dfc, nprob, dpr, kps, nkp, R0, poses, W, usable, trace, trace_stride,
+                                                                             niters, term, ws);
+    B3D_LAUNCH_CHECK();
+    B3D_CUDA(cudaFreeAsync(ws, st));
+    B3D_CUDA(cudaFreeAsync(dpr, st));
+    B3D_CUDA(cudaFreeAsync(dfc, st));
+    return B3D_OK;
+}
+
+int b3d_fit_window(const b3d_model* m, const b3d_fit_opts* opts, int32_t F, const b3d_kp* kps, const int32_t* nkp, const double* R0,
+                   double* poses, double* w, uint8_t* usable, b3d_iter_record* trace, int32_t trace_cap, int32_t* niters, int32_t* term) {
+    if (!m || !opts || !kps || !nkp || !R0 || !poses || !w) return set_error(B3D_EINVAL, "b3d_fit_window: null argument");
+    if (F <= 0) return F < 0 ? set_error(B3D_EINVAL, "b3d_fit_window: F < 0") : B3D_OK;
+    const size_t nf = (size_t)F;
+    auto al = [](size_t x) { return (x + 255) / 256 * 256; };
+    const size_t s_kp = al(sizeof(b3d_kp) * nf * MAXKP), s_nk = al(4 * nf), s_r0 = al(8 * nf * 9), s_po = al(8 * nf * NPF), s_w = al(8 * nf * NS),
+                 s_tr = trace ? al(sizeof(b3d_iter_record) * (size_t)trace_cap) : 0;
+    char* base = nullptr;
+    B3D_CUDA(cudaMalloc(&base, s_kp + s_nk + s_r0 + s_po + s_w + s_tr + 256 * 3));
+    char* q = base;
+    auto take = [&](size_t s) { char* t = q; q += s; return t; };
+    b3d_kp* d_kp = (b3d_kp*)take(s_kp); int32_t* d_nk = (int32_t*)take(s_nk); double* d_r0 = (double*)take(s_r0);
+    double* d_po = (double*)take(s_po); double* d_w = (double*)take(s_w);
+    b3d_iter_record* d_tr = trace ? (b3d_iter_record*)take(s_tr) : nullptr;
+    uint8_t* d_us = (uint8_t*)take(256); int32_t* d_ni = (int32_t*)take(256); int32_t* d_te = (int32_t*)take(256);
+    cudaError_t e = cudaMemcpy(d_kp, kps, sizeof(b3d_kp) * nf * MAXKP, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_nk, nkp, 4 * nf, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_r0, R0, 8 * nf * 9, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_po, poses, 8 * nf * NPF, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemset(d_w, 0, 8 * nf * NS);
+    if (e == cudaSuccess) e = cudaMemcpy(d_w, w, 8 * NS, cudaMemcpyHostToDevice);     // the shared block = the window-front avatar's w
+    if (e == cudaSuccess && d_tr) e = cudaMemset(d_tr, 0, s_tr);
+    int rc = B3D_OK;
+    if (e == cudaSuccess) {
+        const int32_t first = 0, count = F;
+        rc = b3d_fit_windows_dev(m, opts, 1, &first, &count, d_kp, d_nk, d_r0, d_po, d_w, d_us, d_tr, trace_cap, d_ni, d_te, nullptr);
+        if (!rc) {
+            e = cudaStreamSynchronize(nullptr);
+            if (e == cudaSuccess) e = cudaMemcpy(poses, d_po, 8 * nf * NPF, cudaMemcpyDeviceToHost);
+            if (e == cudaSuccess) e = cudaMemcpy(w, d_w, 8 * NS, cudaMemcpyDeviceToHost);
+            if (e == cudaSuccess && usable) e = cudaMemcpy(usable, d_us, 1, cudaMemcpyDeviceToHost);
+            if (e == cudaSuccess && trace) e = cudaMemcpy(trace, d_tr, sizeof(b3d_iter_record) * (size_t)trace_cap, cudaMemcpyDeviceToHost);
+            if (e == cudaSuccess && niters) e = cudaMemcpy(niters, d_ni, 4, cudaMemcpyDeviceToHost);
+            if (e == cudaSuccess && term) e = cudaMemcpy(term, d_te, 4, cudaMemcpyDeviceToHost);
+        }
+    }
+    cudaFree(base);
+    if (e != cudaSuccess) return set_error(B3D_ECUDA, "b3d_fit_window: %s", cudaGetErrorString(e));
+    return rc;
+}
+
+}  // extern "C"

@@ -186,6 +186,25 @@ int b3d_writeback_dev(int32_t F, const double* poses, double* R0, double* r, dou
 int b3d_mean_pixel_error(int32_t F, const b3d_kp* kps, const int32_t* nkp, const double* jointPos, double fx, double fy,
                          double cx, double cy, double* err);
 
+/* ===================================================================================================== */
+/* Entry (2), multi-frame: replaces the ceres::Problem + ceres::Solve inside OptimizeMultiFrame            */
+/*   (include/MultiFrameBA.h:33-177) and the anchor / window schedule of src/main_multi_frame.cpp:109-201   */
+/* ===================================================================================================== */
+/* One window or anchor chain of F frames (opts->mode is ignored; beta_pose is the L2 pose prior, beta_shape the shape
+ * prior, lambda_temp the temporal weight; no bounds):
+ *   kps F x 17, nkp F, R0 F x 9 = avatars[f]->r[0] (in; the caller applies b3d_writeback afterwards, as MultiFrameBA.h:154-172)
+ *   poses F x 76 in/out (FramePoseParams), w 10 in/out (the shared block = avatars.front()->w, MultiFrameBA.h:67)
+ *   usable 1, trace trace_cap records or NULL, niters / term 1 or NULL. */
+int b3d_fit_window(const b3d_model* m, const b3d_fit_opts* opts, int32_t F, const b3d_kp* kps, const int32_t* nkp,
+                   const double* R0, double* poses, double* w, uint8_t* usable, b3d_iter_record* trace, int32_t trace_cap,
+                   int32_t* niters, int32_t* term);
+/* nprob independent windows in one launch.  Problem p covers frames [first[p], first[p] + count[p]) of the DEVICE frame
+ * arrays kps / nkp / R0 / poses / W (N x 10: row first[p] is problem p's shared shape block); first / count are HOST arrays.
+ * usable / niters / term: nprob entries (device); trace: nprob x trace_stride (device) or NULL. */
+int b3d_fit_windows_dev(const b3d_model* m, const b3d_fit_opts* opts, int32_t nprob, const int32_t* first, const int32_t* count,
+                        const b3d_kp* kps, const int32_t* nkp, const double* R0, double* poses, double* W, uint8_t* usable,
+                        b3d_iter_record* trace, int32_t trace_stride, int32_t* niters, int32_t* term, void* stream);
+
 int b3d_mean_pixel_error_dev(int32_t F, const b3d_kp* kps, const int32_t* nkp, const double* jointPos, double fx, double fy,
                              double cx, double cy, double* err, void* stream);
 
