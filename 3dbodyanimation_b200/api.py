@@ -216,6 +216,30 @@ def fit_window(model: AvatarModel, opts: capi.FitOpts, kps, nkp, R0, poses, w, w
     return dict(poses=poses, w=w, usable=bool(usable[0]), trace=None if trace is None else trace[:n], niters=n, term=int(term[0]))
 
 
+def seq_opts(skip=10, wsize=20, overlap=5, it1=1000, it2=60, num_shards=1, beta_pose=5.0, beta_shape=25.0, lambda_temp=3.0,
+             beta_shape_lock=1e5) -> capi.SeqOpts:
+    """Defaults are the code defaults of src/main_multi_frame.cpp:29-36 (it2 = 60 and beta_shape_lock = 1e5 are hard-coded there)."""
+    return capi.SeqOpts(skip, wsize, overlap, it1, it2, num_shards, beta_pose, beta_shape, lambda_temp, beta_shape_lock)
+
+
+def fit_sequences(model: AvatarModel, base: capi.FitOpts, so: capi.SeqOpts, kps, nkp, poses, R0, W, seq_first=None, seq_len=None):
+    """3dba_multi's anchor + sliding-window schedule for one or several back-to-back sequences (b3d_fit_sequences)."""
+    kps = np.ascontiguousarray(kps, dtype=KP_DTYPE).reshape(-1, MAXKP)
+    n = kps.shape[0]
+    nkp = np.ascontiguousarray(nkp, dtype=np.int32).reshape(n)
+    poses, R0, W = _f64(poses).reshape(n, NPF).copy(), _f64(R0).reshape(n, 9).copy(), _f64(W).reshape(n, NS).copy()
+    sf = np.ascontiguousarray([0] if seq_first is None else seq_first, dtype=np.int32)
+    sl = np.ascontiguousarray([n] if seq_len is None else seq_len, dtype=np.int32)
+    r, p = np.zeros((n, NJ, 9)), np.zeros((n, 3))
+    stride = so.wsize - so.overlap
+    cap = int(sum(1 + len(range(0, int(l), stride)) + max(so.num_shards, 1) for l in sl))
+    it, te = np.zeros(cap, dtype=np.int32), np.zeros(cap, dtype=np.int32)
+    nfail = C.c_int32(0)
+    check(lib().b3d_fit_sequences(model.h, C.byref(base), C.byref(so), len(sf), ptr(sf), ptr(sl), n, ptr(kps), ptr(nkp), ptr(poses), ptr(R0),
+                                  ptr(W), ptr(r), ptr(p), ptr(it), ptr(te), C.byref(nfail)), "b3d_fit_sequences")
+    return dict(poses=poses, R0=R0, W=W, r=r, p=p, nfail=nfail.value, solve_iters=it, solve_term=te)
+
+
 def writeback(poses, R0):
     """a15: R0 <- R(rootAA) R0; r[0] = R0, r[j] = R(jointAA_j); p = rootT.  poses (F,76), R0 (F,9)."""
     poses = _f64(poses).reshape(-1, NPF)

@@ -32,12 +32,6 @@ constexpr double wMinRelativeDecrease = 1e-3;
 constexpr double wFunctionTolerance = 1e-6, wGradientTolerance = 1e-10, wParameterTolerance = 1e-8;
 constexpr int wMaxConsecutiveInvalidSteps = 5;
 
-// per-problem global workspace, in doubles
-__host__ __device__ inline size_t win_ws_doubles(int F) {
-    const size_t n = (size_t)F * NB + NS;
-    return 10 * n + (size_t)F * (3 * NB * NB + 2 * NS * NB) + 2 * NS * NS + (size_t)F * NB;
-}
-
 struct WinWs {
     double *x, *cand, *g, *gs, *scale, *diag, *y, *delta, *z, *tmp;   // n each
     double *Hd, *Ld, *Lo;     // F x 76 x 76: scaled J^T J diagonal blocks; factor diagonal blocks; factor sub-diagonal blocks
@@ -86,11 +80,6 @@ struct WinSmem {
     double Hw[NS * NS], gw[NS], yw[NS], Sw[NS * NS], zw[NS];
     double piv[2];
     int32_t flag;
-};
-
-struct WinProblem {
-    int32_t first, count;     // frames [first, first + count) of the frame arrays; the shared w block is row `first` of W
-    int64_t ws_offset;        // doubles into the workspace
 };
 
 // ---- evaluate every frame of the problem at parameters xp (n = 76 F + 10) -----------------------------------------------
@@ -573,7 +562,23 @@ __global__ void __launch_bounds__(T, 1) fit_window_kernel(const FitConst* __rest
     }
 }
 
-int build_fit_const(const b3d_model* m, const b3d_gmm* gmm, const b3d_fit_opts* o, bool multi, FitConst* fc);   // fit_single.cu
+}  // namespace b3d
+
+namespace b3d {
+
+int win_launch(const FitConst* dfc, const WinProblem* dprobs, int nprob, const b3d_kp* kps, const int32_t* nkp, const double* R0, double* poses,
+               double* W, uint8_t* usable, b3d_iter_record* trace, int trace_stride, int32_t* niters, int32_t* term, double* ws, cudaStream_t st) {
+    if (nprob <= 0) return B3D_OK;
+    static bool attr_set = false;
+    if (!attr_set) {
+        B3D_CUDA(cudaFuncSetAttribute(fit_window_kernel<FW_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(WinSmem)));
+        attr_set = true;
+    }
+    fit_window_kernel<FW_THREADS><<<nprob, FW_THREADS, sizeof(WinSmem), st>>>(dfc, nprob, dprobs, kps, nkp, R0, poses, W, usable, trace, trace_stride,
+                                                                             niters, term, ws);
+    B3D_LAUNCH_CHECK();
+    return B3D_OK;
+}
 
 }  // namespace b3d
 
@@ -607,14 +612,7 @@ int b3d_fit_windows_dev(const b3d_model* m, const b3d_fit_opts* opts, int32_t np
     B3D_CUDA(cudaMemcpyAsync(dfc, &fc, sizeof(FitConst), cudaMemcpyHostToDevice, st));
     B3D_CUDA(cudaMemcpyAsync(dpr, probs.data(), sizeof(WinProblem) * nprob, cudaMemcpyHostToDevice, st));
     B3D_CUDA(cudaStreamSynchronize(st));      // probs / fc are stack objects: the staged copies must have left them
-    static bool attr_set = false;
-    if (!attr_set) {
-        B3D_CUDA(cudaFuncSetAttribute(fit_window_kernel<FW_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(WinSmem)));
-        attr_set = true;
-    }
-    fit_window_kernel<FW_THREADS><<<nprob, FW_THREADS, sizeof(WinSmem), st>>>(dfc, nprob, dpr, kps, nkp, R0, poses, W, usable, trace, trace_stride,
-                                                                             niters, term, ws);
-    B3D_LAUNCH_CHECK();
+    if (int rc = win_launch(dfc, dpr, nprob, kps, nkp, R0, poses, W, usable, trace, trace_stride, niters, term, ws, st)) return rc;
     B3D_CUDA(cudaFreeAsync(ws, st));
     B3D_CUDA(cudaFreeAsync(dpr, st));
     B3D_CUDA(cudaFreeAsync(dfc, st));

@@ -38,6 +38,23 @@ struct FitConst {
     const double* gmm_consts;              // ncomp
 };
 
+// host side (fit_single.cu): fills the launch-constant block
+int build_fit_const(const b3d_model* m, const b3d_gmm* gmm, const b3d_fit_opts* o, bool multi, FitConst* fc);
+
+// one multi-frame problem of a batched launch (fit_window.cu)
+struct WinProblem {
+    int32_t first, count;     // frames [first, first + count) of the frame arrays; the shared w block is row `first` of W
+    int64_t ws_offset;        // doubles into the workspace
+};
+// per-problem global workspace, in doubles
+__host__ __device__ inline size_t win_ws_doubles(int F) {
+    const size_t n = (size_t)F * NPF + NS;
+    return 10 * n + (size_t)F * (3 * NPF * NPF + 2 * NS * NPF) + 2 * NS * NS + (size_t)F * NPF;
+}
+// enqueue the LM solves of nprob problems (device-resident constants / problem table / workspace); no synchronisation
+int win_launch(const FitConst* dfc, const WinProblem* dprobs, int nprob, const b3d_kp* kps, const int32_t* nkp, const double* R0, double* poses,
+               double* W, uint8_t* usable, b3d_iter_record* trace, int trace_stride, int32_t* niters, int32_t* term, double* ws, cudaStream_t st);
+
 // ---------------------------------------------------------------------------------------------------------------
 // rotations
 // ---------------------------------------------------------------------------------------------------------------

@@ -205,6 +205,32 @@ int b3d_fit_windows_dev(const b3d_model* m, const b3d_fit_opts* opts, int32_t np
                         const b3d_kp* kps, const int32_t* nkp, const double* R0, double* poses, double* W, uint8_t* usable,
                         b3d_iter_record* trace, int32_t trace_stride, int32_t* niters, int32_t* term, void* stream);
 
+/* The anchor / sliding-window schedule of 3dba_multi (src/main_multi_frame.cpp:109-201; argv defaults :29-36). */
+typedef struct b3d_seq_opts {
+    int32_t skip;            /* anchor_skip (10) */
+    int32_t wsize;           /* WSIZE (20) */
+    int32_t overlap;         /* OVERLAP (5) */
+    int32_t it1;             /* max_iters of the anchor stage (1000) */
+    int32_t it2;             /* max_iters of every window: the reference hard-codes 60 (:185) and ignores argv[6] */
+    int32_t num_shards;      /* 1 = the reference's serial chain of windows; G > 1 = sharded schedule with halo hand-off */
+    double beta_pose, beta_shape, lambda_temp;
+    double beta_shape_lock;  /* beta_shape of stage 2: the reference hard-codes 1e5 (:183) */
+} b3d_seq_opts;
+
+/* One sequence of N frames, host pointers.  In/out per frame: poses N x 76 (FramePoseParams), R0 N x 9 (avatars[i]->r[0]),
+ * W N x 10 (avatars[i]->w).  Out: r N x 24 x 9 and p N x 3 (avatar rotations / translation after the last write-back; may be
+ * NULL); solve_iters / solve_term (may be NULL): one entry per LM solve in the order [anchor stage, windows in index order,
+ * fix-up re-solves in shard order]; nfail = number of solves whose solution is not usable. */
+int b3d_fit_sequence(const b3d_model* m, const b3d_fit_opts* base, const b3d_seq_opts* so, int32_t N, const b3d_kp* kps,
+                     const int32_t* nkp, double* poses, double* R0, double* W, double* r, double* p, int32_t* solve_iters,
+                     int32_t* solve_term, int32_t* nfail);
+/* nseq independent sequences stored back to back in arrays of N frames: sequence q = frames [seq_first[q], + seq_len[q]).
+ * Their chains are batched into the same kernel launches (one CTA per sequence and shard per wave). */
+int b3d_fit_sequences(const b3d_model* m, const b3d_fit_opts* base, const b3d_seq_opts* so, int32_t nseq,
+                      const int32_t* seq_first, const int32_t* seq_len, int32_t N, const b3d_kp* kps, const int32_t* nkp,
+                      double* poses, double* R0, double* W, double* r, double* p, int32_t* solve_iters, int32_t* solve_term,
+                      int32_t* nfail);
+
 int b3d_mean_pixel_error_dev(int32_t F, const b3d_kp* kps, const int32_t* nkp, const double* jointPos, double fx, double fy,
                              double cx, double cy, double* err, void* stream);
 
