@@ -8,6 +8,9 @@
 //                        write (3 V sizeof(T) per body); everything else is L2 resident.
 //   posedirs_kernel    : optional standard-SMPL pose blendshapes (an extension: the reference has them commented out,
 //                        AvatarModel.cpp:104-109), CUDA-core path.
+#include <algorithm>
+#include <cstdlib>
+
 #include "internal.hpp"
 
 namespace b3d {
@@ -199,6 +202,262 @@ __global__ void __launch_bounds__(LBS_THREADS) smpl_lbs_kernel(const T* __restri
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// LBS, float32, <= 4 weights per vertex: the HBM-bound kernel of the path (82,680 B of cloud per body).
+//
+// The generic kernel above is bound by shared-memory bandwidth, not HBM: every lane gathers its own 4 x 12 joint-transform
+// floats per body (6 KB per warp and body through a 128 B/clk crossbar).  Here a CTA still owns 256 consecutive vertices
+// (so that its output is one contiguous 3 KB run per body), but inside the tile the vertices are processed in joint-tuple
+// order (SortedTables): the lanes of a warp then share their joint transforms and each LDS.128 is a broadcast of a few
+// addresses.  Results are scattered into a shared staging row at their original position and leave as coalesced 8-byte
+// stores, two bodies per barrier, double buffered.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int LS_TILE = 256;                       // vertices per CTA = threads per CTA
+constexpr int LS_NB = 8;                           // bodies staged per pass (even)
+constexpr int LS_ROW = 3 * LS_TILE + 2 * (LS_TILE / 32);   // staging row: 2 pad floats after every 96 (bank spreading, keeps 8 B alignment)
+
+__device__ __forceinline__ int ls_pos(int e) { return e + 2 * (e / 96); }   // element 3 * loc + c -> padded position
+
+__global__ void __launch_bounds__(LS_TILE, 3) smpl_lbs_sorted_kernel(const float* __restrict__ vert, const float* __restrict__ wval,
+                                                                      const int32_t* __restrict__ wjoff, const int32_t* __restrict__ locs,
+                                                                      int V, int Vpad, int B, int bodies_per_cta,
+                                                                      const float* __restrict__ wshape, const float* __restrict__ G,
+                                                                      float* __restrict__ cloud) {
+    __shared__ __align__(16) float s_g[LS_NB][NJ * 12];
+    __shared__ __align__(16) float s_w[LS_NB][12];
+    __shared__ __align__(16) float s_out[2][2][LS_ROW];
+    const int tid = threadIdx.x;
+    const int tile_base = blockIdx.x * LS_TILE;
+    const int slot = tile_base + tid;                   // < Vpad by construction of the grid
+    const int nvalid = min(LS_TILE, V - tile_base);     // vertices of this tile that exist
+    const int nout2 = (3 * nvalid) / 2;                 // float2 per body (3 * nvalid is even: V and LS_TILE are even)
+
+    float base[3], sd[3][NS], ww[4];
+    int wj[4];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        base[c] = vert[(size_t)c * Vpad + slot];
+#pragma unroll
+        for (int s = 0; s < NS; ++s) sd[c][s] = vert[(size_t)(3 + NS * c + s) * Vpad + slot];
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        ww[k] = wval[(size_t)k * Vpad + slot];
+        wj[k] = wjoff[(size_t)k * Vpad + slot];
+    }
+    const int opos = ls_pos(3 * locs[slot]);            // 3 * loc + c stays inside one 96-block for c = 0..2
+
+    const int b_begin = blockIdx.y * bodies_per_cta;
+    const int b_end = min(B, b_begin + bodies_per_cta);
+    int buf = 0;
+    for (int b0 = b_begin; b0 < b_end; b0 += LS_NB) {
+        const int nb = min(LS_NB, b_end - b0);
+        __syncthreads();   // previous pass finished reading s_g / s_w
+        {
+            const float4* src = reinterpret_cast<const float4*>(G + (size_t)b0 * NJ * 12);   // 1152 B per body: 16 B aligned
+            float4* dst = reinterpret_cast<float4*>(&s_g[0][0]);
+            for (int i = tid; i < nb * (NJ * 3); i += LS_TILE) dst[i] = src[i];
+            for (int i = tid; i < nb * 12; i += LS_TILE) {
+                const int bb = i / 12, s = i % 12;
+                s_w[bb][s] = s < NS ? wshape[(size_t)(b0 + bb) * NS + s] : 0.f;
+            }
+        }
+        __syncthreads();
+        for (int i = 0; i < nb; i += 2) {
+            const int npair = min(2, nb - i);
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                if (h < npair) {
+                    const float4* sw4 = reinterpret_cast<const float4*>(s_w[i + h]);
+                    const float4 w0 = sw4[0], w1 = sw4[1], w2 = sw4[2];
+                    const float wsv[NS] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w, w2.x, w2.y};
+                    float x = base[0], y = base[1], z = base[2];
+#pragma unroll
+                    for (int s = 0; s < NS; ++s) {
+                        x = fmaf(sd[0][s], wsv[s], x); y = fmaf(sd[1][s], wsv[s], y); z = fmaf(sd[2][s], wsv[s], z);
+                    }
+                    float ax = 0.f, ay = 0.f, az = 0.f;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const float4* g4 = reinterpret_cast<const float4*>(&s_g[i + h][wj[k]]);   // col-major 3x4: g[3 col + row]
+                        const float4 ga = g4[0], gb = g4[1], gc = g4[2];
+                        const float tx = fmaf(ga.x, x, fmaf(ga.w, y, fmaf(gb.z, z, gc.y)));
+                        const float ty = fmaf(ga.y, x, fmaf(gb.x, y, fmaf(gb.w, z, gc.z)));
+                        const float tz = fmaf(ga.z, x, fmaf(gb.y, y, fmaf(gc.x, z, gc.w)));
+                        ax = fmaf(ww[k], tx, ax); ay = fmaf(ww[k], ty, ay); az = fmaf(ww[k], tz, az);
+                    }
+                    float* so = s_out[buf][h] + opos;
+                    so[0] = ax; so[1] = ay; so[2] = az;
+                }
+            }
+            __syncthreads();
+            // copy-out: per body 3 * nvalid consecutive floats of the cloud, as float2 (body rows are 8 B aligned: 3 V is even)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                if (h < npair) {
+                    float2* dst = reinterpret_cast<float2*>(cloud + ((size_t)(b0 + i + h) * V + tile_base) * 3);
+                    const float* row = s_out[buf][h];
+                    for (int e2 = tid; e2 < nout2; e2 += LS_TILE)
+                        dst[e2] = *reinterpret_cast<const float2*>(row + ls_pos(2 * e2));
+                }
+            }
+            buf ^= 1;
+        }
+    }
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------
+// LBS, float32, large batches: lane = body.
+//
+// With lane = vertex every lane has to fetch its own 4 x 12 transform floats per body from shared memory: 48 register-fill
+// wavefronts per warp and body, which is what bounds the kernels above (ncu: LSU wavefronts 72 % of peak, DRAM 15 %).
+// Here the roles are swapped.  A CTA owns one 256-vertex range and streams batches of 32 bodies; a lane keeps ITS body's shape
+// vector and the four transforms of the current joint tuple in registers, and the warp walks its 32 slots of the range in
+// joint-tuple order: per slot the 38 per-vertex constants arrive as ten warp-uniform LDS.128 and the transforms are re-read only
+// when the tuple changes.  Results go to a [body][3 x 256] staging tile (odd row stride: conflict free) and leave as full rows.
+// The transforms of the next batch are fetched by TMA bulk copies (cp.async.bulk + mbarrier) while the current one computes.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int BL_R = 256, BL_THREADS = 256, BL_NB = 32, BL_REC = 40;
+constexpr int BL_GROW = NJ * 12 + 4;     // 292 floats: rows stay 16 B aligned, lanes of a quarter warp hit distinct 16 B bank groups
+constexpr int BL_OROW = 3 * BL_R + 1;    // 769
+
+struct __align__(16) BlSmem {
+    float rec[BL_R * BL_REC];
+    int4 joff[BL_R];
+    float g[2][BL_NB * BL_GROW];
+    float beta[2][BL_NB * NS];
+    float out[BL_NB * BL_OROW];
+    unsigned long long mbar[2];
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// TMA bulk copy global -> shared, completion counted on an mbarrier (bytes % 16 == 0, both addresses 16 B aligned)
+__device__ __forceinline__ void tma_bulk_g2s(void* dst, const void* src, uint32_t bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)), "l"(src),
+                 "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+__global__ void __launch_bounds__(BL_THREADS, 1) smpl_lbs_bodylane_kernel(const float* __restrict__ rec, const int32_t* __restrict__ joff4,
+                                                                           int V, int B, int bodies_per_cta, const float* __restrict__ wshape,
+                                                                           const float* __restrict__ G, float* __restrict__ cloud) {
+    extern __shared__ __align__(16) unsigned char bl_raw[];
+    BlSmem& S = *reinterpret_cast<BlSmem*>(bl_raw);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int range_base = blockIdx.x * BL_R;
+    const int nvalid = min(BL_R, V - range_base);
+    const int b_begin = blockIdx.y * bodies_per_cta;
+    const int b_end = min(B, b_begin + bodies_per_cta);
+    if (b_begin >= b_end) return;
+
+    // per-range constants -> shared memory (once per CTA)
+    {
+        const float4* src = reinterpret_cast<const float4*>(rec + (size_t)range_base * BL_REC);
+        float4* dst = reinterpret_cast<float4*>(S.rec);
+        for (int i = tid; i < BL_R * BL_REC / 4; i += BL_THREADS) dst[i] = src[i];
+        S.joff[tid] = reinterpret_cast<const int4*>(joff4)[range_base + tid];
+    }
+    if (tid == 0) {
+        mbar_init(&S.mbar[0], 1);
+        mbar_init(&S.mbar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    auto load_beta = [&](int buf, int b0) {   // plain loads: 10 floats per body, read back by the owning lane
+        const int nb = min(BL_NB, b_end - b0);
+        for (int i = tid; i < nb * NS; i += BL_THREADS) S.beta[buf][i] = wshape[(size_t)b0 * NS + i];
+    };
+    auto issue_g = [&](int buf, int b0) {     // one thread: one bulk copy per body row (1152 B), all counted on mbar[buf]
+        const int nb = min(BL_NB, b_end - b0);
+        mbar_expect_tx(&S.mbar[buf], (uint32_t)nb * NJ * 12 * 4);
+        for (int i = 0; i < nb; ++i) tma_bulk_g2s(&S.g[buf][i * BL_GROW], G + (size_t)(b0 + i) * NJ * 12, NJ * 12 * 4, &S.mbar[buf]);
+    };
+    load_beta(0, b_begin);
+    __syncthreads();
+    if (tid == 0) issue_g(0, b_begin);
+
+    const int slot_begin = warp * 32, slot_end = min(slot_begin + 32, nvalid);
+    int it = 0;
+    for (int b0 = b_begin; b0 < b_end; b0 += BL_NB, ++it) {
+        const int buf = it & 1;
+        const int nb = min(BL_NB, b_end - b0);
+        const bool has_next = b0 + BL_NB < b_end;
+        if (has_next && tid == 0) issue_g(buf ^ 1, b0 + BL_NB);      // buffer buf^1 was last read before the barrier that closed batch it-1
+        mbar_wait(&S.mbar[buf], (uint32_t)((it >> 1) & 1));
+
+        float be[NS];
+#pragma unroll
+        for (int s = 0; s < NS; ++s) be[s] = S.beta[buf][lane * NS + s];
+        const float* grow = &S.g[buf][lane * BL_GROW];
+        float* orow = &S.out[lane * BL_OROW];
+        float4 g[4][3];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) g[k][0] = g[k][1] = g[k][2] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 2
+        for (int slot = slot_begin; slot < slot_end; ++slot) {
+            const float4* r4 = reinterpret_cast<const float4*>(&S.rec[slot * BL_REC]);
+            const float4 q0 = r4[0], q1 = r4[1], q2 = r4[2], q3 = r4[3], q4 = r4[4], q5 = r4[5], q6 = r4[6], q7 = r4[7], q8 = r4[8], q9 = r4[9];
+            if (__float_as_int(q9.z)) {   // warp-uniform: the joint tuple changed
+                const int4 jo = S.joff[slot];
+                const int o[4] = {jo.x, jo.y, jo.z, jo.w};
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float4* g4 = reinterpret_cast<const float4*>(grow + o[k]);
+                    g[k][0] = g4[0]; g[k][1] = g4[1]; g[k][2] = g4[2];
+                }
+            }
+            // record: q0 = (bx, by, bz, 3 loc); sdx = q1 q2 q3.xy; sdy = q3.zw q4 q5; sdz = q6 q7 q8.xy; weights = q8.zw q9.xy
+            float x = q0.x, y = q0.y, z = q0.z;
+            x = fmaf(q1.x, be[0], x); x = fmaf(q1.y, be[1], x); x = fmaf(q1.z, be[2], x); x = fmaf(q1.w, be[3], x);
+            x = fmaf(q2.x, be[4], x); x = fmaf(q2.y, be[5], x); x = fmaf(q2.z, be[6], x); x = fmaf(q2.w, be[7], x);
+            x = fmaf(q3.x, be[8], x); x = fmaf(q3.y, be[9], x);
+            y = fmaf(q3.z, be[0], y); y = fmaf(q3.w, be[1], y);
+            y = fmaf(q4.x, be[2], y); y = fmaf(q4.y, be[3], y); y = fmaf(q4.z, be[4], y); y = fmaf(q4.w, be[5], y);
+            y = fmaf(q5.x, be[6], y); y = fmaf(q5.y, be[7], y); y = fmaf(q5.z, be[8], y); y = fmaf(q5.w, be[9], y);
+            z = fmaf(q6.x, be[0], z); z = fmaf(q6.y, be[1], z); z = fmaf(q6.z, be[2], z); z = fmaf(q6.w, be[3], z);
+            z = fmaf(q7.x, be[4], z); z = fmaf(q7.y, be[5], z); z = fmaf(q7.z, be[6], z); z = fmaf(q7.w, be[7], z);
+            z = fmaf(q8.x, be[8], z); z = fmaf(q8.y, be[9], z);
+            const float wk[4] = {q8.z, q8.w, q9.x, q9.y};
+            float ax = 0.f, ay = 0.f, az = 0.f;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {   // col-major 3x4 [R|t]: ga = (r00 r10 r20 r01), gb = (r11 r21 r02 r12), gc = (r22 t0 t1 t2)
+                const float4 ga = g[k][0], gb = g[k][1], gc = g[k][2];
+                const float tx = fmaf(ga.x, x, fmaf(ga.w, y, fmaf(gb.z, z, gc.y)));
+                const float ty = fmaf(ga.y, x, fmaf(gb.x, y, fmaf(gb.w, z, gc.z)));
+                const float tz = fmaf(ga.z, x, fmaf(gb.y, y, fmaf(gc.x, z, gc.w)));
+                ax = fmaf(wk[k], tx, ax); ay = fmaf(wk[k], ty, ay); az = fmaf(wk[k], tz, az);
+            }
+            float* so = orow + __float_as_int(q0.w);
+            so[0] = ax; so[1] = ay; so[2] = az;
+        }
+        __syncthreads();
+        // copy-out: rows of 3 * nvalid consecutive floats; meanwhile stage the next batch's shape vectors
+        if (has_next) load_beta(buf ^ 1, b0 + BL_NB);
+        const int nfl = 3 * nvalid;
+        for (int row = 0; row < nb; ++row) {
+            float* dst = cloud + ((size_t)(b0 + row) * V + range_base) * 3;
+            const float* src = &S.out[row * BL_OROW];
+            for (int e = tid; e < nfl; e += BL_THREADS) dst[e] = src[e];
+        }
+        __syncthreads();
+    }
+}
+
 template <typename T>
 static int forward_impl(const b3d_model* m, int B, const T* w, const T* p, const T* r, T* cloud, T* jointPos, T* jointTrans,
                         int flags, cudaStream_t st) {
@@ -236,7 +495,28 @@ static int forward_impl(const b3d_model* m, int B, const T* w, const T* p, const
         if (use_pd) smpl_lbs_kernel<T, NWV, true><<<grid, LBS_THREADS, 0, st>>>(t.vert, t.wval, t.wjoint, m->V, m->Vpad, B, per, w, G, off, cloud); \
         else smpl_lbs_kernel<T, NWV, false><<<grid, LBS_THREADS, 0, st>>>(t.vert, t.wval, t.wjoint, m->V, m->Vpad, B, per, w, G, nullptr, cloud);   \
     } while (0)
-        if (m->nw == 4) B3D_LBS(4);
+        const bool g_al16 = (reinterpret_cast<uintptr_t>(G) & 15) == 0;
+        // measured on B200 (profiles/r01_forward_sweep.txt): the lane = vertex sorted kernel is the faster one today; the
+        // lane = body kernel is kept selectable (B3D_LBS=bodylane) as the base of the tensor-core shape-blend variant
+        static const bool want_bodylane = [] { const char* e = getenv("B3D_LBS"); return e && !strcmp(e, "bodylane"); }();
+        if (want_bodylane && sizeof(T) == 4 && m->nw == 4 && !use_pd && m->ts.rec && g_al16 && B >= 256) {
+            static bool attr_set = false;
+            if (!attr_set) {
+                B3D_CUDA(cudaFuncSetAttribute(smpl_lbs_bodylane_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BlSmem)));
+                attr_set = true;
+            }
+            const int ranges = m->Vpad / BL_R;
+            int bgroups = std::max(1, (148 * 4) / ranges);                      // ~4 CTAs per SM over the launch, 1 resident
+            int bper = (B + bgroups - 1) / bgroups;
+            bper = (bper + BL_NB - 1) / BL_NB * BL_NB;
+            bgroups = (B + bper - 1) / bper;
+            smpl_lbs_bodylane_kernel<<<dim3(ranges, bgroups), BL_THREADS, sizeof(BlSmem), st>>>(m->ts.rec, m->ts.joff4, m->V, B, bper, (const float*)w,
+                                                                                                 (const float*)G, (float*)cloud);
+        } else if (sizeof(T) == 4 && m->nw == 4 && !use_pd && m->ts.vert && m->V % 2 == 0 && g_al16) {
+            static_assert(LS_TILE == 256, "model.cu sorts the tables in 256-vertex tiles");
+            smpl_lbs_sorted_kernel<<<grid, LS_TILE, 0, st>>>(m->ts.vert, m->ts.wval, m->ts.wjoff, m->ts.loc, m->V, m->Vpad, B, per,
+                                                             (const float*)w, (const float*)G, (float*)cloud);
+        } else if (m->nw == 4) B3D_LBS(4);
         else if (m->nw == 8) B3D_LBS(8);
         else B3D_LBS(NJ);
 #undef B3D_LBS
@@ -274,24 +554,25 @@ int b3d_smpl_forward(const b3d_model* m, int32_t B, int32_t dtype, const void* w
     if (dtype != B3D_F32 && dtype != B3D_F64) return set_error(B3D_EINVAL, "b3d_smpl_forward: bad dtype %d", dtype);
     if (B <= 0) return B < 0 ? set_error(B3D_EINVAL, "b3d_smpl_forward: B < 0") : B3D_OK;
     const size_t es = dtype == B3D_F32 ? 4 : 8, nb = (size_t)B;
-    const size_t sz_w = es * nb * NS, sz_p = es * nb * 3, sz_r = es * nb * NJ * 9;
-    const size_t sz_c = es * nb * 3 * m->V, sz_jp = es * nb * NJ * 3, sz_jt = es * nb * NJ * 12;
+    auto al = [](size_t x) { return (x + 255) / 256 * 256; };   // sub-buffers stay 256 B aligned (the float kernels use 16 B loads)
+    const size_t sz_w = al(es * nb * NS), sz_p = al(es * nb * 3), sz_r = al(es * nb * NJ * 9);
+    const size_t sz_c = es * nb * 3 * m->V, sz_jp = al(es * nb * NJ * 3), sz_jt = al(es * nb * NJ * 12);
     char *dw = nullptr, *dc = nullptr;
     B3D_CUDA(cudaMalloc(&dw, sz_w + sz_p + sz_r + sz_jp + sz_jt));
     char *dp = dw + sz_w, *dr = dp + sz_p, *djp = dr + sz_r, *djt = djp + sz_jp;
     int rc = B3D_OK;
     cudaError_t e = cudaSuccess;
     if (cloud) e = cudaMalloc(&dc, sz_c);
-    if (e == cudaSuccess) e = cudaMemcpy(dw, w, sz_w, cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) e = cudaMemcpy(dp, p, sz_p, cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) e = cudaMemcpy(dr, r, sz_r, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(dw, w, es * nb * NS, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(dp, p, es * nb * 3, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(dr, r, es * nb * NJ * 9, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) {
         rc = b3d_smpl_forward_dev(m, B, dtype, dw, dp, dr, dc, djp, djt, flags, nullptr);
         if (!rc) {
             e = cudaStreamSynchronize(nullptr);
             if (e == cudaSuccess && cloud) e = cudaMemcpy(cloud, dc, sz_c, cudaMemcpyDeviceToHost);
-            if (e == cudaSuccess && jointPos) e = cudaMemcpy(jointPos, djp, sz_jp, cudaMemcpyDeviceToHost);
-            if (e == cudaSuccess && jointTrans) e = cudaMemcpy(jointTrans, djt, sz_jt, cudaMemcpyDeviceToHost);
+            if (e == cudaSuccess && jointPos) e = cudaMemcpy(jointPos, djp, es * nb * NJ * 3, cudaMemcpyDeviceToHost);
+            if (e == cudaSuccess && jointTrans) e = cudaMemcpy(jointTrans, djt, es * nb * NJ * 12, cudaMemcpyDeviceToHost);
         }
     }
     cudaFree(dw);

@@ -58,6 +58,22 @@ struct VertexTables {
     int32_t* wjoint = nullptr;
 };
 
+// Tile-sorted copy of the float tables for the float32 LBS kernel (forward.cu, smpl_lbs_sorted_kernel): inside every tile of
+// LBS_TILE consecutive vertices the vertices are ordered by their joint tuple, so that the lanes of a warp mostly read the
+// same joint transforms from shared memory (broadcast instead of a 32-address gather).  Slot t of a tile holds the vertex
+// tile_base + loc[t]; vert / wval are stored in slot order; wjoint holds float offsets (12 * joint) into a body's transforms.
+struct SortedTables {
+    float* vert = nullptr;       // [(3 + 30)][Vpad]
+    float* wval = nullptr;       // [4][Vpad]
+    int32_t* wjoff = nullptr;    // [4][Vpad]
+    int32_t* loc = nullptr;      // [Vpad]
+    // body-lane kernel (smpl_lbs_bodylane_kernel): one 40-float record per slot, in slot order:
+    //   [0..2] template xyz, [3] int 3 * loc, [4..13] [14..23] [24..33] shapedirs of x / y / z, [34..37] weights,
+    //   [38] int 1 if the joint tuple differs from the previous slot's (or the slot opens a warp's 32-slot share), [39] 0
+    float* rec = nullptr;        // [Vpad][40]
+    int32_t* joff4 = nullptr;    // [Vpad][4]  float offsets 12 * joint of the four weight slots
+};
+
 // small per-model constants passed to kernels by value
 struct SkeletonConst {
     int32_t parent[NJ];
@@ -78,6 +94,7 @@ struct b3d_model {
     b3d::SkeletonConst* d_sk = nullptr;         // device copy
     b3d::VertexTables<float> t32;
     b3d::VertexTables<double> t64;
+    b3d::SortedTables ts;                       // only when nw == 4
     float* posedirs32 = nullptr;                // [207][3][Vpad] (k, c, v)
     double* posedirs64 = nullptr;
     std::vector<uint32_t> faces;                // host copy (rendering only)

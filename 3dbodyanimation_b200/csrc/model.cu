@@ -1,5 +1,6 @@
 // Model handle: one-time derivation (host, float64 — as ark::AvatarModel does at load, external/avatar/AvatarModel.cpp:23-127)
 // and upload of the per-vertex tables in the structure-of-arrays layout the forward kernels read.
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include <mutex>
@@ -52,6 +53,71 @@ static int upload_tables(const b3d_model& m, const std::vector<double>& vert, co
     B3D_CUDA(cudaMemcpy(t.wval, tmp.data(), sizeof(T) * tmp.size(), cudaMemcpyHostToDevice));
     B3D_CUDA(cudaMalloc(&t.wjoint, sizeof(int32_t) * wjoint.size()));
     B3D_CUDA(cudaMemcpy(t.wjoint, wjoint.data(), sizeof(int32_t) * wjoint.size(), cudaMemcpyHostToDevice));
+    return B3D_OK;
+}
+
+// Tile-sorted float tables (SortedTables, internal.hpp): slots of a 256-vertex tile ordered by joint tuple, padding last.
+static int upload_sorted_tables(b3d_model& m, const std::vector<double>& vert, const std::vector<double>& wval,
+                                const std::vector<int32_t>& wjoint) {
+    constexpr int TILE = 256;
+    const size_t Vp = (size_t)m.Vpad;
+    const int rows = 3 + 3 * NS;
+    std::vector<float> sv(rows * Vp, 0.f), sw(4 * Vp, 0.f);
+    std::vector<int32_t> sj(4 * Vp, 0), loc(Vp, 0);
+    std::vector<int> order(TILE);
+    for (size_t base = 0; base < Vp; base += TILE) {
+        for (int i = 0; i < TILE; ++i) order[i] = i;
+        auto key = [&](int i) -> uint64_t {
+            const size_t v = base + i;
+            if ((int)v >= m.V) return ~0ull;
+            uint64_t k = 0;
+            for (int q = 0; q < 4; ++q) k = k * 32 + (uint64_t)(wval[q * Vp + v] != 0.0 ? wjoint[q * Vp + v] : 31);
+            return k;
+        };
+        std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return key(a) < key(b); });
+        for (int t = 0; t < TILE; ++t) {
+            const size_t src = base + order[t], dst = base + t;
+            loc[dst] = order[t];
+            for (int r = 0; r < rows; ++r) sv[r * Vp + dst] = (float)vert[r * Vp + src];
+            for (int q = 0; q < 4; ++q) {
+                sw[q * Vp + dst] = (float)wval[q * Vp + src];
+                // a zero-weight slot re-reads the joint of slot 0, so that it does not add a distinct shared-memory address
+                sj[q * Vp + dst] = 12 * (wval[q * Vp + src] != 0.0 ? wjoint[q * Vp + src] : wjoint[src]);
+            }
+        }
+    }
+    // records of the body-lane kernel
+    std::vector<float> rec(40 * Vp, 0.f);
+    std::vector<int32_t> j4(4 * Vp, 0);
+    for (size_t slot = 0; slot < Vp; ++slot) {
+        float* r = &rec[40 * slot];
+        for (int c = 0; c < 3; ++c) {
+            r[c] = sv[c * Vp + slot];
+            for (int s2 = 0; s2 < NS; ++s2) r[4 + NS * c + s2] = sv[(3 + NS * c + s2) * Vp + slot];
+        }
+        const int32_t l3 = 3 * loc[slot];
+        std::memcpy(&r[3], &l3, 4);
+        bool changed = (slot % 32) == 0;
+        for (int q = 0; q < 4; ++q) {
+            r[34 + q] = sw[q * Vp + slot];
+            j4[4 * slot + q] = sj[q * Vp + slot];
+            if (slot > 0 && sj[q * Vp + slot] != sj[q * Vp + slot - 1]) changed = true;
+        }
+        const int32_t flag = changed ? 1 : 0;
+        std::memcpy(&r[38], &flag, 4);
+    }
+    B3D_CUDA(cudaMalloc(&m.ts.rec, sizeof(float) * rec.size()));
+    B3D_CUDA(cudaMemcpy(m.ts.rec, rec.data(), sizeof(float) * rec.size(), cudaMemcpyHostToDevice));
+    B3D_CUDA(cudaMalloc(&m.ts.joff4, sizeof(int32_t) * j4.size()));
+    B3D_CUDA(cudaMemcpy(m.ts.joff4, j4.data(), sizeof(int32_t) * j4.size(), cudaMemcpyHostToDevice));
+    B3D_CUDA(cudaMalloc(&m.ts.vert, sizeof(float) * sv.size()));
+    B3D_CUDA(cudaMemcpy(m.ts.vert, sv.data(), sizeof(float) * sv.size(), cudaMemcpyHostToDevice));
+    B3D_CUDA(cudaMalloc(&m.ts.wval, sizeof(float) * sw.size()));
+    B3D_CUDA(cudaMemcpy(m.ts.wval, sw.data(), sizeof(float) * sw.size(), cudaMemcpyHostToDevice));
+    B3D_CUDA(cudaMalloc(&m.ts.wjoff, sizeof(int32_t) * sj.size()));
+    B3D_CUDA(cudaMemcpy(m.ts.wjoff, sj.data(), sizeof(int32_t) * sj.size(), cudaMemcpyHostToDevice));
+    B3D_CUDA(cudaMalloc(&m.ts.loc, sizeof(int32_t) * loc.size()));
+    B3D_CUDA(cudaMemcpy(m.ts.loc, loc.data(), sizeof(int32_t) * loc.size(), cudaMemcpyHostToDevice));
     return B3D_OK;
 }
 
@@ -143,6 +209,7 @@ int b3d_model_create(const b3d_model_desc* d, b3d_model** out) {
     }
     int rc = upload_tables<float>(*m, vert, wval, wjoint, m->t32);
     if (!rc) rc = upload_tables<double>(*m, vert, wval, wjoint, m->t64);
+    if (!rc && m->nw == 4) rc = upload_sorted_tables(*m, vert, wval, wjoint);
     if (!rc && d->posedirs) {
         const int P = B3D_POSEDIRS_DIM;
         std::vector<float> p32((size_t)P * 3 * Vp, 0.f);
@@ -176,6 +243,8 @@ void b3d_model_destroy(b3d_model* m) {
     if (!m) return;
     cudaFree(m->t32.vert); cudaFree(m->t32.wval); cudaFree(m->t32.wjoint);
     cudaFree(m->t64.vert); cudaFree(m->t64.wval); cudaFree(m->t64.wjoint);
+    cudaFree(m->ts.vert); cudaFree(m->ts.wval); cudaFree(m->ts.wjoff); cudaFree(m->ts.loc);
+    cudaFree(m->ts.rec); cudaFree(m->ts.joff4);
     cudaFree(m->posedirs32); cudaFree(m->posedirs64); cudaFree(m->d_sk);
     delete m;
 }
