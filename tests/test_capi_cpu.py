@@ -66,3 +66,24 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".hpp", ".cpp", ".h")):
                 txt = open(os.path.join(dirpath, f)).read()
                 assert "oracle_api" not in txt and "liboracle" not in txt and '#include "../../oracle' not in txt, f
+
+
+def test_reference_signature_shim_builds_and_fails_loudly_without_gpu(tmp_path):
+    """include/b3d_shim.hpp (the reference's C++ signatures on the C-ABI) compiles with the host compiler and links against the
+    library; without a CUDA device the calls raise (B3D_ECUDA) instead of falling back to anything."""
+    import shutil
+    import subprocess
+    import torch
+    cxx = shutil.which("g++")
+    if cxx is None:
+        pytest.skip("no g++")
+    libdir = os.path.join(ROOT, "3dbodyanimation_b200")
+    exe = str(tmp_path / "shim_test")
+    res = subprocess.run([cxx, "-std=c++14", "-Wall", "-I" + os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "shim_compile.cpp"), "-o", exe,
+                          "-L" + libdir, "-l:lib3dba_b200.so", "-Wl,-rpath," + libdir], capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+    run = subprocess.run([exe], capture_output=True, text=True)
+    if torch.cuda.is_available():
+        assert run.returncode == 0, run.stdout + run.stderr
+    else:
+        assert run.returncode == 3 and "no CPU fallback" in run.stdout, run.stdout + run.stderr
