@@ -35,7 +35,7 @@ constexpr double kFunctionTolerance = 1e-6, kGradientTolerance = 1e-10, kParamet
 constexpr int kMaxConsecutiveInvalidSteps = 5;
 
 // Optional phase timing (debug hook, off unless b3d_debug_phase_timing(1) was called): cycles of block 0 per phase.
-__device__ long long g_phase_cycles[16];
+__device__ long long g_phase_cycles[32];
 __device__ long long g_block_cycles[1024];   // total cycles and line-search evaluations per block (debug)
 __device__ int g_block_ls[1024];
 __device__ int g_phase_on;
@@ -85,38 +85,58 @@ template <int T, bool JAC>
 __device__ double gmm_eval(const FitConst* __restrict__ C, const double* xj /*69*/, SingleSmem& S) {
     const int tid = threadIdx.x, nc = C->gmm_ncomp;
     GmmTmp& G = S.u.gm;
+    PhaseTimer pg;
+    pg.start();
     for (int t = tid; t < nc * NPRI; t += T) G.d[t / NPRI][t % NPRI] = xj[t % NPRI] - C->gmm_mean[t];
     __syncthreads();
-    // h_i[k] = sum_{m >= k} L_i[m][k] d_i[m].  A task takes columns k and 68 - k of one component, so every task has the same
-    // length (70 terms) and consecutive threads read consecutive addresses of L.
-    constexpr int HALF = (NPRI + 1) / 2;   // 35
-    for (int t = tid; t < nc * HALF; t += T) {
-        const int i = t / HALF, k0 = t % HALF, k1 = NPRI - 1 - k0;
-        const double* __restrict__ L = C->gmm_L + (size_t)i * NPRI * NPRI;
+    pg.mark(16);
+    // h_i[k] = sum_{m >= k} L_i[m][k] d_i[m].  A task takes the adjacent column pairs (2q, 2q+1) and (66-2q, 67-2q) of one
+    // component: 72 sixteen-byte loads (rows are padded to 70 doubles, the entries above the diagonal are stored zeros), the
+    // same for every q, so the 8 x 17 tasks finish together in one round; eight loads in flight per pass.
+    constexpr int QT = 17, LD = NPRI + 1;
+    for (int t = tid; t < nc * QT; t += T) {
+        const int i = t / QT, q = t % QT;
+        const int ca = 2 * q, cb = 66 - 2 * q;                  // first column of each pair; rows below cb touch pair A only
+        const double* __restrict__ L = C->gmm_L70 + (size_t)i * NPRI * LD;
         const double* dd = G.d[i];
-        // the two columns are walked together, eight independent loads in flight per pass
-        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0, b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;
-        const double* __restrict__ La = L + k0;
-        const double* __restrict__ Lb = L + k1;
-        int m = k0;
-        for (; m + 8 <= k1; m += 8) {     // rows k0 .. k1-1 touch column k0 only
-            const double v0 = __ldg(La + m * NPRI), v1 = __ldg(La + (m + 1) * NPRI), v2 = __ldg(La + (m + 2) * NPRI), v3 = __ldg(La + (m + 3) * NPRI);
-            const double v4 = __ldg(La + (m + 4) * NPRI), v5 = __ldg(La + (m + 5) * NPRI), v6 = __ldg(La + (m + 6) * NPRI), v7 = __ldg(La + (m + 7) * NPRI);
-            a0 += v0 * dd[m]; a1 += v1 * dd[m + 1]; a2 += v2 * dd[m + 2]; a3 += v3 * dd[m + 3];
-            a0 += v4 * dd[m + 4]; a1 += v5 * dd[m + 5]; a2 += v6 * dd[m + 6]; a3 += v7 * dd[m + 7];
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0, b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;   // (col ca | ca+1) x 2, (cb | cb+1) x 2
+        const double2* __restrict__ La = reinterpret_cast<const double2*>(L + ca);
+        const double2* __restrict__ Lb = reinterpret_cast<const double2*>(L + cb);
+        constexpr int RS = LD / 2;                               // row stride in double2
+        int m = ca;
+        for (; m + 8 <= cb; m += 8) {
+            double2 v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = __ldg(La + (m + u) * RS);
+#pragma unroll
+            for (int u = 0; u < 8; u += 2) {
+                a0 += v[u].x * dd[m + u]; a1 += v[u].y * dd[m + u];
+                a2 += v[u + 1].x * dd[m + u + 1]; a3 += v[u + 1].y * dd[m + u + 1];
+            }
         }
-        for (; m < k1; ++m) a0 += __ldg(La + m * NPRI) * dd[m];
-        for (m = k1; m + 4 <= NPRI; m += 4) {   // rows k1 .. 68 touch both columns
-            const double v0 = __ldg(La + m * NPRI), v1 = __ldg(La + (m + 1) * NPRI), v2 = __ldg(La + (m + 2) * NPRI), v3 = __ldg(La + (m + 3) * NPRI);
-            const double u0 = __ldg(Lb + m * NPRI), u1 = __ldg(Lb + (m + 1) * NPRI), u2 = __ldg(Lb + (m + 2) * NPRI), u3 = __ldg(Lb + (m + 3) * NPRI);
-            a0 += v0 * dd[m]; a1 += v1 * dd[m + 1]; a2 += v2 * dd[m + 2]; a3 += v3 * dd[m + 3];
-            b0 += u0 * dd[m]; b1 += u1 * dd[m + 1]; b2 += u2 * dd[m + 2]; b3 += u3 * dd[m + 3];
+        for (; m < cb; ++m) { const double2 v = __ldg(La + m * RS); a0 += v.x * dd[m]; a1 += v.y * dd[m]; }
+        for (m = cb; m + 4 <= NPRI; m += 4) {
+            double2 v[4], u4[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { v[u] = __ldg(La + (m + u) * RS); u4[u] = __ldg(Lb + (m + u) * RS); }
+#pragma unroll
+            for (int u = 0; u < 4; u += 2) {
+                a0 += v[u].x * dd[m + u]; a1 += v[u].y * dd[m + u];
+                a2 += v[u + 1].x * dd[m + u + 1]; a3 += v[u + 1].y * dd[m + u + 1];
+                b0 += u4[u].x * dd[m + u]; b1 += u4[u].y * dd[m + u];
+                b2 += u4[u + 1].x * dd[m + u + 1]; b3 += u4[u + 1].y * dd[m + u + 1];
+            }
         }
-        for (; m < NPRI; ++m) { a0 += __ldg(La + m * NPRI) * dd[m]; b0 += __ldg(Lb + m * NPRI) * dd[m]; }
-        G.h[i][k0] = (a0 + a1) + (a2 + a3);
-        if (k1 != k0) G.h[i][k1] = (b0 + b1) + (b2 + b3);
+        for (; m < NPRI; ++m) {
+            const double2 v = __ldg(La + m * RS), u2 = __ldg(Lb + m * RS);
+            a0 += v.x * dd[m]; a1 += v.y * dd[m]; b0 += u2.x * dd[m]; b1 += u2.y * dd[m];
+        }
+        G.h[i][ca] = a0 + a2; G.h[i][ca + 1] = a1 + a3;
+        G.h[i][cb] = b0 + b2; G.h[i][cb + 1] = b1 + b3;
+        if (q == 0) G.h[i][NPRI - 1] = __ldg(L + (size_t)(NPRI - 1) * LD + (NPRI - 1)) * dd[NPRI - 1];   // column 68: one entry
     }
     __syncthreads();
+    pg.mark(17);
     if (tid < nc) {
         const double rh = sqrt(0.5);
         double sq = 0.0;
@@ -129,6 +149,7 @@ __device__ double gmm_eval(const FitConst* __restrict__ C, const double* xj /*69
     double best = DBL_MAX;
     for (int i = 0; i < nc; ++i) { const double p = G.p[i]; if (p < best) { best = p; c = i; } }   // strict '<': first wins ties
     if (tid == 0) S.comp = c;
+    pg.mark(18);
     // residual = beta [h_c ; sqrt(-consts_log_c)]  =>  cost = 0.5 beta^2 (|h_c|^2 - consts_log_c)
     const double cost = 0.5 * C->beta_pose * C->beta_pose * (G.sq[c] + (-C->gmm_consts[c]));
     if (JAC) {
@@ -147,15 +168,20 @@ __device__ double gmm_eval(const FitConst* __restrict__ C, const double* xj /*69
         for (int m = tid; m < NPRI; m += T) S.gpri[m] = f * ((G.part[0][m] + G.part[1][m]) + G.part[2][m]);
     }
     __syncthreads();
+    pg.mark(19);
     return cost;
 }
 
 // ---- cost (and with JAC the normal equations) at parameters xf --------------------------------------------------
 // JAC: on return S.Hs holds the packed J^T J in the free layout — scaled by S.scale unless `first`, in which case it is
 // unscaled and the caller derives the Jacobi scaling from its diagonal — and S.g the unscaled gradient J^T r.
-template <int T, bool JAC>
+// MODE 0: cost only.  MODE 1: cost + normal equations (S.Hs, S.g).  MODE 2: cost + gradient only, into S.gc — what the
+// Armijo line search needs at its trial points; S.Hs / S.g / S.gs of the current iterate stay untouched.  The gradient entries
+// are accumulated in the same order as in MODE 1, so both give the same bits.
+template <int T, int MODE>
 __device__ __noinline__ double evaluate(const FitConst* __restrict__ C, const double* xf, const b3d_kp* __restrict__ kps, int nkp, SingleSmem& S,
                            bool first) {
+    constexpr bool JAC = MODE != 0;
     const int tid = threadIdx.x, n = C->n;
     PhaseTimer pe;
     pe.start();
@@ -188,6 +214,26 @@ __device__ __noinline__ double evaluate(const FitConst* __restrict__ C, const do
             S.fcol[k][sl] = (int8_t)C->col_of[col];
             atomicOr(&S.kmask[col], 1u << k);
         }
+    }
+    if (MODE == 2) {
+        __syncthreads();
+        const double bp2g = C->beta_pose * C->beta_pose, bs2g = C->beta_shape * C->beta_shape;
+        for (int i = tid; i < n; i += T) {
+            const int a = C->free_idx[i];
+            uint32_t m = S.kmask[a];
+            double gacc = 0.0;
+            while (m) {
+                const int k = __ffs(m) - 1;
+                m &= m - 1;
+                const int sa = S.slot[k][a];
+                gacc += S.out.J[k][0][sa] * S.out.res[k][0] + S.out.J[k][1][sa] * S.out.res[k][1];
+            }
+            if (pose_prior && a >= IDX_JAA && a < IDX_W) gacc += gmm ? S.gpri[a - IDX_JAA] : bp2g * xf[a];
+            if (C->has_w && a >= IDX_W) gacc += bs2g * xf[a];
+            S.gc[i] = gacc;
+        }
+        __syncthreads();
+        return cost;
     }
     for (int e = tid; e < n * (n + 1) / 2; e += T) S.Hs[e] = 0.0;
     __syncthreads();
@@ -350,7 +396,7 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
 
     // evaluate at x with Jacobian and apply the Jacobi scaling.  Returns false on non-finite cost.
     auto eval_grad_jac = [&](bool first) -> bool {
-        x_cost = evaluate<T, true>(C, S.xfull, kps, nkp, S, first);
+        x_cost = evaluate<T, 1>(C, S.xfull, kps, nkp, S, first);
         if (!isfinite(x_cost)) return false;
         it.cost = x_cost;
         if (first) {
@@ -476,30 +522,26 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
             // ---- DoLineSearch (the problem is bounded: projected Armijo along delta) ----
             make_candidate(1.0);
             pt.mark(5);
-            cand_cost = evaluate<T, false>(C, S.cfull, kps, nkp, S, false);
+            cand_cost = evaluate<T, 0>(C, S.cfull, kps, nkp, S, false);
             pt.mark(6);
-            bool hs_dirty = false;
             {
                 double v = 0.0;
                 for (int k = tid; k < n; k += T) v += S.g[k] * S.delta[k];
                 const double gd = block_sum<T>(v, S.red);
                 const bool valid1 = isfinite(cand_cost);
                 if (!valid1 || cand_cost > x_cost + kSufficientDecrease * gd * 1.0) {
-                    // rare path: interpolate.  Needs the directional derivative at every trial point; the trial evaluations
-                    // overwrite S.Hs / S.g, which are restored below if the step ends up rejected.
-                    hs_dirty = true;
+                    // rare path: interpolate.  Needs the directional derivative at every trial point: gradient-only evaluations
+                    // (MODE 2) that leave the normal equations of x in place.
                     ++n_ls_evals;
                     double dmax = 0.0;
                     for (int k = 0; k < n; ++k) dmax = fmax(dmax, fabs(S.delta[k]));
-                    for (int k = tid; k < n; k += T) S.gc[k] = S.g[k];
-                    __syncthreads();
                     LsSample init{0.0, x_cost, gd, true}, prev{0, 0, 0, false}, cur{1.0, 0, 0, false};
                     auto ls_eval = [&](double a, LsSample& s) {
                         s.x = a; s.valid = false;
                         make_candidate(a);
-                        const double c = evaluate<T, true>(C, S.cfull, kps, nkp, S, false);
+                        const double c = evaluate<T, 2>(C, S.cfull, kps, nkp, S, false);
                         double vv = 0.0;
-                        for (int k = tid; k < n; k += T) vv += S.delta[k] * S.g[k];
+                        for (int k = tid; k < n; k += T) vv += S.delta[k] * S.gc[k];
                         const double gg = block_sum<T>(vv, S.red);
                         if (!isfinite(c) || !isfinite(gg)) return;
                         s.value = c; s.gradient = gg; s.valid = true;
@@ -510,14 +552,14 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
                     while (!cur.valid || cur.value > x_cost + kSufficientDecrease * gd * cur.x) {
                         if (++ls_iters >= kMaxLineSearchIters) { success = false; break; }
                         const double lo = kLsContractLo * cur.x, hi = kLsContractHi * cur.x;
-                        if (tid == 0) {
+                        if (tid < 32) {   // one warp: the quartic's roots are found with a lane per root
                             double ss;
                             if (!cur.valid) ss = fmin(fmax(cur.x * 0.5, lo), hi);
                             else {
                                 LsSample smp[3] = {init, cur, prev};
                                 ss = minimize_interpolating_polynomial(smp, prev.valid ? 3 : 2, lo, hi);
                             }
-                            S.ls_step = ss;
+                            if (tid == 0) S.ls_step = ss;
                         }
                         __syncthreads();
                         const double step_size = S.ls_step;
@@ -533,7 +575,7 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
                     __syncthreads();
                     // ---- ComputeCandidatePointAndEvaluateCost ----
                     make_candidate(1.0);
-                    cand_cost = evaluate<T, false>(C, S.cfull, kps, nkp, S, false);
+                    cand_cost = evaluate<T, 0>(C, S.cfull, kps, nkp, S, false);
                 }
             }
             if (!isfinite(cand_cost)) cand_cost = DBL_MAX;
@@ -568,15 +610,6 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
             } else {
                 radius = radius / decrease_factor; decrease_factor *= 2.0;
                 it.cost = cand_cost;
-                if (hs_dirty) {   // restore the normal equations of x that the line-search evaluations overwrote
-                    __syncthreads();
-                    const int comp_keep = S.comp;
-                    (void)evaluate<T, true>(C, S.xfull, kps, nkp, S, false);
-                    for (int k = tid; k < n; k += T) S.gs[k] = S.g[k] * S.scale[k];
-                    __syncthreads();
-                    if (tid == 0) S.comp = comp_keep;
-                    __syncthreads();
-                }
             }
         }
     }
@@ -638,7 +671,7 @@ int build_fit_const(const b3d_model* m, const b3d_gmm* gmm, const b3d_fit_opts* 
     if (fc->use_gmm) {
         if (gmm->nComps > GMM_MAXC) return set_error(B3D_EINVAL, "GMM with %d components (max %d)", gmm->nComps, GMM_MAXC);
         fc->gmm_ncomp = gmm->nComps;
-        fc->gmm_mean = gmm->d_mean; fc->gmm_L = gmm->d_prec_cho; fc->gmm_LT = gmm->d_prec_choT; fc->gmm_P = gmm->d_prec; fc->gmm_consts = gmm->d_consts;
+        fc->gmm_mean = gmm->d_mean; fc->gmm_L = gmm->d_prec_cho; fc->gmm_L70 = gmm->d_prec_cho70; fc->gmm_LT = gmm->d_prec_choT; fc->gmm_P = gmm->d_prec; fc->gmm_consts = gmm->d_consts;
     }
     return B3D_OK;
 }
@@ -651,7 +684,7 @@ extern "C" {
 
 // debug hooks (not part of include/b3d.h): per-phase cycle counters of block 0
 int b3d_debug_phase_timing(int on) {
-    long long z[16] = {0};
+    long long z[32] = {0};
     cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z));
     return cudaMemcpyToSymbol(g_phase_on, &on, sizeof(int)) == cudaSuccess ? 0 : 2;
 }
@@ -659,7 +692,7 @@ int b3d_debug_block_read(long long* cyc1024, int* ls1024) {
     cudaMemcpyFromSymbol(ls1024, g_block_ls, 1024 * sizeof(int));
     return cudaMemcpyFromSymbol(cyc1024, g_block_cycles, 1024 * sizeof(long long)) == cudaSuccess ? 0 : 2;
 }
-int b3d_debug_phase_read(long long* out16) { return cudaMemcpyFromSymbol(out16, g_phase_cycles, 16 * sizeof(long long)) == cudaSuccess ? 0 : 2; }
+int b3d_debug_phase_read(long long* out32) { return cudaMemcpyFromSymbol(out32, g_phase_cycles, 32 * sizeof(long long)) == cudaSuccess ? 0 : 2; }
 
 int b3d_fit_single_dev(const b3d_model* m, const b3d_gmm* gmm, const b3d_fit_opts* opts, int32_t B, const b3d_kp* kps,
                        const int32_t* nkp, const double* R0, double* sim3, double* w, double* jointAA, uint8_t* usable,

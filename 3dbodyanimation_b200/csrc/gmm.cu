@@ -130,11 +130,19 @@ int b3d_gmm_create(int32_t nc, int32_t nd, const double* weights, const double* 
     for (int i = 0; i < nc; ++i) g->consts_log[i] += std::log(min_det);
     cudaError_t e = cudaMalloc(&g->d_mean, sizeof(double) * nc * nd);
     if (e == cudaSuccess) e = cudaMalloc(&g->d_prec_cho, sizeof(double) * nc * nn);
+    if (e == cudaSuccess) e = cudaMalloc(&g->d_prec_cho70, sizeof(double) * nc * nd * (nd + 1));
     if (e == cudaSuccess) e = cudaMalloc(&g->d_prec_choT, sizeof(double) * nc * nn);
     if (e == cudaSuccess) e = cudaMalloc(&g->d_prec, sizeof(double) * nc * nn);
     if (e == cudaSuccess) e = cudaMalloc(&g->d_consts, sizeof(double) * nc);
     if (e == cudaSuccess) e = cudaMemcpy(g->d_mean, g->mean.data(), sizeof(double) * nc * nd, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(g->d_prec_cho, g->prec_cho.data(), sizeof(double) * nc * nn, cudaMemcpyHostToDevice);
+    {
+        std::vector<double> pad((size_t)nc * nd * (nd + 1), 0.0);
+        for (int i = 0; i < nc; ++i)
+            for (int a = 0; a < nd; ++a)
+                for (int b = 0; b < nd; ++b) pad[((size_t)i * nd + a) * (nd + 1) + b] = g->prec_cho[(size_t)i * nn + (size_t)a * nd + b];
+        if (e == cudaSuccess) e = cudaMemcpy(g->d_prec_cho70, pad.data(), sizeof(double) * pad.size(), cudaMemcpyHostToDevice);
+    }
     if (e == cudaSuccess) e = cudaMemcpy(g->d_prec_choT, precT.data(), sizeof(double) * nc * nn, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(g->d_prec, prec.data(), sizeof(double) * nc * nn, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(g->d_consts, g->consts_log.data(), sizeof(double) * nc, cudaMemcpyHostToDevice);
@@ -162,7 +170,7 @@ int b3d_gmm_load(const char* path, b3d_gmm** out) {
 
 void b3d_gmm_destroy(b3d_gmm* g) {
     if (!g) return;
-    cudaFree(g->d_mean); cudaFree(g->d_prec_cho); cudaFree(g->d_prec_choT); cudaFree(g->d_prec); cudaFree(g->d_consts);
+    cudaFree(g->d_mean); cudaFree(g->d_prec_cho); cudaFree(g->d_prec_cho70); cudaFree(g->d_prec_choT); cudaFree(g->d_prec); cudaFree(g->d_consts);
     delete g;
 }
 

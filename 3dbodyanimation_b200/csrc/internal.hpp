@@ -107,6 +107,7 @@ struct b3d_gmm {
     // device arrays
     double* d_mean = nullptr;        // nComps x 69
     double* d_prec_cho = nullptr;    // nComps x 69 x 69 lower, row-major (L[m][k])
+    double* d_prec_cho70 = nullptr;  // nComps x 69 x 70: L with rows padded to 70 doubles (16-byte aligned column pairs)
     double* d_prec_choT = nullptr;   // nComps x 69 x 69, L^T row-major (coalesced column access)
     double* d_prec = nullptr;        // nComps x 69 x 69  P = L L^T (symmetric)
     double* d_consts = nullptr;      // nComps  consts_log

@@ -33,6 +33,7 @@ struct FitConst {
     int32_t gmm_ncomp, pad;
     const double* gmm_mean;                // ncomp x 69
     const double* gmm_L;                   // ncomp x 69 x 69, lower, row-major  (prec_cho)
+    const double* gmm_L70;                 // the same with rows padded to 70 doubles
     const double* gmm_LT;                  // ncomp x 69 x 69, = L^T row-major
     const double* gmm_P;                   // ncomp x 69 x 69, = L L^T
     const double* gmm_consts;              // ncomp

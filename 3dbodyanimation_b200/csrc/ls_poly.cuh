@@ -1,6 +1,6 @@
 // Armijo line-search helpers of Ceres 1.14 (ArmijoLineSearch + polynomial.cc MinimizeInterpolatingPolynomial), restated
 // for the device.  Only the rare path of the bounded single-frame problems uses them (the step size 1 normally already
-// satisfies the sufficient-decrease test), and then a single thread runs them.
+// satisfies the sufficient-decrease test), and then one warp runs them.
 #pragma once
 #include <cfloat>
 
@@ -10,7 +10,7 @@ constexpr double kSufficientDecrease = 1e-4, kMinLineSearchStepSize = 1e-9;
 constexpr int kMaxLineSearchIters = 20;
 constexpr double kLsContractLo = 1e-3, kLsContractHi = 0.6;   // max_/min_line_search_step_contraction (Solver::Options defaults)
 
-// ---- polynomial helpers for the (rare) Armijo interpolation: thread 0 only --------------------------------------
+// ---- polynomial helpers for the (rare) Armijo interpolation: warp 0, all lanes --------------------------------------
 struct LsSample { double x, value, gradient; bool valid; };
 
 __device__ double poly_eval(const double* p, int nc, double x) { double v = 0; for (int i = 0; i < nc; ++i) v = v * x + p[i]; return v; }
@@ -37,7 +37,9 @@ __device__ bool lu_solve(double* A, int n, double* b, double* x) {
     return true;
 }
 
-// real parts of the roots of a polynomial of degree <= 4 (coefficients highest first): Aberth-Ehrlich iteration
+// real parts of the roots of a polynomial of degree <= 4 (coefficients highest first).  Called by ALL lanes of one warp:
+// degrees 1 and 2 in closed form; degrees 3 and 4 by the Aberth-Ehrlich simultaneous iteration with one lane per root (the
+// other lanes idle along), which is what made the single-thread version the longest serial stretch of a line search.
 __device__ int poly_root_real_parts(const double* pin, int nc, double* out) {
     int lead = 0;
     while (lead + 1 < nc && pin[lead] == 0.0) ++lead;
@@ -54,47 +56,63 @@ __device__ int poly_root_real_parts(const double* pin, int nc, double* out) {
         } else { out[0] = out[1] = -b / (2.0 * a); }
         return 2;
     }
-    double ar[6], zr[5], zi[5];
-    for (int i = 0; i <= deg; ++i) ar[i] = p[i] / p[0];
+    const int lane = threadIdx.x & 31;
+    double ar[6];
+    const double ilead = 1.0 / p[0];
+    for (int i = 0; i <= deg; ++i) ar[i] = p[i] * ilead;
     double rad = 0;
     for (int i = 1; i <= deg; ++i) rad = fmax(rad, fabs(ar[i]));
     rad = 1.0 + rad;
-    for (int i = 0; i < deg; ++i) { double s, c; sincos(2 * 3.14159265358979323846 * i / deg + 0.4, &s, &c); zr[i] = rad * 0.5 * c; zi[i] = rad * 0.5 * s; }
-    for (int it = 0; it < 64; ++it) {
-        double change = 0;
-        for (int i = 0; i < deg; ++i) {
-            double fr = ar[0], fi = 0, dr = 0, di = 0;
-            for (int k = 1; k <= deg; ++k) {
-                double t = dr * zr[i] - di * zi[i] + fr; di = dr * zi[i] + di * zr[i] + fi; dr = t;
-                t = fr * zr[i] - fi * zi[i] + ar[k]; fi = fr * zi[i] + fi * zr[i]; fr = t;
-            }
-            if (fr == 0.0 && fi == 0.0) continue;
-            const double dd = dr * dr + di * di;
-            const double rr = (fr * dr + fi * di) / dd, ri = (fi * dr - fr * di) / dd;   // ratio = f / df
-            double sr = 0, si = 0;
-            for (int j = 0; j < deg; ++j) if (j != i) { const double ur = zr[i] - zr[j], ui = zi[i] - zi[j], uu = ur * ur + ui * ui; sr += ur / uu; si -= ui / uu; }
-            const double er = 1.0 - (rr * sr - ri * si), ei = -(rr * si + ri * sr);
-            const double ee = er * er + ei * ei;
-            const double zr_d = (rr * er + ri * ei) / ee, zi_d = (ri * er - rr * ei) / ee;
-            zr[i] -= zr_d; zi[i] -= zi_d;
-            change = fmax(change, sqrt(zr_d * zr_d + zi_d * zi_d));
-        }
-        if (change < 1e-14 * rad) break;
+    double zr, zi;
+    {
+        double sn, cs;
+        sincos(2 * 3.14159265358979323846 * (lane % deg) / deg + 0.4, &sn, &cs);
+        zr = rad * 0.5 * cs; zi = rad * 0.5 * sn;
     }
-    for (int i = 0; i < deg; ++i) out[i] = zr[i];
+    for (int it = 0; it < 64; ++it) {
+        double fr = ar[0], fi = 0, dr = 0, di = 0;
+        for (int k = 1; k <= deg; ++k) {
+            double t = dr * zr - di * zi + fr; di = dr * zi + di * zr + fi; dr = t;
+            t = fr * zr - fi * zi + ar[k]; fi = fr * zi + fi * zr; fr = t;
+        }
+        double ozr[4], ozi[4];                      // every root, gathered outside any divergent code
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { ozr[j] = __shfl_sync(0xffffffffu, zr, j); ozi[j] = __shfl_sync(0xffffffffu, zi, j); }
+        double wr = 0.0, wi = 0.0;
+        if (!(fr == 0.0 && fi == 0.0)) {
+            const double idd = 1.0 / (dr * dr + di * di);
+            const double rr = (fr * dr + fi * di) * idd, ri = (fi * dr - fr * di) * idd;   // ratio = f / f'
+            double sr = 0, si = 0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                if (j < deg && j != lane) { const double ur = zr - ozr[j], ui = zi - ozi[j], iu = 1.0 / (ur * ur + ui * ui); sr += ur * iu; si -= ui * iu; }
+            const double er = 1.0 - (rr * sr - ri * si), ei = -(rr * si + ri * sr);
+            const double iee = 1.0 / (er * er + ei * ei);
+            wr = (rr * er + ri * ei) * iee; wi = (ri * er - rr * ei) * iee;
+        }
+        zr -= wr; zi -= wi;
+        double change = lane < deg ? sqrt(wr * wr + wi * wi) : 0.0;
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) change = fmax(change, __shfl_xor_sync(0xffffffffu, change, o));
+        change = __shfl_sync(0xffffffffu, change, 0);
+        if (change < 1e-14 * rad) break;   // warp-uniform
+    }
+    for (int i = 0; i < deg; ++i) out[i] = __shfl_sync(0xffffffffu, zr, i);
     return deg;
 }
 
-// ceres MinimizeInterpolatingPolynomial: every sample carries value and gradient
+__device__ __forceinline__ double ipow(double x, int k) { double v = 1.0; for (int i = 0; i < k; ++i) v *= x; return v; }
+
+// ceres MinimizeInterpolatingPolynomial: every sample carries value and gradient.  Called by all lanes of one warp (uniform).
 __device__ double minimize_interpolating_polynomial(const LsSample* s, int ns, double x_min, double x_max) {
     const int nc = 2 * ns, degree = nc - 1;
     double lhs[36], rhs[6], coef[6];
     for (int i = 0; i < nc * nc; ++i) lhs[i] = 0.0;
     int row = 0;
     for (int q = 0; q < ns; ++q) {
-        for (int j = 0; j <= degree; ++j) lhs[row * nc + j] = pow(s[q].x, (double)(degree - j));
+        for (int j = 0; j <= degree; ++j) lhs[row * nc + j] = ipow(s[q].x, degree - j);
         rhs[row++] = s[q].value;
-        for (int j = 0; j < degree; ++j) lhs[row * nc + j] = (degree - j) * pow(s[q].x, (double)(degree - j - 1));
+        for (int j = 0; j < degree; ++j) lhs[row * nc + j] = (degree - j) * ipow(s[q].x, degree - j - 1);
         rhs[row++] = s[q].gradient;
     }
     double best_x = (x_min + x_max) / 2.0;
