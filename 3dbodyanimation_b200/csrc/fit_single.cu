@@ -90,50 +90,52 @@ __device__ double gmm_eval(const FitConst* __restrict__ C, const double* xj /*69
     for (int t = tid; t < nc * NPRI; t += T) G.d[t / NPRI][t % NPRI] = xj[t % NPRI] - C->gmm_mean[t];
     __syncthreads();
     pg.mark(16);
-    // h_i[k] = sum_{m >= k} L_i[m][k] d_i[m].  A task takes the adjacent column pairs (2q, 2q+1) and (66-2q, 67-2q) of one
-    // component: 72 sixteen-byte loads (rows are padded to 70 doubles, the entries above the diagonal are stored zeros), the
-    // same for every q, so the 8 x 17 tasks finish together in one round; eight loads in flight per pass.
-    constexpr int QT = 17, LD = NPRI + 1;
-    for (int t = tid; t < nc * QT; t += T) {
-        const int i = t / QT, q = t % QT;
-        const int ca = 2 * q, cb = 66 - 2 * q;                  // first column of each pair; rows below cb touch pair A only
-        const double* __restrict__ L = C->gmm_L70 + (size_t)i * NPRI * LD;
-        const double* dd = G.d[i];
-        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0, b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;   // (col ca | ca+1) x 2, (cb | cb+1) x 2
-        const double2* __restrict__ La = reinterpret_cast<const double2*>(L + ca);
-        const double2* __restrict__ Lb = reinterpret_cast<const double2*>(L + cb);
-        constexpr int RS = LD / 2;                               // row stride in double2
-        int m = ca;
-        for (; m + 8 <= cb; m += 8) {
-            double2 v[8];
+    // h_i[k] = sum_{m >= k} L_i[m][k] d_i[m].  Warp i takes component i; lane q < 17 owns the adjacent column pairs (2q, 2q+1) and
+    // (66-2q, 67-2q): 72 sixteen-byte loads whatever q (rows are padded to 70 doubles; entries above the diagonal are stored
+    // zeros).  All lanes walk the SAME row in the same instruction, so a warp load touches 3 lines instead of one line per lane
+    // (ncu: the per-lane row order made every load a 17-line gather); rows above a lane's columns are predicated off.
+    constexpr int QT = 17, LD = NPRI + 1, RS = LD / 2;           // row stride in double2
+    static_assert(T / 32 >= 8, "one warp per GMM component");
+    for (int i = tid >> 5; i < nc; i += T / 32) {
+        const int q = tid & 31;
+        if (q < QT) {
+            const int ca = 2 * q, cb = 66 - 2 * q;
+            const double* __restrict__ L = C->gmm_L70 + (size_t)i * NPRI * LD;
+            const double* dd = G.d[i];
+            const double2* __restrict__ La = reinterpret_cast<const double2*>(L + ca);
+            const double2* __restrict__ Lb = reinterpret_cast<const double2*>(L + cb);
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0, b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;
+            const double2 zero2 = make_double2(0.0, 0.0);
+            // rows 0 .. 31 can only touch pair A (cb >= 34); rows 32 .. 68 may touch both
+            for (int m = 0; m < 32; m += 8) {
+                double2 v[8];
 #pragma unroll
-            for (int u = 0; u < 8; ++u) v[u] = __ldg(La + (m + u) * RS);
+                for (int u = 0; u < 8; ++u) v[u] = (m + u >= ca) ? __ldg(La + (m + u) * RS) : zero2;
 #pragma unroll
-            for (int u = 0; u < 8; u += 2) {
-                a0 += v[u].x * dd[m + u]; a1 += v[u].y * dd[m + u];
-                a2 += v[u + 1].x * dd[m + u + 1]; a3 += v[u + 1].y * dd[m + u + 1];
+                for (int u = 0; u < 8; u += 2) {
+                    a0 += v[u].x * dd[m + u]; a1 += v[u].y * dd[m + u];
+                    a2 += v[u + 1].x * dd[m + u + 1]; a3 += v[u + 1].y * dd[m + u + 1];
+                }
             }
-        }
-        for (; m < cb; ++m) { const double2 v = __ldg(La + m * RS); a0 += v.x * dd[m]; a1 += v.y * dd[m]; }
-        for (m = cb; m + 4 <= NPRI; m += 4) {
-            double2 v[4], u4[4];
+            for (int m = 32; m < NPRI; m += 4) {
+                double2 v[4], w4[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) { v[u] = __ldg(La + (m + u) * RS); u4[u] = __ldg(Lb + (m + u) * RS); }
+                for (int u = 0; u < 4; ++u) {
+                    const int r = m + u;
+                    v[u] = (r < NPRI && r >= ca) ? __ldg(La + r * RS) : zero2;
+                    w4[u] = (r < NPRI && r >= cb) ? __ldg(Lb + r * RS) : zero2;
+                }
 #pragma unroll
-            for (int u = 0; u < 4; u += 2) {
-                a0 += v[u].x * dd[m + u]; a1 += v[u].y * dd[m + u];
-                a2 += v[u + 1].x * dd[m + u + 1]; a3 += v[u + 1].y * dd[m + u + 1];
-                b0 += u4[u].x * dd[m + u]; b1 += u4[u].y * dd[m + u];
-                b2 += u4[u + 1].x * dd[m + u + 1]; b3 += u4[u + 1].y * dd[m + u + 1];
+                for (int u = 0; u < 4; u += 2) {
+                    const double d0 = m + u < NPRI ? dd[m + u] : 0.0, d1 = m + u + 1 < NPRI ? dd[m + u + 1] : 0.0;
+                    a0 += v[u].x * d0; a1 += v[u].y * d0; a2 += v[u + 1].x * d1; a3 += v[u + 1].y * d1;
+                    b0 += w4[u].x * d0; b1 += w4[u].y * d0; b2 += w4[u + 1].x * d1; b3 += w4[u + 1].y * d1;
+                }
             }
+            G.h[i][ca] = a0 + a2; G.h[i][ca + 1] = a1 + a3;
+            G.h[i][cb] = b0 + b2; G.h[i][cb + 1] = b1 + b3;
+            if (q == 0) G.h[i][NPRI - 1] = __ldg(L + (size_t)(NPRI - 1) * LD + (NPRI - 1)) * dd[NPRI - 1];   // column 68: one entry
         }
-        for (; m < NPRI; ++m) {
-            const double2 v = __ldg(La + m * RS), u2 = __ldg(Lb + m * RS);
-            a0 += v.x * dd[m]; a1 += v.y * dd[m]; b0 += u2.x * dd[m]; b1 += u2.y * dd[m];
-        }
-        G.h[i][ca] = a0 + a2; G.h[i][ca + 1] = a1 + a3;
-        G.h[i][cb] = b0 + b2; G.h[i][cb + 1] = b1 + b3;
-        if (q == 0) G.h[i][NPRI - 1] = __ldg(L + (size_t)(NPRI - 1) * LD + (NPRI - 1)) * dd[NPRI - 1];   // column 68: one entry
     }
     __syncthreads();
     pg.mark(17);
@@ -287,53 +289,100 @@ __device__ __noinline__ double evaluate(const FitConst* __restrict__ C, const do
     return cost;
 }
 
-// Cholesky (Crout) of the damped system in S.u.L, packed lower, (n + 1) rows: the last row is the right-hand side, so on
-// return it holds z = L^-1 rhs.  The thread pair p owns row p: the two halves split the length-j dot product of column j and
-// combine with one shuffle; the running diagonal A[p][p] - sum_k L[p][k]^2 lives in a register, and the owner of row j + 1
-// publishes the next pivot before the (single) barrier of column j.  Returns false when a pivot is not positive
-// (Eigen LLT / oracle criterion).
+// Cholesky of the damped system in S.u.L, packed lower, (n + 1) rows: the last row is the right-hand side, so on return it
+// holds z = L^-1 rhs.  Blocked left-looking, 4 columns per panel, 2 barriers per panel (44 instead of one per column):
+//   update   the thread pair of row p subtracts sum_{q < j0} L[p][q] L[c][q] from its entries of the panel's columns c — the
+//            four dot products share the loads of row p and the two halves of the pair split q;
+//   factor   every row thread factors the (updated) 4 x 4 diagonal block redundantly in registers — the same arithmetic in
+//            every thread, hence the same bits — and solves its own row against it.
+// Returns false when a pivot is not positive (Eigen LLT / oracle criterion).  1 / L_jj goes to S.invd.
 template <int T>
 __device__ bool chol_factor_aug(SingleSmem& S, int n) {
     static_assert(T >= 2 * NAUG, "one thread pair per row");
+    constexpr int PW = 4;
     double* A = S.u.L;
     const int tid = threadIdx.x, p = tid >> 1, half = tid & 1, np = n + 1;
-    double dg = p < n ? A[tri(p, p)] : 0.0;
-    if (tid == 0) {
-        const double il = rsqrt(dg);
-        S.piv[0] = dg; S.piv[1] = il; S.invd[0] = il;
-    }
     bool ok = true;
-    for (int j = 0; j < n; ++j) {
-        __syncthreads();
-        const double d = S.piv[0];
-        if (!(d > 0.0)) { ok = false; break; }                  // uniform
-        const double inv = S.piv[1];
-        const bool active = p > j && p < np;
-        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0, rij = 0.0;
+    for (int j0 = 0; j0 < n; j0 += PW) {
+        const int w = min(PW, n - j0);
+        const bool active = p >= j0 && p < np;
         double* ri = A + tri(active ? p : 0, 0);
-        if (active) {
-            const double* rj = A + tri(j, 0);
-            rij = ri[j];
-            int q = half;
-            for (; q + 6 < j; q += 8) {
-                const double a0 = ri[q], a1 = ri[q + 2], a2 = ri[q + 4], a3 = ri[q + 6];
-                const double b0 = rj[q], b1 = rj[q + 2], b2 = rj[q + 4], b3 = rj[q + 6];
-                s0 -= a0 * b0; s1 -= a1 * b1; s2 -= a2 * b2; s3 -= a3 * b3;
-            }
-            for (; q < j; q += 2) s0 -= ri[q] * rj[q];
-        }
-        double s = (s0 + s1) + (s2 + s3);
-        s += __shfl_xor_sync(0xffffffffu, s, 1);
-        if (active) {
-            const double val = (rij + s) * inv;
-            dg -= val * val;
-            if (half == 0) {
-                ri[j] = val;
-                if (p == j + 1 && p < n) {
-                    const double il = rsqrt(dg);
-                    S.piv[0] = dg; S.piv[1] = il; S.invd[p] = il;
+        // ---- update ----
+        if (j0 > 0) {
+            double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+            if (active) {
+                const double* r0 = A + tri(j0, 0);
+                const double* r1 = A + tri(min(j0 + 1, n - 1), 0);
+                const double* r2 = A + tri(min(j0 + 2, n - 1), 0);
+                const double* r3 = A + tri(min(j0 + 3, n - 1), 0);
+                int q = half;
+                for (; q + 2 < j0; q += 4) {
+                    const double a0 = ri[q], a1 = ri[q + 2];
+                    s0 -= a0 * r0[q]; s1 -= a0 * r1[q]; s2 -= a0 * r2[q]; s3 -= a0 * r3[q];
+                    s0 -= a1 * r0[q + 2]; s1 -= a1 * r1[q + 2]; s2 -= a1 * r2[q + 2]; s3 -= a1 * r3[q + 2];
+                }
+                for (; q < j0; q += 2) {
+                    const double a0 = ri[q];
+                    s0 -= a0 * r0[q]; s1 -= a0 * r1[q]; s2 -= a0 * r2[q]; s3 -= a0 * r3[q];
                 }
             }
+            s0 += __shfl_xor_sync(0xffffffffu, s0, 1);
+            s1 += __shfl_xor_sync(0xffffffffu, s1, 1);
+            s2 += __shfl_xor_sync(0xffffffffu, s2, 1);
+            s3 += __shfl_xor_sync(0xffffffffu, s3, 1);
+            if (active && half == 0) {
+                const int last = min(w - 1, p - j0);       // columns j0 .. j0 + last exist in row p
+                ri[j0] += s0;
+                if (last >= 1) ri[j0 + 1] += s1;
+                if (last >= 2) ri[j0 + 2] += s2;
+                if (last >= 3) ri[j0 + 3] += s3;
+            }
+            __syncthreads();
+        }
+        // ---- factor the diagonal block (redundantly) and solve the own row ----
+        {
+            const double d00 = A[tri(j0, j0)];
+            if (!(d00 > 0.0)) { ok = false; break; }
+            const double i0 = rsqrt(d00);
+            double l10 = 0.0, l20 = 0.0, l21 = 0.0, l30 = 0.0, l31 = 0.0, l32 = 0.0, i1 = 0.0, i2 = 0.0, i3 = 0.0;
+            if (w > 1) {
+                l10 = A[tri(j0 + 1, j0)] * i0;
+                const double d11 = A[tri(j0 + 1, j0 + 1)] - l10 * l10;
+                if (!(d11 > 0.0)) { ok = false; break; }
+                i1 = rsqrt(d11);
+            }
+            if (w > 2) {
+                l20 = A[tri(j0 + 2, j0)] * i0;
+                l21 = (A[tri(j0 + 2, j0 + 1)] - l20 * l10) * i1;
+                const double d22 = A[tri(j0 + 2, j0 + 2)] - l20 * l20 - l21 * l21;
+                if (!(d22 > 0.0)) { ok = false; break; }
+                i2 = rsqrt(d22);
+            }
+            if (w > 3) {
+                l30 = A[tri(j0 + 3, j0)] * i0;
+                l31 = (A[tri(j0 + 3, j0 + 1)] - l30 * l10) * i1;
+                l32 = (A[tri(j0 + 3, j0 + 2)] - l30 * l20 - l31 * l21) * i2;
+                const double d33 = A[tri(j0 + 3, j0 + 3)] - l30 * l30 - l31 * l31 - l32 * l32;
+                if (!(d33 > 0.0)) { ok = false; break; }
+                i3 = rsqrt(d33);
+            }
+            __syncthreads();    // every thread has read the block before its owners overwrite it
+            if (active && half == 0) {
+                const int last = min(w - 1, p - j0);
+                const double v0 = ri[j0] * i0;
+                double v1 = 0.0, v2 = 0.0, v3 = 0.0;
+                if (last >= 1) v1 = (ri[j0 + 1] - v0 * l10) * i1;
+                if (last >= 2) v2 = (ri[j0 + 2] - v0 * l20 - v1 * l21) * i2;
+                if (last >= 3) v3 = (ri[j0 + 3] - v0 * l30 - v1 * l31 - v2 * l32) * i3;
+                // a row inside the panel stops before its diagonal entry (kept unfactored; 1 / L_jj lives in S.invd)
+                const int stop = p - j0;   // first column index (relative) that is the diagonal or beyond
+                if (stop > 0) ri[j0] = v0;
+                if (last >= 1 && stop > 1) ri[j0 + 1] = v1;
+                if (last >= 2 && stop > 2) ri[j0 + 2] = v2;
+                if (last >= 3 && stop > 3) ri[j0 + 3] = v3;
+                if (p < n && stop < w) S.invd[p] = stop == 0 ? i0 : (stop == 1 ? i1 : (stop == 2 ? i2 : i3));
+            }
+            __syncthreads();
         }
     }
     __syncthreads();
