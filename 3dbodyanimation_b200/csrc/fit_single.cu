@@ -217,9 +217,11 @@ __device__ __noinline__ double evaluate(const FitConst* __restrict__ C, const do
             atomicOr(&S.kmask[col], 1u << k);
         }
     }
-    if (MODE == 2) {
-        __syncthreads();
-        const double bp2g = C->beta_pose * C->beta_pose, bs2g = C->beta_shape * C->beta_shape;
+    __syncthreads();
+    const double bp2 = C->beta_pose * C->beta_pose, bs2 = C->beta_shape * C->beta_shape;
+    // ---- gradient J^T r: thread i sums the keypoints that touch column i in keypoint order, then the priors ----
+    {
+        double* gdst = MODE == 2 ? S.gc : S.g;
         for (int i = tid; i < n; i += T) {
             const int a = C->free_idx[i];
             uint32_t m = S.kmask[a];
@@ -230,59 +232,67 @@ __device__ __noinline__ double evaluate(const FitConst* __restrict__ C, const do
                 const int sa = S.slot[k][a];
                 gacc += S.out.J[k][0][sa] * S.out.res[k][0] + S.out.J[k][1][sa] * S.out.res[k][1];
             }
-            if (pose_prior && a >= IDX_JAA && a < IDX_W) gacc += gmm ? S.gpri[a - IDX_JAA] : bp2g * xf[a];
-            if (C->has_w && a >= IDX_W) gacc += bs2g * xf[a];
-            S.gc[i] = gacc;
+            if (pose_prior && a >= IDX_JAA && a < IDX_W) gacc += gmm ? S.gpri[a - IDX_JAA] : bp2 * xf[a];
+            if (C->has_w && a >= IDX_W) gacc += bs2 * xf[a];
+            gdst[i] = gacc;
         }
+    }
+    if (MODE == 2) {
         __syncthreads();
         return cost;
     }
-    for (int e = tid; e < n * (n + 1) / 2; e += T) S.Hs[e] = 0.0;
-    __syncthreads();
-    // ---- J^T J and J^T r of the reprojection blocks: a warp owns row i of H and walks the keypoints that touch column i in
-    // keypoint order; its lanes cover that keypoint's non-zero slots.  No two warps write the same element: no barriers. ----
-    const int lane = tid & 31;
-    for (int i = tid >> 5; i < n; i += T / 32) {
-        const int a = C->free_idx[i];
-        uint32_t m = S.kmask[a];
-        double gacc = 0.0;
-        while (m) {
-            const int k = __ffs(m) - 1;
-            m &= m - 1;
-            const int sa = S.slot[k][a], nnz = S.out.jnnz[k];
-            const double a0 = S.out.J[k][0][sa], a1 = S.out.J[k][1][sa];
-            for (int sb = lane; sb < nnz; sb += 32) {
-                const int j = S.fcol[k][sb];
-                if (j >= 0 && j <= i) S.Hs[tri(i, j)] += a0 * S.out.J[k][0][sb] + a1 * S.out.J[k][1][sb];
+    // ---- J^T J: a thread owns element (i, j) of the packed lower triangle and sums, in keypoint order and in a register, the
+    // keypoints whose Jacobian touches both columns; then the prior term and the Jacobi scaling, one store per element.  Four
+    // elements per pass, so that the four loads of the GMM precision matrix (L2) are in flight while the keypoints are walked. ----
+    {
+        const double* __restrict__ P = gmm ? C->gmm_P + (size_t)S.comp * NPRI * NPRI : nullptr;
+        const int ne = n * (n + 1) / 2;
+        for (int e0 = tid; e0 < ne; e0 += 4 * T) {
+            int ei[4], ej[4];
+            double pri[4], acc[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int e = e0 + u * T;
+                int i = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
+                while ((i + 1) * (i + 2) / 2 <= e) ++i;
+                while (i * (i + 1) / 2 > e) --i;
+                ei[u] = i; ej[u] = e - i * (i + 1) / 2;
+                pri[u] = 0.0;
+                if (e < ne) {
+                    const int a = C->free_idx[i], b = C->free_idx[ej[u]];
+                    if (pose_prior && a >= IDX_JAA && a < IDX_W && b >= IDX_JAA) {
+                        if (gmm) pri[u] = bp2 * __ldg(P + (a - IDX_JAA) * NPRI + (b - IDX_JAA));
+                        else if (a == b) pri[u] = bp2;
+                    }
+                }
             }
-            gacc += a0 * S.out.res[k][0] + a1 * S.out.res[k][1];
-        }
-        if (lane == 0) S.g[i] = gacc;
-    }
-    __syncthreads();
-    // ---- priors and Jacobi scaling ----
-    const double bp2 = C->beta_pose * C->beta_pose, bs2 = C->beta_shape * C->beta_shape;
-    const double* __restrict__ P = gmm ? C->gmm_P + (size_t)S.comp * NPRI * NPRI : nullptr;
-    for (int i = tid >> 5; i < n; i += T / 32) {
-        const int a = C->free_idx[i];
-        const double si = first ? 1.0 : S.scale[i];
-        for (int j = lane; j <= i; j += 32) {
-            const int b = C->free_idx[j];
-            double acc = S.Hs[tri(i, j)];
-            if (pose_prior && a >= IDX_JAA && a < IDX_W && b >= IDX_JAA) {
-                if (gmm) acc += bp2 * __ldg(P + (a - IDX_JAA) * NPRI + (b - IDX_JAA));
-                else if (a == b) acc += bp2;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                acc[u] = 0.0;
+                if (e0 + u * T < ne) {
+                    const int a = C->free_idx[ei[u]], b = C->free_idx[ej[u]];
+                    uint32_t m = S.kmask[a] & S.kmask[b];
+                    while (m) {
+                        const int k = __ffs(m) - 1;
+                        m &= m - 1;
+                        const int sa = S.slot[k][a], sb = S.slot[k][b];
+                        acc[u] += S.out.J[k][0][sa] * S.out.J[k][0][sb] + S.out.J[k][1][sa] * S.out.J[k][1][sb];
+                    }
+                }
             }
-            if (C->has_w && a >= IDX_W && a == b) acc += bs2;
-            S.Hs[tri(i, j)] = first ? acc : acc * si * S.scale[j];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int e = e0 + u * T;
+                if (e < ne) {
+                    const int i = ei[u], j = ej[u];
+                    const int a = C->free_idx[i], b = C->free_idx[j];
+                    double v2 = acc[u];
+                    if (pose_prior && a >= IDX_JAA && a < IDX_W && b >= IDX_JAA && (gmm || a == b)) v2 += pri[u];
+                    if (C->has_w && a >= IDX_W && a == b) v2 += bs2;
+                    S.Hs[e] = first ? v2 : v2 * S.scale[i] * S.scale[j];
+                }
+            }
         }
-    }
-    for (int i = tid; i < n; i += T) {
-        const int a = C->free_idx[i];
-        double acc = S.g[i];
-        if (pose_prior && a >= IDX_JAA && a < IDX_W) acc += gmm ? S.gpri[a - IDX_JAA] : bp2 * xf[a];
-        if (C->has_w && a >= IDX_W) acc += bs2 * xf[a];
-        S.g[i] = acc;
     }
     __syncthreads();
     pe.mark(11);
