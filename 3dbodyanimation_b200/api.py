@@ -122,7 +122,10 @@ def _gmm_handle(gmm):
 # ---------------------------------------------------------------------------------------------------------
 # batched calls
 # ---------------------------------------------------------------------------------------------------------
-def smpl_forward(model: AvatarModel, w, p, r, dtype=np.float64, posedirs=False, want_cloud=True):
+LBS_FLAGS = {None: 0, "tc": 0x10, "sorted": 0x20, "bodylane": 0x40, "generic": 0x80}   # B3D_FWD_LBS_* (include/b3d.h)
+
+
+def smpl_forward(model: AvatarModel, w, p, r, dtype=np.float64, posedirs=False, want_cloud=True, lbs=None):
     """Batched Avatar::update.  w (B,10), p (B,3), r (B,24,9 col-major).  Returns cloud (B,V,3), jointPos (B,24,3),
     jointTrans (B,24,12) in ``dtype`` (float32 or float64)."""
     dt = np.dtype(dtype)
@@ -133,7 +136,8 @@ def smpl_forward(model: AvatarModel, w, p, r, dtype=np.float64, posedirs=False, 
     r = np.ascontiguousarray(r, dtype=dt).reshape(b, NJ, 9)
     cloud = np.empty((b, model.numPoints, 3), dtype=dt) if want_cloud else None
     jp, jt = np.empty((b, NJ, 3), dtype=dt), np.empty((b, NJ, 12), dtype=dt)
-    check(lib().b3d_smpl_forward(model.h, b, code, ptr(w), ptr(p), ptr(r), ptr(cloud), ptr(jp), ptr(jt), 1 if posedirs else 0),
+    check(lib().b3d_smpl_forward(model.h, b, code, ptr(w), ptr(p), ptr(r), ptr(cloud), ptr(jp), ptr(jt),
+                                 (1 if posedirs else 0) | LBS_FLAGS[lbs]),
           "b3d_smpl_forward")
     return cloud, jp, jt
 

@@ -10,12 +10,15 @@
 //                        AvatarModel.cpp:104-109), CUDA-core path.
 #include <algorithm>
 #include <cstdlib>
+#include <cstring>
+#include <string>
 
 #include "internal.hpp"
 
 namespace b3d {
 
 constexpr int JW = 4;   // warps (= bodies) per CTA in the joints kernel
+constexpr int TC_AUTO_MIN_B = 512;   // batches from which the tensor-core LBS kernel (lbs_tc.cu) is the default float32 path
 
 template <typename T>
 __global__ void __launch_bounds__(32 * JW) smpl_joints_kernel(const SkeletonConst* __restrict__ sk, int B,
@@ -498,8 +501,16 @@ static int forward_impl(const b3d_model* m, int B, const T* w, const T* p, const
         const bool g_al16 = (reinterpret_cast<uintptr_t>(G) & 15) == 0;
         // measured on B200 (profiles/r01_forward_sweep.txt): the lane = vertex sorted kernel is the faster one today; the
         // lane = body kernel is kept selectable (B3D_LBS=bodylane) as the base of the tensor-core shape-blend variant
-        static const bool want_bodylane = [] { const char* e = getenv("B3D_LBS"); return e && !strcmp(e, "bodylane"); }();
-        if (want_bodylane && sizeof(T) == 4 && m->nw == 4 && !use_pd && m->ts.rec && g_al16 && B >= 256) {
+        // B3D_FWD_LBS_* flags (or env B3D_LBS = tc | sorted | bodylane | generic) force a float32 path (tests, profiling); default: tensor-core kernel for
+        // batches that fill the machine, tile-sorted lane = vertex kernel below that
+        static const std::string want_env = [] { const char* e = getenv("B3D_LBS"); return std::string(e ? e : ""); }();
+        const std::string want = (flags & B3D_FWD_LBS_TC) ? "tc" : (flags & B3D_FWD_LBS_SORTED) ? "sorted" : (flags & B3D_FWD_LBS_BODYLANE) ? "bodylane"
+                                 : (flags & B3D_FWD_LBS_GENERIC) ? "generic" : want_env;
+        const bool want_bodylane = want == "bodylane";
+        const bool f32_fast = sizeof(T) == 4 && m->nw == 4 && !use_pd && g_al16;
+        if (f32_fast && m->tc.blob && (want == "tc" || (want.empty() && B >= TC_AUTO_MIN_B))) {
+            if (int rc = launch_lbs_tc(m, B, (const float*)w, (const float*)G, (float*)cloud, st)) return rc;
+        } else if (want != "generic" && want_bodylane && sizeof(T) == 4 && m->nw == 4 && !use_pd && m->ts.rec && g_al16 && B >= 256) {
             static bool attr_set = false;
             if (!attr_set) {
                 B3D_CUDA(cudaFuncSetAttribute(smpl_lbs_bodylane_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BlSmem)));
@@ -512,7 +523,7 @@ static int forward_impl(const b3d_model* m, int B, const T* w, const T* p, const
             bgroups = (B + bper - 1) / bper;
             smpl_lbs_bodylane_kernel<<<dim3(ranges, bgroups), BL_THREADS, sizeof(BlSmem), st>>>(m->ts.rec, m->ts.joff4, m->V, B, bper, (const float*)w,
                                                                                                  (const float*)G, (float*)cloud);
-        } else if (sizeof(T) == 4 && m->nw == 4 && !use_pd && m->ts.vert && m->V % 2 == 0 && g_al16) {
+        } else if (want != "generic" && sizeof(T) == 4 && m->nw == 4 && !use_pd && m->ts.vert && m->V % 2 == 0 && g_al16) {
             static_assert(LS_TILE == 256, "model.cu sorts the tables in 256-vertex tiles");
             smpl_lbs_sorted_kernel<<<grid, LS_TILE, 0, st>>>(m->ts.vert, m->ts.wval, m->ts.wjoff, m->ts.loc, m->V, m->Vpad, B, per,
                                                              (const float*)w, (const float*)G, (float*)cloud);

@@ -74,6 +74,20 @@ struct SortedTables {
     int32_t* joff4 = nullptr;    // [Vpad][4]  float offsets 12 * joint of the four weight slots
 };
 
+// Tables of the tensor-core LBS kernel (lbs_tc.cu): the mesh is cut into sort tiles of TC_T = 96 consecutive vertices; a sort
+// tile is three MMA tiles of 32 slots.  Per MMA tile one contiguous blob (one TMA bulk copy):
+//   [0, 12288)      B operand of the shape blend, 96 columns (slot, coordinate) x K = 32, TF32 hi/lo split, in the canonical
+//                   K-major / no-swizzle shared-memory layout tcgen05.mma reads
+//   [12288, 13312)  32 slot records of 8 words: 4 skinning weights (aligned with the lane's 4 transform registers sets),
+//                   3 * position in the sort tile, control word (reload flags + joint ids), 2 spare
+struct TcTables {
+    uint8_t* blob = nullptr;
+    int sort_tiles = 0;
+    double mean_reloads = 0.0;   // joint transforms re-read from TMEM per slot (host statistic, reported by tools)
+};
+constexpr int TC_T = 96, TC_SLOTS = 32, TC_N = 96, TC_K = 32;
+constexpr int TC_OPER_BYTES = TC_N * TC_K * 4, TC_REC_WORDS = 8, TC_BLOB_BYTES = TC_OPER_BYTES + TC_SLOTS * TC_REC_WORDS * 4;
+
 // small per-model constants passed to kernels by value
 struct SkeletonConst {
     int32_t parent[NJ];
@@ -86,6 +100,13 @@ struct SkeletonConst {
 
 }  // namespace b3d
 
+struct b3d_model;
+namespace b3d {
+// lbs_tc.cu
+int build_tc_tables(b3d_model& m, const std::vector<double>& vert, const std::vector<double>& wval, const std::vector<int32_t>& wjoint);
+int launch_lbs_tc(const b3d_model* m, int B, const float* wshape, const float* G, float* cloud, cudaStream_t st);
+}  // namespace b3d
+
 struct b3d_model {
     int device = -1;
     int V = 0, Vpad = 0, F = 0, nw = 0;        // nw = padded non-zeros per vertex (4, 8 or 24)
@@ -95,6 +116,7 @@ struct b3d_model {
     b3d::VertexTables<float> t32;
     b3d::VertexTables<double> t64;
     b3d::SortedTables ts;                       // only when nw == 4
+    b3d::TcTables tc;                           // only when nw == 4
     float* posedirs32 = nullptr;                // [207][3][Vpad] (k, c, v)
     double* posedirs64 = nullptr;
     std::vector<uint32_t> faces;                // host copy (rendering only)

@@ -1,0 +1,433 @@
+// Entry (1), float32, large batches: shape blend on the tensor cores, skinning on the CUDA cores, one body per TMEM lane.
+// Replaces the per-vertex part of ark::Avatar::update (external/avatar/Avatar.cpp:26 shape blend, :69-73 skinning).
+//
+//   cloud[b][v] = sum_k weight[v][k] * ( R[b][j_vk] * (template[v] + shapedirs[v] w[b]) + t[b][j_vk] )
+//
+// CTA = 128 bodies x a run of sort tiles (96 consecutive vertices each; three MMA tiles of 32 slots).
+//   * shape blend: D[128 bodies x 96 (slot, coordinate)] = A[128 x 32] B[96 x 32]^T by tcgen05.mma kind::tf32 into TMEM.
+//     K = 32 carries a TF32 hi/lo split so that the result is good to ~2^-22:  k 0-9 w_hi * S_hi, 10-19 w_hi * S_lo,
+//     20-29 w_lo * S_hi, 30 1 * T_hi, 31 1 * T_lo (S = shapedirs, T = template).  A is built once per CTA in the canonical
+//     K-major / no-swizzle layout; B arrives per MMA tile as one TMA bulk copy (cp.async.bulk + mbarrier) of a blob the model
+//     build laid out in exactly that layout (internal.hpp TcTables), four stages deep; two accumulator buffers in TMEM.
+//   * a lane of an epilogue warp is a body (tcgen05.ld 32x32b: thread <-> TMEM lane).  The body's 24 joint transforms live in
+//     TMEM columns 0-287 (written once per CTA by tcgen05.st); the four of the current joint set sit in 48 registers and are
+//     re-read only for the register sets the host marked (slots are ordered so that consecutive joint sets overlap).  Per slot
+//     the warp reads one 32-byte record (weights, position, control word) as warp-uniform LDS.128.
+//   * results go to a [32 bodies][3 x 96 + 1] staging tile per TMEM lane quadrant and leave as full rows (coalesced stores):
+//     HBM sees the cloud write only.
+// Warp roles: 0-7 epilogue (quadrant = warp & 3, half of every MMA tile's slots = warp >> 2), 8 TMA producer, 9 MMA issuer.
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+
+#include "internal.hpp"
+
+namespace b3d {
+namespace {
+
+constexpr int TC_NST = 4;
+constexpr int TC_EPI_WARPS = 8;
+constexpr int TC_THREADS = 32 * (TC_EPI_WARPS + 2);
+constexpr int TC_M = 128;
+constexpr int TC_SROW = 3 * TC_T + 1;           // 289 floats: odd stride, lane = row stores are conflict free
+constexpr int TC_COL_D0 = 320, TC_COL_D1 = 416;  // accumulator buffers; columns [0, 288) hold the joint transforms
+constexpr int TC_A_SLAB = TC_M * 32, TC_B_SLAB = TC_N * 32;   // bytes per K = 8 step of the operands
+
+struct __align__(128) TcSmem {
+    float A[TC_M * TC_K];
+    unsigned char stage[TC_NST][TC_BLOB_BYTES];
+    float out[4][32 * TC_SROW];
+    unsigned long long smem_full[TC_NST], stage_free[TC_NST], d_full[2], d_empty[2];
+    uint32_t tmem_base;
+};
+static_assert(TC_BLOB_BYTES % 128 == 0, "stage alignment");
+static_assert(sizeof(TcSmem) <= 227 * 1024, "shared memory budget");
+
+// canonical K-major, no swizzle (UMMA "interleave"): slabs of 8 k; in a slab [row group of 8][k chunk of 4][row][k]; verified
+// against tcgen05.mma on B200 by tools/tc_probe.cu (LBO = 128 B between k chunks, SBO = 256 B between row groups)
+__host__ __device__ inline int canon_off(int rows, int r, int k) {
+    return (k >> 3) * rows * 8 + (r >> 3) * 64 + ((k >> 2) & 1) * 32 + (r & 7) * 4 + (k & 3);
+}
+
+__device__ __forceinline__ uint32_t s_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void bar_init(unsigned long long* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void bar_expect_tx(unsigned long long* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bar_arrive(unsigned long long* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(s_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bar_wait(unsigned long long* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(s_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(s_u32(dst)), "l"(src),
+                 "r"(bytes), "r"(s_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(unsigned long long* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(s_u32(bar)) : "memory");
+}
+__device__ __forceinline__ uint64_t smem_desc(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+    d |= (uint64_t)((128u >> 4) & 0x3FFF) << 16;   // leading-dimension byte offset: between the two k chunks of a K = 8 step
+    d |= (uint64_t)((256u >> 4) & 0x3FFF) << 32;   // stride byte offset: between groups of 8 rows
+    d |= (uint64_t)1 << 46;                        // descriptor version (sm_100); layout type 0 = no swizzle
+    return d;
+}
+__device__ __forceinline__ void mma_tf32(uint32_t d_tmem, uint64_t da, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem), "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]), "=f"(v[8]), "=f"(v[9]),
+                   "=f"(v[10]), "=f"(v[11]), "=f"(v[12]), "=f"(v[13]), "=f"(v[14]), "=f"(v[15])
+                 : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, float* v) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];" : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]) : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_st4(uint32_t taddr, float4 v) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(taddr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float to_tf32(float x) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+    return __uint_as_float(r);
+}
+__device__ __forceinline__ void named_bar(int id, int threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory"); }
+
+__global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsigned char* __restrict__ blob, int V, int B, int sort_tiles, int splits,
+                                                                     const float* __restrict__ wshape, const float* __restrict__ G,
+                                                                     float* __restrict__ cloud) {
+    extern __shared__ __align__(128) unsigned char tc_raw[];
+    TcSmem& S = *reinterpret_cast<TcSmem*>(tc_raw);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int b0 = blockIdx.y * TC_M;
+    const int t_begin = (int)((long long)blockIdx.x * sort_tiles / splits);
+    const int t_end = (int)((long long)(blockIdx.x + 1) * sort_tiles / splits);
+    const int nM = 3 * (t_end - t_begin);
+
+    if (tid == 0) {
+        for (int i = 0; i < TC_NST; ++i) { bar_init(&S.smem_full[i], 1); bar_init(&S.stage_free[i], 1 + TC_EPI_WARPS); }
+        for (int i = 0; i < 2; ++i) { bar_init(&S.d_full[i], 1); bar_init(&S.d_empty[i], TC_EPI_WARPS); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 9) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s_u32(&S.tmem_base)), "r"(512));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
+    // A operand: rows = bodies, TF32 hi / hi / lo copies of the shape vector and two ones for the template columns
+    for (int i = tid; i < TC_M * NS; i += TC_THREADS) {
+        const int r = i / NS, s = i - r * NS;
+        const float w = (b0 + r < B) ? wshape[(size_t)(b0 + r) * NS + s] : 0.f;
+        const float hi = to_tf32(w), lo = to_tf32(w - hi);
+        S.A[canon_off(TC_M, r, s)] = hi;
+        S.A[canon_off(TC_M, r, NS + s)] = hi;
+        S.A[canon_off(TC_M, r, 2 * NS + s)] = lo;
+    }
+    for (int r = tid; r < TC_M; r += TC_THREADS) {
+        S.A[canon_off(TC_M, r, 30)] = 1.f;
+        S.A[canon_off(TC_M, r, 31)] = 1.f;
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes of A -> visible to the tensor core
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tm = S.tmem_base;
+
+    // joint transforms of the CTA's 128 bodies -> TMEM columns [0, 288), body = lane
+    if (warp < TC_EPI_WARPS) {
+        const int q = warp & 3, h = warp >> 2;
+        const int body = b0 + 32 * q + lane;
+        const float4* src = reinterpret_cast<const float4*>(G + (size_t)min(body, B - 1) * (NJ * 12) + 144 * h);
+        const uint32_t taddr = tm + ((uint32_t)(32 * q) << 16) + (uint32_t)(144 * h);
+#pragma unroll 6
+        for (int c = 0; c < 36; ++c) tmem_st4(taddr + 4 * c, src[c]);
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+
+    if (warp == 8) {
+        if (lane == 0) {
+            const unsigned char* src = blob + (size_t)(3 * t_begin) * TC_BLOB_BYTES;
+            for (int m = 0; m < nM; ++m) {
+                const int st = m % TC_NST, u = m / TC_NST;
+                bar_wait(&S.stage_free[st], (uint32_t)((u & 1) ^ 1));
+                bar_expect_tx(&S.smem_full[st], TC_BLOB_BYTES);
+                bulk_g2s(S.stage[st], src + (size_t)m * TC_BLOB_BYTES, TC_BLOB_BYTES, &S.smem_full[st]);
+            }
+        }
+    } else if (warp == 9) {
+        if (lane == 0) {
+            // instruction descriptor: D = F32, A = B = TF32, both K-major, N = 96, M = 128
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_N >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);
+            const uint32_t a_addr = s_u32(S.A);
+            for (int m = 0; m < nM; ++m) {
+                const int st = m % TC_NST, u = m / TC_NST, buf = m & 1, r = m >> 1;
+                bar_wait(&S.smem_full[st], (uint32_t)(u & 1));
+                bar_wait(&S.d_empty[buf], (uint32_t)((r & 1) ^ 1));
+                tc_fence_after();
+                const uint32_t b_addr = s_u32(S.stage[st]);
+                const uint32_t d_tmem = tm + (uint32_t)(buf ? TC_COL_D1 : TC_COL_D0);
+#pragma unroll
+                for (int s = 0; s < TC_K / 8; ++s)
+                    mma_tf32(d_tmem, smem_desc(a_addr + s * TC_A_SLAB), smem_desc(b_addr + s * TC_B_SLAB), idesc, s > 0 ? 1u : 0u);
+                tc_commit(&S.stage_free[st]);
+                tc_commit(&S.d_full[buf]);
+            }
+        }
+    } else {
+        const int q = warp & 3, h = warp >> 2;
+        const uint32_t tm_row = tm + ((uint32_t)(32 * q) << 16);
+        float* const orow = &S.out[q][lane * TC_SROW];
+        float g[4][12];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+#pragma unroll
+            for (int e = 0; e < 12; ++e) g[k][e] = 0.f;
+        for (int m = 0; m < nM; ++m) {
+            const int st = m % TC_NST, u = m / TC_NST, buf = m & 1, r = m >> 1;
+            bar_wait(&S.smem_full[st], (uint32_t)(u & 1));     // slot records of this tile are in shared memory
+            bar_wait(&S.d_full[buf], (uint32_t)(r & 1));       // and its accumulators are complete
+            tc_fence_after();
+            float xyz[48];
+            const uint32_t d_addr = tm_row + (uint32_t)(buf ? TC_COL_D1 : TC_COL_D0) + (uint32_t)(48 * h);
+            tmem_ld16(d_addr, xyz);
+            tmem_ld16(d_addr + 16, xyz + 16);
+            tmem_ld16(d_addr + 32, xyz + 32);
+            tc_wait_ld();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) bar_arrive(&S.d_empty[buf]);        // the accumulator buffer may be overwritten
+
+            const uint4* rec = reinterpret_cast<const uint4*>(S.stage[st] + TC_OPER_BYTES) + 2 * (16 * h);
+#pragma unroll
+            for (int s = 0; s < 16; ++s) {
+                const uint4 r0 = rec[2 * s], r1 = rec[2 * s + 1];
+                const uint32_t ctl = r1.y;
+                if (ctl & 15u) {   // warp-uniform: some of the four register sets change joint
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (ctl & (1u << k)) {
+                            const uint32_t col = 12u * ((ctl >> (4 + 5 * k)) & 31u);
+                            tmem_ld4(tm_row + col, g[k]);
+                            tmem_ld4(tm_row + col + 4, g[k] + 4);
+                            tmem_ld4(tm_row + col + 8, g[k] + 8);
+                        }
+                    tc_wait_ld();
+                }
+                const float x = xyz[3 * s], y = xyz[3 * s + 1], z = xyz[3 * s + 2];
+                const float wk[4] = {__uint_as_float(r0.x), __uint_as_float(r0.y), __uint_as_float(r0.z), __uint_as_float(r0.w)};
+                float ax = 0.f, ay = 0.f, az = 0.f;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {   // column-major 3 x 4 [R | t]
+                    const float tx = fmaf(g[k][0], x, fmaf(g[k][3], y, fmaf(g[k][6], z, g[k][9])));
+                    const float ty = fmaf(g[k][1], x, fmaf(g[k][4], y, fmaf(g[k][7], z, g[k][10])));
+                    const float tz = fmaf(g[k][2], x, fmaf(g[k][5], y, fmaf(g[k][8], z, g[k][11])));
+                    ax = fmaf(wk[k], tx, ax);
+                    ay = fmaf(wk[k], ty, ay);
+                    az = fmaf(wk[k], tz, az);
+                }
+                float* so = orow + r1.x;
+                so[0] = ax; so[1] = ay; so[2] = az;
+            }
+            __syncwarp();
+            if (lane == 0) bar_arrive(&S.stage_free[st]);      // records read: the stage may be refilled
+
+            if (m % 3 == 2) {   // a sort tile is complete: rows of 3 x 96 consecutive floats per body
+                named_bar(1 + q, 64);
+                const int base_v = (t_begin + m / 3) * TC_T;
+                const int nfl = 3 * min(TC_T, V - base_v);
+                for (int row = 16 * h; row < 16 * h + 16; ++row) {
+                    const int body = b0 + 32 * q + row;
+                    if (body >= B) break;
+                    float* dst = cloud + ((size_t)body * V + base_v) * 3;
+                    const float* src = &S.out[q][row * TC_SROW];
+                    float v[9];
+#pragma unroll
+                    for (int i = 0; i < 9; ++i) v[i] = (lane + 32 * i < nfl) ? src[lane + 32 * i] : 0.f;
+#pragma unroll
+                    for (int i = 0; i < 9; ++i)
+                        if (lane + 32 * i < nfl) dst[lane + 32 * i] = v[i];
+                }
+                named_bar(1 + q, 64);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 9) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tm), "r"(512));
+}
+
+inline float tf32_round_host(float x) {   // round to 10 explicit mantissa bits (ties away); the low 13 bits end up zero
+    uint32_t u;
+    std::memcpy(&u, &x, 4);
+    u = (u + 0x1000u) & ~0x1FFFu;
+    float r;
+    std::memcpy(&r, &u, 4);
+    return r;
+}
+
+}  // namespace
+
+// Host side of the tables: slot order, register-set assignment and the operand blobs.
+int build_tc_tables(b3d_model& m, const std::vector<double>& vert, const std::vector<double>& wval, const std::vector<int32_t>& wjoint) {
+    const size_t Vp = (size_t)m.Vpad;
+    const int V = m.V;
+    const int tiles = (V + TC_T - 1) / TC_T;
+    std::vector<unsigned char> blob((size_t)tiles * 3 * TC_BLOB_BYTES, 0);
+    long long reloads = 0, slots_total = 0;
+
+    struct Vtx { int v; int nj; int j[4]; float w[4]; uint64_t key; };
+    for (int t = 0; t < tiles; ++t) {
+        const int base = t * TC_T;
+        std::vector<Vtx> vs(TC_T);
+        int pad_pos = std::min(TC_T, V - base);
+        for (int i = 0; i < TC_T; ++i) {
+            Vtx& x = vs[i];
+            x.v = base + i;
+            x.nj = 0;
+            x.key = ~0ull;
+            if (x.v < V) {
+                uint64_t k = 0;
+                for (int q = 0; q < 4; ++q) {
+                    const double wv = wval[q * Vp + x.v];
+                    if (wv != 0.0) { x.j[x.nj] = wjoint[q * Vp + x.v]; x.w[x.nj] = (float)wv; ++x.nj; }
+                }
+                for (int q = 0; q < 4; ++q) k = k * 32 + (uint64_t)(q < x.nj ? x.j[q] : 31);
+                x.key = k;
+            }
+        }
+        std::vector<int> order(TC_T);
+        for (int i = 0; i < TC_T; ++i) order[i] = i;
+        std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return vs[a].key < vs[b].key; });
+
+        for (int h = 0; h < 2; ++h) {
+            // the half's vertices, grouped by joint set, groups ordered greedily by the number of register sets to re-read
+            std::vector<int> idx(order.begin() + 48 * h, order.begin() + 48 * h + 48);
+            std::vector<std::vector<int>> groups;
+            for (int i : idx) {
+                if (!groups.empty() && vs[groups.back()[0]].key == vs[i].key) groups.back().push_back(i);
+                else groups.push_back({i});
+            }
+            int reg[4] = {-1, -1, -1, -1};
+            std::vector<bool> used(groups.size(), false);
+            int slot = 0;
+            for (size_t done = 0; done < groups.size(); ++done) {
+                int best = -1, best_cost = 99;
+                for (size_t gi = 0; gi < groups.size(); ++gi) {
+                    if (used[gi]) continue;
+                    const Vtx& x = vs[groups[gi][0]];
+                    int cost = 0;
+                    for (int a = 0; a < x.nj; ++a) cost += !(reg[0] == x.j[a] || reg[1] == x.j[a] || reg[2] == x.j[a] || reg[3] == x.j[a]);
+                    if (done == 0) cost = (int)gi;   // start from the first group in key order
+                    if (cost < best_cost) { best_cost = cost; best = (int)gi; }
+                }
+                used[best] = true;
+                const Vtx& g0 = vs[groups[best][0]];
+                // assign missing joints to register sets that hold joints this group does not use
+                uint32_t flags = 0;
+                for (int a = 0; a < g0.nj; ++a) {
+                    bool have = false;
+                    for (int k = 0; k < 4; ++k) have = have || reg[k] == g0.j[a];
+                    if (have) continue;
+                    int k_free = -1;
+                    for (int k = 0; k < 4 && k_free < 0; ++k) {
+                        bool needed = false;
+                        for (int a2 = 0; a2 < g0.nj; ++a2) needed = needed || reg[k] == g0.j[a2];
+                        if (!needed) k_free = k;
+                    }
+                    reg[k_free] = g0.j[a];
+                    flags |= 1u << k_free;
+                }
+                for (size_t gi2 = 0; gi2 < groups[best].size(); ++gi2, ++slot) {
+                    const Vtx& x = vs[groups[best][gi2]];
+                    uint32_t f = gi2 == 0 ? flags : 0u;
+                    if (slot == 0) f = 15u;                        // a warp starts a sort tile with nothing assumed
+                    int jr[4];
+                    for (int k = 0; k < 4; ++k) { jr[k] = reg[k] < 0 ? 0 : reg[k]; if (reg[k] < 0 && slot == 0) reg[k] = 0; }
+                    const int mt = slot / 16, s = slot % 16;
+                    unsigned char* bl = &blob[((size_t)t * 3 + mt) * TC_BLOB_BYTES];
+                    float* oper = reinterpret_cast<float*>(bl);
+                    uint32_t* rec = reinterpret_cast<uint32_t*>(bl + TC_OPER_BYTES) + (16 * h + s) * TC_REC_WORDS;
+                    float wr[4] = {0.f, 0.f, 0.f, 0.f};
+                    for (int a = 0; a < x.nj; ++a)
+                        for (int k = 0; k < 4; ++k)
+                            if (jr[k] == x.j[a]) { wr[k] = x.w[a]; break; }
+                    std::memcpy(rec, wr, 16);
+                    int pos = x.v < V ? x.v - base : pad_pos++;
+                    rec[4] = (uint32_t)(3 * pos);
+                    rec[5] = f | ((uint32_t)jr[0] << 4) | ((uint32_t)jr[1] << 9) | ((uint32_t)jr[2] << 14) | ((uint32_t)jr[3] << 19);
+                    rec[6] = (uint32_t)x.v;
+                    rec[7] = 0;
+                    for (int k = 0; k < 4; ++k) reloads += (f >> k) & 1u;
+                    ++slots_total;
+                    if (x.v < V)
+                        for (int c = 0; c < 3; ++c) {
+                            const int n = 48 * h + 3 * s + c;
+                            for (int k = 0; k < NS; ++k) {
+                                const float sd = (float)vert[(3 + NS * c + k) * Vp + x.v];
+                                const float hi = tf32_round_host(sd), lo = tf32_round_host(sd - hi);
+                                oper[canon_off(TC_N, n, k)] = hi;
+                                oper[canon_off(TC_N, n, NS + k)] = lo;
+                                oper[canon_off(TC_N, n, 2 * NS + k)] = hi;
+                            }
+                            const float tv = (float)vert[c * Vp + x.v];
+                            const float hi = tf32_round_host(tv), lo = tf32_round_host(tv - hi);
+                            oper[canon_off(TC_N, n, 30)] = hi;
+                            oper[canon_off(TC_N, n, 31)] = lo;
+                        }
+                }
+            }
+        }
+    }
+    B3D_CUDA(cudaMalloc(&m.tc.blob, blob.size()));
+    B3D_CUDA(cudaMemcpy(m.tc.blob, blob.data(), blob.size(), cudaMemcpyHostToDevice));
+    m.tc.sort_tiles = tiles;
+    m.tc.mean_reloads = slots_total ? (double)reloads / (double)slots_total : 0.0;
+    return B3D_OK;
+}
+
+int launch_lbs_tc(const b3d_model* m, int B, const float* wshape, const float* G, float* cloud, cudaStream_t st) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        B3D_CUDA(cudaFuncSetAttribute(smpl_lbs_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem)));
+        attr_set = true;
+    }
+    const int groups = (B + TC_M - 1) / TC_M;
+    const int tiles = m->tc.sort_tiles;
+    // vertex splits: fill 148 SMs in whole waves; a CTA's prologue (A operand, transforms -> TMEM) costs about 1/25 of a body
+    // group's full vertex sweep
+    static const int forced = [] { const char* e = getenv("B3D_TC_SPLITS"); return e ? atoi(e) : 0; }();
+    int best_s = 1;
+    double best_cost = 1e30;
+    for (int s = 1; s <= std::min(tiles, 24); ++s) {
+        const long long ctas = (long long)groups * s;
+        const long long waves = (ctas + 147) / 148;
+        const int per = (tiles + s - 1) / s;   // sort tiles of the longest CTA
+        const double cost = (double)waves * ((double)per + 0.04 * tiles);
+        if (cost < best_cost * 0.999) { best_cost = cost; best_s = s; }
+    }
+    if (forced > 0) best_s = std::min(forced, tiles);
+    smpl_lbs_tc_kernel<<<dim3(best_s, groups), TC_THREADS, sizeof(TcSmem), st>>>(m->tc.blob, m->V, B, tiles, best_s, wshape, G, cloud);
+    return B3D_OK;
+}
+
+}  // namespace b3d

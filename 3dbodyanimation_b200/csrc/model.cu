@@ -210,6 +210,7 @@ int b3d_model_create(const b3d_model_desc* d, b3d_model** out) {
     int rc = upload_tables<float>(*m, vert, wval, wjoint, m->t32);
     if (!rc) rc = upload_tables<double>(*m, vert, wval, wjoint, m->t64);
     if (!rc && m->nw == 4) rc = upload_sorted_tables(*m, vert, wval, wjoint);
+    if (!rc && m->nw == 4) rc = build_tc_tables(*m, vert, wval, wjoint);
     if (!rc && d->posedirs) {
         const int P = B3D_POSEDIRS_DIM;
         std::vector<float> p32((size_t)P * 3 * Vp, 0.f);
@@ -244,7 +245,7 @@ void b3d_model_destroy(b3d_model* m) {
     cudaFree(m->t32.vert); cudaFree(m->t32.wval); cudaFree(m->t32.wjoint);
     cudaFree(m->t64.vert); cudaFree(m->t64.wval); cudaFree(m->t64.wjoint);
     cudaFree(m->ts.vert); cudaFree(m->ts.wval); cudaFree(m->ts.wjoff); cudaFree(m->ts.loc);
-    cudaFree(m->ts.rec); cudaFree(m->ts.joff4);
+    cudaFree(m->ts.rec); cudaFree(m->ts.joff4); cudaFree(m->tc.blob);
     cudaFree(m->posedirs32); cudaFree(m->posedirs64); cudaFree(m->d_sk);
     delete m;
 }

@@ -115,7 +115,13 @@ int b3d_gmm_residual(const b3d_gmm* g, int32_t B, const double* x, double* out, 
 /* ===================================================================================================== */
 enum {
     B3D_FWD_DEFAULT = 0,
-    B3D_FWD_POSEDIRS = 1   /* add posedirs . vec(R_j - I) (standard SMPL; the reference has this commented out) */
+    B3D_FWD_POSEDIRS = 1,  /* add posedirs . vec(R_j - I) (standard SMPL; the reference has this commented out) */
+    /* float32 skinning kernel override (tests, profiling); without one of these the library picks by batch size:
+     * tensor-core shape blend (tcgen05, lane = body) for large batches, tile-sorted lane = vertex kernel otherwise */
+    B3D_FWD_LBS_TC = 0x10,
+    B3D_FWD_LBS_SORTED = 0x20,
+    B3D_FWD_LBS_BODYLANE = 0x40,
+    B3D_FWD_LBS_GENERIC = 0x80
 };
 
 /* Inputs per body: w (10) = Avatar::w, p (3) = Avatar::p, r (24 x 9, col-major) = Avatar::r.

@@ -35,6 +35,30 @@ def test_forward_parity(api, gmodel, omodel, synth, B, dtype, tol):
     assert rel_err(jp, jp0) < tol and rel_err(jt, jt0) < tol
 
 
+@pytest.mark.parametrize("lbs", ["tc", "sorted", "bodylane", "generic"])
+@pytest.mark.parametrize("B", [1, 130, 1000])
+def test_forward_parity_every_f32_kernel(api, gmodel, omodel, synth, lbs, B):
+    """Each float32 skinning kernel (B3D_FWD_LBS_*), forced, against the oracle: the tensor-core shape blend (tcgen05 kind::tf32
+    with a hi/lo split) has to meet the same 1e-5 as the CUDA-core kernels; partial body groups (B % 128 != 0) included."""
+    inp = synth.make_forward_inputs(B, 300 + B)
+    c, jp, jt = api.smpl_forward(gmodel, inp["w"], inp["p"], inp["r"], dtype=np.float32, lbs=lbs)
+    w, p, r = (np.asarray(inp[k], dtype=np.float32).astype(np.float64) for k in ("w", "p", "r"))
+    c0, jp0, jt0 = omodel.forward(w, p, r, nthreads=8)
+    worst = max(rel_err(c[b], c0[b]) for b in range(B))
+    assert worst < TOL_F32, (lbs, B, worst)
+
+
+def test_forward_tc_matches_sorted_large_batch(api, gmodel, synth):
+    """BASELINE-scale batch: the tensor-core kernel against the CUDA-core kernel on every (body, vertex) — catches a misplaced
+    row, slot or body group that a small batch cannot reach."""
+    B = 4096 + 37
+    inp = synth.make_forward_inputs(B, 91)
+    a, _, _ = api.smpl_forward(gmodel, inp["w"], inp["p"], inp["r"], dtype=np.float32, lbs="tc")
+    b, _, _ = api.smpl_forward(gmodel, inp["w"], inp["p"], inp["r"], dtype=np.float32, lbs="sorted")
+    err = np.max(np.abs(a.astype(np.float64) - b), axis=(1, 2)) / np.max(np.abs(b), axis=(1, 2))
+    assert err.max() < 2e-6, err.max()
+
+
 def test_forward_posedirs_extension(api, gmodel, omodel_pd, synth):
     inp = synth.make_forward_inputs(9, 5)
     c, _, _ = api.smpl_forward(gmodel, inp["w"], inp["p"], inp["r"], dtype=np.float64, posedirs=True)
