@@ -63,10 +63,10 @@ __device__ __forceinline__ void bar_wait(unsigned long long* bar, uint32_t parit
     asm volatile(
         "{\n\t.reg .pred p;\n\t"
         "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n\t"   // %2: suspend-time hint, the thread sleeps in hardware
         "@p bra DONE_%=;\n\t"
         "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t}" ::"r"(s_u32(bar)), "r"(parity) : "memory");
+        "DONE_%=:\n\t}" ::"r"(s_u32(bar)), "r"(parity), "r"(0x989680u) : "memory");
 }
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, unsigned long long* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(s_u32(dst)), "l"(src),
@@ -207,46 +207,67 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
             bar_wait(&S.smem_full[st], (uint32_t)(u & 1));     // slot records of this tile are in shared memory
             bar_wait(&S.d_full[buf], (uint32_t)(r & 1));       // and its accumulators are complete
             tc_fence_after();
-            float xyz[48];
+            // this warp's 16 slots in 4 groups of 4 (a rolled loop: the body stays inside the instruction cache); the next group's
+            // accumulators (12 TMEM columns) and records are fetched while the current group computes
             const uint32_t d_addr = tm_row + (uint32_t)(buf ? TC_COL_D1 : TC_COL_D0) + (uint32_t)(48 * h);
-            tmem_ld16(d_addr, xyz);
-            tmem_ld16(d_addr + 16, xyz + 16);
-            tmem_ld16(d_addr + 32, xyz + 32);
-            tc_wait_ld();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) bar_arrive(&S.d_empty[buf]);        // the accumulator buffer may be overwritten
-
             const uint4* rec = reinterpret_cast<const uint4*>(S.stage[st] + TC_OPER_BYTES) + 2 * (16 * h);
+            float nxyz[12];
+            tmem_ld4(d_addr, nxyz);
+            tmem_ld4(d_addr + 4, nxyz + 4);
+            tmem_ld4(d_addr + 8, nxyz + 8);
+            uint4 nrec[8];
 #pragma unroll
-            for (int s = 0; s < 16; ++s) {
-                const uint4 r0 = rec[2 * s], r1 = rec[2 * s + 1];
-                const uint32_t ctl = r1.y;
-                if (ctl & 15u) {   // warp-uniform: some of the four register sets change joint
+            for (int e = 0; e < 8; ++e) nrec[e] = rec[e];
+#pragma unroll 1
+            for (int gidx = 0; gidx < 4; ++gidx) {
+                tc_wait_ld();
+                float xyz[12];
+                uint4 r[8];
 #pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        if (ctl & (1u << k)) {
-                            const uint32_t col = 12u * ((ctl >> (4 + 5 * k)) & 31u);
-                            tmem_ld4(tm_row + col, g[k]);
-                            tmem_ld4(tm_row + col + 4, g[k] + 4);
-                            tmem_ld4(tm_row + col + 8, g[k] + 8);
-                        }
-                    tc_wait_ld();
+                for (int e = 0; e < 12; ++e) xyz[e] = nxyz[e];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) r[e] = nrec[e];
+                if (gidx < 3) {
+                    tmem_ld4(d_addr + 12 * (gidx + 1), nxyz);
+                    tmem_ld4(d_addr + 12 * (gidx + 1) + 4, nxyz + 4);
+                    tmem_ld4(d_addr + 12 * (gidx + 1) + 8, nxyz + 8);
+#pragma unroll
+                    for (int e = 0; e < 8; ++e) nrec[e] = rec[8 * (gidx + 1) + e];
+                } else {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) bar_arrive(&S.d_empty[buf]);    // every accumulator of the tile is in registers
                 }
-                const float x = xyz[3 * s], y = xyz[3 * s + 1], z = xyz[3 * s + 2];
-                const float wk[4] = {__uint_as_float(r0.x), __uint_as_float(r0.y), __uint_as_float(r0.z), __uint_as_float(r0.w)};
-                float ax = 0.f, ay = 0.f, az = 0.f;
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {   // column-major 3 x 4 [R | t]
-                    const float tx = fmaf(g[k][0], x, fmaf(g[k][3], y, fmaf(g[k][6], z, g[k][9])));
-                    const float ty = fmaf(g[k][1], x, fmaf(g[k][4], y, fmaf(g[k][7], z, g[k][10])));
-                    const float tz = fmaf(g[k][2], x, fmaf(g[k][5], y, fmaf(g[k][8], z, g[k][11])));
-                    ax = fmaf(wk[k], tx, ax);
-                    ay = fmaf(wk[k], ty, ay);
-                    az = fmaf(wk[k], tz, az);
+                for (int s = 0; s < 4; ++s) {
+                    const uint4 r0 = r[2 * s], r1 = r[2 * s + 1];
+                    const uint32_t ctl = r1.y;
+                    if (ctl & 15u) {   // warp-uniform: some of the four register sets change joint
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            if (ctl & (1u << k)) {
+                                const uint32_t col = 12u * ((ctl >> (4 + 5 * k)) & 31u);
+                                tmem_ld4(tm_row + col, g[k]);
+                                tmem_ld4(tm_row + col + 4, g[k] + 4);
+                                tmem_ld4(tm_row + col + 8, g[k] + 8);
+                            }
+                        tc_wait_ld();
+                    }
+                    const float x = xyz[3 * s], y = xyz[3 * s + 1], z = xyz[3 * s + 2];
+                    const float wk[4] = {__uint_as_float(r0.x), __uint_as_float(r0.y), __uint_as_float(r0.z), __uint_as_float(r0.w)};
+                    float ax = 0.f, ay = 0.f, az = 0.f;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {   // column-major 3 x 4 [R | t]
+                        const float tx = fmaf(g[k][0], x, fmaf(g[k][3], y, fmaf(g[k][6], z, g[k][9])));
+                        const float ty = fmaf(g[k][1], x, fmaf(g[k][4], y, fmaf(g[k][7], z, g[k][10])));
+                        const float tz = fmaf(g[k][2], x, fmaf(g[k][5], y, fmaf(g[k][8], z, g[k][11])));
+                        ax = fmaf(wk[k], tx, ax);
+                        ay = fmaf(wk[k], ty, ay);
+                        az = fmaf(wk[k], tz, az);
+                    }
+                    float* so = orow + r1.x;
+                    so[0] = ax; so[1] = ay; so[2] = az;
                 }
-                float* so = orow + r1.x;
-                so[0] = ax; so[1] = ay; so[2] = az;
             }
             __syncwarp();
             if (lane == 0) bar_arrive(&S.stage_free[st]);      // records read: the stage may be refilled
@@ -255,17 +276,20 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
                 named_bar(1 + q, 64);
                 const int base_v = (t_begin + m / 3) * TC_T;
                 const int nfl = 3 * min(TC_T, V - base_v);
-                for (int row = 16 * h; row < 16 * h + 16; ++row) {
-                    const int body = b0 + 32 * q + row;
-                    if (body >= B) break;
-                    float* dst = cloud + ((size_t)body * V + base_v) * 3;
-                    const float* src = &S.out[q][row * TC_SROW];
-                    float v[9];
+                const int rows = min(16, B - (b0 + 32 * q + 16 * h));   // bodies of this warp's half of the quadrant that exist
+                float* dst = cloud + ((size_t)(b0 + 32 * q + 16 * h) * V + base_v) * 3 + lane;
+                const float* src = &S.out[q][16 * h * TC_SROW + lane];
+                if (nfl == 3 * TC_T) {
+                    for (int row = 0; row < rows; ++row, dst += (size_t)V * 3, src += TC_SROW) {
+                        float v[9];
 #pragma unroll
-                    for (int i = 0; i < 9; ++i) v[i] = (lane + 32 * i < nfl) ? src[lane + 32 * i] : 0.f;
+                        for (int i = 0; i < 9; ++i) v[i] = src[32 * i];
 #pragma unroll
-                    for (int i = 0; i < 9; ++i)
-                        if (lane + 32 * i < nfl) dst[lane + 32 * i] = v[i];
+                        for (int i = 0; i < 9; ++i) dst[32 * i] = v[i];
+                    }
+                } else {
+                    for (int row = 0; row < rows; ++row, dst += (size_t)V * 3, src += TC_SROW)
+                        for (int e = lane; e < nfl; e += 32) dst[e - lane] = src[e - lane];
                 }
                 named_bar(1 + q, 64);
             }
