@@ -86,6 +86,7 @@ struct TcTables {
     double mean_reloads = 0.0;   // joint transforms re-read from TMEM per slot (host statistic, reported by tools)
 };
 constexpr int TC_T = 96, TC_SLOTS = 32, TC_N = 96, TC_K = 32;
+constexpr int TC_SEQS = 4;   // slot sequences per sort tile = epilogue warps per TMEM lane quadrant
 constexpr int TC_OPER_BYTES = TC_N * TC_K * 4, TC_REC_WORDS = 8, TC_BLOB_BYTES = TC_OPER_BYTES + TC_SLOTS * TC_REC_WORDS * 4;
 
 // small per-model constants passed to kernels by value

@@ -15,7 +15,9 @@
 //     the warp reads one 32-byte record (weights, position, control word) as warp-uniform LDS.128.
 //   * results go to a [32 bodies][3 x 96 + 1] staging tile per TMEM lane quadrant and leave as full rows (coalesced stores):
 //     HBM sees the cloud write only.
-// Warp roles: 0-7 epilogue (quadrant = warp & 3, half of every MMA tile's slots = warp >> 2), 8 TMA producer, 9 MMA issuer.
+// Warps: 16, all of them skinning warps (TMEM lane quadrant = warp & 3, slot sequence = warp >> 2: four warps per scheduler
+// hide the FMA / LDS / TMEM latencies); lane 0 of warp 0 also issues the TMA copies (two tiles ahead), lane 0 of warp 1 the MMAs
+// (one tile ahead), at the top of a tile.
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
@@ -26,20 +28,26 @@ namespace b3d {
 namespace {
 
 constexpr int TC_NST = 4;
-constexpr int TC_EPI_WARPS = 8;
-constexpr int TC_THREADS = 32 * (TC_EPI_WARPS + 2);
+constexpr int TC_WPQ = TC_SEQS;                  // epilogue warps per TMEM lane quadrant (= slot sequences per sort tile)
+constexpr int TC_SPW = TC_SLOTS / TC_WPQ;        // slots of an MMA tile per warp
+constexpr int TC_EPI_WARPS = 4 * TC_WPQ;
+constexpr int TC_THREADS = 32 * TC_EPI_WARPS;    // every warp is an epilogue warp; warp 0 / warp 1 also issue the TMA copies / the MMAs
 constexpr int TC_M = 128;
 constexpr int TC_SROW = 3 * TC_T + 1;           // 289 floats: odd stride, lane = row stores are conflict free
 constexpr int TC_COL_D0 = 320, TC_COL_D1 = 416;  // accumulator buffers; columns [0, 288) hold the joint transforms
 constexpr int TC_A_SLAB = TC_M * 32, TC_B_SLAB = TC_N * 32;   // bytes per K = 8 step of the operands
 
+constexpr int TC_GROW = NJ * 12 + 4;            // 292 floats: prologue rows of joint transforms, 16 B aligned and conflict free for LDS.128
+
 struct __align__(128) TcSmem {
     float A[TC_M * TC_K];
-    unsigned char stage[TC_NST][TC_BLOB_BYTES];
-    float out[4][32 * TC_SROW];
-    unsigned long long smem_full[TC_NST], stage_free[TC_NST], d_full[2], d_empty[2];
+    float out[4][32 * TC_SROW];                  // the prologue lands the 128 x 288 joint transforms here (rows of TC_GROW floats,
+    unsigned char stage[TC_NST][TC_BLOB_BYTES];  //   running over into stage[0], which is not in use yet)
+    unsigned long long smem_full[TC_NST], stage_free[TC_NST], d_full[2], d_empty[2], g_full;
     uint32_t tmem_base;
 };
+static_assert(TC_M * TC_GROW * 4 <= (int)(sizeof(float) * 4 * 32 * TC_SROW) + TC_BLOB_BYTES, "prologue staging of the transforms");
+static_assert((sizeof(float) * (TC_M * TC_K + 4 * 32 * TC_SROW)) % 128 == 0, "stage alignment");
 static_assert(TC_BLOB_BYTES % 128 == 0, "stage alignment");
 static_assert(sizeof(TcSmem) <= 227 * 1024, "shared memory budget");
 
@@ -98,6 +106,11 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
                    "=f"(v[10]), "=f"(v[11]), "=f"(v[12]), "=f"(v[13]), "=f"(v[14]), "=f"(v[15])
                  : "r"(taddr));
 }
+__device__ __forceinline__ void tmem_ld8(uint32_t taddr, float* v) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+                 : "r"(taddr));
+}
 __device__ __forceinline__ void tmem_ld4(uint32_t taddr, float* v) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];" : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]) : "r"(taddr));
 }
@@ -125,12 +138,19 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
     if (tid == 0) {
         for (int i = 0; i < TC_NST; ++i) { bar_init(&S.smem_full[i], 1); bar_init(&S.stage_free[i], 1 + TC_EPI_WARPS); }
         for (int i = 0; i < 2; ++i) { bar_init(&S.d_full[i], 1); bar_init(&S.d_empty[i], TC_EPI_WARPS); }
+        bar_init(&S.g_full, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 9) {
+    if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s_u32(&S.tmem_base)), "r"(512));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
     }
+    __syncthreads();
+    // joint transforms of the CTA's bodies: one TMA bulk copy per body row (1152 B) into padded shared rows
+    float* const gst = &S.out[0][0];
+    const int nb = min(TC_M, B - b0);
+    if (tid == 0) bar_expect_tx(&S.g_full, (uint32_t)nb * NJ * 12 * 4);
+    if (tid < nb) bulk_g2s(gst + tid * TC_GROW, G + (size_t)(b0 + tid) * (NJ * 12), NJ * 12 * 4, &S.g_full);
     // A operand: rows = bodies, TF32 hi / hi / lo copies of the shape vector and two ones for the template columns
     for (int i = tid; i < TC_M * NS; i += TC_THREADS) {
         const int r = i / NS, s = i - r * NS;
@@ -150,50 +170,50 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
     tc_fence_after();
     const uint32_t tm = S.tmem_base;
 
-    // joint transforms of the CTA's 128 bodies -> TMEM columns [0, 288), body = lane
-    if (warp < TC_EPI_WARPS) {
+    // shared rows -> TMEM columns [0, 288), body = lane (rows beyond the batch hold whatever the buffer held: never stored)
+    {
         const int q = warp & 3, h = warp >> 2;
-        const int body = b0 + 32 * q + lane;
-        const float4* src = reinterpret_cast<const float4*>(G + (size_t)min(body, B - 1) * (NJ * 12) + 144 * h);
-        const uint32_t taddr = tm + ((uint32_t)(32 * q) << 16) + (uint32_t)(144 * h);
-#pragma unroll 6
-        for (int c = 0; c < 36; ++c) tmem_st4(taddr + 4 * c, src[c]);
+        constexpr int CPW = NJ * 12 / TC_WPQ;   // columns per warp
+        bar_wait(&S.g_full, 0);
+        const float4* src = reinterpret_cast<const float4*>(gst + (32 * q + lane) * TC_GROW + CPW * h);
+        const uint32_t taddr = tm + ((uint32_t)(32 * q) << 16) + (uint32_t)(CPW * h);
+#pragma unroll
+        for (int c = 0; c < CPW / 4; ++c) tmem_st4(taddr + 4 * c, src[c]);
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
     }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // staging rows were read through the generic proxy; TMA writes stage[0] next
     tc_fence_before();
-    __syncthreads();
+    __syncthreads();   // also: the staging rows may now be overwritten (TMA producer, epilogue stores)
     tc_fence_after();
 
-    if (warp == 8) {
-        if (lane == 0) {
-            const unsigned char* src = blob + (size_t)(3 * t_begin) * TC_BLOB_BYTES;
-            for (int m = 0; m < nM; ++m) {
-                const int st = m % TC_NST, u = m / TC_NST;
-                bar_wait(&S.stage_free[st], (uint32_t)((u & 1) ^ 1));
-                bar_expect_tx(&S.smem_full[st], TC_BLOB_BYTES);
-                bulk_g2s(S.stage[st], src + (size_t)m * TC_BLOB_BYTES, TC_BLOB_BYTES, &S.smem_full[st]);
-            }
-        }
-    } else if (warp == 9) {
-        if (lane == 0) {
-            // instruction descriptor: D = F32, A = B = TF32, both K-major, N = 96, M = 128
-            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_N >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);
-            const uint32_t a_addr = s_u32(S.A);
-            for (int m = 0; m < nM; ++m) {
-                const int st = m % TC_NST, u = m / TC_NST, buf = m & 1, r = m >> 1;
-                bar_wait(&S.smem_full[st], (uint32_t)(u & 1));
-                bar_wait(&S.d_empty[buf], (uint32_t)((r & 1) ^ 1));
-                tc_fence_after();
-                const uint32_t b_addr = s_u32(S.stage[st]);
-                const uint32_t d_tmem = tm + (uint32_t)(buf ? TC_COL_D1 : TC_COL_D0);
+    const unsigned char* const blob0 = blob + (size_t)(3 * t_begin) * TC_BLOB_BYTES;
+    auto issue_tma = [&](int m) {   // one thread: the blob of MMA tile m -> its stage, once everybody is done with the stage's last tile
+        const int st = m % TC_NST, u = m / TC_NST;
+        bar_wait(&S.stage_free[st], (uint32_t)((u & 1) ^ 1));
+        bar_expect_tx(&S.smem_full[st], TC_BLOB_BYTES);
+        bulk_g2s(S.stage[st], blob0 + (size_t)m * TC_BLOB_BYTES, TC_BLOB_BYTES, &S.smem_full[st]);
+    };
+    auto issue_mma = [&](int m) {   // one thread: shape blend of MMA tile m into accumulator buffer m & 1
+        // instruction descriptor: D = F32, A = B = TF32, both K-major, N = 96, M = 128
+        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_N >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);
+        const int st = m % TC_NST, u = m / TC_NST, buf = m & 1, r = m >> 1;
+        bar_wait(&S.smem_full[st], (uint32_t)(u & 1));
+        bar_wait(&S.d_empty[buf], (uint32_t)((r & 1) ^ 1));
+        tc_fence_after();
+        const uint32_t a_addr = s_u32(S.A), b_addr = s_u32(S.stage[st]);
+        const uint32_t d_tmem = tm + (uint32_t)(buf ? TC_COL_D1 : TC_COL_D0);
 #pragma unroll
-                for (int s = 0; s < TC_K / 8; ++s)
-                    mma_tf32(d_tmem, smem_desc(a_addr + s * TC_A_SLAB), smem_desc(b_addr + s * TC_B_SLAB), idesc, s > 0 ? 1u : 0u);
-                tc_commit(&S.stage_free[st]);
-                tc_commit(&S.d_full[buf]);
-            }
-        }
-    } else {
+        for (int s = 0; s < TC_K / 8; ++s)
+            mma_tf32(d_tmem, smem_desc(a_addr + s * TC_A_SLAB), smem_desc(b_addr + s * TC_B_SLAB), idesc, s > 0 ? 1u : 0u);
+        tc_commit(&S.stage_free[st]);
+        tc_commit(&S.d_full[buf]);
+    };
+    if (warp == 0 && lane == 0) {
+        issue_tma(0);
+        if (nM > 1) issue_tma(1);
+    }
+    if (warp == 1 && lane == 0) issue_mma(0);
+    {
         const int q = warp & 3, h = warp >> 2;
         const uint32_t tm_row = tm + ((uint32_t)(32 * q) << 16);
         float* const orow = &S.out[q][lane * TC_SROW];
@@ -203,82 +223,68 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
 #pragma unroll
             for (int e = 0; e < 12; ++e) g[k][e] = 0.f;
         for (int m = 0; m < nM; ++m) {
+            // service duties first: dependencies only point at earlier tiles, so a blocked issuer never blocks what it waits for
+            if (warp == 0 && lane == 0 && m + 2 < nM) issue_tma(m + 2);
+            if (warp == 1 && lane == 0 && m + 1 < nM) issue_mma(m + 1);
+            __syncwarp();
             const int st = m % TC_NST, u = m / TC_NST, buf = m & 1, r = m >> 1;
             bar_wait(&S.smem_full[st], (uint32_t)(u & 1));     // slot records of this tile are in shared memory
             bar_wait(&S.d_full[buf], (uint32_t)(r & 1));       // and its accumulators are complete
             tc_fence_after();
-            // this warp's 16 slots in 4 groups of 4 (a rolled loop: the body stays inside the instruction cache); the next group's
-            // accumulators (12 TMEM columns) and records are fetched while the current group computes
-            const uint32_t d_addr = tm_row + (uint32_t)(buf ? TC_COL_D1 : TC_COL_D0) + (uint32_t)(48 * h);
-            const uint4* rec = reinterpret_cast<const uint4*>(S.stage[st] + TC_OPER_BYTES) + 2 * (16 * h);
-            float nxyz[12];
-            tmem_ld4(d_addr, nxyz);
-            tmem_ld4(d_addr + 4, nxyz + 4);
-            tmem_ld4(d_addr + 8, nxyz + 8);
-            uint4 nrec[8];
+            float xyz[3 * TC_SPW];   // accumulators of this warp's slots
+            const uint32_t d_addr = tm_row + (uint32_t)(buf ? TC_COL_D1 : TC_COL_D0) + (uint32_t)(3 * TC_SPW * h);
 #pragma unroll
-            for (int e = 0; e < 8; ++e) nrec[e] = rec[e];
-#pragma unroll 1
-            for (int gidx = 0; gidx < 4; ++gidx) {
-                tc_wait_ld();
-                float xyz[12];
-                uint4 r[8];
+            for (int c = 0; c < 3 * TC_SPW; c += 8) tmem_ld8(d_addr + c, xyz + c);
+            tc_wait_ld();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) bar_arrive(&S.d_empty[buf]);        // the accumulator buffer may be overwritten
+
+            const uint4* rec = reinterpret_cast<const uint4*>(S.stage[st] + TC_OPER_BYTES) + 2 * (TC_SPW * h);
+            uint4 r0 = rec[0], r1 = rec[1];
 #pragma unroll
-                for (int e = 0; e < 12; ++e) xyz[e] = nxyz[e];
+            for (int s = 0; s < TC_SPW; ++s) {
+                uint4 n0 = r0, n1 = r1;
+                if (s + 1 < TC_SPW) { n0 = rec[2 * s + 2]; n1 = rec[2 * s + 3]; }   // next slot's record hides behind this slot
+                const uint32_t ctl = r1.y;
+                if (ctl & 15u) {   // warp-uniform: some of the four register sets change joint
 #pragma unroll
-                for (int e = 0; e < 8; ++e) r[e] = nrec[e];
-                if (gidx < 3) {
-                    tmem_ld4(d_addr + 12 * (gidx + 1), nxyz);
-                    tmem_ld4(d_addr + 12 * (gidx + 1) + 4, nxyz + 4);
-                    tmem_ld4(d_addr + 12 * (gidx + 1) + 8, nxyz + 8);
-#pragma unroll
-                    for (int e = 0; e < 8; ++e) nrec[e] = rec[8 * (gidx + 1) + e];
-                } else {
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) bar_arrive(&S.d_empty[buf]);    // every accumulator of the tile is in registers
+                    for (int k = 0; k < 4; ++k)
+                        if (ctl & (1u << k)) {
+                            const uint32_t col = 12u * ((ctl >> (4 + 5 * k)) & 31u);
+                            tmem_ld4(tm_row + col, g[k]);
+                            tmem_ld4(tm_row + col + 4, g[k] + 4);
+                            tmem_ld4(tm_row + col + 8, g[k] + 8);
+                        }
+                    tc_wait_ld();
                 }
+                const float x = xyz[3 * s], y = xyz[3 * s + 1], z = xyz[3 * s + 2];
+                const float wk[4] = {__uint_as_float(r0.x), __uint_as_float(r0.y), __uint_as_float(r0.z), __uint_as_float(r0.w)};
+                float ax = 0.f, ay = 0.f, az = 0.f;
 #pragma unroll
-                for (int s = 0; s < 4; ++s) {
-                    const uint4 r0 = r[2 * s], r1 = r[2 * s + 1];
-                    const uint32_t ctl = r1.y;
-                    if (ctl & 15u) {   // warp-uniform: some of the four register sets change joint
-#pragma unroll
-                        for (int k = 0; k < 4; ++k)
-                            if (ctl & (1u << k)) {
-                                const uint32_t col = 12u * ((ctl >> (4 + 5 * k)) & 31u);
-                                tmem_ld4(tm_row + col, g[k]);
-                                tmem_ld4(tm_row + col + 4, g[k] + 4);
-                                tmem_ld4(tm_row + col + 8, g[k] + 8);
-                            }
-                        tc_wait_ld();
-                    }
-                    const float x = xyz[3 * s], y = xyz[3 * s + 1], z = xyz[3 * s + 2];
-                    const float wk[4] = {__uint_as_float(r0.x), __uint_as_float(r0.y), __uint_as_float(r0.z), __uint_as_float(r0.w)};
-                    float ax = 0.f, ay = 0.f, az = 0.f;
-#pragma unroll
-                    for (int k = 0; k < 4; ++k) {   // column-major 3 x 4 [R | t]
-                        const float tx = fmaf(g[k][0], x, fmaf(g[k][3], y, fmaf(g[k][6], z, g[k][9])));
-                        const float ty = fmaf(g[k][1], x, fmaf(g[k][4], y, fmaf(g[k][7], z, g[k][10])));
-                        const float tz = fmaf(g[k][2], x, fmaf(g[k][5], y, fmaf(g[k][8], z, g[k][11])));
-                        ax = fmaf(wk[k], tx, ax);
-                        ay = fmaf(wk[k], ty, ay);
-                        az = fmaf(wk[k], tz, az);
-                    }
-                    float* so = orow + r1.x;
-                    so[0] = ax; so[1] = ay; so[2] = az;
+                for (int k = 0; k < 4; ++k) {   // column-major 3 x 4 [R | t]
+                    const float tx = fmaf(g[k][0], x, fmaf(g[k][3], y, fmaf(g[k][6], z, g[k][9])));
+                    const float ty = fmaf(g[k][1], x, fmaf(g[k][4], y, fmaf(g[k][7], z, g[k][10])));
+                    const float tz = fmaf(g[k][2], x, fmaf(g[k][5], y, fmaf(g[k][8], z, g[k][11])));
+                    ax = fmaf(wk[k], tx, ax);
+                    ay = fmaf(wk[k], ty, ay);
+                    az = fmaf(wk[k], tz, az);
                 }
+                float* so = orow + r1.x;
+                so[0] = ax; so[1] = ay; so[2] = az;
+                r0 = n0; r1 = n1;
             }
             __syncwarp();
             if (lane == 0) bar_arrive(&S.stage_free[st]);      // records read: the stage may be refilled
 
             if (m % 3 == 2) {   // a sort tile is complete: rows of 3 x 96 consecutive floats per body
-                named_bar(1 + q, 64);
+                named_bar(1 + q, 32 * TC_WPQ);
+                constexpr int RPW = 32 / TC_WPQ;   // rows per warp
                 const int base_v = (t_begin + m / 3) * TC_T;
                 const int nfl = 3 * min(TC_T, V - base_v);
-                const int rows = min(16, B - (b0 + 32 * q + 16 * h));   // bodies of this warp's half of the quadrant that exist
-                float* dst = cloud + ((size_t)(b0 + 32 * q + 16 * h) * V + base_v) * 3 + lane;
-                const float* src = &S.out[q][16 * h * TC_SROW + lane];
+                const int rows = min(RPW, B - (b0 + 32 * q + RPW * h));   // bodies of this warp's share of the quadrant that exist
+                float* dst = cloud + ((size_t)(b0 + 32 * q + RPW * h) * V + base_v) * 3 + lane;
+                const float* src = &S.out[q][RPW * h * TC_SROW + lane];
                 if (nfl == 3 * TC_T) {
                     for (int row = 0; row < rows; ++row, dst += (size_t)V * 3, src += TC_SROW) {
                         float v[9];
@@ -291,13 +297,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
                     for (int row = 0; row < rows; ++row, dst += (size_t)V * 3, src += TC_SROW)
                         for (int e = lane; e < nfl; e += 32) dst[e - lane] = src[e - lane];
                 }
-                named_bar(1 + q, 64);
+                named_bar(1 + q, 32 * TC_WPQ);
             }
         }
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 9) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tm), "r"(512));
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tm), "r"(512));
 }
 
 inline float tf32_round_host(float x) {   // round to 10 explicit mantissa bits (ties away); the low 13 bits end up zero
@@ -343,9 +349,10 @@ int build_tc_tables(b3d_model& m, const std::vector<double>& vert, const std::ve
         for (int i = 0; i < TC_T; ++i) order[i] = i;
         std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return vs[a].key < vs[b].key; });
 
-        for (int h = 0; h < 2; ++h) {
-            // the half's vertices, grouped by joint set, groups ordered greedily by the number of register sets to re-read
-            std::vector<int> idx(order.begin() + 48 * h, order.begin() + 48 * h + 48);
+        constexpr int SEQ = TC_T / TC_SEQS, SPW = TC_SLOTS / TC_SEQS;   // slots per sequence in a sort tile / in an MMA tile
+        for (int h = 0; h < TC_SEQS; ++h) {
+            // the sequence's vertices, grouped by joint set, groups ordered greedily by the number of register sets to re-read
+            std::vector<int> idx(order.begin() + SEQ * h, order.begin() + SEQ * h + SEQ);
             std::vector<std::vector<int>> groups;
             for (int i : idx) {
                 if (!groups.empty() && vs[groups.back()[0]].key == vs[i].key) groups.back().push_back(i);
@@ -387,10 +394,10 @@ int build_tc_tables(b3d_model& m, const std::vector<double>& vert, const std::ve
                     if (slot == 0) f = 15u;                        // a warp starts a sort tile with nothing assumed
                     int jr[4];
                     for (int k = 0; k < 4; ++k) { jr[k] = reg[k] < 0 ? 0 : reg[k]; if (reg[k] < 0 && slot == 0) reg[k] = 0; }
-                    const int mt = slot / 16, s = slot % 16;
+                    const int mt = slot / SPW, s = slot % SPW;
                     unsigned char* bl = &blob[((size_t)t * 3 + mt) * TC_BLOB_BYTES];
                     float* oper = reinterpret_cast<float*>(bl);
-                    uint32_t* rec = reinterpret_cast<uint32_t*>(bl + TC_OPER_BYTES) + (16 * h + s) * TC_REC_WORDS;
+                    uint32_t* rec = reinterpret_cast<uint32_t*>(bl + TC_OPER_BYTES) + (SPW * h + s) * TC_REC_WORDS;
                     float wr[4] = {0.f, 0.f, 0.f, 0.f};
                     for (int a = 0; a < x.nj; ++a)
                         for (int k = 0; k < 4; ++k)
@@ -405,7 +412,7 @@ int build_tc_tables(b3d_model& m, const std::vector<double>& vert, const std::ve
                     ++slots_total;
                     if (x.v < V)
                         for (int c = 0; c < 3; ++c) {
-                            const int n = 48 * h + 3 * s + c;
+                            const int n = 3 * (SPW * h + s) + c;
                             for (int k = 0; k < NS; ++k) {
                                 const float sd = (float)vert[(3 + NS * c + k) * Vp + x.v];
                                 const float hi = tf32_round_host(sd), lo = tf32_round_host(sd - hi);
