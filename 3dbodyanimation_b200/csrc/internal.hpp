@@ -74,8 +74,8 @@ struct SortedTables {
     int32_t* joff4 = nullptr;    // [Vpad][4]  float offsets 12 * joint of the four weight slots
 };
 
-// Tables of the tensor-core LBS kernel (lbs_tc.cu): the mesh is cut into sort tiles of TC_T = 96 consecutive vertices; a sort
-// tile is three MMA tiles of 32 slots.  Per MMA tile one contiguous blob (one TMA bulk copy):
+// Tables of the tensor-core LBS kernel (lbs_tc.cu): the mesh is cut into sort tiles of TC_T = 64 consecutive vertices; a sort
+// tile is two MMA tiles of 32 slots.  Per MMA tile one contiguous blob (one TMA bulk copy):
 //   [0, 12288)      B operand of the shape blend, 96 columns (slot, coordinate) x K = 32, TF32 hi/lo split, in the canonical
 //                   K-major / no-swizzle shared-memory layout tcgen05.mma reads
 //   [12288, 13312)  32 slot records of 8 words: 4 skinning weights (aligned with the lane's 4 transform registers sets),
@@ -85,7 +85,8 @@ struct TcTables {
     int sort_tiles = 0;
     double mean_reloads = 0.0;   // joint transforms re-read from TMEM per slot (host statistic, reported by tools)
 };
-constexpr int TC_T = 96, TC_SLOTS = 32, TC_N = 96, TC_K = 32;
+constexpr int TC_T = 64, TC_SLOTS = 32, TC_N = 96, TC_K = 32;
+constexpr int TC_MPT = TC_T / TC_SLOTS;   // MMA tiles per sort tile
 constexpr int TC_SEQS = 4;   // slot sequences per sort tile = epilogue warps per TMEM lane quadrant
 constexpr int TC_OPER_BYTES = TC_N * TC_K * 4, TC_REC_WORDS = 8, TC_BLOB_BYTES = TC_OPER_BYTES + TC_SLOTS * TC_REC_WORDS * 4;
 

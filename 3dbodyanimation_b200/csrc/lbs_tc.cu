@@ -33,22 +33,29 @@ constexpr int TC_SPW = TC_SLOTS / TC_WPQ;        // slots of an MMA tile per war
 constexpr int TC_EPI_WARPS = 4 * TC_WPQ;
 constexpr int TC_THREADS = 32 * TC_EPI_WARPS;    // every warp is an epilogue warp; warp 0 / warp 1 also issue the TMA copies / the MMAs
 constexpr int TC_M = 128;
-constexpr int TC_SROW = 3 * TC_T + 1;           // 289 floats: odd stride, lane = row stores are conflict free
+constexpr int TC_SROW = 3 * TC_T + 2;           // 194 floats (see TcSmem::out)
 constexpr int TC_COL_D0 = 320, TC_COL_D1 = 416;  // accumulator buffers; columns [0, 288) hold the joint transforms
 constexpr int TC_A_SLAB = TC_M * 32, TC_B_SLAB = TC_N * 32;   // bytes per K = 8 step of the operands
 
 constexpr int TC_GROW = NJ * 12 + 4;            // 292 floats: prologue rows of joint transforms, 16 B aligned and conflict free for LDS.128
+constexpr int TC_NREC = 4;                       // ring of slot-record blocks (1 KB per MMA tile)
+constexpr int TC_NOP = 2;                        // ring of B operand tiles (12 KB per MMA tile)
+constexpr int TC_REC_BYTES = TC_BLOB_BYTES - TC_OPER_BYTES;
+constexpr int TC_COL_A = 288;                    // A operand (128 bodies x K = 32) lives in TMEM columns [288, 320)
 
 struct __align__(128) TcSmem {
-    float A[TC_M * TC_K];
-    float out[4][32 * TC_SROW];                  // the prologue lands the 128 x 288 joint transforms here (rows of TC_GROW floats,
-    unsigned char stage[TC_NST][TC_BLOB_BYTES];  //   running over into stage[0], which is not in use yet)
-    unsigned long long smem_full[TC_NST], stage_free[TC_NST], d_full[2], d_empty[2], g_full;
+    // staging rows, two buffers (sort tile parity) x four TMEM lane quadrants x 32 bodies; the row stride 194 floats = 776 B makes
+    // even rows 16 B aligned and odd rows 8 mod 16, exactly like the cloud rows of even / odd bodies (6890 * 12 B = 8 mod 16), so a
+    // row leaves as one TMA bulk store (odd bodies: 8 B head and tail by plain stores).  The prologue lands the 128 x 288 joint
+    // transforms here first (rows of TC_GROW floats).
+    float out[2][4][32 * TC_SROW];
+    unsigned char oper[TC_NOP][TC_OPER_BYTES];
+    unsigned char recs[TC_NREC][TC_REC_BYTES];
+    unsigned long long op_full[TC_NOP], op_free[TC_NOP], rec_full[TC_NREC], rec_free[TC_NREC], d_full[2], d_empty[2], g_full;
     uint32_t tmem_base;
 };
-static_assert(TC_M * TC_GROW * 4 <= (int)(sizeof(float) * 4 * 32 * TC_SROW) + TC_BLOB_BYTES, "prologue staging of the transforms");
-static_assert((sizeof(float) * (TC_M * TC_K + 4 * 32 * TC_SROW)) % 128 == 0, "stage alignment");
-static_assert(TC_BLOB_BYTES % 128 == 0, "stage alignment");
+static_assert(TC_M * TC_GROW * 4 <= (int)sizeof(float) * 2 * 4 * 32 * TC_SROW, "prologue staging of the transforms");
+static_assert((sizeof(float) * 2 * 4 * 32 * TC_SROW) % 128 == 0, "operand stage alignment");
 static_assert(sizeof(TcSmem) <= 227 * 1024, "shared memory budget");
 
 // canonical K-major, no swizzle (UMMA "interleave"): slabs of 8 k; in a slab [row group of 8][k chunk of 4][row][k]; verified
@@ -100,6 +107,17 @@ __device__ __forceinline__ void mma_tf32(uint32_t d_tmem, uint64_t da, uint64_t 
         "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(d_tmem), "l"(da), "l"(db), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// A operand from TMEM (row = lane, one column per K element), B through a shared-memory descriptor
+__device__ __forceinline__ void mma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t db, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(d_tmem), "r"(a_tmem), "l"(db), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// TMA bulk store shared -> global (both 16 B aligned, bytes % 16 == 0), tracked by the thread's bulk async-group
+__device__ __forceinline__ void bulk_s2g(void* dst, const void* src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(s_u32(src)), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
     asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
                  : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]), "=f"(v[8]), "=f"(v[9]),
@@ -124,7 +142,11 @@ __device__ __forceinline__ float to_tf32(float x) {
 }
 __device__ __forceinline__ void named_bar(int id, int threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory"); }
 
-__global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsigned char* __restrict__ blob, int V, int B, int sort_tiles, int splits,
+// Optional timeline (debug hook b3d_debug_tc_trace): clock64 of CTA (0, 0)'s warps at five points of every MMA tile.
+constexpr int TC_TRACE_TILES = 256, TC_TRACE_PTS = 5;
+__device__ long long g_tc_trace[TC_EPI_WARPS * TC_TRACE_TILES * TC_TRACE_PTS];
+
+__global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsigned char* __restrict__ blob, int V, int B, int sort_tiles, int splits, int bulk_rows, int trace,
                                                                      const float* __restrict__ wshape, const float* __restrict__ G,
                                                                      float* __restrict__ cloud) {
     extern __shared__ __align__(128) unsigned char tc_raw[];
@@ -133,10 +155,11 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
     const int b0 = blockIdx.y * TC_M;
     const int t_begin = (int)((long long)blockIdx.x * sort_tiles / splits);
     const int t_end = (int)((long long)(blockIdx.x + 1) * sort_tiles / splits);
-    const int nM = 3 * (t_end - t_begin);
+    const int nM = TC_MPT * (t_end - t_begin);
 
     if (tid == 0) {
-        for (int i = 0; i < TC_NST; ++i) { bar_init(&S.smem_full[i], 1); bar_init(&S.stage_free[i], 1 + TC_EPI_WARPS); }
+        for (int i = 0; i < TC_NOP; ++i) { bar_init(&S.op_full[i], 1); bar_init(&S.op_free[i], 1); }
+        for (int i = 0; i < TC_NREC; ++i) { bar_init(&S.rec_full[i], 1); bar_init(&S.rec_free[i], TC_EPI_WARPS); }
         for (int i = 0; i < 2; ++i) { bar_init(&S.d_full[i], 1); bar_init(&S.d_empty[i], TC_EPI_WARPS); }
         bar_init(&S.g_full, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -145,67 +168,69 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s_u32(&S.tmem_base)), "r"(512));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
     }
-    __syncthreads();
-    // joint transforms of the CTA's bodies: one TMA bulk copy per body row (1152 B) into padded shared rows
-    float* const gst = &S.out[0][0];
-    const int nb = min(TC_M, B - b0);
-    if (tid == 0) bar_expect_tx(&S.g_full, (uint32_t)nb * NJ * 12 * 4);
-    if (tid < nb) bulk_g2s(gst + tid * TC_GROW, G + (size_t)(b0 + tid) * (NJ * 12), NJ * 12 * 4, &S.g_full);
-    // A operand: rows = bodies, TF32 hi / hi / lo copies of the shape vector and two ones for the template columns
-    for (int i = tid; i < TC_M * NS; i += TC_THREADS) {
-        const int r = i / NS, s = i - r * NS;
-        const float w = (b0 + r < B) ? wshape[(size_t)(b0 + r) * NS + s] : 0.f;
-        const float hi = to_tf32(w), lo = to_tf32(w - hi);
-        S.A[canon_off(TC_M, r, s)] = hi;
-        S.A[canon_off(TC_M, r, NS + s)] = hi;
-        S.A[canon_off(TC_M, r, 2 * NS + s)] = lo;
-    }
-    for (int r = tid; r < TC_M; r += TC_THREADS) {
-        S.A[canon_off(TC_M, r, 30)] = 1.f;
-        S.A[canon_off(TC_M, r, 31)] = 1.f;
-    }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes of A -> visible to the tensor core
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tm = S.tmem_base;
-
+    const int q = warp & 3, h = warp >> 2;
+    const uint32_t tm_row = tm + ((uint32_t)(32 * q) << 16);
+    // joint transforms of the CTA's bodies: one TMA bulk copy per body row (1152 B) into padded shared rows
+    float* const gst = &S.out[0][0][0];
+    const int nb = min(TC_M, B - b0);
+    if (tid == 0) bar_expect_tx(&S.g_full, (uint32_t)nb * NJ * 12 * 4);
+    if (tid < nb) bulk_g2s(gst + tid * TC_GROW, G + (size_t)(b0 + tid) * (NJ * 12), NJ * 12 * 4, &S.g_full);
+    // A operand -> TMEM columns [288, 320), row = body = lane: TF32 hi / hi / lo copies of the shape vector and two ones for the
+    // template columns (k 0-9 w_hi, 10-19 w_hi, 20-29 w_lo, 30-31 one).  tcgen05.mma reads it from TMEM (tools/tc_probe.cu).
+    if (h == 0) {
+        const int body = b0 + 32 * q + lane;
+        float a[TC_K];
+#pragma unroll
+        for (int s = 0; s < NS; ++s) {
+            const float w = body < B ? wshape[(size_t)body * NS + s] : 0.f;
+            const float hi = to_tf32(w);
+            a[s] = hi; a[NS + s] = hi; a[2 * NS + s] = to_tf32(w - hi);
+        }
+        a[30] = 1.f; a[31] = 1.f;
+#pragma unroll
+        for (int c = 0; c < TC_K; c += 4) tmem_st4(tm_row + TC_COL_A + c, make_float4(a[c], a[c + 1], a[c + 2], a[c + 3]));
+    }
     // shared rows -> TMEM columns [0, 288), body = lane (rows beyond the batch hold whatever the buffer held: never stored)
     {
-        const int q = warp & 3, h = warp >> 2;
         constexpr int CPW = NJ * 12 / TC_WPQ;   // columns per warp
         bar_wait(&S.g_full, 0);
         const float4* src = reinterpret_cast<const float4*>(gst + (32 * q + lane) * TC_GROW + CPW * h);
-        const uint32_t taddr = tm + ((uint32_t)(32 * q) << 16) + (uint32_t)(CPW * h);
 #pragma unroll
-        for (int c = 0; c < CPW / 4; ++c) tmem_st4(taddr + 4 * c, src[c]);
+        for (int c = 0; c < CPW / 4; ++c) tmem_st4(tm_row + CPW * h + 4 * c, src[c]);
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
     }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // staging rows were read through the generic proxy; TMA writes stage[0] next
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // staging rows were read through the generic proxy
     tc_fence_before();
-    __syncthreads();   // also: the staging rows may now be overwritten (TMA producer, epilogue stores)
+    __syncthreads();   // also: the staging rows may now be overwritten
     tc_fence_after();
 
-    const unsigned char* const blob0 = blob + (size_t)(3 * t_begin) * TC_BLOB_BYTES;
-    auto issue_tma = [&](int m) {   // one thread: the blob of MMA tile m -> its stage, once everybody is done with the stage's last tile
-        const int st = m % TC_NST, u = m / TC_NST;
-        bar_wait(&S.stage_free[st], (uint32_t)((u & 1) ^ 1));
-        bar_expect_tx(&S.smem_full[st], TC_BLOB_BYTES);
-        bulk_g2s(S.stage[st], blob0 + (size_t)m * TC_BLOB_BYTES, TC_BLOB_BYTES, &S.smem_full[st]);
+    const unsigned char* const blob0 = blob + (size_t)(TC_MPT * t_begin) * TC_BLOB_BYTES;
+    auto issue_tma = [&](int m) {   // one thread: operand and slot records of MMA tile m -> their rings
+        const int so = m % TC_NOP, uo = m / TC_NOP, sr = m % TC_NREC, ur = m / TC_NREC;
+        bar_wait(&S.op_free[so], (uint32_t)((uo & 1) ^ 1));        // the MMA that read this operand stage is complete
+        bar_expect_tx(&S.op_full[so], TC_OPER_BYTES);
+        bulk_g2s(S.oper[so], blob0 + (size_t)m * TC_BLOB_BYTES, TC_OPER_BYTES, &S.op_full[so]);
+        bar_wait(&S.rec_free[sr], (uint32_t)((ur & 1) ^ 1));       // every warp is done with this record block's last tile
+        bar_expect_tx(&S.rec_full[sr], TC_REC_BYTES);
+        bulk_g2s(S.recs[sr], blob0 + (size_t)m * TC_BLOB_BYTES + TC_OPER_BYTES, TC_REC_BYTES, &S.rec_full[sr]);
     };
     auto issue_mma = [&](int m) {   // one thread: shape blend of MMA tile m into accumulator buffer m & 1
         // instruction descriptor: D = F32, A = B = TF32, both K-major, N = 96, M = 128
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_N >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);
-        const int st = m % TC_NST, u = m / TC_NST, buf = m & 1, r = m >> 1;
-        bar_wait(&S.smem_full[st], (uint32_t)(u & 1));
+        const int so = m % TC_NOP, uo = m / TC_NOP, buf = m & 1, r = m >> 1;
+        bar_wait(&S.op_full[so], (uint32_t)(uo & 1));
         bar_wait(&S.d_empty[buf], (uint32_t)((r & 1) ^ 1));
         tc_fence_after();
-        const uint32_t a_addr = s_u32(S.A), b_addr = s_u32(S.stage[st]);
+        const uint32_t b_addr = s_u32(S.oper[so]);
         const uint32_t d_tmem = tm + (uint32_t)(buf ? TC_COL_D1 : TC_COL_D0);
 #pragma unroll
         for (int s = 0; s < TC_K / 8; ++s)
-            mma_tf32(d_tmem, smem_desc(a_addr + s * TC_A_SLAB), smem_desc(b_addr + s * TC_B_SLAB), idesc, s > 0 ? 1u : 0u);
-        tc_commit(&S.stage_free[st]);
+            mma_tf32_ts(d_tmem, tm + (uint32_t)(TC_COL_A + 8 * s), smem_desc(b_addr + s * TC_B_SLAB), idesc, s > 0 ? 1u : 0u);
+        tc_commit(&S.op_free[so]);
         tc_commit(&S.d_full[buf]);
     };
     if (warp == 0 && lane == 0) {
@@ -214,23 +239,28 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
     }
     if (warp == 1 && lane == 0) issue_mma(0);
     {
-        const int q = warp & 3, h = warp >> 2;
-        const uint32_t tm_row = tm + ((uint32_t)(32 * q) << 16);
-        float* const orow = &S.out[q][lane * TC_SROW];
         float g[4][12];
 #pragma unroll
         for (int k = 0; k < 4; ++k)
 #pragma unroll
             for (int e = 0; e < 12; ++e) g[k][e] = 0.f;
+        const bool tr = trace && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0;
+        auto stamp = [&](int m, int k) { if (tr && m < TC_TRACE_TILES) g_tc_trace[(warp * TC_TRACE_TILES + m) * TC_TRACE_PTS + k] = clock64(); };
+        constexpr int RPW = 32 / TC_WPQ;   // staging rows a warp sends off
+        bool pending_store = false;        // this warp's lanes have a bulk-store group in flight
         for (int m = 0; m < nM; ++m) {
+            stamp(m, 0);
             // service duties first: dependencies only point at earlier tiles, so a blocked issuer never blocks what it waits for
             if (warp == 0 && lane == 0 && m + 2 < nM) issue_tma(m + 2);
             if (warp == 1 && lane == 0 && m + 1 < nM) issue_mma(m + 1);
             __syncwarp();
-            const int st = m % TC_NST, u = m / TC_NST, buf = m & 1, r = m >> 1;
-            bar_wait(&S.smem_full[st], (uint32_t)(u & 1));     // slot records of this tile are in shared memory
+            const int sr = m % TC_NREC, ur = m / TC_NREC, buf = m & 1, r = m >> 1;
+            const int st_tile = m / TC_MPT;                    // sort tile (local); its staging buffer alternates
+            float* const orow = &S.out[st_tile & 1][q][lane * TC_SROW];
+            bar_wait(&S.rec_full[sr], (uint32_t)(ur & 1));     // slot records of this tile are in shared memory
             bar_wait(&S.d_full[buf], (uint32_t)(r & 1));       // and its accumulators are complete
             tc_fence_after();
+            stamp(m, 1);
             float xyz[3 * TC_SPW];   // accumulators of this warp's slots
             const uint32_t d_addr = tm_row + (uint32_t)(buf ? TC_COL_D1 : TC_COL_D0) + (uint32_t)(3 * TC_SPW * h);
 #pragma unroll
@@ -239,8 +269,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
             tc_fence_before();
             __syncwarp();
             if (lane == 0) bar_arrive(&S.d_empty[buf]);        // the accumulator buffer may be overwritten
+            stamp(m, 2);
 
-            const uint4* rec = reinterpret_cast<const uint4*>(S.stage[st] + TC_OPER_BYTES) + 2 * (TC_SPW * h);
+            const uint4* rec = reinterpret_cast<const uint4*>(S.recs[sr]) + 2 * (TC_SPW * h);
             uint4 r0 = rec[0], r1 = rec[1];
 #pragma unroll
             for (int s = 0; s < TC_SPW; ++s) {
@@ -275,31 +306,44 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
                 r0 = n0; r1 = n1;
             }
             __syncwarp();
-            if (lane == 0) bar_arrive(&S.stage_free[st]);      // records read: the stage may be refilled
+            if (lane == 0) bar_arrive(&S.rec_free[sr]);        // records read: the block may be refilled
+            stamp(m, 3);
 
-            if (m % 3 == 2) {   // a sort tile is complete: rows of 3 x 96 consecutive floats per body
+            if (m % TC_MPT == TC_MPT - 1) {   // a sort tile is complete: rows of 3 x 64 consecutive floats per body leave asynchronously
+                // the rows this warp sent off one sort tile ago came from the OTHER buffer, which the quadrant writes next: their
+                // shared-memory reads must be over before anybody passes the barrier below
+                if (pending_store) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // this tile's staging stores -> visible to the bulk copies
                 named_bar(1 + q, 32 * TC_WPQ);
-                constexpr int RPW = 32 / TC_WPQ;   // rows per warp
-                const int base_v = (t_begin + m / 3) * TC_T;
-                const int nfl = 3 * min(TC_T, V - base_v);
-                const int rows = min(RPW, B - (b0 + 32 * q + RPW * h));   // bodies of this warp's share of the quadrant that exist
-                float* dst = cloud + ((size_t)(b0 + 32 * q + RPW * h) * V + base_v) * 3 + lane;
-                const float* src = &S.out[q][RPW * h * TC_SROW + lane];
-                if (nfl == 3 * TC_T) {
-                    for (int row = 0; row < rows; ++row, dst += (size_t)V * 3, src += TC_SROW) {
-                        float v[9];
-#pragma unroll
-                        for (int i = 0; i < 9; ++i) v[i] = src[32 * i];
-#pragma unroll
-                        for (int i = 0; i < 9; ++i) dst[32 * i] = v[i];
+                const int base_v = (t_begin + st_tile) * TC_T;
+                const int nv = min(TC_T, V - base_v);
+                const int row0 = RPW * h;                                   // this warp's rows of the quadrant
+                const int rows = min(RPW, B - (b0 + 32 * q + row0));
+                const float* srow = &S.out[st_tile & 1][q][row0 * TC_SROW];
+                float* drow = cloud + ((size_t)(b0 + 32 * q + row0) * V + base_v) * 3;
+                if (nv == TC_T && bulk_rows) {
+                    if (lane < rows) {
+                        const float* sp = srow + lane * TC_SROW;
+                        float* dp = drow + (size_t)lane * V * 3;
+                        if ((reinterpret_cast<uintptr_t>(dp) & 15) == 0) {
+                            bulk_s2g(dp, sp, 3 * TC_T * 4);
+                        } else {   // 8 mod 16, as is the shared row: head and tail pairs by hand, the 16 B aligned middle in bulk
+                            *reinterpret_cast<float2*>(dp) = *reinterpret_cast<const float2*>(sp);
+                            *reinterpret_cast<float2*>(dp + 3 * TC_T - 2) = *reinterpret_cast<const float2*>(sp + 3 * TC_T - 2);
+                            bulk_s2g(dp + 2, sp + 2, 3 * TC_T * 4 - 16);
+                        }
                     }
-                } else {
-                    for (int row = 0; row < rows; ++row, dst += (size_t)V * 3, src += TC_SROW)
-                        for (int e = lane; e < nfl; e += 32) dst[e - lane] = src[e - lane];
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    pending_store = true;
+                } else {   // the mesh's last, partial sort tile: plain stores (the buffer is not reused afterwards)
+                    const int nfl = 3 * nv;
+                    for (int row = 0; row < rows; ++row)
+                        for (int e = lane; e < nfl; e += 32) drow[(size_t)row * V * 3 + e] = srow[row * TC_SROW + e];
                 }
-                named_bar(1 + q, 32 * TC_WPQ);
             }
+            stamp(m, 4);
         }
+        if (pending_store) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     }
     tc_fence_before();
     __syncthreads();
@@ -322,7 +366,7 @@ int build_tc_tables(b3d_model& m, const std::vector<double>& vert, const std::ve
     const size_t Vp = (size_t)m.Vpad;
     const int V = m.V;
     const int tiles = (V + TC_T - 1) / TC_T;
-    std::vector<unsigned char> blob((size_t)tiles * 3 * TC_BLOB_BYTES, 0);
+    std::vector<unsigned char> blob((size_t)tiles * TC_MPT * TC_BLOB_BYTES, 0);
     long long reloads = 0, slots_total = 0;
 
     struct Vtx { int v; int nj; int j[4]; float w[4]; uint64_t key; };
@@ -395,7 +439,7 @@ int build_tc_tables(b3d_model& m, const std::vector<double>& vert, const std::ve
                     int jr[4];
                     for (int k = 0; k < 4; ++k) { jr[k] = reg[k] < 0 ? 0 : reg[k]; if (reg[k] < 0 && slot == 0) reg[k] = 0; }
                     const int mt = slot / SPW, s = slot % SPW;
-                    unsigned char* bl = &blob[((size_t)t * 3 + mt) * TC_BLOB_BYTES];
+                    unsigned char* bl = &blob[((size_t)t * TC_MPT + mt) * TC_BLOB_BYTES];
                     float* oper = reinterpret_cast<float*>(bl);
                     uint32_t* rec = reinterpret_cast<uint32_t*>(bl + TC_OPER_BYTES) + (SPW * h + s) * TC_REC_WORDS;
                     float wr[4] = {0.f, 0.f, 0.f, 0.f};
@@ -436,6 +480,8 @@ int build_tc_tables(b3d_model& m, const std::vector<double>& vert, const std::ve
     return B3D_OK;
 }
 
+static std::atomic<int> g_tc_trace_on{0};
+
 int launch_lbs_tc(const b3d_model* m, int B, const float* wshape, const float* G, float* cloud, cudaStream_t st) {
     static bool attr_set = false;
     if (!attr_set) {
@@ -457,8 +503,21 @@ int launch_lbs_tc(const b3d_model* m, int B, const float* wshape, const float* G
         if (cost < best_cost * 0.999) { best_cost = cost; best_s = s; }
     }
     if (forced > 0) best_s = std::min(forced, tiles);
-    smpl_lbs_tc_kernel<<<dim3(best_s, groups), TC_THREADS, sizeof(TcSmem), st>>>(m->tc.blob, m->V, B, tiles, best_s, wshape, G, cloud);
+    // rows leave as TMA bulk stores when row r of the cloud is 16 B aligned for even r and 8 mod 16 for odd r (true for V = 6890 and
+    // a 16 B aligned cloud: 6890 * 12 = 8 mod 16), which is how the staging rows are laid out; otherwise plain stores
+    const int bulk_rows = ((reinterpret_cast<uintptr_t>(cloud) & 15) == 0 && ((size_t)m->V * 12) % 16 == 8) ? 1 : 0;
+    const int trace = g_tc_trace_on.load();
+    smpl_lbs_tc_kernel<<<dim3(best_s, groups), TC_THREADS, sizeof(TcSmem), st>>>(m->tc.blob, m->V, B, tiles, best_s, bulk_rows, trace, wshape, G, cloud);
     return B3D_OK;
 }
 
 }  // namespace b3d
+
+extern "C" {
+// debug hooks (tools/prof.py tctrace): switch the timeline on / read it back as [warp][tile][point] clock64 values
+int b3d_debug_tc_trace(int on) { b3d::g_tc_trace_on.store(on); return 0; }
+int b3d_debug_tc_trace_read(long long* out, int n) {
+    const size_t bytes = sizeof(long long) * (size_t)std::min(n, b3d::TC_EPI_WARPS * b3d::TC_TRACE_TILES * b3d::TC_TRACE_PTS);
+    return cudaMemcpyFromSymbol(out, b3d::g_tc_trace, bytes) == cudaSuccess ? 0 : 2;
+}
+}

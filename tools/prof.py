@@ -126,3 +126,31 @@ def phases(n=148, mode="C2"):
 
 if __name__ == "__main__" and sys.argv[1] == "phases":
     phases(int(sys.argv[2]) if len(sys.argv) > 2 else 148, sys.argv[3] if len(sys.argv) > 3 else "C2")
+
+
+def tctrace(B=16384):
+    """Timeline of the tensor-core LBS kernel's CTA (0, 0): per warp and MMA tile, cycles spent in each phase."""
+    lib.b3d_debug_tc_trace(1)
+    forward(B, "f32", reps=1, lbs="tc")
+    lib.b3d_debug_tc_trace(0)
+    W, T, K = 16, 256, 5
+    buf = (C.c_longlong * (W * T * K))()
+    lib.b3d_debug_tc_trace_read(buf, W * T * K)
+    a = np.array(buf[:], dtype=np.int64).reshape(W, T, K)
+    nt = int((a[0, :, 0] > 0).sum())
+    a = a[:, :nt]
+    t0 = a[:, 0, 0].min()
+    print("tiles traced", nt, "total cycles", int(a[:, nt - 1, 4].max() - t0))
+    names = ["service+barrier wait", "D load + release", "slot loop", "copy-out (every 3rd tile)"]
+    d = np.diff(a, axis=2).astype(np.float64)       # W x nt x 4
+    for k in range(4):
+        print(f"{names[k]:28s} mean {d[:, :, k].mean():9.0f}  per-warp means " + " ".join(f"{x:6.0f}" for x in d[:, :, k].mean(axis=1)))
+    per_tile = (a[:, 1:, 0] - a[:, :-1, 0]).astype(np.float64)
+    print("tile period mean", per_tile.mean(), "; by tile % 3:", [float(per_tile[:, i::3].mean()) for i in range(3)])
+    print("start skew of warps at tile 12 (cycles after the first):", (a[:, 12, 0] - a[:, 12, 0].min()).tolist())
+    co = d[:, 2::3, 3]
+    print("copy-out cycles (tiles 2, 5, ...): mean", co.mean(), "min", co.min(), "max", co.max())
+
+
+if __name__ == "__main__" and sys.argv[1] == "tctrace":
+    tctrace(int(sys.argv[2]) if len(sys.argv) > 2 else 16384)

@@ -29,6 +29,7 @@ __device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes
     return d;                                            // base offset 0, layout type 0 = SWIZZLE_NONE
 }
 
+template <bool A_TMEM>
 __global__ void __launch_bounds__(128, 1) probe(const float* __restrict__ A, const float* __restrict__ B, float* __restrict__ D, uint32_t lbo, uint32_t sbo) {
     __shared__ __align__(128) float sA[M * K];
     __shared__ __align__(128) float sB[N * K];
@@ -50,6 +51,16 @@ __global__ void __launch_bounds__(128, 1) probe(const float* __restrict__ A, con
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tm = tmem_base;
+    if (A_TMEM) {   // A[row = lane][k] -> TMEM columns [192, 192 + K) of the thread's lane
+        const uint32_t ta = tm + ((uint32_t)(warp * 32) << 16) + 192u;
+        for (int k = 0; k < K; k += 4)
+            asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(ta + k), "f"(A[tid * K + k]), "f"(A[tid * K + k + 1]),
+                         "f"(A[tid * K + k + 2]), "f"(A[tid * K + k + 3]) : "memory");
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    }
     if (tid == 0) {
         // instruction descriptor: D = F32 (bits 4-5 = 1), A = B = TF32 (bits 7-9, 10-12 = 2), K-major both, N >> 3 at 17, M >> 4 at 24
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
@@ -57,6 +68,12 @@ __global__ void __launch_bounds__(128, 1) probe(const float* __restrict__ A, con
             const uint64_t da = make_desc(smem_u32(sA) + s * M * 32, lbo, sbo);
             const uint64_t db = make_desc(smem_u32(sB) + s * N * 32, lbo, sbo);
             const uint32_t acc = s > 0 ? 1u : 0u;
+            if (A_TMEM)
+                asm volatile(
+                    "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                    "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tm), "r"(tm + 192u + (uint32_t)(8 * s)), "l"(db), "r"(idesc), "r"(acc)
+                    : "memory");
+            else
             asm volatile(
                 "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
                 "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tm), "l"(da), "l"(db), "r"(idesc), "r"(acc)
@@ -107,7 +124,8 @@ int main() {
     const uint32_t variants[2][2] = {{128, 256}, {256, 128}};      // {LBO, SBO}: the first is what the layout above means
     for (int v = 0; v < 2; ++v) {
         cudaMemset(dD, 0xff, D.size() * 4);
-        probe<<<1, 128>>>(dA, dB, dD, variants[v][0], variants[v][1]);
+        if (v == 0) probe<false><<<1, 128>>>(dA, dB, dD, variants[v][0], variants[v][1]);
+        else probe<true><<<1, 128>>>(dA, dB, dD, variants[0][0], variants[0][1]);   // variant 1: A operand read from TMEM
         cudaError_t e = cudaDeviceSynchronize();
         if (e != cudaSuccess) { printf("TC_PROBE CUDA ERROR: %s\n", cudaGetErrorString(e)); return 2; }
         cudaMemcpy(D.data(), dD, D.size() * 4, cudaMemcpyDeviceToHost);
@@ -115,7 +133,7 @@ int main() {
         for (int i = 0; i < M * N; ++i) { const double d = fabs((double)D[i] - R[i]); if (!(d <= 1e-4)) ++bad; if (d > maxerr) maxerr = d; }
         printf("TC_PROBE LBO=%u SBO=%u: max|D - ref| = %.3e, mismatches %d of %d; D[0][0..3] = %g %g %g %g ref %g %g %g %g; D[127][191] = %g ref %g\n",
                variants[v][0], variants[v][1], maxerr, bad, M * N, D[0], D[1], D[2], D[3], R[0], R[1], R[2], R[3], D[127 * N + 191], R[127 * N + 191]);
-        if (bad == 0) { printf("TC_PROBE OK (variant %d)\n", v); rc = 0; }
+        if (bad == 0) { printf("TC_PROBE OK (variant %d: %s)\n", v, v ? "A from TMEM" : "A from shared memory"); if (v == 0) rc = 0; }
     }
     return rc;
 
