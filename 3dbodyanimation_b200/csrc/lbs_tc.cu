@@ -143,7 +143,7 @@ __device__ __forceinline__ float to_tf32(float x) {
 __device__ __forceinline__ void named_bar(int id, int threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory"); }
 
 // Optional timeline (debug hook b3d_debug_tc_trace): clock64 of CTA (0, 0)'s warps at five points of every MMA tile.
-constexpr int TC_TRACE_TILES = 256, TC_TRACE_PTS = 5;
+constexpr int TC_TRACE_TILES = 256, TC_TRACE_PTS = 8;
 __device__ long long g_tc_trace[TC_EPI_WARPS * TC_TRACE_TILES * TC_TRACE_PTS];
 
 __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsigned char* __restrict__ blob, int V, int B, int sort_tiles, int splits, int bulk_rows, int trace,
@@ -208,6 +208,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
     __syncthreads();   // also: the staging rows may now be overwritten
     tc_fence_after();
 
+    const bool tr = trace && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0;
+    auto stamp = [&](int m, int k) { if (tr && m < TC_TRACE_TILES) g_tc_trace[(warp * TC_TRACE_TILES + m) * TC_TRACE_PTS + k] = clock64(); };
     const unsigned char* const blob0 = blob + (size_t)(TC_MPT * t_begin) * TC_BLOB_BYTES;
     auto issue_tma = [&](int m) {   // one thread: operand and slot records of MMA tile m -> their rings
         const int so = m % TC_NOP, uo = m / TC_NOP, sr = m % TC_NREC, ur = m / TC_NREC;
@@ -225,34 +227,37 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
         bar_wait(&S.op_full[so], (uint32_t)(uo & 1));
         bar_wait(&S.d_empty[buf], (uint32_t)((r & 1) ^ 1));
         tc_fence_after();
+        stamp(m - 1, 5);
         const uint32_t b_addr = s_u32(S.oper[so]);
         const uint32_t d_tmem = tm + (uint32_t)(buf ? TC_COL_D1 : TC_COL_D0);
 #pragma unroll
         for (int s = 0; s < TC_K / 8; ++s)
             mma_tf32_ts(d_tmem, tm + (uint32_t)(TC_COL_A + 8 * s), smem_desc(b_addr + s * TC_B_SLAB), idesc, s > 0 ? 1u : 0u);
+        stamp(m - 1, 6);
         tc_commit(&S.op_free[so]);
         tc_commit(&S.d_full[buf]);
+        stamp(m - 1, 7);
     };
-    if (warp == 0 && lane == 0) {
+    if (warp == 4 && lane == 0) {
         issue_tma(0);
         if (nM > 1) issue_tma(1);
     }
-    if (warp == 1 && lane == 0) issue_mma(0);
+    if (warp == 0 && lane == 0) issue_mma(0);
     {
         float g[4][12];
 #pragma unroll
         for (int k = 0; k < 4; ++k)
 #pragma unroll
             for (int e = 0; e < 12; ++e) g[k][e] = 0.f;
-        const bool tr = trace && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0;
-        auto stamp = [&](int m, int k) { if (tr && m < TC_TRACE_TILES) g_tc_trace[(warp * TC_TRACE_TILES + m) * TC_TRACE_PTS + k] = clock64(); };
         constexpr int RPW = 32 / TC_WPQ;   // staging rows a warp sends off
         bool pending_store = false;        // this warp's lanes have a bulk-store group in flight
         for (int m = 0; m < nM; ++m) {
             stamp(m, 0);
             // service duties first: dependencies only point at earlier tiles, so a blocked issuer never blocks what it waits for
-            if (warp == 0 && lane == 0 && m + 2 < nM) issue_tma(m + 2);
-            if (warp == 1 && lane == 0 && m + 1 < nM) issue_mma(m + 1);
+            // (issuing four MMAs and two commits costs the issuing warp ~700 cycles of its own time: the duty rotates over the
+            // quadrants, tile by tile, so that no quadrant is always the one the others wait for)
+            if (lane == 0 && m + 2 < nM && warp == 4 + ((m + 2) & 3)) issue_tma(m + 2);
+            if (lane == 0 && m + 1 < nM && warp == ((m + 1) & 3)) issue_mma(m + 1);
             __syncwarp();
             const int sr = m % TC_NREC, ur = m / TC_NREC, buf = m & 1, r = m >> 1;
             const int st_tile = m / TC_MPT;                    // sort tile (local); its staging buffer alternates
