@@ -31,7 +31,8 @@ constexpr int TC_NST = 4;
 constexpr int TC_WPQ = TC_SEQS;                  // epilogue warps per TMEM lane quadrant (= slot sequences per sort tile)
 constexpr int TC_SPW = TC_SLOTS / TC_WPQ;        // slots of an MMA tile per warp
 constexpr int TC_EPI_WARPS = 4 * TC_WPQ;
-constexpr int TC_THREADS = 32 * TC_EPI_WARPS;    // every warp is an epilogue warp; warp 0 / warp 1 also issue the TMA copies / the MMAs
+constexpr int TC_THREADS = 32 * (TC_EPI_WARPS + 4);   // + a service warpgroup: warp 16 issues the TMA copies, warp 17 the MMAs
+constexpr int TC_EPI_THREADS = 32 * TC_EPI_WARPS;
 constexpr int TC_M = 128;
 constexpr int TC_SROW = 3 * TC_T + 2;           // 194 floats (see TcSmem::out)
 constexpr int TC_COL_D0 = 320, TC_COL_D1 = 416;  // accumulator buffers; columns [0, 288) hold the joint transforms
@@ -144,7 +145,7 @@ __device__ __forceinline__ void named_bar(int id, int threads) { asm volatile("b
 
 // Optional timeline (debug hook b3d_debug_tc_trace): clock64 of CTA (0, 0)'s warps at five points of every MMA tile.
 constexpr int TC_TRACE_TILES = 256, TC_TRACE_PTS = 8;
-__device__ long long g_tc_trace[TC_EPI_WARPS * TC_TRACE_TILES * TC_TRACE_PTS];
+__device__ long long g_tc_trace[(TC_EPI_WARPS + 4) * TC_TRACE_TILES * TC_TRACE_PTS];
 
 __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsigned char* __restrict__ blob, int V, int B, int sort_tiles, int splits, int bulk_rows, int trace,
                                                                      const float* __restrict__ wshape, const float* __restrict__ G,
@@ -172,7 +173,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
     __syncthreads();
     tc_fence_after();
     const uint32_t tm = S.tmem_base;
-    const int q = warp & 3, h = warp >> 2;
+    const int q = warp & 3, h = warp >> 2;   // h == 4: service warpgroup
     const uint32_t tm_row = tm + ((uint32_t)(32 * q) << 16);
     // joint transforms of the CTA's bodies: one TMA bulk copy per body row (1152 B) into padded shared rows
     float* const gst = &S.out[0][0][0];
@@ -195,7 +196,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
         for (int c = 0; c < TC_K; c += 4) tmem_st4(tm_row + TC_COL_A + c, make_float4(a[c], a[c + 1], a[c + 2], a[c + 3]));
     }
     // shared rows -> TMEM columns [0, 288), body = lane (rows beyond the batch hold whatever the buffer held: never stored)
-    {
+    if (h < TC_WPQ) {
         constexpr int CPW = NJ * 12 / TC_WPQ;   // columns per warp
         bar_wait(&S.g_full, 0);
         const float4* src = reinterpret_cast<const float4*>(gst + (32 * q + lane) * TC_GROW + CPW * h);
@@ -224,26 +225,30 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
         // instruction descriptor: D = F32, A = B = TF32, both K-major, N = 96, M = 128
         const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_N >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);
         const int so = m % TC_NOP, uo = m / TC_NOP, buf = m & 1, r = m >> 1;
+        stamp(m, 0);
         bar_wait(&S.op_full[so], (uint32_t)(uo & 1));
         bar_wait(&S.d_empty[buf], (uint32_t)((r & 1) ^ 1));
         tc_fence_after();
-        stamp(m - 1, 5);
+        stamp(m, 5);
         const uint32_t b_addr = s_u32(S.oper[so]);
         const uint32_t d_tmem = tm + (uint32_t)(buf ? TC_COL_D1 : TC_COL_D0);
 #pragma unroll
         for (int s = 0; s < TC_K / 8; ++s)
             mma_tf32_ts(d_tmem, tm + (uint32_t)(TC_COL_A + 8 * s), smem_desc(b_addr + s * TC_B_SLAB), idesc, s > 0 ? 1u : 0u);
-        stamp(m - 1, 6);
+        stamp(m, 6);
         tc_commit(&S.op_free[so]);
         tc_commit(&S.d_full[buf]);
-        stamp(m - 1, 7);
+        stamp(m, 7);
     };
-    if (warp == 4 && lane == 0) {
-        issue_tma(0);
-        if (nM > 1) issue_tma(1);
-    }
-    if (warp == 0 && lane == 0) issue_mma(0);
-    {
+    if (warp >= TC_EPI_WARPS) {
+        // service warpgroup: hands most of its registers to the skinning warps, then two of its threads run the copy / MMA loops
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 24;");
+        if (warp == TC_EPI_WARPS && lane == 0)
+            for (int m = 0; m < nM; ++m) issue_tma(m);
+        if (warp == TC_EPI_WARPS + 1 && lane == 0)
+            for (int m = 0; m < nM; ++m) issue_mma(m);
+    } else {
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
         float g[4][12];
 #pragma unroll
         for (int k = 0; k < 4; ++k)
@@ -253,12 +258,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
         bool pending_store = false;        // this warp's lanes have a bulk-store group in flight
         for (int m = 0; m < nM; ++m) {
             stamp(m, 0);
-            // service duties first: dependencies only point at earlier tiles, so a blocked issuer never blocks what it waits for
-            // (issuing four MMAs and two commits costs the issuing warp ~700 cycles of its own time: the duty rotates over the
-            // quadrants, tile by tile, so that no quadrant is always the one the others wait for)
-            if (lane == 0 && m + 2 < nM && warp == 4 + ((m + 2) & 3)) issue_tma(m + 2);
-            if (lane == 0 && m + 1 < nM && warp == ((m + 1) & 3)) issue_mma(m + 1);
-            __syncwarp();
             const int sr = m % TC_NREC, ur = m / TC_NREC, buf = m & 1, r = m >> 1;
             const int st_tile = m / TC_MPT;                    // sort tile (local); its staging buffer alternates
             float* const orow = &S.out[st_tile & 1][q][lane * TC_SROW];
@@ -522,7 +521,7 @@ extern "C" {
 // debug hooks (tools/prof.py tctrace): switch the timeline on / read it back as [warp][tile][point] clock64 values
 int b3d_debug_tc_trace(int on) { b3d::g_tc_trace_on.store(on); return 0; }
 int b3d_debug_tc_trace_read(long long* out, int n) {
-    const size_t bytes = sizeof(long long) * (size_t)std::min(n, b3d::TC_EPI_WARPS * b3d::TC_TRACE_TILES * b3d::TC_TRACE_PTS);
+    const size_t bytes = sizeof(long long) * (size_t)std::min(n, (b3d::TC_EPI_WARPS + 4) * b3d::TC_TRACE_TILES * b3d::TC_TRACE_PTS);
     return cudaMemcpyFromSymbol(out, b3d::g_tc_trace, bytes) == cudaSuccess ? 0 : 2;
 }
 }

@@ -133,7 +133,7 @@ def tctrace(B=16384):
     lib.b3d_debug_tc_trace(1)
     forward(B, "f32", reps=1, lbs="tc")
     lib.b3d_debug_tc_trace(0)
-    W, T, K = 16, 256, 8
+    W, T, K = 20, 256, 8
     buf = (C.c_longlong * (W * T * K))()
     lib.b3d_debug_tc_trace_read(buf, W * T * K)
     a = np.array(buf[:], dtype=np.int64).reshape(W, T, K)
@@ -142,8 +142,9 @@ def tctrace(B=16384):
     t0 = a[:, 0, 0].min()
     print("tiles traced", nt, "total cycles", int(a[:, nt - 1, 4].max() - t0))
     names = ["service+barrier wait", "D load + release", "slot loop", "copy-out (every 3rd tile)"]
-    mm = a[1, 1:nt - 1]
-    print("MMA issuer (warp 1), cycles after the tile's top: waits over %.0f, 4 MMAs issued %.0f, 2 commits issued %.0f"
+    mm = a[17, 1:nt - 1]
+    a = a[:16]
+    print("MMA issuer (warp 17), cycles after it turns to the tile: waits over %.0f, 4 MMAs issued %.0f, 2 commits issued %.0f"
           % tuple(float((mm[:, k] - mm[:, 0]).mean()) for k in (5, 6, 7)))
     a = a[:, :, :5]
     d = np.diff(a, axis=2).astype(np.float64)       # W x nt x 4
