@@ -281,14 +281,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
             for (int s = 0; s < TC_SPW; ++s) {
                 uint4 n0 = r0, n1 = r1;
                 if (s + 1 < TC_SPW) { n0 = rec[2 * s + 2]; n1 = rec[2 * s + 3]; }   // next slot's record hides behind this slot
-                const uint32_t ctl = r1.y;
+                uint32_t ctl = r1.y;
+                if (s == 0 && m == 0) ctl |= 15u;   // the CTA's first slot: nothing is in registers yet (the control word names all four joints)
                 if (ctl & 15u) {   // warp-uniform: some of the four register sets change joint
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
                         if (ctl & (1u << k)) {
                             const uint32_t col = 12u * ((ctl >> (4 + 5 * k)) & 31u);
-                            tmem_ld4(tm_row + col, g[k]);
-                            tmem_ld4(tm_row + col + 4, g[k] + 4);
+                            tmem_ld8(tm_row + col, g[k]);
                             tmem_ld4(tm_row + col + 8, g[k] + 8);
                         }
                     tc_wait_ld();
@@ -374,6 +374,11 @@ int build_tc_tables(b3d_model& m, const std::vector<double>& vert, const std::ve
     long long reloads = 0, slots_total = 0;
 
     struct Vtx { int v; int nj; int j[4]; float w[4]; uint64_t key; };
+    // register sets of each slot sequence (= warp of a quadrant), carried from sort tile to sort tile: a warp walks the tiles in
+    // order, and a CTA that starts in the middle re-reads all four sets at its first slot
+    int reg_state[TC_SEQS][4];
+    for (int h = 0; h < TC_SEQS; ++h)
+        for (int k = 0; k < 4; ++k) reg_state[h][k] = -1;
     for (int t = 0; t < tiles; ++t) {
         const int base = t * TC_T;
         std::vector<Vtx> vs(TC_T);
@@ -406,7 +411,7 @@ int build_tc_tables(b3d_model& m, const std::vector<double>& vert, const std::ve
                 if (!groups.empty() && vs[groups.back()[0]].key == vs[i].key) groups.back().push_back(i);
                 else groups.push_back({i});
             }
-            int reg[4] = {-1, -1, -1, -1};
+            int* reg = reg_state[h];
             std::vector<bool> used(groups.size(), false);
             int slot = 0;
             for (size_t done = 0; done < groups.size(); ++done) {
@@ -416,7 +421,7 @@ int build_tc_tables(b3d_model& m, const std::vector<double>& vert, const std::ve
                     const Vtx& x = vs[groups[gi][0]];
                     int cost = 0;
                     for (int a = 0; a < x.nj; ++a) cost += !(reg[0] == x.j[a] || reg[1] == x.j[a] || reg[2] == x.j[a] || reg[3] == x.j[a]);
-                    if (done == 0) cost = (int)gi;   // start from the first group in key order
+                    if (done == 0 && reg[0] < 0) cost = (int)gi;   // nothing loaded yet: start from the first group in key order
                     if (cost < best_cost) { best_cost = cost; best = (int)gi; }
                 }
                 used[best] = true;
@@ -439,9 +444,11 @@ int build_tc_tables(b3d_model& m, const std::vector<double>& vert, const std::ve
                 for (size_t gi2 = 0; gi2 < groups[best].size(); ++gi2, ++slot) {
                     const Vtx& x = vs[groups[best][gi2]];
                     uint32_t f = gi2 == 0 ? flags : 0u;
-                    if (slot == 0) f = 15u;                        // a warp starts a sort tile with nothing assumed
                     int jr[4];
-                    for (int k = 0; k < 4; ++k) { jr[k] = reg[k] < 0 ? 0 : reg[k]; if (reg[k] < 0 && slot == 0) reg[k] = 0; }
+                    for (int k = 0; k < 4; ++k) {
+                        if (reg[k] < 0) { reg[k] = 0; f |= 1u << k; }   // very first slot: unused sets hold joint 0
+                        jr[k] = reg[k];
+                    }
                     const int mt = slot / SPW, s = slot % SPW;
                     unsigned char* bl = &blob[((size_t)t * TC_MPT + mt) * TC_BLOB_BYTES];
                     float* oper = reinterpret_cast<float*>(bl);

@@ -6,7 +6,10 @@
 #include <cstdio>
 #include <cuda_runtime.h>
 
-constexpr int ROWS = 128, ROW_FLOATS = 288, PITCH = 292;   // 16 B aligned pitch for the vector / bulk variants
+#ifndef ROW_FLOATS
+#define ROW_FLOATS 288
+#endif
+constexpr int ROWS = 128, PITCH = 292;   // 16 B aligned pitch for the vector / bulk variants
 constexpr size_t BODY_STRIDE = 82688;                        // bytes, 16 B aligned stand-in for 6890 * 12 = 82680
 constexpr int THREADS = 512;
 
@@ -28,11 +31,11 @@ __global__ void __launch_bounds__(THREADS, 1) probe(unsigned char* dst, int tile
             for (int r = warp * 8; r < warp * 8 + 8; ++r) {
                 float* d = reinterpret_cast<float*>(tb + (size_t)r * BODY_STRIDE) + lane;
                 const float* s = sm + r * PITCH + lane;
-                float v[9];
+                float v[ROW_FLOATS / 32];
 #pragma unroll
-                for (int i = 0; i < 9; ++i) v[i] = s[32 * i];
+                for (int i = 0; i < ROW_FLOATS / 32; ++i) v[i] = s[32 * i];
 #pragma unroll
-                for (int i = 0; i < 9; ++i) d[32 * i] = v[i];
+                for (int i = 0; i < ROW_FLOATS / 32; ++i) d[32 * i] = v[i];
             }
         } else if (MODE == 1) {   // LDS.128 + STG.128: 72 float4 per row
             for (int r = warp * 8; r < warp * 8 + 8; ++r) {
@@ -40,9 +43,9 @@ __global__ void __launch_bounds__(THREADS, 1) probe(unsigned char* dst, int tile
                 const float4* s = reinterpret_cast<const float4*>(sm + r * PITCH);
                 float4 v[3];
 #pragma unroll
-                for (int i = 0; i < 3; ++i) if (lane + 32 * i < 72) v[i] = s[lane + 32 * i];
+                for (int i = 0; i < 3; ++i) if (lane + 32 * i < ROW_FLOATS / 4) v[i] = s[lane + 32 * i];
 #pragma unroll
-                for (int i = 0; i < 3; ++i) if (lane + 32 * i < 72) d[lane + 32 * i] = v[i];
+                for (int i = 0; i < 3; ++i) if (lane + 32 * i < ROW_FLOATS / 4) d[lane + 32 * i] = v[i];
             }
         } else {   // TMA bulk store: thread r < 128 stores row r (1152 B)
             if (tid < ROWS) {
@@ -82,7 +85,7 @@ static void run(const char* name, unsigned char* d, long long* c, int ctas, int 
 }
 
 int main() {
-    const int tiles = 71;   // 71 * 1152 B <= 82688
+    const int tiles = 82688 / (ROW_FLOATS * 4) - 1; printf("row bytes %d\n", ROW_FLOATS * 4);   // 71 * 1152 B <= 82688
     unsigned char* d; long long* c;
     cudaMalloc(&d, (size_t)148 * ROWS * BODY_STRIDE);
     cudaMalloc(&c, sizeof(long long) * 148);
