@@ -501,8 +501,8 @@ int launch_lbs_tc(const b3d_model* m, int B, const float* wshape, const float* G
     }
     const int groups = (B + TC_M - 1) / TC_M;
     const int tiles = m->tc.sort_tiles;
-    // vertex splits: fill 148 SMs in whole waves; a CTA's prologue (A operand, transforms -> TMEM) costs about 1/25 of a body
-    // group's full vertex sweep
+    // vertex splits: fill 148 SMs in whole waves; a CTA's prologue (TMEM allocation, transforms -> TMEM, pipeline fill) costs about
+    // one sort tile's worth of time (fitted to B = 65536 timings at 2 and 8 splits)
     static const int forced = [] { const char* e = getenv("B3D_TC_SPLITS"); return e ? atoi(e) : 0; }();
     int best_s = 1;
     double best_cost = 1e30;
@@ -510,7 +510,7 @@ int launch_lbs_tc(const b3d_model* m, int B, const float* wshape, const float* G
         const long long ctas = (long long)groups * s;
         const long long waves = (ctas + 147) / 148;
         const int per = (tiles + s - 1) / s;   // sort tiles of the longest CTA
-        const double cost = (double)waves * ((double)per + 0.04 * tiles);
+        const double cost = (double)waves * ((double)per + 1.1);
         if (cost < best_cost * 0.999) { best_cost = cost; best_s = s; }
     }
     if (forced > 0) best_s = std::min(forced, tiles);

@@ -7,7 +7,7 @@ mean pixel error — the per-frame body of src/main_single_frame.cpp:205-255.
 
   value     : whole-job frames/s with inputs resident in HBM, device-timed (CUDA events, max over ranks)
   e2e       : the same through the host-pointer C-ABI call b3d_fit_frames with pinned HOST buffers (H2D + D2H inside)
-  roofline  : the HBM-bound kernel of the path (smpl_lbs_kernel, float32 cloud) timed live at a batch larger than L2
+  roofline  : the HBM-bound kernel of the path (smpl_lbs_tc_kernel, float32 cloud) timed live at a batch larger than L2
   roofline_lm : the dominant kernel of the step (fit_single_kernel): fp64-ALU/latency bound, reported as achieved GFLOP/s
   cpu_baseline : the CPU oracle (Ceres-1.14-faithful: dense QR + Jet autodiff) on the box's host cores, bounded sample
 
@@ -271,7 +271,7 @@ def run_b200(args):
     e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
     px_err_mean = float(out["px_err"].mean())
 
-    # roofline of the HBM-bound kernel: float32 forward at a batch whose cloud (1.36 GB) is far larger than L2
+    # roofline of the HBM-bound kernel: float32 forward at a batch whose cloud (5.4 GB at B = 65536) is far larger than L2
     FB = args.forward_batch
     synth = pkg("synth")
     fin = synth.make_forward_inputs(FB, 5)
@@ -289,6 +289,16 @@ def run_b200(args):
         fevs.append((e0, e1))
     torch.cuda.synchronize()
     fwd_ms = float(np.mean([a.elapsed_time(b) for a, b in fevs]))
+    # the joints kernel alone (same call without a cloud), to show what share of the call is the skinning kernel
+    fwdj = lambda: capi.check(lib.b3d_smpl_forward_dev(gm.h, FB, capi.F32, P(fw), P(fp_), P(fr_), None, P(fjp), P(fjt), 0, C.c_void_p(st)), "joints only")
+    fwdj(); torch.cuda.synchronize()
+    jevs = []
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fwdj(); e1.record()
+        jevs.append((e0, e1))
+    torch.cuda.synchronize()
+    joints_ms = float(np.mean([a.elapsed_time(b) for a, b in jevs]))
     clk = clocks.stop() if rank == 0 else None
 
     # max over ranks of the device-timed step, the e2e step and the forward
@@ -343,7 +353,10 @@ def run_b200(args):
                 "ms_per_step": e2e_ms, "call": "b3d_fit_frames (host pointers, pinned); cloud computed and left on the device"},
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
-                     "kernel": "smpl_joints_kernel<float> + smpl_lbs_kernel<float,4> (one b3d_smpl_forward_dev call)",
+                     "kernel": "smpl_lbs_tc_kernel (tcgen05 shape blend + skinning) inside one b3d_smpl_forward_dev call, which also runs "
+                               "smpl_joints_kernel<float>; achieved is the WHOLE call",
+                     "joints_kernel_ms": joints_ms, "lbs_kernel_gbs_est": FB * FWD_BYTES_PER_BODY_F32 / max(fwd_ms - joints_ms, 1e-6) / 1e6,
+                     "write_only_peak_gbs": 5400.0, "write_only_peak_source": "tools/store_probe.cu on this pool's B200 (profiles/r01_store_probe.log)",
                      "workload": f"forward sweep point B={FB} (BASELINE configs[3]), {FWD_BYTES_PER_BODY_F32} algorithmic B/body", "ms_per_launch": fwd_ms,
                      "verts_per_sec": world * FB * V / (fwd_ms * 1e-3), "peak_source": peak_src},
         "roofline_lm": {"kernel": "fit_single_kernel<128>", "bound": "fp64 ALU / latency (not HBM: ~1.2 KB algorithmic I/O per frame)",
@@ -366,7 +379,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--frames", type=int, default=FRAMES_PER_GPU, help="frames per GPU per step")
-    ap.add_argument("--forward-batch", type=int, default=16384)
+    ap.add_argument("--forward-batch", type=int, default=65536)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
