@@ -147,6 +147,7 @@ __device__ __forceinline__ void named_bar(int id, int threads) { asm volatile("b
 constexpr int TC_TRACE_TILES = 256, TC_TRACE_PTS = 8;
 __device__ long long g_tc_trace[(TC_EPI_WARPS + 4) * TC_TRACE_TILES * TC_TRACE_PTS];
 
+template <bool TRACE>
 __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsigned char* __restrict__ blob, int V, int B, int sort_tiles, int splits, int bulk_rows, int trace,
                                                                      const float* __restrict__ wshape, const float* __restrict__ G,
                                                                      float* __restrict__ cloud) {
@@ -209,8 +210,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
     __syncthreads();   // also: the staging rows may now be overwritten
     tc_fence_after();
 
-    const bool tr = trace && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0;
-    auto stamp = [&](int m, int k) { if (tr && m < TC_TRACE_TILES) g_tc_trace[(warp * TC_TRACE_TILES + m) * TC_TRACE_PTS + k] = clock64(); };
+    const bool tr = TRACE && trace && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0;
+    auto stamp = [&](int m, int k) { if (TRACE && tr && m < TC_TRACE_TILES) g_tc_trace[(warp * TC_TRACE_TILES + m) * TC_TRACE_PTS + k] = clock64(); };
     const unsigned char* const blob0 = blob + (size_t)(TC_MPT * t_begin) * TC_BLOB_BYTES;
     auto issue_tma = [&](int m) {   // one thread: operand and slot records of MMA tile m -> their rings
         const int so = m % TC_NOP, uo = m / TC_NOP, sr = m % TC_NREC, ur = m / TC_NREC;
@@ -276,11 +277,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
             stamp(m, 2);
 
             const uint4* rec = reinterpret_cast<const uint4*>(S.recs[sr]) + 2 * (TC_SPW * h);
-            uint4 r0 = rec[0], r1 = rec[1];
+            uint4 rq[TC_SPW + 1][2];   // statically indexed (the loop is unrolled): the next slot's record hides behind this slot
+            rq[0][0] = rec[0]; rq[0][1] = rec[1];
 #pragma unroll
             for (int s = 0; s < TC_SPW; ++s) {
-                uint4 n0 = r0, n1 = r1;
-                if (s + 1 < TC_SPW) { n0 = rec[2 * s + 2]; n1 = rec[2 * s + 3]; }   // next slot's record hides behind this slot
+                if (s + 1 < TC_SPW) { rq[s + 1][0] = rec[2 * s + 2]; rq[s + 1][1] = rec[2 * s + 3]; }
+                const uint4 r0 = rq[s][0], r1 = rq[s][1];
                 uint32_t ctl = r1.y;
                 if (s == 0 && m == 0) ctl |= 15u;   // the CTA's first slot: nothing is in registers yet (the control word names all four joints)
                 if (ctl & 15u) {   // warp-uniform: some of the four register sets change joint
@@ -307,7 +309,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
                 }
                 float* so = orow + r1.x;
                 so[0] = ax; so[1] = ay; so[2] = az;
-                r0 = n0; r1 = n1;
             }
             __syncwarp();
             if (lane == 0) bar_arrive(&S.rec_free[sr]);        // records read: the block may be refilled
@@ -496,7 +497,8 @@ static std::atomic<int> g_tc_trace_on{0};
 int launch_lbs_tc(const b3d_model* m, int B, const float* wshape, const float* G, float* cloud, cudaStream_t st) {
     static bool attr_set = false;
     if (!attr_set) {
-        B3D_CUDA(cudaFuncSetAttribute(smpl_lbs_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem)));
+        B3D_CUDA(cudaFuncSetAttribute(smpl_lbs_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem)));
+        B3D_CUDA(cudaFuncSetAttribute(smpl_lbs_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem)));
         attr_set = true;
     }
     const int groups = (B + TC_M - 1) / TC_M;
@@ -518,7 +520,8 @@ int launch_lbs_tc(const b3d_model* m, int B, const float* wshape, const float* G
     // a 16 B aligned cloud: 6890 * 12 = 8 mod 16), which is how the staging rows are laid out; otherwise plain stores
     const int bulk_rows = ((reinterpret_cast<uintptr_t>(cloud) & 15) == 0 && ((size_t)m->V * 12) % 16 == 8) ? 1 : 0;
     const int trace = g_tc_trace_on.load();
-    smpl_lbs_tc_kernel<<<dim3(best_s, groups), TC_THREADS, sizeof(TcSmem), st>>>(m->tc.blob, m->V, B, tiles, best_s, bulk_rows, trace, wshape, G, cloud);
+    if (trace) smpl_lbs_tc_kernel<true><<<dim3(best_s, groups), TC_THREADS, sizeof(TcSmem), st>>>(m->tc.blob, m->V, B, tiles, best_s, bulk_rows, trace, wshape, G, cloud);
+    else smpl_lbs_tc_kernel<false><<<dim3(best_s, groups), TC_THREADS, sizeof(TcSmem), st>>>(m->tc.blob, m->V, B, tiles, best_s, bulk_rows, trace, wshape, G, cloud);
     return B3D_OK;
 }
 
