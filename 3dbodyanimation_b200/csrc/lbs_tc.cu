@@ -3,21 +3,22 @@
 //
 //   cloud[b][v] = sum_k weight[v][k] * ( R[b][j_vk] * (template[v] + shapedirs[v] w[b]) + t[b][j_vk] )
 //
-// CTA = 128 bodies x a run of sort tiles (96 consecutive vertices each; three MMA tiles of 32 slots).
+// CTA = 128 bodies x a run of sort tiles (64 consecutive vertices each; two MMA tiles of 32 slots).
 //   * shape blend: D[128 bodies x 96 (slot, coordinate)] = A[128 x 32] B[96 x 32]^T by tcgen05.mma kind::tf32 into TMEM.
 //     K = 32 carries a TF32 hi/lo split so that the result is good to ~2^-22:  k 0-9 w_hi * S_hi, 10-19 w_hi * S_lo,
-//     20-29 w_lo * S_hi, 30 1 * T_hi, 31 1 * T_lo (S = shapedirs, T = template).  A is built once per CTA in the canonical
-//     K-major / no-swizzle layout; B arrives per MMA tile as one TMA bulk copy (cp.async.bulk + mbarrier) of a blob the model
-//     build laid out in exactly that layout (internal.hpp TcTables), four stages deep; two accumulator buffers in TMEM.
-//   * a lane of an epilogue warp is a body (tcgen05.ld 32x32b: thread <-> TMEM lane).  The body's 24 joint transforms live in
+//     20-29 w_lo * S_hi, 30 1 * T_hi, 31 1 * T_lo (S = shapedirs, T = template).  A lives in TMEM (columns 288-319, written once
+//     per CTA); B arrives per MMA tile as a TMA bulk copy (cp.async.bulk + mbarrier) of a blob the model build laid out in the
+//     canonical K-major / no-swizzle layout (internal.hpp TcTables); two accumulator buffers in TMEM (columns 320-511).
+//   * a lane of a skinning warp is a body (tcgen05.ld 32x32b: thread <-> TMEM lane).  The body's 24 joint transforms live in
 //     TMEM columns 0-287 (written once per CTA by tcgen05.st); the four of the current joint set sit in 48 registers and are
-//     re-read only for the register sets the host marked (slots are ordered so that consecutive joint sets overlap).  Per slot
-//     the warp reads one 32-byte record (weights, position, control word) as warp-uniform LDS.128.
-//   * results go to a [32 bodies][3 x 96 + 1] staging tile per TMEM lane quadrant and leave as full rows (coalesced stores):
-//     HBM sees the cloud write only.
-// Warps: 16, all of them skinning warps (TMEM lane quadrant = warp & 3, slot sequence = warp >> 2: four warps per scheduler
-// hide the FMA / LDS / TMEM latencies); lane 0 of warp 0 also issues the TMA copies (two tiles ahead), lane 0 of warp 1 the MMAs
-// (one tile ahead), at the top of a tile.
+//     re-read only for the register sets the host marked (slots are ordered so that consecutive joint sets overlap, and the sets
+//     carry over from sort tile to sort tile).  Per slot the warp reads one 32-byte record (weights, position, control word) as
+//     warp-uniform LDS.128.
+//   * results go to a [32 bodies][3 x 64 + 2] staging tile per TMEM lane quadrant, double buffered by sort tile; a finished tile
+//     leaves as TMA bulk row stores (768 B per body) while the next one is computed: HBM sees the cloud write only.
+// Warps: 16 skinning warps (TMEM lane quadrant = warp & 3, slot sequence = warp >> 2: four warps per scheduler hide the FMA / LDS /
+// TMEM latencies) + a service warpgroup (warp 16 lane 0 issues the TMA copies, warp 17 lane 0 the MMAs) that hands its registers
+// to the skinning warps with setmaxnreg.  Measurements and the variants that lost: DESIGN.md sections 4 and 6.
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
