@@ -472,13 +472,25 @@ static int forward_impl(const b3d_model* m, int B, const T* w, const T* p, const
     T* pf = nullptr;
     T* off = nullptr;
     if (!G) { B3D_CUDA(cudaMallocAsync(&scratchG, sizeof(T) * (size_t)B * NJ * 12, st)); G = scratchG; }
+    // B3D_FWD_LBS_* flags (or env B3D_LBS = tc | sorted | bodylane | generic) force a float32 path (tests, profiling); default:
+    // tensor-core kernel (lbs_tc.cu; with the pose blendshapes fused in when they are asked for) for batches that fill the
+    // machine, tile-sorted lane = vertex kernel below that
+    static const std::string want_env = [] { const char* e = getenv("B3D_LBS"); return std::string(e ? e : ""); }();
+    const std::string want = (flags & B3D_FWD_LBS_TC) ? "tc" : (flags & B3D_FWD_LBS_SORTED) ? "sorted" : (flags & B3D_FWD_LBS_BODYLANE) ? "bodylane"
+                             : (flags & B3D_FWD_LBS_GENERIC) ? "generic" : want_env;
+    const bool g_al16 = (reinterpret_cast<uintptr_t>(G) & 15) == 0;
+    const bool use_tc = cloud && sizeof(T) == 4 && m->nw == 4 && g_al16 && m->tc.blob && (!use_pd || m->tc.pose_b) &&
+                        (want == "tc" || (want.empty() && B >= TC_AUTO_MIN_B));
     if (use_pd && cloud) {
         B3D_CUDA(cudaMallocAsync(&pf, sizeof(T) * (size_t)B * B3D_POSEDIRS_DIM, st));
-        B3D_CUDA(cudaMallocAsync(&off, sizeof(T) * (size_t)B * 3 * m->Vpad, st));
+        if (!use_tc) B3D_CUDA(cudaMallocAsync(&off, sizeof(T) * (size_t)B * 3 * m->Vpad, st));
     }
     smpl_joints_kernel<T><<<(B + JW - 1) / JW, 32 * JW, 0, st>>>(m->d_sk, B, w, p, r, jointPos, G, pf);
     B3D_LAUNCH_CHECK();
-    if (cloud) {
+    if (use_tc) {
+        if (int rc = launch_lbs_tc(m, B, (const float*)w, (const float*)G, (const float*)pf, (float*)cloud, st)) return rc;
+        B3D_LAUNCH_CHECK();
+    } else if (cloud) {
         if (use_pd) {
             const T* pd = sizeof(T) == 4 ? (const T*)m->posedirs32 : (const T*)m->posedirs64;
             dim3 grid(m->Vpad / 128, (B + PB - 1) / PB);
@@ -498,18 +510,8 @@ static int forward_impl(const b3d_model* m, int B, const T* w, const T* p, const
         if (use_pd) smpl_lbs_kernel<T, NWV, true><<<grid, LBS_THREADS, 0, st>>>(t.vert, t.wval, t.wjoint, m->V, m->Vpad, B, per, w, G, off, cloud); \
         else smpl_lbs_kernel<T, NWV, false><<<grid, LBS_THREADS, 0, st>>>(t.vert, t.wval, t.wjoint, m->V, m->Vpad, B, per, w, G, nullptr, cloud);   \
     } while (0)
-        const bool g_al16 = (reinterpret_cast<uintptr_t>(G) & 15) == 0;
-        // measured on B200 (profiles/r01_forward_sweep.txt): the lane = vertex sorted kernel is the faster one today; the
-        // lane = body kernel is kept selectable (B3D_LBS=bodylane) as the base of the tensor-core shape-blend variant
-        // B3D_FWD_LBS_* flags (or env B3D_LBS = tc | sorted | bodylane | generic) force a float32 path (tests, profiling); default: tensor-core kernel for
-        // batches that fill the machine, tile-sorted lane = vertex kernel below that
-        static const std::string want_env = [] { const char* e = getenv("B3D_LBS"); return std::string(e ? e : ""); }();
-        const std::string want = (flags & B3D_FWD_LBS_TC) ? "tc" : (flags & B3D_FWD_LBS_SORTED) ? "sorted" : (flags & B3D_FWD_LBS_BODYLANE) ? "bodylane"
-                                 : (flags & B3D_FWD_LBS_GENERIC) ? "generic" : want_env;
         const bool want_bodylane = want == "bodylane";
-        const bool f32_fast = sizeof(T) == 4 && m->nw == 4 && !use_pd && g_al16;
-        if (f32_fast && m->tc.blob && (want == "tc" || (want.empty() && B >= TC_AUTO_MIN_B))) {
-            if (int rc = launch_lbs_tc(m, B, (const float*)w, (const float*)G, (float*)cloud, st)) return rc;
+        if (false) {
         } else if (want != "generic" && want_bodylane && sizeof(T) == 4 && m->nw == 4 && !use_pd && m->ts.rec && g_al16 && B >= 256) {
             static bool attr_set = false;
             if (!attr_set) {

@@ -82,12 +82,17 @@ struct SortedTables {
 //                   3 * position in the sort tile, control word (reload flags + joint ids), 2 spare
 struct TcTables {
     uint8_t* blob = nullptr;
+    // pose blendshapes (extension) for the same kernel: per MMA tile 26 K = 8 steps of the [96 columns x 8] B operand, TF32,
+    // canonical layout; columns in the tile's slot order (host copy of that order: slot_vertex)
+    float* pose_b = nullptr;
+    std::vector<int32_t> slot_vertex;   // [sort_tiles * TC_MPT][TC_SLOTS] vertex of every slot (-1: padding)
     int sort_tiles = 0;
     double mean_reloads = 0.0;   // joint transforms re-read from TMEM per slot (host statistic, reported by tools)
 };
 constexpr int TC_T = 64, TC_SLOTS = 32, TC_N = 96, TC_K = 32;
 constexpr int TC_MPT = TC_T / TC_SLOTS;   // MMA tiles per sort tile
-constexpr int TC_SEQS = 4;   // slot sequences per sort tile = epilogue warps per TMEM lane quadrant
+constexpr int TC_SEQS = 4;
+constexpr int TC_POSE_KSTEPS = (B3D_POSEDIRS_DIM + 7) / 8;   // 26   // slot sequences per sort tile = epilogue warps per TMEM lane quadrant
 constexpr int TC_OPER_BYTES = TC_N * TC_K * 4, TC_REC_WORDS = 8, TC_BLOB_BYTES = TC_OPER_BYTES + TC_SLOTS * TC_REC_WORDS * 4;
 
 // small per-model constants passed to kernels by value
@@ -106,7 +111,9 @@ struct b3d_model;
 namespace b3d {
 // lbs_tc.cu
 int build_tc_tables(b3d_model& m, const std::vector<double>& vert, const std::vector<double>& wval, const std::vector<int32_t>& wjoint);
-int launch_lbs_tc(const b3d_model* m, int B, const float* wshape, const float* G, float* cloud, cudaStream_t st);
+int build_tc_pose_tables(b3d_model& m, const std::vector<float>& p32);   // p32[(k * 3 + c) * Vpad + v]
+// posefeat: B x 207 row-major pose features (joints kernel) or null = reference semantics (no pose blendshapes)
+int launch_lbs_tc(const b3d_model* m, int B, const float* wshape, const float* G, const float* posefeat, float* cloud, cudaStream_t st);
 }  // namespace b3d
 
 struct b3d_model {

@@ -43,6 +43,9 @@ constexpr int TC_GROW = NJ * 12 + 4;            // 292 floats: prologue rows of 
 constexpr int TC_NREC = 4;                       // ring of slot-record blocks (1 KB per MMA tile)
 constexpr int TC_NOP = 2;                        // ring of B operand tiles (12 KB per MMA tile)
 constexpr int TC_REC_BYTES = TC_BLOB_BYTES - TC_OPER_BYTES;
+constexpr int TC_CH_A = TC_M * 16 * 4, TC_CH_B = TC_N * 16 * 4, TC_CH_BYTES = TC_CH_A + TC_CH_B;   // 8192 + 6144
+constexpr int TC_NCH = 2 + TC_POSE_KSTEPS / 2;   // chunks per MMA tile with pose blendshapes: 2 shape + 13 pose
+static_assert(TC_POSE_KSTEPS % 2 == 0, "pose K steps come in pairs");
 constexpr int TC_COL_A = 288;                    // A operand (128 bodies x K = 32) lives in TMEM columns [288, 320)
 
 struct __align__(128) TcSmem {
@@ -51,7 +54,13 @@ struct __align__(128) TcSmem {
     // row leaves as one TMA bulk store (odd bodies: 8 B head and tail by plain stores).  The prologue lands the 128 x 288 joint
     // transforms here first (rows of TC_GROW floats).
     float out[2][4][32 * TC_SROW];
-    unsigned char oper[TC_NOP][TC_OPER_BYTES];
+    // B operand ring.  Reference semantics: two stages of a whole K = 32 shape operand (12 KB).  With pose blendshapes: two stages
+    // of a K = 16 chunk, [A 128 x 16 | B 96 x 16] = 8 KB + 6 KB (the two shape chunks use the B part only, their A is in TMEM)
+    union {
+        unsigned char oper[TC_NOP][TC_OPER_BYTES];
+        unsigned char chunk[2][TC_CH_BYTES];
+    };
+    unsigned long long ch_full[2], ch_free[2];
     unsigned char recs[TC_NREC][TC_REC_BYTES];
     unsigned long long op_full[TC_NOP], op_free[TC_NOP], rec_full[TC_NREC], rec_free[TC_NREC], d_full[2], d_empty[2], g_full;
     uint32_t tmem_base;
@@ -148,8 +157,8 @@ __device__ __forceinline__ void named_bar(int id, int threads) { asm volatile("b
 constexpr int TC_TRACE_TILES = 256, TC_TRACE_PTS = 8;
 __device__ long long g_tc_trace[(TC_EPI_WARPS + 4) * TC_TRACE_TILES * TC_TRACE_PTS];
 
-template <bool TRACE>
-__global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsigned char* __restrict__ blob, int V, int B, int sort_tiles, int splits, int bulk_rows, int trace,
+template <bool TRACE, bool POSE>
+__global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsigned char* __restrict__ blob, const float* __restrict__ pose_a, const float* __restrict__ pose_b, int V, int B, int sort_tiles, int splits, int bulk_rows, int trace,
                                                                      const float* __restrict__ wshape, const float* __restrict__ G,
                                                                      float* __restrict__ cloud) {
     extern __shared__ __align__(128) unsigned char tc_raw[];
@@ -165,6 +174,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
         for (int i = 0; i < TC_NREC; ++i) { bar_init(&S.rec_full[i], 1); bar_init(&S.rec_free[i], TC_EPI_WARPS); }
         for (int i = 0; i < 2; ++i) { bar_init(&S.d_full[i], 1); bar_init(&S.d_empty[i], TC_EPI_WARPS); }
         bar_init(&S.g_full, 1);
+        for (int i = 0; i < 2; ++i) { bar_init(&S.ch_full[i], 1); bar_init(&S.ch_free[i], 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
@@ -214,31 +224,68 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
     const bool tr = TRACE && trace && blockIdx.x == 0 && blockIdx.y == 0 && lane == 0;
     auto stamp = [&](int m, int k) { if (TRACE && tr && m < TC_TRACE_TILES) g_tc_trace[(warp * TC_TRACE_TILES + m) * TC_TRACE_PTS + k] = clock64(); };
     const unsigned char* const blob0 = blob + (size_t)(TC_MPT * t_begin) * TC_BLOB_BYTES;
-    auto issue_tma = [&](int m) {   // one thread: operand and slot records of MMA tile m -> their rings
-        const int so = m % TC_NOP, uo = m / TC_NOP, sr = m % TC_NREC, ur = m / TC_NREC;
-        bar_wait(&S.op_free[so], (uint32_t)((uo & 1) ^ 1));        // the MMA that read this operand stage is complete
-        bar_expect_tx(&S.op_full[so], TC_OPER_BYTES);
-        bulk_g2s(S.oper[so], blob0 + (size_t)m * TC_BLOB_BYTES, TC_OPER_BYTES, &S.op_full[so]);
+    // instruction descriptor: D = F32, A = B = TF32, both K-major, N = 96, M = 128
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_N >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);
+    auto issue_tma = [&](int m) {   // one thread: operand(s) and slot records of MMA tile m -> their rings
+        const int sr = m % TC_NREC, ur = m / TC_NREC;
         bar_wait(&S.rec_free[sr], (uint32_t)((ur & 1) ^ 1));       // every warp is done with this record block's last tile
         bar_expect_tx(&S.rec_full[sr], TC_REC_BYTES);
         bulk_g2s(S.recs[sr], blob0 + (size_t)m * TC_BLOB_BYTES + TC_OPER_BYTES, TC_REC_BYTES, &S.rec_full[sr]);
+        if (!POSE) {
+            const int so = m % TC_NOP, uo = m / TC_NOP;
+            bar_wait(&S.op_free[so], (uint32_t)((uo & 1) ^ 1));    // the MMA that read this operand stage is complete
+            bar_expect_tx(&S.op_full[so], TC_OPER_BYTES);
+            bulk_g2s(S.oper[so], blob0 + (size_t)m * TC_BLOB_BYTES, TC_OPER_BYTES, &S.op_full[so]);
+        } else {
+            // 15 chunks of K = 16: two of the shape operand (B only), thirteen of the pose contraction (A: this body group's pose
+            // features, B: the tile's posedirs columns), through a two-stage ring
+            const float* pa = pose_a + (size_t)blockIdx.y * TC_POSE_KSTEPS * (TC_M * 8);
+            const float* pb = pose_b + (size_t)(TC_MPT * t_begin + m) * TC_POSE_KSTEPS * (TC_N * 8);
+            for (int c = 0; c < TC_NCH; ++c) {
+                const int g = m * TC_NCH + c, sc = g & 1, uc = g >> 1;
+                bar_wait(&S.ch_free[sc], (uint32_t)((uc & 1) ^ 1));
+                if (c < 2) {
+                    bar_expect_tx(&S.ch_full[sc], TC_CH_B);
+                    bulk_g2s(S.chunk[sc] + TC_CH_A, blob0 + (size_t)m * TC_BLOB_BYTES + (size_t)c * TC_CH_B, TC_CH_B, &S.ch_full[sc]);
+                } else {
+                    bar_expect_tx(&S.ch_full[sc], TC_CH_BYTES);
+                    bulk_g2s(S.chunk[sc], pa + (size_t)(2 * (c - 2)) * (TC_M * 8), TC_CH_A, &S.ch_full[sc]);
+                    bulk_g2s(S.chunk[sc] + TC_CH_A, pb + (size_t)(2 * (c - 2)) * (TC_N * 8), TC_CH_B, &S.ch_full[sc]);
+                }
+            }
+        }
     };
-    auto issue_mma = [&](int m) {   // one thread: shape blend of MMA tile m into accumulator buffer m & 1
-        // instruction descriptor: D = F32, A = B = TF32, both K-major, N = 96, M = 128
-        const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(TC_N >> 3) << 17) | ((uint32_t)(TC_M >> 4) << 24);
-        const int so = m % TC_NOP, uo = m / TC_NOP, buf = m & 1, r = m >> 1;
-        stamp(m, 0);
-        bar_wait(&S.op_full[so], (uint32_t)(uo & 1));
-        bar_wait(&S.d_empty[buf], (uint32_t)((r & 1) ^ 1));
-        tc_fence_after();
-        stamp(m, 5);
-        const uint32_t b_addr = s_u32(S.oper[so]);
+    auto issue_mma = [&](int m) {   // one thread: blend(s) of MMA tile m into accumulator buffer m & 1
+        const int buf = m & 1, r = m >> 1;
         const uint32_t d_tmem = tm + (uint32_t)(buf ? TC_COL_D1 : TC_COL_D0);
+        stamp(m, 0);
+        if (!POSE) {
+            const int so = m % TC_NOP, uo = m / TC_NOP;
+            bar_wait(&S.op_full[so], (uint32_t)(uo & 1));
+            bar_wait(&S.d_empty[buf], (uint32_t)((r & 1) ^ 1));
+            tc_fence_after();
+            stamp(m, 5);
+            const uint32_t b_addr = s_u32(S.oper[so]);
 #pragma unroll
-        for (int s = 0; s < TC_K / 8; ++s)
-            mma_tf32_ts(d_tmem, tm + (uint32_t)(TC_COL_A + 8 * s), smem_desc(b_addr + s * TC_B_SLAB), idesc, s > 0 ? 1u : 0u);
-        stamp(m, 6);
-        tc_commit(&S.op_free[so]);
+            for (int s = 0; s < TC_K / 8; ++s)
+                mma_tf32_ts(d_tmem, tm + (uint32_t)(TC_COL_A + 8 * s), smem_desc(b_addr + s * TC_B_SLAB), idesc, s > 0 ? 1u : 0u);
+            stamp(m, 6);
+            tc_commit(&S.op_free[so]);
+        } else {
+            bar_wait(&S.d_empty[buf], (uint32_t)((r & 1) ^ 1));
+            for (int c = 0; c < TC_NCH; ++c) {
+                const int g = m * TC_NCH + c, sc = g & 1, uc = g >> 1;
+                bar_wait(&S.ch_full[sc], (uint32_t)(uc & 1));
+                tc_fence_after();
+                const uint32_t a_addr = s_u32(S.chunk[sc]), b_addr = a_addr + TC_CH_A;
+#pragma unroll
+                for (int s = 0; s < 2; ++s) {
+                    if (c < 2) mma_tf32_ts(d_tmem, tm + (uint32_t)(TC_COL_A + 16 * c + 8 * s), smem_desc(b_addr + s * TC_B_SLAB), idesc, (c | s) ? 1u : 0u);
+                    else mma_tf32(d_tmem, smem_desc(a_addr + s * TC_A_SLAB), smem_desc(b_addr + s * TC_B_SLAB), idesc, 1u);
+                }
+                tc_commit(&S.ch_free[sc]);
+            }
+        }
         tc_commit(&S.d_full[buf]);
         stamp(m, 7);
     };
@@ -373,6 +420,7 @@ int build_tc_tables(b3d_model& m, const std::vector<double>& vert, const std::ve
     const int V = m.V;
     const int tiles = (V + TC_T - 1) / TC_T;
     std::vector<unsigned char> blob((size_t)tiles * TC_MPT * TC_BLOB_BYTES, 0);
+    m.tc.slot_vertex.assign((size_t)tiles * TC_MPT * TC_SLOTS, -1);
     long long reloads = 0, slots_total = 0;
 
     struct Vtx { int v; int nj; int j[4]; float w[4]; uint64_t key; };
@@ -465,6 +513,7 @@ int build_tc_tables(b3d_model& m, const std::vector<double>& vert, const std::ve
                     rec[5] = f | ((uint32_t)jr[0] << 4) | ((uint32_t)jr[1] << 9) | ((uint32_t)jr[2] << 14) | ((uint32_t)jr[3] << 19);
                     rec[6] = (uint32_t)x.v;
                     rec[7] = 0;
+                    if (x.v < V) m.tc.slot_vertex[((size_t)t * TC_MPT + mt) * TC_SLOTS + SPW * h + s] = x.v;
                     for (int k = 0; k < 4; ++k) reloads += (f >> k) & 1u;
                     ++slots_total;
                     if (x.v < V)
@@ -495,11 +544,24 @@ int build_tc_tables(b3d_model& m, const std::vector<double>& vert, const std::ve
 
 static std::atomic<int> g_tc_trace_on{0};
 
-int launch_lbs_tc(const b3d_model* m, int B, const float* wshape, const float* G, float* cloud, cudaStream_t st) {
+// Pose features (B x 207 row-major, joints kernel) -> A operand slabs of the pose contraction: per group of 128 bodies, 26 slabs
+// [128 rows x 8 k] in the canonical layout, rounded to TF32 (one pass is enough: the pose term is ~1e-2 of a vertex coordinate).
+__global__ void __launch_bounds__(256) pose_operand_kernel(const float* __restrict__ pf, int B, float* __restrict__ pose_a) {
+    const int g = blockIdx.x;
+    for (int i = threadIdx.x; i < TC_M * 8 * TC_POSE_KSTEPS; i += 256) {
+        const int r = i / (8 * TC_POSE_KSTEPS), k = i - r * (8 * TC_POSE_KSTEPS);   // consecutive threads: consecutive k of one body
+        const int body = g * TC_M + r;
+        const float v = (body < B && k < B3D_POSEDIRS_DIM) ? pf[(size_t)body * B3D_POSEDIRS_DIM + k] : 0.f;
+        pose_a[((size_t)g * TC_POSE_KSTEPS + (k >> 3)) * (TC_M * 8) + canon_off(TC_M, r, k & 7)] = to_tf32(v);
+    }
+}
+
+int launch_lbs_tc(const b3d_model* m, int B, const float* wshape, const float* G, const float* posefeat, float* cloud, cudaStream_t st) {
     static bool attr_set = false;
     if (!attr_set) {
-        B3D_CUDA(cudaFuncSetAttribute(smpl_lbs_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem)));
-        B3D_CUDA(cudaFuncSetAttribute(smpl_lbs_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem)));
+        B3D_CUDA(cudaFuncSetAttribute(smpl_lbs_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem)));
+        B3D_CUDA(cudaFuncSetAttribute(smpl_lbs_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem)));
+        B3D_CUDA(cudaFuncSetAttribute(smpl_lbs_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem)));
         attr_set = true;
     }
     const int groups = (B + TC_M - 1) / TC_M;
@@ -521,8 +583,40 @@ int launch_lbs_tc(const b3d_model* m, int B, const float* wshape, const float* G
     // a 16 B aligned cloud: 6890 * 12 = 8 mod 16), which is how the staging rows are laid out; otherwise plain stores
     const int bulk_rows = ((reinterpret_cast<uintptr_t>(cloud) & 15) == 0 && ((size_t)m->V * 12) % 16 == 8) ? 1 : 0;
     const int trace = g_tc_trace_on.load();
-    if (trace) smpl_lbs_tc_kernel<true><<<dim3(best_s, groups), TC_THREADS, sizeof(TcSmem), st>>>(m->tc.blob, m->V, B, tiles, best_s, bulk_rows, trace, wshape, G, cloud);
-    else smpl_lbs_tc_kernel<false><<<dim3(best_s, groups), TC_THREADS, sizeof(TcSmem), st>>>(m->tc.blob, m->V, B, tiles, best_s, bulk_rows, trace, wshape, G, cloud);
+    const dim3 grid(best_s, groups);
+    if (posefeat) {
+        if (!m->tc.pose_b) return set_error(B3D_EINVAL, "tensor-core LBS: the model has no pose blendshape tables");
+        float* pose_a = nullptr;
+        B3D_CUDA(cudaMallocAsync(&pose_a, sizeof(float) * (size_t)groups * TC_POSE_KSTEPS * TC_M * 8, st));
+        pose_operand_kernel<<<groups, 256, 0, st>>>(posefeat, B, pose_a);
+        B3D_LAUNCH_CHECK();
+        smpl_lbs_tc_kernel<false, true><<<grid, TC_THREADS, sizeof(TcSmem), st>>>(m->tc.blob, pose_a, m->tc.pose_b, m->V, B, tiles, best_s, bulk_rows, 0, wshape, G, cloud);
+        B3D_CUDA(cudaFreeAsync(pose_a, st));
+    } else if (trace) {
+        smpl_lbs_tc_kernel<true, false><<<grid, TC_THREADS, sizeof(TcSmem), st>>>(m->tc.blob, nullptr, nullptr, m->V, B, tiles, best_s, bulk_rows, trace, wshape, G, cloud);
+    } else {
+        smpl_lbs_tc_kernel<false, false><<<grid, TC_THREADS, sizeof(TcSmem), st>>>(m->tc.blob, nullptr, nullptr, m->V, B, tiles, best_s, bulk_rows, 0, wshape, G, cloud);
+    }
+    return B3D_OK;
+}
+
+// B operand slabs of the pose contraction, in every MMA tile's slot order (p32[(k * 3 + c) * Vpad + v], model.cu)
+int build_tc_pose_tables(b3d_model& m, const std::vector<float>& p32) {
+    if (m.tc.slot_vertex.empty()) return B3D_OK;
+    const size_t Vp = (size_t)m.Vpad;
+    const int mtiles = m.tc.sort_tiles * TC_MPT;
+    std::vector<float> pb((size_t)mtiles * TC_POSE_KSTEPS * TC_N * 8, 0.f);
+    for (int mt = 0; mt < mtiles; ++mt)
+        for (int slot = 0; slot < TC_SLOTS; ++slot) {
+            const int v = m.tc.slot_vertex[(size_t)mt * TC_SLOTS + slot];
+            if (v < 0) continue;
+            for (int c = 0; c < 3; ++c)
+                for (int k = 0; k < B3D_POSEDIRS_DIM; ++k)
+                    pb[((size_t)mt * TC_POSE_KSTEPS + (k >> 3)) * (TC_N * 8) + canon_off(TC_N, 3 * slot + c, k & 7)] =
+                        tf32_round_host(p32[((size_t)k * 3 + c) * Vp + v]);
+        }
+    B3D_CUDA(cudaMalloc(&m.tc.pose_b, sizeof(float) * pb.size()));
+    B3D_CUDA(cudaMemcpy(m.tc.pose_b, pb.data(), sizeof(float) * pb.size(), cudaMemcpyHostToDevice));
     return B3D_OK;
 }
 

@@ -227,6 +227,7 @@ int b3d_model_create(const b3d_model_desc* d, b3d_model** out) {
         if (e == cudaSuccess) e = cudaMalloc(&m->posedirs64, sizeof(double) * p64.size());
         if (e == cudaSuccess) e = cudaMemcpy(m->posedirs64, p64.data(), sizeof(double) * p64.size(), cudaMemcpyHostToDevice);
         if (e != cudaSuccess) rc = set_error(B3D_ECUDA, "posedirs upload: %s", cudaGetErrorString(e));
+        if (!rc && m->nw == 4) rc = build_tc_pose_tables(*m, p32);
         m->has_posedirs = (rc == 0);
     }
     if (!rc) {
@@ -245,7 +246,7 @@ void b3d_model_destroy(b3d_model* m) {
     cudaFree(m->t32.vert); cudaFree(m->t32.wval); cudaFree(m->t32.wjoint);
     cudaFree(m->t64.vert); cudaFree(m->t64.wval); cudaFree(m->t64.wjoint);
     cudaFree(m->ts.vert); cudaFree(m->ts.wval); cudaFree(m->ts.wjoff); cudaFree(m->ts.loc);
-    cudaFree(m->ts.rec); cudaFree(m->ts.joff4); cudaFree(m->tc.blob);
+    cudaFree(m->ts.rec); cudaFree(m->ts.joff4); cudaFree(m->tc.blob); cudaFree(m->tc.pose_b);
     cudaFree(m->posedirs32); cudaFree(m->posedirs64); cudaFree(m->d_sk);
     delete m;
 }

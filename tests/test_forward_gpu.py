@@ -68,6 +68,21 @@ def test_forward_posedirs_extension(api, gmodel, omodel_pd, synth):
     assert rel_err(c32, c0) < 2e-5
 
 
+@pytest.mark.parametrize("B", [130, 700])
+def test_forward_posedirs_tensor_core(api, gmodel, omodel_pd, synth, B):
+    """Pose blendshapes fused into the tensor-core kernel (K = 208 more of TF32 on top of the shape blend, one pass): same
+    2e-5 as the CUDA-core float32 posedirs path, against the oracle with posedirs on."""
+    inp = synth.make_forward_inputs(B, 40 + B)
+    c, _, _ = api.smpl_forward(gmodel, inp["w"], inp["p"], inp["r"], dtype=np.float32, posedirs=True, lbs="tc")
+    w, p, r = (np.asarray(inp[k], dtype=np.float32).astype(np.float64) for k in ("w", "p", "r"))
+    c0, _, _ = omodel_pd.forward(w, p, r, nthreads=8)
+    worst = max(rel_err(c[b], c0[b]) for b in range(B))
+    assert worst < 2e-5, worst
+    # and it must differ from the no-posedirs cloud (the term is really there)
+    c1, _, _ = api.smpl_forward(gmodel, inp["w"], inp["p"], inp["r"], dtype=np.float32, lbs="tc")
+    assert rel_err(c1, c0) > 1e-4
+
+
 def test_forward_edge_cases(api, gmodel, omodel, synth):
     # rest pose: w = 0, r = I, p = 0 -> cloud equals the template exactly in float64 up to the weight sum rounding
     w, p = np.zeros((1, 10)), np.zeros((1, 3))

@@ -29,8 +29,8 @@ def timed(fn, reps):
     return float(np.mean(ts)), float(np.min(ts))
 
 
-def forward(B, dtype="f32", reps=5, lbs=None):
-    gm = api.AvatarModel(synth.make_model())
+def forward(B, dtype="f32", reps=5, lbs=None, posedirs=False):
+    gm = api.AvatarModel(synth.make_model(with_posedirs=posedirs))
     fin = synth.make_forward_inputs(B, 5)
     td = torch.float32 if dtype == "f32" else torch.float64
     code = capi.F32 if dtype == "f32" else capi.F64
@@ -38,11 +38,11 @@ def forward(B, dtype="f32", reps=5, lbs=None):
     cloud = torch.empty(B, gm.numPoints, 3, dtype=td, device=dev)
     jp, jt = torch.empty(B, 24, 3, dtype=td, device=dev), torch.empty(B, 24, 12, dtype=td, device=dev)
     st = torch.cuda.current_stream().cuda_stream
-    fn = lambda: capi.check(lib.b3d_smpl_forward_dev(gm.h, B, code, P(w), P(p), P(r), P(cloud), P(jp), P(jt), api.LBS_FLAGS[lbs], C.c_void_p(st)), "fwd")
+    fn = lambda: capi.check(lib.b3d_smpl_forward_dev(gm.h, B, code, P(w), P(p), P(r), P(cloud), P(jp), P(jt), api.LBS_FLAGS[lbs] | (1 if posedirs else 0), C.c_void_p(st)), "fwd")
     mean, best = timed(fn, reps)
     es = 4 if dtype == "f32" else 8
     gb = B * (85036 * es / 4) / 1e9
-    print(f"forward {dtype} lbs={lbs or 'auto'} B={B}: {mean:.3f} ms (best {best:.3f}) -> {gb / mean * 1e3:.0f} GB/s algorithmic, {B * gm.numPoints / mean * 1e3:.3e} verts/s")
+    print(f"forward {dtype} lbs={lbs or 'auto'}{' +posedirs' if posedirs else ''} B={B}: {mean:.3f} ms (best {best:.3f}) -> {gb / mean * 1e3:.0f} GB/s algorithmic, {B * gm.numPoints / mean * 1e3:.3e} verts/s")
 
 
 def fit(n, mode="C2", reps=3):
@@ -80,6 +80,8 @@ if __name__ == "__main__":
     if what == "forward":
         forward(int(sys.argv[2]) if len(sys.argv) > 2 else 16384, sys.argv[3] if len(sys.argv) > 3 else "f32",
                 lbs=sys.argv[4] if len(sys.argv) > 4 else None)
+    elif what == "pforward":   # with pose blendshapes
+        forward(int(sys.argv[2]) if len(sys.argv) > 2 else 16384, "f32", lbs=sys.argv[3] if len(sys.argv) > 3 else None, posedirs=True)
     elif what == "fsweep":   # float32 forward sweep per kernel
         for lbs in (sys.argv[2:] or ["tc", "sorted"]):
             for b in (128, 512, 1024, 4096, 16384, 65536):
