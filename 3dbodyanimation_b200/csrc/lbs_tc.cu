@@ -568,7 +568,7 @@ int launch_lbs_tc(const b3d_model* m, int B, const float* wshape, const float* G
     const int tiles = m->tc.sort_tiles;
     // vertex splits: fill 148 SMs in whole waves; a CTA's prologue (TMEM allocation, transforms -> TMEM, pipeline fill) costs about
     // one sort tile's worth of time (fitted to B = 65536 timings at 2 and 8 splits)
-    static const int forced = [] { const char* e = getenv("B3D_TC_SPLITS"); return e ? atoi(e) : 0; }();
+    const int forced = [] { const char* e = getenv("B3D_TC_SPLITS"); return e ? atoi(e) : 0; }();   // read per call: tests vary it
     int best_s = 1;
     double best_cost = 1e30;
     for (int s = 1; s <= std::min(tiles, 24); ++s) {
