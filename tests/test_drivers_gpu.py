@@ -1,0 +1,134 @@
+"""The executables' replacements (3dbodyanimation_b200/drivers.py) end to end on the shipped MediaPipe fixture
+(tests/golden/keypoints_video1: 38 frames of 480x270 video, 5 of them without a detection) with the synthetic SMPL-shaped model.
+
+3dba_single: log.csv rows and the fitted parameters against the oracle run frame by frame the way
+src/main_single_frame.cpp:192-255 does (tolerances of north_star: parameters 1e-3; see test_fit_single_gpu.py for the gauge note).
+3dba_multi: the driver's chain of b3d_fit_window calls against b3d_fit_sequences (whose schedule is checked against the oracle in
+test_fit_window_gpu.py) and against the oracle's fit_sequence directly."""
+import glob
+import json
+import os
+import shutil
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, PRIOR_TXT, pkg
+
+pytestmark = pytest.mark.gpu
+KPS_DIR = os.path.join(GOLDEN, "keypoints_video1")
+
+
+@pytest.fixture(scope="module")
+def drv(api):
+    return pkg("drivers")
+
+
+@pytest.fixture(scope="module")
+def model_dir(tmp_path_factory, model_np):
+    d = tmp_path_factory.mktemp("avatar-model")
+    np.savez(d / "model.npz", **{k: v for k, v in model_np.items() if k != "posedirs"})
+    shutil.copy(PRIOR_TXT, d / "pose_prior.txt")
+    return str(d)
+
+
+def _px(jp, kps, nkp, cam):
+    fx, fy, cx, cy = cam
+    return np.array([np.mean([np.hypot(fx * jp[f, k["jid"], 0] / jp[f, k["jid"], 2] + cx - k["u"],
+                                       fy * jp[f, k["jid"], 1] / jp[f, k["jid"], 2] + cy - k["v"]) for k in kps[f][:nkp[f]]])
+                     for f in range(len(nkp))])
+
+
+@pytest.mark.parametrize("flags", [(), ("--opt-shape", "--use-gmm")])
+def test_single_driver_on_fixture(drv, orc, omodel, ogmm, model_dir, tmp_path, flags, capsys):
+    out = tmp_path / "out"
+    rc = drv.main_single(["3dba_single", model_dir, KPS_DIR, "unused", str(out), "60", "--size", "480x270", "--save-params", *flags])
+    assert rc == 0
+    io = capsys.readouterr()
+    assert f"[ARGS] max_iters=60  beta_pose=20  beta_shape=30  opt_shape={'true' if flags else 'false'}" in io.out
+    assert "Pose prior components: 8" in io.out and io.err.count("has no valid keypoints; skipping.") == 5
+    files = sorted(glob.glob(os.path.join(KPS_DIR, "*.json")))
+    keep = [i for i, f in enumerate(files) if json.load(open(f))]
+    rows = [l.split(",") for l in open(out / "log.csv").read().splitlines()]
+    assert rows[0] == ["frame", "mean_pixel_error_px", "time_ms"] and [int(r[0]) for r in rows[1:]] == keep and len(keep) == 33
+    z = np.load(out / "params.npz")
+    assert list(z["frames"]) == keep and z["usable"].all() and z["cloud"].shape == (33, 6890, 3) and z["cloud"].dtype == np.float32
+    cam = drv.intrinsics(480, 270)
+    kps, nkp = drv.pack_keypoints([drv.load_mp_json(files[i], 480, 270) for i in keep])
+    # the logged error is the pixel error of the driver's own posed joints (6 significant digits in the file)
+    assert np.allclose([float(r[1]) for r in rows[1:]], _px(z["jointPos"], kps, nkp, cam), rtol=1e-5)
+    # oracle, frame by frame
+    R0 = np.tile(drv.initial_root_rotation(), (33, 1))
+    sim3 = np.tile(np.array([1.0, 0, 0, 0, 0, 0, 3.0]), (33, 1))
+    o = omodel.fit_single(ogmm if flags else None, orc.fit_options(mode=1 if flags else 0, max_iters=60, beta_pose=20.0, beta_shape=30.0, cam=cam,
+                                                                 linear_solver=orc.LS_DENSE_CHOLESKY, use_jets=0),
+                          kps, nkp, R0, sim3, np.zeros((33, 10)), nthreads=8)
+    poses = np.concatenate([o["sim3"], o["jointAA"][:, 1:].reshape(33, 69)], axis=1)
+    _, r, p = orc.writeback(poses, R0)
+    c0, jp0, _ = omodel.forward(o["w"], p, r)
+    e0 = _px(jp0, kps, nkp, cam)
+    same = (z["niters"] == o["niters"]) & (z["term"] == o["term"])
+    assert same.sum() >= 30
+    assert np.max(np.abs(z["jointAA"] - o["jointAA"])) < 1e-3 and np.max(np.abs(z["w"] - o["w"])) < 1e-3
+    assert np.max(np.abs(z["sim3"][:, 1:4] - o["sim3"][:, 1:4])) < 1e-3
+    assert np.max(np.abs(z["sim3"][:, 4:7] / z["sim3"][:, :1] - o["sim3"][:, 4:7] / o["sim3"][:, :1])) < 3.5e-3
+    assert np.max(np.abs(z["sim3"][same] - o["sim3"][same])) < 1e-3
+    assert np.max(np.abs(z["px_err"][same] - e0[same]) / np.maximum(1.0, e0[same])) < 1e-3
+    assert np.max(np.abs(z["cloud"][same] - c0[same])) < 2e-3
+
+
+def test_multi_driver_on_fixture(drv, api, orc, gmodel, omodel, model_dir, tmp_path, capsys):
+    out = tmp_path / "out"
+    rc = drv.main_multi(["3dba", model_dir, KPS_DIR, "unused", str(out), "40", "500", "10", "20", "5", "--size", "480x270", "--save-params"])
+    assert rc == 0
+    text = capsys.readouterr().out
+    assert "[INFO] stage-1  anchor frames = 4" in text and "[INFO] window [30,38)" in text and "done." in text
+    rows = [l.split(",") for l in open(out / "log.csv").read().splitlines()][1:]
+    # anchors 0,10,20,30 then windows [0,20) [15,35) [30,38): frames of an overlap are logged once per window
+    assert [int(r[0]) for r in rows] == [0, 10, 20, 30] + list(range(0, 20)) + list(range(15, 35)) + list(range(30, 38))
+    z = np.load(out / "params.npz")
+    files = sorted(glob.glob(os.path.join(KPS_DIR, "*.json")))
+    frames = [drv.load_mp_json(f, 480, 270) for f in files]
+    kps, nkp = drv.pack_keypoints(frames)
+    cam = drv.intrinsics(480, 270)
+    n = len(files)
+    poses0 = np.zeros((n, 76)); poses0[:, 0] = 1.0; poses0[:, 6] = 3.0
+    R00 = np.tile(drv.initial_root_rotation(), (n, 1))
+    g = api.fit_sequences(gmodel, api.fit_opts(cam=cam), api.seq_opts(it1=40), kps, nkp, poses0, R00, np.zeros((n, 10)))
+    for k in ("poses", "R0", "W", "r", "p"):
+        assert np.max(np.abs(z[k] - g[k])) < 1e-9, k
+    o = omodel.fit_sequence(orc.fit_options(mode=1, cam=cam, use_jets=0), orc.SeqOptions(10, 20, 5, 40, 60, 1, 8, 0, 5.0, 25.0, 3.0, 1e5),
+                            kps, nkp, poses0, R00, np.zeros((n, 10)))
+    assert np.max(np.abs(z["poses"][:, 1:4] - o["poses"][:, 1:4])) < 1e-3 and np.max(np.abs(z["poses"][:, 7:] - o["poses"][:, 7:])) < 1e-3
+    assert np.max(np.abs(z["W"] - o["W"])) < 1e-3 and np.max(np.abs(z["R0"] - o["R0"])) < 1e-3
+    # last window's rows are the final state of its frames
+    _, jp, _ = api.smpl_forward(gmodel, z["W"][30:], z["p"][30:], z["r"][30:], dtype=np.float64, want_cloud=False)
+    have = nkp[30:] > 0
+    assert np.allclose(np.array([float(r[1]) for r in rows[-8:]])[have], _px(jp, kps[30:], nkp[30:], cam)[have] if have.all() else
+                       _px(jp[have], kps[30:][have], nkp[30:][have], cam), rtol=1e-5)
+
+
+def test_reference_loop_equals_batched_driver(drv, api, gmodel, ggmm):
+    """The reference's frame loop written with the mirrored per-object interface (Avatar, Sim3Params, Optimize...) gives the
+    same numbers as the batched driver."""
+    files = sorted(glob.glob(os.path.join(KPS_DIR, "*.json")))[:6]
+    frames = [drv.load_mp_json(f, 480, 270) for f in files]
+    fx, fy, cx, cy = drv.intrinsics(480, 270)
+    gmodel.posePrior = ggmm
+    res = drv.run_single(gmodel, frames, 480, 270, 40, 20.0, 30.0, opt_shape=True, use_gmm=True)
+    k = 0
+    for i, kps in enumerate(frames):
+        if not kps:
+            continue
+        av = api.Avatar(gmodel)
+        av.p = np.array([0.0, 0.0, 3.0])
+        av.r[0] = drv.initial_root_rotation()
+        av.update()
+        sim3 = api.Sim3Params(np.array([1.0, 0, 0, 0, av.p[0], av.p[1], av.p[2]]))
+        ok, _ = api.OptimizePoseShapeReprojection(gmodel, av, kps, fx, fy, cx, cy, [q.jid for q in kps], sim3, 40, 20.0, 30.0, ggmm)
+        av.update()
+        assert ok and res["frames"][k] == i
+        assert abs(api.mean_pixel_error(kps, av, fx, fy, cx, cy) - res["px_err"][k]) < 1e-9
+        assert np.array_equal(sim3.data, res["sim3"][k]) and np.array_equal(av.w, res["w"][k])
+        k += 1
+    assert k == len(res["frames"])
