@@ -329,14 +329,15 @@ def main_single(argv=None) -> int:
 # 3dba_multi
 # ---------------------------------------------------------------------------------------------------------
 def run_multi(model, keypoints, W: int, H: int, it1=1000, skip=10, wsize=20, overlap=5, beta_pose=5.0, beta_shape=25.0,
-              lambda_temp=3.0, it2=60, beta_shape_lock=1e5, log=None, echo=None):
+              lambda_temp=3.0, it2=60, beta_shape_lock=1e5, log=None, echo=None, on_solve=None):
     """Anchor stage + sliding windows of src/main_multi_frame.cpp:80-201 for one sequence.
 
     Each OptimizeMultiFrame is one b3d_fit_window call, in the reference's order (the windows overlap, so they are a serial
     chain).  State kept as the reference keeps it: ``poses`` are the FramePoseParams (anchors work on a COPY, :117, so the
     stage-1 result only reaches the avatars), ``R0`` is avatars[i]->r[0] and accumulates R(rootAA) at every write-back
     (MultiFrameBA.h:160-163), ``Wsh`` is avatars[i]->w (shared after stage 1, :154; a window writes its front avatar's).
-    ``log.row(frame, px, ms)`` gets the anchors' rows, then every window's rows, like log.csv."""
+    ``log.row(frame, px, ms)`` gets the anchors' rows, then every window's rows, like log.csv.  ``on_solve(ids, opts, inputs,
+    result)`` (tests) sees every solve's inputs (R0, poses, w as they went in) and its result with the iteration trace."""
     n = len(keypoints)
     fx, fy, cx, cy = cam = intrinsics(W, H)
     kps, nkp = pack_keypoints(keypoints)
@@ -352,8 +353,11 @@ def run_multi(model, keypoints, W: int, H: int, it1=1000, skip=10, wsize=20, ove
     def solve(ids, P, beta_s, iters):
         """OptimizeMultiFrame over frames ``ids`` with pose blocks P; returns usable, updated P.  Writes the avatars back."""
         o = api.fit_opts(FIT_POSE_SHAPE, iters, beta_pose, beta_s, lambda_temp, cam)
+        before = dict(R0=R0[ids].copy(), poses=np.array(P, copy=True), w=Wsh[ids[0]].copy()) if on_solve else None
         t0 = time.perf_counter()
-        res = api.fit_window(model, o, kps[ids], nkp[ids], R0[ids], P, Wsh[ids[0]], want_trace=False)
+        res = api.fit_window(model, o, kps[ids], nkp[ids], R0[ids], P, Wsh[ids[0]], want_trace=on_solve is not None)
+        if on_solve:
+            on_solve(ids, o, before, res)
         R0n, rn, pn = api.writeback(res["poses"], R0[ids])
         ms = (time.perf_counter() - t0) * 1e3
         R0[ids], r[ids], p[ids] = R0n, rn, pn

@@ -40,12 +40,12 @@ def _px(jp, kps, nkp, cam):
 
 
 @pytest.mark.parametrize("flags", [(), ("--opt-shape", "--use-gmm")])
-def test_single_driver_on_fixture(drv, orc, omodel, ogmm, model_dir, tmp_path, flags, capsys):
+def test_single_driver_on_fixture(drv, api, orc, gmodel, ggmm, omodel, ogmm, model_dir, tmp_path, flags, capsys):
     out = tmp_path / "out"
-    rc = drv.main_single(["3dba_single", model_dir, KPS_DIR, "unused", str(out), "60", "--size", "480x270", "--save-params", *flags])
+    rc = drv.main_single(["3dba_single", model_dir, KPS_DIR, "unused", str(out), "--size", "480x270", "--save-params", *flags])
     assert rc == 0
     io = capsys.readouterr()
-    assert f"[ARGS] max_iters=60  beta_pose=20  beta_shape=30  opt_shape={'true' if flags else 'false'}" in io.out
+    assert f"[ARGS] max_iters=100  beta_pose=20  beta_shape=30  opt_shape={'true' if flags else 'false'}" in io.out
     assert "Pose prior components: 8" in io.out and io.err.count("has no valid keypoints; skipping.") == 5
     files = sorted(glob.glob(os.path.join(KPS_DIR, "*.json")))
     keep = [i for i, f in enumerate(files) if json.load(open(f))]
@@ -57,24 +57,42 @@ def test_single_driver_on_fixture(drv, orc, omodel, ogmm, model_dir, tmp_path, f
     kps, nkp = drv.pack_keypoints([drv.load_mp_json(files[i], 480, 270) for i in keep])
     # the logged error is the pixel error of the driver's own posed joints (6 significant digits in the file)
     assert np.allclose([float(r[1]) for r in rows[1:]], _px(z["jointPos"], kps, nkp, cam), rtol=1e-5)
-    # oracle, frame by frame
+    # oracle, frame by frame.  Real detections on the random-init model leave a flat valley (the scale gauge of
+    # test_fit_single_gpu.py plus a weakly observed root rotation): every solve ends with the trust radius at 1e16 and the
+    # oracle's own two linear solvers (QR / Cholesky) stop a few iterations apart.  What is well defined: the minimum reached
+    # (final cost, north_star 1e-4), the joint angles and shape (1e-3), t / s; the root rotation is compared against the
+    # closer of the two oracle variants, with the spread between those two as the yardstick.
     R0 = np.tile(drv.initial_root_rotation(), (33, 1))
     sim3 = np.tile(np.array([1.0, 0, 0, 0, 0, 0, 3.0]), (33, 1))
-    o = omodel.fit_single(ogmm if flags else None, orc.fit_options(mode=1 if flags else 0, max_iters=60, beta_pose=20.0, beta_shape=30.0, cam=cam,
-                                                                 linear_solver=orc.LS_DENSE_CHOLESKY, use_jets=0),
-                          kps, nkp, R0, sim3, np.zeros((33, 10)), nthreads=8)
+    gm = ogmm if flags else None
+    kw = dict(mode=1 if flags else 0, max_iters=100, beta_pose=20.0, beta_shape=30.0, cam=cam)
+    o = omodel.fit_single(gm, orc.fit_options(linear_solver=orc.LS_DENSE_CHOLESKY, use_jets=0, **kw), kps, nkp, R0, sim3, np.zeros((33, 10)), nthreads=8)
+    q = omodel.fit_single(gm, orc.fit_options(linear_solver=orc.LS_DENSE_QR, use_jets=1, **kw), kps, nkp, R0, sim3, np.zeros((33, 10)), nthreads=8)
+    g = api.fit_single_batch(gmodel, ggmm if flags else None, api.fit_opts(**kw), kps, nkp, R0, sim3, np.zeros((33, 10)))
+    for k in ("sim3", "w", "jointAA", "niters", "term"):
+        assert np.array_equal(g[k], z[k]), k                         # the driver is the batched call, nothing else
+    done = (z["term"] == o["term"]) & (o["term"] == q["term"]) & (z["niters"] <= 100)
+    assert done.sum() >= 32                                          # one frame runs into the iteration cap in all three
+    last = lambda res, f: res["trace"][f]["cost"][:res["niters"][f]].min()
+    for f in np.nonzero(done)[0]:
+        assert abs(last(g, f) - last(o, f)) / last(o, f) < 1e-4, f
+        assert np.max(np.abs(z["jointAA"][f] - o["jointAA"][f])) < 1e-3 and np.max(np.abs(z["w"][f] - o["w"][f])) < 1e-3, f
+        assert np.max(np.abs(z["sim3"][f, 4:7] / z["sim3"][f, 0] - o["sim3"][f, 4:7] / o["sim3"][f, 0])) < 3.5e-3, f
+    # root rotation: weakly observed, so judged against the spread between the oracle's own two variants over the frames
+    rot = lambda a, b: np.max(np.abs(a["sim3"][:, 1:4] - b["sim3"][:, 1:4]), axis=1)[done]
+    d, spread = np.minimum(rot(z, o), rot(z, q)), rot(o, q)
+    assert np.mean(d < 1e-3) >= 0.8 and d.max() < 2.0 * max(spread.max(), 5e-3), (d, spread)
+    # mean_pixel_error poses the avatar WITHOUT the fitted scale (include/Utils.h:102-115), so it inherits the gauge: compare
+    # it (and the cloud) where the scale itself agrees
     poses = np.concatenate([o["sim3"], o["jointAA"][:, 1:].reshape(33, 69)], axis=1)
     _, r, p = orc.writeback(poses, R0)
     c0, jp0, _ = omodel.forward(o["w"], p, r)
     e0 = _px(jp0, kps, nkp, cam)
-    same = (z["niters"] == o["niters"]) & (z["term"] == o["term"])
-    assert same.sum() >= 30
-    assert np.max(np.abs(z["jointAA"] - o["jointAA"])) < 1e-3 and np.max(np.abs(z["w"] - o["w"])) < 1e-3
-    assert np.max(np.abs(z["sim3"][:, 1:4] - o["sim3"][:, 1:4])) < 1e-3
-    assert np.max(np.abs(z["sim3"][:, 4:7] / z["sim3"][:, :1] - o["sim3"][:, 4:7] / o["sim3"][:, :1])) < 3.5e-3
-    assert np.max(np.abs(z["sim3"][same] - o["sim3"][same])) < 1e-3
-    assert np.max(np.abs(z["px_err"][same] - e0[same]) / np.maximum(1.0, e0[same])) < 1e-3
-    assert np.max(np.abs(z["cloud"][same] - c0[same])) < 2e-3
+    tight = done & (np.max(np.abs(z["sim3"] - o["sim3"]), axis=1) < 1e-3)
+    assert tight.sum() >= 4, tight.sum()
+    # 1e-3 on t at z = 3 m is 432 / 3 * 1e-3 = 0.15 px
+    assert np.max(np.abs(z["px_err"][tight] - e0[tight])) < 0.2
+    assert np.max(np.abs(z["cloud"][tight] - c0[tight])) < 4e-3
 
 
 def test_multi_driver_on_fixture(drv, api, orc, gmodel, omodel, model_dir, tmp_path, capsys):
@@ -99,13 +117,42 @@ def test_multi_driver_on_fixture(drv, api, orc, gmodel, omodel, model_dir, tmp_p
         assert np.max(np.abs(z[k] - g[k])) < 1e-9, k
     o = omodel.fit_sequence(orc.fit_options(mode=1, cam=cam, use_jets=0), orc.SeqOptions(10, 20, 5, 40, 60, 1, 8, 0, 5.0, 25.0, 3.0, 1e5),
                             kps, nkp, poses0, R00, np.zeros((n, 10)))
-    assert np.max(np.abs(z["poses"][:, 1:4] - o["poses"][:, 1:4])) < 1e-3 and np.max(np.abs(z["poses"][:, 7:] - o["poses"][:, 7:])) < 1e-3
-    assert np.max(np.abs(z["W"] - o["W"])) < 1e-3 and np.max(np.abs(z["R0"] - o["R0"])) < 1e-3
+    # against the oracle's chain: the frames only the first window touches agree to the parameter tolerance.  Further down
+    # the chain the comparison is made solve by solve (next test): 40 + 60 iterations do not converge these real detections
+    # on the random-init model and every window starts from the previous one's result, so end states drift apart.
+    dpose = np.max(np.abs(np.delete(z["poses"] - o["poses"], [0, 4, 5, 6], axis=1)), axis=1)
+    assert dpose[:15].max() < 1e-3 and np.max(np.abs(z["W"] - o["W"])) < 1e-2, dpose
+    assert np.max(np.abs(z["R0"][:15] - o["R0"][:15])) < 1e-3 and np.max(np.abs(z["r"][:15] - o["r"][:15])) < 1e-3
     # last window's rows are the final state of its frames
     _, jp, _ = api.smpl_forward(gmodel, z["W"][30:], z["p"][30:], z["r"][30:], dtype=np.float64, want_cloud=False)
     have = nkp[30:] > 0
     assert np.allclose(np.array([float(r[1]) for r in rows[-8:]])[have], _px(jp, kps[30:], nkp[30:], cam)[have] if have.all() else
                        _px(jp[have], kps[30:][have], nkp[30:][have], cam), rtol=1e-5)
+
+
+def test_multi_driver_every_solve_vs_oracle(drv, api, orc, gmodel, omodel):
+    """Every OptimizeMultiFrame of the chain (anchors, then the three windows) against the oracle started from the SAME state:
+    cost per iteration to 1e-4 while the trust radius is in the stable regime, the minimum reached to 1e-4."""
+    files = sorted(glob.glob(os.path.join(KPS_DIR, "*.json")))
+    frames = [drv.load_mp_json(f, 480, 270) for f in files]
+    kps, nkp = drv.pack_keypoints(frames)
+    cam = drv.intrinsics(480, 270)
+    seen = []
+
+    def on_solve(ids, o, before, res):
+        ref = omodel.fit_window(orc.fit_options(mode=1, cam=cam, linear_solver=orc.LS_BLOCK_TRIDIAG, use_jets=0, max_iters=o.max_iters,
+                                                beta_pose=o.beta_pose, beta_shape=o.beta_shape, lambda_temp=o.lambda_temp),
+                                kps[ids], nkp[ids], before["R0"], before["poses"], before["w"])
+        n = min(res["niters"], ref["niters"])
+        k = int(np.cumprod(ref["trace"]["radius"][:n] <= 1e12).sum())
+        cg, co = res["trace"]["cost"][:k], ref["trace"]["cost"][:k]
+        assert k >= 10 and np.max(np.abs(cg - co) / co) < 1e-4, (ids[0], k)
+        assert abs(res["trace"]["cost"].min() - ref["trace"]["cost"].min()) / ref["trace"]["cost"].min() < 1e-3, ids[0]
+        seen.append((int(ids[0]), len(ids), k, n))
+
+    out = drv.run_multi(gmodel, frames, 480, 270, it1=40, on_solve=on_solve)
+    assert [(s, l) for s, l, _, _ in seen] == [(0, 4), (0, 20), (15, 20), (30, 8)] and out["nfail"] == 0
+    assert len(out["rows"]) == 4 + 20 + 20 + 8
 
 
 def test_reference_loop_equals_batched_driver(drv, api, gmodel, ggmm):
