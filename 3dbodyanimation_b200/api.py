@@ -265,6 +265,36 @@ def mean_pixel_error_batch(kps, nkp, jointPos, cam):
     return err
 
 
+RENDER_NO_CULL = 1   # B3D_RENDER_NO_CULL
+
+
+def render_overlay(model: AvatarModel, cloud, cam, images, backface_cull=True):
+    """smpl::render::renderSMPLMesh (include/RenderSMPLMesh.h:16-110) for B bodies: cloud (B, V, 3) float32 / float64 in camera
+    coordinates, images (B, H, W, 3) uint8 painted in place (and returned).  See b3d_render_overlay for the fill rule."""
+    cloud = np.asarray(cloud)
+    dt = np.float32 if cloud.dtype == np.float32 else np.float64
+    cloud = np.ascontiguousarray(cloud, dtype=dt).reshape(-1, model.numPoints, 3)
+    b = cloud.shape[0]
+    if not (isinstance(images, np.ndarray) and images.dtype == np.uint8 and images.flags.c_contiguous and images.ndim == 4
+            and images.shape[0] == b and images.shape[3] == 3):
+        raise ValueError("images must be a C-contiguous (B, H, W, 3) uint8 array")
+    h, w = images.shape[1:3]
+    check(lib().b3d_render_overlay(model.h, b, F32 if dt == np.float32 else F64, ptr(cloud), C.c_double(cam[0]), C.c_double(cam[1]),
+                                   C.c_double(cam[2]), C.c_double(cam[3]), w, h, 0 if backface_cull else RENDER_NO_CULL, ptr(images)),
+          "b3d_render_overlay")
+    return images
+
+
+def renderSMPLMesh(model: AvatarModel, cloud, img, fx, fy, cx, cy, fill=True, backface_cull=True, wireframe=False):
+    """The reference's call (RenderSMPLMesh.h:16-24) for one body; ``img`` (H, W, 3) uint8 is painted in place.  The face list is
+    the model's.  wireframe = True is not available (both call sites pass false)."""
+    if wireframe:
+        raise NotImplementedError("wireframe overlay (cv::polylines LINE_AA) is not built")
+    if fill:
+        render_overlay(model, np.asarray(cloud)[None], (fx, fy, cx, cy), img[None], backface_cull)
+    return img
+
+
 # ---------------------------------------------------------------------------------------------------------
 # the reference's per-object interface
 # ---------------------------------------------------------------------------------------------------------

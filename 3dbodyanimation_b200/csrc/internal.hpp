@@ -129,6 +129,7 @@ struct b3d_model {
     float* posedirs32 = nullptr;                // [207][3][Vpad] (k, c, v)
     double* posedirs64 = nullptr;
     std::vector<uint32_t> faces;                // host copy (rendering only)
+    int32_t* d_faces = nullptr;                 // F x 3 on the device (render.cu)
 };
 
 struct b3d_gmm {

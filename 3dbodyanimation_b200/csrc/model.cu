@@ -235,7 +235,16 @@ int b3d_model_create(const b3d_model_desc* d, b3d_model** out) {
         if (e == cudaSuccess) e = cudaMemcpy(m->d_sk, &m->sk, sizeof(SkeletonConst), cudaMemcpyHostToDevice);
         if (e != cudaSuccess) rc = set_error(B3D_ECUDA, "skeleton upload: %s", cudaGetErrorString(e));
     }
-    if (!rc && m->F > 0) m->faces.assign(d->faces, d->faces + 3 * (size_t)m->F);
+    if (!rc && m->F > 0) {
+        m->faces.assign(d->faces, d->faces + 3 * (size_t)m->F);
+        for (uint32_t v : m->faces)
+            if (v >= (uint32_t)m->V) { rc = set_error(B3D_EFORMAT, "face index %u out of range (V = %d)", v, m->V); break; }
+        if (!rc) {
+            cudaError_t e = cudaMalloc(&m->d_faces, sizeof(int32_t) * m->faces.size());
+            if (e == cudaSuccess) e = cudaMemcpy(m->d_faces, m->faces.data(), sizeof(int32_t) * m->faces.size(), cudaMemcpyHostToDevice);
+            if (e != cudaSuccess) rc = set_error(B3D_ECUDA, "faces upload: %s", cudaGetErrorString(e));
+        }
+    }
     if (rc) { b3d_model_destroy(m); return rc; }
     *out = m;
     return B3D_OK;
@@ -247,7 +256,7 @@ void b3d_model_destroy(b3d_model* m) {
     cudaFree(m->t64.vert); cudaFree(m->t64.wval); cudaFree(m->t64.wjoint);
     cudaFree(m->ts.vert); cudaFree(m->ts.wval); cudaFree(m->ts.wjoff); cudaFree(m->ts.loc);
     cudaFree(m->ts.rec); cudaFree(m->ts.joff4); cudaFree(m->tc.blob); cudaFree(m->tc.pose_b);
-    cudaFree(m->posedirs32); cudaFree(m->posedirs64); cudaFree(m->d_sk);
+    cudaFree(m->posedirs32); cudaFree(m->posedirs64); cudaFree(m->d_sk); cudaFree(m->d_faces);
     delete m;
 }
 

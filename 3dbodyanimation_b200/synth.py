@@ -92,6 +92,27 @@ def make_model(seed: int = SEED, with_posedirs: bool = False) -> dict:
     return model
 
 
+def make_mesh_faces(model: dict) -> np.ndarray:
+    """A mesh-like face list for the overlay renderer (make_model's ``f`` joins random vertices: fine for the loader, useless
+    as a surface).  The template is 24 blobs of ~287 vertices around the rest joints; each blob is triangulated as a closed
+    star-shaped surface (convex hull of the vertex directions seen from the blob centre = spherical Delaunay), normals
+    outward: 2 n - 4 small triangles per blob, ~13.7 k faces like SMPL's 13,776.  uint32 (F, 3)."""
+    from scipy.spatial import ConvexHull
+    vt = np.asarray(model["v_template"], dtype=np.float64)
+    cluster = np.arange(V) % J
+    out = []
+    for j in range(J):
+        idx = np.nonzero(cluster == j)[0]
+        d = vt[idx] - vt[idx].mean(axis=0)
+        u = d / np.linalg.norm(d, axis=1, keepdims=True)
+        tri = ConvexHull(u).simplices
+        a, b, c = u[tri[:, 0]], u[tri[:, 1]], u[tri[:, 2]]
+        flip = np.einsum("ij,ij->i", np.cross(b - a, c - a), a + b + c) < 0
+        tri[flip] = tri[flip][:, ::-1]
+        out.append(idx[tri])
+    return np.ascontiguousarray(np.concatenate(out), dtype=np.uint32)
+
+
 def load_pose_prior(path: str) -> dict:
     """pose_prior.txt: 'nComps nDims', weights, means (row-major), covariances (scripts/convert_gmm_to_avatar.py:17-29)."""
     with open(path) as fh:

@@ -241,6 +241,24 @@ int b3d_mean_pixel_error_dev(int32_t F, const b3d_kp* kps, const int32_t* nkp, c
                              double cx, double cy, double* err, void* stream);
 
 /* ===================================================================================================== */
+/* Overlay renderer: smpl::render::renderSMPLMesh (include/RenderSMPLMesh.h:16-110; call sites                */
+/* src/main_single_frame.cpp:273-277, src/main_multi_frame.cpp:206-229)                                       */
+/* ===================================================================================================== */
+/* For each of B bodies: project the cloud (camera coordinates) with fx, fy, cx, cy, cull back faces, flat-shade each face
+ * round(220 * clamp(n^ . v^)), and paint the faces far to near into that body's own H x W x 3 uint8 image (in/out: pixels no
+ * face covers keep their value, so the caller's frame is the background).  fill = true, wireframe = false as at both call sites.
+ *   cloud  B x V x 3 of dtype (what b3d_smpl_forward / b3d_fit_frames produce), images B x H x W x 3.
+ * The model must have been created with faces.  Coverage per face is cv::fillConvexPoly's for LINE_8 (the reference passes
+ * LINE_AA: its anti-aliased edge blend is not reproduced); equal-depth ties go to the higher face index; faces with a
+ * projected pixel coordinate beyond +-2^20 are dropped (cv::Point would overflow / OpenCV would walk millions of rows). */
+enum { B3D_RENDER_NO_CULL = 1 /* backface_cull = false */ };
+int b3d_render_overlay(const b3d_model* m, int32_t B, int32_t dtype, const void* cloud, double fx, double fy, double cx,
+                       double cy, int32_t W, int32_t H, uint32_t flags, uint8_t* images);
+/* Same with device pointers, asynchronous on `stream` (scratch planes come from the stream-ordered allocator). */
+int b3d_render_overlay_dev(const b3d_model* m, int32_t B, int32_t dtype, const void* cloud, double fx, double fy, double cx,
+                           double cy, int32_t W, int32_t H, uint32_t flags, uint8_t* images, void* stream);
+
+/* ===================================================================================================== */
 /* The per-frame body of src/main_single_frame.cpp:205-255, batched: fit -> write-back -> update -> pixel error */
 /* ===================================================================================================== */
 /* Reusable device buffers + one CUDA stream, so that repeated calls do not allocate.  Not thread-safe per handle. */

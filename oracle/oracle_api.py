@@ -242,3 +242,28 @@ def map_mediapipe(landmarks, width, height, variant="utils"):
             continue
         out.append((sid, x * width, y * height))
     return out
+
+
+def fill_triangle(img, pts, color):
+    """cv2.fillConvexPoly(img, pts, (color,)*ch, LINE_8) restated (oracle/render.cpp); img H x W x ch uint8, in place."""
+    h, w, ch = img.shape
+    assert img.dtype == np.uint8 and img.flags.c_contiguous
+    xy = np.ascontiguousarray(pts, dtype=np.int32).reshape(6)
+    lib().orc_fill_triangle(_p(img), w, h, ch, _p(xy), int(color))
+    return img
+
+
+def render_overlay(cloud, faces, cam, images, backface_cull=True, want_order=False):
+    """renderSMPLMesh (include/RenderSMPLMesh.h:16-110) for B bodies: cloud (B, V, 3) any float dtype (converted to double exactly),
+    faces (F, 3), images (B, H, W, 3) uint8 modified in place.  Returns (images, drawn (B,), order (B, F) or None)."""
+    cloud = np.ascontiguousarray(cloud, dtype=np.float64)
+    b, v, _ = cloud.shape
+    faces = np.ascontiguousarray(faces, dtype=np.int32)
+    f = faces.shape[0]
+    assert images.dtype == np.uint8 and images.flags.c_contiguous and images.shape[0] == b and images.shape[3] == 3
+    h, w = images.shape[1:3]
+    drawn = np.zeros(b, dtype=np.int32)
+    order = np.zeros((b, f), dtype=np.int32) if want_order else None
+    lib().orc_render_overlay(b, v, f, _p(cloud), _p(faces), C.c_double(cam[0]), C.c_double(cam[1]), C.c_double(cam[2]), C.c_double(cam[3]),
+                             w, h, 1 if backface_cull else 0, _p(images), _p(drawn), _p(order))
+    return images, drawn, order
