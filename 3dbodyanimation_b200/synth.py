@@ -113,6 +113,23 @@ def make_mesh_faces(model: dict) -> np.ndarray:
     return np.ascontiguousarray(np.concatenate(out), dtype=np.uint32)
 
 
+def make_render_model(radius: float = 0.09, seed: int = SEED) -> dict:
+    """make_model() with a smooth skin for the overlay renderer: every blob's vertices are moved onto a sphere of ``radius``
+    metres around the blob centre (directions kept), and ``f`` is make_mesh_faces of that template.  Faces then project to a
+    couple of pixels each at 480 x 270 like SMPL's; the raw random template gives spiky blobs with ~10 x the overdraw."""
+    model = make_model(seed)
+    vt = model["v_template"].astype(np.float64)
+    cluster = np.arange(V) % J
+    for j in range(J):
+        idx = np.nonzero(cluster == j)[0]
+        c = vt[idx].mean(axis=0)
+        d = vt[idx] - c
+        vt[idx] = c + radius * d / np.linalg.norm(d, axis=1, keepdims=True)
+    model = dict(model, v_template=vt.astype(np.float32))
+    model["f"] = make_mesh_faces(model)
+    return model
+
+
 def load_pose_prior(path: str) -> dict:
     """pose_prior.txt: 'nComps nDims', weights, means (row-major), covariances (scripts/convert_gmm_to_avatar.py:17-29)."""
     with open(path) as fh:

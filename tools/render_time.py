@@ -6,7 +6,9 @@ api = importlib.import_module("3dbodyanimation_b200.api"); synth = importlib.imp
 from importlib import import_module
 capi = import_module("3dbodyanimation_b200._capi")
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 2048
-m = synth.make_model(); faces = synth.make_mesh_faces(m); gm = api.AvatarModel(dict(m, f=faces))
+smooth = len(sys.argv) <= 2 or sys.argv[2] != "spiky"
+m = synth.make_render_model() if smooth else synth.make_model()
+faces = m["f"] if smooth else synth.make_mesh_faces(m); gm = api.AvatarModel(dict(m, f=faces))
 fi = synth.make_forward_inputs(B, 3)
 cloud, _, _ = api.smpl_forward(gm, fi["w"], fi["p"], fi["r"], dtype=np.float32)
 W, H = 480, 270
@@ -23,4 +25,4 @@ for _ in range(10): run()
 e1.record(); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / 10
 cov = float((img[:64] != 0).any(dim=3).float().mean())
-print(f"render B={B}: {ms:.3f} ms per call, {B / ms * 1e3:.0f} bodies/s, {ms / B * 1e3:.2f} us/body, coverage {cov:.3f} of the frame")
+print(f"render {'smooth' if smooth else 'spiky'} B={B}: {ms:.3f} ms per call, {B / ms * 1e3:.0f} bodies/s, {ms / B * 1e3:.2f} us/body, coverage {cov:.3f} of the frame")
