@@ -373,6 +373,12 @@ int b3d_render_overlay_dev(const b3d_model* m, int32_t B, int32_t dtype, const v
     B3D_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
     const int grid = B < sms ? B : sms;
     const size_t npix = (size_t)W * H;
+    static std::atomic<int> pool_kept{-1};      // keep the default pool's memory across calls (the planes are ~1.5 MB per SM)
+    if (pool_kept.exchange(dev) != dev) {
+        cudaMemPool_t pool;
+        unsigned long long keep = ~0ull;
+        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+    }
     unsigned long long* z = nullptr;
     B3D_CUDA(cudaMallocAsync((void**)&z, (size_t)grid * npix * 12, st));
     unsigned int* wn = reinterpret_cast<unsigned int*>(z + (size_t)grid * npix);
