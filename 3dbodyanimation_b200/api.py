@@ -13,6 +13,7 @@ lib3dba_b200.so; there is no numpy/CPU fallback.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass, field
 
 import numpy as np
@@ -66,11 +67,53 @@ class AvatarModel:
         self.useJointShapeRegressor = True
         self.posePrior = None      # GaussianMixture or None (AvatarModel.cpp:296 loads pose_prior.txt when present)
 
+    @classmethod
+    def from_npz_native(cls, path: str, with_posedirs: bool = False):
+        """The same model through the library's own .npz reader (b3d_model_load_npz: zip + inflate + .npy parsing in C++ with
+        the array views of external/avatar/AvatarModel.cpp:23-102) instead of numpy."""
+        self = cls.__new__(cls)
+        self._keep = {}
+        h = C.c_void_p()
+        check(lib().b3d_model_load_npz(os.fsencode(path), 1 if with_posedirs else 0, C.byref(h)), "b3d_model_load_npz")
+        self.h = h
+        shp, nd = (C.c_int64 * 4)(), C.c_int32(0)
+        check(lib().b3d_npz_shape(os.fsencode(path), b"shapedirs", C.byref(nd), shp, None, None), "b3d_npz_shape")
+        self.numPoints, self.numJoints, self.numShapeKeys = int(lib().b3d_model_num_verts(h)), NJ, int(shp[2])
+        self.parent = np.zeros(NJ, dtype=np.int32)
+        check(lib().b3d_model_get_parents(self.h, ptr(self.parent)), "b3d_model_get_parents")
+        self.initialJointPos, self.jointShapeReg, self.offset = np.zeros((NJ, 3)), np.zeros((NJ, 3, NS)), np.zeros((NJ, 3))
+        check(lib().b3d_model_get_constants(self.h, ptr(self.initialJointPos), ptr(self.jointShapeReg), ptr(self.offset)),
+              "b3d_model_get_constants")
+        self.useJointShapeRegressor = True
+        self.posePrior = None
+        return self
+
     def __del__(self):
         h = getattr(self, "h", None)
         if h is not None and h.value:
             lib().b3d_model_destroy(h)
             self.h = None
+
+
+def npz_shape(path: str, name: str):
+    """(shape, element bytes, fortran_order) of one member of an .npz, read by the library (no GPU needed)."""
+    shp, nd, ws, fo = (C.c_int64 * 4)(), C.c_int32(0), C.c_int32(0), C.c_int32(0)
+    check(lib().b3d_npz_shape(os.fsencode(path), name.encode(), C.byref(nd), shp, C.byref(ws), C.byref(fo)), "b3d_npz_shape")
+    return tuple(int(shp[i]) for i in range(nd.value)), ws.value, bool(fo.value)
+
+
+def npz_float_matrix(path: str, name: str, rows: int, cols: int) -> np.ndarray:
+    """util::loadFloatMatrix(npz[name], rows, cols) (external/avatar/Util.cpp:249-271), row-major float64."""
+    out = np.zeros((rows, cols))
+    check(lib().b3d_npz_float_matrix(os.fsencode(path), name.encode(), C.c_int64(rows), C.c_int64(cols), ptr(out)), "b3d_npz_float_matrix")
+    return out
+
+
+def npz_uint_matrix(path: str, name: str, rows: int, cols: int) -> np.ndarray:
+    """util::loadUintMatrix(npz[name], rows, cols) (external/avatar/Util.cpp:272-298), row-major uint32."""
+    out = np.zeros((rows, cols), dtype=np.uint32)
+    check(lib().b3d_npz_uint_matrix(os.fsencode(path), name.encode(), C.c_int64(rows), C.c_int64(cols), ptr(out)), "b3d_npz_uint_matrix")
+    return out
 
 
 class GaussianMixture:

@@ -81,6 +81,19 @@ typedef struct b3d_model_desc {
 } b3d_model_desc;
 
 int b3d_model_create(const b3d_model_desc* desc, b3d_model** out);
+
+/* ark::AvatarModel(model_dir)'s npz branch (external/avatar/AvatarModel.cpp:23-102 with cnpy.cpp:67-301 and
+ * Util.cpp:249-309): reads v_template, kintree_table, f, J_regressor, weights, shapedirs from a NumPy .npz (stored or deflated
+ * members, .npy format 1-3, little-endian float32/float64 and 32/64-bit integers, C or Fortran order) with the reference's
+ * array views — v_template is read flat, shapedirs as a (3V x S) matrix, kintree_table row 0 = parents with the root's
+ * 0xFFFFFFFF / -1 — and builds the model.  B3D_NPZ_WITH_POSEDIRS also loads posedirs (the reference has that commented out). */
+enum { B3D_NPZ_WITH_POSEDIRS = 1 };
+int b3d_model_load_npz(const char* path, uint32_t flags, b3d_model** out);
+/* The loader's building blocks (host only, usable without a GPU): shape / element width / order of a member, and the
+ * (rows x cols) views of Util.cpp's loadFloatMatrix / loadUintMatrix (row-major out). */
+int b3d_npz_shape(const char* path, const char* name, int32_t* ndim, int64_t* shape4, int32_t* word_size, int32_t* fortran_order);
+int b3d_npz_float_matrix(const char* path, const char* name, int64_t rows, int64_t cols, double* out);
+int b3d_npz_uint_matrix(const char* path, const char* name, int64_t rows, int64_t cols, uint32_t* out);
 void b3d_model_destroy(b3d_model* m);
 int b3d_model_num_verts(const b3d_model* m);
 /* parent[24], bit-exact indexing output (AvatarModel.cpp:35-41). */
