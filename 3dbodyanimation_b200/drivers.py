@@ -13,8 +13,11 @@ reference.  What differs, on purpose:
   * 3dba_single fits ALL frames of the folder in ONE batched call (the frames are independent: each one starts from a fresh
     avatar, src/main_single_frame.cpp:205-221), so ``time_ms`` is the batch time divided by the number of fitted frames —
     the same convention the reference's multi-frame driver uses for its anchors and windows (main_multi_frame.cpp:146,190).
-  * nothing is rendered: the overlay PNGs need OpenCV and the rasteriser (SURVEY §8 marks both out of scope).  With
-    ``--save-params`` the fitted parameters (and optionally the float32 clouds) go to ``out_dir/params.npz`` instead.
+  * the overlays (``frame_<i>_render.png`` / ``frame_<i>_multi.png``) come from the CUDA rasteriser (b3d_render_overlay): same
+    triangles, colours and order as renderSMPLMesh, OpenCV's LINE_8 coverage instead of LINE_AA; frames are
+    decoded here (PNG) or by Pillow (JPEG / BMP) instead of cv::imread, RGB instead of BGR (the overlay is grey either way).
+    ``--no-render`` skips them; ``--save-params`` also writes the fitted parameters (and for ``single`` the float32 clouds) to
+    ``out_dir/params.npz``.  Models without a face list (``f``) cannot be rendered: use ``--no-render``.
 Every computation goes through lib3dba_b200.so (api.py); there is no CPU path here.
 """
 from __future__ import annotations
@@ -82,6 +85,108 @@ def image_size(path: str) -> tuple[int, int]:
                     return int(w), int(h)
                 f.seek(n - 2, 1)
     raise ValueError(f"Failed to read {path}")
+
+
+def write_png(path: str, img: np.ndarray) -> None:
+    """(H, W, 3) uint8 RGB -> 8-bit truecolour PNG (zlib only; stands in for cv::imwrite)."""
+    import zlib
+    img = np.ascontiguousarray(img, dtype=np.uint8)
+    h, w, _ = img.shape
+
+    def chunk(tag, data):
+        return struct.pack(">I", len(data)) + tag + data + struct.pack(">I", zlib.crc32(tag + data))
+
+    raw = np.concatenate([np.zeros((h, 1), dtype=np.uint8), img.reshape(h, w * 3)], axis=1).tobytes()
+    with open(path, "wb") as f:
+        f.write(b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, 2, 0, 0, 0)) +
+                chunk(b"IDAT", zlib.compress(raw, 6)) + chunk(b"IEND", b""))
+
+
+def _read_png(path: str):
+    """Non-interlaced 8-bit grey / RGB / RGBA PNG -> (H, W, 3) uint8, or None when the file is another flavour."""
+    import zlib
+    data = open(path, "rb").read()
+    if data[:8] != b"\x89PNG\r\n\x1a\n":
+        return None
+    pos, idat, hdr = 8, [], None
+    while pos + 8 <= len(data):
+        n, tag = struct.unpack(">I", data[pos:pos + 4])[0], data[pos + 4:pos + 8]
+        body = data[pos + 8:pos + 8 + n]
+        if tag == b"IHDR":
+            hdr = struct.unpack(">IIBBBBB", body)
+        elif tag == b"IDAT":
+            idat.append(body)
+        elif tag == b"IEND":
+            break
+        pos += 12 + n
+    if hdr is None or hdr[2] != 8 or hdr[3] not in (0, 2, 6) or hdr[6] != 0:
+        return None
+    w, h, ch = hdr[0], hdr[1], {0: 1, 2: 3, 6: 4}[hdr[3]]
+    raw = np.frombuffer(zlib.decompress(b"".join(idat)), dtype=np.uint8).reshape(h, 1 + w * ch)
+    out = np.zeros((h, w * ch), dtype=np.uint8)
+    prev = np.zeros(w * ch, dtype=np.int32)
+    for y in range(h):
+        ft, line = int(raw[y, 0]), raw[y, 1:].astype(np.int32)
+        if ft == 0:
+            cur = line
+        elif ft == 2:
+            cur = (line + prev) & 255
+        else:                                  # Sub / Average / Paeth depend on the pixel to the left: byte by byte
+            cur = np.zeros(w * ch, dtype=np.int32)
+            for i in range(w * ch):
+                a = cur[i - ch] if i >= ch else 0
+                b, c = prev[i], (prev[i - ch] if i >= ch else 0)
+                if ft == 1:
+                    pr = a
+                elif ft == 3:
+                    pr = (a + b) >> 1
+                else:
+                    pa, pb, pc = abs(b - c), abs(a - c), abs(a + b - 2 * c)
+                    pr = a if (pa <= pb and pa <= pc) else (b if pb <= pc else c)
+                cur[i] = (line[i] + pr) & 255
+        out[y] = cur
+        prev = cur
+    out = out.reshape(h, w, ch)
+    return np.repeat(out, 3, axis=2) if ch == 1 else np.ascontiguousarray(out[:, :, :3])
+
+
+def read_image(path: str) -> np.ndarray:
+    """cv::imread stand-in: (H, W, 3) uint8 RGB.  PNG is decoded here; JPEG / BMP (and exotic PNGs) through Pillow when it is
+    installed.  Raises ValueError otherwise (the caller then paints over a black frame)."""
+    if os.path.splitext(path)[1].lower() == ".png":
+        img = _read_png(path)
+        if img is not None:
+            return img
+    try:
+        from PIL import Image
+    except ImportError as e:
+        raise ValueError(f"Failed to read {path}: no decoder for this format") from e
+    with Image.open(path) as im:
+        return np.ascontiguousarray(np.asarray(im.convert("RGB"), dtype=np.uint8))
+
+
+def _background(images, i, W, H):
+    if images is not None and i < len(images):
+        try:
+            img = read_image(images[i])
+            if img.shape[:2] == (H, W):
+                return img
+            print(f"[WARN] {images[i]} is {img.shape[1]}x{img.shape[0]}, expected {W}x{H}; painting over black", file=sys.stderr)
+        except ValueError as e:
+            print(f"[WARN] {e}", file=sys.stderr)
+    return np.zeros((H, W, 3), dtype=np.uint8)
+
+
+def render_frames(model, clouds, frame_ids, images, W, H, out_dir, suffix, chunk=64):
+    """renderSMPLMesh(cloud, faces, frame.clone(), fx, fy, cx, cy, fill, cull, no wireframe) + imwrite for each fitted frame
+    (main_single_frame.cpp:271-277 -> frame_<i>_render.png, main_multi_frame.cpp:206-229 -> frame_<i>_multi.png)."""
+    cam = intrinsics(W, H)
+    for s in range(0, len(frame_ids), chunk):
+        ids = frame_ids[s:s + chunk]
+        imgs = np.stack([_background(images, int(i), W, H) for i in ids])
+        api.render_overlay(model, clouds[s:s + chunk], cam, imgs)
+        for k, i in enumerate(ids):
+            write_png(os.path.join(out_dir, f"frame_{int(i)}_{suffix}.png"), imgs[k])
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -250,15 +355,17 @@ def run_single(model, keypoints, W: int, H: int, max_iters=100, beta_pose=20.0, 
 
 def main_single(argv=None) -> int:
     argv = list(sys.argv if argv is None else argv)
-    size, save = None, False
+    size, save, render = None, False, True
     rest = []
     it = iter(argv[1:])
-    for a in it:                                   # two extensions, both optional and absent from the reference's CLI
+    for a in it:                                   # three extensions, all optional and absent from the reference's CLI
         if a == "--size":
             wh = next(it, "").lower().split("x")
             size = (int(wh[0]), int(wh[1]))
         elif a == "--save-params":
             save = True
+        elif a == "--no-render":
+            render = False
         else:
             rest.append(a)
     if len(rest) < 4:
@@ -312,7 +419,7 @@ def main_single(argv=None) -> int:
             print(f"Frame {i} has no valid keypoints; skipping.", file=sys.stderr)
         frames.append(k)
     print(f"Pose prior components: {model.posePrior.nComps}  (GMM {'ON' if use_gmm else 'OFF'})")
-    res = run_single(model, frames, W, H, max_iters, beta_pose, beta_shape, opt_shape, use_gmm, want_cloud=save)
+    res = run_single(model, frames, W, H, max_iters, beta_pose, beta_shape, opt_shape, use_gmm, want_cloud=save or render)
     n = len(res["frames"])
     log = _Log(out_dir)
     for k, i in enumerate(res["frames"]):
@@ -321,6 +428,8 @@ def main_single(argv=None) -> int:
     if save and n:
         np.savez(os.path.join(out_dir, "params.npz"), **{k: res[k] for k in
                  ("frames", "sim3", "w", "jointAA", "r", "p", "jointPos", "px_err", "usable", "niters", "term", "cloud") if k in res})
+    if render and n:
+        render_frames(model, res["cloud"], res["frames"], images, W, H, out_dir, "render")
     print("Done.")
     return 0
 
@@ -402,7 +511,7 @@ def run_multi(model, keypoints, W: int, H: int, it1=1000, skip=10, wsize=20, ove
 
 def main_multi(argv=None) -> int:
     argv = list(sys.argv if argv is None else argv)
-    size, save = None, False
+    size, save, render = None, False, True
     rest = []
     it = iter(argv[1:])
     for a in it:
@@ -411,6 +520,8 @@ def main_multi(argv=None) -> int:
             size = (int(wh[0]), int(wh[1]))
         elif a == "--save-params":
             save = True
+        elif a == "--no-render":
+            render = False
         else:
             rest.append(a)
     if len(rest) < 4:
@@ -459,6 +570,10 @@ def main_multi(argv=None) -> int:
     log.close()
     if save:
         np.savez(os.path.join(out_dir, "params.npz"), **{k: res[k] for k in ("poses", "R0", "W", "r", "p")})
+    if render:
+        clouds, _, _ = api.smpl_forward(model, res["W"], res["p"], res["r"], dtype=np.float32)
+        render_frames(model, clouds, np.arange(len(frames)), images, W, H, out_dir, "multi")
+        print(f"[INFO] rendering finished, saved to  \"{out_dir}\"")
     print("done.")
     return 0
 

@@ -7,6 +7,7 @@ import os
 import struct
 import zlib
 
+import numpy as np
 import pytest
 
 from conftest import GOLDEN, pkg
@@ -110,3 +111,21 @@ def test_usage_and_missing_inputs(drv, tmp_path, capsys):
     assert "No JSON files in" in capsys.readouterr().err
     assert drv.main_multi(["3dba", "m.npz", str(tmp_path / "kps"), str(tmp_path / "img"), str(tmp_path / "out")]) == 1
     assert "image / json count mismatch" in capsys.readouterr().err
+
+
+def test_png_round_trip_and_foreign_pngs(drv, tmp_path):
+    rng = np.random.default_rng(0)
+    img = rng.integers(0, 256, size=(37, 53, 3), dtype=np.uint8)
+    drv.write_png(str(tmp_path / "a.png"), img)
+    assert drv.image_size(str(tmp_path / "a.png")) == (53, 37)
+    assert np.array_equal(drv.read_image(str(tmp_path / "a.png")), img)
+    PIL = pytest.importorskip("PIL.Image")
+    assert np.array_equal(np.asarray(PIL.open(tmp_path / "a.png").convert("RGB")), img)       # a standard decoder reads what we write
+    smooth = np.stack([np.add.outer(np.arange(40), np.arange(64)) % 256] * 3, axis=2).astype(np.uint8)
+    smooth[..., 1] = smooth[..., 1] // 2
+    PIL.fromarray(smooth).save(tmp_path / "b.png", optimize=True)                             # adaptive filters (Sub / Up / Avg / Paeth)
+    assert np.array_equal(drv.read_image(str(tmp_path / "b.png")), smooth)
+    PIL.fromarray(smooth[..., 0]).save(tmp_path / "g.png")                                    # greyscale
+    assert np.array_equal(drv.read_image(str(tmp_path / "g.png")), np.repeat(smooth[..., :1], 3, axis=2))
+    PIL.fromarray(smooth).save(tmp_path / "c.jpg", quality=95)                                # JPEG goes through Pillow
+    assert drv.read_image(str(tmp_path / "c.jpg")).shape == (40, 64, 3) and drv.image_size(str(tmp_path / "c.jpg")) == (64, 40)

@@ -25,9 +25,11 @@ def drv(api):
 
 
 @pytest.fixture(scope="module")
-def model_dir(tmp_path_factory, model_np):
+def model_dir(tmp_path_factory, model_np, synth):
     d = tmp_path_factory.mktemp("avatar-model")
-    np.savez(d / "model.npz", **{k: v for k, v in model_np.items() if k != "posedirs"})
+    m = {k: v for k, v in model_np.items() if k != "posedirs"}
+    m["f"] = synth.make_mesh_faces(model_np)          # a surface instead of make_model's random vertex triples: overlays get drawn
+    np.savez(d / "model.npz", **m)
     shutil.copy(PRIOR_TXT, d / "pose_prior.txt")
     return str(d)
 
@@ -53,6 +55,14 @@ def test_single_driver_on_fixture(drv, api, orc, gmodel, ggmm, omodel, ogmm, mod
     assert rows[0] == ["frame", "mean_pixel_error_px", "time_ms"] and [int(r[0]) for r in rows[1:]] == keep and len(keep) == 33
     z = np.load(out / "params.npz")
     assert list(z["frames"]) == keep and z["usable"].all() and z["cloud"].shape == (33, 6890, 3) and z["cloud"].dtype == np.float32
+    # overlays: one PNG per fitted frame, black background (no frames given), equal to the oracle's renderSMPLMesh of the same cloud
+    pngs = sorted(p.name for p in out.glob("frame_*_render.png"))
+    assert pngs == sorted(f"frame_{i}_render.png" for i in keep)
+    faces = np.load(os.path.join(model_dir, "model.npz"))["f"]
+    pick = [0, 16, 32]
+    ref, drawn, _ = orc.render_overlay(z["cloud"][pick], faces, drv.intrinsics(480, 270), np.zeros((3, 270, 480, 3), np.uint8))
+    for k, b in enumerate(pick):
+        assert np.array_equal(drv.read_image(str(out / f"frame_{keep[b]}_render.png")), ref[k]) and drawn[k] > 1000
     cam = drv.intrinsics(480, 270)
     kps, nkp = drv.pack_keypoints([drv.load_mp_json(files[i], 480, 270) for i in keep])
     # the logged error is the pixel error of the driver's own posed joints (6 significant digits in the file)
@@ -97,9 +107,16 @@ def test_single_driver_on_fixture(drv, api, orc, gmodel, ggmm, omodel, ogmm, mod
 
 def test_multi_driver_on_fixture(drv, api, orc, gmodel, omodel, model_dir, tmp_path, capsys):
     out = tmp_path / "out"
-    rc = drv.main_multi(["3dba", model_dir, KPS_DIR, "unused", str(out), "40", "500", "10", "20", "5", "--size", "480x270", "--save-params"])
+    # frames on disk this time: 38 PNGs whose header gives the size and whose pixels are the overlays' background
+    frames_dir = tmp_path / "frames"
+    frames_dir.mkdir()
+    yy, xx = np.mgrid[0:270, 0:480]
+    for i in range(38):
+        drv.write_png(str(frames_dir / f"frame_{i:04d}.png"), np.stack([(xx + i) % 256, yy % 256, (xx // 2 + yy) % 256], axis=2).astype(np.uint8))
+    rc = drv.main_multi(["3dba", model_dir, KPS_DIR, str(frames_dir), str(out), "40", "500", "10", "20", "5", "--save-params"])
     assert rc == 0
     text = capsys.readouterr().out
+    assert len(list(out.glob("frame_*_multi.png"))) == 38 and "rendering finished" in text
     assert "[INFO] stage-1  anchor frames = 4" in text and "[INFO] window [30,38)" in text and "done." in text
     rows = [l.split(",") for l in open(out / "log.csv").read().splitlines()][1:]
     # anchors 0,10,20,30 then windows [0,20) [15,35) [30,38): frames of an overlap are logged once per window
@@ -123,6 +140,11 @@ def test_multi_driver_on_fixture(drv, api, orc, gmodel, omodel, model_dir, tmp_p
     dpose = np.max(np.abs(np.delete(z["poses"] - o["poses"], [0, 4, 5, 6], axis=1)), axis=1)
     assert dpose[:15].max() < 1e-3 and np.max(np.abs(z["W"] - o["W"])) < 1e-2, dpose
     assert np.max(np.abs(z["R0"][:15] - o["R0"][:15])) < 1e-3 and np.max(np.abs(z["r"][:15] - o["r"][:15])) < 1e-3
+    # overlay of the last frame = oracle's renderSMPLMesh of the final avatar over that frame's picture
+    c37, _, _ = api.smpl_forward(gmodel, z["W"][37:], z["p"][37:], z["r"][37:], dtype=np.float32)
+    faces = np.load(os.path.join(model_dir, "model.npz"))["f"]
+    ref, _, _ = orc.render_overlay(c37, faces, cam, drv.read_image(str(frames_dir / "frame_0037.png"))[None].copy())
+    assert np.array_equal(drv.read_image(str(out / "frame_37_multi.png")), ref[0])
     # last window's rows are the final state of its frames
     _, jp, _ = api.smpl_forward(gmodel, z["W"][30:], z["p"][30:], z["r"][30:], dtype=np.float64, want_cloud=False)
     have = nkp[30:] > 0
