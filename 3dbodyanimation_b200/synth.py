@@ -317,3 +317,40 @@ def forward_numpy(model: dict, w: np.ndarray, p: np.ndarray, r: np.ndarray, use_
     T = np.einsum("vj,jab->vab", wt, G)
     cloud = np.einsum("vab,vb->va", T[:, :, :3], shaped) + T[:, :, 3]
     return cloud, posed, G.transpose(0, 2, 1).reshape(J, 12)
+
+
+def make_icp_inputs(model: dict, b: int, seed: int, *, ndata: int | None = None, noise: float = 0.02, miss: float = 0.2) -> dict:
+    """Inputs of AvatarOptimizer's ICP term (external/avatar/AvatarOptimizer.cpp:1246-1460) for b bodies: state (w, p, unit
+    quaternions q in Eigen's (x, y, z, w) order), a data cloud per body (a perturbed, differently posed copy of the model cloud,
+    shuffled) and correspondences in the reference's shape: per model point a list of data points (here 0, 1 or 2 of them; a
+    fraction `miss` of the model points has none), flattened to pairs (mpt, dpt) with per-body offsets cptr / dptr."""
+    rng = np.random.default_rng(seed)
+    V = model["v_template"].shape[0]
+    nd = V if ndata is None else ndata
+    fin = make_forward_inputs(b, seed + 1)
+    aa = rng.normal(0.0, 0.3, size=(b, J, 3))
+    th = np.linalg.norm(aa, axis=-1, keepdims=True)
+    q = np.concatenate([np.sin(th / 2) * aa / np.maximum(th, 1e-300), np.cos(th / 2)], axis=-1)
+    tgt = make_forward_inputs(b, seed + 2)
+    cloud = [forward_numpy(model, fin["w"][i] + 0.3 * tgt["w"][i], fin["p"][i], tgt["r"][i])[0] for i in range(b)]
+    data, mpt, dpt, cptr, dptr = [], [], [], [0], [0]
+    for i in range(b):
+        src = rng.integers(0, V, nd)                       # data point k is a noisy sample of model point src[k]
+        data.append(cloud[i][src] + rng.normal(0.0, noise, (nd, 3)))
+        keep = rng.random(nd) > miss
+        m = src[keep]
+        d = np.nonzero(keep)[0]
+        order = np.argsort(m, kind="stable")               # the reference walks model points in order (:1396-1405)
+        mpt.append(m[order]); dpt.append(d[order])
+        cptr.append(cptr[-1] + len(m)); dptr.append(dptr[-1] + nd)
+    return dict(w=fin["w"], p=fin["p"], q=q, data=np.concatenate(data), mpt=np.concatenate(mpt).astype(np.int32),
+                dpt=np.concatenate(dpt).astype(np.int32), cptr=np.array(cptr, dtype=np.int64), dptr=np.array(dptr, dtype=np.int64))
+
+
+def quat_to_r(q: np.ndarray) -> np.ndarray:
+    """Unit quaternions (..., 4) in (x, y, z, w) order -> col-major 3x3 (..., 9) (Eigen toRotationMatrix)."""
+    x, y, z, w = q[..., 0], q[..., 1], q[..., 2], q[..., 3]
+    R = np.stack([1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w),
+                  2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w),
+                  2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)], axis=-1).reshape(q.shape[:-1] + (3, 3))
+    return np.ascontiguousarray(np.swapaxes(R, -1, -2)).reshape(q.shape[:-1] + (9,))

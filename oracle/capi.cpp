@@ -262,6 +262,25 @@ int orc_fit_sequence(void* mp, const FitOptions* base, const SeqOptions* so, int
     return nfail;
 }
 
+// vertex-level ICP term (icp.cpp): B bodies, each with ncorr[b] correspondences starting at cptr[b]; data cloud of body b
+// starts at point dptr[b].  Outputs per body: cost, grad (85); resid / jac only for B == 1 style calls (may be null).
+void orc_icp_eval(void* mp, int B, const double* w, const double* p, const double* q, const int64_t* cptr, const int32_t* mpt,
+                  const int32_t* dpt, const int64_t* dptr, const double* data, int shape_enabled, double* resid, double* jac,
+                  double* cost, double* grad, int nthreads) {
+    const Model& M = *(Model*)mp;
+    const int NC = 3 + 3 * M.J + M.S;
+#pragma omp parallel for num_threads(nthreads > 0 ? nthreads : 1) schedule(dynamic, 1)
+    for (int b = 0; b < B; ++b) {
+        const int64_t c0 = cptr[b];
+        const int n = (int)(cptr[b + 1] - c0);
+        icp_eval(M, w + (size_t)b * M.S, p + 3 * (size_t)b, q + 4 * (size_t)M.J * b, n, mpt + c0, dpt + c0, data + 3 * dptr[b],
+                 shape_enabled, resid ? resid + 3 * c0 : nullptr, jac ? jac + 3 * c0 * NC : nullptr, cost + b, grad + (size_t)b * NC);
+    }
+}
+void orc_quat_plus(int n, const double* x, const double* d, double* out) {
+    for (int i = 0; i < n; ++i) quat_plus(x + 4 * i, d + 3 * i, out + 4 * i);
+}
+
 int orc_sizeof_iter_record() { return (int)sizeof(IterRecord); }
 int orc_sizeof_fit_options() { return (int)sizeof(FitOptions); }
 int orc_sizeof_kp() { return (int)sizeof(KP); }

@@ -212,4 +212,13 @@ bool fit_window(const Model& M, const FitOptions& o, int F, const KP* kps, const
 // rest-pose offsets (Sim3BA.h:533-555): offset[3j+c] = J0_j - J0_parent (w=0); offset[0]=0
 void rest_offsets(const Model& M, double* offset /*3J*/);
 
+// ---------------------------------------------------------------------------------------------
+// Vertex-level ICP residuals + analytic Jacobians of ark::AvatarOptimizer (icp.cpp; AvatarOptimizer.cpp:161-641)
+// q: J quaternions, Eigen coefficient order (x, y, z, w).  corr e = (model point mpt[e], data point dpt[e]).
+// resid 3 x ncorr, jac (3 ncorr) x (3 + 3J + S) row-major, grad 3 + 3J + S: any may be null.
+// ---------------------------------------------------------------------------------------------
+void icp_eval(const Model& M, const double* w, const double* p, const double* q, int ncorr, const int* mpt, const int* dpt,
+              const double* data, int shape_enabled, double* resid, double* jac, double* cost, double* grad);
+void quat_plus(const double* x, const double* delta, double* out);   // FakeQuaternionParameterization::Plus
+
 }  // namespace orc

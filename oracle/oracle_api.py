@@ -100,6 +100,21 @@ class Model:
         lib().orc_forward(self.h, b, _p(w), _p(p), _p(r), _p(cloud), _p(jp), _p(jt), nthreads)
         return cloud, jp, jt
 
+    def icp_eval(self, w, p, q, cptr, mpt, dpt, dptr, data, shape=True, want_jac=False, nthreads=1):
+        """AvatarOptimizer's ICP term: cost (B,), grad (B, 85) [p | 24 x 3 rotation tangents | 10 shape]; with want_jac also
+        resid (ncorr, 3) and the dense Jacobian (ncorr, 3, 85)."""
+        w, p, q, data = _f64(w), _f64(p), _f64(q), _f64(data)
+        b = w.shape[0]
+        cptr, dptr = np.ascontiguousarray(cptr, dtype=np.int64), np.ascontiguousarray(dptr, dtype=np.int64)
+        mpt, dpt = np.ascontiguousarray(mpt, dtype=np.int32), np.ascontiguousarray(dpt, dtype=np.int32)
+        nc = 3 + 3 * self.J + self.S
+        cost, grad = np.zeros(b), np.zeros((b, nc))
+        resid = np.zeros((int(cptr[-1]), 3)) if want_jac else None
+        jac = np.zeros((int(cptr[-1]), 3, nc)) if want_jac else None
+        lib().orc_icp_eval(self.h, b, _p(w), _p(p), _p(q), _p(cptr), _p(mpt), _p(dpt), _p(dptr), _p(data), int(shape), _p(resid),
+                           _p(jac), _p(cost), _p(grad), nthreads)
+        return dict(cost=cost, grad=grad, resid=resid, jac=jac)
+
     def reproj_check(self, with_shape, jid, u, v, cam, R0, x86):
         out = [np.zeros(2), np.zeros(2), np.zeros((2, NFULL)), np.zeros(2), np.zeros((2, NFULL))]
         lib().orc_reproj_check(self.h, int(with_shape), int(jid), C.c_double(u), C.c_double(v), _p(_f64(cam)), _p(_f64(R0)),
@@ -176,6 +191,14 @@ class GMM:
         out = np.zeros(self.nDims + 1)
         c = lib().orc_gmm_residual(self.h, _p(_f64(x)), _p(out))
         return out, c
+
+
+def quat_plus(x, d):
+    """FakeQuaternionParameterization::Plus on n quaternions (x, y, z, w)."""
+    x, d = _f64(x).reshape(-1, 4), _f64(d).reshape(-1, 3)
+    out = np.zeros_like(x)
+    lib().orc_quat_plus(x.shape[0], _p(x), _p(d), _p(out))
+    return out
 
 
 def aa_to_matrix(aa):

@@ -1,0 +1,53 @@
+"""Oracle self-checks for the vertex-level ICP term (oracle/icp.cpp restating
+external/avatar/AvatarOptimizer.cpp:161-641).  No reference golden vectors exist for this path (parity unpinned): the analytic
+Jacobians are pinned by central differences through the reference's own Plus() and the residuals by Avatar::update."""
+import numpy as np
+
+
+def _one(synth, model_np, seed=5, nd=600):
+    return synth.make_icp_inputs(model_np, 1, seed, ndata=nd)
+
+
+def test_icp_residual_is_cloud_minus_data(synth, orc, model_np):
+    om = orc.Model(model_np)
+    x = _one(synth, model_np)
+    out = om.icp_eval(x["w"], x["p"], x["q"], x["cptr"], x["mpt"], x["dpt"], x["dptr"], x["data"], want_jac=True)
+    cloud, _, _ = om.forward(x["w"], x["p"], synth.quat_to_r(x["q"]))
+    ref = cloud[0][x["mpt"]] - x["data"][x["dpt"]]
+    assert np.max(np.abs(out["resid"] - ref)) < 1e-12
+    assert abs(out["cost"][0] - 0.5 * np.sum(ref ** 2)) < 1e-10 * out["cost"][0]
+    g = np.einsum("erc,er->c", out["jac"], out["resid"])
+    assert np.max(np.abs(g - out["grad"][0])) < 1e-9 * np.max(np.abs(g))
+
+
+def test_icp_jacobian_matches_central_differences_through_plus(synth, orc, model_np):
+    om = orc.Model(model_np)
+    x = _one(synth, model_np, seed=8, nd=300)
+    args = (x["cptr"], x["mpt"], x["dpt"], x["dptr"], x["data"])
+    base = om.icp_eval(x["w"], x["p"], x["q"], *args, want_jac=True)
+    jac = base["jac"]
+    h = 1e-6
+
+    def resid(delta):
+        p = x["p"] + delta[:3]
+        q = orc.quat_plus(x["q"][0], delta[3:75].reshape(24, 3))[None]
+        w = x["w"] + delta[75:]
+        return om.icp_eval(w, p, q, *args, want_jac=True)["resid"]
+
+    worst = 0.0
+    for k in range(85):
+        d = np.zeros(85); d[k] = h
+        num = (resid(d) - resid(-d)) / (2 * h)
+        worst = max(worst, float(np.max(np.abs(num - jac[:, :, k]))))
+    assert worst < 1e-7 * max(1.0, float(np.max(np.abs(jac)))), worst
+    # the quaternions stay unit under Plus
+    assert np.allclose(np.linalg.norm(orc.quat_plus(x["q"][0], np.full((24, 3), 0.3)), axis=1), 1.0)
+
+
+def test_icp_pose_only_has_no_shape_columns(synth, orc, model_np):
+    om = orc.Model(model_np)
+    x = _one(synth, model_np, seed=9, nd=200)
+    a = om.icp_eval(x["w"], x["p"], x["q"], x["cptr"], x["mpt"], x["dpt"], x["dptr"], x["data"], shape=False)
+    b = om.icp_eval(x["w"], x["p"], x["q"], x["cptr"], x["mpt"], x["dpt"], x["dptr"], x["data"], shape=True)
+    assert np.all(a["grad"][:, 75:] == 0.0) and np.allclose(a["grad"][:, :75], b["grad"][:, :75], rtol=0, atol=1e-12)
+    assert np.any(b["grad"][:, 75:] != 0.0)
