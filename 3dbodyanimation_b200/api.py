@@ -428,3 +428,41 @@ def mean_pixel_error(kps, avatar: Avatar, fx, fy, cx, cy) -> float:
     """include/Utils.h:102-115 (uses the avatar's posed joints: scale is not applied)."""
     arr, nkp = _kp_array(kps)
     return float(mean_pixel_error_batch(arr, nkp, avatar.jointPos[None], (fx, fy, cx, cy))[0])
+
+
+class IcpProblem:
+    """The ICP data term of ark::AvatarOptimizer::optimize for a batch of bodies with fixed correspondences (one ICP iteration,
+    external/avatar/AvatarOptimizer.cpp:1386-1412): model point mpt[e] <-> point dpt[e] of body b's data cloud for e in
+    [cptr[b], cptr[b+1]), the cloud of body b starting at point dptr[b] of ``data``.  ``eval`` returns what Ceres' line-search
+    minimiser asks the problem for at a state (w, p, q): the cost and its gradient in the tangent space of the parameter blocks
+    (p | 24 quaternions under FakeQuaternionParameterization | w)."""
+
+    def __init__(self, model: AvatarModel, cptr, mpt, dpt, dptr, data, dtype=np.float32):
+        dt = np.dtype(dtype)
+        self.model = model
+        self.cptr = np.ascontiguousarray(cptr, dtype=np.int64)
+        self.dptr = np.ascontiguousarray(dptr, dtype=np.int64)
+        self.B = self.cptr.shape[0] - 1
+        mpt = np.ascontiguousarray(mpt, dtype=np.int32)
+        dpt = np.ascontiguousarray(dpt, dtype=np.int32)
+        data = np.ascontiguousarray(data, dtype=dt).reshape(-1, 3)
+        if mpt.shape[0] != self.cptr[-1] or dpt.shape[0] != self.cptr[-1] or data.shape[0] != self.dptr[-1]:
+            raise ValueError("IcpProblem: offsets do not match the pair / data arrays")
+        if mpt.size and (mpt.min() < 0 or mpt.max() >= model.numPoints):
+            raise ValueError("IcpProblem: model point out of range")
+        h = C.c_void_p()
+        check(lib().b3d_icp_create(model.h, self.B, F64 if dt == np.float64 else F32, ptr(self.cptr), ptr(mpt), ptr(dpt),
+                                   ptr(self.dptr), ptr(data), 0, C.byref(h)), "b3d_icp_create")
+        self.h = h
+
+    def __del__(self):
+        h = getattr(self, "h", None)
+        if h is not None and h.value:
+            lib().b3d_icp_destroy(h)
+            self.h = None
+
+    def eval(self, w, p, q, shape=True):
+        w, p, q = _f64(w).reshape(self.B, NS), _f64(p).reshape(self.B, 3), _f64(q).reshape(self.B, NJ, 4)
+        cost, grad = np.empty(self.B), np.empty((self.B, 85))
+        check(lib().b3d_icp_eval(self.h, ptr(w), ptr(p), ptr(q), 0 if shape else 2, ptr(cost), ptr(grad)), "b3d_icp_eval")
+        return dict(cost=cost, grad=grad)

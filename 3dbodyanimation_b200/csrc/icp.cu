@@ -1,0 +1,475 @@
+// Entry (3): vertex-level ICP term of ark::AvatarOptimizer — cost and gradient of
+//     sum over correspondences (i, e) of 1/2 | cloud_i(w, p, q) - data_e |^2
+// in the tangent space of the reference's parameter blocks (root position | 24 quaternions under
+// FakeQuaternionParameterization::Plus | 10 shape keys), for a batch of bodies.  Replaces, for this term,
+//   AvatarEvaluationCommonData::PrepareForEvaluation   external/avatar/AvatarOptimizer.cpp:295-362
+//   AvatarCostFunctorCache::updateData                 external/avatar/AvatarOptimizer.cpp:503-577
+//   AvatarICPCostFunctor::Evaluate                     external/avatar/AvatarOptimizer.cpp:621-637
+//   and the J^T r assembly Ceres does for its line-search (BFGS) minimiser (:1318-1321).
+//
+// Not a translation of the reference's tables.  With G_k / g_k the posed rotation / position of joint k and
+// P_ik = G_k (x_i - J_k) + g_k the image of vertex i under joint k, the reference's per-ancestor Jacobian block
+// R(-1, parent j) * dRot(v) * localJacobian_j equals -2 [d_ij]x G_parent(j), d_ij = sum_{k assigned to i below j} w_ik (P_ik - g_j)
+// (the quaternion pseudo-Jacobian only ever meets tangent directions).  The gradient therefore needs no ancestor lists and no
+// joint-pair tables: per assigned joint k two 3-vectors are accumulated over the vertices,
+//     a_k = sum_i w_ik P_ik x rs_i,   b_k = sum_i w_ik rs_i          (rs_i = sum of vertex i's residuals)
+// and a per-body epilogue sums them over subtrees: grad_rot_j = 2 G_parent(j)^T (A_j - g_j x B_j).  The shape gradient is
+//     sum_i D_i^T (T_i^T rs_i) - sum_k S_k^T G_k^T b_k + sum_{j>=1} (S_j - S_parent(j))^T G_parent(j)^T B_j,
+// T_i = sum_k w_ik G_k being the skinning matrix the forward pass forms anyway.
+//
+// Kernels:
+//   icp_gather_kernel / icp_targets_kernel / icp_scatter_kernel : once per set of correspondences (they stay fixed over a whole
+//       ceres::Solve, :1439).  A vertex with n matches d_e contributes n |P - mean|^2 + sum |d_e - mean|^2, so the data cloud
+//       is reduced to one (mean, n) record per vertex and a per-body constant; the records are stored body-minor
+//       [body group][vertex][32 bodies] so that a warp whose lanes are bodies reads them with one coalesced request.
+//   icp_accumulate_kernel<T> : the fused shape blend + skinning + residual + gradient pass.  lane = body, the vertex is warp
+//       uniform: model data are broadcast loads, a body's 24 transforms live in shared memory [entry][lane] (conflict free) and
+//       are cached in registers while consecutive vertices keep the joint of a weight slot, all sums over vertices are per-lane
+//       register / shared accumulators — no shuffles, no atomics inside the loop.  HBM traffic: 16 B (float) per vertex and body.
+//   icp_finish_kernel : the per-body epilogue above, float64.
+#include <algorithm>
+#include <vector>
+
+#include "internal.hpp"
+
+struct b3d_icp {
+    const b3d_model* m = nullptr;
+    int B = 0, dtype = 0, groups = 0;
+    void* tgt = nullptr;        // [groups][V][32] x (mean xyz, n) of T
+    double* scatter = nullptr;  // [B] sum |d - mean|^2
+    double* acc = nullptr;      // [B][ICP_ACC]
+    double* state = nullptr;    // device copies for the host-pointer call: w | p | q | cost | grad
+    double *r = nullptr, *jp = nullptr, *jt = nullptr;
+    int64_t npairs = 0;
+};
+
+namespace b3d {
+
+constexpr int ICP_NC = 3 + 3 * NJ + NS;      // 85 tangent coordinates
+constexpr int ICP_ACC = 16 + 6 * NJ;         // cost, grad_p(3), shape part (10), pad(2), bins [24][6]
+constexpr int ICP_TPAD = 33;                 // row stride of the staged transforms (conflict-free staging and use)
+
+// ---------------------------------------------------------------------------------------------------------------------
+// correspondence reduction
+// ---------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ int body_of_pair(const int64_t* __restrict__ cptr, int B, int64_t e) {
+    int lo = 0, hi = B;   // cptr[lo] <= e < cptr[hi]
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (cptr[mid] <= e) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) icp_gather_kernel(int B, int V, const int64_t* __restrict__ cptr, const int64_t* __restrict__ dptr,
+                                                         const int32_t* __restrict__ mpt, const int32_t* __restrict__ dpt,
+                                                         const T* __restrict__ data, double* __restrict__ tmp) {
+    const int64_t n = cptr[B];
+    for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < n; e += (int64_t)gridDim.x * blockDim.x) {
+        const int b = body_of_pair(cptr, B, e);
+        const T* d = data + 3 * (dptr[b] + dpt[e]);
+        double* t = tmp + 4 * ((size_t)b * V + mpt[e]);
+        atomicAdd(t + 0, (double)d[0]);
+        atomicAdd(t + 1, (double)d[1]);
+        atomicAdd(t + 2, (double)d[2]);
+        atomicAdd(t + 3, 1.0);
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) icp_targets_kernel(int B, int V, double* __restrict__ tmp, T* __restrict__ tgt) {
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= (size_t)B * V) return;
+    const int b = (int)(i / V), v = (int)(i % V);
+    double* t = tmp + 4 * i;
+    const double n = t[3], inv = n > 0.0 ? 1.0 / n : 0.0;
+    t[0] *= inv; t[1] *= inv; t[2] *= inv;
+    T* o = tgt + 4 * (((size_t)(b >> 5) * V + v) * 32 + (b & 31));
+    o[0] = (T)t[0]; o[1] = (T)t[1]; o[2] = (T)t[2]; o[3] = (T)n;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) icp_scatter_kernel(int B, int V, const int64_t* __restrict__ cptr, const int64_t* __restrict__ dptr,
+                                                          const int32_t* __restrict__ mpt, const int32_t* __restrict__ dpt,
+                                                          const T* __restrict__ data, const double* __restrict__ tmp,
+                                                          double* __restrict__ scatter) {
+    const int64_t n = cptr[B];
+    const int64_t span = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t e0 = blockIdx.x * (int64_t)blockDim.x; e0 < n; e0 += span) {
+        const int64_t e = e0 + threadIdx.x;
+        int b = -1;
+        double s = 0.0;
+        if (e < n) {
+            b = body_of_pair(cptr, B, e);
+            const T* d = data + 3 * (dptr[b] + dpt[e]);
+            const double* mu = tmp + 4 * ((size_t)b * V + mpt[e]);   // float64 mean (icp_targets_kernel)
+            const double ax = (double)d[0] - mu[0], ay = (double)d[1] - mu[1], az = (double)d[2] - mu[2];
+            s = ax * ax + ay * ay + az * az;
+        }
+        // one atomic per warp when the warp's pairs belong to one body
+        const int b0 = __shfl_sync(0xffffffffu, b, 0);
+        if (__all_sync(0xffffffffu, b == b0)) {
+#pragma unroll
+            for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+            if ((threadIdx.x & 31) == 0 && b0 >= 0) atomicAdd(scatter + b0, s);
+        } else if (b >= 0) {
+            atomicAdd(scatter + b, s);
+        }
+    }
+}
+
+// quaternions (x, y, z, w) -> column-major rotation matrices (Eigen toRotationMatrix, as the optimiser applies them :326)
+__global__ void __launch_bounds__(256) icp_quat_kernel(int n, const double* __restrict__ q, double* __restrict__ r) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double x = q[4 * i], y = q[4 * i + 1], z = q[4 * i + 2], w = q[4 * i + 3];
+    const double tx = 2 * x, ty = 2 * y, tz = 2 * z;
+    const double twx = tx * w, twy = ty * w, twz = tz * w, txx = tx * x, txy = ty * x, txz = tz * x, tyy = ty * y, tyz = tz * y, tzz = tz * z;
+    double* o = r + 9 * (size_t)i;
+    o[0] = 1 - (tyy + tzz); o[3] = txy - twz;       o[6] = txz + twy;
+    o[1] = txy + twz;       o[4] = 1 - (txx + tzz); o[7] = tyz - twx;
+    o[2] = txz - twy;       o[5] = tyz + twx;       o[8] = 1 - (txx + tyy);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// fused shape blend + skinning + residual + gradient accumulation.  grid = (body groups of 32, vertex splits)
+// ---------------------------------------------------------------------------------------------------------------------
+template <typename T> struct Vec4T;
+template <> struct Vec4T<float> { using type = float4; };
+template <> struct Vec4T<double> { using type = double4; };
+
+template <typename T, int NW, int NWARPS>
+__global__ void __launch_bounds__(32 * NWARPS, 1) icp_accumulate_kernel(const T* __restrict__ vert, const T* __restrict__ wval,
+                                                                        const int32_t* __restrict__ wjoint, int V, int Vpad, int B,
+                                                                        const double* __restrict__ wshape, const double* __restrict__ jointTrans,
+                                                                        const T* __restrict__ tgt, double* __restrict__ acc) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    T* sT = reinterpret_cast<T*>(smem_raw);                 // [NJ * 12][ICP_TPAD]
+    T* sBin = sT + NJ * 12 * ICP_TPAD;                      // [NWARPS][NJ * 6][32]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int b0 = blockIdx.x * 32;
+    const int b = min(b0 + lane, B - 1);
+    // stage the group's transforms: sT[e][body]
+    for (int i = threadIdx.x; i < 32 * NJ * 12; i += 32 * NWARPS) {
+        const int bl = i / (NJ * 12), e = i - bl * (NJ * 12);
+        sT[e * ICP_TPAD + bl] = (T)jointTrans[(size_t)min(b0 + bl, B - 1) * NJ * 12 + e];
+    }
+    T* bins = sBin + (size_t)warp * NJ * 6 * 32;
+    for (int i = lane; i < NJ * 6 * 32; i += 32) bins[i] = (T)0;
+    T ws[NS];
+#pragma unroll
+    for (int s = 0; s < NS; ++s) ws[s] = (T)wshape[(size_t)b * NS + s];
+    __syncthreads();
+
+    // vertex range of this CTA, then of this warp
+    const int per_cta = (V + gridDim.y - 1) / gridDim.y;
+    const int c0 = blockIdx.y * per_cta, c1 = min(V, c0 + per_cta);
+    const int per_warp = (max(c1 - c0, 0) + NWARPS - 1) / NWARPS;
+    const int v0 = c0 + warp * per_warp, v1 = min(c1, v0 + per_warp);
+
+    T cost = 0, gp[3] = {0, 0, 0}, sh[NS];
+#pragma unroll
+    for (int s = 0; s < NS; ++s) sh[s] = 0;
+    int curj[NW];
+    T G[NW][12], bin[NW][6];
+#pragma unroll
+    for (int k = 0; k < NW; ++k) {
+        curj[k] = -1;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) bin[k][c] = 0;
+#pragma unroll
+        for (int c = 0; c < 12; ++c) G[k][c] = 0;
+    }
+    using V4 = typename Vec4T<T>::type;
+    const V4* tg = reinterpret_cast<const V4*>(tgt) + ((size_t)blockIdx.x * V) * 32 + lane;
+
+    for (int v = v0; v < v1; ++v) {
+        const V4 mu = tg[(size_t)v * 32];
+        // shape blend (AvatarOptimizer.cpp:263-264); D kept for the shape gradient
+        T x[3], D[3][NS];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            T a = __ldg(vert + (size_t)c * Vpad + v);
+#pragma unroll
+            for (int s = 0; s < NS; ++s) {
+                D[c][s] = __ldg(vert + (size_t)(3 + NS * c + s) * Vpad + v);
+                a += D[c][s] * ws[s];
+            }
+            x[c] = a;
+        }
+        T wt[NW], Pk[NW][3], P[3] = {0, 0, 0}, Tm[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+        for (int k = 0; k < NW; ++k) {
+            wt[k] = __ldg(wval + (size_t)k * Vpad + v);
+            if ((double)wt[k] > 1e-12) {   // assignedJoints keeps weights > 1e-12 (AvatarModel.cpp:81)
+                const int jk = __ldg(wjoint + (size_t)k * Vpad + v);
+                if (jk != curj[k]) {       // warp-uniform: the vertex is
+                    if (curj[k] >= 0) {
+#pragma unroll
+                        for (int c = 0; c < 6; ++c) { bins[(curj[k] * 6 + c) * 32 + lane] += bin[k][c]; bin[k][c] = 0; }
+                    }
+                    curj[k] = jk;
+#pragma unroll
+                    for (int c = 0; c < 12; ++c) G[k][c] = sT[(jk * 12 + c) * ICP_TPAD + lane];
+                }
+#pragma unroll
+                for (int r = 0; r < 3; ++r) {
+                    Pk[k][r] = G[k][r] * x[0] + G[k][3 + r] * x[1] + G[k][6 + r] * x[2] + G[k][9 + r];
+                    P[r] += wt[k] * Pk[k][r];
+                }
+#pragma unroll
+                for (int c = 0; c < 9; ++c) Tm[c] += wt[k] * G[k][c];
+            }
+        }
+        // sum of the vertex's residuals and its cost share
+        const T n = mu.w;
+        const T e0 = P[0] - mu.x, e1 = P[1] - mu.y, e2 = P[2] - mu.z;
+        const T rs[3] = {n * e0, n * e1, n * e2};
+        cost += n * (e0 * e0 + e1 * e1 + e2 * e2);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) gp[c] += rs[c];
+        // shape: D^T (T^T rs)
+        const T y0 = Tm[0] * rs[0] + Tm[1] * rs[1] + Tm[2] * rs[2];
+        const T y1 = Tm[3] * rs[0] + Tm[4] * rs[1] + Tm[5] * rs[2];
+        const T y2 = Tm[6] * rs[0] + Tm[7] * rs[1] + Tm[8] * rs[2];
+#pragma unroll
+        for (int s = 0; s < NS; ++s) sh[s] += D[0][s] * y0 + D[1][s] * y1 + D[2][s] * y2;
+#pragma unroll
+        for (int k = 0; k < NW; ++k) {
+            if ((double)wt[k] > 1e-12) {
+                const T wr[3] = {wt[k] * rs[0], wt[k] * rs[1], wt[k] * rs[2]};
+                bin[k][0] += Pk[k][1] * wr[2] - Pk[k][2] * wr[1];
+                bin[k][1] += Pk[k][2] * wr[0] - Pk[k][0] * wr[2];
+                bin[k][2] += Pk[k][0] * wr[1] - Pk[k][1] * wr[0];
+                bin[k][3] += wr[0]; bin[k][4] += wr[1]; bin[k][5] += wr[2];
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < NW; ++k)
+        if (curj[k] >= 0) {
+#pragma unroll
+            for (int c = 0; c < 6; ++c) bins[(curj[k] * 6 + c) * 32 + lane] += bin[k][c];
+        }
+    __syncthreads();
+    // dense accumulators through the (now free) transform area: sD[warp][14][32]
+    T* sD = sT;
+    sD[(warp * 14 + 0) * 32 + lane] = cost;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) sD[(warp * 14 + 1 + c) * 32 + lane] = gp[c];
+#pragma unroll
+    for (int s = 0; s < NS; ++s) sD[(warp * 14 + 4 + s) * 32 + lane] = sh[s];
+    __syncthreads();
+    for (int i = threadIdx.x; i < (14 + NJ * 6) * 32; i += 32 * NWARPS) {
+        const int e = i >> 5, l = i & 31;
+        if (b0 + l >= B) continue;
+        double s = 0.0;
+        if (e < 14) {
+#pragma unroll
+            for (int wq = 0; wq < NWARPS; ++wq) s += (double)sD[(wq * 14 + e) * 32 + l];
+        } else {
+#pragma unroll
+            for (int wq = 0; wq < NWARPS; ++wq) s += (double)sBin[((size_t)wq * NJ * 6 + (e - 14)) * 32 + l];
+        }
+        if (s != 0.0) atomicAdd(acc + (size_t)(b0 + l) * ICP_ACC + (e < 14 ? e : e + 2), s);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// per-body epilogue (float64): subtree sums, tangent-space gradient, cost
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(64) icp_finish_kernel(const SkeletonConst* __restrict__ sk, int B, int shape_enabled,
+                                                        const double* __restrict__ acc, const double* __restrict__ scatter,
+                                                        const double* __restrict__ jointPos, const double* __restrict__ jointTrans,
+                                                        double* __restrict__ cost, double* __restrict__ grad) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= B) return;
+    const double* a = acc + (size_t)b * ICP_ACC;
+    const double* G = jointTrans + (size_t)b * NJ * 12;   // per joint col-major [G | t]
+    const double* g = jointPos + (size_t)b * NJ * 3;
+    double* out = grad + (size_t)b * ICP_NC;
+    cost[b] = 0.5 * (a[0] + scatter[b]);
+    for (int c = 0; c < 3; ++c) out[c] = a[1 + c];
+    double A[NJ][3], Bs[NJ][3], sg[NS];
+    for (int s = 0; s < NS; ++s) sg[s] = a[4 + s];
+    for (int k = 0; k < NJ; ++k)
+        for (int c = 0; c < 3; ++c) { A[k][c] = a[16 + 6 * k + c]; Bs[k][c] = a[16 + 6 * k + 3 + c]; }
+    if (shape_enabled) {
+        // - sum_k S_k^T (G_k^T b_k), b_k before the subtree sums
+        for (int k = 0; k < NJ; ++k) {
+            double y[3];
+            for (int c = 0; c < 3; ++c) y[c] = G[12 * k + 3 * c] * Bs[k][0] + G[12 * k + 3 * c + 1] * Bs[k][1] + G[12 * k + 3 * c + 2] * Bs[k][2];
+            for (int s = 0; s < NS; ++s)
+                sg[s] -= sk->JSR[(3 * k) * NS + s] * y[0] + sk->JSR[(3 * k + 1) * NS + s] * y[1] + sk->JSR[(3 * k + 2) * NS + s] * y[2];
+        }
+    }
+    for (int j = NJ - 1; j >= 1; --j) {   // parents precede children (model.cu checks parent[j] < j)
+        const int pa = sk->parent[j];
+        for (int c = 0; c < 3; ++c) { A[pa][c] += A[j][c]; Bs[pa][c] += Bs[j][c]; }
+    }
+    for (int j = 0; j < NJ; ++j) {
+        const double* gj = g + 3 * j;
+        const double tq[3] = {A[j][0] - (gj[1] * Bs[j][2] - gj[2] * Bs[j][1]), A[j][1] - (gj[2] * Bs[j][0] - gj[0] * Bs[j][2]),
+                              A[j][2] - (gj[0] * Bs[j][1] - gj[1] * Bs[j][0])};
+        if (j == 0) {
+            for (int c = 0; c < 3; ++c) out[3 + c] = 2.0 * tq[c];
+        } else {
+            const double* Gp = G + 12 * sk->parent[j];
+            for (int c = 0; c < 3; ++c) out[3 + 3 * j + c] = 2.0 * (Gp[3 * c] * tq[0] + Gp[3 * c + 1] * tq[1] + Gp[3 * c + 2] * tq[2]);
+            if (shape_enabled) {   // + (S_j - S_parent)^T G_parent^T B_j
+                const int pa = sk->parent[j];
+                double y[3];
+                for (int c = 0; c < 3; ++c) y[c] = Gp[3 * c] * Bs[j][0] + Gp[3 * c + 1] * Bs[j][1] + Gp[3 * c + 2] * Bs[j][2];
+                for (int s = 0; s < NS; ++s)
+                    for (int c = 0; c < 3; ++c) sg[s] += (sk->JSR[(3 * j + c) * NS + s] - sk->JSR[(3 * pa + c) * NS + s]) * y[c];
+            }
+        }
+    }
+    for (int s = 0; s < NS; ++s) out[3 + 3 * NJ + s] = shape_enabled ? sg[s] : 0.0;
+}
+
+template <typename T>
+static int icp_reduce(b3d_icp* h, const int64_t* d_cptr, const int64_t* d_dptr, const int32_t* d_mpt, const int32_t* d_dpt, const T* d_data) {
+    const b3d_model* m = h->m;
+    const int B = h->B, V = m->V;
+    double* tmp = nullptr;
+    const size_t tmp_bytes = sizeof(double) * 4 * (size_t)B * V, tgt_bytes = sizeof(T) * 4 * 32 * (size_t)h->groups * V;
+    B3D_CUDA(cudaMalloc(&tmp, tmp_bytes));
+    cudaError_t e = cudaMemsetAsync(tmp, 0, tmp_bytes, nullptr);
+    if (e == cudaSuccess) e = cudaMemsetAsync(h->tgt, 0, tgt_bytes, nullptr);
+    if (e == cudaSuccess) e = cudaMemsetAsync(h->scatter, 0, sizeof(double) * B, nullptr);
+    if (e != cudaSuccess) { cudaFree(tmp); return set_error(B3D_ECUDA, "b3d_icp_create: %s", cudaGetErrorString(e)); }
+    const int pair_blocks = (int)std::min<int64_t>(std::max<int64_t>((h->npairs + 255) / 256, 1), 148 * 16);
+    icp_gather_kernel<T><<<pair_blocks, 256>>>(B, V, d_cptr, d_dptr, d_mpt, d_dpt, d_data, tmp);
+    count_launch();
+    icp_targets_kernel<T><<<(unsigned)(((size_t)B * V + 255) / 256), 256>>>(B, V, tmp, (T*)h->tgt);
+    count_launch();
+    icp_scatter_kernel<T><<<pair_blocks, 256>>>(B, V, d_cptr, d_dptr, d_mpt, d_dpt, d_data, tmp, h->scatter);
+    count_launch();
+    e = cudaStreamSynchronize(nullptr);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    cudaFree(tmp);
+    if (e != cudaSuccess) return set_error(B3D_ECUDA, "b3d_icp_create: %s", cudaGetErrorString(e));
+    return B3D_OK;
+}
+
+template <typename T, int NW, int NWARPS>
+static int launch_accumulate(const b3d_icp* h, const VertexTables<T>& t, const double* w, cudaStream_t st) {
+    const b3d_model* m = h->m;
+    const size_t smem = sizeof(T) * ((size_t)NJ * 12 * ICP_TPAD + (size_t)NWARPS * NJ * 6 * 32);
+    static bool attr_done = false;
+    if (!attr_done) {
+        B3D_CUDA(cudaFuncSetAttribute(icp_accumulate_kernel<T, NW, NWARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_done = true;
+    }
+    // enough CTAs for two waves of the 148 SMs when the batch is small; one CTA per body group when it is large
+    const int vsplit = std::max(1, std::min(32, (2 * 148 + h->groups - 1) / h->groups));
+    icp_accumulate_kernel<T, NW, NWARPS><<<dim3(h->groups, vsplit), 32 * NWARPS, smem, st>>>(t.vert, t.wval, t.wjoint, m->V, m->Vpad, h->B, w,
+                                                                                             h->jt, (const T*)h->tgt, h->acc);
+    B3D_LAUNCH_CHECK();
+    return B3D_OK;
+}
+
+}  // namespace b3d
+
+using namespace b3d;
+
+extern "C" {
+
+int b3d_icp_create(const b3d_model* m, int32_t B, int32_t dtype, const int64_t* cptr, const int32_t* mpt, const int32_t* dpt,
+                   const int64_t* dptr, const void* data, int32_t flags, b3d_icp** out) {
+    if (!m || !cptr || !mpt || !dpt || !dptr || !data || !out) return set_error(B3D_EINVAL, "b3d_icp_create: null argument");
+    if (B <= 0) return set_error(B3D_EINVAL, "b3d_icp_create: B <= 0");
+    if (dtype != B3D_F32 && dtype != B3D_F64) return set_error(B3D_EINVAL, "b3d_icp_create: bad dtype %d", dtype);
+    if (m->nw != 4 && m->nw != 8) return set_error(B3D_EINVAL, "b3d_icp_create: models with more than 8 weights per vertex are not supported (nw = %d)", m->nw);
+    if (int rc = require_device()) return rc;
+    for (int b = 0; b < B; ++b)
+        if (cptr[b + 1] < cptr[b] || dptr[b + 1] < dptr[b]) return set_error(B3D_EINVAL, "b3d_icp_create: offsets of body %d decrease", b);
+    const int64_t np = cptr[B], nd = dptr[B];
+    const size_t es = dtype == B3D_F32 ? 4 : 8;
+    b3d_icp* h = new b3d_icp();
+    h->m = m; h->B = B; h->dtype = dtype; h->groups = (B + 31) / 32; h->npairs = np;
+    const bool dev_in = (flags & B3D_ICP_DEVICE_INPUT) != 0;
+    int64_t *d_cptr = nullptr, *d_dptr = nullptr;
+    int32_t *d_mpt = nullptr, *d_dpt = nullptr;
+    void* d_data = nullptr;
+    cudaError_t e = cudaMalloc(&h->tgt, es * 4 * 32 * (size_t)h->groups * m->V);
+    if (e == cudaSuccess) e = cudaMalloc(&h->scatter, sizeof(double) * B);
+    if (e == cudaSuccess) e = cudaMalloc(&h->acc, sizeof(double) * (size_t)B * ICP_ACC);
+    if (e == cudaSuccess) e = cudaMalloc(&h->state, sizeof(double) * (size_t)B * (NS + 3 + 4 * NJ + 1 + ICP_NC));
+    if (e == cudaSuccess) e = cudaMalloc(&h->r, sizeof(double) * (size_t)B * NJ * 9);
+    if (e == cudaSuccess) e = cudaMalloc(&h->jp, sizeof(double) * (size_t)B * NJ * 3);
+    if (e == cudaSuccess) e = cudaMalloc(&h->jt, sizeof(double) * (size_t)B * NJ * 12);
+    if (e == cudaSuccess) e = cudaMalloc(&d_cptr, sizeof(int64_t) * 2 * (B + 1));
+    if (e == cudaSuccess) {
+        d_dptr = d_cptr + B + 1;
+        e = cudaMemcpy(d_cptr, cptr, sizeof(int64_t) * (B + 1), cudaMemcpyHostToDevice);
+    }
+    if (e == cudaSuccess) e = cudaMemcpy(d_dptr, dptr, sizeof(int64_t) * (B + 1), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && !dev_in) {
+        e = cudaMalloc(&d_mpt, sizeof(int32_t) * 2 * (size_t)std::max<int64_t>(np, 1));
+        if (e == cudaSuccess) { d_dpt = d_mpt + std::max<int64_t>(np, 1); e = cudaMalloc(&d_data, es * 3 * (size_t)std::max<int64_t>(nd, 1)); }
+        if (e == cudaSuccess) e = cudaMemcpy(d_mpt, mpt, sizeof(int32_t) * np, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMemcpy(d_dpt, dpt, sizeof(int32_t) * np, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess) e = cudaMemcpy(d_data, data, es * 3 * nd, cudaMemcpyHostToDevice);
+    }
+    int rc = B3D_OK;
+    if (e != cudaSuccess) rc = set_error(B3D_ECUDA, "b3d_icp_create: %s", cudaGetErrorString(e));
+    if (!rc) {
+        const int32_t* pm = dev_in ? mpt : d_mpt;
+        const int32_t* pd = dev_in ? dpt : d_dpt;
+        const void* pdat = dev_in ? data : d_data;
+        rc = dtype == B3D_F32 ? icp_reduce<float>(h, d_cptr, d_dptr, pm, pd, (const float*)pdat)
+                              : icp_reduce<double>(h, d_cptr, d_dptr, pm, pd, (const double*)pdat);
+    }
+    cudaFree(d_cptr); cudaFree(d_mpt); cudaFree(d_data);
+    if (rc) { b3d_icp_destroy(h); return rc; }
+    *out = h;
+    return B3D_OK;
+}
+
+void b3d_icp_destroy(b3d_icp* h) {
+    if (!h) return;
+    cudaFree(h->tgt); cudaFree(h->scatter); cudaFree(h->acc); cudaFree(h->state); cudaFree(h->r); cudaFree(h->jp); cudaFree(h->jt);
+    delete h;
+}
+
+int b3d_icp_eval_dev(b3d_icp* h, const double* w, const double* p, const double* q, int32_t flags, double* cost, double* grad,
+                     void* stream) {
+    if (!h || !w || !p || !q || !cost || !grad) return set_error(B3D_EINVAL, "b3d_icp_eval: null argument");
+    cudaStream_t st = (cudaStream_t)stream;
+    const b3d_model* m = h->m;
+    const int B = h->B;
+    icp_quat_kernel<<<(B * NJ + 255) / 256, 256, 0, st>>>(B * NJ, q, h->r);
+    B3D_LAUNCH_CHECK();
+    if (int rc = b3d_smpl_forward_dev(m, B, B3D_F64, w, p, h->r, nullptr, h->jp, h->jt, 0, st)) return rc;
+    B3D_CUDA(cudaMemsetAsync(h->acc, 0, sizeof(double) * (size_t)B * ICP_ACC, st));
+    int rc;
+    if (h->dtype == B3D_F32)
+        rc = m->nw == 4 ? launch_accumulate<float, 4, 8>(h, m->t32, w, st) : launch_accumulate<float, 8, 8>(h, m->t32, w, st);
+    else
+        rc = m->nw == 4 ? launch_accumulate<double, 4, 4>(h, m->t64, w, st) : launch_accumulate<double, 8, 4>(h, m->t64, w, st);
+    if (rc) return rc;
+    icp_finish_kernel<<<(B + 63) / 64, 64, 0, st>>>(m->d_sk, B, (flags & B3D_ICP_POSE_ONLY) ? 0 : 1, h->acc, h->scatter, h->jp, h->jt, cost, grad);
+    B3D_LAUNCH_CHECK();
+    return B3D_OK;
+}
+
+int b3d_icp_eval(b3d_icp* h, const double* w, const double* p, const double* q, int32_t flags, double* cost, double* grad) {
+    if (!h || !w || !p || !q || !cost || !grad) return set_error(B3D_EINVAL, "b3d_icp_eval: null argument");
+    const size_t B = (size_t)h->B;
+    double *dw = h->state, *dp = dw + B * NS, *dq = dp + B * 3, *dc = dq + B * 4 * NJ, *dg = dc + B;
+    B3D_CUDA(cudaMemcpy(dw, w, sizeof(double) * B * NS, cudaMemcpyHostToDevice));
+    B3D_CUDA(cudaMemcpy(dp, p, sizeof(double) * B * 3, cudaMemcpyHostToDevice));
+    B3D_CUDA(cudaMemcpy(dq, q, sizeof(double) * B * 4 * NJ, cudaMemcpyHostToDevice));
+    if (int rc = b3d_icp_eval_dev(h, dw, dp, dq, flags, dc, dg, nullptr)) return rc;
+    B3D_CUDA(cudaStreamSynchronize(nullptr));
+    B3D_CUDA(cudaMemcpy(cost, dc, sizeof(double) * B, cudaMemcpyDeviceToHost));
+    B3D_CUDA(cudaMemcpy(grad, dg, sizeof(double) * B * ICP_NC, cudaMemcpyDeviceToHost));
+    return B3D_OK;
+}
+
+int b3d_icp_num_bodies(const b3d_icp* h) { return h ? h->B : 0; }
+
+}  // extern "C"

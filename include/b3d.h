@@ -146,6 +146,35 @@ int b3d_smpl_forward_dev(const b3d_model* m, int32_t B, int32_t dtype, const voi
                          void* cloud, void* jointPos, void* jointTrans, int32_t flags, void* stream);
 
 /* ===================================================================================================== */
+/* Entry (3) vertex-level ICP term of ark::AvatarOptimizer: cost and gradient of       */
+/*   sum over correspondences 1/2 |cloud_i(w, p, q) - data_e|^2 for a batch of bodies.  Replaces            */
+/*   AvatarEvaluationCommonData::PrepareForEvaluation (external/avatar/AvatarOptimizer.cpp:295-362),        */
+/*   AvatarCostFunctorCache::updateData (:503-577), AvatarICPCostFunctor::Evaluate (:621-637) and the       */
+/*   J^T r assembly of Ceres' line-search minimiser (:1318-1321).                                           */
+/* ===================================================================================================== */
+typedef struct b3d_icp b3d_icp;
+enum {
+    B3D_ICP_DEVICE_INPUT = 1,  /* b3d_icp_create: mpt / dpt / data are device pointers (cptr / dptr always host) */
+    B3D_ICP_POSE_ONLY = 2      /* b3d_icp_eval: shapeEnabled = false (:176): the 10 shape entries of grad are 0 */
+};
+#define B3D_ICP_GRAD_DIM 85    /* root position (3) | rotation tangent of joint j at 3 + 3 j (FakeQuaternionParameterization,
+                                  :118-153) | shape keys at 75 */
+
+/* One set of correspondences per body (they stay fixed during a ceres::Solve, :1386-1412 / :1439): pairs e in
+ * [cptr[b], cptr[b+1]) match model point mpt[e] with point dpt[e] of body b's data cloud, which starts at point dptr[b] of
+ * `data` (3 values of `dtype` per point).  The cloud is reduced to one (mean, count) record per model point; `dtype` is also the
+ * arithmetic type of the evaluation kernel (B3D_F32: fast path; B3D_F64: accuracy path). */
+int b3d_icp_create(const b3d_model* m, int32_t B, int32_t dtype, const int64_t* cptr, const int32_t* mpt, const int32_t* dpt,
+                   const int64_t* dptr, const void* data, int32_t flags, b3d_icp** out);
+void b3d_icp_destroy(b3d_icp* h);
+int b3d_icp_num_bodies(const b3d_icp* h);
+/* One evaluation at w (B x 10), p (B x 3), q (B x 24 x 4 quaternions in Eigen's coefficient order x, y, z, w):
+ * cost (B) and grad (B x 85).  Host pointers / device pointers + stream. */
+int b3d_icp_eval(b3d_icp* h, const double* w, const double* p, const double* q, int32_t flags, double* cost, double* grad);
+int b3d_icp_eval_dev(b3d_icp* h, const double* w, const double* p, const double* q, int32_t flags, double* cost, double* grad,
+                     void* stream);
+
+/* ===================================================================================================== */
 /* Entry (2) batched Levenberg-Marquardt driver: replaces the ceres::Problem + ceres::Solve inside          */
 /*   OptimizePoseReprojection (include/Sim3BA.h:515-683), OptimizePoseShapeReprojection (:348-511)          */
 /* ===================================================================================================== */
