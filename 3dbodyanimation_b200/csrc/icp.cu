@@ -36,6 +36,8 @@ struct b3d_icp {
     const b3d_model* m = nullptr;
     int B = 0, dtype = 0, groups = 0;
     void* tgt = nullptr;        // [groups][V][32] x (mean xyz, n) of T
+    int32_t *vertex_of_pos = nullptr, *pos_of_vertex = nullptr;   // processing order: vertices sorted by their joint tuple
+    void* rec = nullptr;        // [V + CH][IcpRec::WORDS] of T: per-vertex model records (icp_records_kernel)
     double* scatter = nullptr;  // [B] sum |d - mean|^2
     double* acc = nullptr;      // [B][ICP_ACC]
     double* state = nullptr;    // device copies for the host-pointer call: w | p | q | cost | grad
@@ -78,14 +80,15 @@ __global__ void __launch_bounds__(256) icp_gather_kernel(int B, int V, const int
 }
 
 template <typename T>
-__global__ void __launch_bounds__(256) icp_targets_kernel(int B, int V, double* __restrict__ tmp, T* __restrict__ tgt) {
+__global__ void __launch_bounds__(256) icp_targets_kernel(int B, int V, const int32_t* __restrict__ pos_of_vertex, double* __restrict__ tmp,
+                                                          T* __restrict__ tgt) {
     const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
     if (i >= (size_t)B * V) return;
     const int b = (int)(i / V), v = (int)(i % V);
     double* t = tmp + 4 * i;
     const double n = t[3], inv = n > 0.0 ? 1.0 / n : 0.0;
     t[0] *= inv; t[1] *= inv; t[2] *= inv;
-    T* o = tgt + 4 * (((size_t)(b >> 5) * V + v) * 32 + (b & 31));
+    T* o = tgt + 4 * (((size_t)(b >> 5) * V + pos_of_vertex[v]) * 32 + (b & 31));
     o[0] = (T)t[0]; o[1] = (T)t[1]; o[2] = (T)t[2]; o[3] = (T)n;
 }
 
@@ -139,34 +142,104 @@ template <typename T> struct Vec4T;
 template <> struct Vec4T<float> { using type = float4; };
 template <> struct Vec4T<double> { using type = double4; };
 
+// One record per vertex, in the joint-tuple order of build_order() (built once per b3d_icp from the model's SoA tables):
+//   [0..2] template xyz, [3] 0, [4 + 10 c + s] shapedirs, [34 + k] weight of slot k, [34 + NW + k] its joint (as a T value)
+template <int NW> struct IcpRec { static constexpr int WORDS = (34 + 2 * NW + 3) / 4 * 4; };   // 44 (NW = 4), 52 (NW = 8)
+template <typename T> struct IcpChunk { static constexpr int CH = sizeof(T) == 4 ? 8 : 4; };   // vertices per prefetched tile
+
+template <typename T, int NW>
+__global__ void __launch_bounds__(256) icp_records_kernel(const T* __restrict__ vert, const T* __restrict__ wval, const int32_t* __restrict__ wjoint,
+                                                          int V, int Vpad, const int32_t* __restrict__ vertex_of_pos, T* __restrict__ rec) {
+    const int pos = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pos >= V) return;
+    const int v = vertex_of_pos[pos];
+    T* o = rec + (size_t)pos * IcpRec<NW>::WORDS;
+    for (int c = 0; c < 3; ++c) o[c] = vert[(size_t)c * Vpad + v];
+    o[3] = 0;
+    for (int i = 0; i < 3 * NS; ++i) o[4 + i] = vert[(size_t)(3 + i) * Vpad + v];
+    for (int k = 0; k < NW; ++k) {
+        o[34 + k] = wval[(size_t)k * Vpad + v];
+        o[34 + NW + k] = (T)wjoint[(size_t)k * Vpad + v];
+    }
+    for (int i = 34 + 2 * NW; i < IcpRec<NW>::WORDS; ++i) o[i] = 0;
+}
+
+__device__ __forceinline__ uint32_t icp_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void icp_mbar_init(unsigned long long* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(icp_smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void icp_mbar_expect_tx(unsigned long long* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(icp_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void icp_mbar_wait(unsigned long long* bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(icp_smem_u32(bar)), "r"(parity) : "memory");
+}
+// TMA bulk copy global -> shared, completion counted on an mbarrier (bytes % 16 == 0, both addresses 16 B aligned)
+__device__ __forceinline__ void icp_bulk_g2s(void* dst, const void* src, uint32_t bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(icp_smem_u32(dst)), "l"(src),
+                 "r"(bytes), "r"(icp_smem_u32(bar)) : "memory");
+}
+
 template <typename T, int NW, int NWARPS>
-__global__ void __launch_bounds__(32 * NWARPS, 1) icp_accumulate_kernel(const T* __restrict__ vert, const T* __restrict__ wval,
-                                                                        const int32_t* __restrict__ wjoint, int V, int Vpad, int B,
+constexpr size_t icp_smem_bytes() {
+    return sizeof(T) * ((size_t)NJ * 12 * ICP_TPAD + (size_t)NJ * 6 * 32 +
+                        (size_t)NWARPS * 2 * IcpChunk<T>::CH * (IcpRec<NW>::WORDS + 128)) + sizeof(unsigned long long) * 2 * NWARPS;
+}
+
+template <typename T, int NW, int NWARPS>
+__global__ void __launch_bounds__(32 * NWARPS, 1) icp_accumulate_kernel(const T* __restrict__ rec, int V, int B,
                                                                         const double* __restrict__ wshape, const double* __restrict__ jointTrans,
                                                                         const T* __restrict__ tgt, double* __restrict__ acc) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    T* sT = reinterpret_cast<T*>(smem_raw);                 // [NJ * 12][ICP_TPAD]
-    T* sBin = sT + NJ * 12 * ICP_TPAD;                      // [NWARPS][NJ * 6][32]
+    constexpr int CH = IcpChunk<T>::CH, RW = IcpRec<NW>::WORDS;
+    constexpr uint32_t REC_BYTES = CH * RW * sizeof(T), TGT_BYTES = CH * 128 * sizeof(T);
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    T* sT = reinterpret_cast<T*>(smem_raw);                 // [NJ * 12][ICP_TPAD] transforms of the 32 bodies
+    T* sBin = sT + NJ * 12 * ICP_TPAD;                      // [NJ * 6][32] per-joint sums of the CTA
+    T* sRec = sBin + NJ * 6 * 32;                           // [NWARPS][2][CH][RW]
+    T* sTgt = sRec + NWARPS * 2 * CH * RW;                  // [NWARPS][2][CH][32][4]
+    unsigned long long* mbar = reinterpret_cast<unsigned long long*>(sTgt + NWARPS * 2 * CH * 128);   // [NWARPS][2]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int b0 = blockIdx.x * 32;
     const int b = min(b0 + lane, B - 1);
-    // stage the group's transforms: sT[e][body]
-    for (int i = threadIdx.x; i < 32 * NJ * 12; i += 32 * NWARPS) {
-        const int bl = i / (NJ * 12), e = i - bl * (NJ * 12);
-        sT[e * ICP_TPAD + bl] = (T)jointTrans[(size_t)min(b0 + bl, B - 1) * NJ * 12 + e];
-    }
-    T* bins = sBin + (size_t)warp * NJ * 6 * 32;
-    for (int i = lane; i < NJ * 6 * 32; i += 32) bins[i] = (T)0;
-    T ws[NS];
-#pragma unroll
-    for (int s = 0; s < NS; ++s) ws[s] = (T)wshape[(size_t)b * NS + s];
-    __syncthreads();
 
     // vertex range of this CTA, then of this warp
     const int per_cta = (V + gridDim.y - 1) / gridDim.y;
     const int c0 = blockIdx.y * per_cta, c1 = min(V, c0 + per_cta);
     const int per_warp = (max(c1 - c0, 0) + NWARPS - 1) / NWARPS;
-    const int v0 = c0 + warp * per_warp, v1 = min(c1, v0 + per_warp);
+    const int v0 = min(c1, c0 + warp * per_warp), v1 = min(c1, v0 + per_warp);
+    const int nch = (v1 - v0 + CH - 1) / CH;
+    T* myRec = sRec + (size_t)warp * 2 * CH * RW;
+    T* myTgt = sTgt + (size_t)warp * 2 * CH * 128;
+    unsigned long long* myBar = mbar + 2 * warp;
+    const T* tgt_group = tgt + (size_t)blockIdx.x * V * 128;
+    auto issue = [&](int c) {   // lane 0: model records and target records of chunk c into buffer c & 1
+        const int vb = v0 + c * CH, s = c & 1;
+        icp_mbar_expect_tx(myBar + s, REC_BYTES + TGT_BYTES);
+        icp_bulk_g2s(myRec + s * CH * RW, rec + (size_t)vb * RW, REC_BYTES, myBar + s);
+        icp_bulk_g2s(myTgt + s * CH * 128, tgt_group + (size_t)vb * 128, TGT_BYTES, myBar + s);
+    };
+    if (lane == 0) {
+        icp_mbar_init(myBar, 1);
+        icp_mbar_init(myBar + 1, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        if (nch > 0) issue(0);
+    }
+    // stage the group's transforms: sT[e][body]
+    for (int i = threadIdx.x; i < 32 * NJ * 12; i += 32 * NWARPS) {
+        const int bl = i / (NJ * 12), e = i - bl * (NJ * 12);
+        sT[e * ICP_TPAD + bl] = (T)jointTrans[(size_t)min(b0 + bl, B - 1) * NJ * 12 + e];
+    }
+    for (int i = threadIdx.x; i < NJ * 6 * 32; i += 32 * NWARPS) sBin[i] = (T)0;
+    T ws[NS];
+#pragma unroll
+    for (int s = 0; s < NS; ++s) ws[s] = (T)wshape[(size_t)b * NS + s];
+    __syncthreads();
 
     T cost = 0, gp[3] = {0, 0, 0}, sh[NS];
 #pragma unroll
@@ -182,97 +255,108 @@ __global__ void __launch_bounds__(32 * NWARPS, 1) icp_accumulate_kernel(const T*
         for (int c = 0; c < 12; ++c) G[k][c] = 0;
     }
     using V4 = typename Vec4T<T>::type;
-    const V4* tg = reinterpret_cast<const V4*>(tgt) + ((size_t)blockIdx.x * V) * 32 + lane;
 
-    for (int v = v0; v < v1; ++v) {
-        const V4 mu = tg[(size_t)v * 32];
-        // shape blend (AvatarOptimizer.cpp:263-264); D kept for the shape gradient
-        T x[3], D[3][NS];
+    for (int c = 0; c < nch; ++c) {
+        const int s = c & 1;
+        if (lane == 0 && c + 1 < nch) issue(c + 1);   // its buffer was released by the __syncwarp that closed chunk c - 1
+        icp_mbar_wait(myBar + s, (uint32_t)((c >> 1) & 1));
+        const int nv = min(CH, v1 - (v0 + c * CH));
+        for (int i = 0; i < nv; ++i) {
+            // the vertex's record: warp-uniform 16-byte shared loads
+            T rv[RW];
+            const V4* r4 = reinterpret_cast<const V4*>(myRec + (s * CH + i) * RW);
 #pragma unroll
-        for (int c = 0; c < 3; ++c) {
-            T a = __ldg(vert + (size_t)c * Vpad + v);
-#pragma unroll
-            for (int s = 0; s < NS; ++s) {
-                D[c][s] = __ldg(vert + (size_t)(3 + NS * c + s) * Vpad + v);
-                a += D[c][s] * ws[s];
+            for (int u = 0; u < RW / 4; ++u) {
+                const V4 t4 = r4[u];
+                rv[4 * u] = t4.x; rv[4 * u + 1] = t4.y; rv[4 * u + 2] = t4.z; rv[4 * u + 3] = t4.w;
             }
-            x[c] = a;
-        }
-        T wt[NW], Pk[NW][3], P[3] = {0, 0, 0}, Tm[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+            const V4 mu = reinterpret_cast<const V4*>(myTgt + (s * CH + i) * 128)[lane];
+            // shape blend (AvatarOptimizer.cpp:263-264)
+            T x[3];
 #pragma unroll
-        for (int k = 0; k < NW; ++k) {
-            wt[k] = __ldg(wval + (size_t)k * Vpad + v);
-            if ((double)wt[k] > 1e-12) {   // assignedJoints keeps weights > 1e-12 (AvatarModel.cpp:81)
-                const int jk = __ldg(wjoint + (size_t)k * Vpad + v);
-                if (jk != curj[k]) {       // warp-uniform: the vertex is
-                    if (curj[k] >= 0) {
+            for (int cc = 0; cc < 3; ++cc) {
+                T a = rv[cc];
 #pragma unroll
-                        for (int c = 0; c < 6; ++c) { bins[(curj[k] * 6 + c) * 32 + lane] += bin[k][c]; bin[k][c] = 0; }
+                for (int q = 0; q < NS; ++q) a += rv[4 + NS * cc + q] * ws[q];
+                x[cc] = a;
+            }
+            T Pk[NW][3], P[3] = {0, 0, 0}, Tm[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+            for (int k = 0; k < NW; ++k) {
+                const T wt = rv[34 + k];
+                if ((double)wt > 1e-12) {   // assignedJoints keeps weights > 1e-12 (AvatarModel.cpp:81)
+                    const int jk = (int)rv[34 + NW + k];
+                    if (jk != curj[k]) {    // warp-uniform: the vertex is
+                        if (curj[k] >= 0) {
+#pragma unroll
+                            for (int cc = 0; cc < 6; ++cc) { atomicAdd(&sBin[(curj[k] * 6 + cc) * 32 + lane], bin[k][cc]); bin[k][cc] = 0; }
+                        }
+                        curj[k] = jk;
+#pragma unroll
+                        for (int cc = 0; cc < 12; ++cc) G[k][cc] = sT[(jk * 12 + cc) * ICP_TPAD + lane];
                     }
-                    curj[k] = jk;
 #pragma unroll
-                    for (int c = 0; c < 12; ++c) G[k][c] = sT[(jk * 12 + c) * ICP_TPAD + lane];
+                    for (int r = 0; r < 3; ++r) {
+                        Pk[k][r] = G[k][r] * x[0] + G[k][3 + r] * x[1] + G[k][6 + r] * x[2] + G[k][9 + r];
+                        P[r] += wt * Pk[k][r];
+                    }
+#pragma unroll
+                    for (int cc = 0; cc < 9; ++cc) Tm[cc] += wt * G[k][cc];
                 }
+            }
+            // sum of the vertex's residuals and its cost share
+            const T n = mu.w;
+            const T e0 = P[0] - mu.x, e1 = P[1] - mu.y, e2 = P[2] - mu.z;
+            const T rs[3] = {n * e0, n * e1, n * e2};
+            cost += n * (e0 * e0 + e1 * e1 + e2 * e2);
 #pragma unroll
-                for (int r = 0; r < 3; ++r) {
-                    Pk[k][r] = G[k][r] * x[0] + G[k][3 + r] * x[1] + G[k][6 + r] * x[2] + G[k][9 + r];
-                    P[r] += wt[k] * Pk[k][r];
+            for (int cc = 0; cc < 3; ++cc) gp[cc] += rs[cc];
+            // shape: D^T (T^T rs)
+            const T y0 = Tm[0] * rs[0] + Tm[1] * rs[1] + Tm[2] * rs[2];
+            const T y1 = Tm[3] * rs[0] + Tm[4] * rs[1] + Tm[5] * rs[2];
+            const T y2 = Tm[6] * rs[0] + Tm[7] * rs[1] + Tm[8] * rs[2];
+#pragma unroll
+            for (int q = 0; q < NS; ++q) sh[q] += rv[4 + q] * y0 + rv[4 + NS + q] * y1 + rv[4 + 2 * NS + q] * y2;
+#pragma unroll
+            for (int k = 0; k < NW; ++k) {
+                const T wt = rv[34 + k];
+                if ((double)wt > 1e-12) {
+                    const T wr[3] = {wt * rs[0], wt * rs[1], wt * rs[2]};
+                    bin[k][0] += Pk[k][1] * wr[2] - Pk[k][2] * wr[1];
+                    bin[k][1] += Pk[k][2] * wr[0] - Pk[k][0] * wr[2];
+                    bin[k][2] += Pk[k][0] * wr[1] - Pk[k][1] * wr[0];
+                    bin[k][3] += wr[0]; bin[k][4] += wr[1]; bin[k][5] += wr[2];
                 }
-#pragma unroll
-                for (int c = 0; c < 9; ++c) Tm[c] += wt[k] * G[k][c];
             }
         }
-        // sum of the vertex's residuals and its cost share
-        const T n = mu.w;
-        const T e0 = P[0] - mu.x, e1 = P[1] - mu.y, e2 = P[2] - mu.z;
-        const T rs[3] = {n * e0, n * e1, n * e2};
-        cost += n * (e0 * e0 + e1 * e1 + e2 * e2);
-#pragma unroll
-        for (int c = 0; c < 3; ++c) gp[c] += rs[c];
-        // shape: D^T (T^T rs)
-        const T y0 = Tm[0] * rs[0] + Tm[1] * rs[1] + Tm[2] * rs[2];
-        const T y1 = Tm[3] * rs[0] + Tm[4] * rs[1] + Tm[5] * rs[2];
-        const T y2 = Tm[6] * rs[0] + Tm[7] * rs[1] + Tm[8] * rs[2];
-#pragma unroll
-        for (int s = 0; s < NS; ++s) sh[s] += D[0][s] * y0 + D[1][s] * y1 + D[2][s] * y2;
-#pragma unroll
-        for (int k = 0; k < NW; ++k) {
-            if ((double)wt[k] > 1e-12) {
-                const T wr[3] = {wt[k] * rs[0], wt[k] * rs[1], wt[k] * rs[2]};
-                bin[k][0] += Pk[k][1] * wr[2] - Pk[k][2] * wr[1];
-                bin[k][1] += Pk[k][2] * wr[0] - Pk[k][0] * wr[2];
-                bin[k][2] += Pk[k][0] * wr[1] - Pk[k][1] * wr[0];
-                bin[k][3] += wr[0]; bin[k][4] += wr[1]; bin[k][5] += wr[2];
-            }
-        }
+        __syncwarp();
     }
 #pragma unroll
     for (int k = 0; k < NW; ++k)
         if (curj[k] >= 0) {
 #pragma unroll
-            for (int c = 0; c < 6; ++c) bins[(curj[k] * 6 + c) * 32 + lane] += bin[k][c];
+            for (int cc = 0; cc < 6; ++cc) atomicAdd(&sBin[(curj[k] * 6 + cc) * 32 + lane], bin[k][cc]);
         }
     __syncthreads();
     // dense accumulators through the (now free) transform area: sD[warp][14][32]
     T* sD = sT;
     sD[(warp * 14 + 0) * 32 + lane] = cost;
 #pragma unroll
-    for (int c = 0; c < 3; ++c) sD[(warp * 14 + 1 + c) * 32 + lane] = gp[c];
+    for (int cc = 0; cc < 3; ++cc) sD[(warp * 14 + 1 + cc) * 32 + lane] = gp[cc];
 #pragma unroll
-    for (int s = 0; s < NS; ++s) sD[(warp * 14 + 4 + s) * 32 + lane] = sh[s];
+    for (int q = 0; q < NS; ++q) sD[(warp * 14 + 4 + q) * 32 + lane] = sh[q];
     __syncthreads();
     for (int i = threadIdx.x; i < (14 + NJ * 6) * 32; i += 32 * NWARPS) {
         const int e = i >> 5, l = i & 31;
         if (b0 + l >= B) continue;
-        double s = 0.0;
+        double sum = 0.0;
         if (e < 14) {
 #pragma unroll
-            for (int wq = 0; wq < NWARPS; ++wq) s += (double)sD[(wq * 14 + e) * 32 + l];
+            for (int wq = 0; wq < NWARPS; ++wq) sum += (double)sD[(wq * 14 + e) * 32 + l];
         } else {
-#pragma unroll
-            for (int wq = 0; wq < NWARPS; ++wq) s += (double)sBin[((size_t)wq * NJ * 6 + (e - 14)) * 32 + l];
+            sum = (double)sBin[(e - 14) * 32 + l];
         }
-        if (s != 0.0) atomicAdd(acc + (size_t)(b0 + l) * ICP_ACC + (e < 14 ? e : e + 2), s);
+        if (sum != 0.0) atomicAdd(acc + (size_t)(b0 + l) * ICP_ACC + (e < 14 ? e : e + 2), sum);
     }
 }
 
@@ -329,12 +413,40 @@ __global__ void __launch_bounds__(64) icp_finish_kernel(const SkeletonConst* __r
     for (int s = 0; s < NS; ++s) out[3 + 3 * NJ + s] = shape_enabled ? sg[s] : 0.0;
 }
 
+// The sums over vertices do not depend on the order, so the vertices are processed sorted by their tuple of assigned joints:
+// a weight slot then keeps its joint over long runs and the accumulate kernel keeps that joint's transform and partial sums in
+// registers (SMPL: a few hundred distinct tuples for 6890 vertices).
+static int build_order(b3d_icp* h) {
+    const b3d_model* m = h->m;
+    const int V = m->V, nw = m->nw;
+    std::vector<int32_t> wj((size_t)nw * m->Vpad);
+    std::vector<double> wv((size_t)nw * m->Vpad);
+    B3D_CUDA(cudaMemcpy(wj.data(), m->t64.wjoint, sizeof(int32_t) * wj.size(), cudaMemcpyDeviceToHost));
+    B3D_CUDA(cudaMemcpy(wv.data(), m->t64.wval, sizeof(double) * wv.size(), cudaMemcpyDeviceToHost));
+    auto key = [&](int v, int k) { return wv[(size_t)k * m->Vpad + v] > 1e-12 ? wj[(size_t)k * m->Vpad + v] : NJ; };
+    std::vector<int32_t> order(V), inv(V);
+    for (int v = 0; v < V; ++v) order[v] = v;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) {
+        for (int k = 0; k < nw; ++k) {
+            const int ka = key(a, k), kb = key(b, k);
+            if (ka != kb) return ka < kb;
+        }
+        return false;
+    });
+    for (int i = 0; i < V; ++i) inv[order[i]] = i;
+    B3D_CUDA(cudaMalloc(&h->vertex_of_pos, sizeof(int32_t) * 2 * V));
+    h->pos_of_vertex = h->vertex_of_pos + V;
+    B3D_CUDA(cudaMemcpy(h->vertex_of_pos, order.data(), sizeof(int32_t) * V, cudaMemcpyHostToDevice));
+    B3D_CUDA(cudaMemcpy(h->pos_of_vertex, inv.data(), sizeof(int32_t) * V, cudaMemcpyHostToDevice));
+    return B3D_OK;
+}
+
 template <typename T>
 static int icp_reduce(b3d_icp* h, const int64_t* d_cptr, const int64_t* d_dptr, const int32_t* d_mpt, const int32_t* d_dpt, const T* d_data) {
     const b3d_model* m = h->m;
     const int B = h->B, V = m->V;
     double* tmp = nullptr;
-    const size_t tmp_bytes = sizeof(double) * 4 * (size_t)B * V, tgt_bytes = sizeof(T) * 4 * 32 * (size_t)h->groups * V;
+    const size_t tmp_bytes = sizeof(double) * 4 * (size_t)B * V, tgt_bytes = sizeof(T) * 128 * ((size_t)h->groups * V + 8);
     B3D_CUDA(cudaMalloc(&tmp, tmp_bytes));
     cudaError_t e = cudaMemsetAsync(tmp, 0, tmp_bytes, nullptr);
     if (e == cudaSuccess) e = cudaMemsetAsync(h->tgt, 0, tgt_bytes, nullptr);
@@ -343,7 +455,7 @@ static int icp_reduce(b3d_icp* h, const int64_t* d_cptr, const int64_t* d_dptr, 
     const int pair_blocks = (int)std::min<int64_t>(std::max<int64_t>((h->npairs + 255) / 256, 1), 148 * 16);
     icp_gather_kernel<T><<<pair_blocks, 256>>>(B, V, d_cptr, d_dptr, d_mpt, d_dpt, d_data, tmp);
     count_launch();
-    icp_targets_kernel<T><<<(unsigned)(((size_t)B * V + 255) / 256), 256>>>(B, V, tmp, (T*)h->tgt);
+    icp_targets_kernel<T><<<(unsigned)(((size_t)B * V + 255) / 256), 256>>>(B, V, h->pos_of_vertex, tmp, (T*)h->tgt);
     count_launch();
     icp_scatter_kernel<T><<<pair_blocks, 256>>>(B, V, d_cptr, d_dptr, d_mpt, d_dpt, d_data, tmp, h->scatter);
     count_launch();
@@ -354,10 +466,22 @@ static int icp_reduce(b3d_icp* h, const int64_t* d_cptr, const int64_t* d_dptr, 
     return B3D_OK;
 }
 
-template <typename T, int NW, int NWARPS>
-static int launch_accumulate(const b3d_icp* h, const VertexTables<T>& t, const double* w, cudaStream_t st) {
+template <typename T, int NW>
+static int build_records(b3d_icp* h, const VertexTables<T>& t) {
     const b3d_model* m = h->m;
-    const size_t smem = sizeof(T) * ((size_t)NJ * 12 * ICP_TPAD + (size_t)NWARPS * NJ * 6 * 32);
+    const size_t bytes = sizeof(T) * IcpRec<NW>::WORDS * ((size_t)m->V + IcpChunk<T>::CH);   // a partial last tile reads past V
+    B3D_CUDA(cudaMalloc(&h->rec, bytes));
+    B3D_CUDA(cudaMemsetAsync(h->rec, 0, bytes, nullptr));
+    icp_records_kernel<T, NW><<<(m->V + 255) / 256, 256>>>(t.vert, t.wval, t.wjoint, m->V, m->Vpad, h->vertex_of_pos, (T*)h->rec);
+    B3D_LAUNCH_CHECK();
+    return B3D_OK;
+}
+
+template <typename T, int NW, int NWARPS>
+static int launch_accumulate(const b3d_icp* h, const double* w, cudaStream_t st) {
+    const b3d_model* m = h->m;
+    constexpr size_t smem = icp_smem_bytes<T, NW, NWARPS>();
+    static_assert(smem <= 232448, "icp_accumulate_kernel: shared memory over the sm_100 limit");
     static bool attr_done = false;
     if (!attr_done) {
         B3D_CUDA(cudaFuncSetAttribute(icp_accumulate_kernel<T, NW, NWARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -365,8 +489,8 @@ static int launch_accumulate(const b3d_icp* h, const VertexTables<T>& t, const d
     }
     // enough CTAs for two waves of the 148 SMs when the batch is small; one CTA per body group when it is large
     const int vsplit = std::max(1, std::min(32, (2 * 148 + h->groups - 1) / h->groups));
-    icp_accumulate_kernel<T, NW, NWARPS><<<dim3(h->groups, vsplit), 32 * NWARPS, smem, st>>>(t.vert, t.wval, t.wjoint, m->V, m->Vpad, h->B, w,
-                                                                                             h->jt, (const T*)h->tgt, h->acc);
+    icp_accumulate_kernel<T, NW, NWARPS><<<dim3(h->groups, vsplit), 32 * NWARPS, smem, st>>>((const T*)h->rec, m->V, h->B, w, h->jt,
+                                                                                             (const T*)h->tgt, h->acc);
     B3D_LAUNCH_CHECK();
     return B3D_OK;
 }
@@ -394,7 +518,7 @@ int b3d_icp_create(const b3d_model* m, int32_t B, int32_t dtype, const int64_t* 
     int64_t *d_cptr = nullptr, *d_dptr = nullptr;
     int32_t *d_mpt = nullptr, *d_dpt = nullptr;
     void* d_data = nullptr;
-    cudaError_t e = cudaMalloc(&h->tgt, es * 4 * 32 * (size_t)h->groups * m->V);
+    cudaError_t e = cudaMalloc(&h->tgt, es * 128 * ((size_t)h->groups * m->V + 8));   // + one tile: a partial last tile reads past V
     if (e == cudaSuccess) e = cudaMalloc(&h->scatter, sizeof(double) * B);
     if (e == cudaSuccess) e = cudaMalloc(&h->acc, sizeof(double) * (size_t)B * ICP_ACC);
     if (e == cudaSuccess) e = cudaMalloc(&h->state, sizeof(double) * (size_t)B * (NS + 3 + 4 * NJ + 1 + ICP_NC));
@@ -416,12 +540,18 @@ int b3d_icp_create(const b3d_model* m, int32_t B, int32_t dtype, const int64_t* 
     }
     int rc = B3D_OK;
     if (e != cudaSuccess) rc = set_error(B3D_ECUDA, "b3d_icp_create: %s", cudaGetErrorString(e));
+    if (!rc) rc = build_order(h);
     if (!rc) {
         const int32_t* pm = dev_in ? mpt : d_mpt;
         const int32_t* pd = dev_in ? dpt : d_dpt;
         const void* pdat = dev_in ? data : d_data;
         rc = dtype == B3D_F32 ? icp_reduce<float>(h, d_cptr, d_dptr, pm, pd, (const float*)pdat)
                               : icp_reduce<double>(h, d_cptr, d_dptr, pm, pd, (const double*)pdat);
+    }
+    if (!rc) {
+        if (dtype == B3D_F32) rc = m->nw == 4 ? build_records<float, 4>(h, m->t32) : build_records<float, 8>(h, m->t32);
+        else rc = m->nw == 4 ? build_records<double, 4>(h, m->t64) : build_records<double, 8>(h, m->t64);
+        if (!rc && cudaStreamSynchronize(nullptr) != cudaSuccess) rc = set_error(B3D_ECUDA, "b3d_icp_create: building the vertex records failed");
     }
     cudaFree(d_cptr); cudaFree(d_mpt); cudaFree(d_data);
     if (rc) { b3d_icp_destroy(h); return rc; }
@@ -431,7 +561,7 @@ int b3d_icp_create(const b3d_model* m, int32_t B, int32_t dtype, const int64_t* 
 
 void b3d_icp_destroy(b3d_icp* h) {
     if (!h) return;
-    cudaFree(h->tgt); cudaFree(h->scatter); cudaFree(h->acc); cudaFree(h->state); cudaFree(h->r); cudaFree(h->jp); cudaFree(h->jt);
+    cudaFree(h->tgt); cudaFree(h->rec); cudaFree(h->vertex_of_pos); cudaFree(h->scatter); cudaFree(h->acc); cudaFree(h->state); cudaFree(h->r); cudaFree(h->jp); cudaFree(h->jt);
     delete h;
 }
 
@@ -447,9 +577,9 @@ int b3d_icp_eval_dev(b3d_icp* h, const double* w, const double* p, const double*
     B3D_CUDA(cudaMemsetAsync(h->acc, 0, sizeof(double) * (size_t)B * ICP_ACC, st));
     int rc;
     if (h->dtype == B3D_F32)
-        rc = m->nw == 4 ? launch_accumulate<float, 4, 8>(h, m->t32, w, st) : launch_accumulate<float, 8, 8>(h, m->t32, w, st);
+        rc = m->nw == 4 ? launch_accumulate<float, 4, 8>(h, w, st) : launch_accumulate<float, 8, 8>(h, w, st);
     else
-        rc = m->nw == 4 ? launch_accumulate<double, 4, 4>(h, m->t64, w, st) : launch_accumulate<double, 8, 4>(h, m->t64, w, st);
+        rc = m->nw == 4 ? launch_accumulate<double, 4, 8>(h, w, st) : launch_accumulate<double, 8, 8>(h, w, st);
     if (rc) return rc;
     icp_finish_kernel<<<(B + 63) / 64, 64, 0, st>>>(m->d_sk, B, (flags & B3D_ICP_POSE_ONLY) ? 0 : 1, h->acc, h->scatter, h->jp, h->jt, cost, grad);
     B3D_LAUNCH_CHECK();
