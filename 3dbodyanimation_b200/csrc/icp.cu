@@ -28,6 +28,7 @@
 //       register / shared accumulators — no shuffles, no atomics inside the loop.  HBM traffic: 16 B (float) per vertex and body.
 //   icp_finish_kernel : the per-body epilogue above, float64.
 #include <algorithm>
+#include <cmath>
 #include <vector>
 
 #include "internal.hpp"
@@ -262,30 +263,44 @@ __global__ void __launch_bounds__(32 * NWARPS, 1) icp_accumulate_kernel(const T*
         icp_mbar_wait(myBar + s, (uint32_t)((c >> 1) & 1));
         const int nv = min(CH, v1 - (v0 + c * CH));
         for (int i = 0; i < nv; ++i) {
-            // the vertex's record: warp-uniform 16-byte shared loads
-            T rv[RW];
+            // the vertex's record: warp-uniform 16-byte shared loads (the shapedirs are read again for the shape gradient
+            // rather than kept in 30 registers)
             const V4* r4 = reinterpret_cast<const V4*>(myRec + (s * CH + i) * RW);
+            const T* r1 = myRec + (s * CH + i) * RW;
+            T wj[RW - 32];   // [2..] weights, then joints
 #pragma unroll
-            for (int u = 0; u < RW / 4; ++u) {
+            for (int u = 8; u < RW / 4; ++u) {
                 const V4 t4 = r4[u];
-                rv[4 * u] = t4.x; rv[4 * u + 1] = t4.y; rv[4 * u + 2] = t4.z; rv[4 * u + 3] = t4.w;
+                wj[4 * (u - 8)] = t4.x; wj[4 * (u - 8) + 1] = t4.y; wj[4 * (u - 8) + 2] = t4.z; wj[4 * (u - 8) + 3] = t4.w;
             }
             const V4 mu = reinterpret_cast<const V4*>(myTgt + (s * CH + i) * 128)[lane];
             // shape blend (AvatarOptimizer.cpp:263-264)
             T x[3];
+            {
+                T rv[32];
 #pragma unroll
-            for (int cc = 0; cc < 3; ++cc) {
-                T a = rv[cc];
+                for (int u = 0; u < 8; ++u) {
+                    const V4 t4 = r4[u];
+                    rv[4 * u] = t4.x; rv[4 * u + 1] = t4.y; rv[4 * u + 2] = t4.z; rv[4 * u + 3] = t4.w;
+                }
+                T hi0 = wj[0], hi1 = wj[1];   // words 32, 33 = shapedirs z, s = 8, 9
 #pragma unroll
-                for (int q = 0; q < NS; ++q) a += rv[4 + NS * cc + q] * ws[q];
-                x[cc] = a;
+                for (int cc = 0; cc < 3; ++cc) {
+                    T a = rv[cc];
+#pragma unroll
+                    for (int q = 0; q < NS; ++q) {
+                        const int idx = 4 + NS * cc + q;
+                        a += (idx < 32 ? rv[idx < 32 ? idx : 0] : (idx == 32 ? hi0 : hi1)) * ws[q];
+                    }
+                    x[cc] = a;
+                }
             }
-            T Pk[NW][3], P[3] = {0, 0, 0}, Tm[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+            T Pk[NW][3], P[3] = {0, 0, 0};
 #pragma unroll
             for (int k = 0; k < NW; ++k) {
-                const T wt = rv[34 + k];
+                const T wt = wj[2 + k];
                 if ((double)wt > 1e-12) {   // assignedJoints keeps weights > 1e-12 (AvatarModel.cpp:81)
-                    const int jk = (int)rv[34 + NW + k];
+                    const int jk = (int)wj[2 + NW + k];
                     if (jk != curj[k]) {    // warp-uniform: the vertex is
                         if (curj[k] >= 0) {
 #pragma unroll
@@ -300,8 +315,6 @@ __global__ void __launch_bounds__(32 * NWARPS, 1) icp_accumulate_kernel(const T*
                         Pk[k][r] = G[k][r] * x[0] + G[k][3 + r] * x[1] + G[k][6 + r] * x[2] + G[k][9 + r];
                         P[r] += wt * Pk[k][r];
                     }
-#pragma unroll
-                    for (int cc = 0; cc < 9; ++cc) Tm[cc] += wt * G[k][cc];
                 }
             }
             // sum of the vertex's residuals and its cost share
@@ -311,23 +324,25 @@ __global__ void __launch_bounds__(32 * NWARPS, 1) icp_accumulate_kernel(const T*
             cost += n * (e0 * e0 + e1 * e1 + e2 * e2);
 #pragma unroll
             for (int cc = 0; cc < 3; ++cc) gp[cc] += rs[cc];
-            // shape: D^T (T^T rs)
-            const T y0 = Tm[0] * rs[0] + Tm[1] * rs[1] + Tm[2] * rs[2];
-            const T y1 = Tm[3] * rs[0] + Tm[4] * rs[1] + Tm[5] * rs[2];
-            const T y2 = Tm[6] * rs[0] + Tm[7] * rs[1] + Tm[8] * rs[2];
-#pragma unroll
-            for (int q = 0; q < NS; ++q) sh[q] += rv[4 + q] * y0 + rv[4 + NS + q] * y1 + rv[4 + 2 * NS + q] * y2;
+            // per-joint sums, and y = T^T rs = sum_k G_k^T (w_k rs) for the shape gradient
+            T y0 = 0, y1 = 0, y2 = 0;
 #pragma unroll
             for (int k = 0; k < NW; ++k) {
-                const T wt = rv[34 + k];
+                const T wt = wj[2 + k];
                 if ((double)wt > 1e-12) {
                     const T wr[3] = {wt * rs[0], wt * rs[1], wt * rs[2]};
                     bin[k][0] += Pk[k][1] * wr[2] - Pk[k][2] * wr[1];
                     bin[k][1] += Pk[k][2] * wr[0] - Pk[k][0] * wr[2];
                     bin[k][2] += Pk[k][0] * wr[1] - Pk[k][1] * wr[0];
                     bin[k][3] += wr[0]; bin[k][4] += wr[1]; bin[k][5] += wr[2];
+                    y0 += G[k][0] * wr[0] + G[k][1] * wr[1] + G[k][2] * wr[2];
+                    y1 += G[k][3] * wr[0] + G[k][4] * wr[1] + G[k][5] * wr[2];
+                    y2 += G[k][6] * wr[0] + G[k][7] * wr[1] + G[k][8] * wr[2];
                 }
             }
+            // shape: D^T y, shapedirs read again from the tile
+#pragma unroll
+            for (int q = 0; q < NS; ++q) sh[q] += r1[4 + q] * y0 + r1[4 + NS + q] * y1 + r1[4 + 2 * NS + q] * y2;
         }
         __syncwarp();
     }
@@ -488,7 +503,15 @@ static int launch_accumulate(const b3d_icp* h, const double* w, cudaStream_t st)
         attr_done = true;
     }
     // enough CTAs for two waves of the 148 SMs when the batch is small; one CTA per body group when it is large
-    const int vsplit = std::max(1, std::min(32, (2 * 148 + h->groups - 1) / h->groups));
+    int vsplit = 1;
+    {   // the split whose grid fills whole waves of the 148 SMs best (ties: the smaller split)
+        double best = 0.0;
+        const int hi = h->groups >= 2 * 148 ? 4 : 32;
+        for (int sp = 1; sp <= hi; ++sp) {
+            const double waves = (double)h->groups * sp / 148.0, eff = waves / std::ceil(waves);
+            if (eff > best + 1e-9) { best = eff; vsplit = sp; }
+        }
+    }
     icp_accumulate_kernel<T, NW, NWARPS><<<dim3(h->groups, vsplit), 32 * NWARPS, smem, st>>>((const T*)h->rec, m->V, h->B, w, h->jt,
                                                                                              (const T*)h->tgt, h->acc);
     B3D_LAUNCH_CHECK();
@@ -577,7 +600,7 @@ int b3d_icp_eval_dev(b3d_icp* h, const double* w, const double* p, const double*
     B3D_CUDA(cudaMemsetAsync(h->acc, 0, sizeof(double) * (size_t)B * ICP_ACC, st));
     int rc;
     if (h->dtype == B3D_F32)
-        rc = m->nw == 4 ? launch_accumulate<float, 4, 8>(h, w, st) : launch_accumulate<float, 8, 8>(h, w, st);
+        rc = m->nw == 4 ? launch_accumulate<float, 4, 12>(h, w, st) : launch_accumulate<float, 8, 8>(h, w, st);
     else
         rc = m->nw == 4 ? launch_accumulate<double, 4, 8>(h, w, st) : launch_accumulate<double, 8, 8>(h, w, st);
     if (rc) return rc;
