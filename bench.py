@@ -348,6 +348,14 @@ def run_b200(args):
         except Exception as e:       # never lose the headline line over the side measurement
             overlay = {"error": str(e)[:200]}
 
+    # SURVEY 8(f) rank 4, reported beside the headline: vertex-level ICP term (cost + gradient) on resident correspondences
+    icp = None
+    if world == 1:
+        try:
+            icp = icp_leg(api, capi, lib, synth, model_np, dev, st, with_cpu=not args.no_cpu_baseline)
+        except Exception as e:
+            icp = {"error": str(e)[:200]}
+
     total_frames = nf * world
     line = {
         "metric": "frames_fitted_per_sec", "value": total_frames / (step_ms * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": args.steps,
@@ -374,6 +382,7 @@ def run_b200(args):
         "cpu_baseline": cpu,
         "clocks": clk,
         "overlay": overlay,
+        "icp": icp,
         "quality": {"usable_frames": int(cnt[1].item()), "mean_lm_iterations": cnt[0].item() / total_frames, "mean_pixel_error_px": px_err_mean},
     }
     print(json.dumps(line))
@@ -422,6 +431,56 @@ def overlay_leg(api, capi, lib, synth, dev, st, with_cpu, nb=2048, W=480, H=270)
         same = bool(np.array_equal(himg, img[:ns].cpu().numpy()))
         out["cpu_baseline"] = {"value": ns / dt, "unit": "overlays/s", "cores": host_threads(), "kind": "port",
                                "sample": f"{ns} of the {nb} bodies, oracle/render.cpp (OpenMP over bodies)", "images_identical_to_gpu": same}
+    return out
+
+
+def icp_leg(api, capi, lib, synth, model_np, dev, st, with_cpu, nb=4096, base=32):
+    """AvatarOptimizer's ICP term (external/avatar/AvatarOptimizer.cpp:295-641) for nb bodies with resident, already reduced
+    correspondences: one b3d_icp_eval_dev call = quaternions -> joints -> fused blend + skinning + residual + gradient -> epilogue.
+    Target records: nb * 6890 * 16 B (451 MB at nb = 4096, larger than L2).  Flop model per (vertex, body): 136 + 60 per non-zero
+    skinning weight."""
+    import torch
+    x = synth.make_icp_inputs(model_np, base, 3)
+    reps = nb // base
+    npair, ndata = int(x["cptr"][-1]), int(x["dptr"][-1])
+    cptr = np.concatenate([x["cptr"][:-1] + r * npair for r in range(reps)] + [[reps * npair]]).astype(np.int64)
+    dptr = np.concatenate([x["dptr"][:-1] + r * ndata for r in range(reps)] + [[reps * ndata]]).astype(np.int64)
+    gm = api.AvatarModel(model_np)
+    prob = api.IcpProblem(gm, cptr, np.tile(x["mpt"], reps), np.tile(x["dpt"], reps), dptr, np.tile(x["data"].astype(np.float32), (reps, 1)))
+    P = lambda t: C.c_void_p(t.data_ptr())
+    w, p, q = [torch.from_numpy(np.ascontiguousarray(np.tile(x[k], (reps,) + (1,) * (x[k].ndim - 1)))).to(dev) for k in ("w", "p", "q")]
+    cost, grad = torch.empty(nb, dtype=torch.float64, device=dev), torch.empty(nb, 85, dtype=torch.float64, device=dev)
+    run = lambda: capi.check(lib.b3d_icp_eval_dev(prob.h, P(w), P(p), P(q), 0, P(cost), P(grad), C.c_void_p(st)), "b3d_icp_eval_dev")
+    for _ in range(3):
+        run()
+    torch.cuda.synchronize()
+    evs = []
+    for _ in range(10):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); run(); e1.record()
+        evs.append((e0, e1))
+    torch.cuda.synchronize()
+    ms = float(np.mean([a.elapsed_time(b) for a, b in evs]))
+    nnz = float((np.asarray(model_np["weights"]) > 1e-12).sum()) / synth.V
+    flop = 136.0 + 60.0 * nnz
+    vb = nb * synth.V / (ms * 1e-3)
+    out = {"kernel": "icp_accumulate_kernel<float, 4, 12> inside one b3d_icp_eval_dev call (5 launches + 1 memset)", "value": nb / (ms * 1e-3),
+           "unit": "evaluations/s", "bodies": nb, "pairs_per_body": npair / base, "ms_per_call": ms, "vertex_bodies_per_sec": vb,
+           "bound": "fp32 issue (22 flop per target-record byte; B200 balance 11 flop/B)", "achieved_tflops": vb * flop / 1e12,
+           "fp32_peak_tflops": 148 * 128 * 2 * 1.965e-3, "frac_fp32": vb * flop / 1e12 / (148 * 128 * 2 * 1.965e-3),
+           "achieved_gbs": vb * 16 / 1e9, "flop_per_vertex_body": flop}
+    if with_cpu:
+        from oracle import oracle_api as orc
+        om = orc.Model(model_np)
+        ns = base
+        t0 = time.perf_counter()
+        ref = om.icp_eval(x["w"], x["p"], x["q"], x["cptr"], x["mpt"], x["dpt"], x["dptr"], x["data"], nthreads=host_threads())
+        dt = time.perf_counter() - t0
+        g = grad[:ns].cpu().numpy()
+        err = float(np.max(np.abs(g - ref["grad"]) / np.max(np.abs(ref["grad"]), axis=1, keepdims=True)))
+        out["cpu_baseline"] = {"value": ns / dt, "unit": "evaluations/s", "cores": host_threads(), "kind": "port",
+                               "sample": f"{ns} of the {nb} bodies, oracle/icp.cpp (per-pair analytic Jacobian blocks, OpenMP over bodies)",
+                               "max_rel_grad_diff_vs_gpu": err}
     return out
 
 
