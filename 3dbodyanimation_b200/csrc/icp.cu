@@ -159,7 +159,8 @@ __global__ void __launch_bounds__(256) icp_records_kernel(const T* __restrict__ 
     o[3] = 0;
     for (int i = 0; i < 3 * NS; ++i) o[4 + i] = vert[(size_t)(3 + i) * Vpad + v];
     for (int k = 0; k < NW; ++k) {
-        o[34 + k] = wval[(size_t)k * Vpad + v];
+        const T wt = wval[(size_t)k * Vpad + v];
+        o[34 + k] = (double)wt > 1e-12 ? wt : (T)0;   // assignedJoints keeps weights > 1e-12 only (AvatarModel.cpp:81)
         o[34 + NW + k] = (T)wjoint[(size_t)k * Vpad + v];
     }
     for (int i = 34 + 2 * NW; i < IcpRec<NW>::WORDS; ++i) o[i] = 0;
@@ -246,10 +247,11 @@ __global__ void __launch_bounds__(32 * NWARPS, 1) icp_accumulate_kernel(const T*
 #pragma unroll
     for (int s = 0; s < NS; ++s) sh[s] = 0;
     int curj[NW];
-    T G[NW][12], bin[NW][6];
+    T curjT[NW], G[NW][12], bin[NW][6];
 #pragma unroll
     for (int k = 0; k < NW; ++k) {
         curj[k] = -1;
+        curjT[k] = (T)-1;
 #pragma unroll
         for (int c = 0; c < 6; ++c) bin[k][c] = 0;
 #pragma unroll
@@ -299,13 +301,14 @@ __global__ void __launch_bounds__(32 * NWARPS, 1) icp_accumulate_kernel(const T*
 #pragma unroll
             for (int k = 0; k < NW; ++k) {
                 const T wt = wj[2 + k];
-                if ((double)wt > 1e-12) {   // assignedJoints keeps weights > 1e-12 (AvatarModel.cpp:81)
-                    const int jk = (int)wj[2 + NW + k];
-                    if (jk != curj[k]) {    // warp-uniform: the vertex is
+                if (wt > (T)0) {            // slots the reference does not assign carry weight 0 (icp_records_kernel)
+                    if (wj[2 + NW + k] != curjT[k]) {    // warp-uniform: the vertex is
                         if (curj[k] >= 0) {
 #pragma unroll
                             for (int cc = 0; cc < 6; ++cc) { atomicAdd(&sBin[(curj[k] * 6 + cc) * 32 + lane], bin[k][cc]); bin[k][cc] = 0; }
                         }
+                        curjT[k] = wj[2 + NW + k];
+                        const int jk = (int)curjT[k];
                         curj[k] = jk;
 #pragma unroll
                         for (int cc = 0; cc < 12; ++cc) G[k][cc] = sT[(jk * 12 + cc) * ICP_TPAD + lane];
@@ -329,7 +332,7 @@ __global__ void __launch_bounds__(32 * NWARPS, 1) icp_accumulate_kernel(const T*
 #pragma unroll
             for (int k = 0; k < NW; ++k) {
                 const T wt = wj[2 + k];
-                if ((double)wt > 1e-12) {
+                if (wt > (T)0) {
                     const T wr[3] = {wt * rs[0], wt * rs[1], wt * rs[2]};
                     bin[k][0] += Pk[k][1] * wr[2] - Pk[k][2] * wr[1];
                     bin[k][1] += Pk[k][2] * wr[0] - Pk[k][0] * wr[2];
@@ -378,54 +381,89 @@ __global__ void __launch_bounds__(32 * NWARPS, 1) icp_accumulate_kernel(const T*
 // ---------------------------------------------------------------------------------------------------------------------
 // per-body epilogue (float64): subtree sums, tangent-space gradient, cost
 // ---------------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(64) icp_finish_kernel(const SkeletonConst* __restrict__ sk, int B, int shape_enabled,
-                                                        const double* __restrict__ acc, const double* __restrict__ scatter,
-                                                        const double* __restrict__ jointPos, const double* __restrict__ jointTrans,
-                                                        double* __restrict__ cost, double* __restrict__ grad) {
-    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(128) icp_finish_kernel(const SkeletonConst* __restrict__ sk, int B, int shape_enabled,
+                                                         const double* __restrict__ acc, const double* __restrict__ scatter,
+                                                         const double* __restrict__ jointPos, const double* __restrict__ jointTrans,
+                                                         double* __restrict__ cost, double* __restrict__ grad) {
+    // warp = body, lane = joint
+    __shared__ double s_ab[4][NJ][6];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int b = blockIdx.x * 4 + warp;
     if (b >= B) return;
     const double* a = acc + (size_t)b * ICP_ACC;
     const double* G = jointTrans + (size_t)b * NJ * 12;   // per joint col-major [G | t]
     const double* g = jointPos + (size_t)b * NJ * 3;
     double* out = grad + (size_t)b * ICP_NC;
-    cost[b] = 0.5 * (a[0] + scatter[b]);
-    for (int c = 0; c < 3; ++c) out[c] = a[1 + c];
-    double A[NJ][3], Bs[NJ][3], sg[NS];
-    for (int s = 0; s < NS; ++s) sg[s] = a[4 + s];
-    for (int k = 0; k < NJ; ++k)
-        for (int c = 0; c < 3; ++c) { A[k][c] = a[16 + 6 * k + c]; Bs[k][c] = a[16 + 6 * k + 3 + c]; }
-    if (shape_enabled) {
-        // - sum_k S_k^T (G_k^T b_k), b_k before the subtree sums
-        for (int k = 0; k < NJ; ++k) {
-            double y[3];
-            for (int c = 0; c < 3; ++c) y[c] = G[12 * k + 3 * c] * Bs[k][0] + G[12 * k + 3 * c + 1] * Bs[k][1] + G[12 * k + 3 * c + 2] * Bs[k][2];
-            for (int s = 0; s < NS; ++s)
-                sg[s] -= sk->JSR[(3 * k) * NS + s] * y[0] + sk->JSR[(3 * k + 1) * NS + s] * y[1] + sk->JSR[(3 * k + 2) * NS + s] * y[2];
+    const int j = lane < NJ ? lane : 0;
+    const bool act = lane < NJ;
+    const int pa = sk->parent[j];
+    // ancestors-or-self of the lane's joint as a bit mask (parents precede children: model.cu checks parent[j] < j)
+    uint32_t anc = 0;
+    for (int k = j; k >= 0; k = sk->parent[k]) anc |= 1u << k;
+    double ab[6];
+#pragma unroll
+    for (int c = 0; c < 6; ++c) { ab[c] = act ? a[16 + 6 * j + c] : 0.0; if (act) s_ab[warp][j][c] = ab[c]; }
+    __syncwarp();
+    double sg[NS];
+#pragma unroll
+    for (int s = 0; s < NS; ++s) sg[s] = 0.0;
+    double Gj[9];
+#pragma unroll
+    for (int c = 0; c < 9; ++c) Gj[c] = G[12 * j + c];
+    if (shape_enabled && act) {   // - S_j^T (G_j^T b_j), b_j before the subtree sums
+        double y[3];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) y[c] = Gj[3 * c] * ab[3] + Gj[3 * c + 1] * ab[4] + Gj[3 * c + 2] * ab[5];
+#pragma unroll
+        for (int s = 0; s < NS; ++s)
+            sg[s] -= sk->JSR[(3 * j) * NS + s] * y[0] + sk->JSR[(3 * j + 1) * NS + s] * y[1] + sk->JSR[(3 * j + 2) * NS + s] * y[2];
+    }
+    // subtree sums A_j, B_j: every joint k that has j among its ancestors-or-self
+    double AB[6] = {0, 0, 0, 0, 0, 0};
+    for (int k = 0; k < NJ; ++k) {   // same trip count on every lane: the shuffle needs the whole warp
+        const uint32_t ak = __shfl_sync(0xffffffffu, anc, k);
+        if ((ak >> j) & 1u) {
+#pragma unroll
+            for (int c = 0; c < 6; ++c) AB[c] += s_ab[warp][k][c];
         }
     }
-    for (int j = NJ - 1; j >= 1; --j) {   // parents precede children (model.cu checks parent[j] < j)
-        const int pa = sk->parent[j];
-        for (int c = 0; c < 3; ++c) { A[pa][c] += A[j][c]; Bs[pa][c] += Bs[j][c]; }
-    }
-    for (int j = 0; j < NJ; ++j) {
-        const double* gj = g + 3 * j;
-        const double tq[3] = {A[j][0] - (gj[1] * Bs[j][2] - gj[2] * Bs[j][1]), A[j][1] - (gj[2] * Bs[j][0] - gj[0] * Bs[j][2]),
-                              A[j][2] - (gj[0] * Bs[j][1] - gj[1] * Bs[j][0])};
+    const double* gj = g + 3 * j;
+    const double tq[3] = {AB[0] - (gj[1] * AB[5] - gj[2] * AB[4]), AB[1] - (gj[2] * AB[3] - gj[0] * AB[5]),
+                          AB[2] - (gj[0] * AB[4] - gj[1] * AB[3])};
+    if (act) {
         if (j == 0) {
+#pragma unroll
             for (int c = 0; c < 3; ++c) out[3 + c] = 2.0 * tq[c];
         } else {
-            const double* Gp = G + 12 * sk->parent[j];
+            double Gp[9];
+#pragma unroll
+            for (int c = 0; c < 9; ++c) Gp[c] = G[12 * pa + c];
+#pragma unroll
             for (int c = 0; c < 3; ++c) out[3 + 3 * j + c] = 2.0 * (Gp[3 * c] * tq[0] + Gp[3 * c + 1] * tq[1] + Gp[3 * c + 2] * tq[2]);
             if (shape_enabled) {   // + (S_j - S_parent)^T G_parent^T B_j
-                const int pa = sk->parent[j];
                 double y[3];
-                for (int c = 0; c < 3; ++c) y[c] = Gp[3 * c] * Bs[j][0] + Gp[3 * c + 1] * Bs[j][1] + Gp[3 * c + 2] * Bs[j][2];
+#pragma unroll
+                for (int c = 0; c < 3; ++c) y[c] = Gp[3 * c] * AB[3] + Gp[3 * c + 1] * AB[4] + Gp[3 * c + 2] * AB[5];
+#pragma unroll
                 for (int s = 0; s < NS; ++s)
+#pragma unroll
                     for (int c = 0; c < 3; ++c) sg[s] += (sk->JSR[(3 * j + c) * NS + s] - sk->JSR[(3 * pa + c) * NS + s]) * y[c];
             }
         }
     }
-    for (int s = 0; s < NS; ++s) out[3 + 3 * NJ + s] = shape_enabled ? sg[s] : 0.0;
+#pragma unroll
+    for (int s = 0; s < NS; ++s) {
+#pragma unroll
+        for (int o = 16; o; o >>= 1) sg[s] += __shfl_xor_sync(0xffffffffu, sg[s], o);
+    }
+    if (lane == 0) cost[b] = 0.5 * (a[0] + scatter[b]);
+    if (lane < 3) out[lane] = a[1 + lane];
+    if (lane < NS) {
+        double v = 0.0;
+#pragma unroll
+        for (int s = 0; s < NS; ++s) if (s == lane) v = sg[s];
+        out[3 + 3 * NJ + lane] = shape_enabled ? a[4 + lane] + v : 0.0;
+    }
 }
 
 // The sums over vertices do not depend on the order, so the vertices are processed sorted by their tuple of assigned joints:
@@ -508,7 +546,9 @@ static int launch_accumulate(const b3d_icp* h, const double* w, cudaStream_t st)
         double best = 0.0;
         const int hi = h->groups >= 2 * 148 ? 4 : 32;
         for (int sp = 1; sp <= hi; ++sp) {
-            const double waves = (double)h->groups * sp / 148.0, eff = waves / std::ceil(waves);
+            // whole waves, and a CTA's fixed cost (transform staging, final reduction) taken as 60 vertices' worth of work
+            const double waves = (double)h->groups * sp / 148.0, per = (double)m->V / sp;
+            const double eff = waves / std::ceil(waves) * per / (per + 60.0);
             if (eff > best + 1e-9) { best = eff; vsplit = sp; }
         }
     }
@@ -604,7 +644,7 @@ int b3d_icp_eval_dev(b3d_icp* h, const double* w, const double* p, const double*
     else
         rc = m->nw == 4 ? launch_accumulate<double, 4, 8>(h, w, st) : launch_accumulate<double, 8, 8>(h, w, st);
     if (rc) return rc;
-    icp_finish_kernel<<<(B + 63) / 64, 64, 0, st>>>(m->d_sk, B, (flags & B3D_ICP_POSE_ONLY) ? 0 : 1, h->acc, h->scatter, h->jp, h->jt, cost, grad);
+    icp_finish_kernel<<<(B + 3) / 4, 128, 0, st>>>(m->d_sk, B, (flags & B3D_ICP_POSE_ONLY) ? 0 : 1, h->acc, h->scatter, h->jp, h->jt, cost, grad);
     B3D_LAUNCH_CHECK();
     return B3D_OK;
 }
