@@ -139,6 +139,9 @@ __global__ void __launch_bounds__(256) icp_quat_kernel(int n, const double* __re
 // ---------------------------------------------------------------------------------------------------------------------
 // fused shape blend + skinning + residual + gradient accumulation.  grid = (body groups of 32, vertex splits)
 // ---------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float fma_(float a, float b, float c) { return fmaf(a, b, c); }
+__device__ __forceinline__ double fma_(double a, double b, double c) { return fma(a, b, c); }
+
 template <typename T> struct Vec4T;
 template <> struct Vec4T<float> { using type = float4; };
 template <> struct Vec4T<double> { using type = double4; };
@@ -297,12 +300,16 @@ __global__ void __launch_bounds__(32 * NWARPS, 1) icp_accumulate_kernel(const T*
                     x[cc] = a;
                 }
             }
-            T Pk[NW][3], P[3] = {0, 0, 0};
+            // A weight slot keeps its joint over long runs of the sorted vertices: one (rarely taken) branch per vertex looks
+            // after the changes; slots the reference does not assign carry weight 0 (icp_records_kernel), keep whatever
+            // transform they hold and contribute exact zeros, so the arithmetic below is branch free.
+            bool changed = false;
 #pragma unroll
-            for (int k = 0; k < NW; ++k) {
-                const T wt = wj[2 + k];
-                if (wt > (T)0) {            // slots the reference does not assign carry weight 0 (icp_records_kernel)
-                    if (wj[2 + NW + k] != curjT[k]) {    // warp-uniform: the vertex is
+            for (int k = 0; k < NW; ++k) changed |= (wj[2 + k] > (T)0) & (wj[2 + NW + k] != curjT[k]);
+            if (changed) {   // warp-uniform: the vertex is
+#pragma unroll
+                for (int k = 0; k < NW; ++k) {
+                    if ((wj[2 + k] > (T)0) & (wj[2 + NW + k] != curjT[k])) {
                         if (curj[k] >= 0) {
 #pragma unroll
                             for (int cc = 0; cc < 6; ++cc) { atomicAdd(&sBin[(curj[k] * 6 + cc) * 32 + lane], bin[k][cc]); bin[k][cc] = 0; }
@@ -313,18 +320,23 @@ __global__ void __launch_bounds__(32 * NWARPS, 1) icp_accumulate_kernel(const T*
 #pragma unroll
                         for (int cc = 0; cc < 12; ++cc) G[k][cc] = sT[(jk * 12 + cc) * ICP_TPAD + lane];
                     }
+                }
+            }
+            T Pk[NW][3], P[3] = {0, 0, 0};
 #pragma unroll
-                    for (int r = 0; r < 3; ++r) {
-                        Pk[k][r] = G[k][r] * x[0] + G[k][3 + r] * x[1] + G[k][6 + r] * x[2] + G[k][9 + r];
-                        P[r] += wt * Pk[k][r];
-                    }
+            for (int k = 0; k < NW; ++k) {
+                const T wt = wj[2 + k];
+#pragma unroll
+                for (int r = 0; r < 3; ++r) {
+                    Pk[k][r] = fma_(G[k][r], x[0], fma_(G[k][3 + r], x[1], fma_(G[k][6 + r], x[2], G[k][9 + r])));
+                    P[r] = fma_(wt, Pk[k][r], P[r]);
                 }
             }
             // sum of the vertex's residuals and its cost share
             const T n = mu.w;
             const T e0 = P[0] - mu.x, e1 = P[1] - mu.y, e2 = P[2] - mu.z;
             const T rs[3] = {n * e0, n * e1, n * e2};
-            cost += n * (e0 * e0 + e1 * e1 + e2 * e2);
+            cost = fma_(n, fma_(e0, e0, fma_(e1, e1, e2 * e2)), cost);
 #pragma unroll
             for (int cc = 0; cc < 3; ++cc) gp[cc] += rs[cc];
             // per-joint sums, and y = T^T rs = sum_k G_k^T (w_k rs) for the shape gradient
@@ -332,20 +344,21 @@ __global__ void __launch_bounds__(32 * NWARPS, 1) icp_accumulate_kernel(const T*
 #pragma unroll
             for (int k = 0; k < NW; ++k) {
                 const T wt = wj[2 + k];
-                if (wt > (T)0) {
+                {
                     const T wr[3] = {wt * rs[0], wt * rs[1], wt * rs[2]};
-                    bin[k][0] += Pk[k][1] * wr[2] - Pk[k][2] * wr[1];
-                    bin[k][1] += Pk[k][2] * wr[0] - Pk[k][0] * wr[2];
-                    bin[k][2] += Pk[k][0] * wr[1] - Pk[k][1] * wr[0];
+                    // straight FMA chains into the accumulators (one instruction per product)
+                    bin[k][0] = fma_(Pk[k][1], wr[2], fma_(-Pk[k][2], wr[1], bin[k][0]));
+                    bin[k][1] = fma_(Pk[k][2], wr[0], fma_(-Pk[k][0], wr[2], bin[k][1]));
+                    bin[k][2] = fma_(Pk[k][0], wr[1], fma_(-Pk[k][1], wr[0], bin[k][2]));
                     bin[k][3] += wr[0]; bin[k][4] += wr[1]; bin[k][5] += wr[2];
-                    y0 += G[k][0] * wr[0] + G[k][1] * wr[1] + G[k][2] * wr[2];
-                    y1 += G[k][3] * wr[0] + G[k][4] * wr[1] + G[k][5] * wr[2];
-                    y2 += G[k][6] * wr[0] + G[k][7] * wr[1] + G[k][8] * wr[2];
+                    y0 = fma_(G[k][0], wr[0], fma_(G[k][1], wr[1], fma_(G[k][2], wr[2], y0)));
+                    y1 = fma_(G[k][3], wr[0], fma_(G[k][4], wr[1], fma_(G[k][5], wr[2], y1)));
+                    y2 = fma_(G[k][6], wr[0], fma_(G[k][7], wr[1], fma_(G[k][8], wr[2], y2)));
                 }
             }
             // shape: D^T y, shapedirs read again from the tile
 #pragma unroll
-            for (int q = 0; q < NS; ++q) sh[q] += r1[4 + q] * y0 + r1[4 + NS + q] * y1 + r1[4 + 2 * NS + q] * y2;
+            for (int q = 0; q < NS; ++q) sh[q] = fma_(r1[4 + q], y0, fma_(r1[4 + NS + q], y1, fma_(r1[4 + 2 * NS + q], y2, sh[q])));
         }
         __syncwarp();
     }
