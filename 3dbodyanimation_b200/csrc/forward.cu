@@ -485,8 +485,12 @@ static int forward_impl(const b3d_model* m, int B, const T* w, const T* p, const
         B3D_CUDA(cudaMallocAsync(&pf, sizeof(T) * (size_t)B * B3D_POSEDIRS_DIM, st));
         if (!use_tc) B3D_CUDA(cudaMallocAsync(&off, sizeof(T) * (size_t)B * 3 * m->Vpad, st));
     }
-    smpl_joints_kernel<T><<<(B + JW - 1) / JW, 32 * JW, 0, st>>>(m->d_sk, B, w, p, r, jointPos, G, pf);
-    B3D_LAUNCH_CHECK();
+    if (flags & B3D_FWD_GIVEN_TRANSFORMS) {
+        if (!jointTrans || !cloud || use_pd) return set_error(B3D_EINVAL, "B3D_FWD_GIVEN_TRANSFORMS needs jointTrans and cloud, and excludes B3D_FWD_POSEDIRS");
+    } else {
+        smpl_joints_kernel<T><<<(B + JW - 1) / JW, 32 * JW, 0, st>>>(m->d_sk, B, w, p, r, jointPos, G, pf);
+        B3D_LAUNCH_CHECK();
+    }
     if (use_tc) {
         if (int rc = launch_lbs_tc(m, B, (const float*)w, (const float*)G, (const float*)pf, (float*)cloud, st)) return rc;
         B3D_LAUNCH_CHECK();
@@ -579,6 +583,7 @@ int b3d_smpl_forward(const b3d_model* m, int32_t B, int32_t dtype, const void* w
     if (e == cudaSuccess) e = cudaMemcpy(dw, w, es * nb * NS, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(dp, p, es * nb * 3, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(dr, r, es * nb * NJ * 9, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && (flags & B3D_FWD_GIVEN_TRANSFORMS) && jointTrans) e = cudaMemcpy(djt, jointTrans, es * nb * NJ * 12, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) {
         rc = b3d_smpl_forward_dev(m, B, dtype, dw, dp, dr, dc, djp, djt, flags, nullptr);
         if (!rc) {

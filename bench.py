@@ -31,6 +31,7 @@ sys.path.insert(0, ROOT)
 
 FRAMES_PER_GPU = 1000
 FLOP_PER_FRAME_ITER_C2 = 0.37e6      # residual+Jacobian, J^T J, GMM, Cholesky n=86, candidate evaluation
+LBS_BYTES_PER_BODY_F32 = 83872       # the skinning kernel alone: 40 B shape + 1,152 B transforms in, 82,680 B cloud out
 FWD_BYTES_PER_BODY_F32 = 85036       # 916 B in + 82,680 B cloud + 288 B jointPos + 1,152 B jointTrans
 CAM = None
 
@@ -299,15 +300,26 @@ def run_b200(args):
         jevs.append((e0, e1))
     torch.cuda.synchronize()
     joints_ms = float(np.mean([a.elapsed_time(b) for a, b in jevs]))
+    # the skinning kernel alone: same call with the transforms given (B3D_FWD_GIVEN_TRANSFORMS = 0x100), so that the CUDA events
+    # bracket exactly one launch of smpl_lbs_tc_kernel
+    lbs = lambda: capi.check(lib.b3d_smpl_forward_dev(gm.h, FB, capi.F32, P(fw), P(fp_), P(fr_), P(fcloud), P(fjp), P(fjt), 0x100, C.c_void_p(st)), "lbs only")
+    lbs(); torch.cuda.synchronize()
+    levs = []
+    for _ in range(10):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); lbs(); e1.record()
+        levs.append((e0, e1))
+    torch.cuda.synchronize()
+    lbs_ms = float(np.mean([a.elapsed_time(b) for a, b in levs]))
     clk = clocks.stop() if rank == 0 else None
 
     # max over ranks of the device-timed step, the e2e step and the forward
-    tt = torch.tensor([step_ms, e2e_ms, fwd_ms, fit_ms], dtype=torch.float64, device=dev)
+    tt = torch.tensor([step_ms, e2e_ms, fwd_ms, fit_ms, lbs_ms], dtype=torch.float64, device=dev)
     cnt = torch.tensor([float(iters_total), float(usable)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
-    step_ms, e2e_ms, fwd_ms, fit_ms = [float(x) for x in tt.tolist()]
+    step_ms, e2e_ms, fwd_ms, fit_ms, lbs_ms = [float(x) for x in tt.tolist()]
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -318,7 +330,8 @@ def run_b200(args):
     if os.path.exists(pk):
         peaks = json.load(open(pk))
     hbm_peak, peak_src = (float(peaks["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, burst copy)") if "hbm_gbs" in peaks else (6650.0, "fallback (B200_PROFILING.md)")
-    achieved = FB * FWD_BYTES_PER_BODY_F32 / (fwd_ms * 1e-3) / 1e9
+    achieved_call = FB * FWD_BYTES_PER_BODY_F32 / (fwd_ms * 1e-3) / 1e9
+    achieved = FB * LBS_BYTES_PER_BODY_F32 / (lbs_ms * 1e-3) / 1e9
     traffic = None
     tfile = os.path.join(ROOT, "profiles", "lbs_traffic.json")
     if os.path.exists(tfile):
@@ -369,11 +382,13 @@ def run_b200(args):
                 "ms_per_step": e2e_ms, "call": "b3d_fit_frames (host pointers, pinned); cloud computed and left on the device"},
         "gpu_launches": launches,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
-                     "kernel": "smpl_lbs_tc_kernel (tcgen05 shape blend + skinning) inside one b3d_smpl_forward_dev call, which also runs "
-                               "smpl_joints_kernel<float>; achieved is the WHOLE call",
-                     "joints_kernel_ms": joints_ms, "lbs_kernel_gbs_est": FB * FWD_BYTES_PER_BODY_F32 / max(fwd_ms - joints_ms, 1e-6) / 1e6,
+                     "kernel": "smpl_lbs_tc_kernel (tcgen05 shape blend + skinning), one launch bracketed by CUDA events "
+                               "(b3d_smpl_forward_dev with B3D_FWD_GIVEN_TRANSFORMS); whole_call_* = the same batch through joints + skinning",
+                     "ms_per_kernel_launch": lbs_ms, "bytes_per_body": LBS_BYTES_PER_BODY_F32,
+                     "whole_call_gbs": achieved_call, "whole_call_frac": achieved_call / hbm_peak, "whole_call_bytes_per_body": FWD_BYTES_PER_BODY_F32,
+                     "joints_kernel_ms": joints_ms,
                      "write_only_peak_gbs": 5400.0, "write_only_peak_source": "tools/store_probe.cu on this pool's B200 (profiles/r01_store_probe.log)",
-                     "workload": f"forward sweep point B={FB} (BASELINE configs[3]), {FWD_BYTES_PER_BODY_F32} algorithmic B/body", "ms_per_launch": fwd_ms,
+                     "workload": f"forward sweep point B={FB} (BASELINE configs[3])", "whole_call_ms": fwd_ms,
                      "verts_per_sec": world * FB * V / (fwd_ms * 1e-3), "peak_source": peak_src},
         "roofline_lm": {"kernel": "fit_single_kernel<128>", "bound": "fp64 ALU / latency (not HBM: ~1.2 KB algorithmic I/O per frame)",
                         "ms_per_launch": fit_ms, "share_of_step": fit_ms / step_ms, "lm_iterations_per_step": cnt[0].item() / world,

@@ -134,7 +134,11 @@ enum {
     B3D_FWD_LBS_TC = 0x10,
     B3D_FWD_LBS_SORTED = 0x20,
     B3D_FWD_LBS_BODYLANE = 0x40,
-    B3D_FWD_LBS_GENERIC = 0x80
+    B3D_FWD_LBS_GENERIC = 0x80,
+    /* skinning only: jointTrans is an INPUT (the rest->posed transforms of an earlier call), the joint chain is not run and
+     * p / r / jointPos are ignored.  Lets a caller re-skin with new shape-independent data, and lets bench.py time the skinning
+     * kernel alone. */
+    B3D_FWD_GIVEN_TRANSFORMS = 0x100
 };
 
 /* Inputs per body: w (10) = Avatar::w, p (3) = Avatar::p, r (24 x 9, col-major) = Avatar::r.

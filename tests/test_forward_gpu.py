@@ -3,7 +3,7 @@ Tolerance (BASELINE.json north_star): vertices 1e-5 relative; indexing outputs b
 import numpy as np
 import pytest
 
-from conftest import rel_err
+from conftest import pkg, rel_err
 
 pytestmark = pytest.mark.gpu
 
@@ -137,3 +137,18 @@ def test_avatar_object_interface(api, gmodel, omodel, synth):
     av.update()
     c0, jp0, jt0 = omodel.forward(av.w[None], av.p[None], av.r[None])
     assert rel_err(av.cloud, c0[0]) < 1e-13 and rel_err(av.jointPos, jp0[0]) < 1e-13 and rel_err(av.jointTrans, jt0[0]) < 1e-13
+
+
+def test_forward_given_transforms_reskins_identically(synth, model_np):
+    """B3D_FWD_GIVEN_TRANSFORMS: the skinning kernel alone, fed the transforms of an earlier call, writes the same cloud."""
+    api, capi = pkg("api"), pkg("_capi")
+    gm = api.AvatarModel(model_np)
+    for b in (5, 700):     # tile-sorted kernel / tensor-core kernel
+        fin = synth.make_forward_inputs(b, 77)
+        cloud, jp, jt = api.smpl_forward(gm, fin["w"], fin["p"], fin["r"], dtype=np.float32)
+        w = np.ascontiguousarray(fin["w"], dtype=np.float32)
+        junk = np.zeros((b, 24, 9), dtype=np.float32)          # p / r are ignored
+        again = np.zeros_like(cloud)
+        capi.check(capi.lib().b3d_smpl_forward(gm.h, b, capi.F32, capi.ptr(w), capi.ptr(junk), capi.ptr(junk), capi.ptr(again), None,
+                                               capi.ptr(jt), 0x100), "given transforms")
+        assert np.array_equal(again, cloud)
