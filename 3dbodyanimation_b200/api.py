@@ -444,12 +444,14 @@ class IcpProblem:
         self.dptr = np.ascontiguousarray(dptr, dtype=np.int64)
         self.B = self.cptr.shape[0] - 1
         mpt = np.ascontiguousarray(mpt, dtype=np.int32)
-        dpt = np.ascontiguousarray(dpt, dtype=np.int32)
+        dpt = None if dpt is None else np.ascontiguousarray(dpt, dtype=np.int32)   # None: pair e is data point e (icp_nearest output)
         data = np.ascontiguousarray(data, dtype=dt).reshape(-1, 3)
-        if mpt.shape[0] != self.cptr[-1] or dpt.shape[0] != self.cptr[-1] or data.shape[0] != self.dptr[-1]:
+        if mpt.shape[0] != self.cptr[-1] or (dpt is not None and dpt.shape[0] != self.cptr[-1]) or data.shape[0] != self.dptr[-1]:
             raise ValueError("IcpProblem: offsets do not match the pair / data arrays")
-        if mpt.size and (mpt.min() < 0 or mpt.max() >= model.numPoints):
+        if mpt.size and mpt.max() >= model.numPoints:
             raise ValueError("IcpProblem: model point out of range")
+        if dpt is None and not np.array_equal(self.cptr, self.dptr):
+            raise ValueError("IcpProblem: dpt=None needs one pair per data point (cptr == dptr)")
         h = C.c_void_p()
         check(lib().b3d_icp_create(model.h, self.B, F64 if dt == np.float64 else F32, ptr(self.cptr), ptr(mpt), ptr(dpt),
                                    ptr(self.dptr), ptr(data), 0, C.byref(h)), "b3d_icp_create")
@@ -466,3 +468,24 @@ class IcpProblem:
         cost, grad = np.empty(self.B), np.empty((self.B, 85))
         check(lib().b3d_icp_eval(self.h, ptr(w), ptr(p), ptr(q), 0 if shape else 2, ptr(cost), ptr(grad)), "b3d_icp_eval")
         return dict(cost=cost, grad=grad)
+
+
+def icp_nearest(model: AvatarModel, cloud, model_part, dptr, data, data_part, visible=None, dtype=np.float64):
+    """findNN with invert = true (external/avatar/AvatarOptimizer.cpp:841-907): for every data point the nearest visible model point
+    with the same part label (-1: none).  cloud (B, V, 3), model_part (V,), visible (B, V) or None, body b's data points at
+    dptr[b]:dptr[b+1].  The result pairs with ``IcpProblem(model, dptr, nn, None, dptr, data)``."""
+    dt = np.dtype(dtype)
+    cloud = np.ascontiguousarray(cloud, dtype=dt).reshape(-1, model.numPoints, 3)
+    b = cloud.shape[0]
+    model_part = np.ascontiguousarray(model_part, dtype=np.int32).reshape(model.numPoints)
+    dptr = np.ascontiguousarray(dptr, dtype=np.int64).reshape(b + 1)
+    data = np.ascontiguousarray(data, dtype=dt).reshape(-1, 3)
+    data_part = np.ascontiguousarray(data_part, dtype=np.int32).reshape(data.shape[0])
+    if data.shape[0] != dptr[-1]:
+        raise ValueError("icp_nearest: dptr does not match the data array")
+    vis = None if visible is None else np.ascontiguousarray(visible, dtype=np.uint8).reshape(b, model.numPoints)
+    out = np.full(data.shape[0], -2, dtype=np.int32)
+    nparts = int(max(model_part.max(), data_part.max() if data_part.size else 0)) + 1
+    check(lib().b3d_icp_nearest(model.h, b, F64 if dt == np.float64 else F32, ptr(cloud), nparts, ptr(model_part), ptr(vis), ptr(dptr),
+                                ptr(data), ptr(data_part), 0, ptr(out)), "b3d_icp_nearest")
+    return out

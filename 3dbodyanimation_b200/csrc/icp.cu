@@ -70,8 +70,9 @@ __global__ void __launch_bounds__(256) icp_gather_kernel(int B, int V, const int
                                                          const T* __restrict__ data, double* __restrict__ tmp) {
     const int64_t n = cptr[B];
     for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < n; e += (int64_t)gridDim.x * blockDim.x) {
+        if (mpt[e] < 0) continue;   // unmatched data point (b3d_icp_nearest)
         const int b = body_of_pair(cptr, B, e);
-        const T* d = data + 3 * (dptr[b] + dpt[e]);
+        const T* d = data + 3 * (dptr[b] + (dpt ? (int64_t)dpt[e] : e - cptr[b]));
         double* t = tmp + 4 * ((size_t)b * V + mpt[e]);
         atomicAdd(t + 0, (double)d[0]);
         atomicAdd(t + 1, (double)d[1]);
@@ -104,9 +105,9 @@ __global__ void __launch_bounds__(256) icp_scatter_kernel(int B, int V, const in
         const int64_t e = e0 + threadIdx.x;
         int b = -1;
         double s = 0.0;
-        if (e < n) {
+        if (e < n && mpt[e] >= 0) {
             b = body_of_pair(cptr, B, e);
-            const T* d = data + 3 * (dptr[b] + dpt[e]);
+            const T* d = data + 3 * (dptr[b] + (dpt ? (int64_t)dpt[e] : e - cptr[b]));
             const double* mu = tmp + 4 * ((size_t)b * V + mpt[e]);   // float64 mean (icp_targets_kernel)
             const double ax = (double)d[0] - mu[0], ay = (double)d[1] - mu[1], az = (double)d[2] - mu[2];
             s = ax * ax + ay * ay + az * az;
@@ -579,7 +580,7 @@ extern "C" {
 
 int b3d_icp_create(const b3d_model* m, int32_t B, int32_t dtype, const int64_t* cptr, const int32_t* mpt, const int32_t* dpt,
                    const int64_t* dptr, const void* data, int32_t flags, b3d_icp** out) {
-    if (!m || !cptr || !mpt || !dpt || !dptr || !data || !out) return set_error(B3D_EINVAL, "b3d_icp_create: null argument");
+    if (!m || !cptr || !mpt || !dptr || !data || !out) return set_error(B3D_EINVAL, "b3d_icp_create: null argument");
     if (B <= 0) return set_error(B3D_EINVAL, "b3d_icp_create: B <= 0");
     if (dtype != B3D_F32 && dtype != B3D_F64) return set_error(B3D_EINVAL, "b3d_icp_create: bad dtype %d", dtype);
     if (m->nw != 4 && m->nw != 8) return set_error(B3D_EINVAL, "b3d_icp_create: models with more than 8 weights per vertex are not supported (nw = %d)", m->nw);
@@ -611,7 +612,7 @@ int b3d_icp_create(const b3d_model* m, int32_t B, int32_t dtype, const int64_t* 
         e = cudaMalloc(&d_mpt, sizeof(int32_t) * 2 * (size_t)std::max<int64_t>(np, 1));
         if (e == cudaSuccess) { d_dpt = d_mpt + std::max<int64_t>(np, 1); e = cudaMalloc(&d_data, es * 3 * (size_t)std::max<int64_t>(nd, 1)); }
         if (e == cudaSuccess) e = cudaMemcpy(d_mpt, mpt, sizeof(int32_t) * np, cudaMemcpyHostToDevice);
-        if (e == cudaSuccess) e = cudaMemcpy(d_dpt, dpt, sizeof(int32_t) * np, cudaMemcpyHostToDevice);
+        if (e == cudaSuccess && dpt) e = cudaMemcpy(d_dpt, dpt, sizeof(int32_t) * np, cudaMemcpyHostToDevice);
         if (e == cudaSuccess) e = cudaMemcpy(d_data, data, es * 3 * nd, cudaMemcpyHostToDevice);
     }
     int rc = B3D_OK;
@@ -619,7 +620,7 @@ int b3d_icp_create(const b3d_model* m, int32_t B, int32_t dtype, const int64_t* 
     if (!rc) rc = build_order(h);
     if (!rc) {
         const int32_t* pm = dev_in ? mpt : d_mpt;
-        const int32_t* pd = dev_in ? dpt : d_dpt;
+        const int32_t* pd = !dpt ? nullptr : dev_in ? dpt : d_dpt;
         const void* pdat = dev_in ? data : d_data;
         rc = dtype == B3D_F32 ? icp_reduce<float>(h, d_cptr, d_dptr, pm, pd, (const float*)pdat)
                               : icp_reduce<double>(h, d_cptr, d_dptr, pm, pd, (const double*)pdat);

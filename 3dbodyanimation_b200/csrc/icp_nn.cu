@@ -1,0 +1,154 @@
+// Correspondence search of ark::AvatarOptimizer's ICP loop: findNN with invert = true
+// (external/avatar/AvatarOptimizer.cpp:841-907, called at :1372-1375) — every data point is matched to the nearest VISIBLE model
+// point that carries its part label.  The reference builds a nanoflann kd-tree per part and asks it for the exact nearest
+// neighbour (metric_L2_Simple, eps = 0); here the search is exhaustive, which returns the same point: a body's posed cloud is
+// staged once per CTA in shared memory, grouped by part (invisible points as +inf so that they never win), threads are data
+// points and walk their part's slice — lanes of one part read the same address (broadcast).  The squared distance is formed as
+// (dx*dx + dy*dy) + dz*dz with separately rounded operations, so that the float64 instantiation reproduces the reference's
+// comparisons bit for bit; ties go to the lowest model index.  Output: matched model point per data point, -1 for none —
+// exactly the pair list b3d_icp_create takes (dpt = NULL).
+#include <algorithm>
+#include <limits>
+#include <vector>
+
+#include "internal.hpp"
+
+namespace b3d {
+
+constexpr int NN_THREADS = 256, NN_PER_THREAD = 4;
+
+template <typename T> __device__ __forceinline__ T inf_();
+template <> __device__ __forceinline__ float inf_<float>() { return __int_as_float(0x7f800000); }
+template <> __device__ __forceinline__ double inf_<double>() { return __longlong_as_double(0x7ff0000000000000LL); }
+__device__ __forceinline__ float mul_rn_(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ float add_rn_(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ double mul_rn_(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double add_rn_(double a, double b) { return __dadd_rn(a, b); }
+
+template <typename T>
+__global__ void __launch_bounds__(NN_THREADS) icp_nearest_kernel(int V, int nparts, const int32_t* __restrict__ part_ptr,
+                                                                 const int32_t* __restrict__ part_idx, const T* __restrict__ cloud,
+                                                                 const uint8_t* __restrict__ visible, const int64_t* __restrict__ dptr,
+                                                                 const T* __restrict__ data, const int32_t* __restrict__ data_part,
+                                                                 int32_t* __restrict__ out) {
+    extern __shared__ __align__(16) unsigned char nn_smem[];
+    T* sx = reinterpret_cast<T*>(nn_smem);
+    T* sy = sx + V;
+    T* sz = sy + V;
+    int32_t* sp = reinterpret_cast<int32_t*>(sz + V);   // [nparts + 1]
+    const int b = blockIdx.y;
+    const int64_t d0 = dptr[b], nd = dptr[b + 1] - d0;
+    const int64_t first = (int64_t)blockIdx.x * NN_THREADS * NN_PER_THREAD;
+    if (first >= nd) return;
+    const T* cb = cloud + 3 * (size_t)V * b;
+    const T inf = inf_<T>();
+    for (int k = threadIdx.x; k < V; k += NN_THREADS) {
+        const int v = part_idx[k];
+        const bool vis = !visible || visible[(size_t)V * b + v];
+        sx[k] = vis ? cb[3 * (size_t)v] : inf;
+        sy[k] = vis ? cb[3 * (size_t)v + 1] : inf;
+        sz[k] = vis ? cb[3 * (size_t)v + 2] : inf;
+    }
+    for (int k = threadIdx.x; k <= nparts; k += NN_THREADS) sp[k] = part_ptr[k];
+    __syncthreads();
+    for (int u = 0; u < NN_PER_THREAD; ++u) {
+        const int64_t i = first + (int64_t)u * NN_THREADS + threadIdx.x;
+        if (i >= nd) break;
+        const T px = data[3 * (d0 + i)], py = data[3 * (d0 + i) + 1], pz = data[3 * (d0 + i) + 2];
+        const int part = data_part[d0 + i];
+        int arg = -1;
+        if (part >= 0 && part < nparts) {
+            T best = inf;
+            const int k1 = sp[part + 1];
+            for (int k = sp[part]; k < k1; ++k) {
+                const T dx = px - sx[k], dy = py - sy[k], dz = pz - sz[k];
+                const T r = add_rn_(add_rn_(mul_rn_(dx, dx), mul_rn_(dy, dy)), mul_rn_(dz, dz));
+                if (r < best) { best = r; arg = k; }
+            }
+        }
+        out[d0 + i] = arg >= 0 ? part_idx[arg] : -1;
+    }
+}
+
+}  // namespace b3d
+
+using namespace b3d;
+
+extern "C" int b3d_icp_nearest(const b3d_model* m, int32_t B, int32_t dtype, const void* cloud, int32_t nparts, const int32_t* model_part,
+                               const uint8_t* visible, const int64_t* dptr, const void* data, const int32_t* data_part, int32_t flags,
+                               int32_t* nn_out) {
+    if (!m || !cloud || !model_part || !dptr || !data || !data_part || !nn_out) return set_error(B3D_EINVAL, "b3d_icp_nearest: null argument");
+    if (B <= 0 || nparts <= 0 || nparts > 4096) return set_error(B3D_EINVAL, "b3d_icp_nearest: bad B / nparts");
+    if (dtype != B3D_F32 && dtype != B3D_F64) return set_error(B3D_EINVAL, "b3d_icp_nearest: bad dtype %d", dtype);
+    if (int rc = require_device()) return rc;
+    const int V = m->V;
+    const size_t es = dtype == B3D_F32 ? 4 : 8;
+    // model points grouped by part, ascending index inside a part (= the order findNN fills its part clouds in, :865-874)
+    std::vector<int32_t> pptr(nparts + 1, 0), pidx(V);
+    int labelled = 0;
+    for (int v = 0; v < V; ++v)
+        if (model_part[v] >= 0 && model_part[v] < nparts) { ++pptr[model_part[v] + 1]; ++labelled; }
+    for (int k = 0; k < nparts; ++k) pptr[k + 1] += pptr[k];
+    {
+        std::vector<int32_t> fill(pptr.begin(), pptr.end() - 1);
+        for (int v = 0; v < V; ++v)
+            if (model_part[v] >= 0 && model_part[v] < nparts) pidx[fill[model_part[v]]++] = v;
+    }
+    for (int k = labelled; k < V; ++k) pidx[k] = 0;   // unlabelled model points are in no part's slice
+    int64_t maxnd = 0;
+    for (int b = 0; b < B; ++b) {
+        if (dptr[b + 1] < dptr[b]) return set_error(B3D_EINVAL, "b3d_icp_nearest: offsets of body %d decrease", b);
+        maxnd = std::max(maxnd, dptr[b + 1] - dptr[b]);
+    }
+    const int64_t ndt = dptr[B];
+    if (maxnd == 0) return B3D_OK;
+    const bool dev = (flags & B3D_ICP_DEVICE_INPUT) != 0;
+    int32_t* d_meta = nullptr;   // part_ptr | part_idx
+    int64_t* d_dptr = nullptr;
+    char* d_in = nullptr;
+    cudaError_t e = cudaMalloc(&d_meta, sizeof(int32_t) * (nparts + 1 + V));
+    if (e == cudaSuccess) e = cudaMalloc(&d_dptr, sizeof(int64_t) * (B + 1));
+    if (e == cudaSuccess) e = cudaMemcpy(d_meta, pptr.data(), sizeof(int32_t) * (nparts + 1), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_meta + nparts + 1, pidx.data(), sizeof(int32_t) * V, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(d_dptr, dptr, sizeof(int64_t) * (B + 1), cudaMemcpyHostToDevice);
+    const void *p_cloud = cloud, *p_data = data;
+    const uint8_t* p_vis = visible;
+    const int32_t* p_dpart = data_part;
+    int32_t* p_out = nn_out;
+    auto al = [](size_t x) { return (x + 255) / 256 * 256; };
+    if (e == cudaSuccess && !dev) {
+        const size_t s_cloud = al(es * 3 * (size_t)V * B), s_data = al(es * 3 * (size_t)ndt), s_part = al(4 * (size_t)ndt), s_vis = visible ? al((size_t)V * B) : 0;
+        e = cudaMalloc(&d_in, s_cloud + s_data + 2 * s_part + s_vis);
+        if (e == cudaSuccess) {
+            char *c = d_in, *d = c + s_cloud, *dp = d + s_data, *o = dp + s_part, *vs = o + s_part;
+            e = cudaMemcpy(c, cloud, es * 3 * (size_t)V * B, cudaMemcpyHostToDevice);
+            if (e == cudaSuccess) e = cudaMemcpy(d, data, es * 3 * (size_t)ndt, cudaMemcpyHostToDevice);
+            if (e == cudaSuccess) e = cudaMemcpy(dp, data_part, 4 * (size_t)ndt, cudaMemcpyHostToDevice);
+            if (e == cudaSuccess && visible) e = cudaMemcpy(vs, visible, (size_t)V * B, cudaMemcpyHostToDevice);
+            p_cloud = c; p_data = d; p_dpart = (const int32_t*)dp; p_out = (int32_t*)o; p_vis = visible ? (const uint8_t*)vs : nullptr;
+        }
+    }
+    int rc = B3D_OK;
+    if (e == cudaSuccess) {
+        const size_t smem = es * 3 * (size_t)V + 4 * (size_t)(nparts + 1);
+        const dim3 grid((unsigned)((maxnd + NN_THREADS * NN_PER_THREAD - 1) / (NN_THREADS * NN_PER_THREAD)), B);
+        if (smem > 232448) rc = set_error(B3D_EINVAL, "b3d_icp_nearest: model too large for the shared-memory cloud (%zu B)", smem);
+        else if (dtype == B3D_F32) {
+            e = cudaFuncSetAttribute(icp_nearest_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e == cudaSuccess)
+                icp_nearest_kernel<float><<<grid, NN_THREADS, smem>>>(V, nparts, d_meta, d_meta + nparts + 1, (const float*)p_cloud, p_vis, d_dptr,
+                                                                      (const float*)p_data, p_dpart, p_out);
+        } else {
+            e = cudaFuncSetAttribute(icp_nearest_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e == cudaSuccess)
+                icp_nearest_kernel<double><<<grid, NN_THREADS, smem>>>(V, nparts, d_meta, d_meta + nparts + 1, (const double*)p_cloud, p_vis, d_dptr,
+                                                                       (const double*)p_data, p_dpart, p_out);
+        }
+        if (!rc && e == cudaSuccess) { count_launch(); e = cudaGetLastError(); }
+        if (!rc && e == cudaSuccess) e = cudaStreamSynchronize(nullptr);
+        if (!rc && e == cudaSuccess && !dev) e = cudaMemcpy(nn_out, p_out, 4 * (size_t)ndt, cudaMemcpyDeviceToHost);
+    }
+    cudaFree(d_meta); cudaFree(d_dptr); cudaFree(d_in);
+    if (e != cudaSuccess) return set_error(B3D_ECUDA, "b3d_icp_nearest: %s", cudaGetErrorString(e));
+    return rc;
+}

@@ -166,11 +166,21 @@ enum {
 
 /* One set of correspondences per body (they stay fixed during a ceres::Solve, :1386-1412 / :1439): pairs e in
  * [cptr[b], cptr[b+1]) match model point mpt[e] with point dpt[e] of body b's data cloud, which starts at point dptr[b] of
- * `data` (3 values of `dtype` per point).  The cloud is reduced to one (mean, count) record per model point; `dtype` is also the
+ * `data` (3 values of `dtype` per point); dpt = NULL means pair e is data point e - cptr[b], and pairs with mpt[e] < 0 are
+ * skipped (the output of b3d_icp_nearest).  The cloud is reduced to one (mean, count) record per model point; `dtype` is also the
  * arithmetic type of the evaluation kernel (B3D_F32: fast path; B3D_F64: accuracy path). */
 int b3d_icp_create(const b3d_model* m, int32_t B, int32_t dtype, const int64_t* cptr, const int32_t* mpt, const int32_t* dpt,
                    const int64_t* dptr, const void* data, int32_t flags, b3d_icp** out);
 void b3d_icp_destroy(b3d_icp* h);
+/* Correspondence search: findNN with invert = true (external/avatar/AvatarOptimizer.cpp:841-907, called at :1372-1375).  For every
+ * data point the nearest VISIBLE model point of the same part, -1 if the part has none.  cloud: B x V x 3 posed model clouds
+ * (Avatar::cloud), model_part: V labels in [0, nparts) (host; modelPartLabels, :1296-1300), visible: B x V bytes or NULL
+ * (pointVisible), data / data_part: the bodies' data points and their labels, body b at [dptr[b], dptr[b+1]) (dptr host).
+ * nn_out has one entry per data point.  With B3D_ICP_DEVICE_INPUT cloud, visible, data, data_part and nn_out are device pointers.
+ * The result is the pair list of b3d_icp_create: cptr = dptr, mpt = nn_out, dpt = NULL (pair e <-> data point e; mpt < 0 skipped). */
+int b3d_icp_nearest(const b3d_model* m, int32_t B, int32_t dtype, const void* cloud, int32_t nparts, const int32_t* model_part,
+                    const uint8_t* visible, const int64_t* dptr, const void* data, const int32_t* data_part, int32_t flags,
+                    int32_t* nn_out);
 int b3d_icp_num_bodies(const b3d_icp* h);
 /* One evaluation at w (B x 10), p (B x 3), q (B x 24 x 4 quaternions in Eigen's coefficient order x, y, z, w):
  * cost (B) and grad (B x 85).  Host pointers / device pointers + stream. */

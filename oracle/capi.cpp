@@ -277,6 +277,13 @@ void orc_icp_eval(void* mp, int B, const double* w, const double* p, const doubl
                  shape_enabled, resid ? resid + 3 * c0 : nullptr, jac ? jac + 3 * c0 * NC : nullptr, cost + b, grad + (size_t)b * NC);
     }
 }
+void orc_icp_nearest(int B, int V, const double* cloud, const int32_t* model_part, const uint8_t* visible, const int64_t* dptr,
+                     const double* data, const int32_t* data_part, int32_t* out, int nthreads) {
+#pragma omp parallel for num_threads(nthreads > 0 ? nthreads : 1) schedule(dynamic, 1)
+    for (int b = 0; b < B; ++b)
+        icp_nearest(V, cloud + 3 * (size_t)V * b, model_part, visible ? visible + (size_t)V * b : nullptr, (int)(dptr[b + 1] - dptr[b]),
+                    data + 3 * dptr[b], data_part + dptr[b], out + dptr[b]);
+}
 void orc_quat_plus(int n, const double* x, const double* d, double* out) {
     for (int i = 0; i < n; ++i) quat_plus(x + 4 * i, d + 3 * i, out + 4 * i);
 }

@@ -203,4 +203,25 @@ void quat_plus(const double* x, const double* d, double* out) {
     }
 }
 
+
+// findNN, invert = true (AvatarOptimizer.cpp:841-907): every data point is matched to the nearest VISIBLE model point that carries
+// its part label; -1 when the part has none.  The reference asks a nanoflann kd-tree per part for the exact nearest neighbour
+// (metric_L2_Simple, eps = 0); exhaustive search returns the same point (ties, measure zero on real data, go to the first model
+// point in index order here).  correspondences[model point] then lists its data points in data order.
+void icp_nearest(int V, const double* cloud, const int* model_part, const uint8_t* visible, int nd, const double* data,
+                 const int* data_part, int* out) {
+    for (int i = 0; i < nd; ++i) {
+        const double* d = data + 3 * (size_t)i;
+        double best = std::numeric_limits<double>::infinity();
+        int arg = -1;
+        for (int v = 0; v < V; ++v) {
+            if (model_part[v] != data_part[i] || (visible && !visible[v])) continue;
+            const double dx = d[0] - cloud[3 * (size_t)v], dy = d[1] - cloud[3 * (size_t)v + 1], dz = d[2] - cloud[3 * (size_t)v + 2];
+            const double r = (dx * dx + dy * dy) + dz * dz;
+            if (r < best) { best = r; arg = v; }
+        }
+        out[i] = arg;
+    }
+}
+
 }  // namespace orc

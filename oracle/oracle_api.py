@@ -193,6 +193,20 @@ class GMM:
         return out, c
 
 
+def icp_nearest(cloud, model_part, visible, dptr, data, data_part, nthreads=1):
+    """findNN (invert = true) for B bodies: cloud (B, V, 3), model_part (V,), visible (B, V) uint8 or None, data points of body b at
+    dptr[b]:dptr[b+1].  Returns the matched model point per data point (-1: none)."""
+    cloud, data = _f64(cloud), _f64(data)
+    b, v = cloud.shape[0], cloud.shape[1]
+    model_part = np.ascontiguousarray(model_part, dtype=np.int32)
+    data_part = np.ascontiguousarray(data_part, dtype=np.int32)
+    dptr = np.ascontiguousarray(dptr, dtype=np.int64)
+    vis = None if visible is None else np.ascontiguousarray(visible, dtype=np.uint8)
+    out = np.full(data.shape[0], -2, dtype=np.int32)
+    lib().orc_icp_nearest(b, v, _p(cloud), _p(model_part), _p(vis), _p(dptr), _p(data), _p(data_part), _p(out), nthreads)
+    return out
+
+
 def quat_plus(x, d):
     """FakeQuaternionParameterization::Plus on n quaternions (x, y, z, w)."""
     x, d = _f64(x).reshape(-1, 4), _f64(d).reshape(-1, 3)

@@ -51,3 +51,23 @@ def test_icp_pose_only_has_no_shape_columns(synth, orc, model_np):
     b = om.icp_eval(x["w"], x["p"], x["q"], x["cptr"], x["mpt"], x["dpt"], x["dptr"], x["data"], shape=True)
     assert np.all(a["grad"][:, 75:] == 0.0) and np.allclose(a["grad"][:, :75], b["grad"][:, :75], rtol=0, atol=1e-12)
     assert np.any(b["grad"][:, 75:] != 0.0)
+
+
+def test_icp_nearest_oracle_matches_numpy(synth, orc, model_np):
+    """The oracle's findNN restatement (exhaustive search per part, visible points only) against numpy."""
+    rng = np.random.default_rng(2)
+    V = model_np["v_template"].shape[0]
+    fin = synth.make_forward_inputs(1, 12)
+    cloud = synth.forward_numpy(model_np, fin["w"][0], fin["p"][0], fin["r"][0])[0][None]
+    model_part = rng.integers(0, 5, V).astype(np.int32)
+    visible = (rng.random((1, V)) > 0.5).astype(np.uint8)
+    visible[0, model_part == 4] = 0
+    data = cloud[0][rng.integers(0, V, 300)] + rng.normal(0, 0.03, (300, 3))
+    data_part = rng.integers(0, 5, 300).astype(np.int32)
+    got = orc.icp_nearest(cloud, model_part, visible, [0, 300], data, data_part)
+    for i in range(300):
+        cand = np.nonzero((model_part == data_part[i]) & (visible[0] == 1))[0]
+        if len(cand) == 0:
+            assert got[i] == -1 and data_part[i] == 4
+        else:
+            assert got[i] == cand[np.argmin(((cloud[0][cand] - data[i]) ** 2).sum(axis=1))]

@@ -75,3 +75,67 @@ def test_icp_descent_step_lowers_cost(synth, orc, model_np, gpu_model):
     pred = np.sum(g * d, axis=1)
     assert np.all(new["cost"] < got["cost"])
     assert np.allclose(new["cost"] - got["cost"], pred, rtol=0.2)
+
+
+def _nn_case(synth, model_np, b, seed, nparts, nd):
+    """Posed clouds, part labels from the heaviest joint (modelPartLabels, AvatarOptimizer.cpp:1296-1300, with partMap = joint mod
+    nparts), a visibility mask, and data points labelled like the model point they were sampled near (a tenth mislabelled)."""
+    rng = np.random.default_rng(seed)
+    x = synth.make_icp_inputs(model_np, b, seed, ndata=nd)
+    V = model_np["v_template"].shape[0]
+    model_part = (np.argmax(model_np["weights"], axis=1) % nparts).astype(np.int32)
+    fin = synth.make_forward_inputs(b, seed + 7)
+    cloud = np.stack([synth.forward_numpy(model_np, fin["w"][i], x["p"][i], fin["r"][i])[0] for i in range(b)])
+    visible = (rng.random((b, V)) > 0.3).astype(np.uint8)
+    near = np.array([np.argmin(((cloud[i // nd][::7] - x["data"][i]) ** 2).sum(axis=1)) * 7 for i in range(b * nd)])
+    data_part = model_part[near].copy()
+    flip = rng.random(b * nd) < 0.1
+    data_part[flip] = rng.integers(0, nparts, int(flip.sum()))
+    return x, cloud, model_part, visible, data_part
+
+
+def test_icp_nearest_f64_indices_bit_exact(synth, orc, model_np, gpu_model):
+    api = pkg("api")
+    x, cloud, model_part, visible, data_part = _nn_case(synth, model_np, 3, 41, 6, 1500)
+    visible[1, model_part == 2] = 0                  # body 1: part 2 has no visible model point -> -1
+    ref = orc.icp_nearest(cloud, model_part, visible, x["dptr"], x["data"], data_part, nthreads=8)
+    got = api.icp_nearest(gpu_model, cloud, model_part, x["dptr"], x["data"], data_part, visible=visible)
+    assert np.array_equal(got, ref)
+    sel = slice(int(x["dptr"][1]), int(x["dptr"][2]))
+    assert np.all(got[sel][data_part[sel] == 2] == -1) and np.any(got >= 0)
+    # no visibility mask, one part: plain nearest neighbour over the whole cloud
+    one = np.zeros_like(model_part)
+    ref1 = orc.icp_nearest(cloud, one, None, x["dptr"], x["data"], np.zeros_like(data_part), nthreads=8)
+    got1 = api.icp_nearest(gpu_model, cloud, one, x["dptr"], x["data"], np.zeros_like(data_part))
+    assert np.array_equal(got1, ref1)
+    brute = np.array([np.argmin(((cloud[0] - d) ** 2).sum(axis=1)) for d in x["data"][:200]])
+    assert np.array_equal(got1[:200], brute)
+
+
+def test_icp_nearest_f32_and_chain_into_problem(synth, orc, model_np, gpu_model):
+    """float32 search: same indices as the oracle on the float-rounded inputs up to near-ties; its output feeds b3d_icp_create
+    directly (dpt = NULL, unmatched points skipped) and the evaluation equals the oracle's on the explicit pair list."""
+    api = pkg("api")
+    x, cloud, model_part, visible, data_part = _nn_case(synth, model_np, 2, 42, 4, 2500)
+    visible[0, model_part == 1] = 0                  # body 0: the data points of part 1 stay unmatched
+    c32, d32 = cloud.astype(np.float32), x["data"].astype(np.float32)
+    ref = orc.icp_nearest(c32.astype(np.float64), model_part, visible, x["dptr"], d32.astype(np.float64), data_part, nthreads=8)
+    got = api.icp_nearest(gpu_model, c32, model_part, x["dptr"], d32, data_part, visible=visible, dtype=np.float32)
+    diff = np.nonzero(got != ref)[0]
+    assert len(diff) <= 2e-3 * len(ref)
+    for i in diff:      # a different answer is a near-tie
+        bdy = int(np.searchsorted(x["dptr"], i, side="right") - 1)
+        da = np.sum((cloud[bdy][got[i]] - x["data"][i]) ** 2)
+        db = np.sum((cloud[bdy][ref[i]] - x["data"][i]) ** 2)
+        assert abs(da - db) < 1e-5 * max(da, db)
+    keep = got >= 0
+    assert keep.sum() < len(got)                      # some data points are unmatched (their part is invisible)
+    prob = api.IcpProblem(gpu_model, x["dptr"], got, None, x["dptr"], x["data"], dtype=np.float64)
+    out = prob.eval(x["w"], x["p"], x["q"])
+    idx = np.arange(len(got))
+    local = idx - x["dptr"][np.searchsorted(x["dptr"], idx, side="right") - 1]
+    cptr = np.concatenate([[0], np.cumsum([keep[x["dptr"][i]:x["dptr"][i + 1]].sum() for i in range(2)])])
+    om = orc.Model(model_np)
+    ref_eval = om.icp_eval(x["w"], x["p"], x["q"], cptr, got[keep], local[keep], x["dptr"], x["data"])
+    assert np.max(np.abs(out["cost"] - ref_eval["cost"]) / ref_eval["cost"]) < 1e-10
+    assert np.max(np.abs(out["grad"] - ref_eval["grad"])) < 1e-10 * np.max(np.abs(ref_eval["grad"]))
