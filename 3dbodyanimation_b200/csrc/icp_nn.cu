@@ -15,7 +15,7 @@
 
 namespace b3d {
 
-constexpr int NN_THREADS = 256, NN_PER_THREAD = 4;
+constexpr int NN_THREADS = 256, NN_PER_THREAD = 4;   // 1024 points per CTA: the local index fits the 12 low bits of `order`
 
 template <typename T> __device__ __forceinline__ T inf_();
 template <> __device__ __forceinline__ float inf_<float>() { return __int_as_float(0x7f800000); }
@@ -25,21 +25,65 @@ __device__ __forceinline__ float add_rn_(float a, float b) { return __fadd_rn(a,
 __device__ __forceinline__ double mul_rn_(double a, double b) { return __dmul_rn(a, b); }
 __device__ __forceinline__ double add_rn_(double a, double b) { return __dadd_rn(a, b); }
 
+// float64: the reference's own operation order, every operation rounded separately (indices bit-identical to the CPU search);
+// float32 (the fast path, no bit-exactness claimed against a float64 reference): fused
+__device__ __forceinline__ double dist2_(double dx, double dy, double dz) { return add_rn_(add_rn_(mul_rn_(dx, dx), mul_rn_(dy, dy)), mul_rn_(dz, dz)); }
+__device__ __forceinline__ float dist2_(float dx, float dy, float dz) { return fmaf(dz, dz, fmaf(dy, dy, dx * dx)); }
+
+template <typename T>
+__device__ __forceinline__ void nn_test(T px, T py, T pz, T mx, T my, T mz, int k, T& best, int& arg) {
+    const T dx = px - mx, dy = py - my, dz = pz - mz;
+    const T r = dist2_(dx, dy, dz);
+    if (r < best) { best = r; arg = k; }
+}
+
+// One work item: c <= 32 U points of one part (bucket-order positions pos0 ...), lane takes positions lane, lane + 32, ...
+template <typename T, int U>
+__device__ __forceinline__ void nn_item(const T* sx, const T* sy, const T* sz, const T* qx, const T* qy, const T* qz, const int32_t* order,
+                                        int k0, int k1, int pos0, int c, int lane, const int32_t* __restrict__ part_idx, int32_t* __restrict__ out) {
+    int li[U], arg[U];
+    T px[U], py[U], pz[U], best[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+        const bool ok = lane + 32 * u < c;
+        li[u] = ok ? (order[pos0 + lane + 32 * u] & 4095) : -1;
+        const int q = ok ? li[u] : 0;
+        px[u] = qx[q]; py[u] = qy[q]; pz[u] = qz[q];
+        best[u] = inf_<T>(); arg[u] = -1;
+    }
+    for (int k = k0; k < k1; ++k) {
+        const T mx = sx[k], my = sy[k], mz = sz[k];
+#pragma unroll
+        for (int u = 0; u < U; ++u) nn_test(px[u], py[u], pz[u], mx, my, mz, k, best[u], arg[u]);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+        if (li[u] >= 0) out[li[u]] = arg[u] >= 0 ? part_idx[arg[u]] : -1;
+}
+
+// CTA = up to NN_THREADS * NN_PER_THREAD data points of one body.  The points are bucketed by part in shared memory first, so that
+// a thread's NN_PER_THREAD points (adjacent in bucket order) and the lanes of a warp nearly always share a part: one broadcast
+// read of a model point then serves NN_PER_THREAD * 32 distance tests.
 template <typename T>
 __global__ void __launch_bounds__(NN_THREADS) icp_nearest_kernel(int V, int nparts, const int32_t* __restrict__ part_ptr,
                                                                  const int32_t* __restrict__ part_idx, const T* __restrict__ cloud,
                                                                  const uint8_t* __restrict__ visible, const int64_t* __restrict__ dptr,
                                                                  const T* __restrict__ data, const int32_t* __restrict__ data_part,
                                                                  int32_t* __restrict__ out) {
+    constexpr int NPTS = NN_THREADS * NN_PER_THREAD;
     extern __shared__ __align__(16) unsigned char nn_smem[];
     T* sx = reinterpret_cast<T*>(nn_smem);
     T* sy = sx + V;
     T* sz = sy + V;
-    int32_t* sp = reinterpret_cast<int32_t*>(sz + V);   // [nparts + 1]
+    T* qx = sz + V;                                       // the CTA's data points
+    T* qy = qx + NPTS;
+    T* qz = qy + NPTS;
+    int32_t* sp = reinterpret_cast<int32_t*>(qz + NPTS);  // [nparts + 1] slices of the part-ordered cloud
+    int32_t* cnt = sp + nparts + 1;                       // [nparts + 2] bucket cursors (bucket nparts = no valid part)
+    int32_t* order = cnt + nparts + 2;                    // [NPTS] (bucket << 12) | local index, in bucket order
     const int b = blockIdx.y;
     const int64_t d0 = dptr[b], nd = dptr[b + 1] - d0;
-    const int64_t first = (int64_t)blockIdx.x * NN_THREADS * NN_PER_THREAD;
-    if (first >= nd) return;
+    if ((int64_t)blockIdx.x * NPTS >= nd) return;
     const T* cb = cloud + 3 * (size_t)V * b;
     const T inf = inf_<T>();
     for (int k = threadIdx.x; k < V; k += NN_THREADS) {
@@ -50,23 +94,52 @@ __global__ void __launch_bounds__(NN_THREADS) icp_nearest_kernel(int V, int npar
         sz[k] = vis ? cb[3 * (size_t)v + 2] : inf;
     }
     for (int k = threadIdx.x; k <= nparts; k += NN_THREADS) sp[k] = part_ptr[k];
+    // the staged cloud serves every chunk of data points this CTA takes
+    for (int64_t first = (int64_t)blockIdx.x * NPTS; first < nd; first += (int64_t)gridDim.x * NPTS) {
+    const int n_here = (int)min((int64_t)NPTS, nd - first);
+    __syncthreads();   // the previous chunk's readers of cnt / order / q are done; the cloud is staged
+    for (int k = threadIdx.x; k < nparts + 2; k += NN_THREADS) cnt[k] = 0;
     __syncthreads();
+    int bucket[NN_PER_THREAD];
+#pragma unroll
     for (int u = 0; u < NN_PER_THREAD; ++u) {
-        const int64_t i = first + (int64_t)u * NN_THREADS + threadIdx.x;
-        if (i >= nd) break;
-        const T px = data[3 * (d0 + i)], py = data[3 * (d0 + i) + 1], pz = data[3 * (d0 + i) + 2];
-        const int part = data_part[d0 + i];
-        int arg = -1;
-        if (part >= 0 && part < nparts) {
-            T best = inf;
-            const int k1 = sp[part + 1];
-            for (int k = sp[part]; k < k1; ++k) {
-                const T dx = px - sx[k], dy = py - sy[k], dz = pz - sz[k];
-                const T r = add_rn_(add_rn_(mul_rn_(dx, dx), mul_rn_(dy, dy)), mul_rn_(dz, dz));
-                if (r < best) { best = r; arg = k; }
+        const int i = u * NN_THREADS + threadIdx.x;
+        bucket[u] = -1;
+        if (i < n_here) {
+            const int64_t g = d0 + first + i;
+            qx[i] = data[3 * g]; qy[i] = data[3 * g + 1]; qz[i] = data[3 * g + 2];
+            const int part = data_part[g];
+            bucket[u] = (part >= 0 && part < nparts) ? part : nparts;
+            atomicAdd(&cnt[bucket[u] + 1], 1);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0)
+        for (int k = 1; k < nparts + 2; ++k) cnt[k] += cnt[k - 1];   // cnt[k] = first position of bucket k
+    __syncthreads();
+#pragma unroll
+    for (int u = 0; u < NN_PER_THREAD; ++u)
+        if (bucket[u] >= 0) order[atomicAdd(&cnt[bucket[u]], 1)] = (bucket[u] << 12) | (u * NN_THREADS + threadIdx.x);
+    __syncthreads();
+    // After the scatter cnt[k] is the END of bucket k.  Work items = (bucket, block of up to 128 of its points), dealt to the warps
+    // round robin; the lanes of a warp take the item's points strided by 32, so a warp always works on ONE part: a model point
+    // is one broadcast read for up to 128 distance tests, and short buckets still fill all 32 lanes.
+    {
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+        int item = 0;
+        for (int k = 0; k < nparts; ++k) {
+            const int start = k ? cnt[k - 1] : 0, count = cnt[k] - start;
+            for (int o = 0; o < count; o += 32 * NN_PER_THREAD, ++item) {
+                if (item % (NN_THREADS / 32) != warp) continue;
+                const int c = min(32 * NN_PER_THREAD, count - o);
+                if (c > 64) nn_item<T, 4>(sx, sy, sz, qx, qy, qz, order, sp[k], sp[k + 1], start + o, c, lane, part_idx, out + d0 + first);
+                else if (c > 32) nn_item<T, 2>(sx, sy, sz, qx, qy, qz, order, sp[k], sp[k + 1], start + o, c, lane, part_idx, out + d0 + first);
+                else nn_item<T, 1>(sx, sy, sz, qx, qy, qz, order, sp[k], sp[k + 1], start + o, c, lane, part_idx, out + d0 + first);
             }
         }
-        out[d0 + i] = arg >= 0 ? part_idx[arg] : -1;
+        // data points without a valid part label
+        for (int pos = (nparts ? cnt[nparts - 1] : 0) + threadIdx.x; pos < n_here; pos += NN_THREADS) out[d0 + first + (order[pos] & 4095)] = -1;
+    }
     }
 }
 
@@ -130,8 +203,10 @@ extern "C" int b3d_icp_nearest(const b3d_model* m, int32_t B, int32_t dtype, con
     }
     int rc = B3D_OK;
     if (e == cudaSuccess) {
-        const size_t smem = es * 3 * (size_t)V + 4 * (size_t)(nparts + 1);
-        const dim3 grid((unsigned)((maxnd + NN_THREADS * NN_PER_THREAD - 1) / (NN_THREADS * NN_PER_THREAD)), B);
+        const size_t smem = es * 3 * ((size_t)V + NN_THREADS * NN_PER_THREAD) + 4 * (size_t)(2 * nparts + 3 + NN_THREADS * NN_PER_THREAD);
+        // one CTA per body when the batch fills the machine (the cloud is staged once), more chunks in flight when it does not
+        const int64_t chunks = (maxnd + NN_THREADS * NN_PER_THREAD - 1) / (NN_THREADS * NN_PER_THREAD);
+        const dim3 grid((unsigned)std::min<int64_t>(chunks, std::max(1, (2 * 148 + B - 1) / B)), B);
         if (smem > 232448) rc = set_error(B3D_EINVAL, "b3d_icp_nearest: model too large for the shared-memory cloud (%zu B)", smem);
         else if (dtype == B3D_F32) {
             e = cudaFuncSetAttribute(icp_nearest_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

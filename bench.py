@@ -484,6 +484,46 @@ def icp_leg(api, capi, lib, synth, model_np, dev, st, with_cpu, nb=4096, base=32
            "bound": "fp32 issue (22 algorithmic flop per target-record byte; B200 balance 11 flop/B); zero-weight slots are computed too (376 flop executed)", "achieved_tflops": vb * flop / 1e12,
            "fp32_peak_tflops": 148 * 128 * 2 * 1.965e-3, "frac_fp32": vb * flop / 1e12 / (148 * 128 * 2 * 1.965e-3),
            "achieved_gbs": vb * 16 / 1e9, "flop_per_vertex_body": flop}
+    # correspondence search (findNN, invert = true) for the first nbn bodies: resident posed clouds and data clouds, 16 parts
+    nbn, nparts = 1024, 16
+    rng = np.random.default_rng(9)
+    model_part = (np.argmax(np.asarray(model_np["weights"]), axis=1) % nparts).astype(np.int32)
+    r_np = np.tile(synth.quat_to_r(x["q"]), (nbn // base, 1, 1)).astype(np.float32)
+    w32, p32 = w[:nbn].float().contiguous(), p[:nbn].float().contiguous()
+    r32 = torch.from_numpy(np.ascontiguousarray(r_np)).to(dev)
+    ncloud = torch.empty(nbn, synth.V, 3, dtype=torch.float32, device=dev)
+    njp, njt = torch.empty(nbn, 24, 3, dtype=torch.float32, device=dev), torch.empty(nbn, 24, 12, dtype=torch.float32, device=dev)
+    capi.check(lib.b3d_smpl_forward_dev(gm.h, nbn, capi.F32, P(w32), P(p32), P(r32), P(ncloud), P(njp), P(njt), 0, C.c_void_p(st)), "icp clouds")
+    nd_per = ndata // base
+    ndata_dev = torch.from_numpy(np.tile(x["data"].astype(np.float32), (nbn // base, 1))).to(dev)
+    dpart_np = rng.integers(0, nparts, nbn * nd_per).astype(np.int32)
+    dpart = torch.from_numpy(dpart_np).to(dev)
+    nn_out = torch.empty(nbn * nd_per, dtype=torch.int32, device=dev)
+    ndptr = (np.arange(nbn + 1, dtype=np.int64) * nd_per)
+    torch.cuda.synchronize()
+    nn = lambda: capi.check(lib.b3d_icp_nearest(gm.h, nbn, capi.F32, P(ncloud), nparts, capi.ptr(model_part), None, capi.ptr(ndptr), P(ndata_dev),
+                                                P(dpart), 1, P(nn_out)), "b3d_icp_nearest")
+    nn()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        nn()                      # the call synchronises: wall clock brackets H2D of the part tables + the kernel
+    nn_ms = (time.perf_counter() - t0) / 3 * 1e3
+    pairs_tested = float(nbn) * nd_per * synth.V / nparts
+    out["nearest"] = {"kernel": "icp_nearest_kernel<float> (exhaustive per part; cloud staged in shared memory, data points bucketed by part, warp = one part)", "bodies": nbn,
+                      "data_points_per_body": nd_per, "parts": nparts, "ms_per_call": nn_ms, "value": nbn / (nn_ms * 1e-3), "unit": "searches/s",
+                      "distance_tests_per_sec": pairs_tested / (nn_ms * 1e-3)}
+    if with_cpu:
+        from oracle import oracle_api as orc
+        nsn = 8
+        hc = ncloud[:nsn].cpu().numpy().astype(np.float64)
+        hd = ndata_dev[:nsn * nd_per].cpu().numpy().astype(np.float64)
+        t0 = time.perf_counter()
+        ref_nn = orc.icp_nearest(hc, model_part, None, ndptr[:nsn + 1], hd, dpart_np[:nsn * nd_per], nthreads=host_threads())
+        dtn = time.perf_counter() - t0
+        same = float(np.mean(ref_nn == nn_out[:nsn * nd_per].cpu().numpy()))
+        out["nearest"]["cpu_baseline"] = {"value": nsn / dtn, "unit": "searches/s", "cores": host_threads(), "kind": "port",
+                                          "sample": f"{nsn} of the {nbn} bodies, oracle exhaustive search (the reference uses nanoflann kd-trees: "
+                                                    "same answer, fewer distance tests)", "fraction_identical_to_gpu_f32": same}
     if with_cpu:
         from oracle import oracle_api as orc
         om = orc.Model(model_np)
