@@ -489,3 +489,13 @@ def icp_nearest(model: AvatarModel, cloud, model_part, dptr, data, data_part, vi
     check(lib().b3d_icp_nearest(model.h, b, F64 if dt == np.float64 else F32, ptr(cloud), nparts, ptr(model_part), ptr(vis), ptr(dptr),
                                 ptr(data), ptr(data_part), 0, ptr(out)), "b3d_icp_nearest")
     return out
+
+
+def icp_visible(model: AvatarModel, cloud, dtype=np.float64):
+    """pointVisible of AvatarOptimizer's ICP loop (external/avatar/AvatarOptimizer.cpp:1337-1352): (B, V) bytes, 1 where the vertex
+    belongs to a face turned towards the camera in the posed cloud (B, V, 3).  The model needs its faces."""
+    dt = np.dtype(dtype)
+    cloud = np.ascontiguousarray(cloud, dtype=dt).reshape(-1, model.numPoints, 3)
+    vis = np.empty(cloud.shape[:2], dtype=np.uint8)
+    check(lib().b3d_icp_visible(model.h, cloud.shape[0], F64 if dt == np.float64 else F32, ptr(cloud), 0, ptr(vis)), "b3d_icp_visible")
+    return vis

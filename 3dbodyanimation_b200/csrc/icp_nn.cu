@@ -143,9 +143,61 @@ __global__ void __launch_bounds__(NN_THREADS) icp_nearest_kernel(int V, int npar
     }
 }
 
+// pointVisible of the ICP loop (AvatarOptimizer.cpp:1337-1352): a vertex is visible if it belongs to a face whose normal has
+// ((p2 - p1) x (p1 - p3)).z > 1e-4 in the posed cloud.  thread = (body, face); the three byte stores race benignly (all write 1).
+template <typename T>
+__global__ void __launch_bounds__(256) icp_visible_kernel(int B, int V, int F, const int32_t* __restrict__ faces, const T* __restrict__ cloud,
+                                                          uint8_t* __restrict__ visible) {
+    const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+    if (i >= (size_t)B * F) return;
+    const int b = (int)(i / F), f = (int)(i % F);
+    const int i1 = faces[3 * f], i2 = faces[3 * f + 1], i3 = faces[3 * f + 2];
+    const T* c = cloud + 3 * (size_t)V * b;
+    const T ax = c[3 * i2] - c[3 * i1], ay = c[3 * i2 + 1] - c[3 * i1 + 1];
+    const T bx = c[3 * i1] - c[3 * i3], by = c[3 * i1 + 1] - c[3 * i3 + 1];
+    const T z = add_rn_(mul_rn_(ax, by), -mul_rn_(ay, bx));   // Eigen's cross(): a.x * b.y - a.y * b.x, no contraction
+    if (z > (T)1e-4) {
+        uint8_t* vb = visible + (size_t)V * b;
+        vb[i1] = 1; vb[i2] = 1; vb[i3] = 1;
+    }
+}
+
 }  // namespace b3d
 
 using namespace b3d;
+
+extern "C" int b3d_icp_visible(const b3d_model* m, int32_t B, int32_t dtype, const void* cloud, int32_t flags, uint8_t* visible) {
+    if (!m || !cloud || !visible) return set_error(B3D_EINVAL, "b3d_icp_visible: null argument");
+    if (B <= 0) return set_error(B3D_EINVAL, "b3d_icp_visible: B <= 0");
+    if (dtype != B3D_F32 && dtype != B3D_F64) return set_error(B3D_EINVAL, "b3d_icp_visible: bad dtype %d", dtype);
+    if (!m->d_faces || m->F <= 0) return set_error(B3D_EINVAL, "b3d_icp_visible: the model was created without faces");
+    if (int rc = require_device()) return rc;
+    const bool dev = (flags & B3D_ICP_DEVICE_INPUT) != 0;
+    const size_t es = dtype == B3D_F32 ? 4 : 8, nc = es * 3 * (size_t)m->V * B, nv = (size_t)m->V * B;
+    char* buf = nullptr;
+    const void* pc = cloud;
+    uint8_t* pv = visible;
+    cudaError_t e = cudaSuccess;
+    if (!dev) {
+        e = cudaMalloc(&buf, nc + nv);
+        if (e == cudaSuccess) e = cudaMemcpy(buf, cloud, nc, cudaMemcpyHostToDevice);
+        pc = buf; pv = (uint8_t*)(buf + nc);
+    }
+    if (e == cudaSuccess) e = cudaMemsetAsync(pv, 0, nv, nullptr);
+    if (e == cudaSuccess) {
+        const unsigned grid = (unsigned)(((size_t)B * m->F + 255) / 256);
+        if (dtype == B3D_F32) icp_visible_kernel<float><<<grid, 256>>>(B, m->V, m->F, m->d_faces, (const float*)pc, pv);
+        else icp_visible_kernel<double><<<grid, 256>>>(B, m->V, m->F, m->d_faces, (const double*)pc, pv);
+        count_launch();
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(nullptr);
+    if (e == cudaSuccess && !dev) e = cudaMemcpy(visible, pv, nv, cudaMemcpyDeviceToHost);
+    cudaFree(buf);
+    if (e != cudaSuccess) return set_error(B3D_ECUDA, "b3d_icp_visible: %s", cudaGetErrorString(e));
+    return B3D_OK;
+}
+
 
 extern "C" int b3d_icp_nearest(const b3d_model* m, int32_t B, int32_t dtype, const void* cloud, int32_t nparts, const int32_t* model_part,
                                const uint8_t* visible, const int64_t* dptr, const void* data, const int32_t* data_part, int32_t flags,

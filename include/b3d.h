@@ -178,6 +178,10 @@ void b3d_icp_destroy(b3d_icp* h);
  * (pointVisible), data / data_part: the bodies' data points and their labels, body b at [dptr[b], dptr[b+1]) (dptr host).
  * nn_out has one entry per data point.  With B3D_ICP_DEVICE_INPUT cloud, visible, data, data_part and nn_out are device pointers.
  * The result is the pair list of b3d_icp_create: cptr = dptr, mpt = nn_out, dpt = NULL (pair e <-> data point e; mpt < 0 skipped). */
+/* pointVisible of the ICP loop (external/avatar/AvatarOptimizer.cpp:1337-1352, enableOcclusion): visible[b][v] = 1 if vertex v of
+ * body b belongs to a face with ((p2 - p1) x (p1 - p3)).z > 1e-4 in the posed cloud (B x V x 3), else 0.  The model must have
+ * been created with its faces.  With B3D_ICP_DEVICE_INPUT cloud and visible are device pointers. */
+int b3d_icp_visible(const b3d_model* m, int32_t B, int32_t dtype, const void* cloud, int32_t flags, uint8_t* visible);
 int b3d_icp_nearest(const b3d_model* m, int32_t B, int32_t dtype, const void* cloud, int32_t nparts, const int32_t* model_part,
                     const uint8_t* visible, const int64_t* dptr, const void* data, const int32_t* data_part, int32_t flags,
                     int32_t* nn_out);

@@ -277,6 +277,9 @@ void orc_icp_eval(void* mp, int B, const double* w, const double* p, const doubl
                  shape_enabled, resid ? resid + 3 * c0 : nullptr, jac ? jac + 3 * c0 * NC : nullptr, cost + b, grad + (size_t)b * NC);
     }
 }
+void orc_icp_visible(int B, int V, int F, const uint32_t* faces, const double* cloud, uint8_t* visible) {
+    for (int b = 0; b < B; ++b) icp_visible(V, F, faces, cloud + 3 * (size_t)V * b, visible + (size_t)V * b);
+}
 void orc_icp_nearest(int B, int V, const double* cloud, const int32_t* model_part, const uint8_t* visible, const int64_t* dptr,
                      const double* data, const int32_t* data_part, int32_t* out, int nthreads) {
 #pragma omp parallel for num_threads(nthreads > 0 ? nthreads : 1) schedule(dynamic, 1)

@@ -224,4 +224,16 @@ void icp_nearest(int V, const double* cloud, const int* model_part, const uint8_
     }
 }
 
+
+// pointVisible (AvatarOptimizer.cpp:1337-1352)
+void icp_visible(int V, int F, const uint32_t* faces, const double* cloud, uint8_t* visible) {
+    std::fill(visible, visible + V, (uint8_t)0);
+    for (int f = 0; f < F; ++f) {
+        const uint32_t i1 = faces[3 * f], i2 = faces[3 * f + 1], i3 = faces[3 * f + 2];
+        const double* p1 = cloud + 3 * (size_t)i1; const double* p2 = cloud + 3 * (size_t)i2; const double* p3 = cloud + 3 * (size_t)i3;
+        const double ax = p2[0] - p1[0], ay = p2[1] - p1[1], bx = p1[0] - p3[0], by = p1[1] - p3[1];
+        if (ax * by - ay * bx > 1e-4) visible[i1] = visible[i2] = visible[i3] = 1;
+    }
+}
+
 }  // namespace orc

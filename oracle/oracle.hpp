@@ -221,6 +221,7 @@ void icp_eval(const Model& M, const double* w, const double* p, const double* q,
               const double* data, int shape_enabled, double* resid, double* jac, double* cost, double* grad);
 void quat_plus(const double* x, const double* delta, double* out);   // FakeQuaternionParameterization::Plus
 // findNN with invert = true (AvatarOptimizer.cpp:841-907): out[i] = nearest visible model point of data point i's part, or -1
+void icp_visible(int V, int F, const uint32_t* faces, const double* cloud, uint8_t* visible);   // pointVisible (:1337-1352)
 void icp_nearest(int V, const double* cloud, const int* model_part, const uint8_t* visible, int nd, const double* data,
                  const int* data_part, int* out);
 

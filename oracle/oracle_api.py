@@ -193,6 +193,15 @@ class GMM:
         return out, c
 
 
+def icp_visible(cloud, faces):
+    """pointVisible of AvatarOptimizer's ICP loop for B posed clouds (B, V, 3); faces (F, 3)."""
+    cloud = _f64(cloud)
+    faces = np.ascontiguousarray(faces, dtype=np.uint32)
+    vis = np.zeros(cloud.shape[:2], dtype=np.uint8)
+    lib().orc_icp_visible(cloud.shape[0], cloud.shape[1], faces.shape[0], _p(faces), _p(cloud), _p(vis))
+    return vis
+
+
 def icp_nearest(cloud, model_part, visible, dptr, data, data_part, nthreads=1):
     """findNN (invert = true) for B bodies: cloud (B, V, 3), model_part (V,), visible (B, V) uint8 or None, data points of body b at
     dptr[b]:dptr[b+1].  Returns the matched model point per data point (-1: none)."""

@@ -139,3 +139,29 @@ def test_icp_nearest_f32_and_chain_into_problem(synth, orc, model_np, gpu_model)
     ref_eval = om.icp_eval(x["w"], x["p"], x["q"], cptr, got[keep], local[keep], x["dptr"], x["data"])
     assert np.max(np.abs(out["cost"] - ref_eval["cost"]) / ref_eval["cost"]) < 1e-10
     assert np.max(np.abs(out["grad"] - ref_eval["grad"])) < 1e-10 * np.max(np.abs(ref_eval["grad"]))
+
+
+def test_icp_visible_bit_exact_and_feeds_the_search(synth, orc):
+    """pointVisible (AvatarOptimizer.cpp:1337-1352) on the smooth render model (it has faces): float64 mask bit-identical to the
+    oracle's; the mask then restricts the correspondence search exactly as on the CPU."""
+    api = pkg("api")
+    rm = synth.make_render_model()
+    gm = api.AvatarModel(rm)
+    fin = synth.make_forward_inputs(4, 51)
+    cloud, _, _ = api.smpl_forward(gm, fin["w"], fin["p"], fin["r"], dtype=np.float64)
+    vis = api.icp_visible(gm, cloud)
+    ref = orc.icp_visible(cloud, rm["f"])
+    assert np.array_equal(vis, ref)
+    assert vis.min() == 0 and vis.max() == 1   # both outcomes occur (the synthetic mesh is not consistently oriented: most vertices pass)
+    rng = np.random.default_rng(3)
+    V = cloud.shape[1]
+    model_part = (np.argmax(rm["weights"], axis=1) % 5).astype(np.int32)
+    nd = 800
+    src = rng.integers(0, V, (4, nd))
+    data = (cloud[np.arange(4)[:, None], src] + rng.normal(0, 0.02, (4, nd, 3))).reshape(-1, 3)
+    data_part = model_part[src].reshape(-1)
+    dptr = np.arange(5) * nd
+    got = api.icp_nearest(gm, cloud, model_part, dptr, data, data_part, visible=vis)
+    want = orc.icp_nearest(cloud, model_part, ref, dptr, data, data_part, nthreads=4)
+    assert np.array_equal(got, want)
+    assert np.all(vis.reshape(-1)[(np.repeat(np.arange(4), nd) * V + got)[got >= 0]] == 1)
