@@ -165,3 +165,24 @@ def test_icp_visible_bit_exact_and_feeds_the_search(synth, orc):
     want = orc.icp_nearest(cloud, model_part, ref, dptr, data, data_part, nthreads=4)
     assert np.array_equal(got, want)
     assert np.all(vis.reshape(-1)[(np.repeat(np.arange(4), nd) * V + got)[got >= 0]] == 1)
+
+
+def test_icp_large_batch_single_split(synth, orc, model_np, gpu_model):
+    """4,736 bodies = 148 body groups: the launch takes one CTA per group over the whole vertex range (no vertex split), and the
+    last tile of the sorted vertex order is partial.  The batch tiles 32 distinct bodies; every copy must reproduce the oracle."""
+    api = pkg("api")
+    base, reps = 32, 148
+    x = synth.make_icp_inputs(model_np, base, 36, ndata=1500)
+    om = orc.Model(model_np)
+    ref = om.icp_eval(x["w"], x["p"], x["q"], x["cptr"], x["mpt"], x["dpt"], x["dptr"], x["data"], nthreads=8)
+    npair, ndata = int(x["cptr"][-1]), int(x["dptr"][-1])
+    cptr = np.concatenate([x["cptr"][:-1] + r * npair for r in range(reps)] + [[reps * npair]])
+    dptr = np.concatenate([x["dptr"][:-1] + r * ndata for r in range(reps)] + [[reps * ndata]])
+    prob = api.IcpProblem(gpu_model, cptr, np.tile(x["mpt"], reps), np.tile(x["dpt"], reps), dptr, np.tile(x["data"], (reps, 1)), dtype=np.float32)
+    t = lambda a: np.tile(a, (reps,) + (1,) * (a.ndim - 1))
+    got = prob.eval(t(x["w"]), t(x["p"]), t(x["q"]))
+    cost = got["cost"].reshape(reps, base)
+    grad = got["grad"].reshape(reps, base, 85)
+    scale = np.max(np.abs(ref["grad"]), axis=1, keepdims=True)
+    assert np.max(np.abs(cost - ref["cost"]) / ref["cost"]) < 1e-5
+    assert np.max(np.abs(grad - ref["grad"]) / scale) < 2e-4
