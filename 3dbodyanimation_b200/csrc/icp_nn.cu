@@ -15,7 +15,9 @@
 
 namespace b3d {
 
-constexpr int NN_THREADS = 256, NN_PER_THREAD = 4;   // 1024 points per CTA: the local index fits the 12 low bits of `order`
+constexpr int NN_THREADS = 256, NN_PER_THREAD = 4;   // a work item: up to 32 * NN_PER_THREAD points of one part
+constexpr int NN_LOAD = 8;                           // 2048 points per CTA chunk (the local index fits the 12 low bits of `order`):
+                                                     // larger chunks give fuller per-part buckets
 
 template <typename T> __device__ __forceinline__ T inf_();
 template <> __device__ __forceinline__ float inf_<float>() { return __int_as_float(0x7f800000); }
@@ -61,7 +63,7 @@ __device__ __forceinline__ void nn_item(const T* sx, const T* sy, const T* sz, c
         if (li[u] >= 0) out[li[u]] = arg[u] >= 0 ? part_idx[arg[u]] : -1;
 }
 
-// CTA = up to NN_THREADS * NN_PER_THREAD data points of one body.  The points are bucketed by part in shared memory first, so that
+// CTA = chunks of up to NN_THREADS * NN_LOAD data points of one body.  The points are bucketed by part in shared memory first, so that
 // a thread's NN_PER_THREAD points (adjacent in bucket order) and the lanes of a warp nearly always share a part: one broadcast
 // read of a model point then serves NN_PER_THREAD * 32 distance tests.
 template <typename T>
@@ -70,7 +72,7 @@ __global__ void __launch_bounds__(NN_THREADS) icp_nearest_kernel(int V, int npar
                                                                  const uint8_t* __restrict__ visible, const int64_t* __restrict__ dptr,
                                                                  const T* __restrict__ data, const int32_t* __restrict__ data_part,
                                                                  int32_t* __restrict__ out) {
-    constexpr int NPTS = NN_THREADS * NN_PER_THREAD;
+    constexpr int NPTS = NN_THREADS * NN_LOAD;
     extern __shared__ __align__(16) unsigned char nn_smem[];
     T* sx = reinterpret_cast<T*>(nn_smem);
     T* sy = sx + V;
@@ -100,9 +102,9 @@ __global__ void __launch_bounds__(NN_THREADS) icp_nearest_kernel(int V, int npar
     __syncthreads();   // the previous chunk's readers of cnt / order / q are done; the cloud is staged
     for (int k = threadIdx.x; k < nparts + 2; k += NN_THREADS) cnt[k] = 0;
     __syncthreads();
-    int bucket[NN_PER_THREAD];
+    int bucket[NN_LOAD];
 #pragma unroll
-    for (int u = 0; u < NN_PER_THREAD; ++u) {
+    for (int u = 0; u < NN_LOAD; ++u) {
         const int i = u * NN_THREADS + threadIdx.x;
         bucket[u] = -1;
         if (i < n_here) {
@@ -118,7 +120,7 @@ __global__ void __launch_bounds__(NN_THREADS) icp_nearest_kernel(int V, int npar
         for (int k = 1; k < nparts + 2; ++k) cnt[k] += cnt[k - 1];   // cnt[k] = first position of bucket k
     __syncthreads();
 #pragma unroll
-    for (int u = 0; u < NN_PER_THREAD; ++u)
+    for (int u = 0; u < NN_LOAD; ++u)
         if (bucket[u] >= 0) order[atomicAdd(&cnt[bucket[u]], 1)] = (bucket[u] << 12) | (u * NN_THREADS + threadIdx.x);
     __syncthreads();
     // After the scatter cnt[k] is the END of bucket k.  Work items = (bucket, block of up to 128 of its points), dealt to the warps
@@ -255,9 +257,9 @@ extern "C" int b3d_icp_nearest(const b3d_model* m, int32_t B, int32_t dtype, con
     }
     int rc = B3D_OK;
     if (e == cudaSuccess) {
-        const size_t smem = es * 3 * ((size_t)V + NN_THREADS * NN_PER_THREAD) + 4 * (size_t)(2 * nparts + 3 + NN_THREADS * NN_PER_THREAD);
+        const size_t smem = es * 3 * ((size_t)V + NN_THREADS * NN_LOAD) + 4 * (size_t)(2 * nparts + 3 + NN_THREADS * NN_LOAD);
         // one CTA per body when the batch fills the machine (the cloud is staged once), more chunks in flight when it does not
-        const int64_t chunks = (maxnd + NN_THREADS * NN_PER_THREAD - 1) / (NN_THREADS * NN_PER_THREAD);
+        const int64_t chunks = (maxnd + NN_THREADS * NN_LOAD - 1) / (NN_THREADS * NN_LOAD);
         const dim3 grid((unsigned)std::min<int64_t>(chunks, std::max(1, (2 * 148 + B - 1) / B)), B);
         if (smem > 232448) rc = set_error(B3D_EINVAL, "b3d_icp_nearest: model too large for the shared-memory cloud (%zu B)", smem);
         else if (dtype == B3D_F32) {
