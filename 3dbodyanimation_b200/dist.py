@@ -37,6 +37,17 @@ def shard_frames(n: int, world: int, rank: int) -> tuple[int, int]:
     return f0, f0 + per + (1 if rank < rem else 0)
 
 
+def shard_icp(cptr, dptr, world: int, rank: int):
+    """Bodies of an ICP batch are independent (api.IcpProblem / api.icp_nearest): rank `rank` takes the contiguous body range of
+    shard_frames and the matching slices of the pair and data arrays.  Returns (b0, b1, cptr_local, dptr_local, pair_slice,
+    data_slice) with the local offsets rebased to 0; no collective is involved, results concatenate in rank order."""
+    import numpy as np
+    cptr, dptr = np.asarray(cptr, dtype=np.int64), np.asarray(dptr, dtype=np.int64)
+    b0, b1 = shard_frames(len(cptr) - 1, world, rank)
+    return (b0, b1, cptr[b0:b1 + 1] - cptr[b0], dptr[b0:b1 + 1] - dptr[b0], slice(int(cptr[b0]), int(cptr[b1])),
+            slice(int(dptr[b0]), int(dptr[b1])))
+
+
 def shard_sequences(nseq: int, world: int, rank: int) -> list[int]:
     """Independent sequences round-robin over ranks (SURVEY §8(e) last row)."""
     return list(range(rank, nseq, world))

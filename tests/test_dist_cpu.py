@@ -54,6 +54,29 @@ def test_shard_frames_and_sequences():
     assert sorted(sum((D.shard_sequences(50, 8, r) for r in range(8)), [])) == list(range(50))
 
 
+def test_shard_icp_partitions_bodies_pairs_and_data():
+    """ICP batches shard by body with no exchange: the ranks' slices tile the pair / data arrays, and evaluating the oracle on
+    every shard reproduces the unsharded cost and gradient bit for bit."""
+    import importlib
+    from oracle import oracle_api as orc
+    dist_mod = importlib.import_module("3dbodyanimation_b200.dist")
+    synth = importlib.import_module("3dbodyanimation_b200.synth")
+    model_np = synth.make_model()
+    x = synth.make_icp_inputs(model_np, 5, 61, ndata=200)
+    om = orc.Model(model_np)
+    full = om.icp_eval(x["w"], x["p"], x["q"], x["cptr"], x["mpt"], x["dpt"], x["dptr"], x["data"])
+    for world in (2, 3):
+        cost, grad, pairs, pts = [], [], 0, 0
+        for rank in range(world):
+            b0, b1, cl, dl, ps, ds = dist_mod.shard_icp(x["cptr"], x["dptr"], world, rank)
+            assert cl[0] == 0 and dl[0] == 0 and ps.start == pairs and ds.start == pts
+            pairs, pts = ps.stop, ds.stop
+            part = om.icp_eval(x["w"][b0:b1], x["p"][b0:b1], x["q"][b0:b1], cl, x["mpt"][ps], x["dpt"][ps], dl, x["data"][ds])
+            cost.append(part["cost"]); grad.append(part["grad"])
+        assert pairs == x["cptr"][-1] and pts == x["dptr"][-1]
+        assert np.array_equal(np.concatenate(cost), full["cost"]) and np.array_equal(np.concatenate(grad), full["grad"])
+
+
 def test_window_plan_matches_reference_schedule():
     # src/main_multi_frame.cpp:109-112, 165-166 with the README values: 2,000 frames -> 200 anchors, 134 windows; 100k -> 10,000 / 6,667
     p = D.WindowPlan(2000, 20, 5, 10, 1)
