@@ -469,6 +469,15 @@ class IcpProblem:
         check(lib().b3d_icp_eval(self.h, ptr(w), ptr(p), ptr(q), 0 if shape else 2, ptr(cost), ptr(grad)), "b3d_icp_eval")
         return dict(cost=cost, grad=grad)
 
+    def eval_full(self, w, p, q, gmm=None, beta_pose=0.0, beta_shape=0.0, shape=True):
+        """The whole objective of one ICP iteration of AvatarOptimizer::optimize (:1386-1428): ICP term + pose prior (betaPose,
+        GMM) + shape prior (betaShape), the prior weights scaled by sqrt(#residual blocks) / 15."""
+        w, p, q = _f64(w).reshape(self.B, NS), _f64(p).reshape(self.B, 3), _f64(q).reshape(self.B, NJ, 4)
+        cost, grad = np.empty(self.B), np.empty((self.B, 85))
+        check(lib().b3d_icp_eval_full(self.h, _gmm_handle(gmm), C.c_double(beta_pose), C.c_double(beta_shape), ptr(w), ptr(p), ptr(q),
+                                      0 if shape else 2, ptr(cost), ptr(grad)), "b3d_icp_eval_full")
+        return dict(cost=cost, grad=grad)
+
 
 def icp_nearest(model: AvatarModel, cloud, model_part, dptr, data, data_part, visible=None, dtype=np.float64):
     """findNN with invert = true (external/avatar/AvatarOptimizer.cpp:841-907): for every data point the nearest visible model point

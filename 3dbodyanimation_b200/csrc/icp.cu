@@ -39,7 +39,7 @@ struct b3d_icp {
     void* tgt = nullptr;        // [groups][V][32] x (mean xyz, n) of T
     int32_t *vertex_of_pos = nullptr, *pos_of_vertex = nullptr;   // processing order: vertices sorted by their joint tuple
     void* rec = nullptr;        // [V + CH][IcpRec::WORDS] of T: per-vertex model records (icp_records_kernel)
-    double* scatter = nullptr;  // [B] sum |d - mean|^2
+    double* scatter = nullptr;  // [B] sum |d - mean|^2, then [B] number of residual blocks (matched pairs) per body
     double* acc = nullptr;      // [B][ICP_ACC]
     double* state = nullptr;    // device copies for the host-pointer call: w | p | q | cost | grad
     double *r = nullptr, *jp = nullptr, *jt = nullptr;
@@ -104,8 +104,9 @@ __global__ void __launch_bounds__(256) icp_scatter_kernel(int B, int V, const in
     for (int64_t e0 = blockIdx.x * (int64_t)blockDim.x; e0 < n; e0 += span) {
         const int64_t e = e0 + threadIdx.x;
         int b = -1;
-        double s = 0.0;
+        double s = 0.0, one = 0.0;
         if (e < n && mpt[e] >= 0) {
+            one = 1.0;
             b = body_of_pair(cptr, B, e);
             const T* d = data + 3 * (dptr[b] + (dpt ? (int64_t)dpt[e] : e - cptr[b]));
             const double* mu = tmp + 4 * ((size_t)b * V + mpt[e]);   // float64 mean (icp_targets_kernel)
@@ -116,10 +117,11 @@ __global__ void __launch_bounds__(256) icp_scatter_kernel(int B, int V, const in
         const int b0 = __shfl_sync(0xffffffffu, b, 0);
         if (__all_sync(0xffffffffu, b == b0)) {
 #pragma unroll
-            for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-            if ((threadIdx.x & 31) == 0 && b0 >= 0) atomicAdd(scatter + b0, s);
+            for (int o = 16; o; o >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, o); one += __shfl_xor_sync(0xffffffffu, one, o); }
+            if ((threadIdx.x & 31) == 0 && b0 >= 0) { atomicAdd(scatter + b0, s); atomicAdd(scatter + B + b0, one); }
         } else if (b >= 0) {
             atomicAdd(scatter + b, s);
+            atomicAdd(scatter + B + b, 1.0);
         }
     }
 }
@@ -480,6 +482,74 @@ __global__ void __launch_bounds__(128) icp_finish_kernel(const SkeletonConst* __
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Prior blocks of AvatarOptimizer::optimize, added to cost / grad of the data term: AvatarPosePriorCostFunctor (:644-700; GMM
+// residual of the 23 joint angle-axes times scaledBetaPose, Jacobian L.middleRows<3>(3 i)^T * 0.707106781186548 * scaledBetaPose)
+// and AvatarShapePriorCostFunctor (:703-726; w * scaledBetaShape), with scaledBeta = beta * sqrt(#residual blocks) / 15
+// (:1412-1414).  CTA = body.
+// ---------------------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) icp_prior_kernel(int B, int nc, const double* __restrict__ mean, const double* __restrict__ L,
+                                                        const double* __restrict__ consts, double beta_pose, double beta_shape,
+                                                        const double* __restrict__ totals, const double* __restrict__ w,
+                                                        const double* __restrict__ q, double* __restrict__ cost, double* __restrict__ grad) {
+    __shared__ double s_x[NPRI], s_h[16][NPRI], s_p[16], s_cost[4];
+    const int b = blockIdx.x, tid = threadIdx.x;
+    const double root = sqrt(totals[b]) / 15.0, sbp = beta_pose * root, sbs = beta_shape * root;
+    double add = 0.0;
+    if (nc > 0 && beta_pose > 0.0) {
+        if (tid < NJ - 1) {   // Eigen::AngleAxisd(q_j): axis * angle
+            const double* qq = q + ((size_t)b * NJ + tid + 1) * 4;
+            double n = sqrt(qq[0] * qq[0] + qq[1] * qq[1] + qq[2] * qq[2]);
+            double ax = 0.0, ay = 0.0, az = 0.0;
+            if (n != 0.0) {
+                const double angle = 2.0 * atan2(n, fabs(qq[3]));
+                if (qq[3] < 0.0) n = -n;
+                ax = qq[0] / n * angle; ay = qq[1] / n * angle; az = qq[2] / n * angle;
+            }
+            s_x[3 * tid] = ax; s_x[3 * tid + 1] = ay; s_x[3 * tid + 2] = az;
+        }
+        __syncthreads();
+        const double rh = sqrt(0.5);
+        for (int t = tid; t < nc * NPRI; t += 128) {   // GaussianMixture::residual (GaussianMixture.cpp:94-113)
+            const int i = t / NPRI, k = t % NPRI;
+            const double* Li = L + (size_t)i * NPRI * NPRI;
+            double acc = 0.0;
+            for (int m = k; m < NPRI; ++m) acc += Li[m * NPRI + k] * (s_x[m] - mean[i * NPRI + m]);
+            s_h[i][k] = acc * rh;
+        }
+        __syncthreads();
+        if (tid < nc) {
+            double sq = 0.0;
+            for (int k = 0; k < NPRI; ++k) sq += s_h[tid][k] * s_h[tid][k];
+            s_p[tid] = sq - consts[tid];
+        }
+        __syncthreads();
+        int c = 0;
+        double best = 1.7976931348623157e308;
+        for (int i = 0; i < nc; ++i) if (s_p[i] < best) { best = s_p[i]; c = i; }
+        // cost: 1/2 |sbp * [h; sqrt(-const)]|^2 ; gradient entry (joint i + 1, a) = 0.7071... sbp^2 * L[3 i + a][.] . h
+        if (tid < NPRI) {
+            const double r = s_h[c][tid] * sbp;
+            add = 0.5 * r * r;
+            const double* Lr = L + (size_t)c * NPRI * NPRI + (size_t)tid * NPRI;
+            double acc = 0.0;
+            for (int k = 0; k <= tid; ++k) acc += Lr[k] * 0.707106781186548 * sbp * (s_h[c][k] * sbp);
+            grad[(size_t)b * ICP_NC + 6 + tid] += acc;   // 3 + 3 (i + 1) + a with tid = 3 i + a
+        }
+        if (tid == NPRI) { const double r = sqrt(-consts[c]) * sbp; add = 0.5 * r * r; }
+    }
+    if (beta_shape > 0.0 && tid >= 96 && tid < 96 + NS) {
+        const double rs = w[(size_t)b * NS + tid - 96] * sbs;
+        add += 0.5 * rs * rs;
+        grad[(size_t)b * ICP_NC + 3 + 3 * NJ + tid - 96] += sbs * rs;
+    }
+#pragma unroll
+    for (int o = 16; o; o >>= 1) add += __shfl_xor_sync(0xffffffffu, add, o);
+    if ((tid & 31) == 0) s_cost[tid >> 5] = add;
+    __syncthreads();
+    if (tid == 0) cost[b] += (s_cost[0] + s_cost[1]) + (s_cost[2] + s_cost[3]);
+}
+
 // The sums over vertices do not depend on the order, so the vertices are processed sorted by their tuple of assigned joints:
 // a weight slot then keeps its joint over long runs and the accumulate kernel keeps that joint's transform and partial sums in
 // registers (SMPL: a few hundred distinct tuples for 6890 vertices).
@@ -517,7 +587,7 @@ static int icp_reduce(b3d_icp* h, const int64_t* d_cptr, const int64_t* d_dptr, 
     B3D_CUDA(cudaMalloc(&tmp, tmp_bytes));
     cudaError_t e = cudaMemsetAsync(tmp, 0, tmp_bytes, nullptr);
     if (e == cudaSuccess) e = cudaMemsetAsync(h->tgt, 0, tgt_bytes, nullptr);
-    if (e == cudaSuccess) e = cudaMemsetAsync(h->scatter, 0, sizeof(double) * B, nullptr);
+    if (e == cudaSuccess) e = cudaMemsetAsync(h->scatter, 0, sizeof(double) * 2 * B, nullptr);
     if (e != cudaSuccess) { cudaFree(tmp); return set_error(B3D_ECUDA, "b3d_icp_create: %s", cudaGetErrorString(e)); }
     const int pair_blocks = (int)std::min<int64_t>(std::max<int64_t>((h->npairs + 255) / 256, 1), 148 * 16);
     icp_gather_kernel<T><<<pair_blocks, 256>>>(B, V, d_cptr, d_dptr, d_mpt, d_dpt, d_data, tmp);
@@ -596,7 +666,7 @@ int b3d_icp_create(const b3d_model* m, int32_t B, int32_t dtype, const int64_t* 
     int32_t *d_mpt = nullptr, *d_dpt = nullptr;
     void* d_data = nullptr;
     cudaError_t e = cudaMalloc(&h->tgt, es * 128 * ((size_t)h->groups * m->V + 8));   // + one tile: a partial last tile reads past V
-    if (e == cudaSuccess) e = cudaMalloc(&h->scatter, sizeof(double) * B);
+    if (e == cudaSuccess) e = cudaMalloc(&h->scatter, sizeof(double) * 2 * B);
     if (e == cudaSuccess) e = cudaMalloc(&h->acc, sizeof(double) * (size_t)B * ICP_ACC);
     if (e == cudaSuccess) e = cudaMalloc(&h->state, sizeof(double) * (size_t)B * (NS + 3 + 4 * NJ + 1 + ICP_NC));
     if (e == cudaSuccess) e = cudaMalloc(&h->r, sizeof(double) * (size_t)B * NJ * 9);
@@ -671,6 +741,34 @@ int b3d_icp_eval(b3d_icp* h, const double* w, const double* p, const double* q, 
     B3D_CUDA(cudaMemcpy(dp, p, sizeof(double) * B * 3, cudaMemcpyHostToDevice));
     B3D_CUDA(cudaMemcpy(dq, q, sizeof(double) * B * 4 * NJ, cudaMemcpyHostToDevice));
     if (int rc = b3d_icp_eval_dev(h, dw, dp, dq, flags, dc, dg, nullptr)) return rc;
+    B3D_CUDA(cudaStreamSynchronize(nullptr));
+    B3D_CUDA(cudaMemcpy(cost, dc, sizeof(double) * B, cudaMemcpyDeviceToHost));
+    B3D_CUDA(cudaMemcpy(grad, dg, sizeof(double) * B * ICP_NC, cudaMemcpyDeviceToHost));
+    return B3D_OK;
+}
+
+int b3d_icp_add_priors_dev(b3d_icp* h, const b3d_gmm* gmm, double beta_pose, double beta_shape, const double* w, const double* q,
+                           double* cost, double* grad, void* stream) {
+    if (!h || !w || !q || !cost || !grad) return set_error(B3D_EINVAL, "b3d_icp_add_priors: null argument");
+    if (beta_pose > 0.0 && !gmm) return set_error(B3D_EINVAL, "b3d_icp_add_priors: beta_pose > 0 needs the pose prior");
+    if (!(beta_pose > 0.0) && !(beta_shape > 0.0)) return B3D_OK;
+    const bool pose = beta_pose > 0.0 && gmm->nComps > 0;   // a missing prior (nComps = -1) contributes nothing
+    icp_prior_kernel<<<h->B, 128, 0, (cudaStream_t)stream>>>(h->B, pose ? gmm->nComps : 0, pose ? gmm->d_mean : nullptr, pose ? gmm->d_prec_cho : nullptr,
+                                                             pose ? gmm->d_consts : nullptr, beta_pose, beta_shape, h->scatter + h->B, w, q, cost, grad);
+    B3D_LAUNCH_CHECK();
+    return B3D_OK;
+}
+
+int b3d_icp_eval_full(b3d_icp* h, const b3d_gmm* gmm, double beta_pose, double beta_shape, const double* w, const double* p, const double* q,
+                      int32_t flags, double* cost, double* grad) {
+    if (!h || !w || !p || !q || !cost || !grad) return set_error(B3D_EINVAL, "b3d_icp_eval_full: null argument");
+    const size_t B = (size_t)h->B;
+    double *dw = h->state, *dp = dw + B * NS, *dq = dp + B * 3, *dc = dq + B * 4 * NJ, *dg = dc + B;
+    B3D_CUDA(cudaMemcpy(dw, w, sizeof(double) * B * NS, cudaMemcpyHostToDevice));
+    B3D_CUDA(cudaMemcpy(dp, p, sizeof(double) * B * 3, cudaMemcpyHostToDevice));
+    B3D_CUDA(cudaMemcpy(dq, q, sizeof(double) * B * 4 * NJ, cudaMemcpyHostToDevice));
+    if (int rc = b3d_icp_eval_dev(h, dw, dp, dq, flags, dc, dg, nullptr)) return rc;
+    if (int rc = b3d_icp_add_priors_dev(h, gmm, beta_pose, beta_shape, dw, dq, dc, dg, nullptr)) return rc;
     B3D_CUDA(cudaStreamSynchronize(nullptr));
     B3D_CUDA(cudaMemcpy(cost, dc, sizeof(double) * B, cudaMemcpyDeviceToHost));
     B3D_CUDA(cudaMemcpy(grad, dg, sizeof(double) * B * ICP_NC, cudaMemcpyDeviceToHost));

@@ -178,6 +178,15 @@ void b3d_icp_destroy(b3d_icp* h);
  * (pointVisible), data / data_part: the bodies' data points and their labels, body b at [dptr[b], dptr[b+1]) (dptr host).
  * nn_out has one entry per data point.  With B3D_ICP_DEVICE_INPUT cloud, visible, data, data_part and nn_out are device pointers.
  * The result is the pair list of b3d_icp_create: cptr = dptr, mpt = nn_out, dpt = NULL (pair e <-> data point e; mpt < 0 skipped). */
+/* The prior blocks AvatarOptimizer::optimize adds to the ICP term (external/avatar/AvatarOptimizer.cpp:1412-1428):
+ * AvatarPosePriorCostFunctor (:644-700, GMM pose prior on the 23 joint rotations) and AvatarShapePriorCostFunctor (:703-726), their
+ * weights scaled by sqrt(number of ICP residual blocks of the body) / 15.  b3d_icp_add_priors_dev ADDS their cost and gradient to
+ * cost / grad (device pointers, as left by b3d_icp_eval_dev on the same stream); b3d_icp_eval_full is the whole objective with host
+ * pointers (data term + priors).  beta <= 0 switches a block off like the reference's `if (beta > 0.)`; gmm may be NULL only then. */
+int b3d_icp_add_priors_dev(b3d_icp* h, const b3d_gmm* gmm, double beta_pose, double beta_shape, const double* w, const double* q,
+                           double* cost, double* grad, void* stream);
+int b3d_icp_eval_full(b3d_icp* h, const b3d_gmm* gmm, double beta_pose, double beta_shape, const double* w, const double* p,
+                      const double* q, int32_t flags, double* cost, double* grad);
 /* pointVisible of the ICP loop (external/avatar/AvatarOptimizer.cpp:1337-1352, enableOcclusion): visible[b][v] = 1 if vertex v of
  * body b belongs to a face with ((p2 - p1) x (p1 - p3)).z > 1e-4 in the posed cloud (B x V x 3), else 0.  The model must have
  * been created with its faces.  With B3D_ICP_DEVICE_INPUT cloud and visible are device pointers. */

@@ -277,6 +277,10 @@ void orc_icp_eval(void* mp, int B, const double* w, const double* p, const doubl
                  shape_enabled, resid ? resid + 3 * c0 : nullptr, jac ? jac + 3 * c0 * NC : nullptr, cost + b, grad + (size_t)b * NC);
     }
 }
+void orc_icp_priors(void* gp, int B, double beta_pose, double beta_shape, const double* totals, const double* w, const double* q,
+                    double* cost, double* grad) {
+    for (int b = 0; b < B; ++b) icp_priors((const GMM*)gp, beta_pose, beta_shape, totals[b], NS, w + (size_t)NS * b, q + 4 * (size_t)NJ * b, cost + b, grad + (size_t)(3 + 3 * NJ + NS) * b);
+}
 void orc_icp_visible(int B, int V, int F, const uint32_t* faces, const double* cloud, uint8_t* visible) {
     for (int b = 0; b < B; ++b) icp_visible(V, F, faces, cloud + 3 * (size_t)V * b, visible + (size_t)V * b);
 }

@@ -225,6 +225,45 @@ void icp_nearest(int V, const double* cloud, const int* model_part, const uint8_
 }
 
 
+// Prior blocks of AvatarOptimizer::optimize: AvatarPosePriorCostFunctor (:644-700) and AvatarShapePriorCostFunctor (:703-726) with
+// the weights scaled by the number of ICP residual blocks (:1412-1414).  Adds their cost and their gradient (tangent layout of
+// icp_eval) to cost / grad.  The pose block's Jacobian is the reference's: L.middleRows<3>(3 i)^T * 0.707106781186548 * beta for
+// joint i + 1, zero for the constant last residual.
+void icp_priors(const GMM* gmm, double beta_pose, double beta_shape, double total_residuals, int S, const double* w, const double* q,
+                double* cost, double* grad) {
+    const double sbp = beta_pose * std::sqrt(total_residuals) / 15.0, sbs = beta_shape * std::sqrt(total_residuals) / 15.0;
+    if (beta_pose > 0.0 && gmm && gmm->nComps > 0) {
+        const int nd = gmm->nDims, nj = nd / 3;
+        std::vector<double> x(nd), r(nd + 1);
+        for (int i = 0; i < nj; ++i) {   // Eigen::AngleAxisd(q): axis * angle
+            const double* qq = q + 4 * (i + 1);
+            double n = std::sqrt(qq[0] * qq[0] + qq[1] * qq[1] + qq[2] * qq[2]);
+            if (n != 0.0) {
+                const double angle = 2.0 * std::atan2(n, std::fabs(qq[3]));
+                if (qq[3] < 0.0) n = -n;
+                for (int c = 0; c < 3; ++c) x[3 * i + c] = qq[c] / n * angle;
+            } else {
+                for (int c = 0; c < 3; ++c) x[3 * i + c] = 0.0;
+            }
+        }
+        const int comp = gmm->residual(x.data(), r.data());
+        for (int k = 0; k <= nd; ++k) { r[k] *= sbp; *cost += 0.5 * r[k] * r[k]; }
+        const double* L = gmm->prec_cho[comp].data();
+        for (int i = 0; i < nj; ++i)
+            for (int a = 0; a < 3; ++a) {
+                double acc = 0.0;
+                for (int k = 0; k < nd; ++k) acc += L[(size_t)(3 * i + a) * nd + k] * 0.707106781186548 * sbp * r[k];
+                grad[3 + 3 * (i + 1) + a] += acc;
+            }
+    }
+    if (beta_shape > 0.0)
+        for (int s = 0; s < S; ++s) {
+            const double rs = w[s] * sbs;
+            *cost += 0.5 * rs * rs;
+            grad[3 + 3 * 24 + s] += sbs * rs;
+        }
+}
+
 // pointVisible (AvatarOptimizer.cpp:1337-1352)
 void icp_visible(int V, int F, const uint32_t* faces, const double* cloud, uint8_t* visible) {
     std::fill(visible, visible + V, (uint8_t)0);

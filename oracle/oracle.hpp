@@ -221,6 +221,8 @@ void icp_eval(const Model& M, const double* w, const double* p, const double* q,
               const double* data, int shape_enabled, double* resid, double* jac, double* cost, double* grad);
 void quat_plus(const double* x, const double* delta, double* out);   // FakeQuaternionParameterization::Plus
 // findNN with invert = true (AvatarOptimizer.cpp:841-907): out[i] = nearest visible model point of data point i's part, or -1
+void icp_priors(const GMM* gmm, double beta_pose, double beta_shape, double total_residuals, int S, const double* w, const double* q,
+                double* cost, double* grad);   // pose / shape prior blocks (:644-726, :1412-1428), added to cost / grad
 void icp_visible(int V, int F, const uint32_t* faces, const double* cloud, uint8_t* visible);   // pointVisible (:1337-1352)
 void icp_nearest(int V, const double* cloud, const int* model_part, const uint8_t* visible, int nd, const double* data,
                  const int* data_part, int* out);

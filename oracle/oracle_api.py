@@ -193,6 +193,16 @@ class GMM:
         return out, c
 
 
+def icp_priors(gmm, beta_pose, beta_shape, totals, w, q, cost, grad):
+    """Adds AvatarOptimizer's pose-prior and shape-prior blocks (weights scaled by sqrt(#ICP residual blocks) / 15) to cost (B,) and
+    grad (B, 85); returns the new arrays."""
+    w, q, totals = _f64(w), _f64(q), _f64(totals)
+    cost, grad = _f64(cost).copy(), _f64(grad).copy()
+    lib().orc_icp_priors(gmm.h if gmm is not None else None, w.shape[0], C.c_double(beta_pose), C.c_double(beta_shape), _p(totals), _p(w),
+                         _p(q), _p(cost), _p(grad))
+    return cost, grad
+
+
 def icp_visible(cloud, faces):
     """pointVisible of AvatarOptimizer's ICP loop for B posed clouds (B, V, 3); faces (F, 3)."""
     cloud = _f64(cloud)

@@ -71,3 +71,29 @@ def test_icp_nearest_oracle_matches_numpy(synth, orc, model_np):
             assert got[i] == -1 and data_part[i] == 4
         else:
             assert got[i] == cand[np.argmin(((cloud[0][cand] - data[i]) ** 2).sum(axis=1))]
+
+
+def test_icp_priors_oracle_matches_numpy(synth, orc, model_np):
+    """The oracle's prior blocks against a numpy restatement built from GaussianMixture::residual and prec_cho."""
+    from conftest import PRIOR_TXT
+    prior = synth.load_pose_prior(PRIOR_TXT)
+    og = orc.GMM(prior=prior)
+    x = synth.make_icp_inputs(model_np, 2, 3, ndata=50)
+    totals = np.array([400.0, 36.0])
+    bp, bs = 0.2, 1.5
+    cost, grad = orc.icp_priors(og, bp, bs, totals, x["w"], x["q"], np.zeros(2), np.zeros((2, 85)))
+    arr = og.arrays()
+    for b in range(2):
+        v, wq = x["q"][b, 1:, :3], x["q"][b, 1:, 3]
+        n = np.linalg.norm(v, axis=1)
+        aa = (v / n[:, None] * np.sign(wq)[:, None] * (2 * np.arctan2(n, np.abs(wq)))[:, None]).reshape(-1)
+        out, comp = og.residual(aa)
+        sbp, sbs = bp * np.sqrt(totals[b]) / 15, bs * np.sqrt(totals[b]) / 15
+        r = np.asarray(out) * sbp
+        c = 0.5 * np.sum(r ** 2) + 0.5 * np.sum((x["w"][b] * sbs) ** 2)
+        L = np.asarray(arr["prec_cho"])[comp].reshape(69, 69)
+        g = np.zeros(85)
+        g[6:75] = L @ r[:69] * 0.707106781186548 * sbp
+        g[75:] = sbs * sbs * x["w"][b]
+        assert abs(cost[b] - c) < 1e-10 * c
+        assert np.max(np.abs(grad[b] - g)) < 1e-10 * np.max(np.abs(g))

@@ -186,3 +186,26 @@ def test_icp_large_batch_single_split(synth, orc, model_np, gpu_model):
     scale = np.max(np.abs(ref["grad"]), axis=1, keepdims=True)
     assert np.max(np.abs(cost - ref["cost"]) / ref["cost"]) < 1e-5
     assert np.max(np.abs(grad - ref["grad"]) / scale) < 2e-4
+
+
+def test_icp_full_objective_with_priors(synth, orc, model_np, gpu_model):
+    """ICP term + AvatarPosePriorCostFunctor + AvatarShapePriorCostFunctor (weights scaled by sqrt(#residual blocks) / 15) against
+    the oracle; a quaternion with negative w and an identity quaternion exercise Eigen's AngleAxis conversion branches."""
+    from conftest import PRIOR_TXT
+    api = pkg("api")
+    prior = synth.load_pose_prior(PRIOR_TXT)
+    gg, og = api.GaussianMixture(prior=prior), orc.GMM(prior=prior)
+    x = synth.make_icp_inputs(model_np, 6, 37, ndata=900)
+    q = x["q"].copy()
+    q[0, 5] *= -1.0
+    q[1, 7] = [0.0, 0.0, 0.0, 1.0]
+    om = orc.Model(model_np)
+    base = om.icp_eval(x["w"], x["p"], q, x["cptr"], x["mpt"], x["dpt"], x["dptr"], x["data"], nthreads=4)
+    totals = np.diff(x["cptr"]).astype(np.float64)
+    prob = api.IcpProblem(gpu_model, x["cptr"], x["mpt"], x["dpt"], x["dptr"], x["data"], dtype=np.float64)
+    for bp, bs, g in ((0.2, 1.0, gg), (0.0, 1.0, None), (0.2, 0.0, gg)):
+        rc, rg = orc.icp_priors(og if bp > 0 else None, bp, bs, totals, x["w"], q, base["cost"], base["grad"])
+        got = prob.eval_full(x["w"], x["p"], q, gmm=g, beta_pose=bp, beta_shape=bs)
+        assert np.max(np.abs(got["cost"] - rc) / rc) < 1e-10
+        assert np.max(np.abs(got["grad"] - rg) / np.max(np.abs(rg), axis=1, keepdims=True)) < 1e-10
+        assert np.all(rc > base["cost"])
