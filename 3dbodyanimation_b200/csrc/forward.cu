@@ -24,26 +24,53 @@ template <typename T>
 __global__ void __launch_bounds__(32 * JW) smpl_joints_kernel(const SkeletonConst* __restrict__ sk, int B,
                                                               const T* __restrict__ w, const T* __restrict__ p,
                                                               const T* __restrict__ r, T* __restrict__ jointPos,
-                                                              T* __restrict__ jointTrans, T* __restrict__ posefeat) {
+                                                              T* __restrict__ jointTrans, T* __restrict__ posefeat, int bpw) {
     __shared__ double s_r[JW][NJ * 9];
     __shared__ double s_g[JW][NJ * 12];
     __shared__ double s_jp[JW][NJ * 3];
     __shared__ double s_w[JW][NS];
+    // model constants of the CTA: jointShapeReg transposed ([s][3 j + c]: lanes = rows read consecutive words; straight from
+    // global memory the row stride of 80 B made every one of these loads a 20-sector gather), initialJointPos, level order
+    __shared__ double s_jsr[NS][NJ * 3], s_j0[NJ * 3];
+    __shared__ int s_order[NJ], s_lvstart[NJ + 2], s_parent[NJ];
+    for (int i = threadIdx.x; i < NJ * 3 * NS; i += 32 * JW) s_jsr[i % NS][i / NS] = sk->JSR[i];
+    for (int i = threadIdx.x; i < NJ * 3; i += 32 * JW) s_j0[i] = sk->J0[i];
+    if (threadIdx.x < NJ) { s_order[threadIdx.x] = sk->order[threadIdx.x]; s_parent[threadIdx.x] = sk->parent[threadIdx.x]; }
+    if (threadIdx.x < NJ + 2) s_lvstart[threadIdx.x] = sk->lvstart[threadIdx.x];
+    __syncthreads();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int b = blockIdx.x * JW + warp;
-    if (b >= B) return;
+    // a warp takes bpw consecutive bodies, so that the staging above is paid once per JW * bpw bodies
+    // a body's 216 rotation entries travel through 7 registers per lane; the next body's are requested before this body's chain
+    // starts, so their latency hides behind it
+    constexpr int RV = (NJ * 9 + 31) / 32;
+    T rv[RV];
+    {
+        const int bf = (blockIdx.x * JW + warp) * bpw;
+#pragma unroll
+        for (int u = 0; u < RV; ++u) rv[u] = (bf < B && lane + 32 * u < NJ * 9) ? r[(size_t)bf * NJ * 9 + lane + 32 * u] : (T)0;
+    }
+    for (int t = 0; t < bpw; ++t) {
+    const int b = (blockIdx.x * JW + warp) * bpw + t;
+    if (b >= B) break;
     double* R = s_r[warp];
     double* G = s_g[warp];
     double* jp = s_jp[warp];
-    for (int i = lane; i < NJ * 9; i += 32) R[i] = (double)r[(size_t)b * NJ * 9 + i];
+#pragma unroll
+    for (int u = 0; u < RV; ++u)
+        if (lane + 32 * u < NJ * 9) R[lane + 32 * u] = (double)rv[u];
+    if (t + 1 < bpw && b + 1 < B) {
+#pragma unroll
+        for (int u = 0; u < RV; ++u)
+            if (lane + 32 * u < NJ * 9) rv[u] = r[(size_t)(b + 1) * NJ * 9 + lane + 32 * u];
+    }
     if (lane < NS) s_w[warp][lane] = (double)w[(size_t)b * NS + lane];
     __syncwarp();
     // jointPos = initialJointPos + jointShapeReg * w
     for (int i = lane; i < NJ * 3; i += 32) {
         double acc = 0.0;
 #pragma unroll
-        for (int s = 0; s < NS; ++s) acc += sk->JSR[i * NS + s] * s_w[warp][s];
-        jp[i] = sk->J0[i] + acc;
+        for (int s = 0; s < NS; ++s) acc += s_jsr[s][i] * s_w[warp][s];
+        jp[i] = s_j0[i] + acc;
     }
     __syncwarp();
     // chain, level by level: global = parent o [r_j | jp_j - jp_parent]   (mulAffine, Util.h:191-199)
@@ -58,19 +85,28 @@ __global__ void __launch_bounds__(32 * JW) smpl_joints_kernel(const SkeletonCons
         for (int c = 0; c < 3; ++c) G[9 + c] = (double)p[(size_t)b * 3 + c];
     }
     __syncwarp();
+    const int* order = s_order;      // joints in depth order (model.cu): a level is the run order[lvstart[l] .. lvstart[l + 1])
+    const int* lvstart = s_lvstart;
+    // One lane per ELEMENT of a child's 3 x 4 matrix (not per joint): a level of n joints is n * 12 independent 3-term sums, so
+    // the warp is busy whatever the width of the tree and a level costs 7 shared-memory instructions per pass instead of 39.
     for (int lvl = 1; lvl <= max_depth; ++lvl) {
-        if (depth == lvl) {
-            const double* A = G + 12 * pa;
-            const double* Rl = R + 9 * j;
-            double* Bm = G + 12 * j;
-            const double t0 = jp[3 * j] - jp[3 * pa], t1 = jp[3 * j + 1] - jp[3 * pa + 1], t2 = jp[3 * j + 2] - jp[3 * pa + 2];
-#pragma unroll
-            for (int col = 0; col < 3; ++col)
-#pragma unroll
-                for (int row = 0; row < 3; ++row)
-                    Bm[3 * col + row] = A[row] * Rl[3 * col] + A[3 + row] * Rl[3 * col + 1] + A[6 + row] * Rl[3 * col + 2];
-#pragma unroll
-            for (int row = 0; row < 3; ++row) Bm[9 + row] = A[9 + row] + (A[row] * t0 + A[3 + row] * t1 + A[6 + row] * t2);
+        const int l0 = lvstart[lvl], work = (lvstart[lvl + 1] - l0) * 12;
+        for (int base = 0; base < work; base += 32) {
+            const int idx = base + lane;
+            if (idx < work) {
+                const int jj = order[l0 + idx / 12], e = idx % 12;
+                const int pj = s_parent[jj];
+                const double* A = G + 12 * pj;
+                if (e < 9) {
+                    const int col = e / 3, row = e - 3 * col;
+                    const double* Rl = R + 9 * jj + 3 * col;
+                    G[12 * jj + e] = A[row] * Rl[0] + A[3 + row] * Rl[1] + A[6 + row] * Rl[2];
+                } else {
+                    const int row = e - 9;
+                    const double t0 = jp[3 * jj] - jp[3 * pj], t1 = jp[3 * jj + 1] - jp[3 * pj + 1], t2 = jp[3 * jj + 2] - jp[3 * pj + 2];
+                    G[12 * jj + e] = A[9 + row] + (A[row] * t0 + A[3 + row] * t1 + A[6 + row] * t2);
+                }
+            }
         }
         __syncwarp();
     }
@@ -92,6 +128,8 @@ __global__ void __launch_bounds__(32 * JW) smpl_joints_kernel(const SkeletonCons
             const int jj = i / 9 + 1, a = (i % 9) / 3, c = i % 3;
             posefeat[(size_t)b * B3D_POSEDIRS_DIM + i] = (T)(R[9 * jj + 3 * c + a] - (a == c ? 1.0 : 0.0));
         }
+    __syncwarp();   // the next body overwrites R / G / jp
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -488,7 +526,8 @@ static int forward_impl(const b3d_model* m, int B, const T* w, const T* p, const
     if (flags & B3D_FWD_GIVEN_TRANSFORMS) {
         if (!jointTrans || !cloud || use_pd) return set_error(B3D_EINVAL, "B3D_FWD_GIVEN_TRANSFORMS needs jointTrans and cloud, and excludes B3D_FWD_POSEDIRS");
     } else {
-        smpl_joints_kernel<T><<<(B + JW - 1) / JW, 32 * JW, 0, st>>>(m->d_sk, B, w, p, r, jointPos, G, pf);
+        const int bpw = B >= 4096 ? 4 : 1;   // bodies per warp: amortise the CTA's constant staging once the machine is full
+        smpl_joints_kernel<T><<<(B + JW * bpw - 1) / (JW * bpw), 32 * JW, 0, st>>>(m->d_sk, B, w, p, r, jointPos, G, pf, bpw);
         B3D_LAUNCH_CHECK();
     }
     if (use_tc) {

@@ -100,6 +100,8 @@ struct SkeletonConst {
     int32_t parent[NJ];
     int32_t depth[NJ];
     int32_t max_depth;
+    int32_t order[NJ];          // joints in (depth, index) order: a level of the tree is a contiguous run
+    int32_t lvstart[NJ + 2];    // lvstart[l] = number of joints of depth < l
     double J0[3 * NJ];          // initialJointPos, J0[3j + c]
     double JSR[3 * NJ * NS];    // jointShapeReg row-major (3j + c) x S
     double offset[3 * NJ];      // rest bone vectors (Sim3BA.h:533-555)

@@ -158,6 +158,11 @@ int b3d_model_create(const b3d_model_desc* d, b3d_model** out) {
         m->sk.depth[j] = m->sk.depth[pa] + 1;
         if (m->sk.depth[j] > m->sk.max_depth) m->sk.max_depth = m->sk.depth[j];
     }
+    for (int l = 0, pos = 0; l <= NJ + 1; ++l) {
+        m->sk.lvstart[l] = pos;
+        for (int j = 0; j < NJ; ++j)
+            if (m->sk.depth[j] == l) m->sk.order[pos++] = j;
+    }
     // initialJointPos = template * jointRegressor; jointShapeReg column s = shapedir s * jointRegressor (AvatarModel.cpp:113-127)
     for (int i = 0; i < 3 * NJ; ++i) m->sk.J0[i] = 0.0;
     for (int i = 0; i < 3 * NJ * NS; ++i) m->sk.JSR[i] = 0.0;

@@ -27,7 +27,7 @@ def main():
                 rows.append((n, fname, int(r[0]), r[1].strip()[:110], int(d["Instructions Executed"] or 0), stalls))
     tot = sum(r[0] for r in rows)
     print(f"total samples {tot}")
-    for n, f, ln, src, inst, st in sorted(rows, reverse=True)[:top]:
+    for n, f, ln, src, inst, st in sorted(rows, key=lambda r: r[:3], reverse=True)[:top]:
         tops = ", ".join(f"{k} {v}" for k, v in sorted(st.items(), key=lambda x: -x[1])[:3])
         print(f"{100 * n / tot:5.1f}%  {f}:{ln:<4d} inst {inst:>10d}  [{tops}]  {src}")
 
