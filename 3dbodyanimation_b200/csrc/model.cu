@@ -32,6 +32,19 @@ int require_device() {
     e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev);
     if (e != cudaSuccess) return set_error(B3D_ECUDA, "cudaDeviceGetAttribute: %s", cudaGetErrorString(e));
     if (major != 10) return set_error(B3D_ECUDA, "device %d has compute capability %d.x; the kernels are built for sm_100a only", dev, major);
+    // The per-call scratch buffers come from the stream-ordered pool (cudaMallocAsync).  Its default release threshold is 0: at
+    // every synchronisation the pool hands its free memory back to the driver, so a caller that synchronises after each call
+    // (b3d_fit_frames, every host-pointer entry point) would pay a real allocation per call — measured as 14 -> 18-58 ms per
+    // 1,000-frame step.  Keep the memory in the pool.
+    static bool pool_set[64] = {};
+    if (dev >= 0 && dev < 64 && !pool_set[dev]) {
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+            uint64_t keep = UINT64_MAX;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+        pool_set[dev] = true;
+    }
     return B3D_OK;
 }
 

@@ -216,7 +216,7 @@ def run_b200(args):
         step_resident()
     barrier()
     clocks = Clocks(local)
-    if rank == 0:
+    if rank == 0 and not os.environ.get("B3D_BENCH_NO_CLOCKS"):
         clocks.start()
     l0 = lib.b3d_launch_count()
     evs = []
