@@ -390,7 +390,7 @@ def run_b200(args):
                      "write_only_peak_gbs": 5400.0, "write_only_peak_source": "tools/store_probe.cu on this pool's B200 (profiles/r01_store_probe.log)",
                      "workload": f"forward sweep point B={FB} (BASELINE configs[3])", "whole_call_ms": fwd_ms,
                      "verts_per_sec": world * FB * V / (fwd_ms * 1e-3), "peak_source": peak_src},
-        "roofline_lm": {"kernel": "fit_single_kernel<128>", "bound": "fp64 ALU / latency (not HBM: ~1.2 KB algorithmic I/O per frame)",
+        "roofline_lm": {"kernel": "fit_single_kernel<256>", "bound": "fp64 ALU / latency (not HBM: ~1.2 KB algorithmic I/O per frame)",
                         "ms_per_launch": fit_ms, "share_of_step": fit_ms / step_ms, "lm_iterations_per_step": cnt[0].item() / world,
                         "achieved_gflops": cnt[0].item() / world * FLOP_PER_FRAME_ITER_C2 / (fit_ms * 1e-3) / 1e9,
                         "flop_model": "0.37 Mflop per frame-iteration (SURVEY 8d)"},
