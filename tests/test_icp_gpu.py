@@ -209,3 +209,50 @@ def test_icp_full_objective_with_priors(synth, orc, model_np, gpu_model):
         assert np.max(np.abs(got["cost"] - rc) / rc) < 1e-10
         assert np.max(np.abs(got["grad"] - rg) / np.max(np.abs(rg), axis=1, keepdims=True)) < 1e-10
         assert np.all(rc > base["cost"])
+
+
+def test_icp_iteration_stays_on_the_device(synth, orc, model_np, gpu_model):
+    """One ICP iteration with everything resident (B3D_ICP_DEVICE_INPUT): posed cloud from b3d_smpl_forward_dev, b3d_icp_visible,
+    b3d_icp_nearest and b3d_icp_create on device pointers, then the evaluation — equal to the host-pointer chain."""
+    import ctypes as C
+    import torch
+    api, capi = pkg("api"), pkg("_capi")
+    lib = capi.lib()
+    rm = synth.make_render_model()          # a model with faces (visibility needs them)
+    gm = api.AvatarModel(rm)
+    b, nd, nparts = 3, 1200, 4
+    x = synth.make_icp_inputs(rm, b, 44, ndata=nd)
+    r = synth.quat_to_r(x["q"])
+    V = gm.numPoints
+    model_part = (np.argmax(rm["weights"], axis=1) % nparts).astype(np.int32)
+    rng = np.random.default_rng(5)
+    data_part = rng.integers(0, nparts, b * nd).astype(np.int32)
+    # host chain
+    cloud, _, _ = api.smpl_forward(gm, x["w"], x["p"], r, dtype=np.float64)
+    vis = api.icp_visible(gm, cloud)
+    nn = api.icp_nearest(gm, cloud, model_part, x["dptr"], x["data"], data_part, visible=vis)
+    want = api.IcpProblem(gm, x["dptr"], nn, None, x["dptr"], x["data"], dtype=np.float64).eval(x["w"], x["p"], x["q"])
+    # device chain
+    dev = torch.device("cuda:0")
+    P = lambda t: C.c_void_p(t.data_ptr())
+    tw, tp, tr, tq = [torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(dev) for a in (x["w"], x["p"], r, x["q"])]
+    tcloud = torch.empty(b, V, 3, dtype=torch.float64, device=dev)
+    tjp, tjt = torch.empty(b, 24, 3, dtype=torch.float64, device=dev), torch.empty(b, 24, 12, dtype=torch.float64, device=dev)
+    capi.check(lib.b3d_smpl_forward_dev(gm.h, b, capi.F64, P(tw), P(tp), P(tr), P(tcloud), P(tjp), P(tjt), 0, None), "forward")
+    tvis = torch.empty(b, V, dtype=torch.uint8, device=dev)
+    capi.check(lib.b3d_icp_visible(gm.h, b, capi.F64, P(tcloud), 1, P(tvis)), "visible")
+    tdata = torch.from_numpy(np.ascontiguousarray(x["data"])).to(dev)
+    tpart = torch.from_numpy(data_part).to(dev)
+    tnn = torch.empty(b * nd, dtype=torch.int32, device=dev)
+    dptr = np.ascontiguousarray(x["dptr"], dtype=np.int64)
+    capi.check(lib.b3d_icp_nearest(gm.h, b, capi.F64, P(tcloud), nparts, capi.ptr(model_part), P(tvis), capi.ptr(dptr), P(tdata), P(tpart), 1,
+                                   P(tnn)), "nearest")
+    assert np.array_equal(tvis.cpu().numpy(), vis) and np.array_equal(tnn.cpu().numpy(), nn)
+    h = C.c_void_p()
+    capi.check(lib.b3d_icp_create(gm.h, b, capi.F64, capi.ptr(dptr), P(tnn), None, capi.ptr(dptr), P(tdata), 1, C.byref(h)), "create")
+    tcost, tgrad = torch.empty(b, dtype=torch.float64, device=dev), torch.empty(b, 85, dtype=torch.float64, device=dev)
+    capi.check(lib.b3d_icp_eval_dev(h, P(tw), P(tp), P(tq), 0, P(tcost), P(tgrad), None), "eval")
+    torch.cuda.synchronize()
+    lib.b3d_icp_destroy(h)
+    assert np.allclose(tcost.cpu().numpy(), want["cost"], rtol=1e-12, atol=0)
+    assert np.allclose(tgrad.cpu().numpy(), want["grad"], rtol=0, atol=1e-11 * np.max(np.abs(want["grad"])))
