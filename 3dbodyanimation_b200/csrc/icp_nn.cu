@@ -15,8 +15,8 @@
 
 namespace b3d {
 
-constexpr int NN_THREADS = 256, NN_PER_THREAD = 4;   // a work item: up to 32 * NN_PER_THREAD points of one part
-constexpr int NN_LOAD = 8;                           // 2048 points per CTA chunk (the local index fits the 12 low bits of `order`):
+constexpr int NN_THREADS = 512, NN_PER_THREAD = 4;   // a work item: up to 32 * NN_PER_THREAD points of one part
+constexpr int NN_LOAD = 4;                           // 2048 points per CTA chunk (the local index fits the 12 low bits of `order`):
                                                      // larger chunks give fuller per-part buckets
 
 template <typename T> __device__ __forceinline__ T inf_();
