@@ -768,11 +768,8 @@ int b3d_fit_single_dev(const b3d_model* m, const b3d_gmm* gmm, const b3d_fit_opt
     B3D_CUDA(cudaMallocAsync(&dfc, sizeof(FitConst), st));
     // pageable source: the copy is staged before the call returns, so the stack object may go out of scope
     B3D_CUDA(cudaMemcpyAsync(dfc, &fc, sizeof(FitConst), cudaMemcpyHostToDevice, st));
-    static bool attr_set = false;
-    if (!attr_set) {
-        B3D_CUDA(cudaFuncSetAttribute(fit_single_kernel<FS_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SingleSmem)));
-        attr_set = true;
-    }
+    // per device and context, cheap: set on every call (a process-wide flag would miss a second GPU)
+    B3D_CUDA(cudaFuncSetAttribute(fit_single_kernel<FS_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SingleSmem)));
     fit_single_kernel<FS_THREADS><<<B, FS_THREADS, sizeof(SingleSmem), st>>>(dfc, B, kps, nkp, R0, sim3, w, jointAA, usable, trace, trace_stride,
                                                                             niters, term);
     B3D_LAUNCH_CHECK();
@@ -787,6 +784,7 @@ int b3d_fit_single(const b3d_model* m, const b3d_gmm* gmm, const b3d_fit_opts* o
     if (B < 0) return set_error(B3D_EINVAL, "b3d_fit_single: B < 0");
     if (B == 0) return B3D_OK;
     const size_t nb = (size_t)B;
+    if (int rc = validate_keypoints(kps, nkp, nb, "b3d_fit_single")) return rc;
     const size_t s_kp = sizeof(b3d_kp) * nb * MAXKP, s_nk = 4 * nb, s_r0 = 8 * nb * 9, s_s3 = 8 * nb * 7, s_w = 8 * nb * NS,
                  s_ja = 8 * nb * NJ * 3, s_tr = trace ? sizeof(b3d_iter_record) * nb * (size_t)trace_stride : 0;
     auto al = [](size_t x) { return (x + 255) / 256 * 256; };

@@ -78,7 +78,7 @@ struct WinSmem {
     double R0[9];
     double red[40];
     double Hw[NS * NS], gw[NS], yw[NS], Sw[NS * NS], zw[NS];
-    double piv[2];
+    double piv[4];                        // pivot (value, 1/sqrt) of the Crout column, double-buffered by column parity
     int32_t flag;
 };
 
@@ -135,6 +135,7 @@ __device__ double win_evaluate(const FitConst* __restrict__ C, int F, const doub
                     const int j = E.fcol[k][sb];
                     if (j <= i) E.Hf[tri(i, j)] += a0 * E.out.J[k][0][sb] + a1 * E.out.J[k][1][sb];
                 }
+                __syncwarp();     // the next keypoint's lanes may hit the same elements of row i (different slot -> lane mapping)
                 gacc += a0 * E.out.res[k][0] + a1 * E.out.res[k][1];
             }
             if (lane == 0) E.gf[i] = gacc;
@@ -249,12 +250,15 @@ __device__ bool win_solve(const FitConst* __restrict__ C, int F, double radius, 
             const bool is_row = r < nrows && (has_next || r < ROW_LO || r >= ROW_W);
             const int c0 = (r >= ROW_LO && r < ROW_W) ? r - ROW_LO : 0;
             double dg = r < NB ? K.M[r][r] : 0.0;
+            // the pivot of column j sits in S.piv[2 (j & 1) ..]: the owner of row j + 1 publishes the pivot of column j + 1 into the
+            // OTHER pair while slower warps may still be reading column j's (one barrier per column is then enough; every thread
+            // reads the same pair after the same barrier, so the non-positive-pivot exit is block-uniform)
             if (tid == 0) { const double il = rsqrt(dg); S.piv[0] = dg; S.piv[1] = il; W.invd[(size_t)f * NB] = il; }
             for (int j = 0; j < NB; ++j) {
                 __syncthreads();
-                const double d = S.piv[0];
+                const double d = S.piv[2 * (j & 1)];
                 if (!(d > 0.0)) { ok = false; break; }
-                const double inv = S.piv[1];
+                const double inv = S.piv[2 * (j & 1) + 1];
                 if (is_row && r > j && c0 <= j) {
                     const double* rj = K.M[j];
                     double* rr = K.M[r];
@@ -268,7 +272,7 @@ __device__ bool win_solve(const FitConst* __restrict__ C, int F, double radius, 
                     rr[j] = val;
                     if (r < NB) {
                         dg -= val * val;
-                        if (r == j + 1) { const double il = rsqrt(dg); S.piv[0] = dg; S.piv[1] = il; W.invd[(size_t)f * NB + r] = il; }
+                        if (r == j + 1) { const double il = rsqrt(dg); S.piv[2 * (r & 1)] = dg; S.piv[2 * (r & 1) + 1] = il; W.invd[(size_t)f * NB + r] = il; }
                     }
                 }
             }
@@ -569,11 +573,7 @@ namespace b3d {
 int win_launch(const FitConst* dfc, const WinProblem* dprobs, int nprob, const b3d_kp* kps, const int32_t* nkp, const double* R0, double* poses,
                double* W, uint8_t* usable, b3d_iter_record* trace, int trace_stride, int32_t* niters, int32_t* term, double* ws, cudaStream_t st) {
     if (nprob <= 0) return B3D_OK;
-    static bool attr_set = false;
-    if (!attr_set) {
-        B3D_CUDA(cudaFuncSetAttribute(fit_window_kernel<FW_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(WinSmem)));
-        attr_set = true;
-    }
+    B3D_CUDA(cudaFuncSetAttribute(fit_window_kernel<FW_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(WinSmem)));   // per device: every call
     fit_window_kernel<FW_THREADS><<<nprob, FW_THREADS, sizeof(WinSmem), st>>>(dfc, nprob, dprobs, kps, nkp, R0, poses, W, usable, trace, trace_stride,
                                                                              niters, term, ws);
     B3D_LAUNCH_CHECK();
@@ -624,6 +624,7 @@ int b3d_fit_window(const b3d_model* m, const b3d_fit_opts* opts, int32_t F, cons
     if (!m || !opts || !kps || !nkp || !R0 || !poses || !w) return set_error(B3D_EINVAL, "b3d_fit_window: null argument");
     if (F <= 0) return F < 0 ? set_error(B3D_EINVAL, "b3d_fit_window: F < 0") : B3D_OK;
     const size_t nf = (size_t)F;
+    if (int rc = validate_keypoints(kps, nkp, nf, "b3d_fit_window")) return rc;
     auto al = [](size_t x) { return (x + 255) / 256 * 256; };
     const size_t s_kp = al(sizeof(b3d_kp) * nf * MAXKP), s_nk = al(4 * nf), s_r0 = al(8 * nf * 9), s_po = al(8 * nf * NPF), s_w = al(8 * nf * NS),
                  s_tr = trace ? al(sizeof(b3d_iter_record) * (size_t)trace_cap) : 0;

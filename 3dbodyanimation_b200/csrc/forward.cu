@@ -505,11 +505,18 @@ static int forward_impl(const b3d_model* m, int B, const T* w, const T* p, const
     const VertexTables<T>& t = sizeof(T) == 4 ? (const VertexTables<T>&)m->t32 : (const VertexTables<T>&)m->t64;
     const bool use_pd = (flags & B3D_FWD_POSEDIRS) != 0;
     if (use_pd && !m->has_posedirs) return set_error(B3D_EINVAL, "B3D_FWD_POSEDIRS requested but the model has no posedirs");
+    if ((flags & B3D_FWD_GIVEN_TRANSFORMS) && (!jointTrans || !cloud || use_pd))   // validated before anything is allocated
+        return set_error(B3D_EINVAL, "B3D_FWD_GIVEN_TRANSFORMS needs jointTrans and cloud, and excludes B3D_FWD_POSEDIRS");
+    // stream-ordered scratch, released on every return path
+    struct Scratch {
+        cudaStream_t st;
+        void* p[3] = {nullptr, nullptr, nullptr};
+        ~Scratch() { for (void* q : p) if (q) cudaFreeAsync(q, st); }
+    } scratch{st};
     T* G = jointTrans;
-    T* scratchG = nullptr;
     T* pf = nullptr;
     T* off = nullptr;
-    if (!G) { B3D_CUDA(cudaMallocAsync(&scratchG, sizeof(T) * (size_t)B * NJ * 12, st)); G = scratchG; }
+    if (!G) { B3D_CUDA(cudaMallocAsync(&scratch.p[0], sizeof(T) * (size_t)B * NJ * 12, st)); G = (T*)scratch.p[0]; }
     // B3D_FWD_LBS_* flags (or env B3D_LBS = tc | sorted | bodylane | generic) force a float32 path (tests, profiling); default:
     // tensor-core kernel (lbs_tc.cu; with the pose blendshapes fused in when they are asked for) for batches that fill the
     // machine, tile-sorted lane = vertex kernel below that
@@ -520,12 +527,11 @@ static int forward_impl(const b3d_model* m, int B, const T* w, const T* p, const
     const bool use_tc = cloud && sizeof(T) == 4 && m->nw == 4 && g_al16 && m->tc.blob && (!use_pd || m->tc.pose_b) &&
                         (want == "tc" || (want.empty() && B >= TC_AUTO_MIN_B));
     if (use_pd && cloud) {
-        B3D_CUDA(cudaMallocAsync(&pf, sizeof(T) * (size_t)B * B3D_POSEDIRS_DIM, st));
-        if (!use_tc) B3D_CUDA(cudaMallocAsync(&off, sizeof(T) * (size_t)B * 3 * m->Vpad, st));
+        B3D_CUDA(cudaMallocAsync(&scratch.p[1], sizeof(T) * (size_t)B * B3D_POSEDIRS_DIM, st));
+        pf = (T*)scratch.p[1];
+        if (!use_tc) { B3D_CUDA(cudaMallocAsync(&scratch.p[2], sizeof(T) * (size_t)B * 3 * m->Vpad, st)); off = (T*)scratch.p[2]; }
     }
-    if (flags & B3D_FWD_GIVEN_TRANSFORMS) {
-        if (!jointTrans || !cloud || use_pd) return set_error(B3D_EINVAL, "B3D_FWD_GIVEN_TRANSFORMS needs jointTrans and cloud, and excludes B3D_FWD_POSEDIRS");
-    } else {
+    if (!(flags & B3D_FWD_GIVEN_TRANSFORMS)) {
         const int bpw = B >= 4096 ? 4 : 1;   // bodies per warp: amortise the CTA's constant staging once the machine is full
         smpl_joints_kernel<T><<<(B + JW * bpw - 1) / (JW * bpw), 32 * JW, 0, st>>>(m->d_sk, B, w, p, r, jointPos, G, pf, bpw);
         B3D_LAUNCH_CHECK();
@@ -556,11 +562,7 @@ static int forward_impl(const b3d_model* m, int B, const T* w, const T* p, const
         const bool want_bodylane = want == "bodylane";
         if (false) {
         } else if (want != "generic" && want_bodylane && sizeof(T) == 4 && m->nw == 4 && !use_pd && m->ts.rec && g_al16 && B >= 256) {
-            static bool attr_set = false;
-            if (!attr_set) {
-                B3D_CUDA(cudaFuncSetAttribute(smpl_lbs_bodylane_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BlSmem)));
-                attr_set = true;
-            }
+            B3D_CUDA(cudaFuncSetAttribute(smpl_lbs_bodylane_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BlSmem)));   // per device: every call
             const int ranges = m->Vpad / BL_R;
             int bgroups = std::max(1, (148 * 4) / ranges);                      // ~4 CTAs per SM over the launch, 1 resident
             int bper = (B + bgroups - 1) / bgroups;
@@ -578,9 +580,6 @@ static int forward_impl(const b3d_model* m, int B, const T* w, const T* p, const
 #undef B3D_LBS
         B3D_LAUNCH_CHECK();
     }
-    if (scratchG) B3D_CUDA(cudaFreeAsync(scratchG, st));
-    if (pf) B3D_CUDA(cudaFreeAsync(pf, st));
-    if (off) B3D_CUDA(cudaFreeAsync(off, st));
     return B3D_OK;
 }
 

@@ -619,11 +619,7 @@ static int launch_accumulate(const b3d_icp* h, const double* w, cudaStream_t st)
     const b3d_model* m = h->m;
     constexpr size_t smem = icp_smem_bytes<T, NW, NWARPS>();
     static_assert(smem <= 232448, "icp_accumulate_kernel: shared memory over the sm_100 limit");
-    static bool attr_done = false;
-    if (!attr_done) {
-        B3D_CUDA(cudaFuncSetAttribute(icp_accumulate_kernel<T, NW, NWARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_done = true;
-    }
+    B3D_CUDA(cudaFuncSetAttribute(icp_accumulate_kernel<T, NW, NWARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));   // per device: every call
     // enough CTAs for two waves of the 148 SMs when the batch is small; one CTA per body group when it is large
     int vsplit = 1;
     {   // the split whose grid fills whole waves of the 148 SMs best (ties: the smaller split)

@@ -43,6 +43,11 @@ void count_launch(int n = 1);
 // element-wise double -> float conversion on the device (util.cu)
 int b3d_convert_f64_f32_dev(const double* src, float* dst, size_t n, cudaStream_t st);
 
+// Host-pointer entry points: every used keypoint must name a joint in [0, 24) (it indexes FitConst tables and jointPos on the
+// device).  Returns B3D_EINVAL naming the first offender.  The _dev entry points cannot look: their kernels clamp jid instead.
+int validate_keypoints(const b3d_kp* kps, const int32_t* nkp, size_t frames, const char* who);
+__host__ __device__ inline int clamp_jid(int jid) { return jid < 0 ? 0 : (jid >= NJ ? NJ - 1 : jid); }
+
 // Verifies that the current device can run sm_100a code.  No CPU fallback: callers propagate the error.
 int require_device();
 

@@ -543,6 +543,7 @@ int build_tc_tables(b3d_model& m, const std::vector<double>& vert, const std::ve
 }
 
 static std::atomic<int> g_tc_trace_on{0};
+static std::atomic<int> g_tc_forced_splits{0};
 
 // Pose features (B x 207 row-major, joints kernel) -> A operand slabs of the pose contraction: per group of 128 bodies, 26 slabs
 // [128 rows x 8 k] in the canonical layout, rounded to TF32 (one pass is enough: the pose term is ~1e-2 of a vertex coordinate).
@@ -557,18 +558,18 @@ __global__ void __launch_bounds__(256) pose_operand_kernel(const float* __restri
 }
 
 int launch_lbs_tc(const b3d_model* m, int B, const float* wshape, const float* G, const float* posefeat, float* cloud, cudaStream_t st) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        B3D_CUDA(cudaFuncSetAttribute(smpl_lbs_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem)));
-        B3D_CUDA(cudaFuncSetAttribute(smpl_lbs_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem)));
-        B3D_CUDA(cudaFuncSetAttribute(smpl_lbs_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem)));
-        attr_set = true;
+    // the attribute is per device and context: set it for the instantiation this call launches (cheap), not once per process
+    const int trace = g_tc_trace_on.load();
+    {
+        const void* fn = posefeat ? (const void*)smpl_lbs_tc_kernel<false, true> : trace ? (const void*)smpl_lbs_tc_kernel<true, false>
+                                                                                        : (const void*)smpl_lbs_tc_kernel<false, false>;
+        B3D_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(TcSmem)));
     }
     const int groups = (B + TC_M - 1) / TC_M;
     const int tiles = m->tc.sort_tiles;
     // vertex splits: fill 148 SMs in whole waves; a CTA's prologue (TMEM allocation, transforms -> TMEM, pipeline fill) costs about
     // one sort tile's worth of time (fitted to B = 65536 timings at 2 and 8 splits)
-    const int forced = [] { const char* e = getenv("B3D_TC_SPLITS"); return e ? atoi(e) : 0; }();   // read per call: tests vary it
+    const int forced = g_tc_forced_splits.load();   // debug hook b3d_debug_tc_splits (tests vary the vertex split); 0 in production
     int best_s = 1;
     double best_cost = 1e30;
     for (int s = 1; s <= std::min(tiles, 24); ++s) {
@@ -582,7 +583,6 @@ int launch_lbs_tc(const b3d_model* m, int B, const float* wshape, const float* G
     // rows leave as TMA bulk stores when row r of the cloud is 16 B aligned for even r and 8 mod 16 for odd r (true for V = 6890 and
     // a 16 B aligned cloud: 6890 * 12 = 8 mod 16), which is how the staging rows are laid out; otherwise plain stores
     const int bulk_rows = ((reinterpret_cast<uintptr_t>(cloud) & 15) == 0 && ((size_t)m->V * 12) % 16 == 8) ? 1 : 0;
-    const int trace = g_tc_trace_on.load();
     const dim3 grid(best_s, groups);
     if (posefeat) {
         if (!m->tc.pose_b) return set_error(B3D_EINVAL, "tensor-core LBS: the model has no pose blendshape tables");
@@ -625,6 +625,8 @@ int build_tc_pose_tables(b3d_model& m, const std::vector<float>& p32) {
 extern "C" {
 // debug hooks (tools/prof.py tctrace): switch the timeline on / read it back as [warp][tile][point] clock64 values
 int b3d_debug_tc_trace(int on) { b3d::g_tc_trace_on.store(on); return 0; }
+// force the number of vertex splits of the tensor-core LBS launch (0 = automatic); tests use it to cover every tile split
+int b3d_debug_tc_splits(int splits) { b3d::g_tc_forced_splits.store(splits > 0 ? splits : 0); return 0; }
 int b3d_debug_tc_trace_read(long long* out, int n) {
     const size_t bytes = sizeof(long long) * (size_t)std::min(n, (b3d::TC_EPI_WARPS + 4) * b3d::TC_TRACE_TILES * b3d::TC_TRACE_PTS);
     return cudaMemcpyFromSymbol(out, b3d::g_tc_trace, bytes) == cudaSuccess ? 0 : 2;

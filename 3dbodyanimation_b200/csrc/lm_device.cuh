@@ -188,7 +188,7 @@ __device__ void eval_reproj(const FitConst* __restrict__ C, const double* x, con
     // phase B1: one thread per keypoint — forward chain, residual, Huber, row-vector back-propagation
     if (tid < nkp) {
         const int k = tid;
-        const int jid = kps[k].jid;
+        const int jid = clamp_jid(kps[k].jid);
         const int len = C->chain_len[jid];
         double q[3] = {S.bone[jid][0], S.bone[jid][1], S.bone[jid][2]};
         S.q[k][0][0] = q[0]; S.q[k][0][1] = q[1]; S.q[k][0][2] = q[2];
@@ -249,7 +249,7 @@ __device__ void eval_reproj(const FitConst* __restrict__ C, const double* x, con
     // phase B2: one task per (keypoint, non-zero column)
     for (int t = tid; t < nkp * NNZPAD; t += T) {
         const int k = t / NNZPAD, slot = t % NNZPAD;
-        const int jid = kps[k].jid;
+        const int jid = clamp_jid(kps[k].jid);
         const int len = C->chain_len[jid];
         const int naa = 3 * (len - 1);
         if (slot >= 7 + naa + (C->with_shape ? NS : 0)) continue;

@@ -88,6 +88,13 @@ int zip_member(FILE* f, const ZipEntry& e, std::vector<unsigned char>& out) {
     unsigned char h[30];
     if (fseek(f, (long)e.offset, SEEK_SET) || fread(h, 1, 30, f) != 30 || rd32(h) != 0x04034b50u) return B3D_EFORMAT;
     if (fseek(f, (long)(e.offset + 30 + rd16(h + 26) + rd16(h + 28)), SEEK_SET)) return B3D_EFORMAT;
+    {   // sizes come from the file: bound them by what the file can hold (deflate expands at most ~1032 : 1)
+        const long here = ftell(f);
+        if (here < 0 || fseek(f, 0, SEEK_END)) return B3D_EFORMAT;
+        const long fsize = ftell(f);
+        if (fseek(f, here, SEEK_SET)) return B3D_EFORMAT;
+        if (e.csize > (uint64_t)(fsize - here) || e.usize > 1040ull * (e.csize + 64)) return B3D_EFORMAT;
+    }
     std::vector<unsigned char> comp((size_t)e.csize);
     if (fread(comp.data(), 1, comp.size(), f) != comp.size()) return B3D_EFORMAT;
     if (e.method == 0) {
@@ -135,7 +142,11 @@ int parse_npy(const std::vector<unsigned char>& raw, NpyArray& a) {
     a.word = atoi(h.c_str() + p + 3);
     p = h.find("'fortran_order'");
     if (p == std::string::npos) return B3D_EFORMAT;
-    a.fortran = h.compare(h.find_first_not_of(" :", p + 15), 4, "True") == 0;
+    {
+        const size_t v = h.find_first_not_of(" :", p + 15);
+        if (v == std::string::npos) return B3D_EFORMAT;
+        a.fortran = h.compare(v, 4, "True") == 0;
+    }
     p = h.find("'shape'");
     if (p == std::string::npos) return B3D_EFORMAT;
     const size_t lo = h.find('(', p), hi = h.find(')', p);
@@ -145,8 +156,17 @@ int parse_npy(const std::vector<unsigned char>& raw, NpyArray& a) {
         while (q < hi && (h[q] == ' ' || h[q] == ',')) ++q;
         if (q >= hi) break;
         char* end = nullptr;
-        a.shape.push_back(strtoll(h.c_str() + q, &end, 10));
+        const long long dim = strtoll(h.c_str() + q, &end, 10);
+        if (end == h.c_str() + q || dim < 0) return B3D_EFORMAT;      // not a number / negative dimension
+        a.shape.push_back(dim);
         q = (size_t)(end - h.c_str());
+    }
+    {   // element count must not overflow and must fit the payload
+        unsigned long long cnt = 1;
+        for (long long d : a.shape) {
+            if (d != 0 && cnt > (1ull << 40) / (unsigned long long)d) return B3D_EFORMAT;
+            cnt *= (unsigned long long)d;
+        }
     }
     if (a.word <= 0 || raw.size() - hoff - hlen < a.count() * (size_t)a.word) return B3D_EFORMAT;
     a.data.assign(raw.begin() + (long)(hoff + hlen), raw.begin() + (long)(hoff + hlen + a.count() * (size_t)a.word));
@@ -162,13 +182,20 @@ int npz_get(const char* path, const char* name, NpyArray& a) {
         auto it = idx.find(std::string(name) + ".npy");
         if (it == idx.end()) rc = B3D_ENOFILE;
         else {
-            std::vector<unsigned char> raw;
-            rc = zip_member(f, it->second, raw);
-            if (rc == B3D_OK) rc = parse_npy(raw, a);
+            try {       // nothing may escape through the extern "C" callers
+                std::vector<unsigned char> raw;
+                rc = zip_member(f, it->second, raw);
+                if (rc == B3D_OK) rc = parse_npy(raw, a);
+            } catch (const std::bad_alloc&) {
+                rc = B3D_ENOMEM;
+            } catch (const std::exception&) {
+                rc = B3D_EFORMAT;
+            }
         }
     }
     fclose(f);
     if (rc == B3D_ENOFILE) return set_error(rc, "%s: no array '%s'", path, name);
+    if (rc == B3D_ENOMEM) return set_error(rc, "%s: out of memory reading '%s'", path, name);
     if (rc != B3D_OK) return set_error(rc, "%s: malformed zip / npy data for '%s'", path, name);
     return B3D_OK;
 }

@@ -48,6 +48,7 @@ int b3d_fit_frames(b3d_workspace* ws, const b3d_model* m, const b3d_gmm* gmm, co
     if (!ws || !m || !opts || !kps || !nkp || !R0 || !sim3 || !w || !jointAA) return set_error(B3D_EINVAL, "b3d_fit_frames: null argument");
     if (cloud_dtype != B3D_F32 && cloud_dtype != B3D_F64) return set_error(B3D_EINVAL, "b3d_fit_frames: bad cloud dtype");
     if (B <= 0) return B < 0 ? set_error(B3D_EINVAL, "b3d_fit_frames: B < 0") : B3D_OK;
+    if (int rc = validate_keypoints(kps, nkp, (size_t)B, "b3d_fit_frames")) return rc;
     const size_t nb = (size_t)B, es = cloud_dtype == B3D_F32 ? 4 : 8;
     const size_t s_kp = al256(sizeof(b3d_kp) * nb * MAXKP), s_nk = al256(4 * nb), s_r0 = al256(8 * nb * 9), s_s3 = al256(8 * nb * 7),
                  s_w = al256(8 * nb * NS), s_ja = al256(8 * nb * NJ * 3), s_us = al256(nb), s_ni = al256(4 * nb), s_po = al256(8 * nb * NPF),

@@ -64,6 +64,7 @@ int b3d_fit_sequences(const b3d_model* m, const b3d_fit_opts* base, const b3d_se
     for (int q = 0; q < nseq; ++q)
         if (seq_first[q] < 0 || seq_len[q] <= 0 || seq_first[q] + seq_len[q] > N) return set_error(B3D_EINVAL, "b3d_fit_sequences: sequence %d out of range", q);
     if (int rc = require_device()) return rc;
+    if (int rc = validate_keypoints(kps, nkp, (size_t)N, "b3d_fit_sequences")) return rc;
     const int stride = so->wsize - so->overlap;
     const int G = std::max(1, so->num_shards);
     const size_t n = (size_t)N;

@@ -1,5 +1,7 @@
 // Small per-frame kernels around the solves: the AA -> rotation write-back (include/Sim3BA.h:481-507, 649-679;
 // include/MultiFrameBA.h:154-172) and mean_pixel_error (include/Utils.h:102-115).
+#include <algorithm>
+
 #include "internal.hpp"
 
 namespace b3d {
@@ -60,7 +62,7 @@ __global__ void pixel_error_kernel(int F, const b3d_kp* __restrict__ kps, const 
     double sum = 0.0;
     for (int k = 0; k < n; ++k) {
         const b3d_kp kp = kps[(size_t)f * MAXKP + k];
-        const double* J = jointPos + ((size_t)f * NJ + kp.jid) * 3;
+        const double* J = jointPos + ((size_t)f * NJ + clamp_jid(kp.jid)) * 3;
         const double u = fx * J[0] / J[2] + cx, v = fy * J[1] / J[2] + cy;
         sum += hypot(u - kp.u, v - kp.v);
     }
@@ -70,6 +72,17 @@ __global__ void pixel_error_kernel(int F, const b3d_kp* __restrict__ kps, const 
 __global__ void convert_kernel(const double* __restrict__ src, float* __restrict__ dst, size_t n) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) dst[i] = (float)src[i];
+}
+
+int validate_keypoints(const b3d_kp* kps, const int32_t* nkp, size_t frames, const char* who) {
+    for (size_t f = 0; f < frames; ++f) {
+        const int n = std::min(std::max(nkp[f], 0), MAXKP);
+        for (int k = 0; k < n; ++k) {
+            const int jid = kps[f * MAXKP + k].jid;
+            if (jid < 0 || jid >= NJ) return set_error(B3D_EINVAL, "%s: frame %zu keypoint %d has jid %d (must be in [0, %d))", who, f, k, jid, NJ);
+        }
+    }
+    return B3D_OK;
 }
 
 int b3d_convert_f64_f32_dev(const double* src, float* dst, size_t n, cudaStream_t st) {
@@ -130,6 +143,7 @@ int b3d_mean_pixel_error(int32_t F, const b3d_kp* kps, const int32_t* nkp, const
     if (!kps || !nkp || !jointPos || !err) return set_error(B3D_EINVAL, "b3d_mean_pixel_error: null argument");
     if (F <= 0) return F < 0 ? set_error(B3D_EINVAL, "b3d_mean_pixel_error: F < 0") : B3D_OK;
     const size_t nf = (size_t)F;
+    if (int rc = validate_keypoints(kps, nkp, nf, "b3d_mean_pixel_error")) return rc;
     char* base = nullptr;
     const size_t s_kp = sizeof(b3d_kp) * nf * MAXKP, s_jp = 8 * nf * NJ * 3, s_nk = (4 * nf + 7) / 8 * 8;
     B3D_CUDA(cudaMalloc(&base, s_kp + s_jp + 8 * nf + s_nk));

@@ -60,17 +60,20 @@ def test_forward_tc_matches_sorted_large_batch(api, gmodel, synth):
 
 
 @pytest.mark.parametrize("splits", [1, 5, 24, 54, 108])
-def test_forward_tc_every_split(api, gmodel, synth, splits, monkeypatch):
+def test_forward_tc_every_split(api, gmodel, synth, splits):
     """The tensor-core kernel's CTAs own runs of sort tiles; every cut of the 108 tiles (down to one tile per CTA, where the
     copy / MMA / store pipelines barely fill) must give the same cloud as the CUDA-core kernel, with and without pose blendshapes."""
-    monkeypatch.setenv("B3D_TC_SPLITS", str(splits))
     B = 300
     inp = synth.make_forward_inputs(B, 17 + splits)
-    for pd in (False, True):
-        a, _, _ = api.smpl_forward(gmodel, inp["w"], inp["p"], inp["r"], dtype=np.float32, lbs="tc", posedirs=pd)
-        b, _, _ = api.smpl_forward(gmodel, inp["w"], inp["p"], inp["r"], dtype=np.float32, lbs="generic" if pd else "sorted", posedirs=pd)
-        err = np.max(np.abs(a.astype(np.float64) - b), axis=(1, 2)) / np.max(np.abs(b), axis=(1, 2))
-        assert err.max() < (2e-5 if pd else 2e-6), (splits, pd, err.max())
+    api.lib().b3d_debug_tc_splits(splits)      # debug hook: force the vertex split (0 = automatic)
+    try:
+        for pd in (False, True):
+            a, _, _ = api.smpl_forward(gmodel, inp["w"], inp["p"], inp["r"], dtype=np.float32, lbs="tc", posedirs=pd)
+            b, _, _ = api.smpl_forward(gmodel, inp["w"], inp["p"], inp["r"], dtype=np.float32, lbs="generic" if pd else "sorted", posedirs=pd)
+            err = np.max(np.abs(a.astype(np.float64) - b), axis=(1, 2)) / np.max(np.abs(b), axis=(1, 2))
+            assert err.max() < (2e-5 if pd else 2e-6), (splits, pd, err.max())
+    finally:
+        api.lib().b3d_debug_tc_splits(0)
 
 
 def test_forward_posedirs_extension(api, gmodel, omodel_pd, synth):
