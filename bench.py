@@ -271,6 +271,24 @@ def run_b200(args):
     torch.cuda.synchronize()
     e2e_ms = (time.perf_counter() - t0) * 1e3 / args.steps
     px_err_mean = float(out["px_err"].mean())
+    # the same call with the 6890-vertex cloud returned to the caller as well (the reference's update() leaves it in host memory)
+    out_c = dict(out)
+    out_c["cloud"] = torch.empty(nf, V, 3, dtype=torch.float32).pin_memory().numpy()
+
+    def step_e2e_cloud():
+        h_s3[...] = h_s3_init; h_w[...] = h_w_init
+        api.fit_frames(ws, gm, gg, opts, h_kps, h_nkp, h_R0, h_s3, h_w, out=out_c, cloud_dtype=np.float32, want_cloud=True)
+
+    for _ in range(2):
+        step_e2e_cloud()
+    barrier()
+    t0 = time.perf_counter()
+    nrep_c = max(3, min(args.steps, 10))
+    for _ in range(nrep_c):
+        step_e2e_cloud()
+    torch.cuda.synchronize()
+    e2e_cloud_ms = (time.perf_counter() - t0) * 1e3 / nrep_c
+    d2h_cloud = d2h + out_c["cloud"].nbytes
 
     # roofline of the HBM-bound kernel: float32 forward at a batch whose cloud (5.4 GB at B = 65536) is far larger than L2
     FB = args.forward_batch
@@ -314,12 +332,19 @@ def run_b200(args):
     clk = clocks.stop() if rank == 0 else None
 
     # max over ranks of the device-timed step, the e2e step and the forward
-    tt = torch.tensor([step_ms, e2e_ms, fwd_ms, fit_ms, lbs_ms], dtype=torch.float64, device=dev)
+    tt = torch.tensor([step_ms, e2e_ms, fwd_ms, fit_ms, lbs_ms, e2e_cloud_ms], dtype=torch.float64, device=dev)
     cnt = torch.tensor([float(iters_total), float(usable)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
-    step_ms, e2e_ms, fwd_ms, fit_ms, lbs_ms = [float(x) for x in tt.tolist()]
+    step_ms, e2e_ms, fwd_ms, fit_ms, lbs_ms, e2e_cloud_ms = [float(x) for x in tt.tolist()]
+    # C5 (BASELINE configs[4]) runs on every rank when N > 1: one long 3dba_multi sequence sharded by window, NCCL halo exchange
+    c5 = None
+    if world > 1 and not args.no_c5:
+        try:
+            c5 = c5_leg(args, api, capi, dev, rank, world)
+        except Exception as e:
+            c5 = {"error": str(e)[:300]}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -369,6 +394,19 @@ def run_b200(args):
         except Exception as e:
             icp = {"error": str(e)[:200]}
 
+    # the other BASELINE configs, reported as extra keys beside the headline (C2): C1, C3, the C4 sweep
+    extra = {}
+    if world == 1 and not args.no_extra_legs:
+        for name, fn in (("c1", lambda: c1_leg(api, capi, lib, dev, st, with_cpu=not args.no_cpu_baseline)),
+                         ("c3", lambda: c3_leg(args, api, with_cpu=not args.no_cpu_baseline)),
+                         ("c4_sweep", lambda: c4_sweep_leg(api, capi, lib, gm, dev, st, hbm_peak, with_cpu=not args.no_cpu_baseline))):
+            try:
+                extra[name] = fn()
+            except Exception as e:
+                extra[name] = {"error": str(e)[:300]}
+    if c5 is not None:
+        extra["c5"] = c5
+
     total_frames = nf * world
     line = {
         "metric": "frames_fitted_per_sec", "value": total_frames / (step_ms * 1e-3), "unit": "frames/s", "n_gpus": world, "steps": args.steps,
@@ -380,8 +418,11 @@ def run_b200(args):
                    "l2": "256 MB flush write between timed steps", "cloud_dtype": "f32 (joints/pixel error f64)"},
         "e2e": {"value": total_frames / (e2e_ms * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": e2e_ms, "call": "b3d_fit_frames (host pointers, pinned); cloud computed and left on the device"},
+        "e2e_with_cloud": {"value": total_frames / (e2e_cloud_ms * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": int(h2d),
+                           "d2h_bytes_per_step": int(d2h_cloud), "ms_per_step": e2e_cloud_ms,
+                           "call": "b3d_fit_frames with the float32 cloud (82,680 B per frame) copied back to pinned host memory too"},
         "gpu_launches": launches,
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
+        "roofline": {"bound": "hbm", "dtype": "f32", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak, "traffic": traffic,
                      "kernel": "smpl_lbs_tc_kernel (tcgen05 shape blend + skinning), one launch bracketed by CUDA events "
                                "(b3d_smpl_forward_dev with B3D_FWD_GIVEN_TRANSFORMS); whole_call_* = the same batch through joints + skinning",
                      "ms_per_kernel_launch": lbs_ms, "bytes_per_body": LBS_BYTES_PER_BODY_F32,
@@ -398,6 +439,7 @@ def run_b200(args):
         "clocks": clk,
         "overlay": overlay,
         "icp": icp,
+        **extra,
         "quality": {"usable_frames": int(cnt[1].item()), "mean_lm_iterations": cnt[0].item() / total_frames, "mean_pixel_error_px": px_err_mean},
     }
     print(json.dumps(line))
@@ -539,6 +581,186 @@ def icp_leg(api, capi, lib, synth, model_np, dev, st, with_cpu, nb=4096, base=32
     return out
 
 
+# -------------------------------------------------------------------------------------------------------------
+# the other BASELINE configs (extra keys on the JSON line)
+# -------------------------------------------------------------------------------------------------------------
+C1_KW = dict(mode=0, max_iters=100, beta_pose=20.0, beta_shape=30.0)     # `3dba_single` pose-only, L2 prior, no GMM
+
+
+def c1_leg(api, capi, lib, dev, st, with_cpu, nf=100):
+    """BASELINE configs[0]: 3dba_single pose-only fit, no GMM, 100 synthetic frames: resident fit kernel and the end-to-end
+    b3d_fit_frames call (pinned host buffers); CPU: the oracle on 1 thread (the reference runs frames serially) and OpenMP."""
+    import torch
+    synth = pkg("synth")
+    model_np = synth.make_model()
+    fr = synth.make_frames(model_np, nf, 2000, shape=False)
+    cam = (synth.FX, synth.FY, synth.CX, synth.CY)
+    gm = api.AvatarModel(model_np)
+    opts = api.fit_opts(cam=cam, **C1_KW)
+    ws = api.Workspace()
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+    h_kps = torch.from_numpy(np.ascontiguousarray(fr["kps"]).view(np.uint8).reshape(nf, -1)).pin_memory().numpy().view(capi.KP_DTYPE).reshape(nf, 17)
+    h_nkp, h_R0, h_s3, h_w = pin(fr["nkp"]), pin(fr["R0"]), pin(fr["sim3"]), pin(fr["w"])
+    out = {}
+
+    def step():
+        h_s3[...] = fr["sim3"]; h_w[...] = fr["w"]
+        api.fit_frames(ws, gm, None, opts, h_kps, h_nkp, h_R0, h_s3, h_w, out=out, cloud_dtype=np.float32, want_cloud=False)
+
+    for _ in range(3):
+        step()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    reps = 10
+    for _ in range(reps):
+        step()
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) * 1e3 / reps
+    res = {"workload": "3dba_single pose-only, L2 prior, no GMM, 100 synthetic frames (BASELINE configs[0]); n = 74 free parameters",
+           "frames": nf, "frames_per_sec": nf / (ms * 1e-3), "ms": ms, "timing": "b3d_fit_frames end to end (pinned host buffers, H2D + D2H inside)",
+           "usable_frames": int(out["usable"].sum()), "mean_lm_iterations": float(out["niters"].mean()), "max_lm_iterations": int(out["niters"].max()),
+           "mean_pixel_error_px": float(out["px_err"].mean())}
+    if with_cpu:
+        from oracle import oracle_api as orc
+        om = orc.Model(model_np)
+        o = orc.fit_options(cam=cam, linear_solver=orc.LS_DENSE_QR, use_jets=1, **C1_KW)
+        threads = host_threads()
+        base = {}
+        for name, th, n in (("one_thread", 1, min(nf, 24)), ("openmp", threads, nf)):
+            t0 = time.perf_counter()
+            om.fit_single(None, o, fr["kps"][:n], fr["nkp"][:n], fr["R0"][:n], fr["sim3"][:n], fr["w"][:n], nthreads=th, want_trace=False)
+            dt = time.perf_counter() - t0
+            base[name] = {"value": n / dt, "unit": "frames/s", "cores": th, "kind": "port",
+                          "sample": f"first {n} of the {nf} frames, oracle (dense QR + Jet autodiff), fit only, {dt:.2f} s"}
+        res["cpu_baseline"] = base["openmp"]
+        res["cpu_baseline_one_thread"] = base["one_thread"]
+    return res
+
+
+def c3_leg(args, api, with_cpu):
+    """BASELINE configs[2]: 3dba_multi on ONE sequence of 2,000 synthetic frames with the reference's schedule and caps
+    (anchor_skip 10, window 20, overlap 5, lambda 3, it1 = 1000, 60 iterations per window, beta_shape_lock 1e5) through
+    b3d_fit_sequence(s) with host pointers.  Stage 2 is a serial chain of windows by definition (num_shards = 1)."""
+    import torch
+    synth = pkg("synth")
+    model_np = synth.make_model()
+    n = args.c3_frames
+    seq = synth.make_sequence(model_np, n, 31)
+    cam = (synth.FX, synth.FY, synth.CX, synth.CY)
+    gm = api.AvatarModel(model_np)
+    base = api.fit_opts(cam=cam)
+    so = api.seq_opts(skip=10, wsize=20, overlap=5, it1=1000, it2=60, num_shards=1, beta_pose=20.0, beta_shape=30.0, lambda_temp=3.0)
+    warm = min(n, 120)
+    api.fit_sequences(gm, base, so, seq["kps"][:warm], seq["nkp"][:warm], seq["poses"][:warm], seq["R0"][:warm], seq["W"][:warm])
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    g = api.fit_sequences(gm, base, so, seq["kps"], seq["nkp"], seq["poses"], seq["R0"], seq["W"])
+    dt = time.perf_counter() - t0
+    it = g["solve_iters"]
+    nwin = len(range(0, n, so.wsize - so.overlap))
+    res = {"workload": f"3dba_multi, one sequence of {n} synthetic frames: anchor_skip 10, window 20, overlap 5, lambda_temp 3, it1 1000, it2 60 "
+                       "(BASELINE configs[2]); exact serial window chain (num_shards = 1)",
+           "frames": n, "frames_per_sec": n / dt, "ms": dt * 1e3, "timing": "b3d_fit_sequences, host pointers in and out, wall clock, one run after a 120-frame warm-up",
+           "anchors": len(range(0, n, 10)), "windows": nwin, "stage1_lm_iterations": int(it[0]), "window_lm_iterations_mean": float(it[1:1 + nwin].mean()),
+           "window_lm_iterations_max": int(it[1:1 + nwin].max()), "failed_solves": int(g["nfail"])}
+    if with_cpu:
+        from oracle import oracle_api as orc
+        om = orc.Model(model_np)
+        threads = host_threads()
+        ns = min(n, 200)      # bounded sample: the structured oracle does ~15 frames/s on one core
+        t0 = time.perf_counter()
+        o = om.fit_sequence(orc.fit_options(mode=1, cam=cam, use_jets=0), orc.SeqOptions(10, 20, 5, 1000, 60, 1, threads, 0, 20.0, 30.0, 3.0, 1e5),
+                            seq["kps"][:ns], seq["nkp"][:ns], seq["poses"][:ns], seq["R0"][:ns], seq["W"][:ns])
+        dts = time.perf_counter() - t0
+        res["cpu_baseline"] = {"value": ns / dts, "unit": "frames/s", "cores": threads, "kind": "port",
+                               "sample": f"first {ns} frames as their own sequence, oracle with the structured (block-tridiagonal + arrowhead) solver and "
+                                         f"analytic Jacobians — NOT what the reference does; {dts:.1f} s"}
+        # reference-style: dense QR on the stacked Jacobian with Jet autodiff (what DENSE_QR + DynamicAutoDiff do); one 20-frame
+        # window is 3,495 x 1,530 -> time-boxed to a few iterations of one window and extrapolated per iteration
+        F, iters = 20, 2
+        kw = dict(max_iters=iters, beta_pose=20.0, beta_shape=1e5, lambda_temp=3.0)
+        t0 = time.perf_counter()
+        o2 = om.fit_window(orc.fit_options(mode=1, cam=cam, linear_solver=orc.LS_DENSE_QR, use_jets=1, **kw),
+                           seq["kps"][:F], seq["nkp"][:F], seq["R0"][:F], seq["poses"][:F], seq["W"][0])
+        dtq = time.perf_counter() - t0
+        per_iter = dtq / max(o2["niters"] - 1, 1)
+        mean_it = float(it[1:1 + nwin].mean())
+        res["cpu_baseline_dense_qr"] = {"seconds_per_window_iteration": per_iter, "cores": 1, "kind": "port",
+                                        "sample": f"{o2['niters'] - 1} LM iterations of one 20-frame window (3,495 x 1,530 dense Householder QR + Jets), {dtq:.1f} s",
+                                        "extrapolated_frames_per_sec_stage2_only": n / (per_iter * mean_it * nwin),
+                                        "note": "stage 1 in the reference's dense form is a 35,535 x 15,210 QR per iteration: infeasible, not timed"}
+    return res
+
+
+def c4_sweep_leg(api, capi, lib, gm, dev, st, hbm_peak, with_cpu):
+    """BASELINE configs[3]: batched SMPL forward (shape blend + joints + LBS, no solver) for B = 1 .. 65,536, float32 (tile-sorted
+    CUDA-core kernel below 512 bodies, tcgen05 kernel from 512 on) and float64 (what a drop-in caller of the shim gets)."""
+    import torch
+    synth = pkg("synth")
+    V = gm.numPoints
+    P = lambda t: C.c_void_p(t.data_ptr())
+    BMAX = 65536
+    fin = synth.make_forward_inputs(BMAX, 5)
+    rows = []
+    for dtype, code, td, bpb in (("f32", capi.F32, torch.float32, FWD_BYTES_PER_BODY_F32), ("f64", capi.F64, torch.float64, 2 * FWD_BYTES_PER_BODY_F32)):
+        w, p, r = [torch.from_numpy(np.ascontiguousarray(fin[k])).to(td).to(dev) for k in ("w", "p", "r")]
+        cloud = torch.empty(BMAX, V, 3, dtype=td, device=dev)
+        jp, jt = torch.empty(BMAX, 24, 3, dtype=td, device=dev), torch.empty(BMAX, 24, 12, dtype=td, device=dev)
+        B = 1
+        while B <= BMAX:
+            run = lambda: capi.check(lib.b3d_smpl_forward_dev(gm.h, B, code, P(w), P(p), P(r), P(cloud), P(jp), P(jt), 0, C.c_void_p(st)), "c4 sweep")
+            for _ in range(3):
+                run()
+            torch.cuda.synchronize()
+            reps = 20 if B <= 4096 else 8
+            evs = []
+            for _ in range(reps):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); run(); e1.record()
+                evs.append((e0, e1))
+            torch.cuda.synchronize()
+            ms = float(np.median([a.elapsed_time(b) for a, b in evs]))
+            gbs = B * bpb / (ms * 1e-3) / 1e9
+            rows.append({"B": B, "dtype": dtype, "ms": ms, "verts_per_sec": B * V / (ms * 1e-3), "gbs": gbs, "frac_hbm": gbs / hbm_peak,
+                         "path": ("tcgen05 shape blend + skinning" if (dtype == "f32" and B >= 512) else "CUDA-core tile-sorted" if dtype == "f32" else "generic float64")})
+            B *= 2
+        del cloud, w, p, r
+        torch.cuda.empty_cache()
+    res = {"workload": "batched SMPL forward sweep B = 1 .. 65,536 (BASELINE configs[3]): whole b3d_smpl_forward_dev call (joints + skinning), inputs resident; "
+                       "outputs of batches below ~1,500 bodies (f32) fit the 126 MB L2 and are not flushed between repetitions",
+           "bytes_per_body_f32": FWD_BYTES_PER_BODY_F32, "bytes_per_body_f64": 2 * FWD_BYTES_PER_BODY_F32, "rows": rows}
+    if with_cpu:
+        from oracle import oracle_api as orc
+        synth_model = synth.make_model()
+        om = orc.Model(synth_model)
+        threads = host_threads()
+        base = {}
+        for name, th, nb in (("one_thread", 1, 64), ("openmp", threads, 64 * threads)):
+            t0 = time.perf_counter()
+            om.forward(fin["w"][:nb], fin["p"][:nb], fin["r"][:nb], nthreads=th)
+            dt = time.perf_counter() - t0
+            base[name] = {"value": nb * V / dt, "unit": "verts/s", "cores": th, "kind": "port", "sample": f"{nb} bodies, oracle update() (float64), {dt:.2f} s"}
+        res["cpu_baseline"] = base["openmp"]
+        res["cpu_baseline_one_thread"] = base["one_thread"]
+    return res
+
+
+def c5_leg(args, api, capi, dev, rank, world):
+    """BASELINE configs[4]: 3dba_multi on ONE sequence of 100,000 synthetic frames, windows sharded over the ranks (sharded schedule
+    of DESIGN 5), OVERLAP x 85 doubles exchanged between neighbouring shards over NCCL.  Every rank runs this."""
+    import torch
+    import torch.distributed as dist
+    synth, D = pkg("synth"), pkg("dist")
+    model_np = synth.make_model()
+    n = args.c5_frames
+    seq = synth.make_sequence_fast(model_np, n, 77)
+    cam = (synth.FX, synth.FY, synth.CX, synth.CY)
+    gm = api.AvatarModel(model_np)
+    base = api.fit_opts(cam=cam)
+    so = api.seq_opts(skip=10, wsize=20, overlap=5, it1=1000, it2=60, num_shards=world, beta_pose=20.0, beta_shape=30.0, lambda_temp=3.0)
+    return D.bench_c5(api, gm, base, so, seq, dev, rank, world)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -548,6 +770,10 @@ def main():
     ap.add_argument("--frames", type=int, default=FRAMES_PER_GPU, help="frames per GPU per step")
     ap.add_argument("--forward-batch", type=int, default=65536)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra-legs", action="store_true", help="skip the C1 / C3 / C4-sweep legs (N = 1)")
+    ap.add_argument("--no-c5", action="store_true", help="skip the C5 leg (N > 1)")
+    ap.add_argument("--c3-frames", type=int, default=2000)
+    ap.add_argument("--c5-frames", type=int, default=100000)
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

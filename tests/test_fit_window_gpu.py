@@ -127,3 +127,30 @@ def test_dist_driver_equals_library_schedule(api, gmodel, synth, model_np, shard
     for k in ("poses", "R0", "W", "p"):
         assert np.array_equal(out[k].cpu().numpy(), g[k].reshape(out[k].shape)), k
     assert np.array_equal(out["r"].cpu().numpy().reshape(n, 24, 9), g["r"])
+
+
+def test_c3_at_stated_size_vs_committed_oracle_result(api, gmodel, synth, model_np, capsys):
+    """BASELINE configs[2] at its stated size: 2,000 frames, anchor_skip 10, window 20, overlap 5, lambda 3, it1 = 1000, it2 = 60
+    (the reference's caps) through b3d_fit_sequences, against the oracle's result for the same sequence committed as
+    tests/golden/c3_oracle_2000.npz (generated by tools/make_c3_golden.py; the oracle needs ~35 s on 8 cores for it)."""
+    import os
+    from conftest import GOLDEN
+    ref = np.load(os.path.join(GOLDEN, "c3_oracle_2000.npz"))
+    n = ref["poses"].shape[0]
+    seq = synth.make_sequence(model_np, n, int(ref["seed"]))
+    cam = (synth.FX, synth.FY, synth.CX, synth.CY)
+    so = api.seq_opts(skip=10, wsize=20, overlap=5, it1=int(ref["it1"]), it2=int(ref["it2"]), num_shards=1, beta_pose=20.0, beta_shape=30.0, lambda_temp=3.0)
+    g = api.fit_sequences(gmodel, api.fit_opts(cam=cam), so, seq["kps"], seq["nkp"], seq["poses"], seq["R0"], seq["W"])
+    nsolve = 1 + len(range(0, n, 15))
+    gi, oi = g["solve_iters"][:nsolve], ref["win_iters"][:nsolve]
+    dev = dict(raa=float(np.max(np.abs(g["poses"][:, 1:4] - ref["poses"][:, 1:4]))), jaa=float(np.max(np.abs(g["poses"][:, 7:] - ref["poses"][:, 7:]))),
+               t_over_s=float(np.max(np.abs(g["poses"][:, 4:7] / g["poses"][:, :1] - ref["poses"][:, 4:7] / ref["poses"][:, :1]))),
+               W=float(np.max(np.abs(g["W"] - ref["W"]))), R0=float(np.max(np.abs(g["R0"] - ref["R0"]))),
+               scale=float(np.max(np.abs(g["poses"][:, 0] - ref["poses"][:, 0]))))
+    with capsys.disabled():
+        print(f"\n[C3 x {n}] stage-1 iterations gpu {gi[0]} oracle {oi[0]}; windows with equal iteration count {int(np.sum(gi[1:] == oi[1:]))} of {nsolve - 1}; "
+              f"worst deviations {dev}")
+    assert g["nfail"] == int(ref["nfail"]) == 0
+    assert dev["raa"] < PARAM_TOL and dev["jaa"] < PARAM_TOL and dev["R0"] < PARAM_TOL
+    assert dev["t_over_s"] < 5e-3 and dev["W"] < 1e-2
+    assert np.mean(gi[1:] == oi[1:]) > 0.8 and abs(int(gi[0]) - int(oi[0])) <= 2

@@ -155,3 +155,31 @@ def test_forward_given_transforms_reskins_identically(synth, model_np):
         capi.check(capi.lib().b3d_smpl_forward(gm.h, b, capi.F32, capi.ptr(w), capi.ptr(junk), capi.ptr(junk), capi.ptr(again), None,
                                                capi.ptr(jt), 0x100), "given transforms")
         assert np.array_equal(again, cloud)
+
+
+def test_forward_at_roofline_batch_vs_oracle_sample(api, gmodel, omodel, synth):
+    """The batch the roofline is quoted on (B = 65,536, float32, tensor-core kernel): 64 bodies spread over the batch (first and last
+    body group, group edges, odd rows) against the oracle evaluated on the float32-rounded inputs; 1e-5 relative per body."""
+    import ctypes as C
+    import torch
+    B = 65536
+    capi, lib = api.capi, api.lib()
+    inp = synth.make_forward_inputs(B, 5)
+    dev = torch.device("cuda", 0)
+    w, p, r = [torch.from_numpy(np.ascontiguousarray(inp[k], dtype=np.float32)).to(dev) for k in ("w", "p", "r")]
+    cloud = torch.empty(B, gmodel.numPoints, 3, dtype=torch.float32, device=dev)
+    jp, jt = torch.empty(B, 24, 3, dtype=torch.float32, device=dev), torch.empty(B, 24, 12, dtype=torch.float32, device=dev)
+    P = lambda t: C.c_void_p(t.data_ptr())
+    capi.check(lib.b3d_smpl_forward_dev(gmodel.h, B, capi.F32, P(w), P(p), P(r), P(cloud), P(jp), P(jt), 0,
+                                        C.c_void_p(torch.cuda.current_stream().cuda_stream)), "forward 65536")
+    torch.cuda.synchronize()
+    rng = np.random.default_rng(1)
+    pick = np.unique(np.concatenate([[0, 1, 127, 128, 129, 32767, 32768, B - 129, B - 128, B - 1], rng.integers(0, B, 54)]))
+    f32 = lambda a: np.asarray(a, dtype=np.float32).astype(np.float64)
+    c0, jp0, jt0 = omodel.forward(f32(inp["w"][pick]), f32(inp["p"][pick]), f32(inp["r"][pick]), nthreads=8)
+    idx = torch.from_numpy(pick).to(dev)
+    c = cloud.index_select(0, idx).cpu().numpy().astype(np.float64)
+    err = np.max(np.abs(c - c0), axis=(1, 2)) / np.max(np.abs(c0), axis=(1, 2))
+    assert err.max() < 1e-5, (err.max(), pick[int(np.argmax(err))])
+    assert rel_err(jp.index_select(0, idx).cpu().numpy(), jp0) < 1e-5
+    assert rel_err(jt.index_select(0, idx).cpu().numpy(), jt0) < 1e-5

@@ -58,6 +58,35 @@ __global__ void sqrt_div_latency(double* out, long long* cyc, int n) {
     out[3] = a; if (threadIdx.x == 0) cyc[0] = t1 - t0;
 }
 
+__global__ void rsqrt_latency(double* out, long long* cyc, int n) {
+    double a = out[0] + 2.0;
+    long long t0 = clock64();
+    for (int i = 0; i < n; ++i) { a = rsqrt(a) + 1.5; }
+    long long t1 = clock64();
+    out[3] = a; if (threadIdx.x == 0) cyc[0] = t1 - t0;
+}
+__global__ void rcp_latency(double* out, long long* cyc, int n) {
+    double a = out[0] + 2.0;
+    long long t0 = clock64();
+    for (int i = 0; i < n; ++i) { a = 1.0 / a + 1.5; }
+    long long t1 = clock64();
+    out[3] = a; if (threadIdx.x == 0) cyc[0] = t1 - t0;
+}
+__global__ void shfl_latency(double* out, long long* cyc, int n) {
+    double a = out[0] + threadIdx.x;
+    long long t0 = clock64();
+    for (int i = 0; i < n; ++i) { a = __shfl_sync(0xffffffffu, a, (threadIdx.x + 1) & 31); }
+    long long t1 = clock64();
+    out[3 + threadIdx.x] = a; if (threadIdx.x == 0) cyc[0] = t1 - t0;
+}
+__global__ void sincos_latency(double* out, long long* cyc, int n) {
+    double a = out[0] + 0.3;
+    long long t0 = clock64();
+    for (int i = 0; i < n; ++i) { double s, c; sincos(a, &s, &c); a = s + c; }
+    long long t1 = clock64();
+    out[3] = a; if (threadIdx.x == 0) cyc[0] = t1 - t0;
+}
+
 int main() {
     double* d; float* f; long long* c; long long h;
     cudaMalloc(&d, 8 * 4096); cudaMalloc(&f, 4 * 4096); cudaMalloc(&c, 8);
@@ -82,6 +111,14 @@ int main() {
     }
     sqrt_div_latency<<<1, 32>>>(d, c, n); cudaMemcpy(&h, c, 8, cudaMemcpyDeviceToHost);
     printf("1/sqrt(x) fp64 dependent: %.1f cycles\n", (double)h / n);
+    rsqrt_latency<<<1, 32>>>(d, c, n); cudaMemcpy(&h, c, 8, cudaMemcpyDeviceToHost);
+    printf("rsqrt(x) + add fp64 dependent: %.1f cycles\n", (double)h / n);
+    rcp_latency<<<1, 32>>>(d, c, n); cudaMemcpy(&h, c, 8, cudaMemcpyDeviceToHost);
+    printf("1/x + add fp64 dependent: %.1f cycles\n", (double)h / n);
+    shfl_latency<<<1, 32>>>(d, c, n); cudaMemcpy(&h, c, 8, cudaMemcpyDeviceToHost);
+    printf("shfl (64-bit) dependent: %.1f cycles\n", (double)h / n);
+    sincos_latency<<<1, 32>>>(d, c, n); cudaMemcpy(&h, c, 8, cudaMemcpyDeviceToHost);
+    printf("sincos fp64 + add dependent: %.1f cycles\n", (double)h / n);
     printf("%s\n", cudaGetErrorString(cudaDeviceSynchronize()));
     return 0;
 }
