@@ -13,10 +13,13 @@
 // (Sim3BA.h:245-320: GMM min-component with the reference's Jacobian that omits sqrt(1/2), or L2), shape prior
 // ShapePriorL2Analytic (Sim3BA.h:323-346).
 //
-// The kernel is latency-bound (one frame's iterations are a serial chain), so the layout aims at few barriers and short
-// dependent chains: J^T J is assembled by element owners walking a per-column keypoint bitmask (no per-keypoint phases),
-// the Cholesky keeps running diagonals in registers and splits each row's dot product over a thread pair (one barrier per
-// column), and the scaled normal equations stay in shared memory across rejected steps.
+// The kernel is latency-bound (one frame's iterations are a serial chain), so the layout aims at few barriers, short dependent
+// chains and little shared-memory traffic.  A thread owns one 4 x 4 tile (ti, tj) of the lower triangle of the (<= 88 x 88)
+// system for the whole solve: the reprojection Jacobian is kept dense ([34][88], lm_device.cuh eval_reproj_dense), so J^T J is a
+// SYRK over register tiles; the Cholesky is right-looking with the matrix held IN REGISTERS (one tile per thread): per 4-column
+// panel the owner of the diagonal tile factors it, the tile column solves against it and publishes its rows ([4][88] doubles), and
+// every trailing tile subtracts the rank-4 product of two 4 x 4 row groups — two barriers per panel, no read-modify-write of the
+// matrix in shared memory.  The scaled normal equations stay in shared memory (packed) across rejected steps.
 #include "lm_device.cuh"
 #include "ls_poly.cuh"
 
@@ -39,11 +42,17 @@ __device__ long long g_phase_cycles[32];
 __device__ long long g_block_cycles[1024];   // total cycles and line-search evaluations per block (debug)
 __device__ int g_block_ls[1024];
 __device__ int g_phase_on;
+// Cycles accumulate in shared memory (a global read-modify-write per mark would stall the timing thread for an L2 round trip and,
+// through the next barrier, the whole block); the kernel adds them to g_phase_cycles once at its end.
+__device__ __forceinline__ long long* phase_acc() {
+    __shared__ long long s_phase[32];
+    return s_phase;
+}
 struct PhaseTimer {
     long long t;
     bool on;
     __device__ void start() { on = g_phase_on != 0 && blockIdx.x == 0 && threadIdx.x == 0; if (on) t = clock64(); }
-    __device__ void mark(int i) { if (on) { const long long u = clock64(); g_phase_cycles[i] += u - t; t = u; } }
+    __device__ void mark(int i) { if (on) { const long long u = clock64(); phase_acc()[i] += u - t; t = u; } }
 };
 
 struct GmmTmp {
@@ -57,12 +66,19 @@ struct GmmTmp {
 union SingleUnion {
     EvalTmp ev;
     GmmTmp gm;
-    double L[LTRI];               // damped system being factored, last row = right-hand side
+    double L[LTRI];               // Cholesky factor (strict lower part) + the forward-substituted right-hand side as last row
 };
 
+constexpr int NTILE = 22;                  // 4-wide tile rows / columns of the augmented system (87 rows -> 22, 86 columns -> 22)
+static_assert(NFULL + 1 <= 4 * NTILE && NTILE * (NTILE + 1) / 2 <= FS_THREADS, "one 4 x 4 tile of the lower triangle per thread");
+
 struct SingleSmem {
-    EvalOut out;
+    EvalDense out;
     SingleUnion u;
+    alignas(16) double2 pan[4][2][NTILE];  // the current panel's solved rows (Cholesky): [panel column][rows 0-1 | rows 2-3 of a tile][tile row]
+    double dk[2][4][4];                    // diagonal tiles (by panel parity): strict lower part = L, diagonal = 1 / L_jj
+    double damp[NFULL];                    // D^2 / radius of the current step
+    int32_t chol_fail;
     double Hs[HTRI];                       // Jacobi-scaled J^T J (free layout, packed lower), kept across rejected steps
     double xfull[NFULL], cfull[NFULL];     // current / candidate parameters, 86-layout
     double g[NFULL], gs[NFULL], gc[NFULL]; // gradient (free layout): unscaled, Jacobi-scaled, saved copy during a line search
@@ -70,12 +86,9 @@ struct SingleSmem {
     double gpri[NPRI];                     // pose-prior gradient, pose-dim layout
     double R0[9];
     double red[40];
-    double piv[2];                         // pivot of the next Cholesky column: value, 1/sqrt
     double ls_step;
     int32_t comp;
-    uint32_t kmask[NFULL];                 // per full-layout column: keypoints whose Jacobian touches it
-    uint8_t slot[MAXKP][NFULL + 2];        // per keypoint: local slot of each full-layout column
-    int8_t fcol[MAXKP][NNZPAD];            // per keypoint slot: free-layout column, -1 = held constant
+    int32_t fidx[NFULL + 2];               // free -> full column (copy of FitConst::free_idx: read on every pass over the system)
 };
 
 // ---- GMM pose prior (GaussianMixture::residual, external/avatar/GaussianMixture.cpp:94-113) --------------------
@@ -180,14 +193,15 @@ __device__ double gmm_eval(const FitConst* __restrict__ C, const double* xj /*69
 // MODE 0: cost only.  MODE 1: cost + normal equations (S.Hs, S.g).  MODE 2: cost + gradient only, into S.gc — what the
 // Armijo line search needs at its trial points; S.Hs / S.g / S.gs of the current iterate stay untouched.  The gradient entries
 // are accumulated in the same order as in MODE 1, so both give the same bits.
+// (ti, tj): this thread's 4 x 4 tile of the lower triangle (tile_ok: it exists for this problem size).
 template <int T, int MODE>
 __device__ __noinline__ double evaluate(const FitConst* __restrict__ C, const double* xf, const b3d_kp* __restrict__ kps, int nkp, SingleSmem& S,
-                           bool first) {
+                           bool first, int ti, int tj, bool tile_ok) {
     constexpr bool JAC = MODE != 0;
     const int tid = threadIdx.x, n = C->n;
     PhaseTimer pe;
     pe.start();
-    eval_reproj<T, JAC>(C, xf, kps, nkp, S.R0, S.u.ev, S.out);
+    eval_reproj_dense<T, JAC>(C, xf, kps, nkp, S.R0, S.u.ev, S.out);
     pe.mark(JAC ? 9 : 12);
     double cost = 0.0;
     for (int k = 0; k < nkp; ++k) cost += S.out.kcost[k];
@@ -201,37 +215,20 @@ __device__ __noinline__ double evaluate(const FitConst* __restrict__ C, const do
         for (int k = tid; k < NPRI; k += T) { const double r = xf[IDX_JAA + k] * C->beta_pose; v += 0.5 * r * r; }
     if (C->has_w)
         for (int k = tid; k < NS; k += T) { const double r = xf[IDX_W + k] * C->beta_shape; v += 0.5 * r * r; }
-    if (JAC) {   // column -> keypoint tables for the assembly below (published by the barriers inside block_sum)
-        for (int k = tid; k < NFULL; k += T) S.kmask[k] = 0u;
-    }
     cost += pcost + block_sum<T>(v, S.red);
     pe.mark(JAC ? 10 : 13);
     if (!JAC) return cost;
 
-    for (int t = tid; t < nkp * NNZPAD; t += T) {
-        const int k = t / NNZPAD, sl = t % NNZPAD;
-        if (sl < S.out.jnnz[k]) {
-            const int col = S.out.jcol[k][sl];
-            S.slot[k][col] = (uint8_t)sl;
-            S.fcol[k][sl] = (int8_t)C->col_of[col];
-            atomicOr(&S.kmask[col], 1u << k);
-        }
-    }
-    __syncthreads();
     const double bp2 = C->beta_pose * C->beta_pose, bs2 = C->beta_shape * C->beta_shape;
-    // ---- gradient J^T r: thread i sums the keypoints that touch column i in keypoint order, then the priors ----
+    const int nrow = 2 * nkp;
+    // ---- gradient J^T r: thread i sums column i of the dense Jacobian in row (= keypoint) order, then the priors ----
     {
         double* gdst = MODE == 2 ? S.gc : S.g;
         for (int i = tid; i < n; i += T) {
-            const int a = C->free_idx[i];
-            uint32_t m = S.kmask[a];
+            const int a = S.fidx[i];
             double gacc = 0.0;
-            while (m) {
-                const int k = __ffs(m) - 1;
-                m &= m - 1;
-                const int sa = S.slot[k][a];
-                gacc += S.out.J[k][0][sa] * S.out.res[k][0] + S.out.J[k][1][sa] * S.out.res[k][1];
-            }
+            for (int r = 0; r < nrow; r += 2)
+                gacc += S.out.J[r][jpos(i)] * S.out.res[r >> 1][0] + S.out.J[r + 1][jpos(i)] * S.out.res[r >> 1][1];
             if (pose_prior && a >= IDX_JAA && a < IDX_W) gacc += gmm ? S.gpri[a - IDX_JAA] : bp2 * xf[a];
             if (C->has_w && a >= IDX_W) gacc += bs2 * xf[a];
             gdst[i] = gacc;
@@ -241,55 +238,56 @@ __device__ __noinline__ double evaluate(const FitConst* __restrict__ C, const do
         __syncthreads();
         return cost;
     }
-    // ---- J^T J: a thread owns element (i, j) of the packed lower triangle and sums, in keypoint order and in a register, the
-    // keypoints whose Jacobian touches both columns; then the prior term and the Jacobi scaling, one store per element.  Four
-    // elements per pass, so that the four loads of the GMM precision matrix (L2) are in flight while the keypoints are walked. ----
-    {
-        const double* __restrict__ P = gmm ? C->gmm_P + (size_t)S.comp * NPRI * NPRI : nullptr;
-        const int ne = n * (n + 1) / 2;
-        for (int e0 = tid; e0 < ne; e0 += 4 * T) {
-            int ei[4], ej[4];
-            double pri[4], acc[4];
+    // ---- J^T J: SYRK over the thread's 4 x 4 register tile, then the prior term and the Jacobi scaling, one store per element.
+    // The 16 entries of the GMM precision matrix (L2) are requested first, so that their latency hides behind the SYRK. ----
+    if (tile_ok) {
+        double pri[4][4];
+        int fa[4], fb[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const int e = e0 + u * T;
-                int i = (int)((sqrtf(8.0f * (float)e + 1.0f) - 1.0f) * 0.5f);
-                while ((i + 1) * (i + 2) / 2 <= e) ++i;
-                while (i * (i + 1) / 2 > e) --i;
-                ei[u] = i; ej[u] = e - i * (i + 1) / 2;
-                pri[u] = 0.0;
-                if (e < ne) {
-                    const int a = C->free_idx[i], b = C->free_idx[ej[u]];
-                    if (pose_prior && a >= IDX_JAA && a < IDX_W && b >= IDX_JAA) {
-                        if (gmm) pri[u] = bp2 * __ldg(P + (a - IDX_JAA) * NPRI + (b - IDX_JAA));
-                        else if (a == b) pri[u] = bp2;
+        for (int a = 0; a < 4; ++a) { fa[a] = S.fidx[4 * ti + a]; fb[a] = S.fidx[4 * tj + a]; }   // NFULL + 1 beyond the last column
+        {
+            const double* __restrict__ P = gmm ? C->gmm_P + (size_t)S.comp * NPRI * NPRI : nullptr;
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) {
+                    const bool in_pose = fa[a] >= IDX_JAA && fa[a] < IDX_W && fb[b] >= IDX_JAA && fb[b] < IDX_W;
+                    double v2 = 0.0;
+                    if (pose_prior && in_pose) {
+                        if (gmm) v2 = bp2 * __ldg(P + (fa[a] - IDX_JAA) * NPRI + (fb[b] - IDX_JAA));
+                        else if (fa[a] == fb[b]) v2 = bp2;
                     }
+                    if (C->has_w && fa[a] >= IDX_W && fa[a] <= NFULL - 1 && fa[a] == fb[b]) v2 += bs2;
+                    pri[a][b] = v2;
                 }
-            }
+        }
+        double acc[4][4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                acc[u] = 0.0;
-                if (e0 + u * T < ne) {
-                    const int a = C->free_idx[ei[u]], b = C->free_idx[ej[u]];
-                    uint32_t m = S.kmask[a] & S.kmask[b];
-                    while (m) {
-                        const int k = __ffs(m) - 1;
-                        m &= m - 1;
-                        const int sa = S.slot[k][a], sb = S.slot[k][b];
-                        acc[u] += S.out.J[k][0][sa] * S.out.J[k][0][sb] + S.out.J[k][1][sa] * S.out.J[k][1][sb];
-                    }
-                }
-            }
+        for (int a = 0; a < 4; ++a)
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const int e = e0 + u * T;
-                if (e < ne) {
-                    const int i = ei[u], j = ej[u];
-                    const int a = C->free_idx[i], b = C->free_idx[j];
-                    double v2 = acc[u];
-                    if (pose_prior && a >= IDX_JAA && a < IDX_W && b >= IDX_JAA && (gmm || a == b)) v2 += pri[u];
-                    if (C->has_w && a >= IDX_W && a == b) v2 += bs2;
-                    S.Hs[e] = first ? v2 : v2 * S.scale[i] * S.scale[j];
+            for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+        const double2* Ja = reinterpret_cast<const double2*>(&S.out.J[0][0]) + ti;     // row layout: lm_device.cuh jpos()
+        const double2* Jb = reinterpret_cast<const double2*>(&S.out.J[0][0]) + tj;
+#pragma unroll 2
+        for (int r = 0; r < nrow; ++r) {
+            const double2 x01 = Ja[r * (LDJ / 2)], x23 = Ja[r * (LDJ / 2) + LDJ / 4];
+            const double2 y01 = Jb[r * (LDJ / 2)], y23 = Jb[r * (LDJ / 2) + LDJ / 4];
+            const double xv[4] = {x01.x, x01.y, x23.x, x23.y}, yv[4] = {y01.x, y01.y, y23.x, y23.y};
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) acc[a][b] = fma(xv[a], yv[b], acc[a][b]);
+        }
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            const int i = 4 * ti + a;
+            const double si = (first || i >= n) ? 1.0 : S.scale[i];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) {
+                const int j = 4 * tj + b;
+                if (i < n && j <= i) {
+                    const double v2 = acc[a][b] + pri[a][b];
+                    S.Hs[tri(i, j)] = first ? v2 : v2 * si * S.scale[j];
                 }
             }
         }
@@ -299,122 +297,183 @@ __device__ __noinline__ double evaluate(const FitConst* __restrict__ C, const do
     return cost;
 }
 
-// Cholesky of the damped system in S.u.L, packed lower, (n + 1) rows: the last row is the right-hand side, so on return it
-// holds z = L^-1 rhs.  Blocked left-looking, 4 columns per panel, 2 barriers per panel (44 instead of one per column):
-//   update   the thread pair of row p subtracts sum_{q < j0} L[p][q] L[c][q] from its entries of the panel's columns c — the
-//            four dot products share the loads of row p and the two halves of the pair split q;
-//   factor   every row thread factors the (updated) 4 x 4 diagonal block redundantly in registers — the same arithmetic in
-//            every thread, hence the same bits — and solves its own row against it.
-// Returns false when a pivot is not positive (Eigen LLT / oracle criterion).  1 / L_jj goes to S.invd.
+// Cholesky of the damped system (H_s + D^2 / radius) with the right-hand side gs as an extra row, the matrix held in registers:
+// thread (ti, tj) owns rows 4 ti .. 4 ti + 3, columns 4 tj .. 4 tj + 3 of the lower triangle (row n = right-hand side, rows > n
+// and columns >= n are zero padding).  Right-looking over 4-column panels; per panel
+//   factor   the owner of the diagonal tile factors it in registers and publishes it (S.dk: L below the diagonal, 1 / L_jj on it);
+//   solve    the tiles below it solve their rows against it and publish them as S.pan[column][row];
+//   update   every tile to the right subtracts (its rows of the panel) x (its columns' rows of the panel)^T.
+// The factorisation of diagonal tile k + 1 is folded into the update phase of panel k: two barriers per panel.
+// On return (true) S.u.L holds the strict lower part of L and, as row n, z = L^-1 gs; 1 / L_jj is in S.invd.  Returns false when a
+// pivot is not positive (Eigen LLT / oracle criterion).
 template <int T>
-__device__ bool chol_factor_aug(SingleSmem& S, int n) {
-    static_assert(T >= 2 * NAUG, "one thread pair per row");
-    constexpr int PW = 4;
-    double* A = S.u.L;
-    const int tid = threadIdx.x, p = tid >> 1, half = tid & 1, np = n + 1;
-    bool ok = true;
-    for (int j0 = 0; j0 < n; j0 += PW) {
-        const int w = min(PW, n - j0);
-        const bool active = p >= j0 && p < np;
-        double* ri = A + tri(active ? p : 0, 0);
-        // ---- update ----
-        if (j0 > 0) {
-            double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-            if (active) {
-                const double* r0 = A + tri(j0, 0);
-                const double* r1 = A + tri(min(j0 + 1, n - 1), 0);
-                const double* r2 = A + tri(min(j0 + 2, n - 1), 0);
-                const double* r3 = A + tri(min(j0 + 3, n - 1), 0);
-                int q = half;
-                for (; q + 2 < j0; q += 4) {
-                    const double a0 = ri[q], a1 = ri[q + 2];
-                    s0 -= a0 * r0[q]; s1 -= a0 * r1[q]; s2 -= a0 * r2[q]; s3 -= a0 * r3[q];
-                    s0 -= a1 * r0[q + 2]; s1 -= a1 * r1[q + 2]; s2 -= a1 * r2[q + 2]; s3 -= a1 * r3[q + 2];
-                }
-                for (; q < j0; q += 2) {
-                    const double a0 = ri[q];
-                    s0 -= a0 * r0[q]; s1 -= a0 * r1[q]; s2 -= a0 * r2[q]; s3 -= a0 * r3[q];
+__device__ bool chol_tiles(SingleSmem& S, int n, double radius, int ti, int tj, bool tile_ok) {
+    const int ntc = (n + 3) >> 2;                         // panels
+    PhaseTimer pc;
+    pc.start();
+    double a[4][4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const int i = 4 * ti + r;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int j = 4 * tj + c;
+            double v = 0.0;
+            if (tile_ok && j < n) {
+                if (i < n) {
+                    if (j <= i) {
+                        v = S.Hs[tri(i, j)];
+                        if (i == j) v += S.damp[i];
+                    }
+                } else if (i == n) {
+                    v = S.gs[j];
                 }
             }
-            s0 += __shfl_xor_sync(0xffffffffu, s0, 1);
-            s1 += __shfl_xor_sync(0xffffffffu, s1, 1);
-            s2 += __shfl_xor_sync(0xffffffffu, s2, 1);
-            s3 += __shfl_xor_sync(0xffffffffu, s3, 1);
-            if (active && half == 0) {
-                const int last = min(w - 1, p - j0);       // columns j0 .. j0 + last exist in row p
-                ri[j0] += s0;
-                if (last >= 1) ri[j0 + 1] += s1;
-                if (last >= 2) ri[j0 + 2] += s2;
-                if (last >= 3) ri[j0 + 3] += s3;
-            }
-            __syncthreads();
+            a[r][c] = v;
         }
-        // ---- factor the diagonal block (redundantly) and solve the own row ----
-        {
-            const double d00 = A[tri(j0, j0)];
-            if (!(d00 > 0.0)) { ok = false; break; }
-            const double i0 = rsqrt(d00);
-            double l10 = 0.0, l20 = 0.0, l21 = 0.0, l30 = 0.0, l31 = 0.0, l32 = 0.0, i1 = 0.0, i2 = 0.0, i3 = 0.0;
-            if (w > 1) {
-                l10 = A[tri(j0 + 1, j0)] * i0;
-                const double d11 = A[tri(j0 + 1, j0 + 1)] - l10 * l10;
-                if (!(d11 > 0.0)) { ok = false; break; }
-                i1 = rsqrt(d11);
+    }
+    if (threadIdx.x == 0) S.chol_fail = 0;
+    __syncthreads();
+    pc.mark(20);
+    // factor the thread's own (diagonal) tile in registers and publish it; padding columns (>= n) have no pivot
+    auto factor_own = [&](int k) {
+        bool bad = false;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int j = 4 * k + c;
+            if (j < n && !bad) {
+                const double piv = a[c][c];
+                if (!(piv > 0.0)) { bad = true; }
+                else {
+                    const double inv = rsqrt(piv);
+                    a[c][c] = inv;
+#pragma unroll
+                    for (int r = c + 1; r < 4; ++r) a[r][c] *= inv;
+#pragma unroll
+                    for (int c2 = c + 1; c2 < 4; ++c2)
+#pragma unroll
+                        for (int r = c2; r < 4; ++r) a[r][c2] -= a[r][c] * a[c2][c];
+                    S.invd[j] = inv;
+                }
+            } else {
+                a[c][c] = 0.0;
+#pragma unroll
+                for (int r = c + 1; r < 4; ++r) a[r][c] = 0.0;
             }
-            if (w > 2) {
-                l20 = A[tri(j0 + 2, j0)] * i0;
-                l21 = (A[tri(j0 + 2, j0 + 1)] - l20 * l10) * i1;
-                const double d22 = A[tri(j0 + 2, j0 + 2)] - l20 * l20 - l21 * l21;
-                if (!(d22 > 0.0)) { ok = false; break; }
-                i2 = rsqrt(d22);
+        }
+        if (bad) S.chol_fail = 1;
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int c = 0; c <= r; ++c) S.dk[k & 1][r][c] = a[r][c];
+    };
+    if (tile_ok && ti == 0 && tj == 0) factor_own(0);
+    __syncthreads();
+    pc.mark(21);
+    for (int k = 0; k < ntc; ++k) {
+        if (S.chol_fail) break;                           // block-uniform (written before the barrier every thread just passed)
+        // ---- solve the tile column against the diagonal tile ----
+        if (tile_ok && tj == k && ti > k) {
+            const double (*D)[4] = S.dk[k & 1];
+            const double d00 = D[0][0], d10 = D[1][0], d11 = D[1][1], d20 = D[2][0], d21 = D[2][1], d22 = D[2][2],
+                         d30 = D[3][0], d31 = D[3][1], d32 = D[3][2], d33 = D[3][3];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                const double x0 = a[r][0] * d00;
+                const double x1 = (a[r][1] - x0 * d10) * d11;
+                const double x2 = (a[r][2] - x0 * d20 - x1 * d21) * d22;
+                const double x3 = (a[r][3] - x0 * d30 - x1 * d31 - x2 * d32) * d33;
+                a[r][0] = x0; a[r][1] = x1; a[r][2] = x2; a[r][3] = x3;
             }
-            if (w > 3) {
-                l30 = A[tri(j0 + 3, j0)] * i0;
-                l31 = (A[tri(j0 + 3, j0 + 1)] - l30 * l10) * i1;
-                l32 = (A[tri(j0 + 3, j0 + 2)] - l30 * l20 - l31 * l21) * i2;
-                const double d33 = A[tri(j0 + 3, j0 + 3)] - l30 * l30 - l31 * l31 - l32 * l32;
-                if (!(d33 > 0.0)) { ok = false; break; }
-                i3 = rsqrt(d33);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                S.pan[c][0][ti] = make_double2(a[0][c], a[1][c]);
+                S.pan[c][1][ti] = make_double2(a[2][c], a[3][c]);
             }
-            __syncthreads();    // every thread has read the block before its owners overwrite it
-            if (active && half == 0) {
-                const int last = min(w - 1, p - j0);
-                const double v0 = ri[j0] * i0;
-                double v1 = 0.0, v2 = 0.0, v3 = 0.0;
-                if (last >= 1) v1 = (ri[j0 + 1] - v0 * l10) * i1;
-                if (last >= 2) v2 = (ri[j0 + 2] - v0 * l20 - v1 * l21) * i2;
-                if (last >= 3) v3 = (ri[j0 + 3] - v0 * l30 - v1 * l31 - v2 * l32) * i3;
-                // a row inside the panel stops before its diagonal entry (kept unfactored; 1 / L_jj lives in S.invd)
-                const int stop = p - j0;   // first column index (relative) that is the diagonal or beyond
-                if (stop > 0) ri[j0] = v0;
-                if (last >= 1 && stop > 1) ri[j0 + 1] = v1;
-                if (last >= 2 && stop > 2) ri[j0 + 2] = v2;
-                if (last >= 3 && stop > 3) ri[j0 + 3] = v3;
-                if (p < n && stop < w) S.invd[p] = stop == 0 ? i0 : (stop == 1 ? i1 : (stop == 2 ? i2 : i3));
+        }
+        // Look-ahead: tile (k + 1, k) and the next diagonal tile (k + 1, k + 1) are neighbouring lanes of one warp (their linear
+        // indices differ by one and never straddle a multiple of 32 for <= 22 tile rows), so a warp barrier is enough for the
+        // diagonal owner to see the rows just solved: it applies panel k to its tile and factors it while the rest of the column
+        // is still being solved, and the pivot chain of panel k + 1 leaves the block-wide critical path.
+        __syncwarp();
+        const bool next_diag = tile_ok && ti == k + 1 && tj == k + 1 && k + 1 < ntc;
+        if (next_diag) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const double2 r01 = S.pan[q][0][ti], r23 = S.pan[q][1][ti];
+                const double rv[4] = {r01.x, r01.y, r23.x, r23.y};
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+#pragma unroll
+                    for (int c = 0; c <= r; ++c) a[r][c] = fma(-rv[r], rv[c], a[r][c]);
             }
-            __syncthreads();
+            factor_own(k + 1);
+        }
+        __syncthreads();
+        pc.mark(22);
+        // ---- rank-4 update of the trailing tiles ----
+        if (tile_ok && tj > k && !next_diag) {
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const double2 r01 = S.pan[q][0][ti], r23 = S.pan[q][1][ti], c01 = S.pan[q][0][tj], c23 = S.pan[q][1][tj];
+                const double rv[4] = {r01.x, r01.y, r23.x, r23.y}, cv[4] = {c01.x, c01.y, c23.x, c23.y};
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) a[r][c] = fma(-rv[r], cv[c], a[r][c]);
+            }
+        }
+        __syncthreads();
+        pc.mark(23);
+    }
+    const bool ok = S.chol_fail == 0;
+    if (ok && tile_ok) {       // the factor's strict lower part and the substituted right-hand side row -> S.u.L for the back substitution
+        double* A = S.u.L;
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const int i = 4 * ti + r;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int j = 4 * tj + c;
+                if (j < n && i <= n && i > j) A[tri(i, j)] = a[r][c];
+            }
         }
     }
     __syncthreads();
+    pc.mark(24);
     return ok;
 }
 
-// back substitution L^T y = z with one warp (z = row n of the augmented factor; 1 / L_jj in S.invd)
+// back substitution L^T y = z with one warp (z = row n of the factor; 1 / L_jj in S.invd).  Row j - 1 is loaded while column j is
+// eliminated, so that the dependent chain per column is shuffle -> multiply -> fused multiply-add only.
 __device__ void chol_backsolve_warp(const SingleSmem& S, int n, double* y) {
     const double* A = S.u.L;
     const int lane = threadIdx.x & 31;
-    double z[3];
+    double z[3], cur[3], nxt[3];
 #pragma unroll
     for (int q = 0; q < 3; ++q) { const int i = lane + 32 * q; z[q] = i < n ? A[tri(n, i)] : 0.0; }
+    {
+        const double* rj = A + tri(n - 1, 0);
+#pragma unroll
+        for (int q = 0; q < 3; ++q) { const int i = lane + 32 * q; cur[q] = i < n - 1 ? rj[i] : 0.0; }
+    }
+    double inv_cur = S.invd[n - 1];
     for (int j = n - 1; j >= 0; --j) {
+        double inv_nxt = 0.0;
+        if (j > 0) {
+            const double* rn = A + tri(j - 1, 0);
+#pragma unroll
+            for (int q = 0; q < 3; ++q) { const int i = lane + 32 * q; nxt[q] = i < j - 1 ? rn[i] : 0.0; }
+            inv_nxt = S.invd[j - 1];
+        }
         const int owner = j & 31, sl = j >> 5;
         double zj = sl == 0 ? z[0] : (sl == 1 ? z[1] : z[2]);
         zj = __shfl_sync(0xffffffffu, zj, owner);
-        const double yj = zj * S.invd[j];
+        const double yj = zj * inv_cur;
         if (lane == owner) y[j] = yj;
-        const double* rj = A + tri(j, 0);
 #pragma unroll
-        for (int q = 0; q < 3; ++q) { const int i = lane + 32 * q; if (i < j) z[q] -= rj[i] * yj; }
+        for (int q = 0; q < 3; ++q) { z[q] = fma(-cur[q], yj, z[q]); cur[q] = nxt[q]; }   // cur is zero beyond the row's entries (i >= j)
+        inv_cur = inv_nxt;
     }
 }
 
@@ -432,8 +491,15 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
     const b3d_kp* kps = kps_all + (size_t)b * MAXKP;
     const int nkp = min(max(nkp_all[b], 0), MAXKP);
     b3d_iter_record* tr = trace ? trace + (size_t)b * trace_stride : nullptr;
+    // this thread's 4 x 4 tile of the lower triangle of the augmented system (rows 0 .. n, columns 0 .. n - 1)
+    int ti = (int)((sqrtf(8.0f * (float)tid + 1.0f) - 1.0f) * 0.5f);
+    while ((ti + 1) * (ti + 2) / 2 <= tid) ++ti;
+    while (ti * (ti + 1) / 2 > tid) --ti;
+    const int tj = tid - ti * (ti + 1) / 2;
+    const bool tile_ok = ti < ((n + 4) >> 2) && tj < ((n + 3) >> 2);
 
     // ---- problem set-up (Sim3BA.h:395-404 / 558-569): sim3 from the caller, jointAA = 0, w from the caller ----
+    for (int k = tid; k < NFULL + 2; k += T) S.fidx[k] = k < n ? C->free_idx[k] : NFULL + 1;
     for (int k = tid; k < NFULL; k += T) {
         double v = 0.0;
         if (k < 7) v = sim3[(size_t)b * 7 + k];
@@ -455,7 +521,7 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
 
     // evaluate at x with Jacobian and apply the Jacobi scaling.  Returns false on non-finite cost.
     auto eval_grad_jac = [&](bool first) -> bool {
-        x_cost = evaluate<T, 1>(C, S.xfull, kps, nkp, S, first);
+        x_cost = evaluate<T, 1>(C, S.xfull, kps, nkp, S, first, ti, tj, tile_ok);
         if (!isfinite(x_cost)) return false;
         it.cost = x_cost;
         if (first) {
@@ -510,6 +576,8 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
         __syncthreads();
     };
 
+    if (tid < 32) phase_acc()[tid] = 0;
+    __syncthreads();
     PhaseTimer pt;
     pt.start();
     const long long t_begin = clock64();
@@ -533,22 +601,16 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
 
             // ---- LevenbergMarquardtStrategy::ComputeStep ----
             pt.mark(0);
-            if (!reuse_diagonal)
-                for (int k = tid; k < n; k += T) S.diag[k] = fmin(fmax(S.Hs[tri(k, k)], kMinDiagonal), kMaxDiagonal);
-            __syncthreads();
-            double* A = S.u.L;
-            for (int i = tid >> 5; i < n; i += T / 32)
-                for (int j = tid & 31; j <= i; j += 32) {
-                    double v = S.Hs[tri(i, j)];
-                    if (i == j) { const double l = sqrt(S.diag[i] / radius); v += l * l; }
-                    A[tri(i, j)] = v;
-                }
-            for (int k = tid; k < n; k += T) A[tri(n, k)] = S.gs[k];
+            for (int k = tid; k < n; k += T) {
+                if (!reuse_diagonal) S.diag[k] = fmin(fmax(S.Hs[tri(k, k)], kMinDiagonal), kMaxDiagonal);
+                const double l = sqrt(S.diag[k] / radius);
+                S.damp[k] = l * l;
+            }
             __syncthreads();
             reuse_diagonal = true;
             bool step_valid = false;
             pt.mark(1);
-            const bool chol_ok = chol_factor_aug<T>(S, n);
+            const bool chol_ok = chol_tiles<T>(S, n, radius, ti, tj, tile_ok);
             pt.mark(2);
             if (chol_ok) {
                 if (tid < 32) chol_backsolve_warp(S, n, S.y);
@@ -581,7 +643,7 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
             // ---- DoLineSearch (the problem is bounded: projected Armijo along delta) ----
             make_candidate(1.0);
             pt.mark(5);
-            cand_cost = evaluate<T, 0>(C, S.cfull, kps, nkp, S, false);
+            cand_cost = evaluate<T, 0>(C, S.cfull, kps, nkp, S, false, ti, tj, tile_ok);
             pt.mark(6);
             {
                 double v = 0.0;
@@ -598,7 +660,7 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
                     auto ls_eval = [&](double a, LsSample& s) {
                         s.x = a; s.valid = false;
                         make_candidate(a);
-                        const double c = evaluate<T, 2>(C, S.cfull, kps, nkp, S, false);
+                        const double c = evaluate<T, 2>(C, S.cfull, kps, nkp, S, false, ti, tj, tile_ok);
                         double vv = 0.0;
                         for (int k = tid; k < n; k += T) vv += S.delta[k] * S.gc[k];
                         const double gg = block_sum<T>(vv, S.red);
@@ -634,7 +696,7 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
                     __syncthreads();
                     // ---- ComputeCandidatePointAndEvaluateCost ----
                     make_candidate(1.0);
-                    cand_cost = evaluate<T, 0>(C, S.cfull, kps, nkp, S, false);
+                    cand_cost = evaluate<T, 0>(C, S.cfull, kps, nkp, S, false, ti, tj, tile_ok);
                 }
             }
             if (!isfinite(cand_cost)) cand_cost = DBL_MAX;
@@ -678,6 +740,7 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
     for (int k = tid; k < NJ * 3; k += T) jointAA[(size_t)b * NJ * 3 + k] = k < 3 ? 0.0 : S.xfull[IDX_JAA + k - 3];
     if (C->has_w && tid < NS) w[(size_t)b * NS + tid] = S.xfull[IDX_W + tid];
     if (tid == 0 && g_phase_on && b < 1024) { g_block_cycles[b] = clock64() - t_begin; g_block_ls[b] = n_ls_evals; }
+    if (b == 0 && tid < 32 && g_phase_on) g_phase_cycles[tid] += phase_acc()[tid];
     if (tid == 0) {
         if (usable) usable[b] = (termination >= B3D_TERM_PARAM_TOL && termination <= B3D_TERM_MIN_RADIUS) ? 1 : 0;
         if (niters) niters[b] = nrec;
@@ -698,6 +761,8 @@ int build_fit_const(const b3d_model* m, const b3d_gmm* gmm, const b3d_fit_opts* 
             fc->chain[j][len++] = cur;
         }
         fc->chain_len[j] = len;
+        for (int a = 0; a < NJ; ++a) fc->chain_pos[j][a] = -1;
+        for (int i = 0; i < len; ++i) fc->chain_pos[j][fc->chain[j][i]] = (int8_t)i;
         for (int c = 0; c < 3; ++c) fc->offset[j][c] = m->sk.offset[3 * j + c];
     }
     // single: jointShapeReg is handed to the functor iff mode == pose+shape && betaShape > 0 (Sim3BA.h:417); pose-only never

@@ -31,6 +31,7 @@ struct FitConst {
     int32_t free_idx[NFULL];               // free -> full (86-layout)
     int32_t col_of[NFULL];                 // full -> free, -1 = held constant
     int32_t gmm_ncomp, pad;
+    int8_t chain_pos[NJ][NJ];              // chain_pos[jid][a] = i with chain[jid][i] == a, or -1 (dense Jacobian rows, eval_reproj_dense)
     const double* gmm_mean;                // ncomp x 69
     const double* gmm_L;                   // ncomp x 69 x 69, lower, row-major  (prec_cho)
     const double* gmm_L70;                 // the same with rows padded to 70 doubles
@@ -300,5 +301,144 @@ __device__ void eval_reproj(const FitConst* __restrict__ C, const double* x, con
 
 // packed lower-triangular index, i >= j
 __device__ __forceinline__ int tri(int i, int j) { return i * (i + 1) / 2 + j; }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Dense variant for the single-frame kernel: the robustified Jacobian of all reprojection blocks as one row-major
+// [2 nkp][LDJ] matrix in the FREE column layout (held-constant parameters have no column), so that J^T J is a plain SYRK over
+// 4 x 4 register tiles and J^T r a column sum.  Same arithmetic per entry as eval_reproj; structural zeros are stored.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int LDJ = 88;                       // 86 columns padded to whole 4-wide tiles (16-byte aligned rows)
+// Position of column c inside a row: the first two columns of every 4-wide tile sit in the lower half of the row, the last two in
+// the upper half.  A thread that owns tile t then reads two 16-byte pieces at [2 t] and [LDJ / 2 + 2 t]: consecutive tiles are 16
+// bytes apart, so a warp's loads spread over all 32 banks (tiles as contiguous 32-byte groups put every load on half of them).
+__host__ __device__ inline int jpos(int c) { return ((c >> 2) << 1) + (c & 1) + ((c & 2) ? LDJ / 2 : 0); }
+struct EvalDense {
+    double res[MAXKP][2];
+    double kcost[MAXKP];
+    alignas(16) double J[2 * MAXKP][LDJ];
+};
+
+template <int T, bool JAC>
+__device__ void eval_reproj_dense(const FitConst* __restrict__ C, const double* x, const b3d_kp* __restrict__ kps, int nkp,
+                                  const double* R0, EvalTmp& S, EvalDense& O) {
+    const int tid = threadIdx.x;
+    for (int t = tid; t < NJ + 3 * NJ; t += T) {
+        if (t < NJ) {
+            const double* aa = t == 0 ? x + IDX_RAA : x + IDX_JAA + 3 * (t - 1);
+            aa_rotation<JAC>(aa, S.R[t], S.dR[t]);
+        } else {
+            const int j = (t - NJ) / 3, c = (t - NJ) % 3;
+            double b = C->offset[j][c];
+            if (C->with_shape) {
+#pragma unroll
+                for (int s = 0; s < NS; ++s) b += C->DB[j][c][s] * x[IDX_W + s];
+            }
+            S.bone[j][c] = b;
+        }
+    }
+    __syncthreads();
+    if (tid < nkp) {
+        const int k = tid;
+        const int jid = clamp_jid(kps[k].jid);
+        const int len = C->chain_len[jid];
+        double q[3] = {S.bone[jid][0], S.bone[jid][1], S.bone[jid][2]};
+        S.q[k][0][0] = q[0]; S.q[k][0][1] = q[1]; S.q[k][0][2] = q[2];
+        for (int i = 1; i < len; ++i) {
+            const int a = C->chain[jid][i];
+            double o[3];
+            mat3_vec(S.R[a], q, o);
+            q[0] = o[0] + S.bone[a][0]; q[1] = o[1] + S.bone[a][1]; q[2] = o[2] + S.bone[a][2];
+            S.q[k][i][0] = q[0]; S.q[k][i][1] = q[1]; S.q[k][i][2] = q[2];
+        }
+        double pc[3], Xp[3];
+#pragma unroll
+        for (int r = 0; r < 3; ++r) pc[r] = R0[r] * q[0] + R0[3 + r] * q[1] + R0[6 + r] * q[2];
+        mat3_vec(S.R[0], pc, Xp);
+        const double s = x[IDX_S];
+        const double X0 = s * Xp[0] + x[IDX_T], X1 = s * Xp[1] + x[IDX_T + 1], X2 = s * Xp[2] + x[IDX_T + 2];
+        const double iz = 1.0 / X2;
+        double r0 = C->cam[0] * X0 * iz + C->cam[2] - kps[k].u;
+        double r1 = C->cam[1] * X1 * iz + C->cam[3] - kps[k].v;
+        const double sq = r0 * r0 + r1 * r1, b = C->huber * C->huber;
+        double rho0, rho1;
+        if (sq > b) { const double rr = sqrt(sq); rho0 = 2.0 * C->huber * rr - b; rho1 = fmax(DBL_MIN, C->huber / rr); }
+        else { rho0 = sq; rho1 = 1.0; }
+        const double sc = sqrt(rho1);
+        O.res[k][0] = r0 * sc; O.res[k][1] = r1 * sc;
+        O.kcost[k] = 0.5 * rho0;
+        if (JAC) {
+#pragma unroll
+            for (int c = 0; c < 3; ++c) { S.pc[k][c] = pc[c]; S.Xp[k][c] = Xp[c]; }
+            double N[6];
+            N[0] = sc * C->cam[0] * iz; N[1] = 0.0;                  N[2] = -sc * C->cam[0] * X0 * iz * iz;
+            N[3] = 0.0;                 N[4] = sc * C->cam[1] * iz;  N[5] = -sc * C->cam[1] * X1 * iz * iz;
+#pragma unroll
+            for (int e = 0; e < 6; ++e) S.N[k][0][e] = N[e];
+            double A[6], Bm[6];
+            n23_mul(N, S.R[0], A);
+            const double R0rm[9] = {R0[0], R0[3], R0[6], R0[1], R0[4], R0[7], R0[2], R0[5], R0[8]};
+            n23_mul(A, R0rm, Bm);
+#pragma unroll
+            for (int e = 0; e < 6; ++e) Bm[e] *= s;
+            for (int i = len - 1; i >= 0; --i) {
+#pragma unroll
+                for (int e = 0; e < 6; ++e) S.N[k][1 + i][e] = Bm[e];
+                if (i > 0) {
+                    n23_mul(Bm, S.R[C->chain[jid][i]], A);
+#pragma unroll
+                    for (int e = 0; e < 6; ++e) Bm[e] = A[e];
+                }
+            }
+        }
+    }
+    __syncthreads();
+    if (!JAC) return;
+    // one task per (keypoint, padded free column): entries of columns the keypoint's chain does not touch are exact zeros
+    const int n = C->n;
+    for (int t = tid; t < nkp * LDJ; t += T) {
+        const int k = t / LDJ, c = t - k * LDJ;
+        double j0 = 0.0, j1 = 0.0;
+        if (c < n) {
+            const int fc = C->free_idx[c];
+            const int jid = clamp_jid(kps[k].jid);
+            const double* N0 = S.N[k][0];
+            if (fc == IDX_S) {
+                j0 = N0[0] * S.Xp[k][0] + N0[1] * S.Xp[k][1] + N0[2] * S.Xp[k][2];
+                j1 = N0[3] * S.Xp[k][0] + N0[4] * S.Xp[k][1] + N0[5] * S.Xp[k][2];
+            } else if (fc < IDX_T) {             // root axis-angle
+                double dv[3];
+                mat3_vec(S.dR[0] + 9 * (fc - IDX_RAA), S.pc[k], dv);
+                const double s = x[IDX_S];
+                j0 = s * (N0[0] * dv[0] + N0[1] * dv[1] + N0[2] * dv[2]);
+                j1 = s * (N0[3] * dv[0] + N0[4] * dv[1] + N0[5] * dv[2]);
+            } else if (fc < IDX_JAA) {           // translation
+                j0 = N0[fc - IDX_T]; j1 = N0[3 + fc - IDX_T];
+            } else if (fc < IDX_W) {             // axis-angle of joint a: non-zero iff a is a strict ancestor a_i, i >= 1, of the keypoint's joint
+                const int a = (fc - IDX_JAA) / 3 + 1, kk = (fc - IDX_JAA) - 3 * (a - 1);
+                const int i = C->chain_pos[jid][a];
+                if (i >= 1) {
+                    double dv[3];
+                    mat3_vec(S.dR[a] + 9 * kk, S.q[k][i - 1], dv);
+                    const double* Ni = S.N[k][1 + i];
+                    j0 = Ni[0] * dv[0] + Ni[1] * dv[1] + Ni[2] * dv[2];
+                    j1 = Ni[3] * dv[0] + Ni[4] * dv[1] + Ni[5] * dv[2];
+                }
+            } else if (C->with_shape) {          // shape key
+                const int sidx = fc - IDX_W;
+                const int len = C->chain_len[jid];
+                for (int i = 0; i < len; ++i) {
+                    const int a = C->chain[jid][i];
+                    const double* Ni = S.N[k][1 + i];
+                    const double d0 = C->DB[a][0][sidx], d1 = C->DB[a][1][sidx], d2 = C->DB[a][2][sidx];
+                    j0 += Ni[0] * d0 + Ni[1] * d1 + Ni[2] * d2;
+                    j1 += Ni[3] * d0 + Ni[4] * d1 + Ni[5] * d2;
+                }
+            }
+        }
+        O.J[2 * k][jpos(c)] = j0;
+        O.J[2 * k + 1][jpos(c)] = j1;
+    }
+    __syncthreads();
+}
 
 }  // namespace b3d

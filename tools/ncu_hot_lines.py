@@ -12,7 +12,7 @@ def main():
     for r in csv.reader(out.splitlines()):
         if not r:
             continue
-        if r[0] == "File Name":
+        if r[0] in ("File Name", "File Path"):
             fname = r[1].split("/")[-1]
         elif r[0] == "Line No":
             hdr = r

@@ -110,7 +110,8 @@ def phases(n=148, mode="C2"):
     tot = sum(out[i] for i in range(9))
     names += [""] * 16
     names[16:20] = ["    gmm: d = x - mu", "    gmm: h = L^T d (8 comps)", "    gmm: |h|^2, argmin", "    gmm: J^T r (JAC only)"]
-    for i in list(range(14)) + [16, 17, 18, 19]:
+    names[20:25] = ["    chol: tile load", "    chol: first factor", "    chol: solve + barrier", "    chol: update + next factor + barrier", "    chol: dump"]
+    for i in list(range(14)) + [16, 17, 18, 19, 20, 21, 22, 23, 24]:
         print(f"{names[i]:22s} {out[i]:12d} cycles {out[i] / max(tot, 1) * 100:6.1f}%")
     cyc, ls = (C.c_longlong * 1024)(), (C.c_int * 1024)()
     lib.b3d_debug_block_read(cyc, ls)
