@@ -41,6 +41,8 @@ constexpr int kMaxConsecutiveInvalidSteps = 5;
 __device__ long long g_phase_cycles[32];
 __device__ long long g_block_cycles[1024];   // total cycles and line-search evaluations per block (debug)
 __device__ int g_block_ls[1024];
+__device__ long long g_block_t0[1024], g_block_t1[1024];   // globaltimer (ns) at the first start and the last end of a frame (debug)
+__device__ __forceinline__ long long global_ns() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 __device__ int g_phase_on;
 // Cycles accumulate in shared memory (a global read-modify-write per mark would stall the timing thread for an L2 round trip and,
 // through the next barrier, the whole block); the kernel adds them to g_phase_cycles once at its end.
@@ -87,6 +89,14 @@ struct SingleSmem {
     double R0[9];
     double red[40];
     double ls_step;
+    double dfull[NFULL];                   // line search: the step in the 86-layout (zero for held-constant parameters)
+    double lsq[GMM_MAXC][3];               // line search: |h_i|^2, h_i . u_i, |u_i|^2 with h_i = L_i^T (x - mu_i), u_i = L_i^T step
+    double lsdphi[MAXKP];
+    double hc[NPRI], hc_sq;                // h of the component chosen at the last cost-only evaluation (reused when that point is accepted)
+    double xref[GMM_MAXC][NPRI];           // per component: the pose at which |h_i| was last computed exactly, and that norm
+    double href[GMM_MAXC];
+    int32_t gskip[GMM_MAXC];               // component skipped at this evaluation (it cannot be the argmin)
+    int32_t ref_valid;
     int32_t comp;
     int32_t fidx[NFULL + 2];               // free -> full column (copy of FitConst::free_idx: read on every pass over the system)
 };
@@ -94,13 +104,22 @@ struct SingleSmem {
 // ---- GMM pose prior (GaussianMixture::residual, external/avatar/GaussianMixture.cpp:94-113) --------------------
 // Returns 0.5 |beta r|^2 of the prior block and sets S.comp; with JAC also S.gpri = J^T r (pose-dim layout), where
 // J = beta L_c^T WITHOUT the sqrt(1/2) the residual carries (reference quirk, Sim3BA.h:298-299).
-template <int T, bool JAC>
-__device__ double gmm_eval(const FitConst* __restrict__ C, const double* xj /*69*/, SingleSmem& S) {
+__device__ int g_gmm_screen = 1;      // debug hook b3d_debug_gmm_screen: 0 evaluates every component at every point
+
+// G.h[i] = L_i^T (v - mu_i) for every component (sub_mean) or L_i^T v (the direction of a line search); ends with a barrier.
+// With `screen` (residual evaluations): component i is skipped (S.gskip[i] = 1) when it provably cannot be the argmin of
+// p_i = |h_i|^2 / 2 - consts_i.  With h_i known exactly at an earlier pose xref_i, |h_i(v)| >= |h_i(xref_i)| - sigma_i |v - xref_i|
+// (sigma_i >= ||L_i||_2) bounds p_i(v) from below, and the same inequality the other way bounds p_c(v) of the previous argmin c from
+// above: if the lower bound of i exceeds the upper bound of c (with slack for rounding), i loses whatever its exact value is.  The
+// chosen component is always evaluated exactly by the same code, so results are bit-identical to evaluating all of them.  Late
+// iterations of a long solve take tiny steps: there seven of the eight 38 KB matrices of the SMPLify prior stay untouched.
+template <int T>
+__device__ void gmm_LTv(const FitConst* __restrict__ C, const double* v /*69*/, bool sub_mean, SingleSmem& S, bool screen = false) {
     const int tid = threadIdx.x, nc = C->gmm_ncomp;
     GmmTmp& G = S.u.gm;
     PhaseTimer pg;
     pg.start();
-    for (int t = tid; t < nc * NPRI; t += T) G.d[t / NPRI][t % NPRI] = xj[t % NPRI] - C->gmm_mean[t];
+    for (int t = tid; t < nc * NPRI; t += T) G.d[t / NPRI][t % NPRI] = v[t % NPRI] - (sub_mean ? C->gmm_mean[t] : 0.0);
     __syncthreads();
     pg.mark(16);
     // h_i[k] = sum_{m >= k} L_i[m][k] d_i[m].  Warp i takes component i; lane q < 17 owns the adjacent column pairs (2q, 2q+1) and
@@ -109,8 +128,26 @@ __device__ double gmm_eval(const FitConst* __restrict__ C, const double* xj /*69
     // (ncu: the per-lane row order made every load a 17-line gather); rows above a lane's columns are predicated off.
     constexpr int QT = 17, LD = NPRI + 1, RS = LD / 2;           // row stride in double2
     static_assert(T / 32 >= 8, "one warp per GMM component");
+    const bool do_screen = screen && g_gmm_screen != 0;
+    const int cprev = S.comp;                 // read before anything of this evaluation writes it
+    const bool have_ref = do_screen && S.ref_valid != 0 && cprev >= 0 && cprev < nc;
     for (int i = tid >> 5; i < nc; i += T / 32) {
         const int q = tid & 31;
+        if (do_screen) {
+            bool skip = false;
+            if (have_ref && i != cprev) {
+                double di = 0.0, dc = 0.0;
+                for (int k = q; k < NPRI; k += 32) { const double a = v[k] - S.xref[i][k], b2 = v[k] - S.xref[cprev][k]; di += a * a; dc += b2 * b2; }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) { di += __shfl_xor_sync(0xffffffffu, di, o); dc += __shfl_xor_sync(0xffffffffu, dc, o); }
+                const double hu = S.href[cprev] + C->gmm_sigma[cprev] * sqrt(dc), hl = S.href[i] - C->gmm_sigma[i] * sqrt(di);
+                const double ub = 0.5 * hu * hu - C->gmm_consts[cprev], lb = (hl > 0.0 ? 0.5 * hl * hl : 0.0) - C->gmm_consts[i];
+                skip = lb > ub + 1e-9 * (fabs(ub) + fabs(lb)) + 1e-12;
+            }
+            if (q == 0) S.gskip[i] = skip ? 1 : 0;
+            if (skip) continue;                                   // warp-uniform
+            for (int k = q; k < NPRI; k += 32) S.xref[i][k] = v[k];   // this component is evaluated exactly at v
+        }
         if (q < QT) {
             const int ca = 2 * q, cb = 66 - 2 * q;
             const double* __restrict__ L = C->gmm_L70 + (size_t)i * NPRI * LD;
@@ -152,21 +189,43 @@ __device__ double gmm_eval(const FitConst* __restrict__ C, const double* xj /*69
     }
     __syncthreads();
     pg.mark(17);
-    if (tid < nc) {
-        const double rh = sqrt(0.5);
-        double sq = 0.0;
-        for (int k = 0; k < NPRI; ++k) { const double h = G.h[tid][k] * rh; sq += h * h; }
-        G.sq[tid] = sq;
-        G.p[tid] = sq - C->gmm_consts[tid];
+}
+
+// `reuse`: xj is the point of the previous (cost-only) evaluation, whose component and h_c are still in S.comp / S.hc.
+template <int T, bool JAC>
+__device__ double gmm_eval(const FitConst* __restrict__ C, const double* xj /*69*/, SingleSmem& S, bool reuse) {
+    const int tid = threadIdx.x, nc = C->gmm_ncomp;
+    GmmTmp& G = S.u.gm;
+    PhaseTimer pg;
+    if (!reuse) {
+        gmm_LTv<T>(C, xj, true, S, true);
+        pg.start();
+        if (tid < nc) {
+            if (g_gmm_screen != 0 && S.gskip[tid]) {
+                G.sq[tid] = DBL_MAX; G.p[tid] = DBL_MAX;
+            } else {
+                const double rh = sqrt(0.5);
+                double sq = 0.0, nn = 0.0;
+                for (int k = 0; k < NPRI; ++k) { const double h0 = G.h[tid][k], h = h0 * rh; sq += h * h; nn += h0 * h0; }
+                G.sq[tid] = sq;
+                G.p[tid] = sq - C->gmm_consts[tid];
+                S.href[tid] = sqrt(nn);
+            }
+        }
+        __syncthreads();
+        int cc = 0;
+        double best = DBL_MAX;
+        for (int i = 0; i < nc; ++i) { const double p = G.p[i]; if (p < best) { best = p; cc = i; } }   // strict '<': first wins ties
+        for (int k = tid; k < NPRI; k += T) S.hc[k] = G.h[cc][k];
+        if (tid == 0) { S.comp = cc; S.hc_sq = G.sq[cc]; S.ref_valid = 1; }
+        __syncthreads();
+    } else {
+        pg.start();
     }
-    __syncthreads();
-    int c = 0;
-    double best = DBL_MAX;
-    for (int i = 0; i < nc; ++i) { const double p = G.p[i]; if (p < best) { best = p; c = i; } }   // strict '<': first wins ties
-    if (tid == 0) S.comp = c;
+    const int c = S.comp;
     pg.mark(18);
     // residual = beta [h_c ; sqrt(-consts_log_c)]  =>  cost = 0.5 beta^2 (|h_c|^2 - consts_log_c)
-    const double cost = 0.5 * C->beta_pose * C->beta_pose * (G.sq[c] + (-C->gmm_consts[c]));
+    const double cost = 0.5 * C->beta_pose * C->beta_pose * (S.hc_sq + (-C->gmm_consts[c]));
     if (JAC) {
         // J^T r = beta^2 sqrt(1/2) L_c h: row m split over three threads
         const double* __restrict__ LT = C->gmm_LT + (size_t)c * NPRI * NPRI;
@@ -174,8 +233,8 @@ __device__ double gmm_eval(const FitConst* __restrict__ C, const double* xj /*69
             const int part = tid / NPRI, m = tid % NPRI;
             double a0 = 0.0, a1 = 0.0;
             int k = part;
-            for (; k + 3 <= m; k += 6) { a0 += __ldg(LT + k * NPRI + m) * G.h[c][k]; a1 += __ldg(LT + (k + 3) * NPRI + m) * G.h[c][k + 3]; }
-            for (; k <= m; k += 3) a0 += __ldg(LT + k * NPRI + m) * G.h[c][k];
+            for (; k + 3 <= m; k += 6) { a0 += __ldg(LT + k * NPRI + m) * S.hc[k]; a1 += __ldg(LT + (k + 3) * NPRI + m) * S.hc[k + 3]; }
+            for (; k <= m; k += 3) a0 += __ldg(LT + k * NPRI + m) * S.hc[k];
             G.part[part][m] = a0 + a1;
         }
         __syncthreads();
@@ -196,7 +255,7 @@ __device__ double gmm_eval(const FitConst* __restrict__ C, const double* xj /*69
 // (ti, tj): this thread's 4 x 4 tile of the lower triangle (tile_ok: it exists for this problem size).
 template <int T, int MODE>
 __device__ __noinline__ double evaluate(const FitConst* __restrict__ C, const double* xf, const b3d_kp* __restrict__ kps, int nkp, SingleSmem& S,
-                           bool first, int ti, int tj, bool tile_ok) {
+                           bool first, int ti, int tj, bool tile_ok, bool reuse_gmm = false) {
     constexpr bool JAC = MODE != 0;
     const int tid = threadIdx.x, n = C->n;
     PhaseTimer pe;
@@ -208,7 +267,7 @@ __device__ __noinline__ double evaluate(const FitConst* __restrict__ C, const do
     double pcost = 0.0;
     const bool pose_prior = C->beta_pose > 0.0;
     const bool gmm = pose_prior && C->use_gmm;
-    if (gmm) pcost = gmm_eval<T, JAC>(C, xf + IDX_JAA, S);   // aliases S.u.ev: the evaluation temporaries are dead
+    if (gmm) pcost = gmm_eval<T, JAC>(C, xf + IDX_JAA, S, reuse_gmm);   // aliases S.u.ev: the evaluation temporaries are dead
     // the remaining prior costs are sums of squares over <= 79 terms: fixed-order block sum
     double v = 0.0;
     if (pose_prior && !gmm)
@@ -477,16 +536,80 @@ __device__ void chol_backsolve_warp(const SingleSmem& S, int n, double* y) {
     }
 }
 
+// Scheduling of frames onto CTAs.  A frame's iterations are a serial chain (up to 101 of them, against a mean of 20), so a batch
+// ends with its longest frames, and with one CTA per frame such a frame starts whenever the block scheduler reaches it — up to
+// several milliseconds late once the batch exceeds the 2 CTAs per SM that fit.  Instead the kernel is persistent (one CTA per slot)
+// and takes frames from a device-side queue in time slices: a frame runs a capped number of iterations; if it is not finished and
+// another frame is waiting for a CTA, it checkpoints itself (what Ceres' minimiser carries between iterations; the normal equations
+// are rebuilt by re-evaluating at x: same inputs, same bits) and goes to the back of the queue.  Fresh frames have priority.  All
+// unfinished frames thus advance at the same rate until no more of them are left than there are CTAs, and from then on the long
+// ones run undisturbed (a barrier between "passes" loses more than it gains: each pass ends with its own slowest frame).
+struct FitCkpt {
+    double xfull[NFULL], scale[NFULL], diag[NFULL];
+    double radius, decrease_factor, x_norm, gmax;
+    int32_t reuse_diagonal, num_invalid, iteration, nrec, n_ls, pad;
+};
+struct FitQueue {
+    FitCkpt* ckpt;            // B entries, or null: no queue, frame = blockIdx.x, one launch slot per frame
+    int32_t* ctl;             // [0] next fresh frame, [1] next queue slot to claim, [2] queue slots handed out, [3] frames finished
+    int32_t* slots;           // queue of checkpointed frames, -1 = not written yet (B + grid entries)
+    int32_t stop_at;          // a fresh frame checkpoints itself once this many iterations are done
+};
+enum { Q_FRESH = 0, Q_HEAD = 1, Q_TAIL = 2, Q_DONE = 3 };
+
+template <int T>
+__device__ void fit_frame(const FitConst* __restrict__ C, int B, const b3d_kp* __restrict__ kps_all, const int32_t* __restrict__ nkp_all,
+                          const double* __restrict__ R0_all, double* __restrict__ sim3, double* __restrict__ w, double* __restrict__ jointAA,
+                          uint8_t* __restrict__ usable, b3d_iter_record* __restrict__ trace, int trace_stride, int32_t* __restrict__ niters,
+                          int32_t* __restrict__ term, const FitQueue& P, SingleSmem& S, int b, bool resumed);
+
+// Persistent driver of fit_frame (or one frame per CTA when there is no queue).
 template <int T>
 __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __restrict__ C, int B, const b3d_kp* __restrict__ kps_all,
                                                           const int32_t* __restrict__ nkp_all, const double* __restrict__ R0_all,
                                                           double* __restrict__ sim3, double* __restrict__ w, double* __restrict__ jointAA,
                                                           uint8_t* __restrict__ usable, b3d_iter_record* __restrict__ trace, int trace_stride,
-                                                          int32_t* __restrict__ niters, int32_t* __restrict__ term) {
+                                                          int32_t* __restrict__ niters, int32_t* __restrict__ term, const FitQueue P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SingleSmem& S = *reinterpret_cast<SingleSmem*>(smem_raw);
-    const int tid = threadIdx.x, b = blockIdx.x;
-    if (b >= B) return;
+    __shared__ int s_item[2];
+    for (;;) {
+        if (!P.ckpt) {
+            if (threadIdx.x == 0) { s_item[0] = (int)blockIdx.x < B ? (int)blockIdx.x : -1; s_item[1] = 0; }
+        } else if (threadIdx.x == 0) {
+            int item = -1, res = 0;
+            if (*(volatile int32_t*)&P.ctl[Q_FRESH] < B) {
+                const int f = atomicAdd(&P.ctl[Q_FRESH], 1);
+                if (f < B) item = f;
+            }
+            if (item < 0) {   // no fresh frame left: claim the next queue slot and wait until it is filled or every frame is finished
+                const int sl = atomicAdd(&P.ctl[Q_HEAD], 1);
+                for (;;) {
+                    const int v = *(volatile int32_t*)&P.slots[sl];
+                    if (v >= 0) { __threadfence(); item = v; res = 1; break; }
+                    if (*(volatile int32_t*)&P.ctl[Q_DONE] >= B) break;
+                    __nanosleep(200);
+                }
+            }
+            s_item[0] = item; s_item[1] = res;
+        }
+        __syncthreads();
+        const int b = s_item[0];
+        const bool resumed = s_item[1] != 0;
+        __syncthreads();
+        if (b < 0) return;
+        fit_frame<T>(C, B, kps_all, nkp_all, R0_all, sim3, w, jointAA, usable, trace, trace_stride, niters, term, P, S, b, resumed);
+        if (!P.ckpt) return;
+        __syncthreads();
+    }
+}
+
+template <int T>
+__device__ void fit_frame(const FitConst* __restrict__ C, int B, const b3d_kp* __restrict__ kps_all, const int32_t* __restrict__ nkp_all,
+                          const double* __restrict__ R0_all, double* __restrict__ sim3, double* __restrict__ w, double* __restrict__ jointAA,
+                          uint8_t* __restrict__ usable, b3d_iter_record* __restrict__ trace, int trace_stride, int32_t* __restrict__ niters,
+                          int32_t* __restrict__ term, const FitQueue& P, SingleSmem& S, int b, bool resumed) {
+    const int tid = threadIdx.x;
     const int n = C->n;
     const b3d_kp* kps = kps_all + (size_t)b * MAXKP;
     const int nkp = min(max(nkp_all[b], 0), MAXKP);
@@ -507,9 +630,14 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
         S.xfull[k] = v;
     }
     if (tid < 9) S.R0[tid] = R0_all[(size_t)b * 9 + tid];
+    if (tid == 0) { S.ref_valid = 0; S.comp = -1; }
+    FitCkpt* ck = P.ckpt ? P.ckpt + b : nullptr;
+    if (resumed) {
+        for (int k = tid; k < NFULL; k += T) { S.xfull[k] = ck->xfull[k]; S.scale[k] = ck->scale[k]; S.diag[k] = ck->diag[k]; }
+    }
     __syncthreads();
     // IterationZero: project onto the bounds (only the scale is bounded)
-    if (tid == 0) S.xfull[IDX_S] = fmin(fmax(S.xfull[IDX_S], C->scale_lo), C->scale_hi);
+    if (tid == 0 && !resumed) S.xfull[IDX_S] = fmin(fmax(S.xfull[IDX_S], C->scale_lo), C->scale_hi);
     __syncthreads();
 
     double radius = kInitialRadius, decrease_factor = 2.0, x_cost = 0.0, cand_cost = 0.0, mcc = 0.0;
@@ -520,8 +648,8 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
     it.flags = 0; it.aux = -1;
 
     // evaluate at x with Jacobian and apply the Jacobi scaling.  Returns false on non-finite cost.
-    auto eval_grad_jac = [&](bool first) -> bool {
-        x_cost = evaluate<T, 1>(C, S.xfull, kps, nkp, S, first, ti, tj, tile_ok);
+    auto eval_grad_jac = [&](bool first, bool reuse_gmm = false) -> bool {
+        x_cost = evaluate<T, 1>(C, S.xfull, kps, nkp, S, first, ti, tj, tile_ok, reuse_gmm);
         if (!isfinite(x_cost)) return false;
         it.cost = x_cost;
         if (first) {
@@ -581,18 +709,45 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
     PhaseTimer pt;
     pt.start();
     const long long t_begin = clock64();
-    int n_ls_evals = 0;
-    double x_norm = x_norm_of(S.xfull);
-    if (!eval_grad_jac(true)) {
+    if (tid == 0 && g_phase_on && b < 1024 && !resumed) g_block_t0[b] = global_ns();
+    int n_ls_evals = 0, slice_end = P.stop_at;
+    double x_norm;
+    bool unfinished = false, skip_head = false, started;
+    if (resumed) {
+        radius = ck->radius; decrease_factor = ck->decrease_factor; x_norm = ck->x_norm;
+        reuse_diagonal = ck->reuse_diagonal != 0; num_invalid = ck->num_invalid; iteration = ck->iteration; nrec = ck->nrec; n_ls_evals = ck->n_ls;
+        slice_end = iteration + P.stop_at;
+        started = eval_grad_jac(false);     // the normal equations, gradient and cost at x, bit for bit what the previous slice held
+        it.gradient_max_norm = ck->gmax;    // (zero after a rejected step: what the next record of an invalid step would repeat)
+        skip_head = true;                   // the checks at the head of this iteration were passed before the checkpoint
+    } else {
+        x_norm = x_norm_of(S.xfull);
+        started = eval_grad_jac(true);
+        it.flags = 3;
+    }
+    if (!started) {
         termination = B3D_TERM_EVAL_FAILURE;
     } else {
-        it.flags = 3;
         for (;;) {
-            // ---- FinalizeIterationAndCheckIfMinimizerCanContinue ----
-            push();
-            if (iteration >= C->max_iters) { termination = B3D_TERM_MAX_ITERS; break; }
-            if (step_successful && it.gradient_max_norm <= kGradientTolerance) { termination = B3D_TERM_GRAD_TOL; break; }
-            if (!(radius > kMinRadius)) { termination = B3D_TERM_MIN_RADIUS; break; }
+            if (!skip_head) {
+                // ---- FinalizeIterationAndCheckIfMinimizerCanContinue ----
+                push();
+                if (iteration >= C->max_iters) { termination = B3D_TERM_MAX_ITERS; break; }
+                if (step_successful && it.gradient_max_norm <= kGradientTolerance) { termination = B3D_TERM_GRAD_TOL; break; }
+                if (!(radius > kMinRadius)) { termination = B3D_TERM_MIN_RADIUS; break; }
+                if (ck && iteration >= slice_end) {
+                    // end of this frame's time slice: yield (checkpoint, go to the back of the queue) if any other frame is waiting
+                    // for a CTA, otherwise carry on.  One thread looks, so that the decision is the same for the whole block.
+                    if (tid == 0)
+                        S.chol_fail = (*(volatile int32_t*)&P.ctl[Q_FRESH] < B || *(volatile int32_t*)&P.ctl[Q_TAIL] > *(volatile int32_t*)&P.ctl[Q_HEAD]) ? 1 : 0;
+                    __syncthreads();
+                    const bool yield = S.chol_fail != 0;
+                    __syncthreads();
+                    if (yield) { unfinished = true; break; }
+                    slice_end += P.stop_at;
+                }
+            }
+            skip_head = false;
             const double prev_gmax = it.gradient_max_norm;
             it.cost = it.cost_change = it.gradient_max_norm = it.step_norm = it.relative_decrease = 0.0;
             it.flags = 0;
@@ -657,13 +812,62 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
                     double dmax = 0.0;
                     for (int k = 0; k < n; ++k) dmax = fmax(dmax, fabs(S.delta[k]));
                     LsSample init{0.0, x_cost, gd, true}, prev{0, 0, 0, false}, cur{1.0, 0, 0, false};
+                    // Along the search line every prior is a quadratic in the step size a: the GMM components through
+                    // h_i(a) = h_i + a u_i (so the argmin component and its cost need no matrix at a trial point), the L2 priors
+                    // through three sums.  Only the reprojection blocks are evaluated per trial (eval_reproj_dir).
+                    const bool pose_prior = C->beta_pose > 0.0, gmm = pose_prior && C->use_gmm;
+                    for (int k = tid; k < NFULL; k += T) S.dfull[k] = 0.0;
+                    __syncthreads();
+                    for (int k = tid; k < n; k += T) S.dfull[S.fidx[k]] = S.delta[k];
+                    __syncthreads();
+                    double sxx = 0.0, sxd = 0.0, sdd = 0.0, pxx = 0.0, pxd = 0.0, pdd = 0.0;     // shape / L2 pose prior sums (every thread)
+                    if (C->has_w)
+                        for (int k = 0; k < NS; ++k) { const double xv = S.xfull[IDX_W + k], dv = S.dfull[IDX_W + k]; sxx += xv * xv; sxd += xv * dv; sdd += dv * dv; }
+                    if (pose_prior && !gmm)
+                        for (int k = 0; k < NPRI; ++k) { const double xv = S.xfull[IDX_JAA + k], dv = S.dfull[IDX_JAA + k]; pxx += xv * xv; pxd += xv * dv; pdd += dv * dv; }
+                    if (gmm) {
+                        const int nc = C->gmm_ncomp;
+                        double* stash = &S.out.J[0][0];                       // the dense Jacobian is dead during a line search
+                        gmm_LTv<T>(C, S.xfull + IDX_JAA, true, S);
+                        for (int t = tid; t < nc * NPRI; t += T) stash[t] = S.u.gm.h[t / NPRI][t % NPRI];
+                        __syncthreads();
+                        gmm_LTv<T>(C, S.dfull + IDX_JAA, false, S);
+                        for (int i = tid >> 5; i < nc; i += T / 32) {
+                            double hh = 0.0, hu = 0.0, uu = 0.0;
+                            for (int k = tid & 31; k < NPRI; k += 32) { const double h = stash[i * NPRI + k], u = S.u.gm.h[i][k]; hh += h * h; hu += h * u; uu += u * u; }
+#pragma unroll
+                            for (int o = 16; o > 0; o >>= 1) {
+                                hh += __shfl_xor_sync(0xffffffffu, hh, o); hu += __shfl_xor_sync(0xffffffffu, hu, o); uu += __shfl_xor_sync(0xffffffffu, uu, o);
+                            }
+                            if ((tid & 31) == 0) { S.lsq[i][0] = hh; S.lsq[i][1] = hu; S.lsq[i][2] = uu; }
+                        }
+                        __syncthreads();
+                    }
+                    const double bp2 = C->beta_pose * C->beta_pose, bs2 = C->beta_shape * C->beta_shape;
                     auto ls_eval = [&](double a, LsSample& s) {
                         s.x = a; s.valid = false;
                         make_candidate(a);
-                        const double c = evaluate<T, 2>(C, S.cfull, kps, nkp, S, false, ti, tj, tile_ok);
-                        double vv = 0.0;
-                        for (int k = tid; k < n; k += T) vv += S.delta[k] * S.gc[k];
-                        const double gg = block_sum<T>(vv, S.red);
+                        eval_reproj_dir<T>(C, S.cfull, S.dfull, kps, nkp, S.R0, S.u.ev, S.out.kcost, S.lsdphi);
+                        double c = 0.0, gg = 0.0;
+                        for (int k = 0; k < nkp; ++k) { c += S.out.kcost[k]; gg += S.lsdphi[k]; }
+                        if (gmm) {
+                            int best_c = 0;
+                            double best = DBL_MAX, best_sq = 0.0;
+                            for (int i = 0; i < C->gmm_ncomp; ++i) {
+                                const double sq = 0.5 * (S.lsq[i][0] + a * (2.0 * S.lsq[i][1] + a * S.lsq[i][2]));
+                                const double p = sq - C->gmm_consts[i];
+                                if (p < best) { best = p; best_c = i; best_sq = sq; }
+                            }
+                            c += 0.5 * bp2 * (best_sq + (-C->gmm_consts[best_c]));
+                            gg += bp2 * sqrt(0.5) * (S.lsq[best_c][1] + a * S.lsq[best_c][2]);      // the reference's gradient (no sqrt(1/2) in J)
+                        } else if (pose_prior) {
+                            c += 0.5 * bp2 * (pxx + a * (2.0 * pxd + a * pdd));
+                            gg += bp2 * (pxd + a * pdd);
+                        }
+                        if (C->has_w) {
+                            c += 0.5 * bs2 * (sxx + a * (2.0 * sxd + a * sdd));
+                            gg += bs2 * (sxd + a * sdd);
+                        }
                         if (!isfinite(c) || !isfinite(gg)) return;
                         s.value = c; s.gradient = gg; s.valid = true;
                     };
@@ -719,7 +923,7 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
                 __syncthreads();
                 x_norm = x_norm_of(S.xfull);
                 pt.mark(7);
-                if (!eval_grad_jac(false)) { termination = B3D_TERM_EVAL_FAILURE; break; }
+                if (!eval_grad_jac(false, true)) { termination = B3D_TERM_EVAL_FAILURE; break; }   // x is the point just evaluated: reuse its GMM component
                 pt.mark(8);
                 step_successful = true;
                 it.flags |= 2;
@@ -735,18 +939,36 @@ __global__ void __launch_bounds__(T, 2) fit_single_kernel(const FitConst* __rest
         }
     }
     __syncthreads();
+    if (tid == 0 && g_phase_on && b < 1024) { g_block_cycles[b] = (resumed ? g_block_cycles[b] : 0) + (clock64() - t_begin); g_block_ls[b] = n_ls_evals; }
+    if (b == 0 && tid < 32 && g_phase_on) g_phase_cycles[tid] += phase_acc()[tid];
+    if (tid == 0 && g_phase_on && b < 1024) g_block_t1[b] = global_ns();
+    if (unfinished) {
+        for (int k = tid; k < NFULL; k += T) { ck->xfull[k] = S.xfull[k]; ck->scale[k] = S.scale[k]; ck->diag[k] = S.diag[k]; }
+        if (tid == 0) {
+            ck->radius = radius; ck->decrease_factor = decrease_factor; ck->x_norm = x_norm; ck->gmax = it.gradient_max_norm;
+            ck->reuse_diagonal = reuse_diagonal ? 1 : 0; ck->num_invalid = num_invalid; ck->iteration = iteration; ck->nrec = nrec; ck->n_ls = n_ls_evals;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence();                                       // the checkpoint is visible before the slot names the frame
+            const int sl = atomicAdd(&P.ctl[Q_TAIL], 1);
+            *(volatile int32_t*)&P.slots[sl] = b;
+        }
+        return;
+    }
     // ---- results: optimised blocks back to the caller's arrays (Sim3BA.h:481-507 reads them from the blocks) ----
     if (tid < 7) sim3[(size_t)b * 7 + tid] = S.xfull[tid];
     for (int k = tid; k < NJ * 3; k += T) jointAA[(size_t)b * NJ * 3 + k] = k < 3 ? 0.0 : S.xfull[IDX_JAA + k - 3];
     if (C->has_w && tid < NS) w[(size_t)b * NS + tid] = S.xfull[IDX_W + tid];
-    if (tid == 0 && g_phase_on && b < 1024) { g_block_cycles[b] = clock64() - t_begin; g_block_ls[b] = n_ls_evals; }
-    if (b == 0 && tid < 32 && g_phase_on) g_phase_cycles[tid] += phase_acc()[tid];
     if (tid == 0) {
         if (usable) usable[b] = (termination >= B3D_TERM_PARAM_TOL && termination <= B3D_TERM_MIN_RADIUS) ? 1 : 0;
         if (niters) niters[b] = nrec;
         if (term) term[b] = termination;
+        if (P.ckpt) { __threadfence(); atomicAdd(&P.ctl[Q_DONE], 1); }
     }
 }
+
+static std::atomic<int> g_fit_stop_at{-1};
 
 // Host side: launch-constant block shared by the single-frame and window drivers.
 int build_fit_const(const b3d_model* m, const b3d_gmm* gmm, const b3d_fit_opts* o, bool multi, FitConst* fc) {
@@ -795,7 +1017,7 @@ int build_fit_const(const b3d_model* m, const b3d_gmm* gmm, const b3d_fit_opts* 
     if (fc->use_gmm) {
         if (gmm->nComps > GMM_MAXC) return set_error(B3D_EINVAL, "GMM with %d components (max %d)", gmm->nComps, GMM_MAXC);
         fc->gmm_ncomp = gmm->nComps;
-        fc->gmm_mean = gmm->d_mean; fc->gmm_L = gmm->d_prec_cho; fc->gmm_L70 = gmm->d_prec_cho70; fc->gmm_LT = gmm->d_prec_choT; fc->gmm_P = gmm->d_prec; fc->gmm_consts = gmm->d_consts;
+        fc->gmm_mean = gmm->d_mean; fc->gmm_L = gmm->d_prec_cho; fc->gmm_L70 = gmm->d_prec_cho70; fc->gmm_LT = gmm->d_prec_choT; fc->gmm_P = gmm->d_prec; fc->gmm_consts = gmm->d_consts; fc->gmm_sigma = gmm->d_sigma;
     }
     return B3D_OK;
 }
@@ -806,6 +1028,13 @@ using namespace b3d;
 
 extern "C" {
 
+// debug hook: iterations after which a fresh frame of the persistent kernel checkpoints itself (0: no queue, one CTA per frame;
+// < 0: automatic)
+int b3d_debug_fit_stop_at(int iters) { g_fit_stop_at.store(iters); return 0; }
+
+// debug hook: 0 switches the GMM component screening off (every component evaluated at every point); results must not change
+int b3d_debug_gmm_screen(int on) { return cudaMemcpyToSymbol(g_gmm_screen, &on, sizeof(int)) == cudaSuccess ? 0 : 2; }
+
 // debug hooks (not part of include/b3d.h): per-phase cycle counters of block 0
 int b3d_debug_phase_timing(int on) {
     long long z[32] = {0};
@@ -815,6 +1044,10 @@ int b3d_debug_phase_timing(int on) {
 int b3d_debug_block_read(long long* cyc1024, int* ls1024) {
     cudaMemcpyFromSymbol(ls1024, g_block_ls, 1024 * sizeof(int));
     return cudaMemcpyFromSymbol(cyc1024, g_block_cycles, 1024 * sizeof(long long)) == cudaSuccess ? 0 : 2;
+}
+int b3d_debug_block_times(long long* t0_1024, long long* t1_1024) {
+    cudaMemcpyFromSymbol(t0_1024, g_block_t0, 1024 * sizeof(long long));
+    return cudaMemcpyFromSymbol(t1_1024, g_block_t1, 1024 * sizeof(long long)) == cudaSuccess ? 0 : 2;
 }
 int b3d_debug_phase_read(long long* out32) { return cudaMemcpyFromSymbol(out32, g_phase_cycles, 32 * sizeof(long long)) == cudaSuccess ? 0 : 2; }
 
@@ -835,9 +1068,36 @@ int b3d_fit_single_dev(const b3d_model* m, const b3d_gmm* gmm, const b3d_fit_opt
     B3D_CUDA(cudaMemcpyAsync(dfc, &fc, sizeof(FitConst), cudaMemcpyHostToDevice, st));
     // per device and context, cheap: set on every call (a process-wide flag would miss a second GPU)
     B3D_CUDA(cudaFuncSetAttribute(fit_single_kernel<FS_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SingleSmem)));
-    fit_single_kernel<FS_THREADS><<<B, FS_THREADS, sizeof(SingleSmem), st>>>(dfc, B, kps, nkp, R0, sim3, w, jointAA, usable, trace, trace_stride,
-                                                                            niters, term);
-    B3D_LAUNCH_CHECK();
+    // Batches larger than the machine holds at once (2 CTAs per SM) go through the persistent kernel and its frame queue (struct
+    // FitCkpt); smaller ones start every frame at once, one CTA each.
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int slots = 2 * sms;
+    int stop_at = g_fit_stop_at.load();
+    if (stop_at < 0) stop_at = 16;                         // automatic: a little under the mean iteration count of the bench frames (8 - 20 measure alike)
+    FitQueue Q;
+    std::memset(&Q, 0, sizeof(Q));
+    if (B <= slots || stop_at == 0 || stop_at >= opts->max_iters) {
+        fit_single_kernel<FS_THREADS><<<B, FS_THREADS, sizeof(SingleSmem), st>>>(dfc, B, kps, nkp, R0, sim3, w, jointAA, usable, trace, trace_stride,
+                                                                                niters, term, Q);
+        B3D_LAUNCH_CHECK();
+    } else {
+        char* scratch = nullptr;
+        const size_t pushes = (size_t)B * (size_t)(opts->max_iters / stop_at + 2);      // a frame yields at most once per slice
+        const size_t s_ck = (sizeof(FitCkpt) * (size_t)B + 255) / 256 * 256, s_q = (4 * (pushes + slots + 8) + 255) / 256 * 256;
+        B3D_CUDA(cudaMallocAsync(&scratch, s_ck + s_q + 256, st));
+        Q.ckpt = (FitCkpt*)scratch;
+        Q.slots = (int32_t*)(scratch + s_ck);
+        Q.ctl = (int32_t*)(scratch + s_ck + s_q);
+        Q.stop_at = stop_at;
+        B3D_CUDA(cudaMemsetAsync(Q.slots, 0xFF, s_q, st));
+        B3D_CUDA(cudaMemsetAsync(Q.ctl, 0, 256, st));
+        fit_single_kernel<FS_THREADS><<<slots, FS_THREADS, sizeof(SingleSmem), st>>>(dfc, B, kps, nkp, R0, sim3, w, jointAA, usable, trace,
+                                                                                    trace_stride, niters, term, Q);
+        B3D_LAUNCH_CHECK();
+        B3D_CUDA(cudaFreeAsync(scratch, st));
+    }
     B3D_CUDA(cudaFreeAsync(dfc, st));
     return B3D_OK;
 }

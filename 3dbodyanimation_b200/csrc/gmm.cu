@@ -128,12 +128,33 @@ int b3d_gmm_create(int32_t nc, int32_t nd, const double* weights, const double* 
             }
     }
     for (int i = 0; i < nc; ++i) g->consts_log[i] += std::log(min_det);
+    // An upper bound of the spectral norm of every L_i (= sqrt(lambda_max(L_i L_i^T))): power iteration on P_i plus a margin, capped
+    // by the Frobenius norm (always valid).  The single-frame kernel uses it to bound |L_i^T (x - mu_i)| away from a point where
+    // it is known, so that components that cannot win the argmin of GaussianMixture::residual are not evaluated (fit_single.cu).
+    std::vector<double> sigma(nc);
+    for (int i = 0; i < nc; ++i) {
+        const double* P = &prec[i * nn];
+        std::vector<double> v(nd, 1.0 / std::sqrt((double)nd)), u(nd);
+        double lam = 0.0, fro = 0.0;
+        for (size_t e = 0; e < nn; ++e) fro += g->prec_cho[i * nn + e] * g->prec_cho[i * nn + e];
+        for (int it = 0; it < 300; ++it) {
+            double nrm = 0.0;
+            for (int a = 0; a < nd; ++a) { double acc = 0.0; for (int b = 0; b < nd; ++b) acc += P[(size_t)a * nd + b] * v[b]; u[a] = acc; nrm += acc * acc; }
+            nrm = std::sqrt(nrm);
+            lam = nrm;
+            if (!(nrm > 0.0)) break;
+            for (int a = 0; a < nd; ++a) v[a] = u[a] / nrm;
+        }
+        sigma[i] = std::min(std::sqrt(fro), 1.05 * std::sqrt(lam));     // power iteration approaches lambda_max from below: 5 % margin on the norm
+    }
     cudaError_t e = cudaMalloc(&g->d_mean, sizeof(double) * nc * nd);
     if (e == cudaSuccess) e = cudaMalloc(&g->d_prec_cho, sizeof(double) * nc * nn);
     if (e == cudaSuccess) e = cudaMalloc(&g->d_prec_cho70, sizeof(double) * nc * nd * (nd + 1));
     if (e == cudaSuccess) e = cudaMalloc(&g->d_prec_choT, sizeof(double) * nc * nn);
     if (e == cudaSuccess) e = cudaMalloc(&g->d_prec, sizeof(double) * nc * nn);
     if (e == cudaSuccess) e = cudaMalloc(&g->d_consts, sizeof(double) * nc);
+    if (e == cudaSuccess) e = cudaMalloc(&g->d_sigma, sizeof(double) * nc);
+    if (e == cudaSuccess) e = cudaMemcpy(g->d_sigma, sigma.data(), sizeof(double) * nc, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(g->d_mean, g->mean.data(), sizeof(double) * nc * nd, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(g->d_prec_cho, g->prec_cho.data(), sizeof(double) * nc * nn, cudaMemcpyHostToDevice);
     {
@@ -170,7 +191,7 @@ int b3d_gmm_load(const char* path, b3d_gmm** out) {
 
 void b3d_gmm_destroy(b3d_gmm* g) {
     if (!g) return;
-    cudaFree(g->d_mean); cudaFree(g->d_prec_cho); cudaFree(g->d_prec_cho70); cudaFree(g->d_prec_choT); cudaFree(g->d_prec); cudaFree(g->d_consts);
+    cudaFree(g->d_mean); cudaFree(g->d_prec_cho); cudaFree(g->d_prec_cho70); cudaFree(g->d_prec_choT); cudaFree(g->d_prec); cudaFree(g->d_consts); cudaFree(g->d_sigma);
     delete g;
 }
 

@@ -150,4 +150,5 @@ struct b3d_gmm {
     double* d_prec_choT = nullptr;   // nComps x 69 x 69, L^T row-major (coalesced column access)
     double* d_prec = nullptr;        // nComps x 69 x 69  P = L L^T (symmetric)
     double* d_consts = nullptr;      // nComps  consts_log
+    double* d_sigma = nullptr;       // nComps  upper bound of ||L_i||_2
 };

@@ -38,6 +38,7 @@ struct FitConst {
     const double* gmm_LT;                  // ncomp x 69 x 69, = L^T row-major
     const double* gmm_P;                   // ncomp x 69 x 69, = L L^T
     const double* gmm_consts;              // ncomp
+    const double* gmm_sigma;               // ncomp: upper bound of the spectral norm of L_i
 };
 
 // host side (fit_single.cu): fills the launch-constant block
@@ -301,6 +302,79 @@ __device__ void eval_reproj(const FitConst* __restrict__ C, const double* x, con
 
 // packed lower-triangular index, i >= j
 __device__ __forceinline__ int tri(int i, int j) { return i * (i + 1) / 2 + j; }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Line-search trial point: per keypoint the robustified cost rho / 2 at x and its derivative along the direction dx (both in the
+// 86-layout), i.e. res^T (J dx) of the robustified block, by forward-mode propagation through the chain — no Jacobian is formed.
+// What Ceres' Armijo search needs at a trial point is exactly the cost and this directional derivative.
+// ---------------------------------------------------------------------------------------------------------------
+template <int T>
+__device__ void eval_reproj_dir(const FitConst* __restrict__ C, const double* x, const double* dx, const b3d_kp* __restrict__ kps, int nkp,
+                                const double* R0, EvalTmp& S, double* kcost, double* kdphi) {
+    const int tid = threadIdx.x;
+    double (*Mj)[9] = reinterpret_cast<double (*)[9]>(&S.N[0][0][0]);     // d Rot(aa_j) along daa_j, one 3 x 3 per joint
+    double (*dbone)[3] = reinterpret_cast<double (*)[3]>(&S.q[0][0][0]);   // d bone along dw
+    static_assert(sizeof(S.N) >= sizeof(double) * NJ * 9 && sizeof(S.q) >= sizeof(double) * NJ * 3, "scratch aliases");
+    for (int t = tid; t < NJ + 3 * NJ; t += T) {
+        if (t < NJ) {
+            const int o = t == 0 ? IDX_RAA : IDX_JAA + 3 * (t - 1);
+            aa_rotation<true>(x + o, S.R[t], S.dR[t]);
+            const double d0 = dx[o], d1 = dx[o + 1], d2 = dx[o + 2];
+#pragma unroll
+            for (int e = 0; e < 9; ++e) Mj[t][e] = d0 * S.dR[t][e] + d1 * S.dR[t][9 + e] + d2 * S.dR[t][18 + e];
+        } else {
+            const int j = (t - NJ) / 3, c = (t - NJ) % 3;
+            double b = C->offset[j][c], db = 0.0;
+            if (C->with_shape) {
+#pragma unroll
+                for (int s = 0; s < NS; ++s) { b += C->DB[j][c][s] * x[IDX_W + s]; db += C->DB[j][c][s] * dx[IDX_W + s]; }
+            }
+            S.bone[j][c] = b;
+            dbone[j][c] = db;
+        }
+    }
+    __syncthreads();
+    if (tid < nkp) {
+        const int k = tid;
+        const int jid = clamp_jid(kps[k].jid);
+        const int len = C->chain_len[jid];
+        double q[3] = {S.bone[jid][0], S.bone[jid][1], S.bone[jid][2]};
+        double dq[3] = {dbone[jid][0], dbone[jid][1], dbone[jid][2]};
+        for (int i = 1; i < len; ++i) {
+            const int a = C->chain[jid][i];
+            double o[3], u[3], v[3];
+            mat3_vec(S.R[a], q, o);
+            mat3_vec(Mj[a], q, u);
+            mat3_vec(S.R[a], dq, v);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) { q[c] = o[c] + S.bone[a][c]; dq[c] = (u[c] + v[c]) + dbone[a][c]; }
+        }
+        double pc[3], dpc[3], Xp[3], dXp[3], tmp[3];
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+            pc[r] = R0[r] * q[0] + R0[3 + r] * q[1] + R0[6 + r] * q[2];
+            dpc[r] = R0[r] * dq[0] + R0[3 + r] * dq[1] + R0[6 + r] * dq[2];
+        }
+        mat3_vec(S.R[0], pc, Xp);
+        mat3_vec(Mj[0], pc, dXp);
+        mat3_vec(S.R[0], dpc, tmp);
+        const double s = x[IDX_S], ds = dx[IDX_S];
+        const double X0 = s * Xp[0] + x[IDX_T], X1 = s * Xp[1] + x[IDX_T + 1], X2 = s * Xp[2] + x[IDX_T + 2];
+        const double dX0 = ds * Xp[0] + s * (dXp[0] + tmp[0]) + dx[IDX_T], dX1 = ds * Xp[1] + s * (dXp[1] + tmp[1]) + dx[IDX_T + 1],
+                     dX2 = ds * Xp[2] + s * (dXp[2] + tmp[2]) + dx[IDX_T + 2];
+        const double iz = 1.0 / X2;
+        const double r0 = C->cam[0] * X0 * iz + C->cam[2] - kps[k].u;
+        const double r1 = C->cam[1] * X1 * iz + C->cam[3] - kps[k].v;
+        const double dr0 = C->cam[0] * iz * (dX0 - X0 * iz * dX2), dr1 = C->cam[1] * iz * (dX1 - X1 * iz * dX2);
+        const double sq = r0 * r0 + r1 * r1, b = C->huber * C->huber;
+        double rho0, rho1;
+        if (sq > b) { const double rr = sqrt(sq); rho0 = 2.0 * C->huber * rr - b; rho1 = fmax(DBL_MIN, C->huber / rr); }
+        else { rho0 = sq; rho1 = 1.0; }
+        kcost[k] = 0.5 * rho0;
+        kdphi[k] = rho1 * (r0 * dr0 + r1 * dr1);
+    }
+    __syncthreads();
+}
 
 // ---------------------------------------------------------------------------------------------------------------
 // Dense variant for the single-frame kernel: the robustified Jacobian of all reprojection blocks as one row-major

@@ -15,28 +15,6 @@ struct LsSample { double x, value, gradient; bool valid; };
 
 __device__ double poly_eval(const double* p, int nc, double x) { double v = 0; for (int i = 0; i < nc; ++i) v = v * x + p[i]; return v; }
 
-// Gaussian elimination with full pivoting (Eigen FullPivLU as used by ceres polynomial.cc); n <= 6
-__device__ bool lu_solve(double* A, int n, double* b, double* x) {
-    int perm[6];
-    for (int i = 0; i < n; ++i) perm[i] = i;
-    for (int k = 0; k < n; ++k) {
-        int pr = k, pc = k; double best = 0.0;
-        for (int i = k; i < n; ++i) for (int j = k; j < n; ++j) if (fabs(A[i * n + j]) > best) { best = fabs(A[i * n + j]); pr = i; pc = j; }
-        if (best == 0.0) return false;
-        if (pr != k) { for (int j = 0; j < n; ++j) { double t = A[k * n + j]; A[k * n + j] = A[pr * n + j]; A[pr * n + j] = t; } double t = b[k]; b[k] = b[pr]; b[pr] = t; }
-        if (pc != k) { for (int i = 0; i < n; ++i) { double t = A[i * n + k]; A[i * n + k] = A[i * n + pc]; A[i * n + pc] = t; } int t = perm[k]; perm[k] = perm[pc]; perm[pc] = t; }
-        for (int i = k + 1; i < n; ++i) {
-            const double f = A[i * n + k] / A[k * n + k];
-            for (int j = k; j < n; ++j) A[i * n + j] -= f * A[k * n + j];
-            b[i] -= f * b[k];
-        }
-    }
-    double z[6];
-    for (int i = n - 1; i >= 0; --i) { double s = b[i]; for (int j = i + 1; j < n; ++j) s -= A[i * n + j] * z[j]; z[i] = s / A[i * n + i]; }
-    for (int i = 0; i < n; ++i) x[perm[i]] = z[i];
-    return true;
-}
-
 // real parts of the roots of a polynomial of degree <= 4 (coefficients highest first).  Called by ALL lanes of one warp:
 // degrees 1 and 2 in closed form; degrees 3 and 4 by the Aberth-Ehrlich simultaneous iteration with one lane per root (the
 // other lanes idle along), which is what made the single-thread version the longest serial stretch of a line search.
@@ -101,22 +79,61 @@ __device__ int poly_root_real_parts(const double* pin, int nc, double* out) {
     return deg;
 }
 
-__device__ __forceinline__ double ipow(double x, int k) { double v = 1.0; for (int i = 0; i < k; ++i) v *= x; return v; }
+// Coefficients (highest degree first) of the polynomial of degree 2 NS - 1 that interpolates value and gradient at NS distinct
+// points: ceres::FindInterpolatingPolynomial.  Ceres solves the 2 NS x 2 NS Vandermonde-type system with Eigen's FullPivLU; the same
+// polynomial is formed here through Hermite divided differences (nodes x_0, x_0, x_1, x_1, ...) expanded into the monomial
+// basis — every index is a compile-time constant, so the whole table lives in registers (the LU on a local-memory matrix was the
+// longest one-warp stretch of a line search: profiles/r02 fit_single notes).  Returns false if two sample points coincide.
+template <int NS>
+__device__ __forceinline__ bool hermite_coefficients(const LsSample* s, double* coef /* 2 NS */) {
+    constexpr int N = 2 * NS;
+    double z[N], d[N];
+#pragma unroll
+    for (int q = 0; q < NS; ++q) { z[2 * q] = s[q].x; z[2 * q + 1] = s[q].x; d[2 * q] = s[q].value; d[2 * q + 1] = s[q].value; }
+    // first-order differences: the gradient inside a doubled node, a secant between different nodes
+    bool ok = true;
+#pragma unroll
+    for (int i = N - 1; i >= 1; --i) {
+        if (i & 1) d[i] = s[i >> 1].gradient;
+        else {
+            const double h = z[i] - z[i - 1];
+            ok = ok && h != 0.0;
+            d[i] = (d[i] - d[i - 1]) / h;
+        }
+    }
+    // higher orders, in place from the bottom of each column
+#pragma unroll
+    for (int k = 2; k < N; ++k)
+#pragma unroll
+        for (int i = N - 1; i >= k; --i) {
+            const double h = z[i] - z[i - k];
+            ok = ok && h != 0.0;
+            d[i] = (d[i] - d[i - 1]) / h;
+        }
+    // Newton form sum_k d_k prod_{m < k} (x - z_m)  ->  monomial coefficients, lowest degree first in c[]
+    double c[N];
+#pragma unroll
+    for (int i = 0; i < N; ++i) c[i] = 0.0;
+    c[0] = d[N - 1];
+#pragma unroll
+    for (int k = N - 2; k >= 0; --k) {
+        // c(x) <- c(x) (x - z_k) + d_k ; the polynomial held so far has degree N - 2 - k
+#pragma unroll
+        for (int i = N - 1; i >= 1; --i) c[i] = c[i - 1] - z[k] * c[i];
+        c[0] = d[k] - z[k] * c[0];
+    }
+#pragma unroll
+    for (int i = 0; i < N; ++i) coef[i] = c[N - 1 - i];
+    return ok;
+}
 
 // ceres MinimizeInterpolatingPolynomial: every sample carries value and gradient.  Called by all lanes of one warp (uniform).
 __device__ double minimize_interpolating_polynomial(const LsSample* s, int ns, double x_min, double x_max) {
     const int nc = 2 * ns, degree = nc - 1;
-    double lhs[36], rhs[6], coef[6];
-    for (int i = 0; i < nc * nc; ++i) lhs[i] = 0.0;
-    int row = 0;
-    for (int q = 0; q < ns; ++q) {
-        for (int j = 0; j <= degree; ++j) lhs[row * nc + j] = ipow(s[q].x, degree - j);
-        rhs[row++] = s[q].value;
-        for (int j = 0; j < degree; ++j) lhs[row * nc + j] = (degree - j) * ipow(s[q].x, degree - j - 1);
-        rhs[row++] = s[q].gradient;
-    }
+    double coef[6];
     double best_x = (x_min + x_max) / 2.0;
-    if (!lu_solve(lhs, nc, rhs, coef)) return best_x;
+    const bool ok = ns == 3 ? hermite_coefficients<3>(s, coef) : hermite_coefficients<2>(s, coef);
+    if (!ok) return best_x;
     double best_v = poly_eval(coef, nc, best_x);
     const double vmin = poly_eval(coef, nc, x_min);
     if (vmin < best_v) { best_v = vmin; best_x = x_min; }

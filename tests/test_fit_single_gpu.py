@@ -228,3 +228,47 @@ def test_fit_single_baseline_config_at_stated_size(api, orc, gmodel, ggmm, omode
         if ga.any():
             assert d["final"][ga].max() < GAUGE_COST_TOL
             assert int((d["pose"][ga] > PARAM_TOL).sum()) <= 2 * noise + 5
+
+
+@pytest.mark.parametrize("name", ["C1", "C2"])
+def test_fit_single_queue_schedule_is_bit_identical(api, gmodel, ggmm, synth, model_np, prior_np, name):
+    """Batches larger than the machine's CTA slots run through a persistent kernel: a fresh frame checkpoints itself after a capped
+    number of iterations and is resumed from a device-side queue (csrc/fit_single.cu FitCkpt).  Whatever the cap, every output and
+    every trace record must equal the one-CTA-per-frame solve bit for bit."""
+    nfr = 700          # more frames than 2 CTAs x 148 SMs
+    fr, kw, use_gmm = _cfg(name, synth, model_np, prior_np, nfr, 77, drop=0.1)
+    cam = (synth.FX, synth.FY, synth.CX, synth.CY)
+    lib = api.lib()
+    run = lambda: api.fit_single_batch(gmodel, ggmm if use_gmm else None, api.fit_opts(cam=cam, **kw), fr["kps"], fr["nkp"], fr["R0"], fr["sim3"], fr["w"])
+    try:
+        lib.b3d_debug_fit_stop_at(0)
+        ref = run()
+        assert ref["niters"].max() > 40          # some frames run long past the caps below
+        for cap in (1, 7, 20, 33):
+            lib.b3d_debug_fit_stop_at(cap)
+            got = run()
+            for k in ("sim3", "w", "jointAA", "usable", "niters", "term"):
+                assert np.array_equal(got[k], ref[k]), (cap, k)
+            assert got["trace"].tobytes() == ref["trace"].tobytes(), cap
+    finally:
+        lib.b3d_debug_fit_stop_at(-1)
+
+
+def test_gmm_component_screening_is_bit_identical(api, gmodel, ggmm, synth, model_np, prior_np):
+    """The kernel skips GMM components that provably cannot be the argmin of GaussianMixture::residual (norm bounds from the last
+    exact evaluation of each component).  Switching the screening off must not change a single bit of any output or trace record."""
+    fr, kw, _ = _cfg("C2", synth, model_np, prior_np, 96, 314, drop=0.05)
+    cam = (synth.FX, synth.FY, synth.CX, synth.CY)
+    lib = api.lib()
+    run = lambda: api.fit_single_batch(gmodel, ggmm, api.fit_opts(cam=cam, **kw), fr["kps"], fr["nkp"], fr["R0"], fr["sim3"], fr["w"])
+    try:
+        assert lib.b3d_debug_gmm_screen(0) == 0
+        ref = run()
+        assert lib.b3d_debug_gmm_screen(1) == 0
+        got = run()
+    finally:
+        lib.b3d_debug_gmm_screen(1)
+    for k in ("sim3", "w", "jointAA", "usable", "niters", "term"):
+        assert np.array_equal(got[k], ref[k]), k
+    assert got["trace"].tobytes() == ref["trace"].tobytes()
+    assert len(set(int(a) for f in range(96) for a in ref["trace"][f]["aux"][:ref["niters"][f]])) >= 2      # more than one component is active

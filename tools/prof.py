@@ -124,8 +124,30 @@ def phases(n=148, mode="C2"):
     for b in order:
         print(f"  block {b}: {cy[b] / 1e6:.2f} Mcycles, iters {int(ni[b])}, per-iter {per[b]:.0f}, line-search fallbacks {lsv[b]}")
     print("frames with line-search fallbacks:", int((lsv > 0).sum()), "total fallbacks", int(lsv.sum()))
+    t0, t1 = (C.c_longlong * 1024)(), (C.c_longlong * 1024)()
+    lib.b3d_debug_block_times(t0, t1)
+    t0, t1 = np.array(t0[:m], dtype=np.float64), np.array(t1[:m], dtype=np.float64)
+    base = t0.min()
+    print("kernel span %.3f ms (first frame start to last frame end)" % ((t1.max() - base) * 1e-6))
+    for b in order:
+        print(f"  block {b}: started at {(t0[b] - base) * 1e-6:.3f} ms, ended at {(t1[b] - base) * 1e-6:.3f} ms, busy {cy[b] / 1e6:.2f} Mcycles "
+              f"-> {cy[b] / max(t1[b] - t0[b], 1.0):.3f} cycles/ns if it ran without waiting")
+    late = np.argsort(-t1)[:5]
+    print("last to finish:", [(int(b), round((t0[b] - base) * 1e-6, 3), round((t1[b] - base) * 1e-6, 3), int(ni[b])) for b in late])
     lib.b3d_debug_phase_timing(0)
 
+
+def passes(n=1000):
+    """Timing of the persistent kernel's frame queue for several checkpoint caps (0 = one CTA per frame)."""
+    for cap in (0, 8, 12, 16, 20, 24, 30, 40):
+        lib.b3d_debug_fit_stop_at(cap)
+        print("stop_at", cap, end=": ")
+        fit(n, "C2", reps=5)
+    lib.b3d_debug_fit_stop_at(-1)
+
+
+if __name__ == "__main__" and sys.argv[1] == "passes":
+    passes(int(sys.argv[2]) if len(sys.argv) > 2 else 1000)
 
 if __name__ == "__main__" and sys.argv[1] == "phases":
     phases(int(sys.argv[2]) if len(sys.argv) > 2 else 148, sys.argv[3] if len(sys.argv) > 3 else "C2")
