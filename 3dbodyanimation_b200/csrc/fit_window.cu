@@ -16,7 +16,7 @@
 
 namespace b3d {
 
-constexpr int FW_THREADS = 256;
+constexpr int FW_THREADS = 512;         // one 4 x 4 tile of a frame's 164 x 76 rows per thread in the sweep (446 tiles)
 constexpr int NB = NPF;                 // 76: diagonal block size
 constexpr int LDM = NB + 1;             // padded leading dimension of the shared-memory blocks (bank-conflict free columns)
 constexpr int ROW_LO = NB;              // rows 76..151 of M: next off-diagonal block L_{f+1,f}
@@ -31,6 +31,20 @@ constexpr double wMinDiagonal = 1e-6, wMaxDiagonal = 1e32;
 constexpr double wMinRelativeDecrease = 1e-3;
 constexpr double wFunctionTolerance = 1e-6, wGradientTolerance = 1e-10, wParameterTolerance = 1e-8;
 constexpr int wMaxConsecutiveInvalidSteps = 5;
+
+// Optional phase timing (debug hook b3d_debug_win_timing): cycles of block 0 per phase, accumulated in shared memory.
+__device__ long long g_win_phase[16];
+__device__ int g_win_phase_on;
+__device__ __forceinline__ long long* win_phase_acc() {
+    __shared__ long long s_win_phase[16];
+    return s_win_phase;
+}
+struct WinTimer {
+    long long t;
+    bool on;
+    __device__ void start() { on = g_win_phase_on != 0 && blockIdx.x == 0 && threadIdx.x == 0; if (on) t = clock64(); }
+    __device__ void mark(int i) { if (on) { const long long u = clock64(); win_phase_acc()[i] += u - t; t = u; } }
+};
 
 struct WinWs {
     double *x, *cand, *g, *gs, *scale, *diag, *y, *delta, *z, *tmp;   // n each
@@ -51,13 +65,9 @@ struct WinWs {
 };
 
 struct WinEval {
-    EvalOut out;
+    EvalDense out;                        // dense robustified Jacobian [34][88] (lm_device.cuh) + residuals
     EvalTmp ev;
-    double Hf[HFTRI];                     // one frame's 86 x 86 J^T J, packed lower
     double gf[NFULL];
-    uint32_t kmask[NFULL];
-    uint8_t slot[MAXKP][NFULL + 2];
-    uint8_t fcol[MAXKP][NNZPAD];
 };
 
 struct WinChain {
@@ -67,9 +77,24 @@ struct WinChain {
     double rhs[NB];
 };
 
+// Forward sweep with the frame's rows held in registers, one 4 x 4 tile per thread (win_solve): the 164 rows of a frame are 41 tile
+// rows — 19 of the diagonal block A (lower triangle), 19 of the next off-diagonal block B (row block R is zero left of column block
+// R: B = diagonal matrix x L^-T), 3 of the arrow rows and the right-hand side — times 19 tile columns.
+constexpr int WT_NC = NB / 4;                 // 19 tile columns / panels
+constexpr int WT_RA = 0, WT_RB = WT_NC, WT_RW = 2 * WT_NC, WT_NR = 2 * WT_NC + 3;   // first tile row of A / B / W; 41 tile rows
+constexpr int WT_TRI = WT_NC * (WT_NC + 1) / 2;                                       // 190 tiles in a triangle
+constexpr int WT_TILES = 2 * WT_TRI + 3 * WT_NC + 9;                                  // + 57 arrow tiles + 9 tiles of the w Schur block = 446
+static_assert(NB % 4 == 0 && NS + 1 <= 12, "tile grid of the multi-frame sweep");
+struct WinTiles {
+    double2 pan[4][2][WT_NR + 1];             // current panel's solved rows: [panel column][rows 0-1 | 2-3 of a tile][tile row]
+    double2 bp[WT_NC][4][2][WT_NR - WT_RB];   // the B and W rows of EVERY panel of the frame just swept: the next frame's Schur update
+    double dk[2][4][4];                       // diagonal tiles by panel parity: strict lower part = L, diagonal = 1 / L_jj
+};
+
 union WinUnion {
     WinEval e;
     WinChain c;
+    WinTiles t;
 };
 
 struct WinSmem {
@@ -83,15 +108,23 @@ struct WinSmem {
 };
 
 // ---- evaluate every frame of the problem at parameters xp (n = 76 F + 10) -----------------------------------------------
-// Returns the cost.  JAC: fills Hd / Ha / Hw (UNSCALED) and g in the workspace.
+// Returns the cost.  JAC: fills Hd / Ha / Hw (UNSCALED) and g in the workspace.  A frame's 86 x 86 normal equations are a SYRK of
+// its dense Jacobian over 4 x 4 register tiles (thread (ti, tj), 253 tiles), scattered straight into the block structure.
 template <int T, bool JAC>
 __device__ double win_evaluate(const FitConst* __restrict__ C, int F, const double* __restrict__ xp, const b3d_kp* __restrict__ kps,
                                const int32_t* __restrict__ nkp_all, const double* __restrict__ R0_all, WinWs& W, WinSmem& S) {
-    const int tid = threadIdx.x, lane = tid & 31;
+    const int tid = threadIdx.x;
     WinEval& E = S.u.e;
     const double bp2 = C->beta_pose * C->beta_pose, bs2 = C->beta_shape * C->beta_shape, lam = C->lambda_temp, lam2 = lam * lam;
     const bool pose_prior = C->beta_pose > 0.0, shape_prior = C->beta_shape > 0.0, temporal = lam > 0.0 && F > 1;
     double part = 0.0;                      // this thread's share of the cost
+    WinTimer wt;
+    wt.start();
+    // this thread's tile of the 86 x 86 lower triangle (22 tile rows)
+    int ti = 0;
+    while ((ti + 1) * (ti + 2) / 2 <= tid) ++ti;
+    const int tj = tid - ti * (ti + 1) / 2;
+    const bool tile_ok = ti < (NFULL + 3) / 4;
     if (JAC) {
         for (int k = tid; k < NS * NS; k += T) S.Hw[k] = 0.0;
         if (tid < NS) S.gw[tid] = 0.0;
@@ -104,61 +137,69 @@ __device__ double win_evaluate(const FitConst* __restrict__ C, int F, const doub
         for (int k = tid; k < NB; k += T) S.xfull[k] = xf[k];
         if (tid < 9) S.R0[tid] = R0_all[(size_t)f * 9 + tid];
         __syncthreads();
-        eval_reproj<T, JAC>(C, S.xfull, kps + (size_t)f * MAXKP, nkp, S.R0, E.ev, E.out);
+        wt.mark(5);
+        eval_reproj_dense<T, JAC>(C, S.xfull, kps + (size_t)f * MAXKP, nkp, S.R0, E.ev, E.out);
+        wt.mark(JAC ? 6 : 4);
         if (tid < nkp) part += E.out.kcost[tid];
         if (pose_prior)
             for (int k = tid; k < NPRI; k += T) { const double r = S.xfull[IDX_JAA + k] * C->beta_pose; part += 0.5 * r * r; }
         if (!JAC) continue;
-        // ---- this frame's 86 x 86 normal equations in shared memory (all 86 columns are free in the multi-frame problem) ----
-        for (int k = tid; k < NFULL; k += T) E.kmask[k] = 0u;
-        for (int e = tid; e < HFTRI; e += T) E.Hf[e] = 0.0;
-        __syncthreads();
-        for (int t = tid; t < nkp * NNZPAD; t += T) {
-            const int k = t / NNZPAD, sl = t % NNZPAD;
-            if (sl < E.out.jnnz[k]) {
-                const int col = E.out.jcol[k][sl];
-                E.slot[k][col] = (uint8_t)sl;
-                E.fcol[k][sl] = (uint8_t)col;
-                atomicOr(&E.kmask[col], 1u << k);
-            }
-        }
-        __syncthreads();
-        for (int i = tid >> 5; i < NFULL; i += T / 32) {      // a warp owns row i; lanes cover the slots of each keypoint touching i
-            uint32_t m = E.kmask[i];
+        const int nrow = 2 * nkp;
+        // gradient of the reprojection blocks: column sums in row order (all 86 columns are free in the multi-frame problem)
+        for (int i = tid; i < NFULL; i += T) {
             double gacc = 0.0;
-            while (m) {
-                const int k = __ffs(m) - 1;
-                m &= m - 1;
-                const int sa = E.slot[k][i], nnz = E.out.jnnz[k];
-                const double a0 = E.out.J[k][0][sa], a1 = E.out.J[k][1][sa];
-                for (int sb = lane; sb < nnz; sb += 32) {
-                    const int j = E.fcol[k][sb];
-                    if (j <= i) E.Hf[tri(i, j)] += a0 * E.out.J[k][0][sb] + a1 * E.out.J[k][1][sb];
-                }
-                __syncwarp();     // the next keypoint's lanes may hit the same elements of row i (different slot -> lane mapping)
-                gacc += a0 * E.out.res[k][0] + a1 * E.out.res[k][1];
+            for (int r = 0; r < nrow; r += 2)
+                gacc += E.out.J[r][jpos(i)] * E.out.res[r >> 1][0] + E.out.J[r + 1][jpos(i)] * E.out.res[r >> 1][1];
+            E.gf[i] = gacc;
+        }
+        double* Hd = W.Hd + (size_t)f * NB * NB;
+        double* Ha = W.Ha + (size_t)f * NS * NB;
+        const int nadj = temporal ? (f > 0) + (f < F - 1) : 0;
+        if (tile_ok) {
+            double acc[4][4];
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+            const double2* Ja = reinterpret_cast<const double2*>(&E.out.J[0][0]) + ti;
+            const double2* Jb = reinterpret_cast<const double2*>(&E.out.J[0][0]) + tj;
+#pragma unroll 2
+            for (int r = 0; r < nrow; ++r) {
+                const double2 x01 = Ja[r * (LDJ / 2)], x23 = Ja[r * (LDJ / 2) + LDJ / 4];
+                const double2 y01 = Jb[r * (LDJ / 2)], y23 = Jb[r * (LDJ / 2) + LDJ / 4];
+                const double xv[4] = {x01.x, x01.y, x23.x, x23.y}, yv[4] = {y01.x, y01.y, y23.x, y23.y};
+#pragma unroll
+                for (int a = 0; a < 4; ++a)
+#pragma unroll
+                    for (int b = 0; b < 4; ++b) acc[a][b] = fma(xv[a], yv[b], acc[a][b]);
             }
-            if (lane == 0) E.gf[i] = gacc;
+            // scatter into the block structure, adding the L2 pose prior and the temporal terms on the diagonal
+#pragma unroll
+            for (int a = 0; a < 4; ++a) {
+                const int i = 4 * ti + a;
+#pragma unroll
+                for (int b = 0; b < 4; ++b) {
+                    const int j = 4 * tj + b;
+                    if (i >= NFULL || j > i) continue;
+                    double v = acc[a][b];
+                    if (i < NB) {
+                        if (i == j) {
+                            if (pose_prior && i >= IDX_JAA) v += bp2;
+                            if (i >= 1) v += nadj * lam2;                 // Vec3DiffCost on every parameter but the scale
+                        }
+                        Hd[i * NB + j] = v;
+                        Hd[j * NB + i] = v;
+                    } else if (j < NB) {
+                        Ha[(i - NB) * NB + j] = v;
+                    } else {                                              // shape x shape: summed over the frames (one owner per entry)
+                        S.Hw[(i - NB) * NS + (j - NB)] += v;
+                        if (i != j) S.Hw[(j - NB) * NS + (i - NB)] += v;
+                    }
+                }
+            }
         }
         __syncthreads();
-        // ---- scatter into the block structure, adding the L2 pose prior and the temporal terms ----
-        double* Hd = W.Hd + (size_t)f * NB * NB;
-        const int nadj = temporal ? (f > 0) + (f < F - 1) : 0;
-        for (int idx = tid; idx < NB * NB; idx += T) {
-            const int r = idx / NB, c = idx % NB;
-            double v = r >= c ? E.Hf[tri(r, c)] : E.Hf[tri(c, r)];
-            if (r == c) {
-                if (pose_prior && r >= IDX_JAA) v += bp2;
-                if (r >= 1) v += nadj * lam2;                     // Vec3DiffCost on every parameter but the scale
-            }
-            Hd[idx] = v;
-        }
-        double* Ha = W.Ha + (size_t)f * NS * NB;
-        for (int idx = tid; idx < NS * NB; idx += T) Ha[idx] = E.Hf[tri(IDX_W + idx / NB, idx % NB)];
-        for (int idx = tid; idx < NS * NS; idx += T) {
-            const int s = idx / NS, t2 = idx % NS;
-            S.Hw[idx] += s >= t2 ? E.Hf[tri(IDX_W + s, IDX_W + t2)] : E.Hf[tri(IDX_W + t2, IDX_W + s)];
-        }
+        wt.mark(7);
         if (tid < NS) S.gw[tid] += E.gf[IDX_W + tid];
         for (int k = tid; k < NB; k += T) {
             double v = E.gf[k];
@@ -169,6 +210,7 @@ __device__ double win_evaluate(const FitConst* __restrict__ C, int F, const doub
             }
             W.g[(size_t)f * NB + k] = v;
         }
+        wt.mark(8);
     }
     // temporal residuals lambda (x_f - x_{f+1}) and the shape prior
     if (temporal)
@@ -196,126 +238,222 @@ __device__ bool win_solve(const FitConst* __restrict__ C, int F, double radius, 
     const double lam2 = C->lambda_temp * C->lambda_temp;
     const bool temporal = C->lambda_temp > 0.0 && F > 1;
     // running Schur complement of the arrow block: thread (s, t), t <= s, owns Sw[s][t]; threads 64..73 own zw[s]
-    int ss = -1, st = -1;
-    if (tid < NS * (NS + 1) / 2) { int s = 0; while ((s + 1) * (s + 2) / 2 <= tid) ++s; ss = s; st = tid - s * (s + 1) / 2; }
-    double sw_acc = 0.0, zw_acc = 0.0;
+    WinTimer wt;
+    wt.start();
+    WinTiles& Q = S.u.t;
+    // ---- this thread's tile: group 0 = A (ti >= tj), 1 = B (row block R <= column block C), 2 = arrow rows / right-hand side,
+    //      3 = one of the 3 x 3 tiles of sum_f [W_f ; z_f] [W_f ; z_f]^T (the w Schur complement), kept across the frames ----
+    int grp = -1, ti = 0, tj = 0;
+    if (tid < WT_TRI) {
+        int r = 0;
+        while ((r + 1) * (r + 2) / 2 <= tid) ++r;
+        grp = 0; ti = r; tj = tid - r * (r + 1) / 2;
+    } else if (tid < 2 * WT_TRI) {
+        const int u = tid - WT_TRI;
+        int c = 0;
+        while ((c + 1) * (c + 2) / 2 <= u) ++c;
+        grp = 1; tj = c; ti = WT_RB + (u - c * (c + 1) / 2);
+    } else if (tid < 2 * WT_TRI + 3 * WT_NC) {
+        const int u = tid - 2 * WT_TRI;
+        grp = 2; ti = WT_RW + u / WT_NC; tj = u % WT_NC;
+    } else if (tid < WT_TILES) {
+        const int u = tid - 2 * WT_TRI - 3 * WT_NC;
+        grp = 3; ti = WT_RW + u / 3; tj = WT_RW + u % 3;      // tj is a tile ROW here: the tile is rows(ti) x rows(tj)^T
+    }
+    static_assert(T >= WT_TILES, "one tile per thread");
+    double a[4][4], sacc[4][4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) sacc[r][c] = 0.0;
     bool ok = true;
+    if (tid == 0) S.flag = 1;
+    __syncthreads();
     for (int f = 0; f < F && ok; ++f) {
         const bool has_next = temporal && f < F - 1;
         const bool has_prev = temporal && f > 0;
-        const int nrows = MROWS;
-        // (1) load this frame's rows: [Hd_f + damping ; next off-diagonal block ; Ha_f ; gs_f]
+        // (1) this frame's rows: [Hd_f + damping ; -lambda^2 S_f E S_f+1 ; Ha_f ; gs_f], minus the products with the previous frame's
+        //     block row [B ; W ; z] (its panels are still in Q.bp)
         const double* Hd = W.Hd + (size_t)f * NB * NB;
-        for (int idx = tid; idx < NB * NB; idx += T) {
-            const int r = idx / NB, c = idx % NB;
-            double v = Hd[idx];
-            if (r == c) { const double l = sqrt(W.diag[(size_t)f * NB + r] / radius); v += l * l; }
-            K.M[r][c] = v;
-        }
-        for (int idx = tid; idx < NB * NB; idx += T) {
-            const int r = idx / NB, c = idx % NB;
-            double v = 0.0;
-            if (has_next && r == c && r >= 1) v = -lam2 * W.scale[(size_t)f * NB + r] * W.scale[(size_t)(f + 1) * NB + r];
-            K.M[ROW_LO + r][c] = v;
-        }
         const double* Ha = W.Ha + (size_t)f * NS * NB;
-        for (int idx = tid; idx < NS * NB; idx += T) K.M[ROW_W + idx / NB][idx % NB] = Ha[idx];
-        for (int c = tid; c < NB; c += T) K.M[ROW_Z][c] = W.gs[(size_t)f * NB + c];
-        __syncthreads();
-        // (2) subtract the products with the previous block row P = [L_{f,f-1} ; W_{f-1} ; z_{f-1}].  L_{f,f-1} is upper
-        //     triangular (it is a diagonal matrix times L^-T), so row r of it starts at column r.
-        if (has_prev) {
-            for (int idx = tid; idx < NB * NB; idx += T) {
-                const int r = idx / NB, c = idx % NB;
-                if (c > r) continue;
-                double a0 = 0.0, a1 = 0.0;
-                int k = r;
-                for (; k + 1 < NB; k += 2) { a0 += K.P[r][k] * K.P[c][k]; a1 += K.P[r][k + 1] * K.P[c][k + 1]; }
-                if (k < NB) a0 += K.P[r][k] * K.P[c][k];
-                K.M[r][c] -= a0 + a1;
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int j = 4 * tj + c;
+                double v = 0.0;
+                if (grp == 0) {
+                    const int i = 4 * ti + r;
+                    if (j <= i) {
+                        v = Hd[i * NB + j];
+                        if (i == j) { const double l = sqrt(W.diag[(size_t)f * NB + i] / radius); v += l * l; }
+                    }
+                } else if (grp == 1) {
+                    const int i = 4 * (ti - WT_RB) + r;
+                    if (has_next && i == j && i >= 1) v = -lam2 * W.scale[(size_t)f * NB + i] * W.scale[(size_t)(f + 1) * NB + i];
+                } else if (grp == 2) {
+                    const int sidx = 4 * (ti - WT_RW) + r;
+                    if (sidx < NS) v = Ha[sidx * NB + j];
+                    else if (sidx == NS) v = W.gs[(size_t)f * NB + j];
+                }
+                a[r][c] = v;
             }
-            for (int idx = tid; idx < (NS + 1) * NB; idx += T) {
-                const int q = idx / NB, c = idx % NB;            // q: arrow row s (0..9) or the right-hand side (10)
-                double a0 = 0.0, a1 = 0.0;
-                int k = c;
-                for (; k + 1 < NB; k += 2) { a0 += K.P[NB + q][k] * K.P[c][k]; a1 += K.P[NB + q][k + 1] * K.P[c][k + 1]; }
-                if (k < NB) a0 += K.P[NB + q][k] * K.P[c][k];
-                K.M[ROW_W + q][c] -= a0 + a1;
+        if (has_prev && (grp == 0 || grp == 2)) {
+            // A_f -= B B^T, [W ; z]_f -= [W ; z] B^T over the panels in which both row blocks are non-zero (B is upper triangular)
+            const int rb = (grp == 0 ? ti : ti - WT_RB), cb = tj;      // row / column tile rows inside Q.bp (B rows 0..18, W rows 19..21)
+            for (int k = (grp == 0 ? ti : tj); k < WT_NC; ++k) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const double2 r01 = Q.bp[k][q][0][rb], r23 = Q.bp[k][q][1][rb], c01 = Q.bp[k][q][0][cb], c23 = Q.bp[k][q][1][cb];
+                    const double rv[4] = {r01.x, r01.y, r23.x, r23.y}, cv[4] = {c01.x, c01.y, c23.x, c23.y};
+#pragma unroll
+                    for (int r = 0; r < 4; ++r)
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) a[r][c] = fma(-rv[r], cv[c], a[r][c]);
+                }
+            }
+        }
+        __syncthreads();           // every thread is done with the previous frame's Q.bp
+        wt.mark(10);
+        // factor the thread's own diagonal tile in registers and publish it
+        auto factor_own = [&](int k) {
+            bool bad = false;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const double piv = a[c][c];
+                if (bad || !(piv > 0.0)) { bad = true; continue; }
+                const double inv = rsqrt(piv);
+                a[c][c] = inv;
+#pragma unroll
+                for (int r = c + 1; r < 4; ++r) a[r][c] *= inv;
+#pragma unroll
+                for (int c2 = c + 1; c2 < 4; ++c2)
+#pragma unroll
+                    for (int r = c2; r < 4; ++r) a[r][c2] -= a[r][c] * a[c2][c];
+                W.invd[(size_t)f * NB + 4 * k + c] = inv;
+            }
+            if (bad) S.flag = 0;
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int c = 0; c <= r; ++c) Q.dk[k & 1][r][c] = a[r][c];
+        };
+        if (grp == 0 && ti == 0 && tj == 0) factor_own(0);
+        __syncthreads();
+        for (int k = 0; k < WT_NC; ++k) {
+            if (!S.flag) { ok = false; break; }               // block-uniform (written before the barrier every thread just passed)
+            // ---- solve the tile column k against the diagonal tile: A rows below it, the B row blocks that have reached column k,
+            //      the arrow rows and the right-hand side ----
+            const bool in_col = tj == k && ((grp == 0 && ti > k) || (grp == 1 && has_next) || grp == 2);
+            if (in_col) {
+                const double (*D)[4] = Q.dk[k & 1];
+                const double d00 = D[0][0], d10 = D[1][0], d11 = D[1][1], d20 = D[2][0], d21 = D[2][1], d22 = D[2][2],
+                             d30 = D[3][0], d31 = D[3][1], d32 = D[3][2], d33 = D[3][3];
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    const double x0 = a[r][0] * d00;
+                    const double x1 = (a[r][1] - x0 * d10) * d11;
+                    const double x2 = (a[r][2] - x0 * d20 - x1 * d21) * d22;
+                    const double x3 = (a[r][3] - x0 * d30 - x1 * d31 - x2 * d32) * d33;
+                    a[r][0] = x0; a[r][1] = x1; a[r][2] = x2; a[r][3] = x3;
+                }
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const double2 lo = make_double2(a[0][c], a[1][c]), hi = make_double2(a[2][c], a[3][c]);
+                    Q.pan[c][0][ti] = lo; Q.pan[c][1][ti] = hi;
+                    if (ti >= WT_RB) { Q.bp[k][c][0][ti - WT_RB] = lo; Q.bp[k][c][1][ti - WT_RB] = hi; }
+                }
+            }
+            // look-ahead: tile (k + 1, k) and the next diagonal tile (k + 1, k + 1) are neighbouring lanes of one warp
+            __syncwarp();
+            const bool next_diag = grp == 0 && ti == k + 1 && tj == k + 1;
+            if (next_diag) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const double2 r01 = Q.pan[q][0][ti], r23 = Q.pan[q][1][ti];
+                    const double rv[4] = {r01.x, r01.y, r23.x, r23.y};
+#pragma unroll
+                    for (int r = 0; r < 4; ++r)
+#pragma unroll
+                        for (int c = 0; c <= r; ++c) a[r][c] = fma(-rv[r], rv[c], a[r][c]);
+                }
+                factor_own(k + 1);
             }
             __syncthreads();
-        }
-        // (3) augmented Crout: thread r owns row r; rows of the next off-diagonal block start at their diagonal column
-        {
-            const int r = tid;
-            const bool is_row = r < nrows && (has_next || r < ROW_LO || r >= ROW_W);
-            const int c0 = (r >= ROW_LO && r < ROW_W) ? r - ROW_LO : 0;
-            double dg = r < NB ? K.M[r][r] : 0.0;
-            // the pivot of column j sits in S.piv[2 (j & 1) ..]: the owner of row j + 1 publishes the pivot of column j + 1 into the
-            // OTHER pair while slower warps may still be reading column j's (one barrier per column is then enough; every thread
-            // reads the same pair after the same barrier, so the non-positive-pivot exit is block-uniform)
-            if (tid == 0) { const double il = rsqrt(dg); S.piv[0] = dg; S.piv[1] = il; W.invd[(size_t)f * NB] = il; }
-            for (int j = 0; j < NB; ++j) {
-                __syncthreads();
-                const double d = S.piv[2 * (j & 1)];
-                if (!(d > 0.0)) { ok = false; break; }
-                const double inv = S.piv[2 * (j & 1) + 1];
-                if (is_row && r > j && c0 <= j) {
-                    const double* rj = K.M[j];
-                    double* rr = K.M[r];
-                    double s0 = rr[j], s1 = 0.0, s2 = 0.0, s3 = 0.0;
-                    int k = c0;
-                    for (; k + 4 <= j; k += 4) {
-                        s0 -= rr[k] * rj[k]; s1 -= rr[k + 1] * rj[k + 1]; s2 -= rr[k + 2] * rj[k + 2]; s3 -= rr[k + 3] * rj[k + 3];
-                    }
-                    for (; k < j; ++k) s0 -= rr[k] * rj[k];
-                    const double val = ((s0 + s1) + (s2 + s3)) * inv;
-                    rr[j] = val;
-                    if (r < NB) {
-                        dg -= val * val;
-                        if (r == j + 1) { const double il = rsqrt(dg); S.piv[2 * (r & 1)] = dg; S.piv[2 * (r & 1) + 1] = il; W.invd[(size_t)f * NB + r] = il; }
-                    }
+            // ---- rank-4 update of the trailing tiles ----
+            if (grp == 3) {
+                // [W ; z] [W ; z]^T accumulates over every panel of every frame
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const double2 r01 = Q.pan[q][0][ti], r23 = Q.pan[q][1][ti], c01 = Q.pan[q][0][tj], c23 = Q.pan[q][1][tj];
+                    const double rv[4] = {r01.x, r01.y, r23.x, r23.y}, cv[4] = {c01.x, c01.y, c23.x, c23.y};
+#pragma unroll
+                    for (int r = 0; r < 4; ++r)
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) sacc[r][c] = fma(rv[r], cv[c], sacc[r][c]);
+                }
+            } else if (grp >= 0 && tj > k && !next_diag && (grp != 1 || (has_next && ti - WT_RB <= k))) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const double2 r01 = Q.pan[q][0][ti], r23 = Q.pan[q][1][ti], c01 = Q.pan[q][0][tj], c23 = Q.pan[q][1][tj];
+                    const double rv[4] = {r01.x, r01.y, r23.x, r23.y}, cv[4] = {c01.x, c01.y, c23.x, c23.y};
+#pragma unroll
+                    for (int r = 0; r < 4; ++r)
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) a[r][c] = fma(-rv[r], cv[c], a[r][c]);
                 }
             }
             __syncthreads();
-            if (!ok) break;
         }
-        // (4) results of this frame: L_ff, L_{f+1,f}, W_f, z_f; running Schur complement; next P
-        double* Ld = W.Ld + (size_t)f * NB * NB;
-        for (int idx = tid; idx < NB * NB; idx += T) { const int r = idx / NB, c = idx % NB; if (c < r) Ld[idx] = K.M[r][c]; }
-        if (has_next) {
+        wt.mark(11);
+        if (!ok) break;
+        // (4) results of this frame for the backward sweep: L_ff (strict lower part), L_{f+1,f} (upper triangle), W_f, z_f
+        if (grp == 0) {
+            double* Ld = W.Ld + (size_t)f * NB * NB;
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) { const int i = 4 * ti + r, j = 4 * tj + c; if (j < i) Ld[i * NB + j] = a[r][c]; }
+        } else if (grp == 1 && has_next) {
             double* Lo = W.Lo + (size_t)f * NB * NB;
-            for (int idx = tid; idx < NB * NB; idx += T) {
-                const int r = idx / NB, c = idx % NB;
-                const double v = K.M[ROW_LO + r][c];
-                Lo[idx] = v;
-                K.P[r][c] = v;
-            }
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) { const int i = 4 * (ti - WT_RB) + r, j = 4 * tj + c; Lo[i * NB + j] = j >= i ? a[r][c] : 0.0; }
+        } else if (grp == 2) {
+            double* Wf = W.Wf + (size_t)f * NS * NB;
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int sidx = 4 * (ti - WT_RW) + r, j = 4 * tj + c;
+                    if (sidx < NS) Wf[sidx * NB + j] = a[r][c];
+                    else if (sidx == NS) W.z[(size_t)f * NB + j] = a[r][c];
+                }
         }
-        double* Wf = W.Wf + (size_t)f * NS * NB;
-        for (int idx = tid; idx < NS * NB; idx += T) { const double v = K.M[ROW_W + idx / NB][idx % NB]; Wf[idx] = v; K.P[NB + idx / NB][idx % NB] = v; }
-        for (int c = tid; c < NB; c += T) { const double v = K.M[ROW_Z][c]; W.z[(size_t)f * NB + c] = v; K.P[NB + NS][c] = v; }
-        if (ss >= 0) {
-            double a = 0.0;
-            for (int k = 0; k < NB; ++k) a += K.M[ROW_W + ss][k] * K.M[ROW_W + st][k];
-            sw_acc += a;
-        } else if (tid >= 64 && tid < 64 + NS) {
-            double a = 0.0;
-            for (int k = 0; k < NB; ++k) a += K.M[ROW_W + tid - 64][k] * K.M[ROW_Z][k];
-            zw_acc += a;
-        }
-        __syncthreads();
-    }
-    if (!ok) return false;
-    // ---- arrow block: Sw = Hw + damping - sum_f W_f W_f^T ; zw = gs_w - sum_f W_f z_f ; 10 x 10 Cholesky by one thread ----
-    const size_t nw0 = (size_t)F * NB;
-    if (ss >= 0) {
-        double v = W.Hw[ss * NS + st] - sw_acc;
-        if (ss == st) { const double l = sqrt(W.diag[nw0 + ss] / radius); v += l * l; }
-        S.Sw[ss * NS + st] = v;
-    } else if (tid >= 64 && tid < 64 + NS) {
-        S.zw[tid - 64] = W.gs[nw0 + tid - 64] - zw_acc;
+        wt.mark(12);
     }
     __syncthreads();
+    if (!ok) return false;
+    // ---- arrow block: Sw = Hw + damping - sum_f W_f W_f^T ; zw = gs_w - sum_f W_f z_f (the group-3 tiles) ----
+    const size_t nw0 = (size_t)F * NB;
+    if (grp == 3) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int sr = 4 * (ti - WT_RW) + r, sc = 4 * (tj - WT_RW) + c;
+                if (sr < NS && sc <= sr) {
+                    double v = W.Hw[sr * NS + sc] - sacc[r][c];
+                    if (sr == sc) { const double l = sqrt(W.diag[nw0 + sr] / radius); v += l * l; }
+                    S.Sw[sr * NS + sc] = v;
+                } else if (sr == NS && sc < NS) {
+                    S.zw[sc] = W.gs[nw0 + sc] - sacc[r][c];
+                }
+            }
+    }
+    __syncthreads();
+    // 10 x 10 Cholesky by one thread
     if (tid == 0) {
         int good = 1;
         for (int j = 0; j < NS && good; ++j) {
@@ -377,6 +515,7 @@ __device__ bool win_solve(const FitConst* __restrict__ C, int F, double radius, 
         }
         __syncthreads();
     }
+    wt.mark(13);
     return true;
 }
 
@@ -406,7 +545,10 @@ __global__ void __launch_bounds__(T, 1) fit_window_kernel(const FitConst* __rest
 
     for (int k = tid; k < F * NB; k += T) W.x[k] = xin[k];
     if (tid < NS) W.x[(size_t)F * NB + tid] = win[tid];
+    if (tid < 16) win_phase_acc()[tid] = 0;
     __syncthreads();
+    WinTimer kt;
+    kt.start();
 
     double radius = wInitialRadius, decrease_factor = 2.0, x_cost = 0.0, cand_cost = 0.0, mcc = 0.0;
     bool reuse_diagonal = false, step_successful = true;
@@ -489,7 +631,10 @@ __global__ void __launch_bounds__(T, 1) fit_window_kernel(const FitConst* __rest
             __syncthreads();
             reuse_diagonal = true;
             bool step_valid = false;
-            if (win_solve<T>(C, F, radius, W, S)) {
+            kt.mark(0);
+            const bool solved = win_solve<T>(C, F, radius, W, S);
+            kt.mark(2);
+            if (solved) {
                 __syncthreads();
                 // model_cost_change = y^T gs - y^T H_s y / 2 (step = -y)
                 double v = 0.0, fin = 0.0;
@@ -530,7 +675,9 @@ __global__ void __launch_bounds__(T, 1) fit_window_kernel(const FitConst* __rest
             }
             it.flags = 1;
             __syncthreads();
+            kt.mark(3);
             cand_cost = win_evaluate<T, false>(C, F, W.cand, kps, nkp, R0, W, S);
+            kt.mark(14);
             if (!isfinite(cand_cost)) cand_cost = DBL_MAX;
             it.step_norm = sqrt(block_sum<T>(sn, S.red));
             if (it.step_norm <= wParameterTolerance * (x_norm + wParameterTolerance)) { termination = B3D_TERM_PARAM_TOL; break; }
@@ -542,7 +689,9 @@ __global__ void __launch_bounds__(T, 1) fit_window_kernel(const FitConst* __rest
                 for (int k = tid; k < n; k += T) W.x[k] = W.cand[k];
                 __syncthreads();
                 x_norm = norm_of(W.x);
+                kt.mark(0);
                 if (!eval_grad_jac(false)) { termination = B3D_TERM_EVAL_FAILURE; break; }
+                kt.mark(1);
                 step_successful = true;
                 it.flags |= 2;
                 const double q = 2.0 * it.relative_decrease - 1.0;
@@ -557,6 +706,7 @@ __global__ void __launch_bounds__(T, 1) fit_window_kernel(const FitConst* __rest
         }
     }
     __syncthreads();
+    if (pb == 0 && tid < 16 && g_win_phase_on) g_win_phase[tid] += win_phase_acc()[tid];
     for (int k = tid; k < F * NB; k += T) xin[k] = W.x[k];
     if (tid < NS) win[tid] = W.x[(size_t)F * NB + tid];
     if (tid == 0) {
@@ -585,6 +735,14 @@ int win_launch(const FitConst* dfc, const WinProblem* dprobs, int nprob, const b
 using namespace b3d;
 
 extern "C" {
+
+// debug hooks (not part of include/b3d.h): per-phase cycle counters of block 0 of fit_window_kernel
+int b3d_debug_win_timing(int on) {
+    long long z[16] = {0};
+    cudaMemcpyToSymbol(g_win_phase, z, sizeof(z));
+    return cudaMemcpyToSymbol(g_win_phase_on, &on, sizeof(int)) == cudaSuccess ? 0 : 2;
+}
+int b3d_debug_win_read(long long* out16) { return cudaMemcpyFromSymbol(out16, g_win_phase, 16 * sizeof(long long)) == cudaSuccess ? 0 : 2; }
 
 int b3d_fit_windows_dev(const b3d_model* m, const b3d_fit_opts* opts, int32_t nprob, const int32_t* first, const int32_t* count,
                         const b3d_kp* kps, const int32_t* nkp, const double* R0, double* poses, double* W, uint8_t* usable,

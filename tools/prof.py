@@ -146,6 +146,33 @@ def passes(n=1000):
     lib.b3d_debug_fit_stop_at(-1)
 
 
+def winphases(F=20, iters=60):
+    """Per-phase cycles of one OptimizeMultiFrame solve (block 0 of fit_window_kernel)."""
+    model_np = synth.make_model()
+    gm = api.AvatarModel(model_np)
+    seq = synth.make_sequence(model_np, F, 31)
+    cam = (synth.FX, synth.FY, synth.CX, synth.CY)
+    o = api.fit_opts(cam=cam, max_iters=iters, beta_pose=20.0, beta_shape=30.0, lambda_temp=3.0)
+    api.fit_window(gm, o, seq["kps"], seq["nkp"], seq["R0"], seq["poses"], seq["W"][0])
+    lib.b3d_debug_win_timing(1)
+    t0 = time.perf_counter()
+    r = api.fit_window(gm, o, seq["kps"], seq["nkp"], seq["R0"], seq["poses"], seq["W"][0])
+    dt = time.perf_counter() - t0
+    out = (C.c_longlong * 16)()
+    lib.b3d_debug_win_read(out)
+    lib.b3d_debug_win_timing(0)
+    names = ["kernel: other (diag, tolerances)", "kernel: Jacobi scaling + gradient norm after eval", "kernel: solve total", "kernel: model cost change + candidate",
+             "eval: reproj (cost only)", "eval: frame load", "eval: reproj + Jacobian", "eval: 86 x 86 assembly", "eval: scatter to blocks", "solve: load rows",
+             "solve: products with previous block row", "solve: Crout sweep", "solve: store + Schur", "solve: arrow block + back sweep", "kernel: candidate evaluation total", ""]
+    tot = out[0] + out[1] + out[2] + out[3] + out[14]
+    print(f"fit_window F={F}: {r['niters']} records, {dt * 1e3:.2f} ms wall for the call; {tot / max(r['niters'] - 1, 1) / F:.0f} cycles per frame-iteration")
+    for i in range(15):
+        print(f"  {names[i]:52s} {out[i]:12d} {100.0 * out[i] / max(tot, 1):6.1f}%")
+
+
+if __name__ == "__main__" and sys.argv[1] == "winphases":
+    winphases(int(sys.argv[2]) if len(sys.argv) > 2 else 20)
+
 if __name__ == "__main__" and sys.argv[1] == "passes":
     passes(int(sys.argv[2]) if len(sys.argv) > 2 else 1000)
 
