@@ -503,37 +503,16 @@ __device__ bool chol_tiles(SingleSmem& S, int n, double radius, int ti, int tj, 
     return ok;
 }
 
-// back substitution L^T y = z with one warp (z = row n of the factor; 1 / L_jj in S.invd).  Row j - 1 is loaded while column j is
-// eliminated, so that the dependent chain per column is shuffle -> multiply -> fused multiply-add only.
+// back substitution L^T y = z with one warp (z = row n of the factor; 1 / L_jj in S.invd): lm_device.cuh backsolve_warp_blocked
 __device__ void chol_backsolve_warp(const SingleSmem& S, int n, double* y) {
     const double* A = S.u.L;
     const int lane = threadIdx.x & 31;
-    double z[3], cur[3], nxt[3];
+    double z[3];
 #pragma unroll
     for (int q = 0; q < 3; ++q) { const int i = lane + 32 * q; z[q] = i < n ? A[tri(n, i)] : 0.0; }
-    {
-        const double* rj = A + tri(n - 1, 0);
-#pragma unroll
-        for (int q = 0; q < 3; ++q) { const int i = lane + 32 * q; cur[q] = i < n - 1 ? rj[i] : 0.0; }
-    }
-    double inv_cur = S.invd[n - 1];
-    for (int j = n - 1; j >= 0; --j) {
-        double inv_nxt = 0.0;
-        if (j > 0) {
-            const double* rn = A + tri(j - 1, 0);
-#pragma unroll
-            for (int q = 0; q < 3; ++q) { const int i = lane + 32 * q; nxt[q] = i < j - 1 ? rn[i] : 0.0; }
-            inv_nxt = S.invd[j - 1];
-        }
-        const int owner = j & 31, sl = j >> 5;
-        double zj = sl == 0 ? z[0] : (sl == 1 ? z[1] : z[2]);
-        zj = __shfl_sync(0xffffffffu, zj, owner);
-        const double yj = zj * inv_cur;
-        if (lane == owner) y[j] = yj;
-#pragma unroll
-        for (int q = 0; q < 3; ++q) { z[q] = fma(-cur[q], yj, z[q]); cur[q] = nxt[q]; }   // cur is zero beyond the row's entries (i >= j)
-        inv_cur = inv_nxt;
-    }
+    // packed rows: reads past a row's end stay inside S.u.L for every row < n (tri(n - 1, 95) < LTRI)
+    static_assert((NFULL - 1) * NFULL / 2 + 95 < LTRI, "row reads of the blocked back substitution stay inside the factor");
+    backsolve_warp_blocked(n, [A](int r) { return A + tri(r, 0); }, S.invd, z, y);
 }
 
 // Scheduling of frames onto CTAs.  A frame's iterations are a serial chain (up to 101 of them, against a mean of 20), so a batch

@@ -498,20 +498,15 @@ __device__ bool win_solve(const FitConst* __restrict__ C, int F, double radius, 
             K.rhs[i] = v;
         }
         __syncthreads();
-        if (tid < 32) {      // back substitution with one warp
+        if (tid < 32) {      // back substitution with one warp (lm_device.cuh backsolve_warp_blocked)
             const int lane = tid;
             double zz[3];
 #pragma unroll
             for (int q = 0; q < 3; ++q) { const int i = lane + 32 * q; zz[q] = i < NB ? K.rhs[i] : 0.0; }
-            for (int j = NB - 1; j >= 0; --j) {
-                const int owner = j & 31, sl = j >> 5;
-                double zj = sl == 0 ? zz[0] : (sl == 1 ? zz[1] : zz[2]);
-                zj = __shfl_sync(0xffffffffu, zj, owner);
-                const double yj = zj * W.invd[(size_t)f * NB + j];
-                if (lane == owner) { K.yn[j] = yj; W.y[(size_t)f * NB + j] = yj; }
-#pragma unroll
-                for (int q = 0; q < 3; ++q) { const int i = lane + 32 * q; if (i < j) zz[q] -= K.M[j][i] * yj; }
-            }
+            static_assert(LDM >= NB && MROWS * LDM >= (NB - 1) * LDM + 96, "row reads of the blocked back substitution stay inside K.M");
+            backsolve_warp_blocked(NB, [&K](int r) { return (const double*)K.M[r]; }, W.invd + (size_t)f * NB, zz, K.yn);
+            __syncwarp();
+            for (int i = lane; i < NB; i += 32) W.y[(size_t)f * NB + i] = K.yn[i];
         }
         __syncthreads();
     }

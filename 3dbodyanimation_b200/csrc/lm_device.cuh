@@ -304,6 +304,54 @@ __device__ void eval_reproj(const FitConst* __restrict__ C, const double* x, con
 __device__ __forceinline__ int tri(int i, int j) { return i * (i + 1) / 2 + j; }
 
 // ---------------------------------------------------------------------------------------------------------------
+// Back substitution L^T y = z by ONE warp, four columns per step.  lane l holds z[l], z[l + 32], z[l + 64] in zreg.  Lget(r, i) reads
+// L[r][i] (i < r < n), inv[j] = 1 / L_jj.  Per block of four columns (from the bottom): every lane gathers the block's four z by
+// shuffles, solves the 4 x 4 triangle redundantly in registers, and subtracts the block's contribution from its own z entries.  The
+// dependent chain per block is shuffle -> 4 x (multiply-add, multiply) -> 4 multiply-adds, about a third of one column at a time; the
+// block's L entries are read before its chain starts.  n <= 96.
+// ---------------------------------------------------------------------------------------------------------------
+// Rows are addressed through a row pointer and a stride rule: row r starts at base + row_off(r).  Entries of a row at or right of
+// its diagonal block are never meant to be used; they are read (valid memory, finite values) and only ever reach z entries that are
+// dead by then, which keeps the loop free of predicates and index arithmetic — the chain is instruction-bound, not FMA-bound.
+template <class RowPtr>
+__device__ __forceinline__ void backsolve_warp_blocked(int n, RowPtr row_ptr, const double* inv, double (&zreg)[3], double* y) {
+    const int lane = threadIdx.x & 31;
+    int b = (n - 1) >> 2;
+    // a partial top block (n not a multiple of 4): one column at a time
+    for (int j = n - 1; j >= 4 * b && (n & 3); --j) {
+        const int sl = j >> 5;
+        const double v = sl == 0 ? zreg[0] : (sl == 1 ? zreg[1] : zreg[2]);
+        const double yj = __shfl_sync(0xffffffffu, v, j & 31) * inv[j];
+        if (lane == 0) y[j] = yj;
+        const double* rj = row_ptr(j);
+#pragma unroll
+        for (int q = 0; q < 3; ++q) { const int i = lane + 32 * q; if (i < j) zreg[q] = fma(-rj[i], yj, zreg[q]); }
+    }
+    if (n & 3) --b;
+    for (; b >= 0; --b) {
+        const int j0 = 4 * b;
+        const double *p0 = row_ptr(j0), *p1 = row_ptr(j0 + 1), *p2 = row_ptr(j0 + 2), *p3 = row_ptr(j0 + 3);
+        const double l10 = p1[j0], l20 = p2[j0], l21 = p2[j0 + 1], l30 = p3[j0], l31 = p3[j0 + 1], l32 = p3[j0 + 2];
+        const double i0 = inv[j0], i1 = inv[j0 + 1], i2 = inv[j0 + 2], i3 = inv[j0 + 3];
+        double u0[3], u1[3], u2[3], u3[3];
+#pragma unroll
+        for (int q = 0; q < 3; ++q) { u0[q] = p0[lane + 32 * q]; u1[q] = p1[lane + 32 * q]; u2[q] = p2[lane + 32 * q]; u3[q] = p3[lane + 32 * q]; }
+        // the block's z: its four entries sit in consecutive lanes of one register slot (j0 is a multiple of 4)
+        const int sl = j0 >> 5, l0 = j0 & 31;
+        const double v = sl == 0 ? zreg[0] : (sl == 1 ? zreg[1] : zreg[2]);
+        const double z0 = __shfl_sync(0xffffffffu, v, l0), z1 = __shfl_sync(0xffffffffu, v, l0 + 1), z2 = __shfl_sync(0xffffffffu, v, l0 + 2),
+                     z3 = __shfl_sync(0xffffffffu, v, l0 + 3);
+        const double y3 = z3 * i3;
+        const double y2 = (z2 - l32 * y3) * i2;
+        const double y1 = (z1 - l21 * y2 - l31 * y3) * i1;
+        const double y0 = (z0 - l10 * y1 - l20 * y2 - l30 * y3) * i0;
+        if (lane == 0) { y[j0] = y0; y[j0 + 1] = y1; y[j0 + 2] = y2; y[j0 + 3] = y3; }
+#pragma unroll
+        for (int q = 0; q < 3; ++q) zreg[q] = zreg[q] - ((u0[q] * y0 + u1[q] * y1) + (u2[q] * y2 + u3[q] * y3));
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 // Line-search trial point: per keypoint the robustified cost rho / 2 at x and its derivative along the direction dx (both in the
 // 86-layout), i.e. res^T (J dx) of the robustified block, by forward-mode propagation through the chain — no Jacobian is formed.
 // What Ceres' Armijo search needs at a trial point is exactly the cost and this directional derivative.

@@ -103,8 +103,9 @@ def phases(n=148, mode="C2"):
     names = ["loop head", "build A", "cholesky", "backsolve", "mcc", "delta+candidate", "cand evaluate", "accept copy", "eval_grad_jac total",
              "  JAC reproj", "  JAC gmm+cost", "  JAC assemble", "  cand reproj", "  cand gmm+cost", "", ""]
     lib.b3d_debug_phase_timing(1)
-    import io, contextlib
+    lib.b3d_debug_fit_stop_at(0)          # one CTA per frame: the phase counters follow CTA 0 = frame 0
     fit(n, mode, reps=1)
+    lib.b3d_debug_fit_stop_at(-1)
     out = (C.c_longlong * 32)()
     lib.b3d_debug_phase_read(out)
     tot = sum(out[i] for i in range(9))
