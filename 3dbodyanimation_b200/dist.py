@@ -125,6 +125,7 @@ class GpuWindowSolver:
         # stage 1: beta_shape, it1; stage 2: the reference hard-codes beta_shape = 1e5 and 60 iterations (main_multi_frame.cpp:183-185)
         self.opts = {1: mk(seq_opts.beta_shape, seq_opts.it1), 2: mk(seq_opts.beta_shape_lock, seq_opts.it2)}
         self.solves = []          # (stage, first, count, iterations, termination, usable) per solve, read back lazily
+        self.batches = []
 
     def solve(self, stage, first, count, st):
         dev = st["poses"].device
@@ -146,8 +147,32 @@ class GpuWindowSolver:
         self.capi.check(self.lib.b3d_writeback_dev(count, P(st["poses"], first * NPF * 8), P(st["R0"], first * 9 * 8), P(st["r"], first * NJ * 9 * 8),
                                                    P(st["p"], first * 3 * 8), stream), "b3d_writeback_dev")
 
+    def solve_batch(self, stage, firsts, counts, st):
+        """Independent problems in ONE launch (one CTA each): problem p covers rows [firsts[p], firsts[p] + counts[p]) of st."""
+        n = len(firsts)
+        if n == 0:
+            return
+        dev = st["poses"].device
+        assert dev.type == "cuda", "GpuWindowSolver needs device tensors (there is no CPU fitting path)"
+        stat = torch.zeros(2, n, dtype=torch.int32, device=dev)
+        us = torch.zeros(n, dtype=torch.uint8, device=dev)
+        f, c = (C.c_int32 * n)(*[int(x) for x in firsts]), (C.c_int32 * n)(*[int(x) for x in counts])
+        P = lambda t: C.c_void_p(t.data_ptr())
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        self.capi.check(self.lib.b3d_fit_windows_dev(self.model.h, C.byref(self.opts[stage]), n, f, c, P(st["kps"]), P(st["nkp"]), P(st["R0"]),
+                                                     P(st["poses"]), P(st["W"]), P(us), None, 0, P(stat[0]), P(stat[1]), stream),
+                        "b3d_fit_windows_dev")
+        self.batches.append((stage, list(firsts), list(counts), stat, us))
+
     def report(self):
         return [(s, f, c, int(stat[0]), int(stat[1]), bool(us[0])) for (s, f, c, stat, us) in self.solves]
+
+    def batch_report(self):
+        """(solves, unusable solves, LM iterations) over every solve_batch call so far."""
+        n = sum(len(f) for (_, f, _, _, _) in self.batches)
+        bad = sum(int((us == 0).sum()) for (*_, us) in self.batches)
+        its = sum(int(stat[0].sum()) for (_, _, _, stat, _) in self.batches)
+        return n, bad, its
 
 
 # ---------------------------------------------------------------------------------------------------------
@@ -248,3 +273,167 @@ def emulate_sharded(solver, st, plan: WindowPlan):
             out[k][f0:f1] = states[r][k][f0:f1]
             out[k][k0:k1] = f[k][k0:k1]
     return out
+
+
+# ---------------------------------------------------------------------------------------------------------
+# one sequence over G ranks, several shards per rank (throughput mode: a rank's shards are solved as batches of independent chains)
+# ---------------------------------------------------------------------------------------------------------
+def _solve_batch(solver, stage, firsts, counts, st):
+    if hasattr(solver, "solve_batch"):
+        solver.solve_batch(stage, firsts, counts, st)
+    else:
+        for f, c in zip(firsts, counts):
+            solver.solve(stage, f, c, st)
+
+
+def _writeback_batch(solver, firsts, counts, st):
+    for f, c in zip(firsts, counts):
+        solver.writeback(f, c, st)
+
+
+def shards_of_rank(plan: WindowPlan, rank: int, world: int) -> range:
+    """Contiguous block of the plan's shards owned by `rank` (shard g lives on rank g * world // plan.g)."""
+    lo = -(-rank * plan.g // world)            # ceil
+    hi = -(-(rank + 1) * plan.g // world)
+    return range(lo, min(hi, plan.g))
+
+
+def fit_sequence_multishard(solver, st, plan: WindowPlan, rank=None, world=None, group=None, gather=True, stage1=True):
+    """The sharded 3dba_multi schedule (fit_sequence_sharded: pass 1 per shard from the post-stage-1 state, halo hand-off of the
+    OVERLAP frames the left neighbour refined, pass-2 re-solve of every shard's first window) with plan.g >= world shards: rank r owns
+    a contiguous block of shards and solves them TOGETHER — wave i of pass 1 is one batched launch of the i-th window of every local
+    shard, pass 2 one batched launch of all fix-ups.  Each shard works on a private copy of its rows (its frames plus the reach of
+    its last window), exactly as if it had the whole post-stage-1 state to itself.  Halos between shards of one rank are device
+    copies; the one halo per rank edge goes over the process group (NCCL send / recv: OVERLAP x 85 doubles).  Result: identical to
+    emulate_sharded / b3d_fit_sequences(num_shards = plan.g).  Returns st (assembled on every rank when `gather`)."""
+    if rank is None:
+        rank = dist.get_rank(group) if dist.is_initialized() else 0
+        world = dist.get_world_size(group) if dist.is_initialized() else 1
+    dev = st["poses"].device
+    if stage1:
+        _stage1(solver, st, plan)      # redundantly on every rank (deterministic; stage 2 needs its result everywhere)
+    mine = list(shards_of_rank(plan, rank, world))
+    # ---- private rows of every local shard, back to back in one set of arrays ----
+    lo = {g: plan.window(plan.cuts[g])[0] for g in mine}
+    hi = {g: plan.window(plan.cuts[g + 1] - 1)[1] for g in mine}
+    base, off = {}, 0
+    for g in mine:
+        base[g] = off
+        off += hi[g] - lo[g]
+    priv = {k: (torch.cat([st[k][lo[g]:hi[g]] for g in mine]) if mine else st[k][:0].clone()) for k in STATE_KEYS}
+    # ---- pass 1: wave i = the i-th window of every local shard ----
+    nwin = max([plan.cuts[g + 1] - plan.cuts[g] for g in mine], default=0)
+    for i in range(nwin):
+        firsts, counts = [], []
+        for g in mine:
+            k = plan.cuts[g] + i
+            if k < plan.cuts[g + 1]:
+                s, e = plan.window(k)
+                firsts.append(base[g] + s - lo[g]); counts.append(e - s)
+        _solve_batch(solver, 2, firsts, counts, priv)
+        _writeback_batch(solver, firsts, counts, priv)
+    # ---- halo hand-off ----
+    halo = {}                                  # shard -> (OVERLAP x 85) rows refined by its left neighbour
+    for g in mine:
+        if g > 0 and (g - 1) in base:
+            h0, h1 = plan.halo_range(g)
+            a = base[g - 1] + h0 - lo[g - 1]
+            halo[g] = torch.cat([priv["poses"][a:a + h1 - h0], priv["R0"][a:a + h1 - h0]], dim=1).clone()
+    ops, recv_buf, send_buf = [], None, None
+    if mine and mine[-1] + 1 < plan.g:         # my last shard feeds the first shard of the next rank
+        h0, h1 = plan.halo_range(mine[-1] + 1)
+        a = base[mine[-1]] + h0 - lo[mine[-1]]
+        send_buf = torch.cat([priv["poses"][a:a + h1 - h0], priv["R0"][a:a + h1 - h0]], dim=1).contiguous()
+        if world > 1 and h1 > h0:
+            peer = (mine[-1] + 1) * world // plan.g
+            ops.append(dist.P2POp(dist.isend, send_buf, peer if group is None else dist.get_global_rank(group, peer), group))
+    if mine and mine[0] > 0 and (mine[0] - 1) not in base:
+        h0, h1 = plan.halo_range(mine[0])
+        recv_buf = torch.empty(h1 - h0, NPF + 9, dtype=torch.float64, device=dev)
+        if world > 1 and h1 > h0:
+            peer = (mine[0] - 1) * world // plan.g
+            ops.append(dist.P2POp(dist.irecv, recv_buf, peer if group is None else dist.get_global_rank(group, peer), group))
+    if ops:
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+    if recv_buf is not None:
+        halo[mine[0]] = recv_buf
+    # ---- pass 2: every shard but the sequence's first re-solves its first window from the post-stage-1 state + halo (one batch) ----
+    fix = [g for g in mine if g > 0]
+    if fix:
+        fbase, off = {}, 0
+        for g in fix:
+            s, e = plan.window(plan.cuts[g])
+            fbase[g] = off
+            off += e - s
+        fx = {k: torch.cat([st[k][plan.window(plan.cuts[g])[0]:plan.window(plan.cuts[g])[1]] for g in fix]) for k in ("kps", "nkp", "poses", "R0", "W")}
+        fx["r"] = torch.zeros(off, st["r"].shape[1], dtype=st["r"].dtype, device=dev)
+        fx["p"] = torch.zeros(off, 3, dtype=st["p"].dtype, device=dev)
+        for g in fix:
+            h0, h1 = plan.halo_range(g)
+            if h1 > h0:
+                fx["poses"][fbase[g]:fbase[g] + h1 - h0] = halo[g][:, :NPF]
+                fx["R0"][fbase[g]:fbase[g] + h1 - h0] = halo[g][:, NPF:]
+        firsts = [fbase[g] for g in fix]
+        counts = [plan.window(plan.cuts[g])[1] - plan.window(plan.cuts[g])[0] for g in fix]
+        _solve_batch(solver, 2, firsts, counts, fx)
+        _writeback_batch(solver, firsts, counts, fx)
+    # ---- assemble the owned frames ----
+    for g in mine:
+        f0, f1 = plan.own_range(g)
+        for k in ("poses", "R0", "W", "r", "p"):
+            st[k][f0:f1] = priv[k][base[g] + f0 - lo[g]:base[g] + f1 - lo[g]]
+        if g > 0:
+            k0, k1 = plan.fix_keep_range(g)
+            s = plan.window(plan.cuts[g])[0]
+            for k in ("poses", "R0", "W", "r", "p"):
+                st[k][k0:k1] = fx[k][fbase[g] + k0 - s:fbase[g] + k1 - s]
+    if gather and world > 1:
+        own = [plan.own_range(g) for g in mine]
+        for k in ("poses", "R0", "W", "r", "p"):
+            t = torch.zeros_like(st[k])
+            for f0, f1 in own:
+                t[f0:f1] = st[k][f0:f1]
+            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+            st[k].copy_(t)
+    return st
+
+
+def bench_c5(api, gm, base, so, seq, dev, rank, world, shards_per_rank=32):
+    """BASELINE configs[4] for bench.py: one long 3dba_multi sequence, windows sharded over the ranks (shards_per_rank chains per GPU
+    solved as batches), OVERLAP x 85 doubles per rank edge over NCCL.  Every rank calls this; returns the JSON fragment on rank 0."""
+    import time
+    n = seq["kps"].shape[0]
+    st = make_state(seq["kps"], seq["nkp"], seq["poses"], seq["R0"], seq["W"], dev)
+    plan = WindowPlan(n, so.wsize, so.overlap, so.skip, world * shards_per_rank)
+    solver = GpuWindowSolver(gm, base, so)
+    bar = lambda: (dist.barrier() if world > 1 else None, torch.cuda.synchronize())
+    bar()
+    t0 = time.perf_counter()
+    _stage1(solver, st, plan)
+    bar()
+    t1 = time.perf_counter()
+    fit_sequence_multishard(solver, st, plan, rank=rank, world=world, gather=False, stage1=False)
+    bar()
+    t2 = time.perf_counter()
+    tt = torch.tensor([t1 - t0, t2 - t1], dtype=torch.float64, device=dev)
+    nsolve, bad, its = solver.batch_report()
+    cnt = torch.tensor([float(nsolve), float(bad), float(its)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    s1, s2 = float(tt[0]), float(tt[1])
+    stage1_rep = solver.report()
+    edges = world - 1
+    return {"workload": f"3dba_multi, ONE sequence of {n} synthetic frames (BASELINE configs[4]): anchor_skip {so.skip}, window {so.wsize}, overlap {so.overlap}, "
+                        f"lambda_temp {so.lambda_temp}, it1 {so.it1}, it2 {so.it2}; sharded schedule, {plan.g} shards = {world} ranks x {shards_per_rank}",
+            "frames": n, "frames_per_sec": n / (s1 + s2), "ms": (s1 + s2) * 1e3,
+            "stage1_ms": s1 * 1e3, "stage1": f"{len(plan.anchors)} anchors in one chain, solved redundantly on every rank by ONE CTA (not partitioned: the serial fraction)",
+            "stage1_lm_iterations": stage1_rep[0][3] if stage1_rep else None,
+            "stage2_ms": s2 * 1e3, "stage2_frames_per_sec": n / s2, "windows": len(plan.starts), "window_solves_incl_fixups": int(cnt[0]), "unusable_solves": int(cnt[1]),
+            "window_lm_iterations_mean": float(cnt[2]) / max(float(cnt[0]), 1.0),
+            "collective": "NCCL send/recv (batch_isend_irecv) between neighbouring ranks, once per solve", "halo_bytes_per_rank_edge": so.overlap * (NPF + 9) * 8,
+            "halo_bytes_total": edges * so.overlap * (NPF + 9) * 8, "intra_rank_halos": plan.g - 1 - edges,
+            "timing": "wall clock between barriers + device synchronisation, max over ranks; state resident on the device",
+            "schedule_note": "the sharded schedule is an opt-in approximation of the reference's serial window chain (DESIGN 5); its deviation from the "
+                             "serial chain is measured in tests/test_fit_window_gpu.py::test_sharded_schedule_deviation_from_serial"}

@@ -272,6 +272,63 @@ def make_sequence(model: dict, n: int, seed: int, *, drop_prob: float = 0.0, noi
     return dict(kps=kps, nkp=nkp, R0=np.tile(R0.T.reshape(9), (n, 1)).copy(), poses=poses, W=np.zeros((n, S)), gt=gt)
 
 
+def _rodrigues_batch(aa: np.ndarray, p: np.ndarray) -> np.ndarray:
+    """ceres::AngleAxisRotatePoint for arrays of axis-angles (n, 3) and points (n, 3) (the Rodrigues branch; the synthetic
+    trajectories never come near theta = 0)."""
+    th = np.linalg.norm(aa, axis=1, keepdims=True)
+    w = aa / np.maximum(th, 1e-300)
+    c, sn = np.cos(th), np.sin(th)
+    return p * c + np.cross(w, p) * sn + w * np.sum(w * p, axis=1, keepdims=True) * (1.0 - c)
+
+
+def make_sequence_fast(model: dict, n: int, seed: int, *, noise_px: float = 1.0) -> dict:
+    """make_sequence for long sequences (C5: 100,000 frames), vectorised over the frames: the same kind of trajectory (per-sequence
+    mean plus three sinusoids per parameter) and the same forward model, all 17 keypoint slots per frame.  Not bit-identical to
+    make_sequence (the random draws come in a different order)."""
+    rng = np.random.default_rng(seed)
+    consts = model_constants(model)
+    off, jsr = consts["offset"], consts["JSR"]
+    R0 = initial_root_rotation()
+    tt = np.arange(n)[:, None]
+
+    def traj(mean, amp):
+        mean = np.atleast_1d(np.asarray(mean, dtype=np.float64))
+        out = np.tile(mean, (n, 1))
+        for _ in range(3):
+            period = rng.uniform(40.0, 400.0, size=mean.shape)
+            phase = rng.uniform(0.0, 2 * np.pi, size=mean.shape)
+            out = out + (amp / 3.0) * np.sin(2 * np.pi * tt / period + phase)
+        return out
+
+    jaa_all = traj(rng.normal(0.0, 0.15, size=3 * (J - 1)), 0.25)
+    raa_all = traj(rng.normal(0.0, 0.10, size=3), 0.15)
+    t_all = traj([rng.uniform(-0.2, 0.2), rng.uniform(-0.15, 0.15), rng.uniform(2.8, 3.2)], 0.2)
+    s_all = traj([rng.uniform(0.95, 1.05)], 0.05)[:, 0]
+    w = rng.normal(size=S)
+    bone = off + jsr @ w
+    bone[1:] -= (jsr @ w)[PARENT[1:]]                 # bone(j) = offset_j + (JSR_j - JSR_parent(j)) w ; the root has no parent term
+    jaa = np.concatenate([np.zeros((n, 1, 3)), jaa_all.reshape(n, J - 1, 3)], axis=1)
+    kps = np.zeros((n, MAXKP), dtype=KP_DTYPE)
+    for k, sid in enumerate(USE_SMPL):
+        pos = np.tile(bone[sid], (n, 1))
+        cur = int(sid)
+        while PARENT[cur] != -1 and PARENT[cur] != 0:
+            pa = int(PARENT[cur])
+            pos = _rodrigues_batch(jaa[:, pa], pos) + bone[pa]
+            cur = pa
+        pc = _rodrigues_batch(raa_all, pos @ R0.T)
+        pc = s_all[:, None] * pc + t_all
+        uv = np.stack([FX * pc[:, 0] / pc[:, 2] + CX, FY * pc[:, 1] / pc[:, 2] + CY], axis=1) + rng.normal(0.0, noise_px, size=(n, 2))
+        kps["jid"][:, k] = int(sid)
+        kps["u"][:, k], kps["v"][:, k] = uv[:, 0], uv[:, 1]
+    gt = np.zeros((n, NPF + S))
+    gt[:, 0], gt[:, 1:4], gt[:, 4:7], gt[:, 7:76], gt[:, 76:] = s_all, raa_all, t_all, jaa_all, w
+    poses = np.zeros((n, NPF))
+    poses[:, 0] = 1.0
+    poses[:, 6] = 3.0
+    return dict(kps=kps, nkp=np.full(n, MAXKP, dtype=np.int32), R0=np.tile(R0.T.reshape(9), (n, 1)).copy(), poses=poses, W=np.zeros((n, S)), gt=gt)
+
+
 def make_forward_inputs(b: int, seed: int) -> dict:
     """C4 inputs: w ~ N(0,1), r from AA ~ N(0, 0.3^2) (col-major 3x3 per joint), p as the frame generator."""
     rng = np.random.default_rng(seed)

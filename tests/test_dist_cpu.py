@@ -143,3 +143,32 @@ def test_sharded_schedule_under_gloo(tmp_path, world, n):
     f0, f1 = plan.own_range(0)
     keep = f1 if plan.g == 1 else plan.halo_range(1)[0]
     assert torch.equal(serial["poses"][f0:keep], ref["poses"][f0:keep])
+
+
+def _worker_multi(rank, world, port, n, seed, per_rank, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        st = make_state(n, seed)
+        plan = D.WindowPlan(n, 20, 5, 10, world * per_rank)
+        res = D.fit_sequence_multishard(StandInSolver(), st, plan)
+        torch.save({k: res[k] for k in ("poses", "R0", "W", "r", "p")}, os.path.join(out_dir, f"rank{rank}.pt"))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,n,per_rank", [(2, 200, 3), (3, 260, 2), (2, 40, 4)])
+def test_multishard_schedule_under_gloo(tmp_path, world, n, per_rank):
+    """Several shards per rank (a rank's shards advance together, wave by wave; halos inside a rank are copies, the one per rank
+    edge goes over the process group): every rank ends with the result of the same schedule played in one process."""
+    mp.spawn(_worker_multi, args=(world, _free_port(), n, 11, per_rank, str(tmp_path)), nprocs=world, join=True)
+    plan = D.WindowPlan(n, 20, 5, 10, world * per_rank)
+    ref = D.emulate_sharded(StandInSolver(), make_state(n, 11), plan)
+    for r in range(world):
+        got = torch.load(os.path.join(str(tmp_path), f"rank{r}.pt"))
+        for k in ("poses", "R0", "W", "r", "p"):
+            assert torch.equal(got[k], ref[k]), (r, k)
+    # shard -> rank map: contiguous blocks that cover every shard once
+    owned = [list(D.shards_of_rank(plan, r, world)) for r in range(world)]
+    assert sum(owned, []) == list(range(plan.g))

@@ -154,3 +154,54 @@ def test_c3_at_stated_size_vs_committed_oracle_result(api, gmodel, synth, model_
     assert dev["raa"] < PARAM_TOL and dev["jaa"] < PARAM_TOL and dev["R0"] < PARAM_TOL
     assert dev["t_over_s"] < 5e-3 and dev["W"] < 1e-2
     assert np.mean(gi[1:] == oi[1:]) > 0.8 and abs(int(gi[0]) - int(oi[0])) <= 2
+
+
+@pytest.mark.parametrize("shards", [2, 5])
+def test_multishard_driver_equals_library_schedule(api, gmodel, synth, model_np, shards):
+    """dist.fit_sequence_multishard with every shard on this one rank (batched waves, private rows per shard) reproduces
+    b3d_fit_sequences(num_shards = G) bit for bit."""
+    import importlib
+    import torch
+    D = importlib.import_module("3dbodyanimation_b200.dist")
+    n = 143
+    seq = synth.make_sequence(model_np, n, 57)
+    cam = (synth.FX, synth.FY, synth.CX, synth.CY)
+    base, so = api.fit_opts(cam=cam), api.seq_opts(it1=25, it2=20, num_shards=shards, beta_pose=20.0, beta_shape=30.0)
+    g = api.fit_sequences(gmodel, base, so, seq["kps"], seq["nkp"], seq["poses"], seq["R0"], seq["W"])
+    dev = torch.device("cuda", 0)
+    st = D.make_state(seq["kps"], seq["nkp"], seq["poses"], seq["R0"], seq["W"], dev)
+    plan = D.WindowPlan(n, so.wsize, so.overlap, so.skip, shards)
+    solver = D.GpuWindowSolver(gmodel, base, so)
+    out = D.fit_sequence_multishard(solver, st, plan, rank=0, world=1)
+    torch.cuda.synchronize()
+    nsolve, bad, _ = solver.batch_report()
+    assert bad == 0 and nsolve == len(plan.starts) + plan.g - 1
+    for k in ("poses", "R0", "W", "p"):
+        assert np.array_equal(out[k].cpu().numpy(), g[k].reshape(out[k].shape)), k
+    assert np.array_equal(out["r"].cpu().numpy().reshape(n, 24, 9), g["r"])
+
+
+def test_sharded_schedule_deviation_from_serial(api, gmodel, synth, model_np, capsys):
+    """How far the opt-in sharded schedule (num_shards = G: every shard starts from the post-stage-1 state, only its first window is
+    re-solved from the neighbour's halo) is from the reference's serial window chain (num_shards = 1) on the same sequence.  The
+    number is printed and quoted beside every sharded throughput figure; it is bounded here so that it cannot grow
+    unnoticed."""
+    n = 600
+    seq = synth.make_sequence(model_np, n, 91)
+    cam = (synth.FX, synth.FY, synth.CX, synth.CY)
+    base = api.fit_opts(cam=cam)
+    run = lambda G: api.fit_sequences(gmodel, base, api.seq_opts(it1=1000, it2=60, num_shards=G, beta_pose=20.0, beta_shape=30.0),
+                                      seq["kps"], seq["nkp"], seq["poses"], seq["R0"], seq["W"])
+    a = run(1)
+    rows = []
+    for G in (2, 8):
+        b = run(G)
+        dj = float(np.max(np.abs(a["poses"][:, 7:] - b["poses"][:, 7:])))
+        dr = float(np.max(np.abs(a["R0"] - b["R0"])))
+        dts = float(np.max(np.abs(a["poses"][:, 4:7] / a["poses"][:, :1] - b["poses"][:, 4:7] / b["poses"][:, :1])))
+        dw = float(np.max(np.abs(a["W"] - b["W"])))
+        rows.append((G, dj, dr, dts, dw))
+        assert dj < 1e-2 and dr < 1e-2 and dts < 1e-2, rows
+    with capsys.disabled():
+        for G, dj, dr, dts, dw in rows:
+            print(f"\n[sharded vs serial, {n} frames, G = {G}] max |d jointAA| {dj:.2e}, max |d R0| {dr:.2e}, max |d t/s| {dts:.2e}, max |d w| {dw:.2e}")
