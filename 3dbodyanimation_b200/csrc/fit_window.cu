@@ -60,9 +60,22 @@ struct WinWs {
         Hd = p; p += (size_t)F * NB * NB; Ld = p; p += (size_t)F * NB * NB; Lo = p; p += (size_t)F * NB * NB;
         Ha = p; p += (size_t)F * NS * NB; Wf = p; p += (size_t)F * NS * NB;
         Hw = p; p += NS * NS; Lw = p; p += NS * NS;
-        invd = p;
+        invd = p; p += (size_t)F * NB;
+        xc = p;
     }
+    double* xc;               // exchange area of the cluster's two CTAs (offsets XC_*)
 };
+// exchange area, in doubles: the master's command and its operands, the helper's partial results
+constexpr int XC_CMD = 0, XC_RADIUS = 1, XC_OK = 2, XC_COST = 4 /* 2 */, XC_HW = 16 /* 2 x 100 */, XC_GW = 216 /* 2 x 10 */, XC_SACC = 240 /* 144 */,
+              XC_BP = 512;  /* the helper's last frame's panels: WT_NC x 4 x 2 x 22 double2 */
+enum { CMD_EVAL_JAC = 1, CMD_EVAL_COST = 2, CMD_SOLVE = 3, CMD_EXIT = 9 };
+
+// Both CTAs of a problem's cluster: global writes before, reads after (release / acquire at cluster scope).
+__device__ __forceinline__ void cluster_sync_all() {
+    __threadfence();
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ unsigned cluster_ctarank() { unsigned r; asm volatile("mov.u32 %0, %cluster_ctarank;" : "=r"(r)); return r; }
 
 struct WinEval {
     EvalDense out;                        // dense robustified Jacobian [34][88] (lm_device.cuh) + residuals
@@ -108,11 +121,14 @@ struct WinSmem {
 };
 
 // ---- evaluate every frame of the problem at parameters xp (n = 76 F + 10) -----------------------------------------------
-// Returns the cost.  JAC: fills Hd / Ha / Hw (UNSCALED) and g in the workspace.  A frame's 86 x 86 normal equations are a SYRK of
-// its dense Jacobian over 4 x 4 register tiles (thread (ti, tj), 253 tiles), scattered straight into the block structure.
+// Frames [f_lo, f_hi) only (the cluster's two CTAs split the frames); returns this CTA's share of the cost (rank 0 carries the shape
+// prior).  JAC: fills Hd / Ha (UNSCALED) and g of those frames in the workspace and leaves this CTA's share of the shape block in the
+// exchange area (XC_HW / XC_GW, slot `rank`); the master adds the two shares.  A frame's 86 x 86 normal equations are a SYRK of its
+// dense Jacobian over 4 x 4 register tiles (thread (ti, tj), 253 tiles), scattered straight into the block structure.
 template <int T, bool JAC>
-__device__ double win_evaluate(const FitConst* __restrict__ C, int F, const double* __restrict__ xp, const b3d_kp* __restrict__ kps,
-                               const int32_t* __restrict__ nkp_all, const double* __restrict__ R0_all, WinWs& W, WinSmem& S) {
+__device__ double win_evaluate(const FitConst* __restrict__ C, int F, const double* xp /* written by the master during the kernel: no read-only path */, const b3d_kp* __restrict__ kps,
+                               const int32_t* __restrict__ nkp_all, const double* __restrict__ R0_all, WinWs& W, WinSmem& S, int f_lo, int f_hi,
+                               int rank) {
     const int tid = threadIdx.x;
     WinEval& E = S.u.e;
     const double bp2 = C->beta_pose * C->beta_pose, bs2 = C->beta_shape * C->beta_shape, lam = C->lambda_temp, lam2 = lam * lam;
@@ -130,7 +146,7 @@ __device__ double win_evaluate(const FitConst* __restrict__ C, int F, const doub
         if (tid < NS) S.gw[tid] = 0.0;
     }
     if (tid < NS) S.xfull[IDX_W + tid] = xp[(size_t)F * NB + tid];
-    for (int f = 0; f < F; ++f) {
+    for (int f = f_lo; f < f_hi; ++f) {
         const int nkp = min(max(nkp_all[f], 0), MAXKP);
         const double* xf = xp + (size_t)f * NB;
         __syncthreads();                    // previous frame's consumers are done with xfull / R0 / E
@@ -213,31 +229,57 @@ __device__ double win_evaluate(const FitConst* __restrict__ C, int F, const doub
         wt.mark(8);
     }
     // temporal residuals lambda (x_f - x_{f+1}) and the shape prior
-    if (temporal)
-        for (int idx = tid; idx < (F - 1) * (NB - 1); idx += T) {
-            const int f = idx / (NB - 1), k = 1 + idx % (NB - 1);
+    if (temporal) {      // the pair (f, f + 1) belongs to the CTA that owns f
+        const int p_hi = min(f_hi, F - 1);
+        for (int idx = tid; idx < (p_hi - f_lo) * (NB - 1); idx += T) {
+            const int f = f_lo + idx / (NB - 1), k = 1 + idx % (NB - 1);
             const double d = lam * (xp[(size_t)f * NB + k] - xp[(size_t)(f + 1) * NB + k]);
             part += 0.5 * d * d;
         }
-    if (shape_prior && tid < NS) { const double r = C->beta_shape * S.xfull[IDX_W + tid]; part += 0.5 * r * r; }
+    }
+    if (rank == 0 && shape_prior && tid < NS) { const double r = C->beta_shape * S.xfull[IDX_W + tid]; part += 0.5 * r * r; }
     __syncthreads();
     if (JAC) {
-        for (int idx = tid; idx < NS * NS; idx += T) W.Hw[idx] = S.Hw[idx] + ((shape_prior && idx / NS == idx % NS) ? bs2 : 0.0);
-        if (tid < NS) W.g[(size_t)F * NB + tid] = S.gw[tid] + (shape_prior ? bs2 * S.xfull[IDX_W + tid] : 0.0);
+        for (int idx = tid; idx < NS * NS; idx += T) W.xc[XC_HW + rank * NS * NS + idx] = S.Hw[idx];
+        if (tid < NS) W.xc[XC_GW + rank * NS + tid] = S.gw[tid];
     }
-    return block_sum<T>(part, S.red);
+    const double total = block_sum<T>(part, S.red);
+    if (tid == 0) W.xc[XC_COST + rank] = total;
+    return total;
+}
+
+// master, after the cluster barrier that follows an evaluation with Jacobian: the shape block = both shares + the shape prior
+template <int T>
+__device__ void win_combine_shape(const FitConst* __restrict__ C, int F, const double* xp, WinWs& W) {
+    const int tid = threadIdx.x;
+    const double bs2 = C->beta_shape * C->beta_shape;
+    const bool shape_prior = C->beta_shape > 0.0;
+    for (int idx = tid; idx < NS * NS; idx += T)
+        W.Hw[idx] = (W.xc[XC_HW + idx] + W.xc[XC_HW + NS * NS + idx]) + ((shape_prior && idx / NS == idx % NS) ? bs2 : 0.0);
+    if (tid < NS) W.g[(size_t)F * NB + tid] = (W.xc[XC_GW + tid] + W.xc[XC_GW + NS + tid]) + (shape_prior ? bs2 * xp[(size_t)F * NB + tid] : 0.0);
 }
 
 // ---- block-tridiagonal + arrowhead solve of (H_s + D^2 / radius) y = gs ---------------------------------------------------
 // H_s: scaled J^T J held as Hd (diagonal blocks), Ha (arrow rows), Hw, and the implicit off-diagonal blocks
-// -lambda^2 diag(scale_f,i scale_{f+1},i), i >= 1.  Returns false when a pivot is not positive.
+// -lambda^2 diag(scale_f,i scale_{f+1},i), i >= 1.
+//
+// The chain is eliminated FROM BOTH ENDS by the two CTAs of the problem's cluster: the master sweeps frames 0, 1, ... up to the
+// junction frame m = F / 2, the helper sweeps F - 1, F - 2, ... down to m + 1 (a block-tridiagonal matrix read backwards is block
+// tridiagonal again: the same code with the frame order reversed).  Before the master eliminates the junction frame it waits for
+// the helper and subtracts the helper's last block row as well (its panels travel through the exchange area), adds the helper's share
+// of the w Schur complement, solves the 10 x 10 arrow block and the junction frame; then both halves are back-substituted at the
+// same time, each away from the junction.
+//
+// win_forward: frames f0, f0 + dir, ... (nsteps of them).  Every frame couples to the next one visited; the last one does iff
+// `last_couples` (the helper's last frame couples to the junction).  `sync_last`: a cluster barrier precedes the last step, and the
+// block row in the exchange area (the helper's) is subtracted there too if `extra`.  sacc: this thread's tile of
+// sum [W ; z] [W ; z]^T (group-3 threads).  Returns false when a pivot is not positive.
 template <int T>
-__device__ bool win_solve(const FitConst* __restrict__ C, int F, double radius, WinWs& W, WinSmem& S) {
+__device__ bool win_forward(const FitConst* __restrict__ C, int F, double radius, WinWs& W, WinSmem& S, int f0, int dir, int nsteps, bool last_couples,
+                            bool sync_last, bool extra, double (&sacc)[4][4], int& grp_out, int& ti_out, int& tj_out) {
     const int tid = threadIdx.x;
-    WinChain& K = S.u.c;
     const double lam2 = C->lambda_temp * C->lambda_temp;
     const bool temporal = C->lambda_temp > 0.0 && F > 1;
-    // running Schur complement of the arrow block: thread (s, t), t <= s, owns Sw[s][t]; threads 64..73 own zw[s]
     WinTimer wt;
     wt.start();
     WinTiles& Q = S.u.t;
@@ -261,17 +303,18 @@ __device__ bool win_solve(const FitConst* __restrict__ C, int F, double radius, 
         grp = 3; ti = WT_RW + u / 3; tj = WT_RW + u % 3;      // tj is a tile ROW here: the tile is rows(ti) x rows(tj)^T
     }
     static_assert(T >= WT_TILES, "one tile per thread");
-    double a[4][4], sacc[4][4];
-#pragma unroll
-    for (int r = 0; r < 4; ++r)
-#pragma unroll
-        for (int c = 0; c < 4; ++c) sacc[r][c] = 0.0;
-    bool ok = true;
+    grp_out = grp; ti_out = ti; tj_out = tj;
+    double a[4][4];
+    bool ok = true, synced = false;
     if (tid == 0) S.flag = 1;
     __syncthreads();
-    for (int f = 0; f < F && ok; ++f) {
-        const bool has_next = temporal && f < F - 1;
-        const bool has_prev = temporal && f > 0;
+    for (int t = 0; t < nsteps; ++t) {
+        const int f = f0 + dir * t, fn = f + dir;             // this frame and the next one visited
+        const bool last = t == nsteps - 1;
+        const bool has_next = temporal && (!last || last_couples);
+        const bool has_prev = temporal && t > 0;
+        if (last && sync_last) { cluster_sync_all(); synced = true; }   // the helper's block row and its share of sacc are in the exchange area
+        const bool use_extra = last && extra && temporal;
         // (1) this frame's rows: [Hd_f + damping ; -lambda^2 S_f E S_f+1 ; Ha_f ; gs_f], minus the products with the previous frame's
         //     block row [B ; W ; z] (its panels are still in Q.bp)
         const double* Hd = W.Hd + (size_t)f * NB * NB;
@@ -290,7 +333,7 @@ __device__ bool win_solve(const FitConst* __restrict__ C, int F, double radius, 
                     }
                 } else if (grp == 1) {
                     const int i = 4 * (ti - WT_RB) + r;
-                    if (has_next && i == j && i >= 1) v = -lam2 * W.scale[(size_t)f * NB + i] * W.scale[(size_t)(f + 1) * NB + i];
+                    if (has_next && i == j && i >= 1) v = -lam2 * W.scale[(size_t)f * NB + i] * W.scale[(size_t)fn * NB + i];
                 } else if (grp == 2) {
                     const int sidx = 4 * (ti - WT_RW) + r;
                     if (sidx < NS) v = Ha[sidx * NB + j];
@@ -305,6 +348,24 @@ __device__ bool win_solve(const FitConst* __restrict__ C, int F, double radius, 
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const double2 r01 = Q.bp[k][q][0][rb], r23 = Q.bp[k][q][1][rb], c01 = Q.bp[k][q][0][cb], c23 = Q.bp[k][q][1][cb];
+                    const double rv[4] = {r01.x, r01.y, r23.x, r23.y}, cv[4] = {c01.x, c01.y, c23.x, c23.y};
+#pragma unroll
+                    for (int r = 0; r < 4; ++r)
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) a[r][c] = fma(-rv[r], cv[c], a[r][c]);
+                }
+            }
+        }
+        if (use_extra && (grp == 0 || grp == 2)) {
+            // the same products with the helper's last block row, read from the exchange area (layout of Q.bp)
+            const double2* xb = reinterpret_cast<const double2*>(W.xc + XC_BP);
+            constexpr int XR = WT_NR - WT_RB;
+            const int rb = (grp == 0 ? ti : ti - WT_RB), cb = tj;
+            for (int k = (grp == 0 ? ti : tj); k < WT_NC; ++k) {
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const double2* base = xb + (size_t)((k * 4 + q) * 2) * XR;
+                    const double2 r01 = base[rb], r23 = base[XR + rb], c01 = base[cb], c23 = base[XR + cb];
                     const double rv[4] = {r01.x, r01.y, r23.x, r23.y}, cv[4] = {c01.x, c01.y, c23.x, c23.y};
 #pragma unroll
                     for (int r = 0; r < 4; ++r)
@@ -434,21 +495,47 @@ __device__ bool win_solve(const FitConst* __restrict__ C, int F, double radius, 
         wt.mark(12);
     }
     __syncthreads();
-    if (!ok) return false;
-    // ---- arrow block: Sw = Hw + damping - sum_f W_f W_f^T ; zw = gs_w - sum_f W_f z_f (the group-3 tiles) ----
+    if (sync_last && !synced) cluster_sync_all();        // a failed sweep still meets the helper at the barrier
+    return ok;
+}
+
+// The helper hands its last block row (the panels of the last frame it swept, still in shared memory) and its share of the w Schur
+// complement to the master through the exchange area.
+template <int T>
+__device__ void win_publish_half(WinWs& W, WinSmem& S, const double (&sacc)[4][4], int grp, int ti, int tj, bool ok) {
+    const int tid = threadIdx.x;
+    const double2* src = reinterpret_cast<const double2*>(&S.u.t.bp[0][0][0][0]);
+    double2* dst = reinterpret_cast<double2*>(W.xc + XC_BP);
+    for (int i = tid; i < WT_NC * 4 * 2 * (WT_NR - WT_RB); i += T) dst[i] = src[i];
+    if (grp == 3) {
+        const int u = (ti - WT_RW) * 3 + (tj - WT_RW);
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) W.xc[XC_SACC + u * 16 + r * 4 + c] = sacc[r][c];
+    }
+    if (tid == 0) W.xc[XC_OK] = ok ? 1.0 : 0.0;
+}
+
+// master: Sw = Hw + damping - sum_f W_f W_f^T, zw = gs_w - sum_f W_f z_f from the group-3 tiles of both CTAs; 10 x 10 Cholesky; y_w.
+template <int T>
+__device__ bool win_arrow(int F, double radius, WinWs& W, WinSmem& S, const double (&sacc)[4][4], int grp, int ti, int tj, bool helper_has) {
+    const int tid = threadIdx.x;
     const size_t nw0 = (size_t)F * NB;
     if (grp == 3) {
+        const int u = (ti - WT_RW) * 3 + (tj - WT_RW);
 #pragma unroll
         for (int r = 0; r < 4; ++r)
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 const int sr = 4 * (ti - WT_RW) + r, sc = 4 * (tj - WT_RW) + c;
+                const double acc = sacc[r][c] + (helper_has ? W.xc[XC_SACC + u * 16 + r * 4 + c] : 0.0);
                 if (sr < NS && sc <= sr) {
-                    double v = W.Hw[sr * NS + sc] - sacc[r][c];
+                    double v = W.Hw[sr * NS + sc] - acc;
                     if (sr == sc) { const double l = sqrt(W.diag[nw0 + sr] / radius); v += l * l; }
                     S.Sw[sr * NS + sc] = v;
                 } else if (sr == NS && sc < NS) {
-                    S.zw[sc] = W.gs[nw0 + sc] - sacc[r][c];
+                    S.zw[sc] = W.gs[nw0 + sc] - acc;
                 }
             }
     }
@@ -477,9 +564,26 @@ __device__ bool win_solve(const FitConst* __restrict__ C, int F, double radius, 
     __syncthreads();
     if (!S.flag) return false;
     if (tid < NS) W.y[nw0 + tid] = S.yw[tid];
-    // ---- backward sweep: L_ff^T y_f = z_f - W_f^T y_w - L_{f+1,f}^T y_{f+1} ----
-    for (int f = F - 1; f >= 0; --f) {
-        const bool has_next = temporal && f < F - 1;
+    return true;
+}
+
+// ---- backward sweep: L_ff^T y_f = z_f - W_f^T y_w - Lo_f^T y_next(f), frames f0, f0 + dir, ... (nsteps), each after its `next` =
+//      f - dir (the frame it was coupled to in the forward sweep).  first_has_next: the first frame has one (the helper's first
+//      frame: the junction, whose y the master has left in W.y). ----
+template <int T>
+__device__ void win_back(const FitConst* __restrict__ C, int F, WinWs& W, WinSmem& S, int f0, int dir, int nsteps, bool first_has_next) {
+    const int tid = threadIdx.x;
+    WinChain& K = S.u.c;
+    const bool temporal = C->lambda_temp > 0.0 && F > 1;
+    WinTimer wt;
+    wt.start();
+    if (tid < NS) S.yw[tid] = W.y[(size_t)F * NB + tid];
+    if (nsteps > 0 && first_has_next && temporal)
+        for (int i = tid; i < NB; i += T) K.yn[i] = W.y[(size_t)(f0 - dir) * NB + i];
+    __syncthreads();
+    for (int t = 0; t < nsteps; ++t) {
+        const int f = f0 + dir * t;
+        const bool has_next = temporal && (t > 0 || first_has_next);
         const double* Ld = W.Ld + (size_t)f * NB * NB;
         for (int idx = tid; idx < NB * NB; idx += T) { const int r = idx / NB, c = idx % NB; if (c < r) K.M[r][c] = Ld[idx]; }
         if (has_next) {
@@ -494,7 +598,7 @@ __device__ bool win_solve(const FitConst* __restrict__ C, int F, double radius, 
 #pragma unroll
             for (int s = 0; s < NS; ++s) v -= K.M[ROW_W + s][i] * S.yw[s];
             if (has_next)
-                for (int k = 0; k <= i; ++k) v -= K.M[ROW_LO + k][i] * K.yn[k];      // L_{f+1,f} is upper triangular
+                for (int k = 0; k <= i; ++k) v -= K.M[ROW_LO + k][i] * K.yn[k];      // the coupling block is upper triangular
             K.rhs[i] = v;
         }
         __syncthreads();
@@ -511,11 +615,12 @@ __device__ bool win_solve(const FitConst* __restrict__ C, int F, double radius, 
         __syncthreads();
     }
     wt.mark(13);
-    return true;
 }
 
+// One problem = one cluster of two CTAs.  The master (cluster rank 0) runs the Levenberg-Marquardt loop; the helper waits for its
+// commands at a cluster barrier: evaluate the upper half of the frames, or eliminate / back-substitute the far half of the chain.
 template <int T>
-__global__ void __launch_bounds__(T, 1) fit_window_kernel(const FitConst* __restrict__ C, int nprob, const WinProblem* __restrict__ probs,
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T, 1) fit_window_kernel(const FitConst* __restrict__ C, int nprob, const WinProblem* __restrict__ probs,
                                                           const b3d_kp* __restrict__ kps_all, const int32_t* __restrict__ nkp_all,
                                                           const double* __restrict__ R0_all, double* __restrict__ poses,
                                                           double* __restrict__ Wshape, uint8_t* __restrict__ usable,
@@ -523,8 +628,9 @@ __global__ void __launch_bounds__(T, 1) fit_window_kernel(const FitConst* __rest
                                                           int32_t* __restrict__ term, double* __restrict__ workspace) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     WinSmem& S = *reinterpret_cast<WinSmem*>(smem_raw);
-    const int tid = threadIdx.x, pb = blockIdx.x;
-    if (pb >= nprob) return;
+    const int tid = threadIdx.x, pb = blockIdx.x >> 1;
+    const int rank = (int)cluster_ctarank();
+    if (pb >= nprob) return;                 // (both CTAs of the cluster)
     const WinProblem pr = probs[pb];
     const int F = pr.count, n = F * NB + NS;
     const b3d_kp* kps = kps_all + (size_t)pr.first * MAXKP;
@@ -537,13 +643,80 @@ __global__ void __launch_bounds__(T, 1) fit_window_kernel(const FitConst* __rest
     W.carve(workspace + pr.ws_offset, F);
     const double lam2 = C->lambda_temp * C->lambda_temp;
     const bool temporal = C->lambda_temp > 0.0 && F > 1;
+    const int m = F / 2, nh = F - 1 - m;                     // junction frame; frames the helper eliminates (F - 1 .. m + 1)
+    const int ev_split = (F + 1) / 2;                        // the master evaluates frames [0, ev_split), the helper the rest
+    if (tid < 16) win_phase_acc()[tid] = 0;
+    __syncthreads();
 
+    if (rank == 1) {
+        // ---------------- helper ----------------
+        double sacc[4][4];
+        int grp, ti, tj;
+        for (;;) {
+            cluster_sync_all();
+            const int cmd = (int)*(volatile double*)&W.xc[XC_CMD];
+            if (cmd == CMD_EXIT) break;
+            if (cmd == CMD_EVAL_JAC) {
+                win_evaluate<T, true>(C, F, W.x, kps, nkp, R0, W, S, ev_split, F, 1);
+                cluster_sync_all();
+            } else if (cmd == CMD_EVAL_COST) {
+                win_evaluate<T, false>(C, F, W.cand, kps, nkp, R0, W, S, ev_split, F, 1);
+                cluster_sync_all();
+            } else if (cmd == CMD_SOLVE) {
+                const double radius_h = *(volatile double*)&W.xc[XC_RADIUS];
+#pragma unroll
+                for (int r = 0; r < 4; ++r)
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) sacc[r][c] = 0.0;
+                const bool okh = win_forward<T>(C, F, radius_h, W, S, F - 1, -1, nh, true, false, false, sacc, grp, ti, tj);
+                win_publish_half<T>(W, S, sacc, grp, ti, tj, okh);
+                cluster_sync_all();                              // (A) the master takes the junction
+                cluster_sync_all();                              // (B) y_w and y of the junction frame are in W.y, or the solve failed
+                if (*(volatile double*)&W.xc[XC_OK] > 0.5) win_back<T>(C, F, W, S, m + 1, +1, nh, true);
+                cluster_sync_all();                              // (C)
+            }
+        }
+        return;
+    }
+    // ---------------- master ----------------
     for (int k = tid; k < F * NB; k += T) W.x[k] = xin[k];
     if (tid < NS) W.x[(size_t)F * NB + tid] = win[tid];
-    if (tid < 16) win_phase_acc()[tid] = 0;
     __syncthreads();
     WinTimer kt;
     kt.start();
+    // evaluation of all frames by both CTAs: command, barrier, own half, barrier, sum of the two shares
+    auto evaluate_all = [&](const double* xvec, bool jac) -> double {
+        if (tid == 0) *(volatile double*)&W.xc[XC_CMD] = jac ? (double)CMD_EVAL_JAC : (double)CMD_EVAL_COST;
+        cluster_sync_all();
+        const double part = jac ? win_evaluate<T, true>(C, F, xvec, kps, nkp, R0, W, S, 0, ev_split, 0)
+                                : win_evaluate<T, false>(C, F, xvec, kps, nkp, R0, W, S, 0, ev_split, 0);
+        cluster_sync_all();
+        const double total = part + *(volatile double*)&W.xc[XC_COST + 1];
+        if (jac) win_combine_shape<T>(C, F, xvec, W);
+        __syncthreads();
+        return total;
+    };
+    // the damped linear solve by both CTAs (see win_forward)
+    auto solve_all = [&](double rad) -> bool {
+        double sacc[4][4];
+        int grp, ti, tj;
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) sacc[r][c] = 0.0;
+        if (tid == 0) { *(volatile double*)&W.xc[XC_CMD] = (double)CMD_SOLVE; *(volatile double*)&W.xc[XC_RADIUS] = rad; }
+        cluster_sync_all();
+        bool ok = win_forward<T>(C, F, rad, W, S, 0, +1, m + 1, false, true, nh > 0, sacc, grp, ti, tj);      // barrier (A) inside
+        if (nh > 0) ok = ok && *(volatile double*)&W.xc[XC_OK] > 0.5;
+        if (ok) ok = win_arrow<T>(F, rad, W, S, sacc, grp, ti, tj, nh > 0);
+        if (ok) win_back<T>(C, F, W, S, m, -1, 1, false);          // the junction frame
+        __syncthreads();
+        if (tid == 0) *(volatile double*)&W.xc[XC_OK] = ok ? 1.0 : 0.0;
+        cluster_sync_all();                                      // (B)
+        if (ok) win_back<T>(C, F, W, S, m - 1, -1, m, true);
+        cluster_sync_all();                                      // (C)
+        return ok;
+    };
 
     double radius = wInitialRadius, decrease_factor = 2.0, x_cost = 0.0, cand_cost = 0.0, mcc = 0.0;
     bool reuse_diagonal = false, step_successful = true;
@@ -564,7 +737,7 @@ __global__ void __launch_bounds__(T, 1) fit_window_kernel(const FitConst* __rest
         return m;
     };
     auto eval_grad_jac = [&](bool first) -> bool {
-        x_cost = win_evaluate<T, true>(C, F, W.x, kps, nkp, R0, W, S);
+        x_cost = evaluate_all(W.x, true);
         if (!isfinite(x_cost)) return false;
         it.cost = x_cost;
         __syncthreads();
@@ -627,7 +800,7 @@ __global__ void __launch_bounds__(T, 1) fit_window_kernel(const FitConst* __rest
             reuse_diagonal = true;
             bool step_valid = false;
             kt.mark(0);
-            const bool solved = win_solve<T>(C, F, radius, W, S);
+            const bool solved = solve_all(radius);
             kt.mark(2);
             if (solved) {
                 __syncthreads();
@@ -671,7 +844,7 @@ __global__ void __launch_bounds__(T, 1) fit_window_kernel(const FitConst* __rest
             it.flags = 1;
             __syncthreads();
             kt.mark(3);
-            cand_cost = win_evaluate<T, false>(C, F, W.cand, kps, nkp, R0, W, S);
+            cand_cost = evaluate_all(W.cand, false);
             kt.mark(14);
             if (!isfinite(cand_cost)) cand_cost = DBL_MAX;
             it.step_norm = sqrt(block_sum<T>(sn, S.red));
@@ -701,6 +874,8 @@ __global__ void __launch_bounds__(T, 1) fit_window_kernel(const FitConst* __rest
         }
     }
     __syncthreads();
+    if (tid == 0) *(volatile double*)&W.xc[XC_CMD] = (double)CMD_EXIT;
+    cluster_sync_all();                      // releases the helper
     if (pb == 0 && tid < 16 && g_win_phase_on) g_win_phase[tid] += win_phase_acc()[tid];
     for (int k = tid; k < F * NB; k += T) xin[k] = W.x[k];
     if (tid < NS) win[tid] = W.x[(size_t)F * NB + tid];
@@ -719,7 +894,7 @@ int win_launch(const FitConst* dfc, const WinProblem* dprobs, int nprob, const b
                double* W, uint8_t* usable, b3d_iter_record* trace, int trace_stride, int32_t* niters, int32_t* term, double* ws, cudaStream_t st) {
     if (nprob <= 0) return B3D_OK;
     B3D_CUDA(cudaFuncSetAttribute(fit_window_kernel<FW_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(WinSmem)));   // per device: every call
-    fit_window_kernel<FW_THREADS><<<nprob, FW_THREADS, sizeof(WinSmem), st>>>(dfc, nprob, dprobs, kps, nkp, R0, poses, W, usable, trace, trace_stride,
+    fit_window_kernel<FW_THREADS><<<2 * nprob, FW_THREADS, sizeof(WinSmem), st>>>(dfc, nprob, dprobs, kps, nkp, R0, poses, W, usable, trace, trace_stride,
                                                                              niters, term, ws);
     B3D_LAUNCH_CHECK();
     return B3D_OK;

@@ -49,10 +49,12 @@ struct WinProblem {
     int32_t first, count;     // frames [first, first + count) of the frame arrays; the shared w block is row `first` of W
     int64_t ws_offset;        // doubles into the workspace
 };
+// exchange area between the two CTAs of a problem's cluster (fit_window.cu), at the end of the per-problem workspace
+constexpr int WIN_XC_DOUBLES = 7424;
 // per-problem global workspace, in doubles
 __host__ __device__ inline size_t win_ws_doubles(int F) {
     const size_t n = (size_t)F * NPF + NS;
-    return 10 * n + (size_t)F * (3 * NPF * NPF + 2 * NS * NPF) + 2 * NS * NS + (size_t)F * NPF;
+    return 10 * n + (size_t)F * (3 * NPF * NPF + 2 * NS * NPF) + 2 * NS * NS + (size_t)F * NPF + WIN_XC_DOUBLES;
 }
 // enqueue the LM solves of nprob problems (device-resident constants / problem table / workspace); no synchronisation
 int win_launch(const FitConst* dfc, const WinProblem* dprobs, int nprob, const b3d_kp* kps, const int32_t* nkp, const double* R0, double* poses,
