@@ -156,27 +156,29 @@ __device__ void gmm_LTv(const FitConst* __restrict__ C, const double* v /*69*/, 
             const double2* __restrict__ Lb = reinterpret_cast<const double2*>(L + cb);
             double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0, b0 = 0.0, b1 = 0.0, b2 = 0.0, b3 = 0.0;
             const double2 zero2 = make_double2(0.0, 0.0);
-            // rows 0 .. 31 can only touch pair A (cb >= 34); rows 32 .. 68 may touch both
-            for (int m = 0; m < 32; m += 8) {
-                double2 v[8];
+            // rows 0 .. 31 can only touch pair A (cb >= 34); rows 32 .. 68 may touch both.  Sixteen 16-byte loads are requested
+            // before the first is used: the matrices stream from L2 (~800 cycles away), and the bytes in flight per warp are what
+            // paces this loop (8 loads per batch: 13 k cycles per evaluation of the 8 components; the accumulation order is kept).
+            for (int m = 0; m < 32; m += 16) {
+                double2 v[16];
 #pragma unroll
-                for (int u = 0; u < 8; ++u) v[u] = (m + u >= ca) ? __ldg(La + (m + u) * RS) : zero2;
+                for (int u = 0; u < 16; ++u) v[u] = (m + u >= ca) ? __ldg(La + (m + u) * RS) : zero2;
 #pragma unroll
-                for (int u = 0; u < 8; u += 2) {
+                for (int u = 0; u < 16; u += 2) {
                     a0 += v[u].x * dd[m + u]; a1 += v[u].y * dd[m + u];
                     a2 += v[u + 1].x * dd[m + u + 1]; a3 += v[u + 1].y * dd[m + u + 1];
                 }
             }
-            for (int m = 32; m < NPRI; m += 4) {
-                double2 v[4], w4[4];
+            for (int m = 32; m < NPRI; m += 8) {
+                double2 v[8], w4[8];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
+                for (int u = 0; u < 8; ++u) {
                     const int r = m + u;
                     v[u] = (r < NPRI && r >= ca) ? __ldg(La + r * RS) : zero2;
                     w4[u] = (r < NPRI && r >= cb) ? __ldg(Lb + r * RS) : zero2;
                 }
 #pragma unroll
-                for (int u = 0; u < 4; u += 2) {
+                for (int u = 0; u < 8; u += 2) {
                     const double d0 = m + u < NPRI ? dd[m + u] : 0.0, d1 = m + u + 1 < NPRI ? dd[m + u + 1] : 0.0;
                     a0 += v[u].x * d0; a1 += v[u].y * d0; a2 += v[u + 1].x * d1; a3 += v[u + 1].y * d1;
                     b0 += w4[u].x * d0; b1 += w4[u].y * d0; b2 += w4[u + 1].x * d1; b3 += w4[u + 1].y * d1;
@@ -396,29 +398,24 @@ __device__ bool chol_tiles(SingleSmem& S, int n, double radius, int ti, int tj, 
     pc.mark(20);
     // factor the thread's own (diagonal) tile in registers and publish it; padding columns (>= n) have no pivot
     auto factor_own = [&](int k) {
+        // branch-free: the pivot chain is a serial stretch of ONE lane, paced by its instruction count.  A non-positive (or NaN)
+        // pivot only raises the flag; what the tile then holds is never used.  Padding columns (>= n) get 1 / L_jj = 0.
         bool bad = false;
 #pragma unroll
         for (int c = 0; c < 4; ++c) {
             const int j = 4 * k + c;
-            if (j < n && !bad) {
-                const double piv = a[c][c];
-                if (!(piv > 0.0)) { bad = true; }
-                else {
-                    const double inv = rsqrt(piv);
-                    a[c][c] = inv;
+            const bool exists = j < n;
+            const double piv = a[c][c];
+            bad = bad || (exists && !(piv > 0.0));
+            const double inv = exists ? rsqrt(piv) : 0.0;
+            a[c][c] = inv;
 #pragma unroll
-                    for (int r = c + 1; r < 4; ++r) a[r][c] *= inv;
+            for (int r = c + 1; r < 4; ++r) a[r][c] *= inv;
 #pragma unroll
-                    for (int c2 = c + 1; c2 < 4; ++c2)
+            for (int c2 = c + 1; c2 < 4; ++c2)
 #pragma unroll
-                        for (int r = c2; r < 4; ++r) a[r][c2] -= a[r][c] * a[c2][c];
-                    S.invd[j] = inv;
-                }
-            } else {
-                a[c][c] = 0.0;
-#pragma unroll
-                for (int r = c + 1; r < 4; ++r) a[r][c] = 0.0;
-            }
+                for (int r = c2; r < 4; ++r) a[r][c2] -= a[r][c] * a[c2][c];
+            if (exists) S.invd[j] = inv;
         }
         if (bad) S.chol_fail = 1;
 #pragma unroll

