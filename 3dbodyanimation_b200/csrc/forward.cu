@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 
 #include "internal.hpp"
@@ -638,3 +639,80 @@ int b3d_smpl_forward(const b3d_model* m, int32_t B, int32_t dtype, const void* w
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------------
+// b3d_smpl_forward_noalloc_dev: the evaluator for callers that may not allocate (CUDA graph capture, serving loops).  The
+// rest->posed joint transforms between the joint-chain kernel and the skinning kernel — the one scratch buffer of
+// b3d_smpl_forward_dev when the caller passes jointTrans = NULL — live in a file-scope device array sized for
+// B3D_NOALLOC_MAX_BODIES bodies of doubles (1024 * 24 * 12 * 8 B = 2.25 MiB, held by every GPU that loads the library).
+// The array's name is only a host-side handle: the device address is taken once per device with cudaGetSymbolAddress.
+// ---------------------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_noalloc_trans[(size_t)B3D_NOALLOC_MAX_BODIES * NJ * 12 * sizeof(double)];
+
+namespace b3d {
+
+static int noalloc_scratch(void** out) {
+    constexpr int MAXDEV = 64;
+    static std::mutex mu;
+    static void* addr[MAXDEV] = {};
+    int dev = -1;
+    B3D_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAXDEV) return set_error(B3D_EINVAL, "b3d_smpl_forward_noalloc_dev: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {   // once per device, with that device current
+        void* q = nullptr;
+        B3D_CUDA(cudaGetSymbolAddress(&q, g_noalloc_trans));
+        if (!q) return set_error(B3D_ECUDA, "b3d_smpl_forward_noalloc_dev: cudaGetSymbolAddress returned a null address");
+        addr[dev] = q;
+    }
+    *out = addr[dev];
+    return B3D_OK;
+}
+
+template <typename T>
+static int forward_noalloc_impl(const b3d_model* m, int B, const T* w, const T* p, const T* r, T* cloud, T* jointPos, cudaStream_t st) {
+    void* q = nullptr;
+    if (int rc = noalloc_scratch(&q)) return rc;
+    T* G = static_cast<T*>(q);   // every entry of the B x 24 x 12 block is written by the joint kernel before the skinning kernel
+                                 // reads it: nothing has to start at zero, and nothing of the previous call is read
+    const VertexTables<T>& t = sizeof(T) == 4 ? (const VertexTables<T>&)m->t32 : (const VertexTables<T>&)m->t64;
+    smpl_joints_kernel<T><<<(B + JW - 1) / JW, 32 * JW, 0, st>>>(m->d_sk, B, w, p, r, jointPos, G, nullptr, 1);
+    B3D_LAUNCH_CHECK();
+    if (!cloud) return B3D_OK;
+    const int tiles = (m->Vpad + LBS_THREADS - 1) / LBS_THREADS;
+    int groups = (148 * 8 + tiles - 1) / tiles;
+    if (groups > B) groups = B;
+    int per = (B + groups - 1) / groups;
+    per = (per + LBS_NB - 1) / LBS_NB * LBS_NB;
+    groups = (B + per - 1) / per;
+    dim3 grid(tiles, groups);
+    if (sizeof(T) == 4 && m->nw == 4 && m->ts.vert && m->V % 2 == 0) {
+        smpl_lbs_sorted_kernel<<<grid, LS_TILE, 0, st>>>(m->ts.vert, m->ts.wval, m->ts.wjoff, m->ts.loc, m->V, m->Vpad, B, per,
+                                                         (const float*)w, (const float*)G, (float*)cloud);
+    } else if (m->nw == 4) {
+        smpl_lbs_kernel<T, 4, false><<<grid, LBS_THREADS, 0, st>>>(t.vert, t.wval, t.wjoint, m->V, m->Vpad, B, per, w, G, nullptr, cloud);
+    } else if (m->nw == 8) {
+        smpl_lbs_kernel<T, 8, false><<<grid, LBS_THREADS, 0, st>>>(t.vert, t.wval, t.wjoint, m->V, m->Vpad, B, per, w, G, nullptr, cloud);
+    } else {
+        smpl_lbs_kernel<T, NJ, false><<<grid, LBS_THREADS, 0, st>>>(t.vert, t.wval, t.wjoint, m->V, m->Vpad, B, per, w, G, nullptr, cloud);
+    }
+    B3D_LAUNCH_CHECK();
+    return B3D_OK;
+}
+
+}  // namespace b3d
+
+extern "C" int b3d_smpl_forward_noalloc_dev(const b3d_model* m, int32_t B, int32_t dtype, const void* w, const void* p, const void* r,
+                                            void* cloud, void* jointPos, void* stream) {
+    if (!m || !w || !p || !r) return set_error(B3D_EINVAL, "b3d_smpl_forward_noalloc_dev: null argument");
+    if (B < 0) return set_error(B3D_EINVAL, "b3d_smpl_forward_noalloc_dev: B < 0");
+    if (B > B3D_NOALLOC_MAX_BODIES)
+        return set_error(B3D_EINVAL, "b3d_smpl_forward_noalloc_dev: B = %d exceeds B3D_NOALLOC_MAX_BODIES = %d (the static scratch holds no more; "
+                         "split the batch or call b3d_smpl_forward_dev)", B, B3D_NOALLOC_MAX_BODIES);
+    if (B == 0) return B3D_OK;
+    if (dtype == B3D_F32)
+        return forward_noalloc_impl<float>(m, B, (const float*)w, (const float*)p, (const float*)r, (float*)cloud, (float*)jointPos, (cudaStream_t)stream);
+    if (dtype == B3D_F64)
+        return forward_noalloc_impl<double>(m, B, (const double*)w, (const double*)p, (const double*)r, (double*)cloud, (double*)jointPos, (cudaStream_t)stream);
+    return set_error(B3D_EINVAL, "b3d_smpl_forward_noalloc_dev: bad dtype %d", dtype);
+}

@@ -149,6 +149,20 @@ int b3d_smpl_forward(const b3d_model* m, int32_t B, int32_t dtype, const void* w
 int b3d_smpl_forward_dev(const b3d_model* m, int32_t B, int32_t dtype, const void* w, const void* p, const void* r,
                          void* cloud, void* jointPos, void* jointTrans, int32_t flags, void* stream);
 
+/* Allocation-free variant of b3d_smpl_forward_dev (cloud and jointPos only; no flags: shape blend + skinning, float32 through the
+ * tile-sorted kernel, float64 through the generic one).  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  It calls no cudaMalloc / cudaMallocAsync / cudaFree and no allocating library routine: the B x 24 x 12 joint
+ * transforms that b3d_smpl_forward_dev keeps in stream-ordered scratch live in a file-scope `static __device__` array sized for
+ * B3D_NOALLOC_MAX_BODIES bodies of doubles (2.25 MiB, resident on every GPU that loads the library until exit).
+ * B > B3D_NOALLOC_MAX_BODIES is rejected with B3D_EINVAL.  All pointers are DEVICE pointers; cloud and jointPos may be NULL.
+ * Every call on a device shares the one array (it keeps the previous call's contents; the joint kernel overwrites every entry a
+ * call reads, so nothing needs clearing): calls that overlap on the GPU — different streams, or two host threads — RACE and
+ * must be serialised by the caller. */
+#define B3D_NOALLOC_MAX_BODIES 1024
+int b3d_smpl_forward_noalloc_dev(const b3d_model* m, int32_t B, int32_t dtype, const void* w, const void* p, const void* r,
+                                 void* cloud, void* jointPos, void* stream);
+
 /* ===================================================================================================== */
 /* Entry (3) vertex-level ICP term of ark::AvatarOptimizer: cost and gradient of       */
 /*   sum over correspondences 1/2 |cloud_i(w, p, q) - data_e|^2 for a batch of bodies.  Replaces            */
