@@ -68,7 +68,7 @@ struct WinWs {
 // exchange area, in doubles: the master's command and its operands, the helper's partial results
 constexpr int XC_CMD = 0, XC_RADIUS = 1, XC_OK = 2, XC_COST = 4 /* 2 */, XC_HW = 16 /* 2 x 100 */, XC_GW = 216 /* 2 x 10 */, XC_SACC = 240 /* 144 */,
               XC_BP = 512;  /* the helper's last frame's panels: WT_NC x 4 x 2 x 22 double2 */
-enum { CMD_EVAL_JAC = 1, CMD_EVAL_COST = 2, CMD_SOLVE = 3, CMD_EXIT = 9 };
+enum { CMD_EVAL_JAC = 1, CMD_EVAL_COST = 2, CMD_SOLVE = 3, CMD_EVAL_JAC0 = 4 /* first evaluation: no Jacobi scales yet */, CMD_EXIT = 9 };
 
 // Both CTAs of a problem's cluster: global writes before, reads after (release / acquire at cluster scope).
 __device__ __forceinline__ void cluster_sync_all() {
@@ -113,6 +113,7 @@ union WinUnion {
 struct WinSmem {
     WinUnion u;
     double xfull[NFULL];
+    double sc[NFULL];                     // Jacobi scales of the frame being evaluated (76) and of the shape (10)
     double R0[9];
     double red[40];
     double Hw[NS * NS], gw[NS], yw[NS], Sw[NS * NS], zw[NS];
@@ -122,13 +123,15 @@ struct WinSmem {
 
 // ---- evaluate every frame of the problem at parameters xp (n = 76 F + 10) -----------------------------------------------
 // Frames [f_lo, f_hi) only (the cluster's two CTAs split the frames); returns this CTA's share of the cost (rank 0 carries the shape
-// prior).  JAC: fills Hd / Ha (UNSCALED) and g of those frames in the workspace and leaves this CTA's share of the shape block in the
-// exchange area (XC_HW / XC_GW, slot `rank`); the master adds the two shares.  A frame's 86 x 86 normal equations are a SYRK of its
+// prior).  JAC: fills Hd / Ha and g of those frames in the workspace and leaves this CTA's share of the shape block in the
+// exchange area (XC_HW / XC_GW, slot `rank`); the master adds the two shares.  With `scaled` the Jacobi scaling of Ceres
+// (H_ij s_i s_j, gs = g s) is applied while the blocks are written (W.scale is fixed after the first evaluation of a solve);
+// without it (first evaluation) the blocks are left unscaled and the master scales them once the scales exist.  A frame's 86 x 86 normal equations are a SYRK of its
 // dense Jacobian over 4 x 4 register tiles (thread (ti, tj), 253 tiles), scattered straight into the block structure.
 template <int T, bool JAC>
 __device__ double win_evaluate(const FitConst* __restrict__ C, int F, const double* xp /* written by the master during the kernel: no read-only path */, const b3d_kp* __restrict__ kps,
                                const int32_t* __restrict__ nkp_all, const double* __restrict__ R0_all, WinWs& W, WinSmem& S, int f_lo, int f_hi,
-                               int rank) {
+                               int rank, bool scaled = false) {
     const int tid = threadIdx.x;
     WinEval& E = S.u.e;
     const double bp2 = C->beta_pose * C->beta_pose, bs2 = C->beta_shape * C->beta_shape, lam = C->lambda_temp, lam2 = lam * lam;
@@ -145,12 +148,18 @@ __device__ double win_evaluate(const FitConst* __restrict__ C, int F, const doub
         for (int k = tid; k < NS * NS; k += T) S.Hw[k] = 0.0;
         if (tid < NS) S.gw[tid] = 0.0;
     }
-    if (tid < NS) S.xfull[IDX_W + tid] = xp[(size_t)F * NB + tid];
+    if (tid < NS) {
+        S.xfull[IDX_W + tid] = xp[(size_t)F * NB + tid];
+        if (JAC) S.sc[NB + tid] = scaled ? W.scale[(size_t)F * NB + tid] : 1.0;
+    }
     for (int f = f_lo; f < f_hi; ++f) {
         const int nkp = min(max(nkp_all[f], 0), MAXKP);
         const double* xf = xp + (size_t)f * NB;
         __syncthreads();                    // previous frame's consumers are done with xfull / R0 / E
-        for (int k = tid; k < NB; k += T) S.xfull[k] = xf[k];
+        for (int k = tid; k < NB; k += T) {
+            S.xfull[k] = xf[k];
+            if (JAC) S.sc[k] = scaled ? W.scale[(size_t)f * NB + k] : 1.0;
+        }
         if (tid < 9) S.R0[tid] = R0_all[(size_t)f * 9 + tid];
         __syncthreads();
         wt.mark(5);
@@ -203,9 +212,11 @@ __device__ double win_evaluate(const FitConst* __restrict__ C, int F, const doub
                             if (pose_prior && i >= IDX_JAA) v += bp2;
                             if (i >= 1) v += nadj * lam2;                 // Vec3DiffCost on every parameter but the scale
                         }
+                        if (scaled) v *= S.sc[i] * S.sc[j];
                         Hd[i * NB + j] = v;
                         Hd[j * NB + i] = v;
                     } else if (j < NB) {
+                        if (scaled) v *= S.sc[i] * S.sc[j];
                         Ha[(i - NB) * NB + j] = v;
                     } else {                                              // shape x shape: summed over the frames (one owner per entry)
                         S.Hw[(i - NB) * NS + (j - NB)] += v;
@@ -225,6 +236,7 @@ __device__ double win_evaluate(const FitConst* __restrict__ C, int F, const doub
                 if (f > 0) v -= lam2 * (xf[k - NB] - xf[k]);
             }
             W.g[(size_t)f * NB + k] = v;
+            if (scaled) W.gs[(size_t)f * NB + k] = v * S.sc[k];
         }
         wt.mark(8);
     }
@@ -657,8 +669,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T, 1) fit_window_ker
             cluster_sync_all();
             const int cmd = (int)*(volatile double*)&W.xc[XC_CMD];
             if (cmd == CMD_EXIT) break;
-            if (cmd == CMD_EVAL_JAC) {
-                win_evaluate<T, true>(C, F, W.x, kps, nkp, R0, W, S, ev_split, F, 1);
+            if (cmd == CMD_EVAL_JAC || cmd == CMD_EVAL_JAC0) {
+                win_evaluate<T, true>(C, F, W.x, kps, nkp, R0, W, S, ev_split, F, 1, cmd == CMD_EVAL_JAC);
                 cluster_sync_all();
             } else if (cmd == CMD_EVAL_COST) {
                 win_evaluate<T, false>(C, F, W.cand, kps, nkp, R0, W, S, ev_split, F, 1);
@@ -686,10 +698,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T, 1) fit_window_ker
     WinTimer kt;
     kt.start();
     // evaluation of all frames by both CTAs: command, barrier, own half, barrier, sum of the two shares
-    auto evaluate_all = [&](const double* xvec, bool jac) -> double {
-        if (tid == 0) *(volatile double*)&W.xc[XC_CMD] = jac ? (double)CMD_EVAL_JAC : (double)CMD_EVAL_COST;
+    auto evaluate_all = [&](const double* xvec, bool jac, bool scaled) -> double {
+        if (tid == 0) *(volatile double*)&W.xc[XC_CMD] = jac ? (double)(scaled ? CMD_EVAL_JAC : CMD_EVAL_JAC0) : (double)CMD_EVAL_COST;
         cluster_sync_all();
-        const double part = jac ? win_evaluate<T, true>(C, F, xvec, kps, nkp, R0, W, S, 0, ev_split, 0)
+        const double part = jac ? win_evaluate<T, true>(C, F, xvec, kps, nkp, R0, W, S, 0, ev_split, 0, scaled)
                                 : win_evaluate<T, false>(C, F, xvec, kps, nkp, R0, W, S, 0, ev_split, 0);
         cluster_sync_all();
         const double total = part + *(volatile double*)&W.xc[XC_COST + 1];
@@ -738,7 +750,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T, 1) fit_window_ker
         return m;
     };
     auto eval_grad_jac = [&](bool first) -> bool {
-        x_cost = evaluate_all(W.x, true);
+        x_cost = evaluate_all(W.x, true, !first);
         if (!isfinite(x_cost)) return false;
         it.cost = x_cost;
         __syncthreads();
@@ -748,19 +760,22 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T, 1) fit_window_ker
                 W.scale[k] = 1.0 / (1.0 + sqrt(d));
             }
             __syncthreads();
-        }
-        // Jacobi scaling of the blocks (column scaling of J on both sides of J^T J)
-        for (size_t idx = tid; idx < (size_t)F * NB * NB; idx += T) {
-            const int f = (int)(idx / (NB * NB)), r = (int)(idx % (NB * NB)) / NB, c = (int)(idx % NB);
-            W.Hd[idx] *= W.scale[(size_t)f * NB + r] * W.scale[(size_t)f * NB + c];
-        }
-        for (size_t idx = tid; idx < (size_t)F * NS * NB; idx += T) {
-            const int f = (int)(idx / (NS * NB)), s = (int)(idx % (NS * NB)) / NB, c = (int)(idx % NB);
-            W.Ha[idx] *= W.scale[(size_t)F * NB + s] * W.scale[(size_t)f * NB + c];
+            // Jacobi scaling of the blocks (column scaling of J on both sides of J^T J).  Only here: every later evaluation applies
+            // the (now fixed) scales while it writes the blocks (win_evaluate, `scaled`)
+            for (size_t idx = tid; idx < (size_t)F * NB * NB; idx += T) {
+                const int f = (int)(idx / (NB * NB)), r = (int)(idx % (NB * NB)) / NB, c = (int)(idx % NB);
+                W.Hd[idx] *= W.scale[(size_t)f * NB + r] * W.scale[(size_t)f * NB + c];
+            }
+            for (size_t idx = tid; idx < (size_t)F * NS * NB; idx += T) {
+                const int f = (int)(idx / (NS * NB)), s = (int)(idx % (NS * NB)) / NB, c = (int)(idx % NB);
+                W.Ha[idx] *= W.scale[(size_t)F * NB + s] * W.scale[(size_t)f * NB + c];
+            }
+            for (int k = tid; k < F * NB; k += T) W.gs[k] = W.g[k] * W.scale[k];
         }
         if (tid < NS * NS) W.Hw[tid] *= W.scale[(size_t)F * NB + tid / NS] * W.scale[(size_t)F * NB + tid % NS];
+        if (tid < NS) W.gs[(size_t)F * NB + tid] = W.g[(size_t)F * NB + tid] * W.scale[(size_t)F * NB + tid];
         double gm = 0.0;
-        for (int k = tid; k < n; k += T) { const double gk = W.g[k]; W.gs[k] = gk * W.scale[k]; gm = fmax(gm, fabs(gk)); }
+        for (int k = tid; k < n; k += T) gm = fmax(gm, fabs(W.g[k]));
         it.gradient_max_norm = block_max(gm);     // unconstrained: |x - (x - g)| = |g|
         return true;
     };
@@ -845,7 +860,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T, 1) fit_window_ker
             it.flags = 1;
             __syncthreads();
             kt.mark(3);
-            cand_cost = evaluate_all(W.cand, false);
+            cand_cost = evaluate_all(W.cand, false, false);
             kt.mark(14);
             if (!isfinite(cand_cost)) cand_cost = DBL_MAX;
             it.step_norm = sqrt(block_sum<T>(sn, S.red));
