@@ -42,6 +42,12 @@ class SeqOpts(C.Structure):
                 ("beta_shape_lock", C.c_double)]
 
 
+class IcpSolveOpts(C.Structure):
+    _fields_ = [("max_iterations", C.c_int32), ("flags", C.c_int32), ("function_tolerance", C.c_double),
+                ("gradient_tolerance", C.c_double), ("parameter_tolerance", C.c_double), ("beta_pose", C.c_double),
+                ("beta_shape", C.c_double)]
+
+
 class B3DError(RuntimeError):
     def __init__(self, code: int, where: str):
         self.code = code

@@ -479,6 +479,24 @@ class IcpProblem:
         return dict(cost=cost, grad=grad)
 
 
+    def solve(self, w, p, q, gmm=None, beta_pose=0.0, beta_shape=0.0, shape=True, max_iterations=50, function_tolerance=1e-4,
+              gradient_tolerance=1e-10, parameter_tolerance=1e-8, trace_cap=128):
+        """The ceres::Solve of one ICP iteration (external/avatar/AvatarOptimizer.cpp:1486; LINE_SEARCH / BFGS / WOLFE / CUBIC,
+        options :1313-1339) for every body of the batch, on the GPU: returns the minimiser (w, p, q), the per-iteration records
+        (cost, cost_change, gradient_max_norm, step_norm, step_size, line-search evaluations, line-search iterations) and a
+        summary per body."""
+        w, p, q = _f64(w).reshape(self.B, NS).copy(), _f64(p).reshape(self.B, 3).copy(), _f64(q).reshape(self.B, NJ, 4).copy()
+        o = capi.IcpSolveOpts(int(max_iterations), 0 if shape else 2, function_tolerance, gradient_tolerance, parameter_tolerance,
+                              beta_pose, beta_shape)
+        trace, nrec, summ = np.zeros((self.B, trace_cap, 7)), np.zeros(self.B, dtype=np.int32), np.zeros((self.B, 6))
+        evals = C.c_int32(0)
+        check(lib().b3d_icp_solve(self.h, _gmm_handle(gmm), C.byref(o), ptr(w), ptr(p), ptr(q), ptr(trace), trace_cap, ptr(nrec),
+                                  ptr(summ), C.byref(evals)), "b3d_icp_solve")
+        return dict(w=w, p=p, q=q, trace=trace, nrec=nrec, initial_cost=summ[:, 0], final_cost=summ[:, 1],
+                    iterations=summ[:, 2].astype(int), evaluations=summ[:, 3].astype(int), restarts=summ[:, 4].astype(int),
+                    termination=summ[:, 5].astype(int), batched_evaluations=int(evals.value))
+
+
 def icp_nearest(model: AvatarModel, cloud, model_part, dptr, data, data_part, visible=None, dtype=np.float64):
     """findNN with invert = true (external/avatar/AvatarOptimizer.cpp:841-907): for every data point the nearest visible model point
     with the same part label (-1: none).  cloud (B, V, 3), model_part (V,), visible (B, V) or None, body b's data points at
@@ -508,3 +526,32 @@ def icp_visible(model: AvatarModel, cloud, dtype=np.float64):
     vis = np.empty(cloud.shape[:2], dtype=np.uint8)
     check(lib().b3d_icp_visible(model.h, cloud.shape[0], F64 if dt == np.float64 else F32, ptr(cloud), 0, ptr(vis)), "b3d_icp_visible")
     return vis
+
+
+def avatar_optimize(model: AvatarModel, w, p, q, dptr, data, data_part, model_part, *, gmm=None, beta_pose=0.0, beta_shape=0.0,
+                    icp_iters=3, max_iters_per_icp=20, enable_occlusion=True, shape=True, dtype=np.float64, function_tolerance=1e-4):
+    """ark::AvatarOptimizer::optimize (external/avatar/AvatarOptimizer.cpp:1246-1520) for a batch of bodies, every stage on the GPU:
+    per ICP iteration the posed cloud (Avatar::update), the occlusion mask (:1347-1365), the correspondences (findNN, invert = true,
+    :1391-1394), the residual blocks of the matched pairs (:1396-1474) and the BFGS line-search solve (:1486); the quaternions the
+    solve returns are the next iteration's rotations (:1491-1494).  Body b's data points are data[dptr[b]:dptr[b+1]] with part labels
+    data_part; model_part labels the model points (modelPartLabels, :1306-1310).  Returns the final state and one summary per
+    ICP iteration."""
+    from . import synth
+    w, p, q = _f64(w).copy(), _f64(p).copy(), _f64(q).copy()
+    b = w.shape[0]
+    dptr = np.ascontiguousarray(dptr, dtype=np.int64)
+    history = []
+    for _ in range(int(icp_iters)):
+        r = synth.quat_to_r(q)
+        cloud, _, _ = smpl_forward(model, w, p, r, dtype=np.float64)
+        vis = icp_visible(model, cloud) if enable_occlusion else None
+        nn = icp_nearest(model, cloud, model_part, dptr, data, data_part, visible=vis, dtype=np.float64)
+        prob = IcpProblem(model, dptr, nn, None, dptr, data, dtype=dtype)
+        res = prob.solve(w, p, q, gmm=gmm, beta_pose=beta_pose, beta_shape=beta_shape, shape=shape, max_iterations=max_iters_per_icp,
+                         function_tolerance=function_tolerance)
+        w, p, q = res["w"], res["p"], res["q"]
+        history.append(dict(matched=np.array([int((nn[dptr[i]:dptr[i + 1]] >= 0).sum()) for i in range(b)]), initial_cost=res["initial_cost"],
+                            final_cost=res["final_cost"], iterations=res["iterations"], evaluations=res["evaluations"],
+                            termination=res["termination"], nn=nn))
+        del prob
+    return dict(w=w, p=p, q=q, history=history)

@@ -578,6 +578,38 @@ def icp_leg(api, capi, lib, synth, model_np, dev, st, with_cpu, nb=4096, base=32
         out["cpu_baseline"] = {"value": ns / dt, "unit": "evaluations/s", "cores": host_threads(), "kind": "port",
                                "sample": f"{ns} of the {nb} bodies, oracle/icp.cpp (per-pair analytic Jacobian blocks, OpenMP over bodies)",
                                "max_rel_grad_diff_vs_gpu": err}
+    # the ceres::Solve of one ICP iteration (LINE_SEARCH / BFGS / WOLFE, AvatarOptimizer.cpp:1313-1339, :1486) for the whole batch:
+    # b3d_icp_solve_dev on resident state, shape prior on, 20 iterations at most (float32 evaluation kernel)
+    so = capi.IcpSolveOpts(20, 0, 1e-4, 1e-10, 1e-8, 0.0, 0.1)
+    summ = torch.empty(nb, 6, dtype=torch.float64, device=dev)
+    nrec = torch.empty(nb, dtype=torch.int32, device=dev)
+    evals = C.c_int32(0)
+
+    def solve():
+        ww, pp, qq = w.clone(), p.clone(), q.clone()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        capi.check(lib.b3d_icp_solve_dev(prob.h, None, C.byref(so), P(ww), P(pp), P(qq), None, 0, P(nrec), P(summ), C.byref(evals), C.c_void_p(st)),
+                   "b3d_icp_solve_dev")
+        torch.cuda.synchronize()
+        return time.perf_counter() - t0, ww, pp, qq
+    solve()
+    dts = [solve()[0] for _ in range(3)]
+    dt_s = float(np.mean(dts))
+    sm = summ.cpu().numpy()
+    out["solve"] = {"call": "b3d_icp_solve_dev: per batched objective evaluation one b3d_icp_eval_dev + priors + icp_bfgs_advance_kernel (CTA = body)",
+                    "bodies": nb, "value": nb / dt_s, "unit": "solves/s", "ms_per_call": dt_s * 1e3, "max_iterations": 20,
+                    "batched_evaluations": int(evals.value), "mean_iterations": float(sm[:, 2].mean()), "mean_evaluations_per_body": float(sm[:, 3].mean()),
+                    "mean_cost_ratio_final_over_initial": float((sm[:, 1] / sm[:, 0]).mean()), "timing": "wall clock around the call, state resident"}
+    if with_cpu:
+        ns = base
+        t0 = time.perf_counter()
+        refs = om.icp_minimize(None, 0.0, 0.1, x["w"], x["p"], x["q"], x["cptr"], x["mpt"], x["dpt"], x["dptr"], x["data"], max_iterations=20,
+                               nthreads=host_threads())
+        dtc = time.perf_counter() - t0
+        out["solve"]["cpu_baseline"] = {"value": ns / dtc, "unit": "solves/s", "cores": host_threads(), "kind": "port",
+                                        "sample": f"{ns} of the {nb} bodies, oracle/icp_solve.cpp (Ceres 1.14 line-search minimiser restated) on oracle/icp.cpp, OpenMP over bodies",
+                                        "max_rel_final_cost_diff_vs_gpu_f32": float(np.max(np.abs(sm[:ns, 1] - refs["final_cost"]) / refs["final_cost"]))}
     return out
 
 
@@ -775,10 +807,19 @@ def main():
     ap.add_argument("--c3-frames", type=int, default=2000)
     ap.add_argument("--c5-frames", type=int, default=100000)
     args = ap.parse_args()
-    if args.impl == "reference":
-        run_reference(args)
-    else:
-        run_b200(args)
+    # stdout carries ONE JSON line: anything a library writes to file descriptor 1 meanwhile (NCCL prints its version there when
+    # NCCL_DEBUG asks for it) goes to stderr instead
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w")
+    try:
+        if args.impl == "reference":
+            run_reference(args)
+        else:
+            run_b200(args)
+    finally:
+        sys.stdout.flush()
 
 
 if __name__ == "__main__":

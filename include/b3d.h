@@ -215,6 +215,31 @@ int b3d_icp_eval(b3d_icp* h, const double* w, const double* p, const double* q, 
 int b3d_icp_eval_dev(b3d_icp* h, const double* w, const double* p, const double* q, int32_t flags, double* cost, double* grad,
                      void* stream);
 
+/* The solve of one ICP iteration for a batch of bodies: replaces the ceres::Solve call of AvatarOptimizer::optimize
+ * (external/avatar/AvatarOptimizer.cpp:1486) with the options set at :1313-1339 — minimizer_type LINE_SEARCH, line_search_direction_type
+ * BFGS, line_search_interpolation_type CUBIC, line_search_type WOLFE (Ceres default), function_tolerance 1e-4, max_num_iterations =
+ * maxItersPerICP, every other option at its Ceres 1.14 default — on the objective b3d_icp_eval_dev + b3d_icp_add_priors_dev evaluate
+ * (ICP blocks + pose prior + shape prior, :1439-1474).  w (B x 10), p (B x 3), q (B x 24 x 4) are the starting point on entry and
+ * the minimiser's result on return (what :1491-1494 converts back to rotation matrices).  Optional outputs: trace (B x trace_cap x
+ * 7 doubles per iteration record: cost, cost_change, gradient_max_norm, step_norm, step_size, line-search evaluations,
+ * line-search iterations; record 0 is the starting point), nrec (B: records written or wanted), summary (B x 6 doubles: initial
+ * cost, final cost, iterations, evaluations, direction restarts, termination B3D_ICP_TERM_*), evaluations_out (batched objective
+ * evaluations launched = evaluations of the slowest body, rounded up to the host's polling interval). */
+enum { B3D_ICP_TERM_NO_CONVERGENCE = 0, B3D_ICP_TERM_GRADIENT_TOL = 1, B3D_ICP_TERM_PARAMETER_TOL = 2, B3D_ICP_TERM_FUNCTION_TOL = 3,
+       B3D_ICP_TERM_FAILURE = 4 };
+typedef struct b3d_icp_solve_opts {
+    int32_t max_iterations;        /* maxItersPerICP */
+    int32_t flags;                 /* B3D_ICP_POSE_ONLY: shapeEnabled = false */
+    double function_tolerance;     /* 1e-4 (:1334) */
+    double gradient_tolerance;     /* 1e-10 (Ceres default) */
+    double parameter_tolerance;    /* 1e-8 (Ceres default) */
+    double beta_pose, beta_shape;  /* betaPose, betaShape (scaled by sqrt(#residual blocks) / 15 inside, :1457-1458) */
+} b3d_icp_solve_opts;
+int b3d_icp_solve(b3d_icp* h, const b3d_gmm* gmm, const b3d_icp_solve_opts* opts, double* w, double* p, double* q, double* trace,
+                  int32_t trace_cap, int32_t* nrec, double* summary, int32_t* evaluations_out);
+int b3d_icp_solve_dev(b3d_icp* h, const b3d_gmm* gmm, const b3d_icp_solve_opts* opts, double* w, double* p, double* q, double* trace,
+                      int32_t trace_cap, int32_t* nrec, double* summary, int32_t* evaluations_out, void* stream);
+
 /* ===================================================================================================== */
 /* Entry (2) batched Levenberg-Marquardt driver: replaces the ceres::Problem + ceres::Solve inside          */
 /*   OptimizePoseReprojection (include/Sim3BA.h:515-683), OptimizePoseShapeReprojection (:348-511)          */

@@ -291,6 +291,35 @@ void orc_icp_nearest(int B, int V, const double* cloud, const int32_t* model_par
         icp_nearest(V, cloud + 3 * (size_t)V * b, model_part, visible ? visible + (size_t)V * b : nullptr, (int)(dptr[b + 1] - dptr[b]),
                     data + 3 * dptr[b], data_part + dptr[b], out + dptr[b]);
 }
+// the BFGS / Wolfe minimiser on the ICP objective (icp_solve.cpp), body by body (OpenMP over bodies).  trace: B x trace_cap records
+// of 7 doubles (cost, cost_change, gradient_max_norm, step_norm, step_size, line-search evaluations, line-search iterations);
+// summary: B x 6 doubles (initial cost, final cost, iterations, evaluations, restarts, termination)
+void orc_icp_minimize(void* mp, void* gp, int B, double beta_pose, double beta_shape, const int64_t* cptr, const int32_t* mpt,
+                      const int32_t* dpt, const int64_t* dptr, const double* data, int shape_enabled, int max_iterations,
+                      double function_tolerance, double gradient_tolerance, double parameter_tolerance, double* w, double* p, double* q,
+                      double* trace, int trace_cap, int32_t* nrec, double* summary, int nthreads) {
+    const Model& M = *(Model*)mp;
+    IcpSolveOptions o;
+    o.max_iterations = max_iterations; o.function_tolerance = function_tolerance; o.gradient_tolerance = gradient_tolerance;
+    o.parameter_tolerance = parameter_tolerance;
+#pragma omp parallel for num_threads(nthreads > 0 ? nthreads : 1) schedule(dynamic, 1)
+    for (int b = 0; b < B; ++b) {
+        const int64_t c0 = cptr[b];
+        std::vector<IcpSolveRecord> tr;
+        IcpSolveSummary sm;
+        icp_minimize(M, (const GMM*)gp, beta_pose, beta_shape, (int)(cptr[b + 1] - c0), mpt + c0, dpt + c0, data + 3 * dptr[b], shape_enabled,
+                     o, w + (size_t)b * M.S, p + 3 * (size_t)b, q + 4 * (size_t)M.J * b, &tr, &sm);
+        const int n = std::min<int>((int)tr.size(), trace_cap);
+        if (nrec) nrec[b] = (int)tr.size();
+        for (int i = 0; i < n && trace; ++i) {
+            double* t = trace + ((size_t)b * trace_cap + i) * 7;
+            t[0] = tr[i].cost; t[1] = tr[i].cost_change; t[2] = tr[i].gradient_max_norm; t[3] = tr[i].step_norm; t[4] = tr[i].step_size;
+            t[5] = tr[i].line_search_evals; t[6] = tr[i].line_search_iters;
+        }
+        double* sv = summary + (size_t)b * 6;
+        sv[0] = sm.initial_cost; sv[1] = sm.final_cost; sv[2] = sm.iterations; sv[3] = sm.evaluations; sv[4] = sm.restarts; sv[5] = sm.termination;
+    }
+}
 void orc_quat_plus(int n, const double* x, const double* d, double* out) {
     for (int i = 0; i < n; ++i) quat_plus(x + 4 * i, d + 3 * i, out + 4 * i);
 }

@@ -227,4 +227,25 @@ void icp_visible(int V, int F, const uint32_t* faces, const double* cloud, uint8
 void icp_nearest(int V, const double* cloud, const int* model_part, const uint8_t* visible, int nd, const double* data,
                  const int* data_part, int* out);
 
+// The minimiser of AvatarOptimizer::optimize (icp_solve.cpp): Ceres 1.14 LINE_SEARCH / BFGS / WOLFE / CUBIC on the ICP objective
+// (data term + pose prior + shape prior).  w / p / q in and out.
+enum { ICP_TERM_NO_CONVERGENCE = 0, ICP_TERM_GRADIENT_TOL = 1, ICP_TERM_PARAMETER_TOL = 2, ICP_TERM_FUNCTION_TOL = 3, ICP_TERM_FAILURE = 4 };
+struct IcpSolveOptions {
+    int max_iterations = 50;
+    double function_tolerance = 1e-4;     // AvatarOptimizer.cpp:1334
+    double gradient_tolerance = 1e-10;    // Ceres default
+    double parameter_tolerance = 1e-8;    // Ceres default
+};
+struct IcpSolveRecord {
+    double cost = 0, cost_change = 0, gradient_max_norm = 0, step_norm = 0, step_size = 0;
+    int line_search_evals = 0, line_search_iters = 0;
+};
+struct IcpSolveSummary {
+    double initial_cost = 0, final_cost = 0;
+    int iterations = 0, evaluations = 0, restarts = 0, termination = 0;
+};
+int icp_minimize(const Model& M, const GMM* gmm, double beta_pose, double beta_shape, int ncorr, const int* mpt, const int* dpt,
+                 const double* data, int shape_enabled, const IcpSolveOptions& o, double* w, double* p, double* q,
+                 std::vector<IcpSolveRecord>* trace, IcpSolveSummary* summary);
+
 }  // namespace orc

@@ -115,6 +115,23 @@ class Model:
                            _p(jac), _p(cost), _p(grad), nthreads)
         return dict(cost=cost, grad=grad, resid=resid, jac=jac)
 
+    def icp_minimize(self, gmm, beta_pose, beta_shape, w, p, q, cptr, mpt, dpt, dptr, data, shape=True, max_iterations=50,
+                     function_tolerance=1e-4, gradient_tolerance=1e-10, parameter_tolerance=1e-8, trace_cap=128, nthreads=1):
+        """The ceres::Solve of AvatarOptimizer::optimize (LINE_SEARCH, BFGS, WOLFE, CUBIC) on the ICP objective; returns the
+        minimiser (w, p, q), per-iteration records and a summary per body."""
+        w, p, q, data = _f64(w).copy(), _f64(p).copy(), _f64(q).copy(), _f64(data)
+        b = w.shape[0]
+        cptr, dptr = np.ascontiguousarray(cptr, dtype=np.int64), np.ascontiguousarray(dptr, dtype=np.int64)
+        mpt, dpt = np.ascontiguousarray(mpt, dtype=np.int32), np.ascontiguousarray(dpt, dtype=np.int32)
+        trace, nrec, summ = np.zeros((b, trace_cap, 7)), np.zeros(b, dtype=np.int32), np.zeros((b, 6))
+        lib().orc_icp_minimize(self.h, gmm.h if gmm is not None else None, b, C.c_double(beta_pose), C.c_double(beta_shape), _p(cptr),
+                               _p(mpt), _p(dpt), _p(dptr), _p(data), int(shape), int(max_iterations), C.c_double(function_tolerance),
+                               C.c_double(gradient_tolerance), C.c_double(parameter_tolerance), _p(w), _p(p), _p(q), _p(trace),
+                               int(trace_cap), _p(nrec), _p(summ), nthreads)
+        return dict(w=w, p=p, q=q, trace=trace, nrec=nrec, initial_cost=summ[:, 0], final_cost=summ[:, 1],
+                    iterations=summ[:, 2].astype(int), evaluations=summ[:, 3].astype(int), restarts=summ[:, 4].astype(int),
+                    termination=summ[:, 5].astype(int))
+
     def reproj_check(self, with_shape, jid, u, v, cam, R0, x86):
         out = [np.zeros(2), np.zeros(2), np.zeros((2, NFULL)), np.zeros(2), np.zeros((2, NFULL))]
         lib().orc_reproj_check(self.h, int(with_shape), int(jid), C.c_double(u), C.c_double(v), _p(_f64(cam)), _p(_f64(R0)),

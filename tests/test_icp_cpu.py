@@ -97,3 +97,43 @@ def test_icp_priors_oracle_matches_numpy(synth, orc, model_np):
         g[75:] = sbs * sbs * x["w"][b]
         assert abs(cost[b] - c) < 1e-10 * c
         assert np.max(np.abs(grad[b] - g)) < 1e-10 * np.max(np.abs(g))
+
+
+def test_icp_minimiser_oracle_properties(synth, orc, model_np):
+    """The oracle's restatement of the Ceres 1.14 minimiser AvatarOptimizer::optimize configures (LINE_SEARCH, BFGS, WOLFE, CUBIC;
+    AvatarOptimizer.cpp:1313-1339).  Ceres is absent and the reference never tests this loop, so it is pinned by what the published
+    algorithm guarantees: every accepted step satisfies the strong Wolfe conditions' sufficient decrease (cost strictly decreasing,
+    cost_change equal to the difference of consecutive costs), the first record is the starting point, the termination test is the
+    function tolerance |cost_change| <= 1e-4 * previous cost, the result re-evaluates to the reported final cost, and
+    shapeEnabled = false leaves the shape keys untouched."""
+    from conftest import PRIOR_TXT
+    prior = synth.load_pose_prior(PRIOR_TXT)
+    og = orc.GMM(prior=prior)
+    om = orc.Model(model_np)
+    x = synth.make_icp_inputs(model_np, 3, 77, ndata=600)
+    args = (x["cptr"], x["mpt"], x["dpt"], x["dptr"], x["data"])
+    r = om.icp_minimize(og, 0.05, 0.12, x["w"], x["p"], x["q"], *args, max_iterations=200, function_tolerance=1e-4, nthreads=3)
+    totals = np.diff(x["cptr"]).astype(np.float64)
+    for b in range(3):
+        n = int(r["nrec"][b])
+        t = r["trace"][b, :n]
+        assert n == r["iterations"][b] + 1
+        assert t[0, 1] == 0.0 and t[0, 4] == 0.0
+        assert np.all(np.diff(t[:, 0]) < 0.0)
+        assert np.allclose(t[1:, 1], t[:-1, 0] - t[1:, 0], rtol=0, atol=1e-9 * t[0, 0])
+        assert np.all(t[1:, 4] > 0.0) and np.all(t[1:, 5] >= 1) and np.all(t[1:, 5] <= 20)
+        if r["termination"][b] == 3:   # function tolerance: met at the last record, not before
+            assert abs(t[-1, 1]) <= 1e-4 * t[-2, 0]
+            assert np.all(np.abs(t[1:-1, 1]) > 1e-4 * t[:-2, 0])
+        assert r["termination"][b] in (0, 3)
+    assert np.all(np.abs(np.linalg.norm(r["q"], axis=-1) - 1.0) < 1e-12), "Plus keeps the quaternions on the unit sphere"
+    e = om.icp_eval(r["w"], r["p"], r["q"], *args, nthreads=3)
+    c, _ = orc.icp_priors(og, 0.05, 0.12, totals, r["w"], r["q"], e["cost"], e["grad"])
+    assert np.max(np.abs(c - r["final_cost"]) / c) < 1e-12
+    assert np.all(r["final_cost"] < 0.2 * r["initial_cost"])
+    # pose only
+    r2 = om.icp_minimize(og, 0.05, 0.12, x["w"], x["p"], x["q"], *args, shape=False, max_iterations=10, nthreads=3)
+    assert np.array_equal(r2["w"], x["w"]) and np.all(r2["final_cost"] < r2["initial_cost"])
+    # max_iterations = 0: nothing but the first evaluation
+    r0 = om.icp_minimize(None, 0.0, 0.0, x["w"], x["p"], x["q"], *args, max_iterations=0)
+    assert np.all(r0["nrec"] == 1) and np.all(r0["evaluations"] == 1) and np.array_equal(r0["q"], x["q"])

@@ -256,3 +256,125 @@ def test_icp_iteration_stays_on_the_device(synth, orc, model_np, gpu_model):
     lib.b3d_icp_destroy(h)
     assert np.allclose(tcost.cpu().numpy(), want["cost"], rtol=1e-12, atol=0)
     assert np.allclose(tgrad.cpu().numpy(), want["grad"], rtol=0, atol=1e-11 * np.max(np.abs(want["grad"])))
+
+
+def _solve_inputs(synth, model_np, b, seed, ndata):
+    x = synth.make_icp_inputs(model_np, b, seed, ndata=ndata)
+    return x
+
+
+@pytest.mark.parametrize("shape", [True, False])
+def test_icp_solve_matches_oracle_minimiser(synth, orc, model_np, gpu_model, shape):
+    """b3d_icp_solve (the ceres::Solve of AvatarOptimizer::optimize: LINE_SEARCH / BFGS / WOLFE / CUBIC, AvatarOptimizer.cpp:1313-1339,
+    :1486) against the oracle's restatement of the same minimiser, float64 evaluation kernel, ICP term + both priors: per body the
+    iteration records (cost, step size, line-search evaluations) and the minimiser.  Iteration, evaluation and line-search counts
+    must be equal.  Tolerances: the two sides evaluate the same objective to 1e-10 (test_icp_full_objective_with_priors) and a
+    quasi-Newton trajectory amplifies rounding differences from iteration to iteration (the inverse Hessian is built from gradient
+    differences): cost trace 1e-10 relative over the first 12 iterations and 1e-8 over all 25, minimiser 1e-7 (measured on B200:
+    5e-14, 1.6e-11 and 1e-11)."""
+    from conftest import PRIOR_TXT
+    api = pkg("api")
+    prior = synth.load_pose_prior(PRIOR_TXT)
+    gg, og = api.GaussianMixture(prior=prior), orc.GMM(prior=prior)
+    B = 5
+    x = _solve_inputs(synth, model_np, B, 52, 1500)
+    om = orc.Model(model_np)
+    kw = dict(max_iterations=25, function_tolerance=1e-4)
+    ref = om.icp_minimize(og, 0.05, 0.12, x["w"], x["p"], x["q"], x["cptr"], x["mpt"], x["dpt"], x["dptr"], x["data"], shape=shape,
+                          nthreads=5, **kw)
+    prob = api.IcpProblem(gpu_model, x["cptr"], x["mpt"], x["dpt"], x["dptr"], x["data"], dtype=np.float64)
+    got = prob.solve(x["w"], x["p"], x["q"], gmm=gg, beta_pose=0.05, beta_shape=0.12, shape=shape, **kw)
+    worst = dict(cost_head=0.0, cost_tail=0.0, step=0.0, w=0.0, p=0.0, q=0.0)
+    for b in range(B):
+        assert got["nrec"][b] == ref["nrec"][b], (b, got["nrec"][b], ref["nrec"][b])
+        assert got["iterations"][b] == ref["iterations"][b] and got["termination"][b] == ref["termination"][b]
+        assert got["evaluations"][b] == ref["evaluations"][b]
+        n = int(ref["nrec"][b])
+        tg, tr = got["trace"][b, :n], ref["trace"][b, :n]
+        assert np.array_equal(tg[:, 5:], tr[:, 5:]), "line-search evaluation / iteration counts per iteration"
+        rel = np.abs(tg[:, 0] - tr[:, 0]) / tr[:, 0]
+        worst["cost_head"] = max(worst["cost_head"], float(rel[:13].max()))
+        worst["cost_tail"] = max(worst["cost_tail"], float(rel.max()))
+        worst["step"] = max(worst["step"], float(np.max(np.abs(tg[1:, 4] - tr[1:, 4]) / tr[1:, 4])))
+        assert np.all(np.diff(tg[:, 0]) < 0), "the Wolfe search only accepts decreasing steps"
+    worst["w"] = float(np.max(np.abs(got["w"] - ref["w"])))
+    worst["p"] = float(np.max(np.abs(got["p"] - ref["p"])))
+    worst["q"] = float(np.max(np.abs(got["q"] - ref["q"])))
+    print("\n[icp solve, shape=%s] iterations %s, evaluations %s, batched evaluations %d; worst deviations %s"
+          % (shape, got["iterations"].tolist(), got["evaluations"].tolist(), got["batched_evaluations"], worst))
+    assert worst["cost_head"] < 1e-10 and worst["cost_tail"] < 1e-8 and worst["step"] < 1e-6
+    assert worst["w"] < 1e-7 and worst["p"] < 1e-7 and worst["q"] < 1e-7
+    if not shape:
+        assert np.array_equal(got["w"], x["w"]), "shapeEnabled = false leaves the shape keys alone"
+    # the result is a better point of the objective the evaluator reports
+    chk = prob.eval_full(got["w"], got["p"], got["q"], gmm=gg, beta_pose=0.05, beta_shape=0.12, shape=shape)
+    assert np.max(np.abs(chk["cost"] - got["final_cost"]) / got["final_cost"]) < 1e-9
+    assert np.all(got["final_cost"] < 0.5 * got["initial_cost"])
+
+
+def test_icp_solve_float32_kernel_and_limits(synth, orc, model_np, gpu_model):
+    """The float32 evaluation kernel under the same minimiser: it converges to the same basin (final cost within 2 % of the float64
+    run).  max_iterations = 0 returns the starting point with one record; a batch whose bodies stop at different iterations keeps
+    the finished bodies' results."""
+    api = pkg("api")
+    B = 4
+    x = _solve_inputs(synth, model_np, B, 53, 1200)
+    p64 = api.IcpProblem(gpu_model, x["cptr"], x["mpt"], x["dpt"], x["dptr"], x["data"], dtype=np.float64)
+    p32 = api.IcpProblem(gpu_model, x["cptr"], x["mpt"], x["dpt"], x["dptr"], x["data"], dtype=np.float32)
+    a = p64.solve(x["w"], x["p"], x["q"], beta_shape=0.1, max_iterations=30)
+    b = p32.solve(x["w"], x["p"], x["q"], beta_shape=0.1, max_iterations=30)
+    assert np.max(np.abs(a["final_cost"] - b["final_cost"]) / a["final_cost"]) < 2e-2
+    z = p64.solve(x["w"], x["p"], x["q"], beta_shape=0.1, max_iterations=0)
+    assert np.array_equal(z["w"], x["w"]) and np.array_equal(z["q"], x["q"]) and np.all(z["nrec"] == 1) and np.all(z["iterations"] == 0)
+    assert np.allclose(z["initial_cost"], a["initial_cost"], rtol=1e-12)
+    # different stopping points inside one batch: a loose tolerance stops some bodies early
+    c = p64.solve(x["w"], x["p"], x["q"], beta_shape=0.1, max_iterations=30, function_tolerance=2e-2)
+    assert len(set(c["iterations"].tolist())) > 1 or np.all(c["iterations"] < 30)
+    for bb in range(B):
+        n = int(c["nrec"][bb])
+        assert np.allclose(c["trace"][bb, :n, 0], a["trace"][bb, :n, 0], rtol=1e-6)
+
+
+def test_avatar_optimize_loop_matches_oracle_chain(synth, orc):
+    """The whole AvatarOptimizer::optimize loop (AvatarOptimizer.cpp:1346-1516: occlusion mask -> findNN -> residual blocks -> BFGS
+    solve -> rotations, icp_iters times) on the GPU against the same chain of oracle calls: identical correspondences in every ICP
+    iteration, equal iteration / evaluation counts, final state to 1e-6."""
+    from conftest import PRIOR_TXT
+    api = pkg("api")
+    rm = synth.make_render_model()          # a model with faces (the occlusion test needs them)
+    gm, om = api.AvatarModel(rm), orc.Model(rm)
+    prior = synth.load_pose_prior(PRIOR_TXT)
+    gg, og = api.GaussianMixture(prior=prior), orc.GMM(prior=prior)
+    B, nd, nparts = 3, 1200, 6
+    rng = np.random.default_rng(11)
+    V = rm["v_template"].shape[0]
+    model_part = (np.argmax(rm["weights"], axis=1) % nparts).astype(np.int32)
+    x = synth.make_icp_inputs(rm, B, 91, ndata=nd)
+    # data: noisy samples of a differently posed copy of the body, labelled with the part of the model point they came from
+    tgt = synth.make_forward_inputs(B, 93)
+    tq = x["q"] + 0.05 * rng.normal(size=x["q"].shape)
+    tq /= np.linalg.norm(tq, axis=-1, keepdims=True)
+    tcloud, _, _ = om.forward(x["w"] + 0.2 * tgt["w"], x["p"] + 0.02, synth.quat_to_r(tq))
+    src = rng.integers(0, V, (B, nd))
+    data = (tcloud[np.arange(B)[:, None], src] + rng.normal(0, 0.005, (B, nd, 3))).reshape(-1, 3)
+    data_part = model_part[src].reshape(-1)
+    dptr = np.arange(B + 1, dtype=np.int64) * nd
+    kw = dict(beta_pose=0.05, beta_shape=0.1)
+    got = api.avatar_optimize(gm, x["w"], x["p"], x["q"], dptr, data, data_part, model_part, gmm=gg, icp_iters=3, max_iters_per_icp=12, **kw)
+    # the same chain on the CPU
+    w, p, q = x["w"].copy(), x["p"].copy(), x["q"].copy()
+    for it in range(3):
+        cloud, _, _ = om.forward(w, p, synth.quat_to_r(q))
+        vis = orc.icp_visible(cloud, rm["f"])
+        nn = orc.icp_nearest(cloud, model_part, vis, dptr, data, data_part, nthreads=3)
+        h = got["history"][it]
+        assert np.array_equal(nn, h["nn"]), f"ICP iteration {it}: correspondences differ"
+        keep = nn >= 0                                                    # unmatched data points add no residual block
+        local = (np.arange(B * nd) - np.repeat(dptr[:-1], nd)).astype(np.int32)
+        cptr = np.concatenate([[0], np.cumsum([int(keep[dptr[i]:dptr[i + 1]].sum()) for i in range(B)])]).astype(np.int64)
+        ref = om.icp_minimize(og, kw["beta_pose"], kw["beta_shape"], w, p, q, cptr, nn[keep], local[keep], dptr, data, max_iterations=12, nthreads=3)
+        assert np.array_equal(ref["iterations"], h["iterations"]) and np.array_equal(ref["evaluations"], h["evaluations"])
+        assert np.max(np.abs(ref["final_cost"] - h["final_cost"]) / ref["final_cost"]) < 1e-8
+        w, p, q = ref["w"], ref["p"], ref["q"]
+    assert np.max(np.abs(got["w"] - w)) < 1e-6 and np.max(np.abs(got["p"] - p)) < 1e-6 and np.max(np.abs(got["q"] - q)) < 1e-6
+    assert np.all(got["history"][-1]["final_cost"] < got["history"][0]["initial_cost"])
