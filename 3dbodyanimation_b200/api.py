@@ -90,7 +90,7 @@ class AvatarModel:
 
     def __del__(self):
         h = getattr(self, "h", None)
-        if h is not None and h.value:
+        if h is not None and h.value and lib is not None:      # (lib is None while the interpreter shuts down)
             lib().b3d_model_destroy(h)
             self.h = None
 
@@ -459,7 +459,7 @@ class IcpProblem:
 
     def __del__(self):
         h = getattr(self, "h", None)
-        if h is not None and h.value:
+        if h is not None and h.value and lib is not None:
             lib().b3d_icp_destroy(h)
             self.h = None
 

@@ -1,0 +1,670 @@
+// Entry (2), multi-frame, LONG chains (stage 1 of 3dba_multi: one OptimizeMultiFrame over all anchors, src/main_multi_frame.cpp:109-134,
+// include/MultiFrameBA.h:33-177): the same Levenberg-Marquardt loop as fit_window_kernel, run by a GRID of CTAs (one per SM,
+// cooperative launch) instead of one cluster, so that a chain of thousands of frames is not a serial sweep on two SMs.
+//
+//   * evaluation (residuals, Jacobians, per-frame normal equations): frames dealt to the CTAs in contiguous chunks (win_evaluate);
+//   * the damped normal equations  [T C^T; C Hw] [y; y_w] = [gs; gs_w]  (T block tridiagonal, 76 x 76 blocks; C the 10-wide arrow):
+//     BLOCK CYCLIC REDUCTION over the frames with 11 right-hand sides [gs | C^T].  Level l (stride s = 2^l) eliminates the frames
+//     f = s (2 k + 1) all at once — phase 1, one CTA per eliminated frame: L = chol(A_f), U_a = L^-1 E_fa, U_c = L^-1 E_fc,
+//     v = L^-1 R_f, new coupling E_ac = -U_a^T U_c; phase 2, one CTA per surviving frame: A_a -= U^T U, R_a -= U^T v for its one or
+//     two eliminated neighbours (each block has ONE writer per phase: deterministic, no atomics) — then the stride doubles; log2 F
+//     levels, back substitution in reverse.  The shape block closes the system: S_w = Hw - sum_f C_f X_f, y = X_0 - X_w y_w.
+//     About 7x the flops of the sequential sweep per frame, but F / 2 of them run side by side.
+//   * every CTA runs the scalar LM logic redundantly on the same reduced sums (sums over CTAs are taken in CTA order by every CTA:
+//     identical decisions, no broadcast); grid barriers separate the phases.
+// The LM loop itself (tolerances, radius updates, records) is fit_window_kernel's, statement for statement.
+#pragma once
+
+namespace b3d {
+
+constexpr int CLD = NB + 2;          // 78: leading dimension of the shared-memory blocks (rows 16 B aligned for double2 loads)
+constexpr int NRHS = NS + 1;         // right-hand sides carried through the reduction: gs and the 10 arrow columns
+constexpr int RLD = CH_RLD;          // 12 (lm_device.cuh sizes the workspace with it)
+static_assert(RLD == NRHS + 1, "right-hand side blocks are 76 x 12");
+// CH_PART doubles of private exchange area per CTA (layout of WinWs::xc: cost / Hw / gw shares), CH_RED reduction slots per CTA,
+// CH_MIN_FRAMES: lm_device.cuh
+
+struct ChainBlocks {
+    double A[NB][CLD], E1[NB][CLD], E2[NB][CLD];
+    double R[NB][RLD], X1[NB][RLD], X2[NB][RLD];
+    double invd[NB];
+    double Sw[NS * NS], zw[NS], yw[NS];
+    double red[40];
+    double bc[4];                    // broadcast slots
+    int flag;
+};
+struct ChainSmem {
+    union { WinSmem w; ChainBlocks b; } u;
+};
+
+struct ChainWs {
+    double *Aw, *EL, *ER;            // F x 76 x 76: working diagonal blocks (-> L), couplings to the left / right active neighbour (-> U)
+    double *Rr, *Xs;                 // F x 76 x 12: right-hand sides (-> v), solutions
+    double *part;                    // G x CH_PART
+    double *red;                     // G x CH_RED
+    unsigned* bar;                   // [0] arrivals, [1] generation, [2] failure flag of the current solve
+};
+
+// all CTAs of the (cooperative) grid: global writes before, reads after
+__device__ __forceinline__ void grid_sync(unsigned* bar, unsigned nblocks) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        volatile unsigned* vgen = bar + 1;
+        const unsigned gen = *vgen;
+        __threadfence();
+        if (atomicAdd(bar, 1u) == nblocks - 1) {
+            atomicExch(bar, 0u);
+            __threadfence();
+            atomicAdd(bar + 1, 1u);
+        } else {
+            while (*vgen == gen) __nanosleep(32);
+        }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+// ---- dense 76 x 76 helpers on shared-memory blocks (T threads) ----
+template <int T>
+__device__ void blk_load(double (*dst)[CLD], const double* __restrict__ src) {     // row-major 76 x 76 from global
+    for (int idx = threadIdx.x; idx < NB * NB; idx += T) dst[idx / NB][idx % NB] = src[idx];
+}
+template <int T>
+__device__ void blk_store(double* __restrict__ dst, const double (*src)[CLD]) {
+    for (int idx = threadIdx.x; idx < NB * NB; idx += T) dst[idx] = src[idx / NB][idx % NB];
+}
+template <int T>
+__device__ void rhs_load(double (*dst)[RLD], const double* __restrict__ src) {     // 76 x 12 (12th column unused)
+    for (int idx = threadIdx.x; idx < NB * RLD; idx += T) dst[idx / RLD][idx % RLD] = src[idx];
+}
+template <int T>
+__device__ void rhs_store(double* __restrict__ dst, const double (*src)[RLD]) {
+    for (int idx = threadIdx.x; idx < NB * RLD; idx += T) dst[idx] = src[idx / RLD][idx % RLD];
+}
+
+// in-place lower Cholesky of A (lower triangle read), 1 / L_jj -> invd.  Returns false on a non-positive pivot (uniform).
+template <int T>
+__device__ bool blk_chol(double (*A)[CLD], double* invd) {
+    const int tid = threadIdx.x;
+    for (int j = 0; j < NB; ++j) {
+        const double d = A[j][j];
+        if (!(d > 0.0)) return false;                    // every thread reads the same value
+        const double inv = 1.0 / sqrt(d);
+        __syncthreads();                                  // all reads of the pivot are done
+        for (int i = j + tid; i < NB; i += T) {
+            if (i == j) { A[j][j] = d * inv; invd[j] = inv; }
+            else A[i][j] *= inv;
+        }
+        __syncthreads();
+        const int m = NB - 1 - j;
+        for (int idx = tid; idx < m * m; idx += T) {
+            const int i = j + 1 + idx / m, k = j + 1 + idx % m;
+            if (k <= i) A[i][k] -= A[i][j] * A[k][j];
+        }
+        __syncthreads();
+    }
+    return true;
+}
+
+// B <- L^-1 B, one thread per column, columns [0, ncols) of a block with leading dimension LD
+template <int LD>
+__device__ void blk_trsm_col(const double (*L)[CLD], const double* invd, double (*B)[LD], int col) {
+    for (int i = 0; i < NB; ++i) {
+        double s0 = B[i][col], s1 = 0.0, s2 = 0.0, s3 = 0.0;
+        int k = 0;
+        for (; k + 3 < i; k += 4) {
+            s0 -= L[i][k] * B[k][col];
+            s1 -= L[i][k + 1] * B[k + 1][col];
+            s2 -= L[i][k + 2] * B[k + 2][col];
+            s3 -= L[i][k + 3] * B[k + 3][col];
+        }
+        for (; k < i; ++k) s0 -= L[i][k] * B[k][col];
+        B[i][col] = ((s0 + s1) + (s2 + s3)) * invd[i];
+    }
+}
+// B <- L^-T B (back substitution), one thread per column
+template <int LD>
+__device__ void blk_trsm_t_col(const double (*L)[CLD], const double* invd, double (*B)[LD], int col) {
+    for (int i = NB - 1; i >= 0; --i) {
+        double s0 = B[i][col], s1 = 0.0;
+        int k = i + 1;
+        for (; k + 1 < NB; k += 2) {
+            s0 -= L[k][i] * B[k][col];
+            s1 -= L[k + 1][i] * B[k + 1][col];
+        }
+        for (; k < NB; ++k) s0 -= L[k][i] * B[k][col];
+        B[i][col] = (s0 + s1) * invd[i];
+    }
+}
+
+// 4 x 4 register tile (ti, tj) of X^T Y for 76 x 76 blocks: acc[a][b] = sum_k X[k][4 ti + a] * Y[k][4 tj + b]
+__device__ __forceinline__ void blk_tile_xty(const double (*X)[CLD], const double (*Y)[CLD], int ti, int tj, double (&acc)[4][4]) {
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+#pragma unroll 4
+    for (int k = 0; k < NB; ++k) {
+        const double2 x01 = *reinterpret_cast<const double2*>(&X[k][4 * ti]), x23 = *reinterpret_cast<const double2*>(&X[k][4 * ti + 2]);
+        const double2 y01 = *reinterpret_cast<const double2*>(&Y[k][4 * tj]), y23 = *reinterpret_cast<const double2*>(&Y[k][4 * tj + 2]);
+        const double xv[4] = {x01.x, x01.y, x23.x, x23.y}, yv[4] = {y01.x, y01.y, y23.x, y23.y};
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) acc[a][b] = fma(xv[a], yv[b], acc[a][b]);
+    }
+}
+
+// ---- the damped linear solve by block cyclic reduction: y (W.y) <- solution of (H_s + D^2 / radius) y = gs.  All CTAs. ----
+template <int T>
+__device__ bool chain_solve(const FitConst* __restrict__ C, int F, double radius, WinWs& W, ChainWs& CW, ChainBlocks& B, int cta, int G) {
+    const int tid = threadIdx.x;
+    const double lam2 = C->lambda_temp * C->lambda_temp;
+    const bool temporal = C->lambda_temp > 0.0 && F > 1;
+    const size_t BB = (size_t)NB * NB, RR = (size_t)NB * RLD;
+    if (cta == 0 && tid == 0) CW.bar[2] = 0u;
+    // (0) working copies: A_f = Hd_f + D^2 / radius, couplings to the neighbours (diagonal matrices at level 0), R_f = [gs_f | Ha_f^T]
+    for (int f = cta; f < F; f += G) {
+        const double* Hd = W.Hd + (size_t)f * BB;
+        double* Aw = CW.Aw + (size_t)f * BB;
+        for (int idx = tid; idx < NB * NB; idx += T) {
+            const int i = idx / NB, j = idx % NB;
+            double v = Hd[idx];
+            if (i == j) { const double l = sqrt(W.diag[(size_t)f * NB + i] / radius); v += l * l; }
+            Aw[idx] = v;
+        }
+        double* EL = CW.EL + (size_t)f * BB;
+        double* ER = CW.ER + (size_t)f * BB;
+        for (int idx = tid; idx < NB * NB; idx += T) {
+            const int i = idx / NB, j = idx % NB;
+            double el = 0.0, er = 0.0;
+            if (temporal && i == j && i >= 1) {
+                if (f > 0) el = -lam2 * W.scale[(size_t)f * NB + i] * W.scale[(size_t)(f - 1) * NB + i];
+                if (f < F - 1) er = -lam2 * W.scale[(size_t)f * NB + i] * W.scale[(size_t)(f + 1) * NB + i];
+            }
+            EL[idx] = el; ER[idx] = er;
+        }
+        const double* Ha = W.Ha + (size_t)f * NS * NB;
+        double* Rr = CW.Rr + (size_t)f * RR;
+        for (int idx = tid; idx < NB * RLD; idx += T) {
+            const int i = idx / RLD, c = idx % RLD;
+            Rr[idx] = c == 0 ? W.gs[(size_t)f * NB + i] : (c <= NS ? Ha[(c - 1) * NB + i] : 0.0);
+        }
+    }
+    grid_sync(CW.bar, G);
+    // (1) forward reduction
+    int nlev = 0;
+    for (int s = 1; s < F; s <<= 1, ++nlev) {
+        // phase 1: eliminate f = s (2 t + 1)
+        const int nodd = (F - s + 2 * s - 1) / (2 * s);
+        for (int t = cta; t < nodd; t += G) {
+            const int f = s * (2 * t + 1), a = f - s, c = f + s;
+            const bool has_c = c < F;
+            __syncthreads();
+            blk_load<T>(B.A, CW.Aw + (size_t)f * BB);
+            blk_load<T>(B.E1, CW.EL + (size_t)f * BB);
+            if (has_c) blk_load<T>(B.E2, CW.ER + (size_t)f * BB);
+            rhs_load<T>(B.R, CW.Rr + (size_t)f * RR);
+            __syncthreads();
+            const bool ok = blk_chol<T>(B.A, B.invd);
+            if (!ok) { if (tid == 0) atomicExch(&CW.bar[2], 1u); continue; }     // uniform; the solve is void, the barriers go on
+            __syncthreads();
+            // U_a = L^-1 E_fa, U_c = L^-1 E_fc, v = L^-1 R: one thread per column
+            if (tid < NB) blk_trsm_col<CLD>(B.A, B.invd, B.E1, tid);
+            else if (tid >= 96 && tid < 96 + NB) { if (has_c) blk_trsm_col<CLD>(B.A, B.invd, B.E2, tid - 96); }
+            else if (tid >= 192 && tid < 192 + NRHS) blk_trsm_col<RLD>(B.A, B.invd, B.R, tid - 192);
+            __syncthreads();
+            blk_store<T>(CW.Aw + (size_t)f * BB, B.A);
+            for (int i = tid; i < NB; i += T) W.invd[(size_t)f * NB + i] = B.invd[i];
+            blk_store<T>(CW.EL + (size_t)f * BB, B.E1);
+            if (has_c) blk_store<T>(CW.ER + (size_t)f * BB, B.E2);
+            rhs_store<T>(CW.Rr + (size_t)f * RR, B.R);
+            if (has_c && tid < 361) {     // new coupling of the survivors: E_ac = -U_a^T U_c (block (a, c)) and its transpose (block (c, a))
+                const int ti = tid / 19, tj = tid % 19;
+                double acc[4][4];
+                blk_tile_xty(B.E1, B.E2, ti, tj, acc);
+                double* Eac = CW.ER + (size_t)a * BB;
+                double* Eca = CW.EL + (size_t)c * BB;
+#pragma unroll
+                for (int x = 0; x < 4; ++x)
+#pragma unroll
+                    for (int y = 0; y < 4; ++y) {
+                        const int i = 4 * ti + x, j = 4 * tj + y;
+                        Eac[i * NB + j] = -acc[x][y];
+                        Eca[j * NB + i] = -acc[x][y];
+                    }
+            }
+        }
+        grid_sync(CW.bar, G);
+        // phase 2: the survivors a = 2 s t take the Schur updates of their eliminated neighbours
+        const int nev = (F + 2 * s - 1) / (2 * s);
+        for (int t = cta; t < nev; t += G) {
+            const int a = 2 * s * t, fl = a - s, fr = a + s;
+            double upd[4][4];
+            const int ti = tid / 19, tj = tid % 19;
+#pragma unroll
+            for (int x = 0; x < 4; ++x)
+#pragma unroll
+                for (int y = 0; y < 4; ++y) upd[x][y] = 0.0;
+            double rupd[2] = {0.0, 0.0};     // this thread's entries of R_a: idx = tid and tid + T (76 x 11 = 836 <= 2 T)
+            for (int side = 0; side < 2; ++side) {
+                const int fo = side == 0 ? fl : fr;
+                if (fo < 0 || fo >= F) continue;       // uniform
+                __syncthreads();
+                // U of the eliminated neighbour towards a: its right coupling if it sits on the left of a, else its left coupling
+                blk_load<T>(B.E1, (side == 0 ? CW.ER : CW.EL) + (size_t)fo * BB);
+                rhs_load<T>(B.R, CW.Rr + (size_t)fo * RR);
+                __syncthreads();
+                if (tid < 361) {
+                    double acc[4][4];
+                    blk_tile_xty(B.E1, B.E1, ti, tj, acc);
+#pragma unroll
+                    for (int x = 0; x < 4; ++x)
+#pragma unroll
+                        for (int y = 0; y < 4; ++y) upd[x][y] += acc[x][y];
+                }
+                for (int q = 0; q < 2; ++q) {
+                    const int idx = tid + q * T;
+                    if (idx < NB * NRHS) {
+                        const int i = idx / NRHS, c = idx % NRHS;
+                        double sacc = 0.0;
+                        for (int k = 0; k < NB; ++k) sacc += B.E1[k][i] * B.R[k][c];
+                        rupd[q] += sacc;
+                    }
+                }
+            }
+            double* Aw = CW.Aw + (size_t)a * BB;
+            if (tid < 361) {
+#pragma unroll
+                for (int x = 0; x < 4; ++x)
+#pragma unroll
+                    for (int y = 0; y < 4; ++y) Aw[(4 * ti + x) * NB + 4 * tj + y] -= upd[x][y];
+            }
+            double* Rr = CW.Rr + (size_t)a * RR;
+            for (int q = 0; q < 2; ++q) {
+                const int idx = tid + q * T;
+                if (idx < NB * NRHS) Rr[(idx / NRHS) * RLD + idx % NRHS] -= rupd[q];
+            }
+        }
+        grid_sync(CW.bar, G);
+    }
+    // (2) root: frame 0
+    if (cta == 0) {
+        __syncthreads();
+        blk_load<T>(B.A, CW.Aw);
+        rhs_load<T>(B.R, CW.Rr);
+        __syncthreads();
+        const bool ok = blk_chol<T>(B.A, B.invd);
+        if (!ok) { if (tid == 0) atomicExch(&CW.bar[2], 1u); }
+        else {
+            __syncthreads();
+            if (tid < NRHS) { blk_trsm_col<RLD>(B.A, B.invd, B.R, tid); blk_trsm_t_col<RLD>(B.A, B.invd, B.R, tid); }
+            __syncthreads();
+            rhs_store<T>(CW.Xs, B.R);
+        }
+    }
+    grid_sync(CW.bar, G);
+    // (3) back substitution, levels in reverse: X_f = L_f^-T (v_f - U_a X_a - U_c X_c)
+    for (int lev = nlev - 1; lev >= 0; --lev) {
+        const int s = 1 << lev;
+        const int nodd = (F - s + 2 * s - 1) / (2 * s);
+        for (int t = cta; t < nodd; t += G) {
+            const int f = s * (2 * t + 1), a = f - s, c = f + s;
+            const bool has_c = c < F;
+            __syncthreads();
+            blk_load<T>(B.A, CW.Aw + (size_t)f * BB);
+            blk_load<T>(B.E1, CW.EL + (size_t)f * BB);
+            if (has_c) blk_load<T>(B.E2, CW.ER + (size_t)f * BB);
+            rhs_load<T>(B.R, CW.Rr + (size_t)f * RR);
+            rhs_load<T>(B.X1, CW.Xs + (size_t)a * RR);
+            if (has_c) rhs_load<T>(B.X2, CW.Xs + (size_t)c * RR);
+            for (int i = tid; i < NB; i += T) B.invd[i] = W.invd[(size_t)f * NB + i];
+            __syncthreads();
+            double r[2] = {0.0, 0.0};
+            for (int q = 0; q < 2; ++q) {
+                const int idx = tid + q * T;
+                if (idx < NB * NRHS) {
+                    const int i = idx / NRHS, col = idx % NRHS;
+                    double sacc = B.R[i][col];
+                    for (int k = 0; k < NB; ++k) sacc -= B.E1[i][k] * B.X1[k][col];
+                    if (has_c)
+                        for (int k = 0; k < NB; ++k) sacc -= B.E2[i][k] * B.X2[k][col];
+                    r[q] = sacc;
+                }
+            }
+            __syncthreads();
+            for (int q = 0; q < 2; ++q) {
+                const int idx = tid + q * T;
+                if (idx < NB * NRHS) B.R[idx / NRHS][idx % NRHS] = r[q];
+            }
+            __syncthreads();
+            if (tid < NRHS) blk_trsm_t_col<RLD>(B.A, B.invd, B.R, tid);
+            __syncthreads();
+            rhs_store<T>(CW.Xs + (size_t)f * RR, B.R);
+        }
+        grid_sync(CW.bar, G);
+    }
+    // (4) the shape block: S_w = Hw + D_w^2 / radius - sum_f Ha_f X_f[:, 1:], z_w = gs_w - sum_f Ha_f X_f[:, 0]; partial sums per CTA
+    {
+        const int chunk = (F + G - 1) / G, fa = min(F, cta * chunk), fb = min(F, fa + chunk);
+        double accw = 0.0;                       // thread (s, c): s < 10 rows of Ha, c < 11 columns of X
+        const int sr = tid / NRHS, sc = tid % NRHS;
+        if (tid < NS * NRHS)
+            for (int f = fa; f < fb; ++f) {
+                const double* Ha = W.Ha + (size_t)f * NS * NB + (size_t)sr * NB;
+                const double* X = CW.Xs + (size_t)f * RR + sc;
+                double sacc = 0.0;
+                for (int k = 0; k < NB; ++k) sacc += Ha[k] * X[(size_t)k * RLD];
+                accw += sacc;
+            }
+        if (tid < NS * NRHS) CW.part[(size_t)cta * CH_PART + 256 + tid] = accw;
+    }
+    grid_sync(CW.bar, G);
+    const bool failed = *(volatile unsigned*)&CW.bar[2] != 0u;
+    const size_t nw0 = (size_t)F * NB;
+    if (tid < NS * NRHS) {
+        double tot = 0.0;
+        for (int g = 0; g < G; ++g) tot += CW.part[(size_t)g * CH_PART + 256 + tid];
+        const int sr = tid / NRHS, sc = tid % NRHS;
+        if (sc == 0) B.zw[sr] = W.gs[nw0 + sr] - tot;
+        else {
+            double v = W.Hw[sr * NS + (sc - 1)] - tot;
+            if (sr == sc - 1) { const double l = sqrt(W.diag[nw0 + sr] / radius); v += l * l; }
+            B.Sw[sr * NS + (sc - 1)] = v;
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {     // 10 x 10 Cholesky by one thread, every CTA alike (win_arrow)
+        int good = failed ? 0 : 1;
+        for (int j = 0; j < NS && good; ++j) {
+            double d = B.Sw[j * NS + j];
+            for (int k = 0; k < j; ++k) d -= B.Sw[j * NS + k] * B.Sw[j * NS + k];
+            if (!(d > 0.0)) { good = 0; break; }
+            d = sqrt(d);
+            B.Sw[j * NS + j] = d;
+            for (int i = j + 1; i < NS; ++i) {
+                double sacc = B.Sw[i * NS + j];
+                for (int k = 0; k < j; ++k) sacc -= B.Sw[i * NS + k] * B.Sw[j * NS + k];
+                B.Sw[i * NS + j] = sacc / d;
+            }
+        }
+        if (good) {
+            for (int i = 0; i < NS; ++i) { double sacc = B.zw[i]; for (int k = 0; k < i; ++k) sacc -= B.Sw[i * NS + k] * B.zw[k]; B.zw[i] = sacc / B.Sw[i * NS + i]; }
+            for (int i = NS - 1; i >= 0; --i) { double sacc = B.zw[i]; for (int k = i + 1; k < NS; ++k) sacc -= B.Sw[k * NS + i] * B.yw[k]; B.yw[i] = sacc / B.Sw[i * NS + i]; }
+        }
+        B.flag = good;
+    }
+    __syncthreads();
+    const bool ok = B.flag != 0;
+    if (ok) {
+        const int chunk = (F + G - 1) / G, fa = min(F, cta * chunk), fb = min(F, fa + chunk);
+        for (int idx = fa * NB + tid; idx < fb * NB; idx += T) {
+            const int f = idx / NB, i = idx % NB;
+            const double* X = CW.Xs + (size_t)f * RR + (size_t)i * RLD;
+            double v = X[0];
+            for (int sidx = 0; sidx < NS; ++sidx) v -= X[1 + sidx] * B.yw[sidx];
+            W.y[idx] = v;
+        }
+        if (cta == 0 && tid < NS) W.y[nw0 + tid] = B.yw[tid];
+    }
+    grid_sync(CW.bar, G);
+    return ok;
+}
+
+// ---- the LM loop of one long chain on a cooperative grid of G CTAs ----
+template <int T>
+__global__ void __launch_bounds__(T, 1) fit_chain_kernel(const FitConst* __restrict__ C, WinProblem pr, int pb, const b3d_kp* __restrict__ kps_all,
+                                                         const int32_t* __restrict__ nkp_all, const double* __restrict__ R0_all,
+                                                         double* __restrict__ poses, double* __restrict__ Wshape, uint8_t* __restrict__ usable,
+                                                         b3d_iter_record* __restrict__ trace, int trace_stride, int32_t* __restrict__ niters,
+                                                         int32_t* __restrict__ term, double* __restrict__ workspace) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    ChainSmem& S = *reinterpret_cast<ChainSmem*>(smem_raw);
+    const int tid = threadIdx.x, cta = blockIdx.x, G = gridDim.x;
+    const int F = pr.count, n = F * NB + NS;
+    const b3d_kp* kps = kps_all + (size_t)pr.first * MAXKP;
+    const int32_t* nkp = nkp_all + pr.first;
+    const double* R0 = R0_all + (size_t)pr.first * 9;
+    double* xin = poses + (size_t)pr.first * NB;
+    double* win = Wshape + (size_t)pr.first * NS;
+    b3d_iter_record* tr = trace ? trace + (size_t)pb * trace_stride : nullptr;
+    WinWs W;
+    W.carve(workspace + pr.ws_offset, F);
+    ChainWs CW;
+    {
+        double* p = W.xc + WIN_XC_DOUBLES;
+        CW.Aw = W.Ld; CW.EL = W.Lo;
+        CW.ER = p; p += (size_t)F * NB * NB;
+        CW.Rr = p; p += (size_t)F * NB * RLD;
+        CW.Xs = p; p += (size_t)F * NB * RLD;
+        CW.part = p; p += (size_t)G * CH_PART;
+        CW.red = p; p += (size_t)G * CH_RED;
+        CW.bar = reinterpret_cast<unsigned*>(p);
+    }
+    WinWs Wl = W;                               // evaluation shares go to this CTA's private exchange area
+    Wl.xc = CW.part + (size_t)cta * CH_PART;
+    const int erank = cta == 0 ? 0 : 1;         // slot inside it; rank 0 carries the shape prior
+    const double lam2 = C->lambda_temp * C->lambda_temp;
+    const bool temporal = C->lambda_temp > 0.0 && F > 1;
+    const int chunk = (F + G - 1) / G, fa = min(F, cta * chunk), fb = min(F, fa + chunk);   // this CTA's frames
+    const size_t nw0 = (size_t)F * NB;
+    if (tid < 16) win_phase_acc()[tid] = 0;
+    __syncthreads();
+
+    // sums / maxima over the grid: per-CTA values in CW.red (slot), summed in CTA order by every CTA
+    auto grid_sum = [&](double v, int slot) -> double {
+        const double b = block_sum<T>(v, S.u.b.red);
+        if (tid == 0) CW.red[(size_t)cta * CH_RED + slot] = b;
+        grid_sync(CW.bar, G);
+        double tot = 0.0;
+        for (int g = 0; g < G; ++g) tot += *(volatile double*)&CW.red[(size_t)g * CH_RED + slot];
+        return tot;
+    };
+    auto grid_max = [&](double v, int slot) -> double {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_down_sync(0xffffffffu, v, o));
+        __syncthreads();
+        if ((tid & 31) == 0) S.u.b.red[tid >> 5] = v;
+        __syncthreads();
+        double m = 0.0;
+        for (int i = 0; i < T / 32; ++i) m = fmax(m, S.u.b.red[i]);
+        __syncthreads();
+        if (tid == 0) CW.red[(size_t)cta * CH_RED + slot] = m;
+        grid_sync(CW.bar, G);
+        double tot = 0.0;
+        for (int g = 0; g < G; ++g) tot = fmax(tot, *(volatile double*)&CW.red[(size_t)g * CH_RED + slot]);
+        return tot;
+    };
+    // evaluation of the CTA's frames; the cost is summed over the grid.  With the Jacobian: CTA 0 then adds the shape-block shares
+    auto evaluate_all = [&](const double* xvec, bool jac, bool scaled) -> double {
+        const double part = jac ? win_evaluate<T, true>(C, F, xvec, kps, nkp, R0, Wl, S.u.w, fa, fb, erank, scaled)
+                                : win_evaluate<T, false>(C, F, xvec, kps, nkp, R0, Wl, S.u.w, fa, fb, erank, false);
+        __syncthreads();
+        const double total = grid_sum(tid == 0 ? part : 0.0, jac ? 0 : 1);      // (the barrier inside also publishes the shares)
+        if (jac && cta == 0) {
+            const double bs2 = C->beta_shape * C->beta_shape;
+            const bool shape_prior = C->beta_shape > 0.0;
+            for (int idx = tid; idx < NS * NS; idx += T) {
+                double a = 0.0;
+                for (int g = 0; g < G; ++g) a += CW.part[(size_t)g * CH_PART + XC_HW + (g == 0 ? 0 : NS * NS) + idx];
+                W.Hw[idx] = a + ((shape_prior && idx / NS == idx % NS) ? bs2 : 0.0);
+            }
+            if (tid < NS) {
+                double a = 0.0;
+                for (int g = 0; g < G; ++g) a += CW.part[(size_t)g * CH_PART + XC_GW + (g == 0 ? 0 : NS) + tid];
+                W.g[nw0 + tid] = a + (shape_prior ? bs2 * xvec[nw0 + tid] : 0.0);
+            }
+        }
+        if (jac) grid_sync(CW.bar, G);
+        return total;
+    };
+
+    for (int k = fa * NB + tid; k < fb * NB; k += T) W.x[k] = xin[k];
+    if (cta == 0 && tid < NS) W.x[nw0 + tid] = win[tid];
+    grid_sync(CW.bar, G);
+
+    double radius = wInitialRadius, decrease_factor = 2.0, x_cost = 0.0, cand_cost = 0.0, mcc = 0.0;
+    bool reuse_diagonal = false, step_successful = true;
+    int num_invalid = 0, iteration = 0, nrec = 0, termination = 0;
+    b3d_iter_record it;
+    it.cost = it.cost_change = it.gradient_max_norm = it.step_norm = it.relative_decrease = it.radius = 0.0;
+    it.flags = 0; it.aux = -1;
+
+    auto eval_grad_jac = [&](bool first) -> bool {
+        x_cost = evaluate_all(W.x, true, !first);
+        if (!isfinite(x_cost)) return false;
+        it.cost = x_cost;
+        if (first) {
+            for (int k = fa * NB + tid; k < fb * NB; k += T) {
+                const double d = W.Hd[(size_t)(k / NB) * NB * NB + (k % NB) * (NB + 1)];
+                W.scale[k] = 1.0 / (1.0 + sqrt(d));
+            }
+            if (cta == 0 && tid < NS) W.scale[nw0 + tid] = 1.0 / (1.0 + sqrt(W.Hw[tid * (NS + 1)]));
+            grid_sync(CW.bar, G);
+            for (size_t idx = (size_t)fa * NB * NB + tid; idx < (size_t)fb * NB * NB; idx += T) {
+                const int f = (int)(idx / (NB * NB)), r = (int)(idx % (NB * NB)) / NB, c = (int)(idx % NB);
+                W.Hd[idx] *= W.scale[(size_t)f * NB + r] * W.scale[(size_t)f * NB + c];
+            }
+            for (size_t idx = (size_t)fa * NS * NB + tid; idx < (size_t)fb * NS * NB; idx += T) {
+                const int f = (int)(idx / (NS * NB)), sidx = (int)(idx % (NS * NB)) / NB, c = (int)(idx % NB);
+                W.Ha[idx] *= W.scale[nw0 + sidx] * W.scale[(size_t)f * NB + c];
+            }
+            for (int k = fa * NB + tid; k < fb * NB; k += T) W.gs[k] = W.g[k] * W.scale[k];
+        }
+        if (cta == 0) {
+            if (tid < NS * NS) W.Hw[tid] *= W.scale[nw0 + tid / NS] * W.scale[nw0 + tid % NS];
+            if (tid < NS) W.gs[nw0 + tid] = W.g[nw0 + tid] * W.scale[nw0 + tid];
+        }
+        double gm = 0.0;
+        for (int k = fa * NB + tid; k < fb * NB; k += T) gm = fmax(gm, fabs(W.g[k]));
+        if (cta == 0 && tid < NS) gm = fmax(gm, fabs(W.g[nw0 + tid]));
+        it.gradient_max_norm = grid_max(gm, 2);     // (its barrier also publishes the scaled shape block)
+        return true;
+    };
+    auto push = [&]() {
+        it.radius = radius;
+        it.aux = -1;
+        if (tr && nrec < trace_stride && tid == 0 && cta == 0) tr[nrec] = it;
+        ++nrec;
+    };
+    auto norm_of = [&](const double* v, int slot) -> double {
+        double a = 0.0;
+        for (int k = fa * NB + tid; k < fb * NB; k += T) a += v[k] * v[k];
+        if (cta == 0 && tid < NS) a += v[nw0 + tid] * v[nw0 + tid];
+        return sqrt(grid_sum(a, slot));
+    };
+
+    double x_norm = norm_of(W.x, 3);
+    if (!eval_grad_jac(true)) {
+        termination = B3D_TERM_EVAL_FAILURE;
+    } else {
+        it.flags = 3;
+        for (;;) {
+            push();
+            if (iteration >= C->max_iters) { termination = B3D_TERM_MAX_ITERS; break; }
+            if (step_successful && it.gradient_max_norm <= wGradientTolerance) { termination = B3D_TERM_GRAD_TOL; break; }
+            if (!(radius > wMinRadius)) { termination = B3D_TERM_MIN_RADIUS; break; }
+            const double prev_gmax = it.gradient_max_norm;
+            it.cost = it.cost_change = it.gradient_max_norm = it.step_norm = it.relative_decrease = 0.0;
+            it.flags = 0;
+            ++iteration;
+            step_successful = false;
+            if (!reuse_diagonal) {
+                for (int k = fa * NB + tid; k < fb * NB; k += T) {
+                    const double d = W.Hd[(size_t)(k / NB) * NB * NB + (k % NB) * (NB + 1)];
+                    W.diag[k] = fmin(fmax(d, wMinDiagonal), wMaxDiagonal);
+                }
+                if (cta == 0 && tid < NS) W.diag[nw0 + tid] = fmin(fmax(W.Hw[tid * (NS + 1)], wMinDiagonal), wMaxDiagonal);
+            }
+            grid_sync(CW.bar, G);
+            reuse_diagonal = true;
+            bool step_valid = false;
+            const bool solved = chain_solve<T>(C, F, radius, W, CW, S.u.b, cta, G);
+            if (solved) {
+                // model_cost_change = y^T gs - y^T H_s y / 2 (step = -y), summed over the CTAs' frames
+                double v = 0.0, fin = 0.0;
+                for (size_t idx = (size_t)fa * NB * NB + tid; idx < (size_t)fb * NB * NB; idx += T) {
+                    const int f = (int)(idx / (NB * NB)), r = (int)(idx % (NB * NB)) / NB, c = (int)(idx % NB);
+                    v -= 0.5 * W.Hd[idx] * W.y[(size_t)f * NB + r] * W.y[(size_t)f * NB + c];
+                }
+                for (size_t idx = (size_t)fa * NS * NB + tid; idx < (size_t)fb * NS * NB; idx += T) {
+                    const int f = (int)(idx / (NS * NB)), sidx = (int)(idx % (NS * NB)) / NB, c = (int)(idx % NB);
+                    v -= W.Ha[idx] * W.y[nw0 + sidx] * W.y[(size_t)f * NB + c];
+                }
+                if (cta == 0 && tid < NS * NS) v -= 0.5 * W.Hw[tid] * W.y[nw0 + tid / NS] * W.y[nw0 + tid % NS];
+                if (temporal) {      // the pair (f, f + 1) belongs to the owner of f
+                    const int p_hi = min(fb, F - 1);
+                    for (int idx = tid; idx < (p_hi - fa) * (NB - 1); idx += T) {
+                        const int f = fa + idx / (NB - 1), k = 1 + idx % (NB - 1);
+                        const size_t a = (size_t)f * NB + k, b = a + NB;
+                        v += lam2 * W.scale[a] * W.scale[b] * W.y[a] * W.y[b];
+                    }
+                }
+                for (int k = fa * NB + tid; k < fb * NB; k += T) { v += W.y[k] * W.gs[k]; fin += isfinite(W.y[k]) ? 0.0 : 1.0; }
+                if (cta == 0 && tid < NS) { v += W.y[nw0 + tid] * W.gs[nw0 + tid]; fin += isfinite(W.y[nw0 + tid]) ? 0.0 : 1.0; }
+                mcc = grid_sum(v, 4);
+                const double bad = grid_sum(fin, 5);
+                step_valid = (bad == 0.0) && (mcc > 0.0);
+            }
+            if (!step_valid) {
+                if (++num_invalid >= wMaxConsecutiveInvalidSteps) { termination = B3D_TERM_INVALID_STEPS; break; }
+                radius = radius / decrease_factor; decrease_factor *= 2.0;
+                it.cost = x_cost; it.gradient_max_norm = prev_gmax;
+                continue;
+            }
+            num_invalid = 0;
+            double sn = 0.0;
+            for (int k = fa * NB + tid; k < fb * NB + (cta == 0 ? 0 : 0); k += T) {
+                const double d = -W.y[k] * W.scale[k];
+                const double c = W.x[k] + d;
+                W.cand[k] = c;
+                const double e = W.x[k] - c;
+                sn += e * e;
+            }
+            if (cta == 0 && tid < NS) {
+                const size_t k = nw0 + tid;
+                const double d = -W.y[k] * W.scale[k];
+                const double c = W.x[k] + d;
+                W.cand[k] = c;
+                const double e = W.x[k] - c;
+                sn += e * e;
+            }
+            it.flags = 1;
+            it.step_norm = sqrt(grid_sum(sn, 6));          // (its barrier publishes the candidate)
+            cand_cost = evaluate_all(W.cand, false, false);
+            if (!isfinite(cand_cost)) cand_cost = DBL_MAX;
+            if (it.step_norm <= wParameterTolerance * (x_norm + wParameterTolerance)) { termination = B3D_TERM_PARAM_TOL; break; }
+            it.cost_change = x_cost - cand_cost;
+            if (fabs(it.cost_change) <= wFunctionTolerance * x_cost) { termination = B3D_TERM_FUNC_TOL; break; }
+            it.relative_decrease = it.cost_change / mcc;
+            if (it.relative_decrease > wMinRelativeDecrease) {
+                for (int k = fa * NB + tid; k < fb * NB; k += T) W.x[k] = W.cand[k];
+                if (cta == 0 && tid < NS) W.x[nw0 + tid] = W.cand[nw0 + tid];
+                x_norm = norm_of(W.x, 7);                   // (its barrier publishes x)
+                if (!eval_grad_jac(false)) { termination = B3D_TERM_EVAL_FAILURE; break; }
+                step_successful = true;
+                it.flags |= 2;
+                const double q = 2.0 * it.relative_decrease - 1.0;
+                radius = radius / fmax(1.0 / 3.0, 1.0 - q * q * q);
+                radius = fmin(wMaxRadius, radius);
+                decrease_factor = 2.0;
+                reuse_diagonal = false;
+            } else {
+                radius = radius / decrease_factor; decrease_factor *= 2.0;
+                it.cost = cand_cost;
+            }
+        }
+    }
+    grid_sync(CW.bar, G);
+    for (int k = fa * NB + tid; k < fb * NB; k += T) xin[k] = W.x[k];
+    if (cta == 0) {
+        if (tid < NS) win[tid] = W.x[nw0 + tid];
+        if (tid == 0) {
+            if (usable) usable[pb] = (termination >= B3D_TERM_PARAM_TOL && termination <= B3D_TERM_MIN_RADIUS) ? 1 : 0;
+            if (niters) niters[pb] = nrec;
+            if (term) term[pb] = termination;
+        }
+    }
+}
+
+}  // namespace b3d

@@ -12,6 +12,9 @@
 // They are factored frame by frame by one augmented Crout elimination per frame: the rows of the next off-diagonal block, the
 // 10 arrow rows and the right-hand side ride along below the 76 x 76 diagonal block, so that L_{f+1,f}, W_f and the forward
 // substitution come out of the same column sweep; the 10 x 10 Schur complement of w closes the system.
+#include <algorithm>
+#include <atomic>
+
 #include "lm_device.cuh"
 
 namespace b3d {
@@ -904,11 +907,46 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T, 1) fit_window_ker
 
 }  // namespace b3d
 
+#include "fit_chain.cuh"
+
 namespace b3d {
 
+static std::atomic<int> g_chain_min_frames{CH_MIN_FRAMES};      // debug hook b3d_debug_chain_min_frames (tests force either kernel)
+
+// one long chain on a cooperative grid: G CTAs, one per SM at most
+static int chain_launch(const FitConst* dfc, const WinProblem& pr, int pb, const b3d_kp* kps, const int32_t* nkp, const double* R0, double* poses,
+                        double* W, uint8_t* usable, b3d_iter_record* trace, int trace_stride, int32_t* niters, int32_t* term, double* ws, cudaStream_t st) {
+    int dev = 0, sms = 0;
+    B3D_CUDA(cudaGetDevice(&dev));
+    B3D_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    B3D_CUDA(cudaFuncSetAttribute(fit_chain_kernel<FW_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(ChainSmem)));
+    int per_sm = 0;
+    B3D_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fit_chain_kernel<FW_THREADS>, FW_THREADS, sizeof(ChainSmem)));
+    if (per_sm < 1) return set_error(B3D_ECUDA, "fit_chain_kernel does not fit on an SM");
+    const int G = std::max(1, std::min(std::min(sms * per_sm, (int)CH_MAX_GRID), (pr.count + 1) / 2));
+    B3D_CUDA(cudaMemsetAsync(ws + pr.ws_offset + chain_bar_offset(pr.count, G), 0, 64, st));
+    WinProblem prv = pr;
+    void* args[] = {(void*)&dfc, (void*)&prv, (void*)&pb, (void*)&kps, (void*)&nkp, (void*)&R0, (void*)&poses, (void*)&W, (void*)&usable,
+                    (void*)&trace, (void*)&trace_stride, (void*)&niters, (void*)&term, (void*)&ws};
+    B3D_CUDA(cudaLaunchCooperativeKernel((const void*)fit_chain_kernel<FW_THREADS>, dim3(G), dim3(FW_THREADS), args, sizeof(ChainSmem), st));
+    B3D_LAUNCH_CHECK();
+    return B3D_OK;
+}
+
 int win_launch(const FitConst* dfc, const WinProblem* dprobs, int nprob, const b3d_kp* kps, const int32_t* nkp, const double* R0, double* poses,
-               double* W, uint8_t* usable, b3d_iter_record* trace, int trace_stride, int32_t* niters, int32_t* term, double* ws, cudaStream_t st) {
+               double* W, uint8_t* usable, b3d_iter_record* trace, int trace_stride, int32_t* niters, int32_t* term, double* ws, cudaStream_t st,
+               const WinProblem* hprobs) {
     if (nprob <= 0) return B3D_OK;
+    if (hprobs) {      // a launch made only of long chains (stage 1): each takes the whole machine, one after the other
+        const int min_f = g_chain_min_frames.load();
+        bool all_long = true;
+        for (int p = 0; p < nprob; ++p) all_long = all_long && hprobs[p].count >= std::max(min_f, (int)CH_MIN_FRAMES);
+        if (all_long) {
+            for (int p = 0; p < nprob; ++p)
+                if (int rc = chain_launch(dfc, hprobs[p], p, kps, nkp, R0, poses, W, usable, trace, trace_stride, niters, term, ws, st)) return rc;
+            return B3D_OK;
+        }
+    }
     B3D_CUDA(cudaFuncSetAttribute(fit_window_kernel<FW_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(WinSmem)));   // per device: every call
     fit_window_kernel<FW_THREADS><<<2 * nprob, FW_THREADS, sizeof(WinSmem), st>>>(dfc, nprob, dprobs, kps, nkp, R0, poses, W, usable, trace, trace_stride,
                                                                              niters, term, ws);
@@ -928,6 +966,9 @@ int b3d_debug_win_timing(int on) {
     cudaMemcpyToSymbol(g_win_phase, z, sizeof(z));
     return cudaMemcpyToSymbol(g_win_phase_on, &on, sizeof(int)) == cudaSuccess ? 0 : 2;
 }
+// chains of at least this many frames take the grid kernel (never below CH_MIN_FRAMES: the workspace is sized by it); a huge value
+// forces the cluster kernel everywhere
+int b3d_debug_chain_min_frames(int frames) { g_chain_min_frames.store(frames); return 0; }
 int b3d_debug_win_read(long long* out16) { return cudaMemcpyFromSymbol(out16, g_win_phase, 16 * sizeof(long long)) == cudaSuccess ? 0 : 2; }
 
 int b3d_fit_windows_dev(const b3d_model* m, const b3d_fit_opts* opts, int32_t nprob, const int32_t* first, const int32_t* count,
@@ -956,7 +997,7 @@ int b3d_fit_windows_dev(const b3d_model* m, const b3d_fit_opts* opts, int32_t np
     B3D_CUDA(cudaMemcpyAsync(dfc, &fc, sizeof(FitConst), cudaMemcpyHostToDevice, st));
     B3D_CUDA(cudaMemcpyAsync(dpr, probs.data(), sizeof(WinProblem) * nprob, cudaMemcpyHostToDevice, st));
     B3D_CUDA(cudaStreamSynchronize(st));      // probs / fc are stack objects: the staged copies must have left them
-    if (int rc = win_launch(dfc, dpr, nprob, kps, nkp, R0, poses, W, usable, trace, trace_stride, niters, term, ws, st)) return rc;
+    if (int rc = win_launch(dfc, dpr, nprob, kps, nkp, R0, poses, W, usable, trace, trace_stride, niters, term, ws, st, probs.data())) return rc;
     B3D_CUDA(cudaFreeAsync(ws, st));
     B3D_CUDA(cudaFreeAsync(dpr, st));
     B3D_CUDA(cudaFreeAsync(dfc, st));

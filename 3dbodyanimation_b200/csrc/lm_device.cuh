@@ -52,13 +52,27 @@ struct WinProblem {
 // exchange area between the two CTAs of a problem's cluster (fit_window.cu), at the end of the per-problem workspace
 constexpr int WIN_XC_DOUBLES = 7424;
 // per-problem global workspace, in doubles
-__host__ __device__ inline size_t win_ws_doubles(int F) {
+// chains from CH_MIN_FRAMES frames on are solved by a cooperative grid (fit_chain.cuh: block cyclic reduction); their workspace also
+// holds the reduction's working blocks and one exchange area per CTA (at most CH_MAX_GRID CTAs)
+constexpr int CH_MIN_FRAMES = 48, CH_MAX_GRID = 160, CH_PART = 512, CH_RED = 16, CH_RLD = NS + 2;
+__host__ __device__ inline size_t win_ws_base_doubles(int F) {
     const size_t n = (size_t)F * NPF + NS;
     return 10 * n + (size_t)F * (3 * NPF * NPF + 2 * NS * NPF) + 2 * NS * NS + (size_t)F * NPF + WIN_XC_DOUBLES;
 }
+__host__ __device__ inline size_t win_ws_doubles(int F) {
+    size_t total = win_ws_base_doubles(F);
+    if (F >= CH_MIN_FRAMES) total += (size_t)F * NPF * NPF + 2 * (size_t)F * NPF * CH_RLD + (size_t)CH_MAX_GRID * (CH_PART + CH_RED) + 64;
+    return total;
+}
+// doubles from the start of a chain problem's workspace to its grid-barrier words, for a grid of G CTAs
+__host__ __device__ inline size_t chain_bar_offset(int F, int G) {
+    return win_ws_base_doubles(F) + (size_t)F * NPF * NPF + 2 * (size_t)F * NPF * CH_RLD + (size_t)G * (CH_PART + CH_RED);
+}
 // enqueue the LM solves of nprob problems (device-resident constants / problem table / workspace); no synchronisation
+// hprobs (optional): the same problem table on the host; with it, launches made only of long chains take the grid kernel
 int win_launch(const FitConst* dfc, const WinProblem* dprobs, int nprob, const b3d_kp* kps, const int32_t* nkp, const double* R0, double* poses,
-               double* W, uint8_t* usable, b3d_iter_record* trace, int trace_stride, int32_t* niters, int32_t* term, double* ws, cudaStream_t st);
+               double* W, uint8_t* usable, b3d_iter_record* trace, int trace_stride, int32_t* niters, int32_t* term, double* ws, cudaStream_t st,
+               const WinProblem* hprobs = nullptr);
 
 // ---------------------------------------------------------------------------------------------------------------
 // rotations

@@ -200,7 +200,7 @@ int b3d_fit_sequences(const b3d_model* m, const b3d_fit_opts* base, const b3d_se
         for (int i = 0; i < TA; ++i) a_nk[i] = nkp[anchor_idx[i]];
         B3D_CUDA(cudaMemcpyAsync(a_nkp, a_nk.data(), 4 * (size_t)TA, cudaMemcpyHostToDevice, st));
         B3D_CUDA(cudaStreamSynchronize(st));
-        if (int rc = win_launch(fc_d, probs_d, nseq, a_kps, a_nkp, a_R0, a_poses, a_W, us_d, nullptr, 0, ni_d, te_d, (double*)d_ws.p, st)) return rc;
+        if (int rc = win_launch(fc_d, probs_d, nseq, a_kps, a_nkp, a_R0, a_poses, a_W, us_d, nullptr, 0, ni_d, te_d, (double*)d_ws.p, st, probs.data())) return rc;   // long anchor chains: grid kernel
         if (int rc = b3d_writeback_dev(TA, a_poses, a_R0, a_r, a_p, st)) return rc;               // into the avatars only
         if (int rc = gather(st, TA, idx_d, a_R0, R0_d, 9, true)) return rc;
         if (int rc = gather(st, TA, idx_d, a_r, r_d, NJ * 9, true)) return rc;

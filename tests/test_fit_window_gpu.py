@@ -205,3 +205,34 @@ def test_sharded_schedule_deviation_from_serial(api, gmodel, synth, model_np, ca
     with capsys.disabled():
         for G, dj, dr, dts, dw in rows:
             print(f"\n[sharded vs serial, {n} frames, G = {G}] max |d jointAA| {dj:.2e}, max |d R0| {dr:.2e}, max |d t/s| {dts:.2e}, max |d w| {dw:.2e}")
+
+
+@pytest.mark.parametrize("F", [48, 97, 260])
+def test_grid_chain_kernel_equals_cluster_kernel(api, synth, F):
+    """Long chains (stage 1 of 3dba_multi: all anchors in one OptimizeMultiFrame) take fit_chain_kernel — the same LM loop on a
+    cooperative grid, normal equations by block cyclic reduction — from 48 frames on.  Against the 2-CTA cluster kernel (sequential
+    two-ended elimination, parity-tested against the oracle above) on the same chain: same iteration count and termination, cost
+    trace to 1e-10 relative, parameters to 1e-7 (measured on B200: 1e-14 and 1e-10; the two factorisations round differently).
+    F = 97 and 260 are not powers of two: levels with a missing right neighbour."""
+    model_np = synth.make_model()
+    gm = api.AvatarModel(model_np)
+    seq = synth.make_sequence(model_np, F * 10, 77)
+    idx = np.arange(0, F * 10, 10)
+    cam = (synth.FX, synth.FY, synth.CX, synth.CY)
+    o = api.fit_opts(cam=cam, mode=1, max_iters=40, beta_pose=20.0, beta_shape=30.0, lambda_temp=3.0)
+    args = (seq["kps"][idx], seq["nkp"][idx], seq["R0"][idx], seq["poses"][idx], seq["W"][0])
+    lib = api.lib()
+    try:
+        lib.b3d_debug_chain_min_frames(10 ** 9)
+        a = api.fit_window(gm, o, *args)
+        lib.b3d_debug_chain_min_frames(0)
+        b = api.fit_window(gm, o, *args)
+    finally:
+        lib.b3d_debug_chain_min_frames(48)
+    assert a["niters"] == b["niters"] and a["term"] == b["term"] and a["usable"] == b["usable"]
+    n = a["niters"]
+    assert n >= 5
+    ca, cb = a["trace"]["cost"][:n], b["trace"]["cost"][:n]
+    assert np.max(np.abs(ca - cb) / ca) < 1e-10
+    assert np.array_equal(a["trace"]["flags"][:n], b["trace"]["flags"][:n])
+    assert np.max(np.abs(a["poses"] - b["poses"])) < 1e-7 and np.max(np.abs(a["w"] - b["w"])) < 1e-9
