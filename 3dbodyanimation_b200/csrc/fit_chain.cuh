@@ -82,58 +82,162 @@ __device__ void rhs_store(double* __restrict__ dst, const double (*src)[RLD]) {
     for (int idx = threadIdx.x; idx < NB * RLD; idx += T) dst[idx] = src[idx / RLD][idx % RLD];
 }
 
-// in-place lower Cholesky of A (lower triangle read), 1 / L_jj -> invd.  Returns false on a non-positive pivot (uniform).
+// In-place lower Cholesky of A (lower triangle read), 1 / L_jj -> invd, blocked over 4-column panels: every thread factors the
+// 4 x 4 diagonal tile redundantly in registers (same shared-memory words for all: broadcast reads, no hand-over barrier), one thread
+// per row solves the panel, one thread per 4 x 4 tile of the trailing lower triangle applies the rank-4 update.  Two barriers per
+// panel.  Returns false on a non-positive pivot (uniform: every thread sees the same tile).
 template <int T>
 __device__ bool blk_chol(double (*A)[CLD], double* invd) {
     const int tid = threadIdx.x;
-    for (int j = 0; j < NB; ++j) {
-        const double d = A[j][j];
-        if (!(d > 0.0)) return false;                    // every thread reads the same value
-        const double inv = 1.0 / sqrt(d);
-        __syncthreads();                                  // all reads of the pivot are done
-        for (int i = j + tid; i < NB; i += T) {
-            if (i == j) { A[j][j] = d * inv; invd[j] = inv; }
-            else A[i][j] *= inv;
+    constexpr int NT4 = NB / 4;                         // 19
+    // this thread's tile of the lower triangle (tid < 190)
+    int ti = 0;
+    while ((ti + 1) * (ti + 2) / 2 <= tid) ++ti;
+    const int tj = tid - ti * (ti + 1) / 2;
+    const bool has_tile = tid < NT4 * (NT4 + 1) / 2;
+    for (int kb = 0; kb < NT4; ++kb) {
+        const int j0 = 4 * kb;
+        double l[4][4], inv[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int c = 0; c <= r; ++c) l[r][c] = A[j0 + r][j0 + c];
+        bool bad = false;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const double piv = l[c][c];
+            bad = bad || !(piv > 0.0);
+            inv[c] = rsqrt(piv);
+            l[c][c] = piv * inv[c];
+#pragma unroll
+            for (int r = c + 1; r < 4; ++r) l[r][c] *= inv[c];
+#pragma unroll
+            for (int c2 = c + 1; c2 < 4; ++c2)
+#pragma unroll
+                for (int r = c2; r < 4; ++r) l[r][c2] -= l[r][c] * l[c2][c];
         }
-        __syncthreads();
-        const int m = NB - 1 - j;
-        for (int idx = tid; idx < m * m; idx += T) {
-            const int i = j + 1 + idx / m, k = j + 1 + idx % m;
-            if (k <= i) A[i][k] -= A[i][j] * A[k][j];
+        if (bad) return false;
+        // panel rows below the diagonal tile: x = a L_kk^-T
+        for (int i = j0 + 4 + tid; i < NB; i += T) {
+            const double x0 = A[i][j0] * inv[0];
+            const double x1 = (A[i][j0 + 1] - x0 * l[1][0]) * inv[1];
+            const double x2 = (A[i][j0 + 2] - x0 * l[2][0] - x1 * l[2][1]) * inv[2];
+            const double x3 = (A[i][j0 + 3] - x0 * l[3][0] - x1 * l[3][1] - x2 * l[3][2]) * inv[3];
+            A[i][j0] = x0; A[i][j0 + 1] = x1; A[i][j0 + 2] = x2; A[i][j0 + 3] = x3;
+        }
+        __syncthreads();                                 // every thread has read the diagonal tile; the panel is complete
+        if (tid == 0) {
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                invd[j0 + r] = inv[r];
+#pragma unroll
+                for (int c = 0; c <= r; ++c) A[j0 + r][j0 + c] = l[r][c];
+            }
+        }
+        if (has_tile && tj > kb) {
+            double pr[4][4], pc[4][4];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) {
+                const double2 r01 = *reinterpret_cast<const double2*>(&A[4 * ti + a][j0]), r23 = *reinterpret_cast<const double2*>(&A[4 * ti + a][j0 + 2]);
+                const double2 c01 = *reinterpret_cast<const double2*>(&A[4 * tj + a][j0]), c23 = *reinterpret_cast<const double2*>(&A[4 * tj + a][j0 + 2]);
+                pr[a][0] = r01.x; pr[a][1] = r01.y; pr[a][2] = r23.x; pr[a][3] = r23.y;
+                pc[a][0] = c01.x; pc[a][1] = c01.y; pc[a][2] = c23.x; pc[a][3] = c23.y;
+            }
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) {
+                    double v = A[4 * ti + a][4 * tj + b];
+#pragma unroll
+                    for (int r = 0; r < 4; ++r) v = fma(-pr[a][r], pc[b][r], v);
+                    A[4 * ti + a][4 * tj + b] = v;
+                }
         }
         __syncthreads();
     }
     return true;
 }
 
-// B <- L^-1 B, one thread per column, columns [0, ncols) of a block with leading dimension LD
-template <int LD>
-__device__ void blk_trsm_col(const double (*L)[CLD], const double* invd, double (*B)[LD], int col) {
-    for (int i = 0; i < NB; ++i) {
-        double s0 = B[i][col], s1 = 0.0, s2 = 0.0, s3 = 0.0;
-        int k = 0;
-        for (; k + 3 < i; k += 4) {
-            s0 -= L[i][k] * B[k][col];
-            s1 -= L[i][k + 1] * B[k + 1][col];
-            s2 -= L[i][k + 2] * B[k + 2][col];
-            s3 -= L[i][k + 3] * B[k + 3][col];
+// [E1 | E2 | R] <- L^-1 [E1 | E2 | R], blocked over 4-row panels of L: a thread per column solves the panel's 4 rows, a thread per
+// 4 x 4 tile below applies the rank-4 update.  ntc tile columns: 19 of E1, then 19 of E2 (if with_e2), then 3 of R.
+struct TileCol { double* base; int ld; };
+__device__ __forceinline__ TileCol blk_tile_col(double (*E1)[CLD], double (*E2)[CLD], double (*R)[RLD], bool with_e2, int tc) {
+    constexpr int NT4 = NB / 4;
+    if (tc < NT4) return {&E1[0][4 * tc], CLD};
+    if (with_e2) { if (tc < 2 * NT4) return {&E2[0][4 * (tc - NT4)], CLD}; return {&R[0][4 * (tc - 2 * NT4)], RLD}; }
+    return {&R[0][4 * (tc - NT4)], RLD};
+}
+template <int T>
+__device__ void blk_trsm(const double (*L)[CLD], const double* invd, double (*E1)[CLD], double (*E2)[CLD], double (*R)[RLD], bool with_e2) {
+    const int tid = threadIdx.x;
+    constexpr int NT4 = NB / 4;
+    const int ntc = (with_e2 ? 2 * NT4 : NT4) + 3;
+    for (int kb = 0; kb < NT4; ++kb) {
+        const int j0 = 4 * kb;
+        // (a) the panel's 4 rows of every column
+        for (int col = tid; col < 4 * ntc; col += T) {
+            const TileCol tcl = blk_tile_col(E1, E2, R, with_e2, col >> 2);
+            double* b = tcl.base + (col & 3);
+            const double x0 = b[(size_t)j0 * tcl.ld] * invd[j0];
+            const double x1 = (b[(size_t)(j0 + 1) * tcl.ld] - L[j0 + 1][j0] * x0) * invd[j0 + 1];
+            const double x2 = (b[(size_t)(j0 + 2) * tcl.ld] - L[j0 + 2][j0] * x0 - L[j0 + 2][j0 + 1] * x1) * invd[j0 + 2];
+            const double x3 = (b[(size_t)(j0 + 3) * tcl.ld] - L[j0 + 3][j0] * x0 - L[j0 + 3][j0 + 1] * x1 - L[j0 + 3][j0 + 2] * x2) * invd[j0 + 3];
+            b[(size_t)j0 * tcl.ld] = x0; b[(size_t)(j0 + 1) * tcl.ld] = x1; b[(size_t)(j0 + 2) * tcl.ld] = x2; b[(size_t)(j0 + 3) * tcl.ld] = x3;
         }
-        for (; k < i; ++k) s0 -= L[i][k] * B[k][col];
-        B[i][col] = ((s0 + s1) + (s2 + s3)) * invd[i];
+        __syncthreads();
+        // (b) rows below: tile (tr, tc) -= L[rows of tr][panel] * B[panel rows][cols of tc]
+        const int nrows = NT4 - 1 - kb;
+        for (int u = tid; u < nrows * ntc; u += T) {
+            const int tr = kb + 1 + u / ntc, tc = u % ntc;
+            const TileCol tcl = blk_tile_col(E1, E2, R, with_e2, tc);
+            double lv[4][4], bv[4][4];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) {
+                const double2 l01 = *reinterpret_cast<const double2*>(&L[4 * tr + a][j0]), l23 = *reinterpret_cast<const double2*>(&L[4 * tr + a][j0 + 2]);
+                lv[a][0] = l01.x; lv[a][1] = l01.y; lv[a][2] = l23.x; lv[a][3] = l23.y;
+                const double2 b01 = *reinterpret_cast<const double2*>(tcl.base + (size_t)(j0 + a) * tcl.ld), b23 = *reinterpret_cast<const double2*>(tcl.base + (size_t)(j0 + a) * tcl.ld + 2);
+                bv[a][0] = b01.x; bv[a][1] = b01.y; bv[a][2] = b23.x; bv[a][3] = b23.y;
+            }
+#pragma unroll
+            for (int a = 0; a < 4; ++a) {
+                double2* row = reinterpret_cast<double2*>(tcl.base + (size_t)(4 * tr + a) * tcl.ld);
+                double2 v01 = row[0], v23 = row[1];
+#pragma unroll
+                for (int r = 0; r < 4; ++r) {
+                    v01.x = fma(-lv[a][r], bv[r][0], v01.x); v01.y = fma(-lv[a][r], bv[r][1], v01.y);
+                    v23.x = fma(-lv[a][r], bv[r][2], v23.x); v23.y = fma(-lv[a][r], bv[r][3], v23.y);
+                }
+                row[0] = v01; row[1] = v23;
+            }
+        }
+        __syncthreads();
     }
 }
-// B <- L^-T B (back substitution), one thread per column
-template <int LD>
-__device__ void blk_trsm_t_col(const double (*L)[CLD], const double* invd, double (*B)[LD], int col) {
-    for (int i = NB - 1; i >= 0; --i) {
-        double s0 = B[i][col], s1 = 0.0;
-        int k = i + 1;
-        for (; k + 1 < NB; k += 2) {
-            s0 -= L[k][i] * B[k][col];
-            s1 -= L[k + 1][i] * B[k + 1][col];
+
+// R <- L^-T R (12 columns), blocked backwards over 4-row panels
+template <int T>
+__device__ void blk_trsm_t(const double (*L)[CLD], const double* invd, double (*R)[RLD]) {
+    const int tid = threadIdx.x;
+    constexpr int NT4 = NB / 4;
+    for (int kb = NT4 - 1; kb >= 0; --kb) {
+        const int j0 = 4 * kb;
+        if (tid < RLD) {
+            const int c = tid;
+            const double x3 = R[j0 + 3][c] * invd[j0 + 3];
+            const double x2 = (R[j0 + 2][c] - L[j0 + 3][j0 + 2] * x3) * invd[j0 + 2];
+            const double x1 = (R[j0 + 1][c] - L[j0 + 3][j0 + 1] * x3 - L[j0 + 2][j0 + 1] * x2) * invd[j0 + 1];
+            const double x0 = (R[j0][c] - L[j0 + 3][j0] * x3 - L[j0 + 2][j0] * x2 - L[j0 + 1][j0] * x1) * invd[j0];
+            R[j0][c] = x0; R[j0 + 1][c] = x1; R[j0 + 2][c] = x2; R[j0 + 3][c] = x3;
         }
-        for (; k < NB; ++k) s0 -= L[k][i] * B[k][col];
-        B[i][col] = (s0 + s1) * invd[i];
+        __syncthreads();
+        for (int idx = tid; idx < j0 * RLD; idx += T) {
+            const int i = idx / RLD, c = idx % RLD;
+            double v = R[i][c];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) v = fma(-L[j0 + r][i], R[j0 + r][c], v);
+            R[i][c] = v;
+        }
+        __syncthreads();
     }
 }
 
@@ -163,6 +267,8 @@ __device__ bool chain_solve(const FitConst* __restrict__ C, int F, double radius
     const bool temporal = C->lambda_temp > 0.0 && F > 1;
     const size_t BB = (size_t)NB * NB, RR = (size_t)NB * RLD;
     if (cta == 0 && tid == 0) CW.bar[2] = 0u;
+    WinTimer ct;          // debug hook b3d_debug_win_timing: cycles of CTA 0 per part of the solve
+    ct.start();
     // (0) working copies: A_f = Hd_f + D^2 / radius, couplings to the neighbours (diagonal matrices at level 0), R_f = [gs_f | Ha_f^T]
     for (int f = cta; f < F; f += G) {
         const double* Hd = W.Hd + (size_t)f * BB;
@@ -192,6 +298,7 @@ __device__ bool chain_solve(const FitConst* __restrict__ C, int F, double radius
         }
     }
     grid_sync(CW.bar, G);
+    ct.mark(0);
     // (1) forward reduction
     int nlev = 0;
     for (int s = 1; s < F; s <<= 1, ++nlev) {
@@ -206,14 +313,14 @@ __device__ bool chain_solve(const FitConst* __restrict__ C, int F, double radius
             if (has_c) blk_load<T>(B.E2, CW.ER + (size_t)f * BB);
             rhs_load<T>(B.R, CW.Rr + (size_t)f * RR);
             __syncthreads();
+            ct.mark(1);
             const bool ok = blk_chol<T>(B.A, B.invd);
             if (!ok) { if (tid == 0) atomicExch(&CW.bar[2], 1u); continue; }     // uniform; the solve is void, the barriers go on
             __syncthreads();
-            // U_a = L^-1 E_fa, U_c = L^-1 E_fc, v = L^-1 R: one thread per column
-            if (tid < NB) blk_trsm_col<CLD>(B.A, B.invd, B.E1, tid);
-            else if (tid >= 96 && tid < 96 + NB) { if (has_c) blk_trsm_col<CLD>(B.A, B.invd, B.E2, tid - 96); }
-            else if (tid >= 192 && tid < 192 + NRHS) blk_trsm_col<RLD>(B.A, B.invd, B.R, tid - 192);
-            __syncthreads();
+            ct.mark(2);
+            // U_a = L^-1 E_fa, U_c = L^-1 E_fc, v = L^-1 R
+            blk_trsm<T>(B.A, B.invd, B.E1, B.E2, B.R, has_c);
+            ct.mark(3);
             blk_store<T>(CW.Aw + (size_t)f * BB, B.A);
             for (int i = tid; i < NB; i += T) W.invd[(size_t)f * NB + i] = B.invd[i];
             blk_store<T>(CW.EL + (size_t)f * BB, B.E1);
@@ -234,14 +341,20 @@ __device__ bool chain_solve(const FitConst* __restrict__ C, int F, double radius
                         Eca[j * NB + i] = -acc[x][y];
                     }
             }
+            ct.mark(9);
         }
+        ct.mark(9);
         grid_sync(CW.bar, G);
+        ct.mark(10);
         // phase 2: the survivors a = 2 s t take the Schur updates of their eliminated neighbours
         const int nev = (F + 2 * s - 1) / (2 * s);
         for (int t = cta; t < nev; t += G) {
             const int a = 2 * s * t, fl = a - s, fr = a + s;
             double upd[4][4];
-            const int ti = tid / 19, tj = tid % 19;
+            int ti = 0;                                  // this thread's tile of the lower triangle (tid < 190): U^T U is symmetric
+            while ((ti + 1) * (ti + 2) / 2 <= tid) ++ti;
+            const int tj = tid - ti * (ti + 1) / 2;
+            const bool has_tile = tid < 190;
 #pragma unroll
             for (int x = 0; x < 4; ++x)
 #pragma unroll
@@ -255,7 +368,7 @@ __device__ bool chain_solve(const FitConst* __restrict__ C, int F, double radius
                 blk_load<T>(B.E1, (side == 0 ? CW.ER : CW.EL) + (size_t)fo * BB);
                 rhs_load<T>(B.R, CW.Rr + (size_t)fo * RR);
                 __syncthreads();
-                if (tid < 361) {
+                if (has_tile) {
                     double acc[4][4];
                     blk_tile_xty(B.E1, B.E1, ti, tj, acc);
 #pragma unroll
@@ -274,11 +387,18 @@ __device__ bool chain_solve(const FitConst* __restrict__ C, int F, double radius
                 }
             }
             double* Aw = CW.Aw + (size_t)a * BB;
-            if (tid < 361) {
+            if (has_tile) {
 #pragma unroll
                 for (int x = 0; x < 4; ++x)
 #pragma unroll
-                    for (int y = 0; y < 4; ++y) Aw[(4 * ti + x) * NB + 4 * tj + y] -= upd[x][y];
+                    for (int y = 0; y < 4; ++y) {
+                        const int i = 4 * ti + x, j = 4 * tj + y;
+                        if (ti != tj || j <= i) {
+                            const double v = Aw[i * NB + j] - upd[x][y];
+                            Aw[i * NB + j] = v;
+                            if (i != j) Aw[j * NB + i] = v;
+                        }
+                    }
             }
             double* Rr = CW.Rr + (size_t)a * RR;
             for (int q = 0; q < 2; ++q) {
@@ -286,7 +406,9 @@ __device__ bool chain_solve(const FitConst* __restrict__ C, int F, double radius
                 if (idx < NB * NRHS) Rr[(idx / NRHS) * RLD + idx % NRHS] -= rupd[q];
             }
         }
+        ct.mark(11);
         grid_sync(CW.bar, G);
+        ct.mark(10);
     }
     // (2) root: frame 0
     if (cta == 0) {
@@ -298,12 +420,13 @@ __device__ bool chain_solve(const FitConst* __restrict__ C, int F, double radius
         if (!ok) { if (tid == 0) atomicExch(&CW.bar[2], 1u); }
         else {
             __syncthreads();
-            if (tid < NRHS) { blk_trsm_col<RLD>(B.A, B.invd, B.R, tid); blk_trsm_t_col<RLD>(B.A, B.invd, B.R, tid); }
-            __syncthreads();
+            blk_trsm<T>(B.A, B.invd, B.E1, B.E2, B.R, false);     // (E1 rides along: its content is not used)
+            blk_trsm_t<T>(B.A, B.invd, B.R);
             rhs_store<T>(CW.Xs, B.R);
         }
     }
     grid_sync(CW.bar, G);
+    ct.mark(12);
     // (3) back substitution, levels in reverse: X_f = L_f^-T (v_f - U_a X_a - U_c X_c)
     for (int lev = nlev - 1; lev >= 0; --lev) {
         const int s = 1 << lev;
@@ -338,11 +461,12 @@ __device__ bool chain_solve(const FitConst* __restrict__ C, int F, double radius
                 if (idx < NB * NRHS) B.R[idx / NRHS][idx % NRHS] = r[q];
             }
             __syncthreads();
-            if (tid < NRHS) blk_trsm_t_col<RLD>(B.A, B.invd, B.R, tid);
-            __syncthreads();
+            blk_trsm_t<T>(B.A, B.invd, B.R);
             rhs_store<T>(CW.Xs + (size_t)f * RR, B.R);
         }
+        ct.mark(13);
         grid_sync(CW.bar, G);
+        ct.mark(10);
     }
     // (4) the shape block: S_w = Hw + D_w^2 / radius - sum_f Ha_f X_f[:, 1:], z_w = gs_w - sum_f Ha_f X_f[:, 0]; partial sums per CTA
     {
@@ -408,6 +532,7 @@ __device__ bool chain_solve(const FitConst* __restrict__ C, int F, double radius
         if (cta == 0 && tid < NS) W.y[nw0 + tid] = B.yw[tid];
     }
     grid_sync(CW.bar, G);
+    ct.mark(14);
     return ok;
 }
 
@@ -554,6 +679,8 @@ __global__ void __launch_bounds__(T, 1) fit_chain_kernel(const FitConst* __restr
         return sqrt(grid_sum(a, slot));
     };
 
+    WinTimer kt;
+    kt.start();
     double x_norm = norm_of(W.x, 3);
     if (!eval_grad_jac(true)) {
         termination = B3D_TERM_EVAL_FAILURE;
@@ -656,6 +783,8 @@ __global__ void __launch_bounds__(T, 1) fit_chain_kernel(const FitConst* __restr
         }
     }
     grid_sync(CW.bar, G);
+    kt.mark(15);
+    if (cta == 0 && tid < 16 && g_win_phase_on) g_win_phase[tid] += win_phase_acc()[tid];
     for (int k = fa * NB + tid; k < fb * NB; k += T) xin[k] = W.x[k];
     if (cta == 0) {
         if (tid < NS) win[tid] = W.x[nw0 + tid];

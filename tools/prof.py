@@ -171,6 +171,36 @@ def winphases(F=20, iters=60):
         print(f"  {names[i]:52s} {out[i]:12d} {100.0 * out[i] / max(tot, 1):6.1f}%")
 
 
+def chainphases(F=200, iters=30):
+    """Per-phase cycles of CTA 0 of fit_chain_kernel (grid kernel for long chains) on a chain of F anchors."""
+    model_np = synth.make_model()
+    gm = api.AvatarModel(model_np)
+    seq = synth.make_sequence_fast(model_np, F * 10, 31)
+    idx = np.arange(0, F * 10, 10)
+    cam = (synth.FX, synth.FY, synth.CX, synth.CY)
+    o = api.fit_opts(cam=cam, max_iters=iters, beta_pose=20.0, beta_shape=30.0, lambda_temp=3.0)
+    args = (seq["kps"][idx], seq["nkp"][idx], seq["R0"][idx], seq["poses"][idx], seq["W"][0])
+    lib.b3d_debug_chain_min_frames(0)
+    api.fit_window(gm, o, *args)
+    lib.b3d_debug_win_timing(1)
+    t0 = time.perf_counter()
+    r = api.fit_window(gm, o, *args)
+    dt = time.perf_counter() - t0
+    out = (C.c_longlong * 16)()
+    lib.b3d_debug_win_read(out)
+    lib.b3d_debug_win_timing(0)
+    names = ["solve: working copies", "solve p1: load blocks", "solve p1: Cholesky", "solve p1: triangular solves", "eval: reproj (cost only)", "eval: frame load",
+             "eval: reproj + Jacobian", "eval: 86 x 86 assembly", "eval: scatter to blocks", "solve p1: stores + new coupling", "solve: grid barrier waits",
+             "solve p2: Schur updates of the survivors", "solve: root", "solve: back substitution", "solve: shape block + y", "kernel total (LM loop)"]
+    tot = max(out[15], 1)
+    print(f"fit_chain F={F}: {r['niters']} records, {dt * 1e3:.2f} ms wall for the call; {tot / max(r['niters'] - 1, 1):.0f} cycles per LM iteration")
+    for i in range(16):
+        print(f"  {names[i]:44s} {out[i]:12d} {100.0 * out[i] / tot:6.1f}%")
+
+
+if __name__ == "__main__" and sys.argv[1] == "chainphases":
+    chainphases(int(sys.argv[2]) if len(sys.argv) > 2 else 200)
+
 if __name__ == "__main__" and sys.argv[1] == "winphases":
     winphases(int(sys.argv[2]) if len(sys.argv) > 2 else 20)
 
