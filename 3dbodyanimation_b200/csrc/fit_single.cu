@@ -41,6 +41,9 @@ constexpr int kMaxConsecutiveInvalidSteps = 5;
 __device__ long long g_phase_cycles[32];
 __device__ long long g_block_cycles[1024];   // total cycles and line-search evaluations per block (debug)
 __device__ int g_block_ls[1024];
+__device__ long long g_block_lscyc[1024];     // cycles inside line-search fall-backs, trial evaluations (debug)
+__device__ int g_block_lstrials[1024];
+__device__ long long g_block_lsparts[1024][4];  // set-up, trial evaluations, polynomial minimisation, final evaluation
 __device__ long long g_block_t0[1024], g_block_t1[1024];   // globaltimer (ns) at the first start and the last end of a frame (debug)
 __device__ __forceinline__ long long global_ns() { long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 __device__ int g_phase_on;
@@ -687,6 +690,8 @@ __device__ void fit_frame(const FitConst* __restrict__ C, int B, const b3d_kp* _
     const long long t_begin = clock64();
     if (tid == 0 && g_phase_on && b < 1024 && !resumed) g_block_t0[b] = global_ns();
     int n_ls_evals = 0, slice_end = P.stop_at;
+    long long ls_cyc = 0, ls_part[4] = {0, 0, 0, 0};
+    int ls_trials = 0;
     double x_norm;
     bool unfinished = false, skip_head = false, started;
     if (resumed) {
@@ -785,6 +790,7 @@ __device__ void fit_frame(const FitConst* __restrict__ C, int B, const b3d_kp* _
                     // rare path: interpolate.  Needs the directional derivative at every trial point: gradient-only evaluations
                     // (MODE 2) that leave the normal equations of x in place.
                     ++n_ls_evals;
+                    const long long ls_t0 = clock64();
                     double dmax = 0.0;
                     for (int k = 0; k < n; ++k) dmax = fmax(dmax, fabs(S.delta[k]));
                     LsSample init{0.0, x_cost, gd, true}, prev{0, 0, 0, false}, cur{1.0, 0, 0, false};
@@ -822,6 +828,7 @@ __device__ void fit_frame(const FitConst* __restrict__ C, int B, const b3d_kp* _
                     const double bp2 = C->beta_pose * C->beta_pose, bs2 = C->beta_shape * C->beta_shape;
                     auto ls_eval = [&](double a, LsSample& s) {
                         s.x = a; s.valid = false;
+                        ++ls_trials;
                         make_candidate(a);
                         eval_reproj_dir<T>(C, S.cfull, S.dfull, kps, nkp, S.R0, S.u.ev, S.out.kcost, S.lsdphi);
                         double c = 0.0, gg = 0.0;
@@ -847,7 +854,10 @@ __device__ void fit_frame(const FitConst* __restrict__ C, int B, const b3d_kp* _
                         if (!isfinite(c) || !isfinite(gg)) return;
                         s.value = c; s.gradient = gg; s.valid = true;
                     };
+                    long long ls_t1 = clock64();
+                    ls_part[0] += ls_t1 - ls_t0;
                     ls_eval(1.0, cur);
+                    { const long long u = clock64(); ls_part[1] += u - ls_t1; ls_t1 = u; }
                     bool success = true;
                     int ls_iters = 0;
                     while (!cur.valid || cur.value > x_cost + kSufficientDecrease * gd * cur.x) {
@@ -865,9 +875,11 @@ __device__ void fit_frame(const FitConst* __restrict__ C, int B, const b3d_kp* _
                         __syncthreads();
                         const double step_size = S.ls_step;
                         __syncthreads();
+                        { const long long u = clock64(); ls_part[2] += u - ls_t1; ls_t1 = u; }
                         if (step_size * dmax < kMinLineSearchStepSize) { success = false; break; }
                         prev = cur;
                         ls_eval(step_size, cur);
+                        { const long long u = clock64(); ls_part[1] += u - ls_t1; ls_t1 = u; }
                     }
                     if (success && cur.x != 1.0) {
                         for (int k = tid; k < n; k += T) S.delta[k] *= cur.x;
@@ -877,6 +889,7 @@ __device__ void fit_frame(const FitConst* __restrict__ C, int B, const b3d_kp* _
                     // ---- ComputeCandidatePointAndEvaluateCost ----
                     make_candidate(1.0);
                     cand_cost = evaluate<T, 0>(C, S.cfull, kps, nkp, S, false, ti, tj, tile_ok);
+                    { const long long u = clock64(); ls_part[3] += u - ls_t1; ls_cyc += u - ls_t0; }
                 }
             }
             if (!isfinite(cand_cost)) cand_cost = DBL_MAX;
@@ -915,7 +928,8 @@ __device__ void fit_frame(const FitConst* __restrict__ C, int B, const b3d_kp* _
         }
     }
     __syncthreads();
-    if (tid == 0 && g_phase_on && b < 1024) { g_block_cycles[b] = (resumed ? g_block_cycles[b] : 0) + (clock64() - t_begin); g_block_ls[b] = n_ls_evals; }
+    if (tid == 0 && g_phase_on && b < 1024) { g_block_cycles[b] = (resumed ? g_block_cycles[b] : 0) + (clock64() - t_begin); g_block_ls[b] = n_ls_evals; g_block_lscyc[b] = (resumed ? g_block_lscyc[b] : 0) + ls_cyc; g_block_lstrials[b] = (resumed ? g_block_lstrials[b] : 0) + ls_trials;
+        for (int q = 0; q < 4; ++q) g_block_lsparts[b][q] = (resumed ? g_block_lsparts[b][q] : 0) + ls_part[q]; }
     if (b == 0 && tid < 32 && g_phase_on) g_phase_cycles[tid] += phase_acc()[tid];
     if (tid == 0 && g_phase_on && b < 1024) g_block_t1[b] = global_ns();
     if (unfinished) {
@@ -1016,6 +1030,12 @@ int b3d_debug_phase_timing(int on) {
     long long z[32] = {0};
     cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z));
     return cudaMemcpyToSymbol(g_phase_on, &on, sizeof(int)) == cudaSuccess ? 0 : 2;
+}
+int b3d_debug_poly_read(unsigned long long* out8) { return cudaMemcpyFromSymbol(out8, g_poly_cyc, 8 * sizeof(unsigned long long)) == cudaSuccess ? 0 : 2; }
+int b3d_debug_block_lsparts_read(long long* parts4096) { return cudaMemcpyFromSymbol(parts4096, g_block_lsparts, 4096 * sizeof(long long)) == cudaSuccess ? 0 : 2; }
+int b3d_debug_block_ls_read(long long* cyc1024, int* trials1024) {
+    cudaMemcpyFromSymbol(trials1024, g_block_lstrials, 1024 * sizeof(int));
+    return cudaMemcpyFromSymbol(cyc1024, g_block_lscyc, 1024 * sizeof(long long)) == cudaSuccess ? 0 : 2;
 }
 int b3d_debug_block_read(long long* cyc1024, int* ls1024) {
     cudaMemcpyFromSymbol(ls1024, g_block_ls, 1024 * sizeof(int));

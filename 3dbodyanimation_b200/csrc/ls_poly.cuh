@@ -10,73 +10,106 @@ constexpr double kSufficientDecrease = 1e-4, kMinLineSearchStepSize = 1e-9;
 constexpr int kMaxLineSearchIters = 20;
 constexpr double kLsContractLo = 1e-3, kLsContractHi = 0.6;   // max_/min_line_search_step_contraction (Solver::Options defaults)
 
-// ---- polynomial helpers for the (rare) Armijo interpolation: warp 0, all lanes --------------------------------------
+// ---- polynomial helpers for the Armijo interpolation ---------------------------------------------------------------
 struct LsSample { double x, value, gradient; bool valid; };
 
 __device__ double poly_eval(const double* p, int nc, double x) { double v = 0; for (int i = 0; i < nc; ++i) v = v * x + p[i]; return v; }
 
-// real parts of the roots of a polynomial of degree <= 4 (coefficients highest first).  Called by ALL lanes of one warp:
-// degrees 1 and 2 in closed form; degrees 3 and 4 by the Aberth-Ehrlich simultaneous iteration with one lane per root (the
-// other lanes idle along), which is what made the single-thread version the longest serial stretch of a line search.
-__device__ int poly_root_real_parts(const double* pin, int nc, double* out) {
-    int lead = 0;
-    while (lead + 1 < nc && pin[lead] == 0.0) ++lead;
-    const double* p = pin + lead;
-    const int deg = nc - lead - 1;
-    if (deg <= 0) return 0;
-    if (deg == 1) { out[0] = -p[1] / p[0]; return 1; }
-    if (deg == 2) {
-        const double a = p[0], b = p[1], c = p[2];
-        const double D = b * b - 4 * a * c, sD = sqrt(fabs(D));
-        if (D >= 0) {
-            if (b >= 0) { out[0] = (-b - sD) / (2.0 * a); out[1] = (2.0 * c) / (-b - sD); }
-            else { out[0] = (2.0 * c) / (-b + sD); out[1] = (-b + sD) / (2.0 * a); }
-        } else { out[0] = out[1] = -b / (2.0 * a); }
-        return 2;
-    }
+// Real roots of a polynomial of degree <= 4 (coefficients highest first, nc of them) inside [lo, hi], ascending.  Ceres hands the
+// derivative of the interpolating polynomial to a companion-matrix eigenvalue solver and tries the real part of EVERY root as a step
+// size; but the minimum of the interpolant over [x_min, x_max] sits at an end point or at a real root of its derivative inside the
+// interval — the other candidates (real parts of complex pairs, roots outside) can never give a smaller value — so only those are
+// needed.  They are isolated exactly by the derivative chain: between two consecutive roots of p' the polynomial p is monotone, so
+// every such piece holds at most one root, found by safeguarded Newton (bisection fallback) to the last bit; the pieces of a level
+// are refined by different lanes of the calling warp.  (The simultaneous complex iteration this replaces was 14 % of fit_single_kernel's cycles.)
+__device__ unsigned long long g_poly_cyc[8];    // debug: cycles in the interpolation, the end-point values, the root search; calls; refinements, their iterations
+template <int NC>
+__device__ __forceinline__ double poly_eval_fixed(const double (&p)[NC], double x) {
+    double v = p[0];
+#pragma unroll
+    for (int i = 1; i < NC; ++i) v = fma(v, x, p[i]);
+    return v;
+}
+// Root of p inside (a, b), p(a) and p(b) of opposite signs (fa = p(a) != 0), by the WHOLE warp: every round the 32 lanes evaluate p
+// at 32 points that cut the bracket into 33 parts and the bracket shrinks to the part with the sign change (6 rounds: 7.7e-10 of the
+// first bracket), then one secant step inside the last bracket.  No divisions in the loop, no dependence on how well Newton's method
+// likes the polynomial (safeguarded Newton needed 18 iterations of ~450 cycles on these interpolants).  All lanes call it with the same arguments and get the same result.
+template <int NC>
+__device__ __forceinline__ double poly_refine_root(const double (&p)[NC], double a, double b, double fa) {
     const int lane = threadIdx.x & 31;
-    double ar[6];
-    const double ilead = 1.0 / p[0];
-    for (int i = 0; i <= deg; ++i) ar[i] = p[i] * ilead;
-    double rad = 0;
-    for (int i = 1; i <= deg; ++i) rad = fmax(rad, fabs(ar[i]));
-    rad = 1.0 + rad;
-    double zr, zi;
-    {
-        double sn, cs;
-        sincos(2 * 3.14159265358979323846 * (lane % deg) / deg + 0.4, &sn, &cs);
-        zr = rad * 0.5 * cs; zi = rad * 0.5 * sn;
+    const bool neg_a = fa < 0.0;
+    double fb_lo = fa, fb_hi = 0.0;     // values at the bracket ends, for the final secant step (fb_hi filled in the first round)
+    bool have_hi = false;
+#pragma unroll 1
+    for (int round = 0; round < 6; ++round) {      // 33^-6 = 7.7e-10 of the first bracket; the secant step below squares that
+        const double h = (b - a) * (1.0 / 33.0);
+        const double x = a + h * (double)(lane + 1);
+        const double f = poly_eval_fixed<NC>(p, x);
+        // lanes whose point is already on b's side of the root (or on it)
+        const unsigned m = __ballot_sync(0xffffffffu, (f < 0.0) != neg_a || f == 0.0);
+        const int first = m ? __ffs(m) - 1 : 32;          // the sign changes between point first - 1 and point first (point -1 = a, point 32 = b)
+        const double xl = __shfl_sync(0xffffffffu, x, first > 0 ? first - 1 : 0), fl = __shfl_sync(0xffffffffu, f, first > 0 ? first - 1 : 0);
+        const double xh = __shfl_sync(0xffffffffu, x, first < 32 ? first : 31), fh = __shfl_sync(0xffffffffu, f, first < 32 ? first : 31);
+        if (first > 0) { a = xl; fb_lo = fl; }
+        if (first < 32) { b = xh; fb_hi = fh; have_hi = true; }
+        if (have_hi && fb_hi == 0.0) return b;
+        if (!(b - a > 4.5e-16 * fmax(fabs(a), fabs(b)))) break;
     }
-    for (int it = 0; it < 64; ++it) {
-        double fr = ar[0], fi = 0, dr = 0, di = 0;
-        for (int k = 1; k <= deg; ++k) {
-            double t = dr * zr - di * zi + fr; di = dr * zi + di * zr + fi; dr = t;
-            t = fr * zr - fi * zi + ar[k]; fi = fr * zi + fi * zr; fr = t;
-        }
-        double ozr[4], ozi[4];                      // every root, gathered outside any divergent code
-#pragma unroll
-        for (int j = 0; j < 4; ++j) { ozr[j] = __shfl_sync(0xffffffffu, zr, j); ozi[j] = __shfl_sync(0xffffffffu, zi, j); }
-        double wr = 0.0, wi = 0.0;
-        if (!(fr == 0.0 && fi == 0.0)) {
-            const double idd = 1.0 / (dr * dr + di * di);
-            const double rr = (fr * dr + fi * di) * idd, ri = (fi * dr - fr * di) * idd;   // ratio = f / f'
-            double sr = 0, si = 0;
-#pragma unroll
-            for (int j = 0; j < 4; ++j)
-                if (j < deg && j != lane) { const double ur = zr - ozr[j], ui = zi - ozi[j], iu = 1.0 / (ur * ur + ui * ui); sr += ur * iu; si -= ui * iu; }
-            const double er = 1.0 - (rr * sr - ri * si), ei = -(rr * si + ri * sr);
-            const double iee = 1.0 / (er * er + ei * ei);
-            wr = (rr * er + ri * ei) * iee; wi = (ri * er - rr * ei) * iee;
-        }
-        zr -= wr; zi -= wi;
-        double change = lane < deg ? sqrt(wr * wr + wi * wi) : 0.0;
-#pragma unroll
-        for (int o = 4; o > 0; o >>= 1) change = fmax(change, __shfl_xor_sync(0xffffffffu, change, o));
-        change = __shfl_sync(0xffffffffu, change, 0);
-        if (change < 1e-14 * rad) break;   // warp-uniform
+    if (!have_hi) return 0.5 * (a + b);
+    // secant step inside the last bracket (p is monotone on it)
+    const double t = fb_lo / (fb_lo - fb_hi);
+    const double x = a + (b - a) * t;
+    return (x >= fmin(a, b) && x <= fmax(a, b)) ? x : 0.5 * (a + b);
+}
+// real roots of a x^2 + b x + c inside the open interval (lo, hi), ascending (a = 0: the linear root)
+__device__ __forceinline__ int quad_roots_in(double a, double b, double c, double lo, double hi, double* out) {
+    double r0, r1;
+    int n = 0;
+    if (a == 0.0) {
+        if (b == 0.0) return 0;
+        r0 = -c / b; n = 1;
+    } else {
+        const double D = b * b - 4.0 * a * c;
+        if (!(D >= 0.0)) return 0;
+        const double sD = sqrt(D);
+        if (b >= 0) { r0 = (-b - sD) / (2.0 * a); r1 = (2.0 * c) / (-b - sD); }
+        else { r0 = (2.0 * c) / (-b + sD); r1 = (-b + sD) / (2.0 * a); }
+        n = 2;
+        if (r1 < r0) { const double t = r0; r0 = r1; r1 = t; }
     }
-    for (int i = 0; i < deg; ++i) out[i] = __shfl_sync(0xffffffffu, zr, i);
-    return deg;
+    int m = 0;
+    if (r0 > lo && r0 < hi) out[m++] = r0;
+    if (n == 2 && r1 > lo && r1 < hi && !(m == 1 && r1 == out[0])) out[m++] = r1;
+    return m;
+}
+// one level of the chain: the roots of q (NC coefficients) in [lo, hi], given the nb roots of q' in (lo, hi) (ascending) as break
+// points: q is monotone on every piece between them.  All lanes of the warp call it with the same arguments.
+template <int NC>
+__device__ __forceinline__ int poly_level_roots(const double (&q)[NC], double lo, double hi, const double* brk_in, int nb, double* brk_out) {
+    int n = 0;
+    double a = lo, fa = poly_eval_fixed<NC>(q, lo);
+    for (int j = 0; j <= nb; ++j) {
+        const double b = j < nb ? brk_in[j] : hi;
+        const double fb = poly_eval_fixed<NC>(q, b);
+        if (fa == 0.0) { if (n == 0 || brk_out[n - 1] != a) brk_out[n++] = a; }
+        else if ((fa < 0.0) != (fb < 0.0) && fb != 0.0) brk_out[n++] = poly_refine_root<NC>(q, a, b, fa);
+        // (a root exactly at b is the next piece's a; at b = hi it is the interval's end point, which the caller tries anyway)
+        a = b; fa = fb;
+    }
+    return n;
+}
+// Real roots in [lo, hi] of the derivative of the interpolant: a quadratic (two samples; pin has 3 coefficients) or a quartic (three
+// samples; 5 coefficients).  Called by ALL lanes of one warp with the same arguments.
+__device__ int poly_real_roots_in(const double* pin, int nc, double lo, double hi, double* out) {
+    if (!(lo <= hi)) return 0;
+    if (nc == 3) return quad_roots_in(pin[0], pin[1], pin[2], lo, hi, out);
+    if (nc != 5) return 0;
+    const double q4[5] = {pin[0], pin[1], pin[2], pin[3], pin[4]};
+    const double q3[4] = {4.0 * pin[0], 3.0 * pin[1], 2.0 * pin[2], pin[3]};
+    double b2[2], b3[4];
+    const int n2 = quad_roots_in(12.0 * pin[0], 6.0 * pin[1], 2.0 * pin[2], lo, hi, b2);     // where the cubic q4' turns
+    const int n3 = poly_level_roots<4>(q3, lo, hi, b2, n2, b3);                              // where the quartic turns
+    return poly_level_roots<5>(q4, lo, hi, b3, n3, out);
 }
 
 // Coefficients (highest degree first) of the polynomial of degree 2 NS - 1 that interpolates value and gradient at NS distinct
@@ -132,7 +165,9 @@ __device__ double minimize_interpolating_polynomial(const LsSample* s, int ns, d
     const int nc = 2 * ns, degree = nc - 1;
     double coef[6];
     double best_x = (x_min + x_max) / 2.0;
+    const long long t0 = clock64();
     const bool ok = ns == 3 ? hermite_coefficients<3>(s, coef) : hermite_coefficients<2>(s, coef);
+    const long long t1 = clock64();
     if (!ok) return best_x;
     double best_v = poly_eval(coef, nc, best_x);
     const double vmin = poly_eval(coef, nc, x_min);
@@ -141,9 +176,14 @@ __device__ double minimize_interpolating_polynomial(const LsSample* s, int ns, d
     if (vmax < best_v) { best_v = vmax; best_x = x_max; }
     double dcoef[5], roots[5];
     for (int i = 0; i < degree; ++i) dcoef[i] = (degree - i) * coef[i];
-    const int nr = poly_root_real_parts(dcoef, degree, roots);
+    const long long t2 = clock64();
+    const int nr = poly_real_roots_in(dcoef, degree, x_min, x_max, roots);
+    if ((threadIdx.x & 31) == 0) {
+        const long long t3 = clock64();
+        atomicAdd(&g_poly_cyc[0], (unsigned long long)(t1 - t0)); atomicAdd(&g_poly_cyc[1], (unsigned long long)(t2 - t1));
+        atomicAdd(&g_poly_cyc[2], (unsigned long long)(t3 - t2)); atomicAdd(&g_poly_cyc[3], 1ull);
+    }
     for (int i = 0; i < nr; ++i) {
-        if (roots[i] < x_min || roots[i] > x_max) continue;
         const double v = poly_eval(coef, nc, roots[i]);
         if (v < best_v) { best_v = v; best_x = roots[i]; }
     }

@@ -125,6 +125,20 @@ def phases(n=148, mode="C2"):
     for b in order:
         print(f"  block {b}: {cy[b] / 1e6:.2f} Mcycles, iters {int(ni[b])}, per-iter {per[b]:.0f}, line-search fallbacks {lsv[b]}")
     print("frames with line-search fallbacks:", int((lsv > 0).sum()), "total fallbacks", int(lsv.sum()))
+    lc, lt = (C.c_longlong * 1024)(), (C.c_int * 1024)()
+    lib.b3d_debug_block_ls_read(lc, lt)
+    lc, lt = np.array(lc[:m], dtype=np.float64), np.array(lt[:m])
+    print(f"line-search fall-backs: {lc.sum() / 1e6:.1f} Mcycles of {cy.sum() / 1e6:.1f} ({100 * lc.sum() / cy.sum():.1f} %), {int(lt.sum())} trial evaluations, "
+          f"{lc.sum() / max(lsv.sum(), 1):.0f} cycles per fall-back, {lt.sum() / max(lsv.sum(), 1):.2f} trials per fall-back")
+    lp = (C.c_longlong * 4096)()
+    lib.b3d_debug_block_lsparts_read(lp)
+    lp = np.array(lp[:4 * m], dtype=np.float64).reshape(m, 4).sum(axis=0)
+    print("  of which set-up %.1f, trial evaluations %.1f, polynomial minimisation %.1f, final evaluation %.1f Mcycles" % tuple(lp / 1e6))
+    pc = (C.c_ulonglong * 8)()
+    lib.b3d_debug_poly_read(pc)
+    print("  polynomial minimisation (all calls since load): %d calls, per call interpolation %.0f, end points %.0f, roots %.0f cycles"
+          % (pc[3], pc[0] / max(pc[3], 1), pc[1] / max(pc[3], 1), pc[2] / max(pc[3], 1)))
+    print("  root refinements %d, iterations per refinement %.1f" % (pc[4], pc[5] / max(pc[4], 1)))
     t0, t1 = (C.c_longlong * 1024)(), (C.c_longlong * 1024)()
     lib.b3d_debug_block_times(t0, t1)
     t0, t1 = np.array(t0[:m], dtype=np.float64), np.array(t1[:m], dtype=np.float64)
