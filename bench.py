@@ -701,10 +701,12 @@ def c3_leg(args, api, with_cpu):
     # shard edge).  Not the reference's serial chain: it deviates from it by <= 8.6e-4 in the joint angles on the 600-frame test
     # sequence (tests/test_fit_window_gpu.py::test_sharded_schedule_deviation_from_serial); reported beside the exact number, never instead
     so16 = api.seq_opts(skip=10, wsize=20, overlap=5, it1=1000, it2=60, num_shards=16, beta_pose=20.0, beta_shape=30.0, lambda_temp=3.0)
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    g16 = api.fit_sequences(gm, base, so16, seq["kps"], seq["nkp"], seq["poses"], seq["R0"], seq["W"])
-    dt16 = time.perf_counter() - t0
+    dt16 = 1e30
+    for _ in range(2):      # best of two: the call allocates its (large) workspaces itself, and a first cudaMalloc of a new size can cost as much as the solve
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        g16 = api.fit_sequences(gm, base, so16, seq["kps"], seq["nkp"], seq["poses"], seq["R0"], seq["W"])
+        dt16 = min(dt16, time.perf_counter() - t0)
     res["sharded_schedule"] = {"num_shards": 16, "frames_per_sec": n / dt16, "ms": dt16 * 1e3, "failed_solves": int(g16["nfail"]),
                                "max_abs_jointAA_deviation_from_serial": float(np.max(np.abs(g16["poses"][:, 7:] - g["poses"][:, 7:]))),
                                "max_abs_t_over_s_deviation_from_serial": float(np.max(np.abs(g16["poses"][:, 4:7] / g16["poses"][:, :1] - g["poses"][:, 4:7] / g["poses"][:, :1]))),
