@@ -53,7 +53,10 @@ def _compare(g, o, tight):
         assert np.max(np.abs(g["jointAA"][f] - o["jointAA"][f])) < PARAM_TOL
         assert np.max(np.abs(g["sim3"][f, 1:4] - o["sim3"][f, 1:4])) < PARAM_TOL
         assert np.max(np.abs(g["w"][f] - o["w"][f])) < PARAM_TOL
-        assert np.max(np.abs(g["sim3"][f, 4:7] / g["sim3"][f, 0] - o["sim3"][f, 4:7] / o["sim3"][f, 0])) < PARAM_TOL * 3.5
+        # translation as t / s, the gauge-invariant combination (DESIGN "Gauge freedom"); it is a length of ~3-4 units (the camera
+        # distance), so 1e-3 is taken relative to it
+        ts_g, ts_o = g["sim3"][f, 4:7] / g["sim3"][f, 0], o["sim3"][f, 4:7] / o["sim3"][f, 0]
+        assert np.max(np.abs(ts_g - ts_o)) < PARAM_TOL * max(1.0, float(np.max(np.abs(ts_o))))
         if k == n and ng == no:     # the whole solve stayed in the stable regime: scale and translation themselves
             n_full += 1
             assert np.max(np.abs(g["sim3"][f] - o["sim3"][f])) < PARAM_TOL

@@ -69,11 +69,12 @@ def _seq_compare(g, o, n):
     assert g["nfail"] == o["nfail"]
     assert np.max(np.abs(g["poses"][:, 1:4] - o["poses"][:, 1:4])) < PARAM_TOL
     assert np.max(np.abs(g["poses"][:, 7:] - o["poses"][:, 7:])) < PARAM_TOL
-    assert np.max(np.abs(g["poses"][:, 4:7] / g["poses"][:, :1] - o["poses"][:, 4:7] / o["poses"][:, :1])) < 5e-3
-    assert np.max(np.abs(g["W"] - o["W"])) < 1e-2
+    # translation is compared as t / s (the gauge-invariant combination, DESIGN "Gauge freedom"), at the parameter tolerance like the rest
+    assert np.max(np.abs(g["poses"][:, 4:7] / g["poses"][:, :1] - o["poses"][:, 4:7] / o["poses"][:, :1])) < PARAM_TOL
+    assert np.max(np.abs(g["W"] - o["W"])) < PARAM_TOL
     assert np.max(np.abs(g["R0"] - o["R0"])) < PARAM_TOL
     assert np.max(np.abs(g["r"] - o["r"])) < PARAM_TOL
-    assert np.max(np.abs(g["p"] / g["poses"][:, :1] - o["p"] / o["poses"][:, :1])) < 5e-3
+    assert np.max(np.abs(g["p"] / g["poses"][:, :1] - o["p"] / o["poses"][:, :1])) < PARAM_TOL
 
 
 @pytest.mark.parametrize("shards", [1, 2, 3])
@@ -152,7 +153,7 @@ def test_c3_at_stated_size_vs_committed_oracle_result(api, gmodel, synth, model_
               f"worst deviations {dev}")
     assert g["nfail"] == int(ref["nfail"]) == 0
     assert dev["raa"] < PARAM_TOL and dev["jaa"] < PARAM_TOL and dev["R0"] < PARAM_TOL
-    assert dev["t_over_s"] < 5e-3 and dev["W"] < 1e-2
+    assert dev["t_over_s"] < PARAM_TOL and dev["W"] < PARAM_TOL and dev["scale"] < 2e-3    # (the scale alone is the gauge direction)
     assert np.mean(gi[1:] == oi[1:]) > 0.8 and abs(int(gi[0]) - int(oi[0])) <= 2
 
 
@@ -201,7 +202,7 @@ def test_sharded_schedule_deviation_from_serial(api, gmodel, synth, model_np, ca
         dts = float(np.max(np.abs(a["poses"][:, 4:7] / a["poses"][:, :1] - b["poses"][:, 4:7] / b["poses"][:, :1])))
         dw = float(np.max(np.abs(a["W"] - b["W"])))
         rows.append((G, dj, dr, dts, dw))
-        assert dj < 1e-2 and dr < 1e-2 and dts < 1e-2, rows
+        assert dj < 2e-3 and dr < 2e-3 and dts < 2e-3, rows      # an approximation by construction: bounded at twice the parameter tolerance, measured 8.6e-4
     with capsys.disabled():
         for G, dj, dr, dts, dw in rows:
             print(f"\n[sharded vs serial, {n} frames, G = {G}] max |d jointAA| {dj:.2e}, max |d R0| {dr:.2e}, max |d t/s| {dts:.2e}, max |d w| {dw:.2e}")
