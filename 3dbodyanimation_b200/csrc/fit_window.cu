@@ -14,8 +14,10 @@
 // substitution come out of the same column sweep; the 10 x 10 Schur complement of w closes the system.
 #include <algorithm>
 #include <atomic>
+#include <vector>
 
 #include "lm_device.cuh"
+#include "writeback.cuh"
 
 namespace b3d {
 
@@ -133,7 +135,7 @@ struct WinSmem {
 // dense Jacobian over 4 x 4 register tiles (thread (ti, tj), 253 tiles), scattered straight into the block structure.
 template <int T, bool JAC>
 __device__ double win_evaluate(const FitConst* __restrict__ C, int F, const double* xp /* written by the master during the kernel: no read-only path */, const b3d_kp* __restrict__ kps,
-                               const int32_t* __restrict__ nkp_all, const double* __restrict__ R0_all, WinWs& W, WinSmem& S, int f_lo, int f_hi,
+                               const int32_t* __restrict__ nkp_all, const double* R0_all, WinWs& W, WinSmem& S, int f_lo, int f_hi,
                                int rank, bool scaled = false) {
     const int tid = threadIdx.x;
     WinEval& E = S.u.e;
@@ -638,15 +640,22 @@ __device__ void win_back(const FitConst* __restrict__ C, int F, WinWs& W, WinSme
 template <int T>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T, 1) fit_window_kernel(const FitConst* __restrict__ C, int nprob, const WinProblem* __restrict__ probs,
                                                           const b3d_kp* __restrict__ kps_all, const int32_t* __restrict__ nkp_all,
-                                                          const double* __restrict__ R0_all, double* __restrict__ poses,
+                                                          double* R0_all /* chain mode rotates it between solves: no read-only path */, double* poses,
                                                           double* __restrict__ Wshape, uint8_t* __restrict__ usable,
                                                           b3d_iter_record* __restrict__ trace, int trace_stride, int32_t* __restrict__ niters,
-                                                          int32_t* __restrict__ term, double* __restrict__ workspace) {
+                                                          int32_t* __restrict__ term, double* __restrict__ workspace,
+                                                          const int32_t* __restrict__ chain_order, int chain_len, double* r_out, double* p_out) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     WinSmem& S = *reinterpret_cast<WinSmem*>(smem_raw);
-    const int tid = threadIdx.x, pb = blockIdx.x >> 1;
+    const int tid = threadIdx.x, cid = blockIdx.x >> 1;
     const int rank = (int)cluster_ctarank();
-    if (pb >= nprob) return;                 // (both CTAs of the cluster)
+    // Chain mode (chain_order != null): this cluster solves the problems chain_order[cid * chain_len + 0, 1, ...] one after the other
+    // (the windows of one shard: window k + 1 starts from what window k left in its overlap frames), each followed by the write-back
+    // of its frames (R0 <- R(rootAA) R0, r, p: include/MultiFrameBA.h:154-172) — no host round trip and no wave barrier across shards.
+    const int nsteps = chain_order ? chain_len : 1;
+    for (int step = 0; step < nsteps; ++step) {
+    const int pb = chain_order ? chain_order[(size_t)cid * chain_len + step] : cid;
+    if (pb < 0 || pb >= nprob) break;        // (both CTAs of the cluster)
     const WinProblem pr = probs[pb];
     const int F = pr.count, n = F * NB + NS;
     const b3d_kp* kps = kps_all + (size_t)pr.first * MAXKP;
@@ -692,8 +701,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T, 1) fit_window_ker
                 cluster_sync_all();                              // (C)
             }
         }
-        return;
-    }
+    } else {
     // ---------------- master ----------------
     for (int k = tid; k < F * NB; k += T) W.x[k] = xin[k];
     if (tid < NS) W.x[(size_t)F * NB + tid] = win[tid];
@@ -903,6 +911,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T, 1) fit_window_ker
         if (niters) niters[pb] = nrec;
         if (term) term[pb] = termination;
     }
+    }   // master
+    if (chain_order) {
+        cluster_sync_all();                  // the master's poses are visible
+        if (rank == 0)
+            for (int t = tid; t < F * NJ; t += T)
+                writeback_entry(pr.first + t / NJ, t % NJ, poses, R0_all, r_out, p_out);
+        cluster_sync_all();                  // ... and so are the rotated R0 / r / p, before the chain's next window reads them
+    }
+    }   // chain steps
 }
 
 }  // namespace b3d
@@ -948,8 +965,19 @@ int win_launch(const FitConst* dfc, const WinProblem* dprobs, int nprob, const b
         }
     }
     B3D_CUDA(cudaFuncSetAttribute(fit_window_kernel<FW_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(WinSmem)));   // per device: every call
-    fit_window_kernel<FW_THREADS><<<2 * nprob, FW_THREADS, sizeof(WinSmem), st>>>(dfc, nprob, dprobs, kps, nkp, R0, poses, W, usable, trace, trace_stride,
-                                                                             niters, term, ws);
+    fit_window_kernel<FW_THREADS><<<2 * nprob, FW_THREADS, sizeof(WinSmem), st>>>(dfc, nprob, dprobs, kps, nkp, const_cast<double*>(R0), poses, W, usable, trace,
+                                                                             trace_stride, niters, term, ws, nullptr, 0, nullptr, nullptr);
+    B3D_LAUNCH_CHECK();
+    return B3D_OK;
+}
+
+int win_launch_chains(const FitConst* dfc, const WinProblem* dprobs, int nprob, const int32_t* order_d, int nchain, int chain_len, const b3d_kp* kps,
+                      const int32_t* nkp, double* R0, double* poses, double* W, double* r, double* p, uint8_t* usable, int32_t* niters, int32_t* term,
+                      double* ws, cudaStream_t st) {
+    if (nchain <= 0 || chain_len <= 0) return B3D_OK;
+    B3D_CUDA(cudaFuncSetAttribute(fit_window_kernel<FW_THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(WinSmem)));
+    fit_window_kernel<FW_THREADS><<<2 * nchain, FW_THREADS, sizeof(WinSmem), st>>>(dfc, nprob, dprobs, kps, nkp, R0, poses, W, usable, nullptr, 0, niters, term, ws,
+                                                                              order_d, chain_len, r, p);
     B3D_LAUNCH_CHECK();
     return B3D_OK;
 }
@@ -959,6 +987,56 @@ int win_launch(const FitConst* dfc, const WinProblem* dprobs, int nprob, const b
 using namespace b3d;
 
 extern "C" {
+
+int b3d_fit_window_chains_dev(const b3d_model* m, const b3d_fit_opts* opts, int32_t nchain, const int32_t* chain_ptr, const int32_t* first,
+                              const int32_t* count, const b3d_kp* kps, const int32_t* nkp, double* R0, double* poses, double* W, double* r, double* p,
+                              uint8_t* usable, int32_t* niters, int32_t* term, void* stream) {
+    if (!m || !opts || !chain_ptr || !first || !count || !kps || !nkp || !R0 || !poses || !W) return set_error(B3D_EINVAL, "b3d_fit_window_chains: null argument");
+    if (nchain < 0 || opts->max_iters < 0) return set_error(B3D_EINVAL, "b3d_fit_window_chains: negative size");
+    if (nchain == 0) return B3D_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int nprob = chain_ptr[nchain];
+    if (chain_ptr[0] != 0 || nprob < 0) return set_error(B3D_EINVAL, "b3d_fit_window_chains: chain_ptr must start at 0 and ascend");
+    int chain_len = 0, max_count = 0;
+    for (int c = 0; c < nchain; ++c) {
+        if (chain_ptr[c + 1] < chain_ptr[c]) return set_error(B3D_EINVAL, "b3d_fit_window_chains: chain_ptr must ascend");
+        chain_len = std::max(chain_len, chain_ptr[c + 1] - chain_ptr[c]);
+    }
+    for (int q = 0; q < nprob; ++q) {
+        if (count[q] <= 0 || first[q] < 0) return set_error(B3D_EINVAL, "b3d_fit_window_chains: problem %d has first=%d count=%d", q, first[q], count[q]);
+        max_count = std::max(max_count, count[q]);
+    }
+    if (nprob == 0) return B3D_OK;
+    if (max_count >= CH_MIN_FRAMES) return set_error(B3D_EINVAL, "b3d_fit_window_chains: windows of %d frames or more go through b3d_fit_windows_dev", (int)CH_MIN_FRAMES);
+    const size_t slot = win_ws_doubles(max_count);
+    std::vector<WinProblem> probs(nprob);
+    std::vector<int32_t> order((size_t)nchain * chain_len, -1);
+    for (int c = 0; c < nchain; ++c)
+        for (int q = chain_ptr[c]; q < chain_ptr[c + 1]; ++q) {
+            probs[q].first = first[q]; probs[q].count = count[q]; probs[q].ws_offset = (int64_t)((size_t)c * slot);
+            order[(size_t)c * chain_len + (q - chain_ptr[c])] = q;
+        }
+    FitConst fc;
+    if (int rc = build_fit_const(m, nullptr, opts, true, &fc)) return rc;
+    FitConst* dfc = nullptr;
+    WinProblem* dpr = nullptr;
+    int32_t* dord = nullptr;
+    double* ws = nullptr;
+    B3D_CUDA(cudaMallocAsync(&dfc, sizeof(FitConst), st));
+    B3D_CUDA(cudaMallocAsync(&dpr, sizeof(WinProblem) * nprob, st));
+    B3D_CUDA(cudaMallocAsync(&dord, sizeof(int32_t) * order.size(), st));
+    B3D_CUDA(cudaMallocAsync(&ws, sizeof(double) * slot * (size_t)nchain, st));
+    B3D_CUDA(cudaMemcpyAsync(dfc, &fc, sizeof(FitConst), cudaMemcpyHostToDevice, st));
+    B3D_CUDA(cudaMemcpyAsync(dpr, probs.data(), sizeof(WinProblem) * nprob, cudaMemcpyHostToDevice, st));
+    B3D_CUDA(cudaMemcpyAsync(dord, order.data(), sizeof(int32_t) * order.size(), cudaMemcpyHostToDevice, st));
+    B3D_CUDA(cudaStreamSynchronize(st));      // the staged copies must have left the host vectors
+    if (int rc = win_launch_chains(dfc, dpr, nprob, dord, nchain, chain_len, kps, nkp, R0, poses, W, r, p, usable, niters, term, ws, st)) return rc;
+    B3D_CUDA(cudaFreeAsync(ws, st));
+    B3D_CUDA(cudaFreeAsync(dord, st));
+    B3D_CUDA(cudaFreeAsync(dpr, st));
+    B3D_CUDA(cudaFreeAsync(dfc, st));
+    return B3D_OK;
+}
 
 // debug hooks (not part of include/b3d.h): per-phase cycle counters of block 0 of fit_window_kernel
 int b3d_debug_win_timing(int on) {

@@ -74,6 +74,12 @@ int win_launch(const FitConst* dfc, const WinProblem* dprobs, int nprob, const b
                double* W, uint8_t* usable, b3d_iter_record* trace, int trace_stride, int32_t* niters, int32_t* term, double* ws, cudaStream_t st,
                const WinProblem* hprobs = nullptr);
 
+// chain mode: cluster c solves the problems order[c * chain_len + 0 .. chain_len) (-1 = none) one after the other, each followed by the
+// write-back of its frames into R0 / r / p (problems of one chain share a workspace slot; different chains must not)
+int win_launch_chains(const FitConst* dfc, const WinProblem* dprobs, int nprob, const int32_t* order_d, int nchain, int chain_len, const b3d_kp* kps,
+                      const int32_t* nkp, double* R0, double* poses, double* W, double* r, double* p, uint8_t* usable, int32_t* niters, int32_t* term,
+                      double* ws, cudaStream_t st);
+
 // ---------------------------------------------------------------------------------------------------------------
 // rotations
 // ---------------------------------------------------------------------------------------------------------------

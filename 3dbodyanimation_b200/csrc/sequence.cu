@@ -13,6 +13,7 @@
 // hand-off — OVERLAP x (76 + 9) doubles per edge, what NCCL send/recv carries between GPUs).  Independent sequences and the
 // shards of one sequence are batched into the same launches: one CTA per (sequence, shard) chain per wave.
 #include <algorithm>
+#include <atomic>
 
 #include "lm_device.cuh"
 
@@ -35,6 +36,8 @@ __global__ void share_shape(int N, const int32_t* __restrict__ front_of, double*
     if (q != f) W[t] = W[(size_t)q * NS + s];
 }
 
+static std::atomic<int> g_seq_waves{0};     // debug hook b3d_debug_seq_waves: 1 = stage 2 as one launch per wave (the round-1 schedule)
+
 struct DevBuf {
     char* p = nullptr;
     ~DevBuf() { cudaFree(p); }
@@ -54,6 +57,8 @@ static int gather(cudaStream_t st, int n, const int32_t* idx, const void* src, v
 using namespace b3d;
 
 extern "C" {
+
+int b3d_debug_seq_waves(int on) { g_seq_waves.store(on); return 0; }
 
 int b3d_fit_sequences(const b3d_model* m, const b3d_fit_opts* base, const b3d_seq_opts* so, int32_t nseq, const int32_t* seq_first,
                       const int32_t* seq_len, int32_t N, const b3d_kp* kps, const int32_t* nkp, double* poses, double* R0, double* W,
@@ -104,34 +109,33 @@ int b3d_fit_sequences(const b3d_model* m, const b3d_fit_opts* base, const b3d_se
         for (int q = 0; q < nseq; ++q) { probs.push_back({anchor_first[q], anchor_cnt[q], (int64_t)off}); off += win_ws_doubles(anchor_cnt[q]); }
         ws_need = off;
     }
+    // every chain owns one workspace slot for all its windows: the chains run unsynchronised (chain mode of fit_window_kernel)
+    const size_t slot = win_ws_doubles(so->wsize);
+    ws_need = std::max(ws_need, slot * (size_t)NC);
     std::vector<std::vector<int>> wave_chain(waves);
+    std::vector<int32_t> order((size_t)NC * std::max(waves, 1), -1);      // order[c][i] = problem of chain c's i-th window
     for (int i = 0; i < waves; ++i) {
         wave_off[i] = (int)probs.size();
-        size_t off = 0;
         for (int c = 0; c < NC; ++c) {
             const Chain& ch = chains[c];
             if (ch.k0 + i >= ch.k1) continue;
             const int s = starts[ch.q][ch.k0 + i], e = std::min(s + so->wsize, (int)seq_len[ch.q]);
-            probs.push_back({(int32_t)(base_row(c) + seq_first[ch.q] + s), e - s, (int64_t)off});
-            off += win_ws_doubles(e - s);
+            order[(size_t)c * waves + i] = (int32_t)probs.size();
+            probs.push_back({(int32_t)(base_row(c) + seq_first[ch.q] + s), e - s, (int64_t)(slot * (size_t)c)});
             wave_chain[i].push_back(c);
         }
-        ws_need = std::max(ws_need, off);
     }
     wave_off[waves] = (int)probs.size();
     const int fix_off = (int)probs.size();
     std::vector<int> fix_chain;
     if (sharded) {
-        size_t off = 0;
         for (int c = 0; c < NC; ++c) {
             const Chain& ch = chains[c];
             if (ch.g == 0) continue;
             const int s = starts[ch.q][ch.k0], e = std::min(s + so->wsize, (int)seq_len[ch.q]);
-            probs.push_back({(int32_t)(base_row(c) + seq_first[ch.q] + s), e - s, (int64_t)off});     // fix-up copies reuse the slot of chain c
-            off += win_ws_doubles(e - s);
+            probs.push_back({(int32_t)(base_row(c) + seq_first[ch.q] + s), e - s, (int64_t)(slot * (size_t)c)});     // the fix-up of chain c takes chain c's slot
             fix_chain.push_back(c);
         }
-        ws_need = std::max(ws_need, off);
     }
     const int NP = (int)probs.size();
 
@@ -231,12 +235,23 @@ int b3d_fit_sequences(const b3d_model* m, const b3d_fit_opts* base, const b3d_se
             B3D_CUDA(cudaMemcpyAsync(p_d + (size_t)c * n * 3, p_d, 8 * n * 3, cudaMemcpyDeviceToDevice, st));
         }
     }
-    for (int i = 0; i < waves; ++i) {
-        const int p0 = wave_off[i], np = wave_off[i + 1] - p0;
-        if (int rc = win_launch(fc_d + 1, probs_d + p0, np, kps_d, nkp_d, R0_d, poses_d, W_d, us_d + p0, nullptr, 0, ni_d + p0, te_d + p0,
-                                (double*)d_ws.p, st)) return rc;
-        for (int j = 0; j < np; ++j)
-            if (int rc = writeback_problem(probs[p0 + j], poses_d, R0_d, r_d, p_d)) return rc;
+    if (g_seq_waves.load() == 0 && waves > 0 && so->wsize < CH_MIN_FRAMES) {
+        // every chain's windows back to back in ONE launch (cluster = chain), the write-back between two windows done by the kernel
+        DevBuf d_order;
+        if (int rc = d_order.alloc(sizeof(int32_t) * order.size())) return rc;
+        B3D_CUDA(cudaMemcpyAsync(d_order.p, order.data(), sizeof(int32_t) * order.size(), cudaMemcpyHostToDevice, st));
+        if (int rc = win_launch_chains(fc_d + 1, probs_d, NP, (const int32_t*)d_order.p, NC, waves, kps_d, nkp_d, R0_d, poses_d, W_d, r_d, p_d, us_d, ni_d, te_d,
+                                       (double*)d_ws.p, st)) return rc;
+        B3D_CUDA(cudaStreamSynchronize(st));          // d_order is released at the end of this scope
+    } else {
+        // wave i = the i-th window of every chain in one launch, the write-backs as separate launches (debug hook b3d_debug_seq_waves)
+        for (int i = 0; i < waves; ++i) {
+            const int p0 = wave_off[i], np = wave_off[i + 1] - p0;
+            if (int rc = win_launch(fc_d + 1, probs_d + p0, np, kps_d, nkp_d, R0_d, poses_d, W_d, us_d + p0, nullptr, 0, ni_d + p0, te_d + p0,
+                                    (double*)d_ws.p, st)) return rc;
+            for (int j = 0; j < np; ++j)
+                if (int rc = writeback_problem(probs[p0 + j], poses_d, R0_d, r_d, p_d)) return rc;
+        }
     }
     if (sharded) {
         // ownership: chain (q, g) owns frames [start(k0), start(k1 of the same chain)) of its sequence (last shard: to the end)

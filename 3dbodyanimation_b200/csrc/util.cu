@@ -3,54 +3,16 @@
 #include <algorithm>
 
 #include "internal.hpp"
+#include "writeback.cuh"
 
 namespace b3d {
-
-// Eigen::AngleAxisd(theta, aa/theta).toRotationMatrix() for theta > 1e-12, identity otherwise (Sim3BA.h:483-489). Col-major out.
-__device__ __forceinline__ void aa_to_matrix_cm(const double* aa, double* R) {
-    const double th = sqrt(aa[0] * aa[0] + aa[1] * aa[1] + aa[2] * aa[2]);
-    if (th > 1e-12) {
-        const double x = aa[0] / th, y = aa[1] / th, z = aa[2] / th;
-        double s, c;
-        sincos(th, &s, &c);
-        const double t = 1.0 - c;
-        R[0] = t * x * x + c;     R[3] = t * x * y - s * z; R[6] = t * x * z + s * y;
-        R[1] = t * x * y + s * z; R[4] = t * y * y + c;     R[7] = t * y * z - s * x;
-        R[2] = t * x * z - s * y; R[5] = t * y * z + s * x; R[8] = t * z * z + c;
-    } else {
-        R[0] = 1; R[1] = 0; R[2] = 0; R[3] = 0; R[4] = 1; R[5] = 0; R[6] = 0; R[7] = 0; R[8] = 1;
-    }
-}
 
 // one thread per (frame, joint)
 __global__ void writeback_kernel(int F, const double* __restrict__ poses, double* __restrict__ R0, double* __restrict__ r,
                                  double* __restrict__ p) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= F * NJ) return;
-    const int f = t / NJ, j = t % NJ;
-    const double* pose = poses + (size_t)f * NPF;
-    double R[9];
-    if (j == 0) {
-        double Rr[9], A[9];
-        aa_to_matrix_cm(pose + IDX_RAA, Rr);
-#pragma unroll
-        for (int k = 0; k < 9; ++k) A[k] = R0[(size_t)f * 9 + k];
-        // r[0] <- R(rootAA) * r[0]  (col-major product)
-#pragma unroll
-        for (int col = 0; col < 3; ++col)
-#pragma unroll
-            for (int row = 0; row < 3; ++row)
-                R[3 * col + row] = Rr[row] * A[3 * col] + Rr[3 + row] * A[3 * col + 1] + Rr[6 + row] * A[3 * col + 2];
-#pragma unroll
-        for (int k = 0; k < 9; ++k) R0[(size_t)f * 9 + k] = R[k];
-        if (p) { p[(size_t)f * 3] = pose[IDX_T]; p[(size_t)f * 3 + 1] = pose[IDX_T + 1]; p[(size_t)f * 3 + 2] = pose[IDX_T + 2]; }
-    } else {
-        aa_to_matrix_cm(pose + IDX_JAA + 3 * (j - 1), R);
-    }
-    if (r) {
-#pragma unroll
-        for (int k = 0; k < 9; ++k) r[((size_t)f * NJ + j) * 9 + k] = R[k];
-    }
+    writeback_entry(t / NJ, t % NJ, poses, R0, r, p);
 }
 
 __global__ void pixel_error_kernel(int F, const b3d_kp* __restrict__ kps, const int32_t* __restrict__ nkp,

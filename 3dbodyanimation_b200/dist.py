@@ -164,6 +164,31 @@ class GpuWindowSolver:
                         "b3d_fit_windows_dev")
         self.batches.append((stage, list(firsts), list(counts), stat, us))
 
+    def solve_chains(self, stage, chains, st):
+        """chains: per chain the list of (first, count) windows, solved back to back ON THE DEVICE by one cluster per chain, the
+        write-back of each window done between the solves (b3d_fit_window_chains_dev): the chains run side by side without a barrier
+        per window.  Same results as solve_batch + writeback wave by wave."""
+        chains = [c for c in chains if c]
+        if not chains:
+            return
+        dev = st["poses"].device
+        assert dev.type == "cuda", "GpuWindowSolver needs device tensors (there is no CPU fitting path)"
+        firsts = [int(f) for c in chains for (f, _) in c]
+        counts = [int(n) for c in chains for (_, n) in c]
+        ptr = [0]
+        for c in chains:
+            ptr.append(ptr[-1] + len(c))
+        n = len(firsts)
+        stat = torch.zeros(2, n, dtype=torch.int32, device=dev)
+        us = torch.zeros(n, dtype=torch.uint8, device=dev)
+        cp, f, c = (C.c_int32 * len(ptr))(*ptr), (C.c_int32 * n)(*firsts), (C.c_int32 * n)(*counts)
+        P = lambda t: C.c_void_p(t.data_ptr())
+        stream = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        self.capi.check(self.lib.b3d_fit_window_chains_dev(self.model.h, C.byref(self.opts[stage]), len(chains), cp, f, c, P(st["kps"]), P(st["nkp"]),
+                                                           P(st["R0"]), P(st["poses"]), P(st["W"]), P(st["r"]), P(st["p"]), P(us), P(stat[0]), P(stat[1]),
+                                                           stream), "b3d_fit_window_chains_dev")
+        self.batches.append((stage, firsts, counts, stat, us))
+
     def report(self):
         return [(s, f, c, int(stat[0]), int(stat[1]), bool(us[0])) for (s, f, c, stat, us) in self.solves]
 
@@ -323,15 +348,23 @@ def fit_sequence_multishard(solver, st, plan: WindowPlan, rank=None, world=None,
     priv = {k: (torch.cat([st[k][lo[g]:hi[g]] for g in mine]) if mine else st[k][:0].clone()) for k in STATE_KEYS}
     # ---- pass 1: wave i = the i-th window of every local shard ----
     nwin = max([plan.cuts[g + 1] - plan.cuts[g] for g in mine], default=0)
-    for i in range(nwin):
-        firsts, counts = [], []
+    if hasattr(solver, "solve_chains") and plan.wsize < 48:
+        # one launch: every local shard is a chain of windows solved back to back on the device (cluster = shard)
+        chains = []
         for g in mine:
-            k = plan.cuts[g] + i
-            if k < plan.cuts[g + 1]:
-                s, e = plan.window(k)
-                firsts.append(base[g] + s - lo[g]); counts.append(e - s)
-        _solve_batch(solver, 2, firsts, counts, priv)
-        _writeback_batch(solver, firsts, counts, priv)
+            wins = [plan.window(k) for k in range(plan.cuts[g], plan.cuts[g + 1])]
+            chains.append([(base[g] + s - lo[g], e - s) for (s, e) in wins])
+        solver.solve_chains(2, chains, priv)
+    else:
+        for i in range(nwin):
+            firsts, counts = [], []
+            for g in mine:
+                k = plan.cuts[g] + i
+                if k < plan.cuts[g + 1]:
+                    s, e = plan.window(k)
+                    firsts.append(base[g] + s - lo[g]); counts.append(e - s)
+            _solve_batch(solver, 2, firsts, counts, priv)
+            _writeback_batch(solver, firsts, counts, priv)
     # ---- halo hand-off ----
     halo = {}                                  # shard -> (OVERLAP x 85) rows refined by its left neighbour
     for g in mine:
@@ -399,7 +432,7 @@ def fit_sequence_multishard(solver, st, plan: WindowPlan, rank=None, world=None,
     return st
 
 
-def bench_c5(api, gm, base, so, seq, dev, rank, world, shards_per_rank=32):
+def bench_c5(api, gm, base, so, seq, dev, rank, world, shards_per_rank=74):
     """BASELINE configs[4] for bench.py: one long 3dba_multi sequence, windows sharded over the ranks (shards_per_rank chains per GPU
     solved as batches), OVERLAP x 85 doubles per rank edge over NCCL.  Every rank calls this; returns the JSON fragment on rank 0."""
     import time

@@ -318,6 +318,15 @@ int b3d_fit_window(const b3d_model* m, const b3d_fit_opts* opts, int32_t F, cons
 int b3d_fit_windows_dev(const b3d_model* m, const b3d_fit_opts* opts, int32_t nprob, const int32_t* first, const int32_t* count,
                         const b3d_kp* kps, const int32_t* nkp, const double* R0, double* poses, double* W, uint8_t* usable,
                         b3d_iter_record* trace, int32_t trace_stride, int32_t* niters, int32_t* term, void* stream);
+/* Chains of windows: chain c = problems [chain_ptr[c], chain_ptr[c + 1]) of the first / count tables, solved ONE AFTER THE OTHER on
+ * the device by one thread-block cluster per chain — what `3dba_multi` does per sequence in its window loop
+ * (src/main_multi_frame.cpp:165-201: OptimizeMultiFrame on the window, then the write-back of :154-172 before the next window, which
+ * overlaps it) — with the write-back of each window's frames into R0 (rotated in place), r (F x 24 x 9) and p (F x 3) done between the
+ * solves.  Different chains run side by side and must not share frames (the sharded schedule gives every chain private rows).  All
+ * pointers but chain_ptr / first / count are device pointers; windows must be shorter than 48 frames. */
+int b3d_fit_window_chains_dev(const b3d_model* m, const b3d_fit_opts* opts, int32_t nchain, const int32_t* chain_ptr, const int32_t* first,
+                              const int32_t* count, const b3d_kp* kps, const int32_t* nkp, double* R0, double* poses, double* W, double* r,
+                              double* p, uint8_t* usable, int32_t* niters, int32_t* term, void* stream);
 
 /* The anchor / sliding-window schedule of 3dba_multi (src/main_multi_frame.cpp:109-201; argv defaults :29-36). */
 typedef struct b3d_seq_opts {

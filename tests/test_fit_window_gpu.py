@@ -237,3 +237,24 @@ def test_grid_chain_kernel_equals_cluster_kernel(api, synth, F):
     assert np.max(np.abs(ca - cb) / ca) < 1e-10
     assert np.array_equal(a["trace"]["flags"][:n], b["trace"]["flags"][:n])
     assert np.max(np.abs(a["poses"] - b["poses"])) < 1e-7 and np.max(np.abs(a["w"] - b["w"])) < 1e-9
+
+
+@pytest.mark.parametrize("shards", [1, 3])
+def test_chain_mode_equals_wave_mode(api, gmodel, synth, model_np, shards):
+    """Stage 2 runs as ONE launch in which every shard's windows are solved back to back by one cluster, the write-back between two
+    windows done on the device (chain mode of fit_window_kernel); the round-1 schedule — one launch per wave of windows plus
+    write-back launches — is still there behind a debug switch.  Same arithmetic, so the results are bit-identical."""
+    n = 173
+    seq = synth.make_sequence(model_np, n, 12)
+    cam = (synth.FX, synth.FY, synth.CX, synth.CY)
+    so = api.seq_opts(it1=20, it2=15, num_shards=shards, beta_pose=20.0, beta_shape=30.0)
+    lib = api.lib()
+    try:
+        lib.b3d_debug_seq_waves(1)
+        a = api.fit_sequences(gmodel, api.fit_opts(cam=cam), so, seq["kps"], seq["nkp"], seq["poses"], seq["R0"], seq["W"])
+    finally:
+        lib.b3d_debug_seq_waves(0)
+    b = api.fit_sequences(gmodel, api.fit_opts(cam=cam), so, seq["kps"], seq["nkp"], seq["poses"], seq["R0"], seq["W"])
+    for k in ("poses", "R0", "W", "r", "p", "solve_iters", "solve_term"):
+        assert np.array_equal(a[k], b[k]), k
+    assert a["nfail"] == b["nfail"]

@@ -13,7 +13,7 @@ if world > 1:
     dist.init_process_group("nccl", device_id=dev)
 synth, api, D = pkg("synth"), pkg("api"), pkg("dist")
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 20000
-spr = int(sys.argv[2]) if len(sys.argv) > 2 else 32
+spr = int(sys.argv[2]) if len(sys.argv) > 2 else 74
 model_np = synth.make_model()
 seq = synth.make_sequence_fast(model_np, n, 77)
 gm = api.AvatarModel(model_np)
