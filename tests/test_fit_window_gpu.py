@@ -258,3 +258,29 @@ def test_chain_mode_equals_wave_mode(api, gmodel, synth, model_np, shards):
     for k in ("poses", "R0", "W", "r", "p", "solve_iters", "solve_term"):
         assert np.array_equal(a[k], b[k]), k
     assert a["nfail"] == b["nfail"]
+
+
+def test_window_chains_entry_point_validates_its_tables(api, gmodel, synth, model_np):
+    """b3d_fit_window_chains_dev: malformed chain tables and windows that belong to the grid kernel are rejected with B3D_EINVAL
+    before anything is launched."""
+    import ctypes as C
+    import torch
+    lib, capi = api.lib(), api.capi
+    dev = torch.device("cuda", 0)
+    n = 60
+    z = lambda *s: torch.zeros(*s, dtype=torch.float64, device=dev)
+    kps = torch.zeros(n * capi.MAXKP * 24, dtype=torch.uint8, device=dev)
+    nkp = torch.zeros(n, dtype=torch.int32, device=dev)
+    R0, poses, W, r, p = z(n, 9), z(n, 76), z(n, 10), z(n, 216), z(n, 3)
+    o = api.fit_opts(cam=(synth.FX, synth.FY, synth.CX, synth.CY), mode=1, max_iters=3)
+    P = lambda t: C.c_void_p(t.data_ptr())
+
+    def call(ptr, first, count):
+        a = lambda v: (C.c_int32 * len(v))(*v)
+        return lib.b3d_fit_window_chains_dev(gmodel.h, C.byref(o), len(ptr) - 1, a(ptr), a(first), a(count), P(kps), P(nkp), P(R0), P(poses), P(W), P(r), P(p),
+                                             None, None, None, None)
+    assert call([1, 2], [0, 10], [10, 10]) == 1 and "chain_ptr" in capi.last_error()
+    assert call([0, 2, 1], [0, 10], [10, 10]) == 1
+    assert call([0, 1], [0], [0]) == 1
+    assert call([0, 1], [0], [50]) == 1 and "b3d_fit_windows_dev" in capi.last_error()
+    assert call([0, 0], [], []) == 0          # an empty chain is nothing to do
