@@ -326,20 +326,25 @@ __device__ bool chain_solve(const FitConst* __restrict__ C, int F, double radius
             blk_store<T>(CW.EL + (size_t)f * BB, B.E1);
             if (has_c) blk_store<T>(CW.ER + (size_t)f * BB, B.E2);
             rhs_store<T>(CW.Rr + (size_t)f * RR, B.R);
-            if (has_c && tid < 361) {     // new coupling of the survivors: E_ac = -U_a^T U_c (block (a, c)) and its transpose (block (c, a))
-                const int ti = tid / 19, tj = tid % 19;
+            if (has_c) {     // new coupling of the survivors: E_ac = -U_a^T U_c (block (a, c)) and its transpose (block (c, a))
                 double acc[4][4];
-                blk_tile_xty(B.E1, B.E2, ti, tj, acc);
+                const int ti = tid / 19, tj = tid % 19;
+                if (tid < 361) blk_tile_xty(B.E1, B.E2, ti, tj, acc);
+                __syncthreads();                                   // the factor has left B.A: it becomes the staging tile of E_ac
+                if (tid < 361) {
+#pragma unroll
+                    for (int x = 0; x < 4; ++x) {
+                        *reinterpret_cast<double2*>(&B.A[4 * ti + x][4 * tj]) = make_double2(-acc[x][0], -acc[x][1]);
+                        *reinterpret_cast<double2*>(&B.A[4 * ti + x][4 * tj + 2]) = make_double2(-acc[x][2], -acc[x][3]);
+                    }
+                }
+                __syncthreads();
                 double* Eac = CW.ER + (size_t)a * BB;
                 double* Eca = CW.EL + (size_t)c * BB;
-#pragma unroll
-                for (int x = 0; x < 4; ++x)
-#pragma unroll
-                    for (int y = 0; y < 4; ++y) {
-                        const int i = 4 * ti + x, j = 4 * tj + y;
-                        Eac[i * NB + j] = -acc[x][y];
-                        Eca[j * NB + i] = -acc[x][y];
-                    }
+                for (int idx = tid; idx < NB * NB; idx += T) {     // both orientations as coalesced rows
+                    Eac[idx] = B.A[idx / NB][idx % NB];
+                    Eca[idx] = B.A[idx % NB][idx / NB];
+                }
             }
             ct.mark(9);
         }
@@ -387,19 +392,18 @@ __device__ bool chain_solve(const FitConst* __restrict__ C, int F, double radius
                 }
             }
             double* Aw = CW.Aw + (size_t)a * BB;
+            __syncthreads();                                       // B.E1 has been read by every tile: B.A (unused in this phase) stages the update
             if (has_tile) {
 #pragma unroll
                 for (int x = 0; x < 4; ++x)
 #pragma unroll
                     for (int y = 0; y < 4; ++y) {
-                        const int i = 4 * ti + x, j = 4 * tj + y;
-                        if (ti != tj || j <= i) {
-                            const double v = Aw[i * NB + j] - upd[x][y];
-                            Aw[i * NB + j] = v;
-                            if (i != j) Aw[j * NB + i] = v;
-                        }
+                        B.A[4 * ti + x][4 * tj + y] = upd[x][y];
+                        B.A[4 * tj + y][4 * ti + x] = upd[x][y];  // (diagonal tiles write their entries twice with the same value up to symmetry of U^T U)
                     }
             }
+            __syncthreads();
+            for (int idx = tid; idx < NB * NB; idx += T) Aw[idx] -= B.A[idx / NB][idx % NB];
             double* Rr = CW.Rr + (size_t)a * RR;
             for (int q = 0; q < 2; ++q) {
                 const int idx = tid + q * T;
