@@ -1031,6 +1031,27 @@ int b3d_debug_phase_timing(int on) {
     cudaMemcpyToSymbol(g_phase_cycles, z, sizeof(z));
     return cudaMemcpyToSymbol(g_phase_on, &on, sizeof(int)) == cudaSuccess ? 0 : 2;
 }
+// debug / test hook: ceres' MinimizeInterpolatingPolynomial as the line search runs it (ls_poly.cuh), one warp per problem.
+// in: n x 12 doubles (number of samples 2 | 3, then x, value, gradient of up to 3 samples, x_min, x_max); out: n step sizes
+__global__ void poly_min_kernel(int n, const double* __restrict__ in, double* __restrict__ out) {
+    const int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (w >= n) return;
+    const double* q = in + (size_t)w * 12;
+    LsSample s[3];
+    for (int i = 0; i < 3; ++i) { s[i].x = q[1 + 3 * i]; s[i].value = q[2 + 3 * i]; s[i].gradient = q[3 + 3 * i]; s[i].valid = true; }
+    const double r = minimize_interpolating_polynomial(s, (int)q[0], q[10], q[11]);
+    if ((threadIdx.x & 31) == 0) out[w] = r;
+}
+int b3d_debug_poly_min(int n, const double* in_host, double* out_host) {
+    double *din = nullptr, *dout = nullptr;
+    if (cudaMalloc(&din, sizeof(double) * 12 * (size_t)n) != cudaSuccess) return 2;
+    if (cudaMalloc(&dout, sizeof(double) * (size_t)n) != cudaSuccess) { cudaFree(din); return 2; }
+    cudaMemcpy(din, in_host, sizeof(double) * 12 * (size_t)n, cudaMemcpyHostToDevice);
+    poly_min_kernel<<<(n + 3) / 4, 128>>>(n, din, dout);
+    const cudaError_t e = cudaMemcpy(out_host, dout, sizeof(double) * (size_t)n, cudaMemcpyDeviceToHost);
+    cudaFree(din); cudaFree(dout);
+    return e == cudaSuccess ? 0 : 2;
+}
 int b3d_debug_poly_read(unsigned long long* out8) { return cudaMemcpyFromSymbol(out8, g_poly_cyc, 8 * sizeof(unsigned long long)) == cudaSuccess ? 0 : 2; }
 int b3d_debug_block_lsparts_read(long long* parts4096) { return cudaMemcpyFromSymbol(parts4096, g_block_lsparts, 4096 * sizeof(long long)) == cudaSuccess ? 0 : 2; }
 int b3d_debug_block_ls_read(long long* cyc1024, int* trials1024) {

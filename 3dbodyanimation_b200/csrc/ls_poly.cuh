@@ -35,29 +35,26 @@ __device__ __forceinline__ double poly_eval_fixed(const double (&p)[NC], double 
 // first bracket), then one secant step inside the last bracket.  No divisions in the loop, no dependence on how well Newton's method
 // likes the polynomial (safeguarded Newton needed 18 iterations of ~450 cycles on these interpolants).  All lanes call it with the same arguments and get the same result.
 template <int NC>
-__device__ __forceinline__ double poly_refine_root(const double (&p)[NC], double a, double b, double fa) {
+__device__ __noinline__ double poly_refine_root(const double (&p)[NC], double a, double b, double fa) {
     const int lane = threadIdx.x & 31;
     const bool neg_a = fa < 0.0;
-    double fb_lo = fa, fb_hi = 0.0;     // values at the bracket ends, for the final secant step (fb_hi filled in the first round)
-    bool have_hi = false;
-#pragma unroll 1
-    for (int round = 0; round < 6; ++round) {      // 33^-6 = 7.7e-10 of the first bracket; the secant step below squares that
+    double f_lo = fa, f_hi = poly_eval_fixed<NC>(p, b);       // values at the bracket ends (kept for the final secant step)
+    for (int round = 0; round < 6; ++round) {                  // 33^-6 = 7.7e-10 of the first bracket; the secant step below squares that
         const double h = (b - a) * (1.0 / 33.0);
-        const double x = a + h * (double)(lane + 1);
-        const double f = poly_eval_fixed<NC>(p, x);
-        // lanes whose point is already on b's side of the root (or on it)
+        const double f = poly_eval_fixed<NC>(p, a + h * (double)(lane + 1));
+        // lanes whose point is already on b's side of the root (or on it); every lane then knows between which two points the sign
+        // changes and evaluates the new end points itself (no shuffles: the bracket stays identical in all lanes by construction)
         const unsigned m = __ballot_sync(0xffffffffu, (f < 0.0) != neg_a || f == 0.0);
-        const int first = m ? __ffs(m) - 1 : 32;          // the sign changes between point first - 1 and point first (point -1 = a, point 32 = b)
-        const double xl = __shfl_sync(0xffffffffu, x, first > 0 ? first - 1 : 0), fl = __shfl_sync(0xffffffffu, f, first > 0 ? first - 1 : 0);
-        const double xh = __shfl_sync(0xffffffffu, x, first < 32 ? first : 31), fh = __shfl_sync(0xffffffffu, f, first < 32 ? first : 31);
-        if (first > 0) { a = xl; fb_lo = fl; }
-        if (first < 32) { b = xh; fb_hi = fh; have_hi = true; }
-        if (have_hi && fb_hi == 0.0) return b;
-        if (!(b - a > 4.5e-16 * fmax(fabs(a), fabs(b)))) break;
+        const int first = m ? __ffs(m) - 1 : 32;              // between point first - 1 and point first (point -1 = a, point 32 = b)
+        const double a0 = a;
+        if (first > 0) { a = a0 + h * (double)first; f_lo = poly_eval_fixed<NC>(p, a); }
+        if (first < 32) { b = a0 + h * (double)(first + 1); f_hi = poly_eval_fixed<NC>(p, b); }
+        if (f_hi == 0.0) return b;
+        if (f_lo == 0.0) return a;
+        if (!(fabs(b - a) > 4.5e-16 * fmax(fabs(a), fabs(b)))) break;
     }
-    if (!have_hi) return 0.5 * (a + b);
     // secant step inside the last bracket (p is monotone on it)
-    const double t = fb_lo / (fb_lo - fb_hi);
+    const double t = f_lo / (f_lo - f_hi);
     const double x = a + (b - a) * t;
     return (x >= fmin(a, b) && x <= fmax(a, b)) ? x : 0.5 * (a + b);
 }
@@ -99,8 +96,11 @@ __device__ __forceinline__ int poly_level_roots(const double (&q)[NC], double lo
     return n;
 }
 // Real roots in [lo, hi] of the derivative of the interpolant: a quadratic (two samples; pin has 3 coefficients) or a quartic (three
-// samples; 5 coefficients).  Called by ALL lanes of one warp with the same arguments.
-__device__ int poly_real_roots_in(const double* pin, int nc, double lo, double hi, double* out) {
+// samples; 5 coefficients).  Called by ALL lanes of one warp with the same arguments.  __noinline__ on purpose, here and on
+// poly_refine_root: inlined into a caller whose control flow the compiler cannot prove warp-uniform, the __ballot_sync of the
+// refinement was observed to see a partial warp (the standalone test hook returned no roots); the call boundary keeps it convergent.
+// tests/test_fit_single_gpu.py::test_line_search_polynomial_minimiser_vs_numpy pins this function against numpy.
+__device__ __noinline__ int poly_real_roots_in(const double* pin, int nc, double lo, double hi, double* out) {
     if (!(lo <= hi)) return 0;
     if (nc == 3) return quad_roots_in(pin[0], pin[1], pin[2], lo, hi, out);
     if (nc != 5) return 0;

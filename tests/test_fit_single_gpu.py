@@ -275,3 +275,53 @@ def test_gmm_component_screening_is_bit_identical(api, gmodel, ggmm, synth, mode
         assert np.array_equal(got[k], ref[k]), k
     assert got["trace"].tobytes() == ref["trace"].tobytes()
     assert len(set(int(a) for f in range(96) for a in ref["trace"][f]["aux"][:ref["niters"][f]])) >= 2      # more than one component is active
+
+
+def test_line_search_polynomial_minimiser_vs_numpy(api):
+    """ceres::MinimizeInterpolatingPolynomial as the Armijo search runs it on the device (ls_poly.cuh: Hermite interpolant through two or
+    three samples with gradients, real roots of its derivative inside [x_min, x_max] by exact isolation + whole-warp refinement) against
+    numpy on random samples: the chosen step must give the interpolant's minimum over the candidates Ceres tries (mid point, end
+    points, real parts of ALL roots of the derivative that fall inside the interval) to 1e-6 of the polynomial's range, and the step
+    itself must agree to 1e-9 wherever that minimum is not a near-tie."""
+    import ctypes as C
+    rng = np.random.default_rng(5)
+    n = 4000
+    rows = np.zeros((n, 12))
+    for i in range(n):
+        ns = 2 if i % 3 == 0 else 3
+        xs = np.sort(rng.uniform(0.0, 1.0, 3)) * rng.choice([1.0, 1e-3, 10.0])
+        xs[0] = 0.0 if i % 2 == 0 else xs[0]
+        xs += np.arange(3) * 1e-3 * max(xs[-1], 1e-3)           # distinct nodes
+        vals = rng.normal(0, 1, 3) * rng.choice([1.0, 1e3, 1e-3])
+        grads = rng.normal(0, 1, 3) * np.abs(vals).max() / max(xs[-1] - xs[0], 1e-6)
+        lo, hi = sorted(rng.uniform(xs[0], xs[-1] * 1.2 + 1e-6, 2))
+        rows[i, 0] = ns
+        for k in range(3):
+            rows[i, 1 + 3 * k:4 + 3 * k] = (xs[k], vals[k], grads[k])
+        rows[i, 10], rows[i, 11] = lo, hi + 1e-9
+    out = np.zeros(n)
+    assert api.lib().b3d_debug_poly_min(n, rows.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p)) == 0
+    worst_val, nclose = 0.0, 0
+    for i in range(n):
+        ns = int(rows[i, 0])
+        xs, vals, grads = rows[i, 1:1 + 3 * ns:3], rows[i, 2:2 + 3 * ns:3], rows[i, 3:3 + 3 * ns:3]
+        deg = 2 * ns - 1
+        A, b = [], []
+        for x, v, g in zip(xs, vals, grads):
+            A.append([x ** (deg - j) for j in range(deg + 1)]); b.append(v)
+            A.append([(deg - j) * x ** (deg - j - 1) if deg - j > 0 else 0.0 for j in range(deg + 1)]); b.append(g)
+        coef = np.linalg.solve(np.array(A), np.array(b))
+        lo, hi = rows[i, 10], rows[i, 11]
+        cand = [0.5 * (lo + hi), lo, hi] + [float(z.real) for z in np.roots(np.polyder(coef)) if lo <= z.real <= hi]
+        pv = np.polyval(coef, cand)
+        best = float(np.min(pv))
+        scale = max(float(np.ptp(np.polyval(coef, np.linspace(lo, hi, 64)))), 1e-300)
+        got_v = float(np.polyval(coef, out[i]))
+        assert lo <= out[i] <= hi
+        worst_val = max(worst_val, (got_v - best) / scale)
+        second = np.sort(pv)[1] if len(pv) > 1 else best
+        if (second - best) / scale > 1e-6:        # a clear winner: the step itself must match
+            nclose += 1
+            assert abs(out[i] - cand[int(np.argmin(pv))]) <= 1e-9 * max(abs(hi), 1e-300) + 1e-7 * (hi - lo), (i, out[i], cand, pv)
+    assert worst_val < 1e-6, worst_val      # (both sides evaluate an ill-conditioned monomial form: coefficients up to 1e15 at x ~ 1e-3)
+    assert nclose > n // 2
