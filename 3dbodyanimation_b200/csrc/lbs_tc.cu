@@ -63,6 +63,7 @@ struct __align__(128) TcSmem {
     unsigned long long ch_full[2], ch_free[2];
     unsigned char recs[TC_NREC][TC_REC_BYTES];
     unsigned long long op_full[TC_NOP], op_free[TC_NOP], rec_full[TC_NREC], rec_free[TC_NREC], d_full[2], d_empty[2], g_full;
+    unsigned long long out_full[2][4], out_free[2][4];   // staging buffer x quadrant: skinning warps -> store warp and back
     uint32_t tmem_base;
 };
 static_assert(TC_M * TC_GROW * 4 <= (int)sizeof(float) * 2 * 4 * 32 * TC_SROW, "prologue staging of the transforms");
@@ -93,6 +94,14 @@ __device__ __forceinline__ void bar_wait(unsigned long long* bar, uint32_t parit
         "@p bra DONE_%=;\n\t"
         "bra WAIT_%=;\n\t"
         "DONE_%=:\n\t}" ::"r"(s_u32(bar)), "r"(parity), "r"(0x989680u) : "memory");
+}
+__device__ __forceinline__ bool bar_test(unsigned long long* bar, uint32_t parity) {   // one non-blocking look
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}" : "=r"(ok) : "r"(s_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
 }
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, unsigned long long* bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(s_u32(dst)), "l"(src),
@@ -151,6 +160,18 @@ __device__ __forceinline__ float to_tf32(float x) {
     asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
     return __uint_as_float(r);
 }
+// packed FP32: one FFMA2 issue slot does two lanes' worth of fused multiply-adds (tools/ffma_probe.cu: the FP32 rate at half the slots)
+__device__ __forceinline__ unsigned long long pack2(float lo, float hi) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(unsigned long long v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ unsigned long long fma2(unsigned long long a, unsigned long long b, unsigned long long c) {
+    unsigned long long d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
 __device__ __forceinline__ void named_bar(int id, int threads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory"); }
 
 // Optional timeline (debug hook b3d_debug_tc_trace): clock64 of CTA (0, 0)'s warps at five points of every MMA tile.
@@ -174,6 +195,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
         for (int i = 0; i < TC_NREC; ++i) { bar_init(&S.rec_full[i], 1); bar_init(&S.rec_free[i], TC_EPI_WARPS); }
         for (int i = 0; i < 2; ++i) { bar_init(&S.d_full[i], 1); bar_init(&S.d_empty[i], TC_EPI_WARPS); }
         bar_init(&S.g_full, 1);
+        for (int i = 0; i < 2; ++i)
+            for (int j = 0; j < 4; ++j) { bar_init(&S.out_full[i][j], TC_WPQ); bar_init(&S.out_free[i][j], 1); }
         for (int i = 0; i < 2; ++i) { bar_init(&S.ch_full[i], 1); bar_init(&S.ch_free[i], 1); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -211,9 +234,16 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
     if (h < TC_WPQ) {
         constexpr int CPW = NJ * 12 / TC_WPQ;   // columns per warp
         bar_wait(&S.g_full, 0);
+        // per joint the column-major [R | t] is re-ordered to [r00 r10 | r01 r11 | r02 r12 | t0 t1 | r20 r21 r22 t2]: the x / y rows
+        // come back from tcgen05.ld as aligned register pairs for the packed FMAs of the slot loop
         const float4* src = reinterpret_cast<const float4*>(gst + (32 * q + lane) * TC_GROW + CPW * h);
 #pragma unroll
-        for (int c = 0; c < CPW / 4; ++c) tmem_st4(tm_row + CPW * h + 4 * c, src[c]);
+        for (int j = 0; j < CPW / 12; ++j) {
+            const float4 a = src[3 * j], b = src[3 * j + 1], c = src[3 * j + 2];
+            tmem_st4(tm_row + CPW * h + 12 * j, make_float4(a.x, a.y, a.w, b.x));
+            tmem_st4(tm_row + CPW * h + 12 * j + 4, make_float4(b.z, b.w, c.y, c.z));
+            tmem_st4(tm_row + CPW * h + 12 * j + 8, make_float4(a.z, b.y, c.x, c.w));
+        }
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // staging rows were read through the generic proxy
@@ -296,6 +326,40 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
             for (int m = 0; m < nM; ++m) issue_tma(m);
         if (warp == TC_EPI_WARPS + 1 && lane == 0)
             for (int m = 0; m < nM; ++m) issue_mma(m);
+        if (warp >= TC_EPI_WARPS + 2 && bulk_rows) {
+            // store warps (18: quadrants 0 and 2, 19: quadrants 1 and 3), lane = body of the quadrant.  Issuing a bulk store blocks
+            // the issuing warp until the SM's store path takes it (a quadrant's 24 KB: ~1,300 cycles, all four skinning warps of a
+            // scheduler at once when they issued their own rows) - here it blocks a warp that has nothing else to do.
+            const int nfull = min(t_end, V / TC_T) - t_begin;   // complete sort tiles (the mesh's last, partial one leaves by plain stores)
+            const int q0 = warp - (TC_EPI_WARPS + 2);
+            int sent[2] = {0, 0};
+            while (sent[0] < nfull || sent[1] < nfull) {
+#pragma unroll
+                for (int i = 0; i < 2; ++i) {
+                    const int st = sent[i], qq = q0 + 2 * i, buf = st & 1;
+                    if (st >= nfull) continue;
+                    if (!__all_sync(0xffffffffu, bar_test(&S.out_full[buf][qq], (uint32_t)((st >> 1) & 1)))) continue;
+                    const int body = b0 + 32 * qq + lane;
+                    if (body < B) {
+                        const float* sp = &S.out[buf][qq][lane * TC_SROW];
+                        float* dp = cloud + ((size_t)body * V + (size_t)(t_begin + st) * TC_T) * 3;
+                        if ((reinterpret_cast<uintptr_t>(dp) & 15) == 0) {
+                            bulk_s2g(dp, sp, 3 * TC_T * 4);
+                        } else {   // 8 mod 16, as is the shared row: head and tail pairs by hand, the 16 B aligned middle in bulk
+                            *reinterpret_cast<float2*>(dp) = *reinterpret_cast<const float2*>(sp);
+                            *reinterpret_cast<float2*>(dp + 3 * TC_T - 2) = *reinterpret_cast<const float2*>(sp + 3 * TC_T - 2);
+                            bulk_s2g(dp + 2, sp + 2, 3 * TC_T * 4 - 16);
+                        }
+                    }
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // the rows have left shared memory
+                    __syncwarp();
+                    if (lane == 0) bar_arrive(&S.out_free[buf][qq]);
+                    sent[i] = st + 1;
+                }
+            }
+            asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+        }
     } else {
         asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
         float g[4][12];
@@ -303,13 +367,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
         for (int k = 0; k < 4; ++k)
 #pragma unroll
             for (int e = 0; e < 12; ++e) g[k][e] = 0.f;
-        constexpr int RPW = 32 / TC_WPQ;   // staging rows a warp sends off
-        bool pending_store = false;        // this warp's lanes have a bulk-store group in flight
+        constexpr int RPW = 32 / TC_WPQ;   // staging rows a warp sends off (plain-store path)
         for (int m = 0; m < nM; ++m) {
             stamp(m, 0);
             const int sr = m % TC_NREC, ur = m / TC_NREC, buf = m & 1, r = m >> 1;
             const int st_tile = m / TC_MPT;                    // sort tile (local); its staging buffer alternates
-            float* const orow = &S.out[st_tile & 1][q][lane * TC_SROW];
+            const uint32_t orow_s = s_u32(&S.out[st_tile & 1][q][lane * TC_SROW]);
+            // the store warp has sent off the rows this staging buffer held two sort tiles ago
+            if (bulk_rows && m % TC_MPT == 0 && st_tile >= 2) bar_wait(&S.out_free[st_tile & 1][q], (uint32_t)(((st_tile >> 1) - 1) & 1));
             bar_wait(&S.rec_full[sr], (uint32_t)(ur & 1));     // slot records of this tile are in shared memory
             bar_wait(&S.d_full[buf], (uint32_t)(r & 1));       // and its accumulators are complete
             tc_fence_after();
@@ -344,51 +409,45 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
                     tc_wait_ld();
                 }
                 const float x = xyz[3 * s], y = xyz[3 * s + 1], z = xyz[3 * s + 2];
+                // x and y rows: one packed FMA chain per joint, sum_k w_k (R_k p + t_k) in that order; z row: the weighted row
+                // sum_k w_k [r20 r21 r22 t2]_k first (two packed FMAs per joint), then one dot product.  27 issue slots instead of 48.
+                const unsigned long long X = pack2(x, x), Y = pack2(y, y), Z = pack2(z, z);
                 const float wk[4] = {__uint_as_float(r0.x), __uint_as_float(r0.y), __uint_as_float(r0.z), __uint_as_float(r0.w)};
-                float ax = 0.f, ay = 0.f, az = 0.f;
+                unsigned long long axy = 0ull, mz01 = 0ull, mz23 = 0ull;
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {   // column-major 3 x 4 [R | t]
-                    const float tx = fmaf(g[k][0], x, fmaf(g[k][3], y, fmaf(g[k][6], z, g[k][9])));
-                    const float ty = fmaf(g[k][1], x, fmaf(g[k][4], y, fmaf(g[k][7], z, g[k][10])));
-                    const float tz = fmaf(g[k][2], x, fmaf(g[k][5], y, fmaf(g[k][8], z, g[k][11])));
-                    ax = fmaf(wk[k], tx, ax);
-                    ay = fmaf(wk[k], ty, ay);
-                    az = fmaf(wk[k], tz, az);
+                for (int k = 0; k < 4; ++k) {
+                    const unsigned long long W = pack2(wk[k], wk[k]);   // ptxas folds (v, v) pairs into the FFMA2 broadcast operand form
+                    const unsigned long long txy = fma2(pack2(g[k][0], g[k][1]), X, fma2(pack2(g[k][2], g[k][3]), Y, fma2(pack2(g[k][4], g[k][5]), Z, pack2(g[k][6], g[k][7]))));
+                    axy = fma2(W, txy, axy);
+                    mz01 = fma2(W, pack2(g[k][8], g[k][9]), mz01);
+                    mz23 = fma2(W, pack2(g[k][10], g[k][11]), mz23);
                 }
-                float* so = orow + r1.x;
-                so[0] = ax; so[1] = ay; so[2] = az;
+                float ax, ay, m0, m1, m2, m3;
+                unpack2(axy, ax, ay);
+                unpack2(mz01, m0, m1);
+                unpack2(mz23, m2, m3);
+                const float az = fmaf(m0, x, fmaf(m1, y, fmaf(m2, z, m3)));
+                // no "memory" clobber: the stores only have to stay ahead of the (volatile, clobbering) barrier arrive below
+                const uint32_t so = orow_s + (r1.x << 2);
+                asm volatile("st.shared.f32 [%0], %1;\n\tst.shared.f32 [%0+4], %2;\n\tst.shared.f32 [%0+8], %3;" ::"r"(so), "f"(ax), "f"(ay), "f"(az));
             }
             __syncwarp();
             if (lane == 0) bar_arrive(&S.rec_free[sr]);        // records read: the block may be refilled
             stamp(m, 3);
 
-            if (m % TC_MPT == TC_MPT - 1) {   // a sort tile is complete: rows of 3 x 64 consecutive floats per body leave asynchronously
-                // the rows this warp sent off one sort tile ago came from the OTHER buffer, which the quadrant writes next: their
-                // shared-memory reads must be over before anybody passes the barrier below
-                if (pending_store) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // this tile's staging stores -> visible to the bulk copies
-                named_bar(1 + q, 32 * TC_WPQ);
+            if (m % TC_MPT == TC_MPT - 1) {   // a sort tile is complete: rows of 3 x 64 consecutive floats per body
                 const int base_v = (t_begin + st_tile) * TC_T;
                 const int nv = min(TC_T, V - base_v);
-                const int row0 = RPW * h;                                   // this warp's rows of the quadrant
-                const int rows = min(RPW, B - (b0 + 32 * q + row0));
-                const float* srow = &S.out[st_tile & 1][q][row0 * TC_SROW];
-                float* drow = cloud + ((size_t)(b0 + 32 * q + row0) * V + base_v) * 3;
-                if (nv == TC_T && bulk_rows) {
-                    if (lane < rows) {
-                        const float* sp = srow + lane * TC_SROW;
-                        float* dp = drow + (size_t)lane * V * 3;
-                        if ((reinterpret_cast<uintptr_t>(dp) & 15) == 0) {
-                            bulk_s2g(dp, sp, 3 * TC_T * 4);
-                        } else {   // 8 mod 16, as is the shared row: head and tail pairs by hand, the 16 B aligned middle in bulk
-                            *reinterpret_cast<float2*>(dp) = *reinterpret_cast<const float2*>(sp);
-                            *reinterpret_cast<float2*>(dp + 3 * TC_T - 2) = *reinterpret_cast<const float2*>(sp + 3 * TC_T - 2);
-                            bulk_s2g(dp + 2, sp + 2, 3 * TC_T * 4 - 16);
-                        }
-                    }
-                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-                    pending_store = true;
-                } else {   // the mesh's last, partial sort tile: plain stores (the buffer is not reused afterwards)
+                if (nv == TC_T && bulk_rows) {   // hand the quadrant's rows to the store warp
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // this tile's staging stores -> visible to the bulk copies
+                    __syncwarp();
+                    if (lane == 0) bar_arrive(&S.out_full[st_tile & 1][q]);
+                } else {   // the mesh's last, partial sort tile (or a cloud the bulk stores cannot address): plain stores
+                    named_bar(1 + q, 32 * TC_WPQ);
+                    const int row0 = RPW * h;                                   // this warp's rows of the quadrant
+                    const int rows = min(RPW, B - (b0 + 32 * q + row0));
+                    const float* srow = &S.out[st_tile & 1][q][row0 * TC_SROW];
+                    float* drow = cloud + ((size_t)(b0 + 32 * q + row0) * V + base_v) * 3;
                     const int nfl = 3 * nv;
                     for (int row = 0; row < rows; ++row)
                         for (int e = lane; e < nfl; e += 32) drow[(size_t)row * V * 3 + e] = srow[row * TC_SROW + e];
@@ -396,7 +455,6 @@ __global__ void __launch_bounds__(TC_THREADS, 1) smpl_lbs_tc_kernel(const unsign
             }
             stamp(m, 4);
         }
-        if (pending_store) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     }
     tc_fence_before();
     __syncthreads();
