@@ -15,10 +15,13 @@
 //     carry over from sort tile to sort tile).  Per slot the warp reads one 32-byte record (weights, position, control word) as
 //     warp-uniform LDS.128.
 //   * results go to a [32 bodies][3 x 64 + 2] staging tile per TMEM lane quadrant, double buffered by sort tile; a finished tile
-//     leaves as TMA bulk row stores (768 B per body) while the next one is computed: HBM sees the cloud write only.
+//     leaves as TMA bulk row stores (768 B per body) while the next one is computed: HBM sees the cloud write only.  The stores
+//     are issued by two store warps (mbarrier hand-over out_full / out_free per quadrant and buffer): a bulk store holds its
+//     issuing warp until the SM's store path has taken it, and a skinning warp that waits there idles its scheduler.
 // Warps: 16 skinning warps (TMEM lane quadrant = warp & 3, slot sequence = warp >> 2: four warps per scheduler hide the FMA / LDS /
-// TMEM latencies) + a service warpgroup (warp 16 lane 0 issues the TMA copies, warp 17 lane 0 the MMAs) that hands its registers
-// to the skinning warps with setmaxnreg.  Measurements and the variants that lost: DESIGN.md sections 4 and 6.
+// TMEM latencies) + a service warpgroup (warp 16 lane 0 issues the TMA copies, warp 17 lane 0 the MMAs, warps 18 / 19 the row
+// stores of quadrants 0, 2 / 1, 3) that hands its registers to the skinning warps with setmaxnreg (which only redistributes what
+// the CTA's own warps release).  Measurements and the variants that lost: DESIGN.md sections 4, 6 and 8.
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
