@@ -144,6 +144,30 @@ __global__ void __launch_bounds__(256) icp_quat_kernel(int n, const double* __re
 // ---------------------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ float fma_(float a, float b, float c) { return fmaf(a, b, c); }
 __device__ __forceinline__ double fma_(double a, double b, double c) { return fma(a, b, c); }
+// packed FP32 (FFMA2): two lanes per issue slot; a (v, v) pair becomes the instruction's broadcast operand (no copy)
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpk2(f32x2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) {
+    f32x2 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ float hsum2(f32x2 v) { float lo, hi; unpk2(v, lo, hi); return lo + hi; }
 
 template <typename T> struct Vec4T;
 template <> struct Vec4T<float> { using type = float4; };
@@ -244,9 +268,14 @@ __global__ void __launch_bounds__(32 * NWARPS, 1) icp_accumulate_kernel(const T*
         sT[e * ICP_TPAD + bl] = (T)jointTrans[(size_t)min(b0 + bl, B - 1) * NJ * 12 + e];
     }
     for (int i = threadIdx.x; i < NJ * 6 * 32; i += 32 * NWARPS) sBin[i] = (T)0;
+    constexpr bool PACKED = sizeof(T) == 4;   // float32: packed FFMA2 arithmetic (the float64 instance keeps the scalar chains)
+    static_assert(NS % 2 == 0, "shape coefficients are processed in pairs");
     T ws[NS];
 #pragma unroll
     for (int s = 0; s < NS; ++s) ws[s] = (T)wshape[(size_t)b * NS + s];
+    f32x2 wsp[NS / 2], shp[NS / 2];
+#pragma unroll
+    for (int s = 0; s < NS / 2; ++s) { wsp[s] = pk2((float)ws[2 * s], (float)ws[2 * s + 1]); shp[s] = 0ull; }
     __syncthreads();
 
     T cost = 0, gp[3] = {0, 0, 0}, sh[NS];
@@ -284,7 +313,27 @@ __global__ void __launch_bounds__(32 * NWARPS, 1) icp_accumulate_kernel(const T*
             const V4 mu = reinterpret_cast<const V4*>(myTgt + (s * CH + i) * 128)[lane];
             // shape blend (AvatarOptimizer.cpp:263-264)
             T x[3];
-            {
+            if constexpr (PACKED) {
+                // words 4 .. 33 = shapedirs [coordinate][s]: ten consecutive words per coordinate, i.e. five aligned pairs;
+                // products pair by pair against (w_s, w_s+1), the two halves added at the end
+                const V4 t0 = r4[0];
+                const float tpl[3] = {t0.x, t0.y, t0.z};
+                f32x2 dp[15];
+#pragma unroll
+                for (int u = 1; u < 8; ++u) {
+                    const V4 t4 = r4[u];
+                    dp[2 * (u - 1)] = pk2(t4.x, t4.y);
+                    dp[2 * (u - 1) + 1] = pk2(t4.z, t4.w);
+                }
+                dp[14] = pk2(wj[0], wj[1]);
+#pragma unroll
+                for (int cc = 0; cc < 3; ++cc) {
+                    f32x2 a2 = mul2(dp[5 * cc], wsp[0]);
+#pragma unroll
+                    for (int q = 1; q < NS / 2; ++q) a2 = fma2(dp[5 * cc + q], wsp[q], a2);
+                    x[cc] = tpl[cc] + hsum2(a2);
+                }
+            } else {
                 T rv[32];
 #pragma unroll
                 for (int u = 0; u < 8; ++u) {
@@ -325,45 +374,104 @@ __global__ void __launch_bounds__(32 * NWARPS, 1) icp_accumulate_kernel(const T*
                     }
                 }
             }
-            T Pk[NW][3], P[3] = {0, 0, 0};
+            if constexpr (PACKED) {
+                // rows x / y of every 3-vector as one packed value, row z scalar; dot products against (wr_x, wr_y) pair-wise
+                // with the halves added once per vertex
+                const f32x2 X0 = pk2(x[0], x[0]), X1 = pk2(x[1], x[1]), X2 = pk2(x[2], x[2]);
+                f32x2 Pkxy[NW], Pxy = 0ull;
+                float Pkz[NW], Pz = 0.f;
 #pragma unroll
-            for (int k = 0; k < NW; ++k) {
-                const T wt = wj[2 + k];
-#pragma unroll
-                for (int r = 0; r < 3; ++r) {
-                    Pk[k][r] = fma_(G[k][r], x[0], fma_(G[k][3 + r], x[1], fma_(G[k][6 + r], x[2], G[k][9 + r])));
-                    P[r] = fma_(wt, Pk[k][r], P[r]);
+                for (int k = 0; k < NW; ++k) {
+                    const float wt = wj[2 + k];
+                    Pkxy[k] = fma2(pk2(G[k][0], G[k][1]), X0, fma2(pk2(G[k][3], G[k][4]), X1, fma2(pk2(G[k][6], G[k][7]), X2, pk2(G[k][9], G[k][10]))));
+                    Pkz[k] = fmaf(G[k][2], x[0], fmaf(G[k][5], x[1], fmaf(G[k][8], x[2], G[k][11])));
+                    Pxy = fma2(pk2(wt, wt), Pkxy[k], Pxy);
+                    Pz = fmaf(wt, Pkz[k], Pz);
                 }
-            }
-            // sum of the vertex's residuals and its cost share
-            const T n = mu.w;
-            const T e0 = P[0] - mu.x, e1 = P[1] - mu.y, e2 = P[2] - mu.z;
-            const T rs[3] = {n * e0, n * e1, n * e2};
-            cost = fma_(n, fma_(e0, e0, fma_(e1, e1, e2 * e2)), cost);
+                float Px, Py;
+                unpk2(Pxy, Px, Py);
+                const float n = mu.w;
+                const float e0 = Px - mu.x, e1 = Py - mu.y, e2 = Pz - mu.z;
+                const float rs0 = n * e0, rs1 = n * e1, rs2 = n * e2;
+                cost = fmaf(n, fmaf(e0, e0, fmaf(e1, e1, e2 * e2)), cost);
+                gp[0] += rs0; gp[1] += rs1; gp[2] += rs2;
+                const f32x2 RS = pk2(rs0, rs1);
+                f32x2 Y0 = 0ull, Y1 = 0ull, Y2 = 0ull;
+                float y0z = 0.f, y1z = 0.f, y2z = 0.f;
 #pragma unroll
-            for (int cc = 0; cc < 3; ++cc) gp[cc] += rs[cc];
-            // per-joint sums, and y = T^T rs = sum_k G_k^T (w_k rs) for the shape gradient
-            T y0 = 0, y1 = 0, y2 = 0;
-#pragma unroll
-            for (int k = 0; k < NW; ++k) {
-                const T wt = wj[2 + k];
-                {
-                    const T wr[3] = {wt * rs[0], wt * rs[1], wt * rs[2]};
-                    // straight FMA chains into the accumulators (one instruction per product)
-                    bin[k][0] = fma_(Pk[k][1], wr[2], fma_(-Pk[k][2], wr[1], bin[k][0]));
-                    bin[k][1] = fma_(Pk[k][2], wr[0], fma_(-Pk[k][0], wr[2], bin[k][1]));
-                    bin[k][2] = fma_(Pk[k][0], wr[1], fma_(-Pk[k][1], wr[0], bin[k][2]));
-                    bin[k][3] += wr[0]; bin[k][4] += wr[1]; bin[k][5] += wr[2];
-                    y0 = fma_(G[k][0], wr[0], fma_(G[k][1], wr[1], fma_(G[k][2], wr[2], y0)));
-                    y1 = fma_(G[k][3], wr[0], fma_(G[k][4], wr[1], fma_(G[k][5], wr[2], y1)));
-                    y2 = fma_(G[k][6], wr[0], fma_(G[k][7], wr[1], fma_(G[k][8], wr[2], y2)));
+                for (int k = 0; k < NW; ++k) {
+                    const float wt = wj[2 + k];
+                    const f32x2 WR = mul2(pk2(wt, wt), RS);
+                    const float wr2 = wt * rs2;
+                    float wr0, wr1, pk0, pk1;
+                    unpk2(WR, wr0, wr1);
+                    unpk2(Pkxy[k], pk0, pk1);
+                    bin[k][0] = fmaf(pk1, wr2, fmaf(-Pkz[k], wr1, bin[k][0]));
+                    bin[k][1] = fmaf(Pkz[k], wr0, fmaf(-pk0, wr2, bin[k][1]));
+                    bin[k][2] = fmaf(pk0, wr1, fmaf(-pk1, wr0, bin[k][2]));
+                    bin[k][3] += wr0; bin[k][4] += wr1; bin[k][5] += wr2;
+                    Y0 = fma2(pk2(G[k][0], G[k][1]), WR, Y0); y0z = fmaf(G[k][2], wr2, y0z);
+                    Y1 = fma2(pk2(G[k][3], G[k][4]), WR, Y1); y1z = fmaf(G[k][5], wr2, y1z);
+                    Y2 = fma2(pk2(G[k][6], G[k][7]), WR, Y2); y2z = fmaf(G[k][8], wr2, y2z);
                 }
-            }
-            // shape: D^T y, shapedirs read again from the tile
+                const float y0 = hsum2(Y0) + y0z, y1 = hsum2(Y1) + y1z, y2 = hsum2(Y2) + y2z;
+                // shape: D^T y, shapedirs read again from the tile as pairs (s, s + 1)
+                const f32x2 YB0 = pk2(y0, y0), YB1 = pk2(y1, y1), YB2 = pk2(y2, y2);
+                f32x2 dq[15];
 #pragma unroll
-            for (int q = 0; q < NS; ++q) sh[q] = fma_(r1[4 + q], y0, fma_(r1[4 + NS + q], y1, fma_(r1[4 + 2 * NS + q], y2, sh[q])));
-        }
+                for (int u = 1; u < 8; ++u) {
+                    const V4 t4 = r4[u];
+                    dq[2 * (u - 1)] = pk2(t4.x, t4.y);
+                    dq[2 * (u - 1) + 1] = pk2(t4.z, t4.w);
+                }
+                dq[14] = pk2(wj[0], wj[1]);
+#pragma unroll
+                for (int q = 0; q < NS / 2; ++q) shp[q] = fma2(dq[q], YB0, fma2(dq[5 + q], YB1, fma2(dq[10 + q], YB2, shp[q])));
+            } else {
+                T Pk[NW][3], P[3] = {0, 0, 0};
+    #pragma unroll
+                for (int k = 0; k < NW; ++k) {
+                    const T wt = wj[2 + k];
+    #pragma unroll
+                    for (int r = 0; r < 3; ++r) {
+                        Pk[k][r] = fma_(G[k][r], x[0], fma_(G[k][3 + r], x[1], fma_(G[k][6 + r], x[2], G[k][9 + r])));
+                        P[r] = fma_(wt, Pk[k][r], P[r]);
+                    }
+                }
+                // sum of the vertex's residuals and its cost share
+                const T n = mu.w;
+                const T e0 = P[0] - mu.x, e1 = P[1] - mu.y, e2 = P[2] - mu.z;
+                const T rs[3] = {n * e0, n * e1, n * e2};
+                cost = fma_(n, fma_(e0, e0, fma_(e1, e1, e2 * e2)), cost);
+    #pragma unroll
+                for (int cc = 0; cc < 3; ++cc) gp[cc] += rs[cc];
+                // per-joint sums, and y = T^T rs = sum_k G_k^T (w_k rs) for the shape gradient
+                T y0 = 0, y1 = 0, y2 = 0;
+    #pragma unroll
+                for (int k = 0; k < NW; ++k) {
+                    const T wt = wj[2 + k];
+                    {
+                        const T wr[3] = {wt * rs[0], wt * rs[1], wt * rs[2]};
+                        // straight FMA chains into the accumulators (one instruction per product)
+                        bin[k][0] = fma_(Pk[k][1], wr[2], fma_(-Pk[k][2], wr[1], bin[k][0]));
+                        bin[k][1] = fma_(Pk[k][2], wr[0], fma_(-Pk[k][0], wr[2], bin[k][1]));
+                        bin[k][2] = fma_(Pk[k][0], wr[1], fma_(-Pk[k][1], wr[0], bin[k][2]));
+                        bin[k][3] += wr[0]; bin[k][4] += wr[1]; bin[k][5] += wr[2];
+                        y0 = fma_(G[k][0], wr[0], fma_(G[k][1], wr[1], fma_(G[k][2], wr[2], y0)));
+                        y1 = fma_(G[k][3], wr[0], fma_(G[k][4], wr[1], fma_(G[k][5], wr[2], y1)));
+                        y2 = fma_(G[k][6], wr[0], fma_(G[k][7], wr[1], fma_(G[k][8], wr[2], y2)));
+                    }
+                }
+                // shape: D^T y, shapedirs read again from the tile
+    #pragma unroll
+                for (int q = 0; q < NS; ++q) sh[q] = fma_(r1[4 + q], y0, fma_(r1[4 + NS + q], y1, fma_(r1[4 + 2 * NS + q], y2, sh[q])));
+            }
+            }
         __syncwarp();
+    }
+    if constexpr (PACKED) {
+#pragma unroll
+        for (int q = 0; q < NS / 2; ++q) { float lo, hi; unpk2(shp[q], lo, hi); sh[2 * q] = (T)lo; sh[2 * q + 1] = (T)hi; }
     }
 #pragma unroll
     for (int k = 0; k < NW; ++k)
