@@ -48,10 +48,15 @@ def initial_root_rotation() -> np.ndarray:
     return ry @ np.diag([1.0, -1.0, 1.0])
 
 
-def make_model(seed: int = SEED, with_posedirs: bool = False) -> dict:
-    """Random-init model with SMPL's key names / shapes / dtypes (float32 arrays, uint32 kintree and faces)."""
+def make_model(seed: int = SEED, with_posedirs: bool = False, rig: str = "cyclic") -> dict:
+    """Random-init model with SMPL's key names / shapes / dtypes (float32 arrays, uint32 kintree and faces).
+    rig = "cyclic" (default, what every test, fixture and headline number uses): vertex v hangs on joint v mod 24, so any run of
+    consecutive vertices mixes all joints; rig = "blocks": every joint owns a contiguous range of vertex numbers, the way a mesh
+    that was modelled body part by body part is numbered (bench.py reports the skinning kernel on it as a second data point)."""
     rng = np.random.default_rng(seed)
-    cluster = np.arange(V) % J
+    if rig not in ("cyclic", "blocks"):
+        raise ValueError("rig must be 'cyclic' or 'blocks'")
+    cluster = np.arange(V) % J if rig == "cyclic" else (np.arange(V) * J) // V
     v_template = (REST_JOINTS[cluster] + rng.normal(0.0, 0.06, size=(V, 3))).astype(np.float32)
     j_reg = np.zeros((J, V), dtype=np.float32)
     for j in range(J):

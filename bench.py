@@ -330,6 +330,26 @@ def run_b200(args):
     torch.cuda.synchronize()
     lbs_ms = float(np.mean([a.elapsed_time(b) for a, b in levs]))
     clk = clocks.stop() if rank == 0 else None
+    # second data point, rank 0 only, outside every headline number: the same launch on a model whose joints own contiguous vertex
+    # ranges (synth.make_model(rig="blocks")) - the default synthetic model rigs vertex v to joint v mod 24, which makes the kernel
+    # change its register-resident joint transforms on every third vertex
+    lbs_blocks_ms = None
+    if rank == 0:
+        try:
+            gmb = api.AvatarModel(synth.make_model(rig="blocks"))
+            lbsb = lambda: capi.check(lib.b3d_smpl_forward_dev(gmb.h, FB, capi.F32, P(fw), P(fp_), P(fr_), P(fcloud), P(fjp), P(fjt), 0x100, C.c_void_p(st)), "lbs only, block-rigged model")
+            lbsb(); torch.cuda.synchronize()
+            bevs = []
+            for _ in range(10):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); lbsb(); e1.record()
+                bevs.append((e0, e1))
+            torch.cuda.synchronize()
+            lbs_blocks_ms = float(np.mean([a.elapsed_time(b) for a, b in bevs]))
+            del gmb
+        except Exception as e:   # informational only
+            lbs_blocks_ms = None
+            print(f"block-rigged skinning point skipped: {e}", file=sys.stderr)
 
     # max over ranks of the device-timed step, the e2e step and the forward
     tt = torch.tensor([step_ms, e2e_ms, fwd_ms, fit_ms, lbs_ms, e2e_cloud_ms], dtype=torch.float64, device=dev)
@@ -432,7 +452,11 @@ def run_b200(args):
                      "joints_kernel_ms": joints_ms,
                      "write_only_peak_gbs": 5400.0, "write_only_peak_source": "tools/store_probe.cu on this pool's B200 (profiles/r01_store_probe.log)",
                      "workload": f"forward sweep point B={FB} (BASELINE configs[3])", "whole_call_ms": fwd_ms,
-                     "verts_per_sec": world * FB * V / (fwd_ms * 1e-3), "peak_source": peak_src},
+                     "verts_per_sec": world * FB * V / (fwd_ms * 1e-3), "peak_source": peak_src,
+                     "block_rigged_model": None if lbs_blocks_ms is None else {
+                         "ms_per_kernel_launch": lbs_blocks_ms, "achieved": FB * LBS_BYTES_PER_BODY_F32 / (lbs_blocks_ms * 1e-3) / 1e9,
+                         "frac": FB * LBS_BYTES_PER_BODY_F32 / (lbs_blocks_ms * 1e-3) / 1e9 / hbm_peak,
+                         "note": "same launch on synth.make_model(rig='blocks'): joints own contiguous vertex ranges; informational, not the headline model"}},
         "roofline_lm": {"kernel": "fit_single_kernel<256>", "bound": "fp64 ALU / latency (not HBM: ~1.2 KB algorithmic I/O per frame)",
                         "ms_per_launch": fit_ms, "share_of_step": fit_ms / step_ms, "lm_iterations_per_step": cnt[0].item() / world,
                         "achieved_gflops": cnt[0].item() / world * FLOP_PER_FRAME_ITER_C2 / (fit_ms * 1e-3) / 1e9,
