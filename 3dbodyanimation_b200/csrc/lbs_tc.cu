@@ -543,12 +543,16 @@ int build_tc_tables(b3d_model& m, const std::vector<double>& vert, const std::ve
                     bool have = false;
                     for (int k = 0; k < 4; ++k) have = have || reg[k] == g0.j[a];
                     if (have) continue;
+                    // a set is taken if it is the FIRST one that holds a joint of this group (the weights below go to the first
+                    // match); a second copy of such a joint - the unused sets start out on joint 0 - is free like any other
                     int k_free = -1;
                     for (int k = 0; k < 4 && k_free < 0; ++k) {
                         bool needed = false;
                         for (int a2 = 0; a2 < g0.nj; ++a2) needed = needed || reg[k] == g0.j[a2];
+                        for (int k2 = 0; k2 < k; ++k2) needed = needed && reg[k2] != reg[k];
                         if (!needed) k_free = k;
                     }
+                    if (k_free < 0) return B3D_EINVAL;   // cannot happen: at most three of the four sets are first holders of other joints
                     reg[k_free] = g0.j[a];
                     flags |= 1u << k_free;
                 }

@@ -183,3 +183,21 @@ def test_forward_at_roofline_batch_vs_oracle_sample(api, gmodel, omodel, synth):
     assert err.max() < 1e-5, (err.max(), pick[int(np.argmax(err))])
     assert rel_err(jp.index_select(0, idx).cpu().numpy(), jp0) < 1e-5
     assert rel_err(jt.index_select(0, idx).cpu().numpy(), jt0) < 1e-5
+
+
+@pytest.mark.parametrize("lbs", ["tc", "sorted"])
+def test_forward_parity_block_rigged_model(api, orc, synth, lbs):
+    """A model whose joints own contiguous vertex ranges (synth.make_model(rig="blocks")): the sorted kernels then keep their
+    register-resident joint transforms over long runs of slots and across sort tiles - the opposite control flow of the default
+    model (vertex v on joint v mod 24), where they change on every third slot.  Same 1e-5 against the oracle; partial body group
+    and a batch big enough for several CTAs per body group."""
+    m = synth.make_model(rig="blocks")
+    gm, om = api.AvatarModel(m), orc.Model(m)
+    B = 640 + 45
+    inp = synth.make_forward_inputs(B, 77)
+    c, jp, jt = api.smpl_forward(gm, inp["w"], inp["p"], inp["r"], dtype=np.float32, lbs=lbs)
+    w, p, r = (np.asarray(inp[k], dtype=np.float32).astype(np.float64) for k in ("w", "p", "r"))
+    c0, jp0, jt0 = om.forward(w, p, r, nthreads=8)
+    worst = max(rel_err(c[b], c0[b]) for b in range(B))
+    assert worst < TOL_F32, (lbs, worst)
+    assert rel_err(jp, jp0) < TOL_F32 and rel_err(jt, jt0) < TOL_F32

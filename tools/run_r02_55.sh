@@ -1,0 +1,2 @@
+set -x
+timeout 200 python -m pytest tests/test_forward_gpu.py -x -q -m gpu --timeout 60 2>&1 | tail -4
