@@ -201,3 +201,34 @@ def test_forward_parity_block_rigged_model(api, orc, synth, lbs):
     worst = max(rel_err(c[b], c0[b]) for b in range(B))
     assert worst < TOL_F32, (lbs, worst)
     assert rel_err(jp, jp0) < TOL_F32 and rel_err(jt, jt0) < TOL_F32
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2, 3])
+def test_forward_tc_random_rigs(api, synth, seed):
+    """The host tables of the tensor-core kernel (slot order, register-set assignment) on rigs the two synthetic models do not
+    produce: runs of 1 - 300 consecutive vertices share a random set of 1 - 4 joints (joint 0, which the unused register sets start
+    on, over-represented), weights random.  Tensor-core kernel against the generic kernel on every (body, vertex)."""
+    rng = np.random.default_rng(1000 + seed)
+    m = dict(synth.make_model())
+    V, J = m["weights"].shape
+    wt = np.zeros((V, J), dtype=np.float32)
+    v = 0
+    while v < V:
+        run = int(rng.integers(1, 301)) if seed % 2 == 0 else int(rng.integers(1, 12))
+        nj = int(rng.integers(1, 5))
+        js = rng.choice(J, size=nj, replace=False)
+        if rng.random() < 0.3 and 0 not in js:
+            js[0] = 0
+        for u in range(v, min(V, v + run)):
+            ww = rng.dirichlet(np.ones(nj)).astype(np.float32)
+            ww = np.maximum(ww, np.float32(1e-3))
+            wt[u, js] = ww / ww.sum(dtype=np.float32)
+        v += run
+    m["weights"] = wt
+    gm = api.AvatarModel(m)
+    B = 256 + 19
+    inp = synth.make_forward_inputs(B, 500 + seed)
+    a, _, _ = api.smpl_forward(gm, inp["w"], inp["p"], inp["r"], dtype=np.float32, lbs="tc")
+    b, _, _ = api.smpl_forward(gm, inp["w"], inp["p"], inp["r"], dtype=np.float32, lbs="generic")
+    err = np.max(np.abs(a.astype(np.float64) - b), axis=(1, 2)) / np.max(np.abs(b), axis=(1, 2))
+    assert err.max() < 2e-6, (seed, err.max())
