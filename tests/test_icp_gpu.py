@@ -39,6 +39,18 @@ def test_icp_f32_matches_oracle(synth, orc, model_np, gpu_model):
     assert np.max(np.abs(got["grad"] - ref["grad"]) / scale) < 2e-4
 
 
+@pytest.mark.parametrize("dtype,ctol,gtol", [(np.float64, 1e-10, 1e-10), (np.float32, 1e-5, 2e-4)])
+def test_icp_block_rigged_model(synth, orc, dtype, ctol, gtol):
+    """The same parity on a model whose joints own contiguous vertex ranges (synth.make_model(rig="blocks")): a weight slot of the
+    accumulation kernel then keeps its joint for hundreds of vertices (long per-joint partial sums, few flushes)."""
+    m = synth.make_model(rig="blocks")
+    gm = pkg("api").AvatarModel(m)
+    ref, got, _, _ = _run(synth, orc, m, gm, 37, 35, dtype, nd=2500)
+    assert np.max(np.abs(got["cost"] - ref["cost"]) / ref["cost"]) < ctol
+    scale = np.max(np.abs(ref["grad"]), axis=1, keepdims=True)
+    assert np.max(np.abs(got["grad"] - ref["grad"]) / scale) < gtol
+
+
 def test_icp_pose_only_and_repeatable(synth, orc, model_np, gpu_model):
     ref, got, prob, x = _run(synth, orc, model_np, gpu_model, 3, 33, np.float64, nd=500, shape=False)
     assert np.all(got["grad"][:, 75:] == 0.0)
