@@ -233,3 +233,28 @@ def test_forward_tc_random_rigs(api, synth, seed):
         a, _, _ = api.smpl_forward(gm, inp["w"], inp["p"], inp["r"], dtype=np.float32, lbs=lbs)
         err = np.max(np.abs(a.astype(np.float64) - b), axis=(1, 2)) / np.max(np.abs(b), axis=(1, 2))
         assert err.max() < 2e-6, (seed, lbs, err.max())
+
+
+@pytest.mark.parametrize("maxnz", [6, 11])
+def test_forward_more_than_four_weights_per_vertex(api, orc, synth, maxnz):
+    """Rigs with up to 6 (weight table of 8) and up to 11 (table of 24) joints per vertex take the generic skinning kernel in both
+    precisions (the sorted / tensor-core tables exist for 4-weight models only); same tolerances against the oracle."""
+    rng = np.random.default_rng(40 + maxnz)
+    m = dict(synth.make_model())
+    V, J = m["weights"].shape
+    wt = np.zeros((V, J), dtype=np.float32)
+    for v in range(V):
+        nj = int(rng.integers(1, maxnz + 1))
+        js = rng.choice(J, size=nj, replace=False)
+        ww = rng.dirichlet(np.ones(nj)).astype(np.float32) + np.float32(1e-3)
+        wt[v, js] = ww / ww.sum(dtype=np.float32)
+    m["weights"] = wt
+    gm, om = api.AvatarModel(m), orc.Model(m)
+    B = 37
+    inp = synth.make_forward_inputs(B, 600 + maxnz)
+    for dtype, tol in ((np.float32, TOL_F32), (np.float64, TOL_F64)):
+        c, jp, jt = api.smpl_forward(gm, inp["w"], inp["p"], inp["r"], dtype=dtype)
+        w, p, r = (np.asarray(inp[k], dtype=dtype).astype(np.float64) for k in ("w", "p", "r"))
+        c0, jp0, jt0 = om.forward(w, p, r, nthreads=8)
+        assert max(rel_err(c[b], c0[b]) for b in range(B)) < tol, (maxnz, dtype)
+        assert rel_err(jp, jp0) < tol and rel_err(jt, jt0) < tol
