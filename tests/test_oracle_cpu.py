@@ -23,6 +23,23 @@ def test_forward_matches_numpy(orc, omodel, omodel_pd, model_np, synth):
     assert np.allclose(jp[:, 0], inp["p"], atol=1e-14)
 
 
+def test_forward_matches_numpy_on_the_block_rigged_model(orc, synth):
+    """synth.make_model(rig="blocks") (joints own contiguous vertex ranges; the GPU tests use it as a second rig): oracle against
+    the numpy restatement, and the rig really is block-wise with at most four joints per vertex."""
+    m = synth.make_model(rig="blocks")
+    nz = m["weights"] != 0
+    assert np.count_nonzero(np.any(nz[1:] != nz[:-1], axis=1)) == 23          # the joint set changes at the 23 block boundaries only
+    assert (np.count_nonzero(m["weights"], axis=1) <= 4).all() and np.allclose(m["weights"].sum(axis=1), 1.0, atol=1e-6)
+    with pytest.raises(ValueError):
+        synth.make_model(rig="spiral")
+    om = orc.Model(m)
+    inp = synth.make_forward_inputs(2, 9)
+    c, jp, jt = om.forward(inp["w"], inp["p"], inp["r"])
+    for b in range(2):
+        c0, jp0, jt0 = synth.forward_numpy(m, inp["w"][b], inp["p"][b], inp["r"][b])
+        assert rel_err(c[b], c0) < 1e-12 and rel_err(jp[b], jp0) < 1e-12 and rel_err(jt[b], jt0) < 1e-12
+
+
 def test_parents_and_constants(omodel, synth, model_np):
     k = omodel.constants()
     assert k["parent"].dtype == np.int32 and np.array_equal(k["parent"], synth.PARENT)
